@@ -1,0 +1,4 @@
+"""adaface_b200: B200-native (sm_100a) implementation of the AdaPrompt-conditioned U-Net transformer path of
+zyt334/AdaFace - SpatialTransformer / BasicTransformerBlock / CrossAttention, AdaEmbedding + AttentionalPooler,
+and the CFG combine + DDIM update - behind the reference's own module signatures.  See DESIGN.md."""
+__version__ = "0.1.0"

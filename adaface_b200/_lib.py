@@ -1,0 +1,94 @@
+"""ctypes binding of the C ABI declared in include/adaface_b200.h.
+
+The product path fails loudly when the CUDA library is missing or unusable: there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+_LIB = None
+
+
+class AdafaceB200Error(RuntimeError):
+    pass
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [("a", C.c_void_p), ("w", C.c_void_p), ("out", C.c_void_p), ("bias", C.c_void_p),
+                ("residual", C.c_void_p), ("m", C.c_int64), ("n", C.c_int64), ("k", C.c_int64),
+                ("lda", C.c_int64), ("ldw", C.c_int64), ("ldo", C.c_int64), ("ldr", C.c_int64),
+                ("epilogue", C.c_int), ("out_dtype", C.c_int), ("residual_dtype", C.c_int), ("hw", C.c_int)]
+
+
+class AttnArgs(C.Structure):
+    _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("out", C.c_void_p),
+                ("key_mask", C.c_void_p), ("batch", C.c_int), ("heads", C.c_int), ("head_dim", C.c_int),
+                ("q_len", C.c_int), ("kv_len", C.c_int), ("ldq", C.c_int64), ("ldk", C.c_int64),
+                ("ldv", C.c_int64), ("ldo", C.c_int64), ("scale", C.c_float)]
+
+
+EPI_STORE, EPI_GEGLU, EPI_NCHW = 0, 1, 2
+DT_BF16, DT_F32 = 0, 1
+
+_P, _I, _I64, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
+_SIGNATURES = {
+    "afb_last_error": (C.c_char_p, []),
+    "afb_abi_version": (_I, []),
+    "afb_launch_count": (_I64, []),
+    "afb_cfg_ddim_step": (_I, [_P, _P, _P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _F, _P]),
+    "afb_groupnorm_ws_floats": (_I64, [_I, _I, _I]),
+    "afb_groupnorm_tokens": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _F, _P]),
+    "afb_layernorm_bf16": (_I, [_P, _P, _P, _P, _I64, _I, _F, _P]),
+    "afb_gemm_bf16": (_I, [C.POINTER(GemmArgs), _P]),
+    "afb_attention_fwd": (_I, [C.POINTER(AttnArgs), _P]),
+    "afb_ada_pool_ws_floats": (_I64, [_I, _I, _I]),
+    "afb_ada_pool_prep": (_I, [_P, _I, _P, _P, _P, _P, _P, _I, _I, _P]),
+    "afb_ada_pool": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "afb_ada_head": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "afb_cast_f32_to_bf16": (_I, [_P, _P, _I64, _P]),
+    "afb_cast_bf16_to_f32": (_I, [_P, _P, _I64, _P]),
+}
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load():
+    """Loads (building first if sources changed and nvcc is present) the shared library."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not _build.is_current():
+        try:
+            _build.build()
+        except Exception as exc:  # no nvcc on this machine: accept a prebuilt library, else fail loudly
+            if not os.path.exists(path):
+                raise AdafaceB200Error(
+                    f"adaface_b200: CUDA library {path} is missing and could not be built ({exc}). "
+                    "There is no CPU fallback for this path.") from exc
+    try:
+        lib = C.CDLL(path)
+    except OSError as exc:
+        raise AdafaceB200Error(f"adaface_b200: cannot load {path}: {exc}. There is no CPU fallback.") from exc
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError here = ABI mismatch, fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    _LIB = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().afb_last_error()
+        raise AdafaceB200Error(f"{what or 'adaface_b200'} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+def launch_count() -> int:
+    return int(load().afb_launch_count())

@@ -1,0 +1,495 @@
+// K12/K13: AttentionalPooler + AdaEmbedding head (ldm/modules/embedding_manager.py:100-321, 539-910).
+//
+// K12 streams the layer's x and q ([B,N,C] bf16) exactly once (HBM-bound: 2*N*C*2 bytes per sample):
+//   prep    per sample: fg_q/bg_q = to_k(query embedding), LayerNorm, grouped 1x1 conv -> lora_q [2, C/8]
+//   main    one warp per token: LN(q), v = (x + LN(q))/sqrt(8), grouped 1x1 conv -> lora_k [C/8], the two
+//           per-head scores, head-average smoothing, then a flash-style online softmax over the joint
+//           (fg|bg) x token axis accumulating the fg- and bg-weighted sums of v; per-block partials
+//   combine per sample: exact merge of the block partials -> fg_out, bg_out [B, C] (+ softmax stats)
+//   probs   optional: attn_fg/attn_bg [B, 8, N] from the stored scores and the merged stats
+// K13 is one block per sample: LNCat, Linear -> K*r coefficients, basis combination, per-vector LN, bias.
+#include "common.cuh"
+#include "../../include/adaface_b200.h"
+
+namespace afb {
+void count_launch();
+namespace {
+
+constexpr int kHeads = 8;
+constexpr int kPoolThreads = 256;          // 8 warps
+constexpr int kMaxChunksPerLane = 5;       // C <= 1280: C/8 16-byte chunks spread over 32 lanes
+constexpr float kInvSqrt8 = 0.35355339059327373f;
+constexpr float kPoolMasked = -3.0e38f;
+
+__device__ __forceinline__ float block_sum_256(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.f;
+  if (warp == 0) {
+    t = warp_sum(t);
+    if (lane == 0) red[0] = t;
+  }
+  __syncthreads();
+  return red[0];
+}
+
+// ---- prep: lora_q[b][i][g*lg + o], i = 0 (fg), 1 (bg); includes the 8^-1/2 * 8^-1/2 factor (:235) -----------
+__global__ void __launch_bounds__(kPoolThreads) ada_pool_prep_kernel(
+    const float* __restrict__ to_k_w, const float* __restrict__ fg_q_emb, const float* __restrict__ bg_q_emb,
+    const float* __restrict__ w_fg, const float* __restrict__ w_bg, float* __restrict__ lora_q, int C, int ctx_dim) {
+  extern __shared__ float sh[];      // [2][C] projected queries
+  __shared__ float red[32];
+  const int b = blockIdx.x;
+  const int dg = C / kHeads, lg = dg / kHeads;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = 0; i < 2; ++i) {
+    const float* emb = (i == 0) ? fg_q_emb : bg_q_emb + static_cast<long long>(b) * ctx_dim;
+    for (int c = warp; c < C; c += (kPoolThreads >> 5)) {                       // to_k(emb): :193, :203
+      const float* wr = to_k_w + static_cast<long long>(c) * ctx_dim;
+      float a = 0.f;
+      for (int k = lane; k < ctx_dim; k += 32) a += wr[k] * emb[k];
+      a = warp_sum(a);
+      if (lane == 0) sh[i * C + c] = a;
+    }
+  }
+  __syncthreads();
+  for (int i = 0; i < 2; ++i) {                                                 // LayerNorm, no affine: :208-209
+    float s = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) s += sh[i * C + c];
+    const float mean = block_sum_256(s, red) / C;
+    float m2 = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const float d = sh[i * C + c] - mean;
+      m2 += d * d;
+    }
+    const float rstd = rsqrtf(block_sum_256(m2, red) / C + 1e-5f);
+    for (int c = threadIdx.x; c < C; c += blockDim.x) sh[i * C + c] = (sh[i * C + c] - mean) * rstd;
+    __syncthreads();
+  }
+  for (int idx = threadIdx.x; idx < 2 * dg; idx += blockDim.x) {                // grouped conv: :219, :222, :235
+    const int i = idx / dg, j = idx % dg;       // j = g*lg + o
+    const int g = j / lg;
+    const float* w = ((i == 0) ? w_fg : w_bg) + static_cast<long long>(j) * dg;
+    float a = 0.f;
+    for (int k = 0; k < dg; ++k) a += w[k] * sh[i * C + g * dg + k];
+    lora_q[(static_cast<long long>(b) * 2 + i) * dg + j] = a * kInvSqrt8 * kInvSqrt8;
+  }
+}
+
+// partial record per block: m[8], l[8], acc_fg[C], acc_bg[C]
+__host__ __device__ inline long long pool_partial_floats(int C) { return 16 + 2ll * C; }
+
+template <int kChunks>
+__global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ lora_q,
+    const float* __restrict__ w_k, const uint8_t* __restrict__ key_mask, float* __restrict__ scores,
+    float* __restrict__ partials, int N, int C, int tokens_per_block) {
+  extern __shared__ float sh[];
+  const int dg = C / kHeads, lg = dg / kHeads;          // per-head in / out channels of the grouped conv
+  const int nout = dg;                                  // = 8 * lg outputs
+  float* s_wt = sh;                                     // [8][dg][lg]  transposed lora_to_k weights
+  float* s_lq = s_wt + kHeads * dg * lg;                // [2][nout]
+  float* s_v = s_lq + 2 * nout;                         // [8 warps][C]
+  float* s_lk = s_v + 8 * C;                            // [8 warps][nout]
+  float* s_red = sh;                                    // [8 warps][16 + 2C], reuses the buffers above after the token loop
+
+  const int b = blockIdx.y, blk = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int idx = threadIdx.x; idx < kHeads * dg * lg; idx += blockDim.x) {
+    // w_k is [nout][dg] (row j = g*lg + o); store as [g][i][o]
+    const int j = idx / dg, i = idx % dg;
+    const int g = j / lg, o = j % lg;
+    s_wt[(g * dg + i) * lg + o] = w_k[idx];
+  }
+  for (int idx = threadIdx.x; idx < 2 * nout; idx += blockDim.x)
+    s_lq[idx] = lora_q[static_cast<long long>(b) * 2 * nout + idx];
+  __syncthreads();
+
+  const int nchunks = C >> 3;
+  const int chunks_per_group = dg >> 3;
+  float acc_fg[kChunks][8], acc_bg[kChunks][8];
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc_fg[i][j] = acc_bg[i][j] = 0.f;
+  // lanes 0..7 carry the running max / sum of head g = lane
+  float m_run = -INFINITY, l_run = 0.f;
+
+  float* my_v = s_v + warp * C;
+  float* my_lk = s_lk + warp * nout;
+  const int t_begin = blk * tokens_per_block;
+  const int t_end = min(N, t_begin + tokens_per_block);
+  for (int t = t_begin + warp; t < t_end; t += 8) {
+    const long long rowoff = (static_cast<long long>(b) * N + t) * C;
+    const uint4* xr = reinterpret_cast<const uint4*>(x + rowoff);
+    const uint4* qr = reinterpret_cast<const uint4*>(q + rowoff);
+    float xv[kChunks][8], qv[kChunks][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+        const uint4 ux = xr[ch], uq = qr[ch];
+        float2 a;
+        a = unpack_bf16x2(ux.x); xv[i][0] = a.x; xv[i][1] = a.y;
+        a = unpack_bf16x2(ux.y); xv[i][2] = a.x; xv[i][3] = a.y;
+        a = unpack_bf16x2(ux.z); xv[i][4] = a.x; xv[i][5] = a.y;
+        a = unpack_bf16x2(ux.w); xv[i][6] = a.x; xv[i][7] = a.y;
+        a = unpack_bf16x2(uq.x); qv[i][0] = a.x; qv[i][1] = a.y;
+        a = unpack_bf16x2(uq.y); qv[i][2] = a.x; qv[i][3] = a.y;
+        a = unpack_bf16x2(uq.z); qv[i][4] = a.x; qv[i][5] = a.y;
+        a = unpack_bf16x2(uq.w); qv[i][6] = a.x; qv[i][7] = a.y;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += qv[i][j];
+      }
+    }
+    const float mean = warp_sum(s) / C;                                        // k_ln = LN(q): :160
+    float m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i)
+      if (lane + 32 * i < nchunks)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = qv[i][j] - mean;
+          m2 += d * d;
+        }
+    const float rstd = rsqrtf(warp_sum(m2) / C + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xv[i][j] = (xv[i][j] + (qv[i][j] - mean) * rstd) * kInvSqrt8;       // v = (x + k_ln) * 8^-1/2 : :178
+          my_v[ch * 8 + j] = xv[i][j];
+        }
+      }
+    }
+    __syncwarp();
+    // lora_k[j] = 8^-1/2 * sum_i W[g][o][i] v[g*dg + i]  (:227); product with both queries right away
+    for (int j = lane; j < nout; j += 32) {
+      const int g = j / lg, o = j % lg;
+      const float* wt = s_wt + g * dg * lg + o;
+      const float* vv = my_v + g * dg;
+      float a = 0.f;
+      for (int i = 0; i < dg; ++i) a += wt[i * lg] * vv[i];
+      my_lk[j] = a * kInvSqrt8;
+    }
+    __syncwarp();
+    // lanes 0..15: (i = lane>>3, g = lane&7) score = sum_o lora_q[i][g][o] * lora_k[g][o]  (:247)
+    float sc = 0.f;
+    if (lane < 16) {
+      const int i = lane >> 3, g = lane & 7;
+      for (int o = 0; o < lg; ++o) sc += s_lq[i * nout + g * lg + o] * my_lk[g * lg + o];
+    }
+    // smooth with the head average (:251-257): mean over the 8 lanes of each i
+    float tot = sc;
+    tot += __shfl_xor_sync(0xffffffffu, tot, 1);
+    tot += __shfl_xor_sync(0xffffffffu, tot, 2);
+    tot += __shfl_xor_sync(0xffffffffu, tot, 4);
+    sc = 0.5f * sc + 0.5f * (tot * 0.125f);
+    if (key_mask != nullptr && key_mask[static_cast<long long>(b) * N + t] == 0) sc = kPoolMasked;   // :259-269
+    if (lane < 16) scores[((static_cast<long long>(b) * kHeads + (lane & 7)) * 2 + (lane >> 3)) * N + t] = sc;
+    // online joint softmax over (fg|bg) x tokens, per head g (lanes 0..7 own the state)
+    const float s_fg = __shfl_sync(0xffffffffu, sc, lane & 7);
+    const float s_bg = __shfl_sync(0xffffffffu, sc, 8 + (lane & 7));
+    const float m_new = fmaxf(m_run, fmaxf(s_fg, s_bg));
+    const float corr = (m_run == -INFINITY) ? 0.f : __expf(m_run - m_new);
+    const float e_fg = __expf(s_fg - m_new), e_bg = __expf(s_bg - m_new);
+    l_run = l_run * corr + e_fg + e_bg;
+    m_run = m_new;
+    // every lane (all lanes computed the state of head lane&7) scales its channel chunks by their head's factors
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      const bool ok = ch < nchunks;
+      const int g = ok ? ch / chunks_per_group : 0;
+      const float cg = __shfl_sync(0xffffffffu, corr, g);
+      const float fg = __shfl_sync(0xffffffffu, e_fg, g);
+      const float bg = __shfl_sync(0xffffffffu, e_bg, g);
+      if (ok) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          acc_fg[i][j] = acc_fg[i][j] * cg + fg * xv[i][j];
+          acc_bg[i][j] = acc_bg[i][j] * cg + bg * xv[i][j];
+        }
+      }
+    }
+    __syncwarp();
+  }
+
+  // ---- merge the 8 warps of the block (exact log-sum-exp merge), then write the block partial
+  __syncthreads();
+  float* rec = s_red + warp * (16 + 2 * C);
+  if (lane < 8) {
+    rec[lane] = m_run;
+    rec[8 + lane] = l_run;
+  }
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i) {
+    const int ch = lane + 32 * i;
+    if (ch < nchunks)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        rec[16 + ch * 8 + j] = acc_fg[i][j];
+        rec[16 + C + ch * 8 + j] = acc_bg[i][j];
+      }
+  }
+  __syncthreads();
+  float* out = partials + (static_cast<long long>(b) * gridDim.x + blk) * pool_partial_floats(C);
+  __shared__ float s_m[8], s_scale[8][8];
+  if (threadIdx.x < 8) {
+    const int g = threadIdx.x;
+    float m = -INFINITY;
+    for (int w = 0; w < 8; ++w) m = fmaxf(m, s_red[w * (16 + 2 * C) + g]);
+    float l = 0.f;
+    for (int w = 0; w < 8; ++w) {
+      const float mw = s_red[w * (16 + 2 * C) + g];
+      const float sc = (mw == -INFINITY) ? 0.f : __expf(mw - m);
+      s_scale[w][g] = sc;
+      l += sc * s_red[w * (16 + 2 * C) + 8 + g];
+    }
+    s_m[g] = m;
+    out[g] = m;
+    out[8 + g] = l;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) {
+    const int c = idx % C;
+    const int g = c / dg;
+    float a = 0.f;
+    for (int w = 0; w < 8; ++w) a += s_scale[w][g] * s_red[w * (16 + 2 * C) + 16 + idx];
+    out[16 + idx] = a;
+  }
+}
+
+__global__ void __launch_bounds__(256) ada_pool_combine_kernel(const float* __restrict__ partials, int nblocks, int C,
+                                                               float* __restrict__ fg_out, float* __restrict__ bg_out,
+                                                               float* __restrict__ stats) {
+  extern __shared__ float sh[];     // [nblocks][8] scales
+  __shared__ float s_m[8], s_l[8];
+  const int b = blockIdx.x;
+  const int dg = C / kHeads;
+  const long long rec = pool_partial_floats(C);
+  const float* base = partials + static_cast<long long>(b) * nblocks * rec;
+  if (threadIdx.x < 8) {
+    const int g = threadIdx.x;
+    float m = -INFINITY;
+    for (int k = 0; k < nblocks; ++k) m = fmaxf(m, base[k * rec + g]);
+    float l = 0.f;
+    for (int k = 0; k < nblocks; ++k) {
+      const float mk = base[k * rec + g];
+      const float sc = (mk == -INFINITY) ? 0.f : __expf(mk - m);
+      sh[k * 8 + g] = sc;
+      l += sc * base[k * rec + 8 + g];
+    }
+    s_m[g] = m;
+    s_l[g] = l;
+    stats[(static_cast<long long>(b) * 8 + g) * 2] = m;
+    stats[(static_cast<long long>(b) * 8 + g) * 2 + 1] = l;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) {
+    const int c = idx % C, g = c / dg;
+    float a = 0.f;
+    for (int k = 0; k < nblocks; ++k) a += sh[k * 8 + g] * base[k * rec + 16 + idx];
+    a /= s_l[g];
+    if (idx < C) fg_out[static_cast<long long>(b) * C + c] = a;
+    else bg_out[static_cast<long long>(b) * C + c] = a;
+  }
+}
+
+__global__ void __launch_bounds__(256) ada_pool_probs_kernel(const float* __restrict__ scores, const float* __restrict__ stats,
+                                                             float* __restrict__ attn_fg, float* __restrict__ attn_bg, int N,
+                                                             long long total) {
+  // scores: [B][8][2][N]; attn_*: [B][8][N]
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long bg_idx = i / N;            // (b*8 + g)*2 + which
+    const int n = static_cast<int>(i % N);
+    const long long bgi = bg_idx >> 1;
+    const int which = static_cast<int>(bg_idx & 1);
+    const float m = stats[bgi * 2], l = stats[bgi * 2 + 1];
+    const float pr = __expf(scores[i] - m) / l;
+    (which == 0 ? attn_fg : attn_bg)[bgi * N + n] = pr;
+  }
+}
+
+// ---- K13 ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__ infeat_fg, const float* __restrict__ infeat_bg,
+                                                       const float* __restrict__ time_emb, int time_ld,
+                                                       const float* __restrict__ coeff_w, const float* __restrict__ coeff_b,
+                                                       const float* __restrict__ basis, const float* __restrict__ bias,
+                                                       float* __restrict__ out, int C, int TD, int K, int R, int D) {
+  extern __shared__ float sh[];    // feat [2C + TD], coeffs [K*R], vec [D]
+  __shared__ float red[32];
+  const int b = blockIdx.x;
+  const int F = 2 * C + TD;
+  float* feat = sh;
+  float* coeffs = feat + F;
+  float* vec = coeffs + K * R;
+  for (int i = threadIdx.x; i < F; i += blockDim.x) {
+    float v;
+    if (i < C) v = infeat_fg[static_cast<long long>(b) * C + i];
+    else if (i < 2 * C) v = infeat_bg[static_cast<long long>(b) * C + i - C];
+    else v = time_emb[static_cast<long long>(b) * time_ld + i - 2 * C];        // time_emb[:, :TD]  :849
+    feat[i] = v;
+  }
+  __syncthreads();
+  // LNCat3 (:38-58): LayerNorm (no affine) on the pooled features and on the time slice separately
+  for (int part = 0; part < 2; ++part) {
+    const int lo = part == 0 ? 0 : 2 * C, n = part == 0 ? 2 * C : TD;
+    float s = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += feat[lo + i];
+    const float mean = block_sum_256(s, red) / n;
+    float m2 = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const float d = feat[lo + i] - mean;
+      m2 += d * d;
+    }
+    const float rstd = rsqrtf(block_sum_256(m2, red) / n + 1e-5f);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) feat[lo + i] = (feat[lo + i] - mean) * rstd;
+    __syncthreads();
+  }
+  // basis_dyn_coeffs = Linear(feat) (:858), one warp per output
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int o = warp; o < K * R; o += (blockDim.x >> 5)) {
+    const float* w = coeff_w + static_cast<long long>(o) * F;
+    float a = 0.f;
+    for (int i = lane; i < F; i += 32) a += w[i] * feat[i];
+    a = warp_sum(a);
+    if (lane == 0) coeffs[o] = a + coeff_b[o];
+  }
+  __syncthreads();
+  // out[k] = LN(coeffs[k] @ basis[k]) / sqrt(D) + bias[k]  (:881-893)
+  const float inv_sqrt_d = rsqrtf(static_cast<float>(D));
+  for (int k = 0; k < K; ++k) {
+    float s = 0.f;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+      float a = 0.f;
+      for (int r = 0; r < R; ++r) a += coeffs[k * R + r] * basis[(static_cast<long long>(k) * R + r) * D + d];
+      vec[d] = a;
+      s += a;
+    }
+    const float mean = block_sum_256(s, red) / D;
+    float m2 = 0.f;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+      const float dd = vec[d] - mean;
+      m2 += dd * dd;
+    }
+    const float rstd = rsqrtf(block_sum_256(m2, red) / D + 1e-5f);
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+      float v = (vec[d] - mean) * rstd * inv_sqrt_d;
+      if (bias != nullptr) v += bias[static_cast<long long>(k) * D + d];
+      out[(static_cast<long long>(b) * K + k) * D + d] = v;
+    }
+    __syncthreads();
+  }
+}
+
+int pool_blocks_per_sample(int batch, int n_tokens) {
+  // ~2 waves of blocks over the GPU, at least 8 tokens (one per warp) per block
+  int want = (2 * num_sms() + batch - 1) / batch;
+  int max_blocks = (n_tokens + 7) / 8;
+  if (want > max_blocks) want = max_blocks;
+  if (want < 1) want = 1;
+  return want;
+}
+
+}  // namespace
+}  // namespace afb
+
+extern "C" int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels) {
+  using namespace afb;
+  const int64_t nblocks = (n_tokens + 7) / 8 < 2 * 160 ? (n_tokens + 7) / 8 : 2 * 160;   // upper bound on blocks/sample
+  return static_cast<int64_t>(batch) * kHeads * 2 * n_tokens        // scores
+         + static_cast<int64_t>(batch) * nblocks * pool_partial_floats(channels)
+         + static_cast<int64_t>(batch) * kHeads * 2;                // merged (max, sum)
+}
+
+extern "C" int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
+                                 const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, int batch,
+                                 int channels, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(to_k_weight && fg_q_emb && bg_q_emb && lora_to_fg_q && lora_to_bg_q && lora_q, "afb_ada_pool_prep: NULL argument");
+  AFB_REQUIRE(batch > 0 && ctx_dim > 0, "afb_ada_pool_prep: empty input");
+  AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool_prep: channels %d must be a multiple of 64, <= 1280", channels);
+  ada_pool_prep_kernel<<<batch, kPoolThreads, 2 * channels * sizeof(float), stream>>>(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q,
+                                                                                    lora_to_bg_q, lora_q, channels, ctx_dim);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* lora_q, const float* lora_to_k,
+                            const uint8_t* key_mask, float* fg_out, float* bg_out, float* attn_fg, float* attn_bg, float* ws,
+                            int batch, int n_tokens, int channels, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(x && q && lora_q && lora_to_k && fg_out && bg_out && ws, "afb_ada_pool: NULL argument");
+  AFB_REQUIRE(batch > 0 && n_tokens > 0, "afb_ada_pool: empty input");
+  AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool: channels %d must be a multiple of 64, <= 1280", channels);
+  AFB_REQUIRE((attn_fg == nullptr) == (attn_bg == nullptr), "afb_ada_pool: attn_fg and attn_bg must both be given or both NULL");
+  AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) & 15) == 0, "afb_ada_pool: x/q must be 16-byte aligned");
+  const int C = channels, dg = C / kHeads, lg = dg / kHeads;
+  const int nblocks = pool_blocks_per_sample(batch, n_tokens);
+  const int tokens_per_block = (n_tokens + nblocks - 1) / nblocks;
+  const int grid_x = (n_tokens + tokens_per_block - 1) / tokens_per_block;
+  float* scores = ws;
+  float* partials = scores + static_cast<long long>(batch) * kHeads * 2 * n_tokens;
+  float* stats = partials + static_cast<long long>(batch) * grid_x * pool_partial_floats(C);
+
+  const size_t sh_a = (static_cast<size_t>(kHeads) * dg * lg + 2 * dg + 8 * C + 8 * dg) * sizeof(float);
+  const size_t sh_b = 8 * (16 + 2 * static_cast<size_t>(C)) * sizeof(float);
+  const size_t sh_main = sh_a > sh_b ? sh_a : sh_b;
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(q);
+  dim3 grid(grid_x, batch);
+  const int chunks_per_lane = (C / 8 + 31) / 32;
+  if (chunks_per_lane <= 2) {
+    auto kern = ada_pool_main_kernel<2>;
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main)));
+    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
+  } else if (chunks_per_lane <= 3) {
+    auto kern = ada_pool_main_kernel<3>;
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main)));
+    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
+  } else {
+    auto kern = ada_pool_main_kernel<kMaxChunksPerLane>;
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main)));
+    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
+  }
+  count_launch();
+  ada_pool_combine_kernel<<<batch, 256, grid_x * 8 * sizeof(float), stream>>>(partials, grid_x, C, fg_out, bg_out, stats);
+  count_launch();
+  if (attn_fg != nullptr) {
+    const long long total = static_cast<long long>(batch) * kHeads * 2 * n_tokens;
+    const long long blocks = (total + 255) / 256;
+    ada_pool_probs_kernel<<<static_cast<unsigned>(blocks < 2048 ? blocks : 2048), 256, 0, stream>>>(scores, stats, attn_fg, attn_bg,
+                                                                                                 n_tokens, total);
+    count_launch();
+  }
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
+                            const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
+                            int batch, int channels, int td, int num_vectors, int r, int out_dim, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(infeat_fg && infeat_bg && time_emb && coeff_w && coeff_b && basis && out, "afb_ada_head: NULL argument");
+  AFB_REQUIRE(batch > 0 && channels > 0 && td > 0 && td <= time_ld && num_vectors > 0 && r > 0 && out_dim > 0,
+              "afb_ada_head: bad sizes");
+  const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>(num_vectors) * r + out_dim) * sizeof(float);
+  AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head: feature vector too large for one block (%zu bytes)", sh);
+  ada_head_kernel<<<batch, 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias, out,
+                                              channels, td, num_vectors, r, out_dim);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

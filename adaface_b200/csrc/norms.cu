@@ -1,0 +1,316 @@
+// GroupNorm (K1) and LayerNorm (K3) for the token-major bf16 activation layout.  HBM-bound kernels:
+// fp32 statistics (two-pass, exact merge of per-chunk partials), vectorised coalesced streams.
+// Replaces attention.py:71-72,325 (GroupNorm(32, C, eps=1e-6) + 'b c h w -> b (h w) c') and
+// attention.py:267-269,277-283 (LayerNorm, eps=1e-5).
+#include "common.cuh"
+#include "../../include/adaface_b200.h"
+
+namespace afb {
+void count_launch();
+namespace {
+
+constexpr int kGnChunkTokens = 64;
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = (threadIdx.x < nwarps) ? red[threadIdx.x] : 0.f;
+  if (warp == 0) {
+    t = warp_sum(t);
+    if (lane == 0) red[0] = t;
+  }
+  __syncthreads();
+  return red[0];
+}
+
+// ---- layout 0: x fp32 [B, C, HW]; one block per (b, group): contiguous cpg*HW floats ------------------
+__global__ void __launch_bounds__(512) gn_stats_nchw_kernel(const float* __restrict__ x, float* __restrict__ stats,
+                                                            int cpg_hw, float eps) {
+  __shared__ float red[32];
+  const float* base = x + static_cast<long long>(blockIdx.x) * cpg_hw;
+  const float4* b4 = reinterpret_cast<const float4*>(base);
+  const int n4 = cpg_hw >> 2;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    const float4 v = b4[i];
+    s += (v.x + v.y) + (v.z + v.w);
+  }
+  for (int i = (n4 << 2) + threadIdx.x; i < cpg_hw; i += blockDim.x) s += base[i];
+  const float mean = block_sum(s, red) / static_cast<float>(cpg_hw);
+  float m2 = 0.f;
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    const float4 v = b4[i];
+    const float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
+    m2 += (a * a + b * b) + (c * c + d * d);
+  }
+  for (int i = (n4 << 2) + threadIdx.x; i < cpg_hw; i += blockDim.x) {
+    const float a = base[i] - mean;
+    m2 += a * a;
+  }
+  const float var = block_sum(m2, red) / static_cast<float>(cpg_hw);
+  if (threadIdx.x == 0) {
+    stats[2 * blockIdx.x] = mean;
+    stats[2 * blockIdx.x + 1] = rsqrtf(var + eps);
+  }
+}
+
+// y[b, t, c] = (x[b, c, t] - mean) * rstd * gamma[c] + beta[c]; 32 tokens x 64 channels per block
+__global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restrict__ x, const float* __restrict__ stats,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            __nv_bfloat16* __restrict__ y, int C, int HW, int cpg) {
+  __shared__ float tile[64][33];
+  const int b = blockIdx.z, c0 = blockIdx.y * 64, t0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  const int groups = C / cpg;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = c0 + ty + 8 * i;
+    const int t = t0 + tx;
+    float v = 0.f;
+    if (c < C && t < HW) {
+      const int g = c / cpg;
+      const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
+      v = (x[(static_cast<long long>(b) * C + c) * HW + t] - mean) * rstd * gamma[c] + beta[c];
+    }
+    tile[ty + 8 * i][tx] = v;
+  }
+  __syncthreads();
+  // write: each thread packs 2 channels; 32 channel pairs x 8 tokens per pass
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int t = t0 + ty + 8 * i;
+    const int c = c0 + 2 * tx;
+    if (t < HW && c < C) {
+      const uint32_t pk = pack_bf16x2(tile[2 * tx][ty + 8 * i], tile[2 * tx + 1][ty + 8 * i]);
+      *reinterpret_cast<uint32_t*>(y + (static_cast<long long>(b) * HW + t) * C + c) = pk;
+    }
+  }
+}
+
+// ---- layout 1: x bf16 [B, HW, C]; thread = channel pair, block = (chunk of 64 tokens, b) ---------------
+// partial[((b*groups + g)*nchunks + chunk)*2] = (chunk mean, chunk M2)
+__global__ void gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, int C, int HW,
+                                      int cpg, int nchunks) {
+  extern __shared__ float sh[];   // [C/2] per-thread sums, then [groups] means
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int t0 = chunk * kGnChunkTokens;
+  const int nt = min(kGnChunkTokens, HW - t0);
+  const int groups = C / cpg, tpg = cpg >> 1;   // threads per group
+  float* gmean = sh + (C >> 1);
+  const uint32_t* xp = reinterpret_cast<const uint32_t*>(x + (static_cast<long long>(b) * HW + t0) * C) + threadIdx.x;
+  const int row = C >> 1;
+  float s = 0.f;
+  for (int t = 0; t < nt; ++t) {
+    const float2 v = unpack_bf16x2(xp[static_cast<long long>(t) * row]);
+    s += v.x + v.y;
+  }
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    float a = 0.f;
+    for (int i = 0; i < tpg; ++i) a += sh[threadIdx.x * tpg + i];
+    gmean[threadIdx.x] = a / static_cast<float>(nt * cpg);
+  }
+  __syncthreads();
+  const float mean = gmean[threadIdx.x / tpg];
+  float m2 = 0.f;
+  for (int t = 0; t < nt; ++t) {
+    const float2 v = unpack_bf16x2(xp[static_cast<long long>(t) * row]);
+    const float a = v.x - mean, c = v.y - mean;
+    m2 += a * a + c * c;
+  }
+  __syncthreads();
+  sh[threadIdx.x] = m2;
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    float a = 0.f;
+    for (int i = 0; i < tpg; ++i) a += sh[threadIdx.x * tpg + i];
+    float* out = partial + (static_cast<long long>(b * groups + threadIdx.x) * nchunks + chunk) * 2;
+    out[0] = gmean[threadIdx.x];
+    out[1] = a;
+  }
+}
+
+// exact (Chan) merge of the chunk partials; one thread per (b, group)
+__global__ void gn_finalize_kernel(const float* __restrict__ partial, float* __restrict__ stats, int n_bg, int nchunks,
+                                   int HW, int cpg, float eps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_bg) return;
+  const float* p = partial + static_cast<long long>(i) * nchunks * 2;
+  float tot = 0.f, wsum = 0.f;
+  for (int c = 0; c < nchunks; ++c) {
+    const float n = static_cast<float>(min(kGnChunkTokens, HW - c * kGnChunkTokens) * cpg);
+    wsum += n * p[2 * c];
+    tot += n;
+  }
+  const float mean = wsum / tot;
+  float m2 = 0.f;
+  for (int c = 0; c < nchunks; ++c) {
+    const float n = static_cast<float>(min(kGnChunkTokens, HW - c * kGnChunkTokens) * cpg);
+    const float d = p[2 * c] - mean;
+    m2 += p[2 * c + 1] + n * d * d;
+  }
+  stats[2 * i] = mean;
+  stats[2 * i + 1] = rsqrtf(m2 / tot + eps);
+}
+
+__global__ void gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                    __nv_bfloat16* __restrict__ y, int C, int HW, int cpg) {
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * kGnChunkTokens;
+  const int nt = min(kGnChunkTokens, HW - t0);
+  const int groups = C / cpg;
+  const int c = 2 * threadIdx.x;
+  const int g = c / cpg;
+  const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
+  const float s0 = rstd * gamma[c], s1 = rstd * gamma[c + 1];
+  const float o0 = beta[c] - mean * s0, o1 = beta[c + 1] - mean * s1;
+  const long long base = (static_cast<long long>(b) * HW + t0) * C + c;
+  for (int t = 0; t < nt; ++t) {
+    const float2 v = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(x + base + static_cast<long long>(t) * C));
+    *reinterpret_cast<uint32_t*>(y + base + static_cast<long long>(t) * C) = pack_bf16x2(v.x * s0 + o0, v.y * s1 + o1);
+  }
+}
+
+// ---- LayerNorm: one warp per row, row kept in registers (C <= 8*32*kMaxChunks) -------------------------
+template <int kMaxChunks>
+__global__ void __launch_bounds__(256) layernorm_bf16_kernel(const __nv_bfloat16* __restrict__ x,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta,
+                                                             __nv_bfloat16* __restrict__ y, long long rows, int C,
+                                                             float eps) {
+  const long long row = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nchunks = C >> 3;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + row * C);
+  float v[kMaxChunks][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int ch = lane + 32 * i;
+    if (ch < nchunks) {
+      const uint4 u = xr[ch];
+      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      v[i][0] = a.x; v[i][1] = a.y; v[i][2] = b.x; v[i][3] = b.y;
+      v[i][4] = c.x; v[i][5] = c.y; v[i][6] = d.x; v[i][7] = d.y;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[i][j];
+    }
+  }
+  const float mean = warp_sum(s) / static_cast<float>(C);
+  float m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    if (lane + 32 * i < nchunks) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[i][j] - mean;
+        m2 += d * d;
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(m2) / static_cast<float>(C) + eps);
+  uint4* yr = reinterpret_cast<uint4*>(y + row * C);
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int ch = lane + 32 * i;
+    if (ch < nchunks) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd;
+      if (gamma != nullptr) {
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + 8 * ch));
+        const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + 8 * ch + 4));
+        o[0] *= g0.x; o[1] *= g0.y; o[2] *= g0.z; o[3] *= g0.w;
+        o[4] *= g1.x; o[5] *= g1.y; o[6] *= g1.z; o[7] *= g1.w;
+      }
+      if (beta != nullptr) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + 8 * ch));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta + 8 * ch + 4));
+        o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
+        o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
+      }
+      yr[ch] = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                          pack_bf16x2(o[6], o[7]));
+    }
+  }
+}
+
+}  // namespace
+}  // namespace afb
+
+extern "C" int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups) {
+  const int64_t nchunks = (hw + afb::kGnChunkTokens - 1) / afb::kGnChunkTokens;
+  return 2ll * batch * groups * (nchunks + 1);
+}
+
+extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
+                                    float* stats_ws, int batch, int channels, int hw, int groups, float eps,
+                                    afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(x && gamma && beta && y && stats_ws, "afb_groupnorm_tokens: NULL argument");
+  AFB_REQUIRE(batch > 0 && channels > 0 && hw > 0 && groups > 0, "afb_groupnorm_tokens: empty input");
+  AFB_REQUIRE(channels % groups == 0, "afb_groupnorm_tokens: channels %d not divisible by groups %d", channels, groups);
+  const int cpg = channels / groups;
+  AFB_REQUIRE(cpg % 2 == 0 && channels % 64 == 0, "afb_groupnorm_tokens: need channels %% 64 == 0 and even channels/group");
+  __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(y);
+  if (x_layout == 0) {
+    AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (static_cast<long long>(cpg) * hw) % 4 == 0,
+                "afb_groupnorm_tokens: NCHW input must be 16-byte aligned with (C/groups)*HW %% 4 == 0");
+    gn_stats_nchw_kernel<<<batch * groups, 512, 0, stream>>>(static_cast<const float*>(x), stats_ws, cpg * hw, eps);
+    count_launch();
+    dim3 grid((hw + 31) / 32, channels / 64, batch);
+    gn_apply_nchw_kernel<<<grid, 256, 0, stream>>>(static_cast<const float*>(x), stats_ws, gamma, beta, yb, channels, hw, cpg);
+    count_launch();
+  } else if (x_layout == 1) {
+    AFB_REQUIRE(channels / 2 <= 1024, "afb_groupnorm_tokens: channels %d too large", channels);
+    const int nchunks = (hw + kGnChunkTokens - 1) / kGnChunkTokens;
+    float* partial = stats_ws + 2ll * batch * groups;
+    const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
+    dim3 grid(nchunks, batch);
+    const size_t sh = (channels / 2 + groups) * sizeof(float);
+    gn_partial_tok_kernel<<<grid, channels / 2, sh, stream>>>(xb, partial, channels, hw, cpg, nchunks);
+    count_launch();
+    const int n_bg = batch * groups;
+    gn_finalize_kernel<<<(n_bg + 127) / 128, 128, 0, stream>>>(partial, stats_ws, n_bg, nchunks, hw, cpg, eps);
+    count_launch();
+    gn_apply_tok_kernel<<<grid, channels / 2, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
+    count_launch();
+  } else {
+    AFB_FAIL(2, "afb_groupnorm_tokens: unknown x_layout %d", x_layout);
+  }
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_layernorm_bf16(const afb_bf16* x, const float* gamma, const float* beta, afb_bf16* y, int64_t rows,
+                                  int channels, float eps, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(x && y, "afb_layernorm_bf16: NULL argument");
+  AFB_REQUIRE(rows > 0 && channels > 0, "afb_layernorm_bf16: empty input");
+  AFB_REQUIRE(channels % 8 == 0 && channels <= 8 * 32 * 12, "afb_layernorm_bf16: channels %d must be a multiple of 8, <= 3072",
+              channels);
+  AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0,
+              "afb_layernorm_bf16: buffers must be 16-byte aligned");
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(y);
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  const int chunks_per_lane = (channels / 8 + 31) / 32;
+  if (chunks_per_lane <= 2)
+    layernorm_bf16_kernel<2><<<grid, 256, 0, stream>>>(xb, gamma, beta, yb, rows, channels, eps);
+  else if (chunks_per_lane <= 5)
+    layernorm_bf16_kernel<5><<<grid, 256, 0, stream>>>(xb, gamma, beta, yb, rows, channels, eps);
+  else
+    layernorm_bf16_kernel<12><<<grid, 256, 0, stream>>>(xb, gamma, beta, yb, rows, channels, eps);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

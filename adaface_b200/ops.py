@@ -1,0 +1,317 @@
+"""Tensor-level wrappers of the C ABI (include/adaface_b200.h), registered as torch.library custom ops in
+the `adaface_b200::` namespace.  PyTorch is plumbing here: device memory, streams, op registration.
+
+Every op launches hand-written sm_100a kernels on torch's current CUDA stream; none has a CPU or eager
+fallback - a non-CUDA tensor or a missing library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import AttnArgs, GemmArgs, check
+
+Tensor = torch.Tensor
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts: Optional[Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.AdafaceB200Error("adaface_b200 ops run on CUDA tensors only (no CPU fallback)")
+
+
+def _ptr(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# ------------------------------------------------------------------------------------------- K14
+@torch.library.custom_op("adaface_b200::cfg_ddim_step", mutates_args=())
+def cfg_ddim_step(x: Tensor, e_cond: Tensor, e_uncond: Tensor, noise: Optional[Tensor], guidance_scale: float,
+                  a_t: float, a_prev: float, sigma_t: float, sqrt_one_minus_at: float,
+                  temperature: float) -> Tuple[Tensor, Tensor]:
+    """ddim.py:252-296.  fp32; returns (x_prev, pred_x0)."""
+    _need_cuda(x, e_cond, e_uncond, noise)
+    for t in (x, e_cond, e_uncond, noise):
+        if t is not None and (t.dtype != torch.float32 or t.shape != x.shape):
+            raise ValueError("cfg_ddim_step: fp32 tensors of one shape expected")
+    x, e_cond, e_uncond = x.contiguous(), e_cond.contiguous(), e_uncond.contiguous()
+    noise = None if noise is None else noise.contiguous()
+    x_prev, pred_x0 = torch.empty_like(x), torch.empty_like(x)
+    check(_lib.load().afb_cfg_ddim_step(_ptr(x), _ptr(e_cond), _ptr(e_uncond), _ptr(noise), _ptr(x_prev),
+                                        _ptr(pred_x0), x.numel(), guidance_scale, a_t, a_prev, sigma_t,
+                                        sqrt_one_minus_at, temperature, _stream()), "cfg_ddim_step")
+    return x_prev, pred_x0
+
+
+@cfg_ddim_step.register_fake
+def _(x, e_cond, e_uncond, noise, guidance_scale, a_t, a_prev, sigma_t, sqrt_one_minus_at, temperature):
+    return torch.empty_like(x), torch.empty_like(x)
+
+
+# ------------------------------------------------------------------------------------------- K1 / K3
+@torch.library.custom_op("adaface_b200::groupnorm_tokens", mutates_args=())
+def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: float) -> Tensor:
+    """GroupNorm over x [B,C,h,w] -> normalised tokens bf16 [B, h*w, C] (attention.py:325-327).
+    fp32 NCHW-contiguous and bf16 channels-last inputs are consumed in place; anything else is rejected."""
+    _need_cuda(x, gamma, beta)
+    b, c, h, w = x.shape
+    hw = h * w
+    if x.dtype == torch.float32 and x.is_contiguous():
+        layout = 0
+    elif x.dtype == torch.bfloat16 and x.permute(0, 2, 3, 1).is_contiguous():
+        layout = 1
+    else:
+        raise ValueError("groupnorm_tokens: x must be fp32 NCHW-contiguous or bf16 channels-last")
+    lib = _lib.load()
+    ws = torch.empty(int(lib.afb_groupnorm_ws_floats(b, hw, groups)), dtype=torch.float32, device=x.device)
+    y = torch.empty((b, hw, c), dtype=torch.bfloat16, device=x.device)
+    check(lib.afb_groupnorm_tokens(_ptr(x), layout, _ptr(gamma), _ptr(beta), _ptr(y), _ptr(ws), b, c, hw, groups,
+                                   eps, _stream()), "groupnorm_tokens")
+    return y
+
+
+@groupnorm_tokens.register_fake
+def _(x, gamma, beta, groups, eps):
+    b, c, h, w = x.shape
+    return x.new_empty((b, h * w, c), dtype=torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::layernorm", mutates_args=())
+def layernorm(x: Tensor, gamma: Optional[Tensor], beta: Optional[Tensor], eps: float) -> Tensor:
+    """LayerNorm over the last dim of a contiguous bf16 tensor (attention.py:267-269)."""
+    _need_cuda(x, gamma, beta)
+    if x.dtype != torch.bfloat16 or not x.is_contiguous():
+        raise ValueError("layernorm: contiguous bf16 input expected")
+    y = torch.empty_like(x)
+    c = x.shape[-1]
+    check(_lib.load().afb_layernorm_bf16(_ptr(x), _ptr(gamma), _ptr(beta), _ptr(y), x.numel() // c, c, eps,
+                                         _stream()), "layernorm")
+    return y
+
+
+@layernorm.register_fake
+def _(x, gamma, beta, eps):
+    return torch.empty_like(x)
+
+
+# ------------------------------------------------------------------------------------------- GEMMs
+def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], epilogue: int,
+          ldo: int, ldr: int, hw: int = 0) -> None:
+    _need_cuda(a, w, out, bias, residual)
+    if a.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or a.stride(-1) != 1 or w.stride(-1) != 1:
+        raise ValueError("gemm: bf16 operands with contiguous K expected")
+    if bias is not None and bias.dtype != torch.float32:
+        raise ValueError("gemm: bias must be fp32")
+    args = GemmArgs(a=_ptr(a), w=_ptr(w), out=_ptr(out), bias=_ptr(bias), residual=_ptr(residual),
+                    m=a.shape[0], n=w.shape[0], k=a.shape[1], lda=a.stride(0), ldw=w.stride(0), ldo=ldo, ldr=ldr,
+                    epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
+                    residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
+                    else _lib.DT_BF16, hw=hw)
+    check(_lib.load().afb_gemm_bf16(C.byref(args), _stream()), "gemm_bf16")
+
+
+@torch.library.custom_op("adaface_b200::linear", mutates_args=())
+def linear(a: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], out_fp32: bool) -> Tensor:
+    """out[M,N] = a[M,K] @ w[N,K]^T + bias (+ residual[M,N]).  bf16 operands, fp32 accumulate."""
+    if a.dim() != 2 or w.dim() != 2 or a.shape[1] != w.shape[1]:
+        raise ValueError("linear: a [M,K] and w [N,K] expected")
+    out = torch.empty((a.shape[0], w.shape[0]), dtype=torch.float32 if out_fp32 else torch.bfloat16, device=a.device)
+    if residual is not None and (residual.shape != out.shape or residual.stride(-1) != 1):
+        raise ValueError("linear: residual must be [M,N] with contiguous rows")
+    _gemm(a, w, out, bias, residual, _lib.EPI_STORE, out.stride(0), 0 if residual is None else residual.stride(0))
+    return out
+
+
+@linear.register_fake
+def _(a, w, bias, residual, out_fp32):
+    return a.new_empty((a.shape[0], w.shape[0]), dtype=torch.float32 if out_fp32 else torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::linear_geglu", mutates_args=())
+def linear_geglu(a: Tensor, w_interleaved: Tensor, bias_interleaved: Tensor) -> Tensor:
+    """GEGLU (attention.py:32-39): w/bias rows pre-interleaved by `interleave_geglu`; returns bf16 [M, N/2]."""
+    out = torch.empty((a.shape[0], w_interleaved.shape[0] // 2), dtype=torch.bfloat16, device=a.device)
+    _gemm(a, w_interleaved, out, bias_interleaved, None, _lib.EPI_GEGLU, out.stride(0), 0)
+    return out
+
+
+@linear_geglu.register_fake
+def _(a, w_interleaved, bias_interleaved):
+    return a.new_empty((a.shape[0], w_interleaved.shape[0] // 2), dtype=torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::linear_nchw", mutates_args=())
+def linear_nchw(a: Tensor, w: Tensor, bias: Tensor, residual: Tensor) -> Tensor:
+    """proj_out + 'b (h w) c -> b c h w' + x_in (attention.py:335-341): a [B*hw, K] tokens, residual fp32
+    NCHW-contiguous [B, N, h, w]; returns fp32 [B, N, h, w]."""
+    if residual.dtype != torch.float32 or not residual.is_contiguous():
+        raise ValueError("linear_nchw: fp32 NCHW-contiguous residual expected")
+    out = torch.empty_like(residual)
+    hw = residual.shape[2] * residual.shape[3]
+    _gemm(a, w, out, bias, residual, _lib.EPI_NCHW, 0, 0, hw)
+    return out
+
+
+@linear_nchw.register_fake
+def _(a, w, bias, residual):
+    return torch.empty_like(residual)
+
+
+def interleave_geglu(weight: Tensor, bias: Tensor) -> Tuple[Tensor, Tensor]:
+    """Reorders GEGLU.proj rows [value(4C); gate(4C)] into 16-row groups (16 value rows, their 16 gate rows, ...)
+    so that one 32-column accumulator chunk of the GEMM epilogue holds both halves of 16 outputs."""
+    half = weight.shape[0] // 2
+    if half % 16:
+        raise ValueError("interleave_geglu: inner dim must be a multiple of 16")
+    idx = torch.arange(half, device=weight.device).reshape(-1, 16)
+    order = torch.cat([idx, idx + half], dim=1).reshape(-1)
+    return weight[order].contiguous(), bias[order].contiguous()
+
+
+# ------------------------------------------------------------------------------------------- K5 / K8
+def _ld3(t: Tensor, name: str) -> int:
+    if t.dim() != 3 or t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != t.shape[1] * t.stride(1):
+        raise ValueError(f"attention: {name} must be bf16 [B, L, C] with contiguous channels and a uniform row pitch")
+    return t.stride(1)
+
+
+@torch.library.custom_op("adaface_b200::attention", mutates_args=())
+def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float, key_mask: Optional[Tensor]) -> Tensor:
+    """softmax(q k^T * scale [+ key mask]) v with heads concatenated along channels (attention.py:198-242).
+    q [B,Nq,C], k/v [B,Nk,C] may be column slices of a fused projection buffer; key_mask uint8/bool [B,Nk]."""
+    _need_cuda(q, k, v, key_mask)
+    b, nq, c = q.shape
+    nk = k.shape[1]
+    if k.shape != v.shape or k.shape[0] != b or k.shape[2] != c or c % heads:
+        raise ValueError("attention: shape mismatch")
+    out = torch.empty((b, nq, c), dtype=torch.bfloat16, device=q.device)
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, nk).to(torch.uint8).contiguous()
+    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=_ptr(key_mask), batch=b, heads=heads,
+                    head_dim=c // heads, q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"),
+                    ldo=c, scale=scale)
+    check(_lib.load().afb_attention_fwd(C.byref(args), _stream()), "attention_fwd")
+    return out
+
+
+@attention.register_fake
+def _(q, k, v, heads, scale, key_mask):
+    return q.new_empty(q.shape, dtype=torch.bfloat16)
+
+
+# ------------------------------------------------------------------------------------------- K12 / K13
+@torch.library.custom_op("adaface_b200::ada_pool_prep", mutates_args=())
+def ada_pool_prep(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_to_fg_q: Tensor,
+                  lora_to_bg_q: Tensor) -> Tensor:
+    """Step-invariant part of AttentionalPooler (embedding_manager.py:186-235) -> lora_q fp32 [B, 2, C/8]."""
+    _need_cuda(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q)
+    c, ctx_dim = to_k_weight.shape
+    b = bg_q_emb.shape[0]
+    f = lambda t: t.to(torch.float32).contiguous()
+    lora_q = torch.empty((b, 2, c // 8), dtype=torch.float32, device=to_k_weight.device)
+    check(_lib.load().afb_ada_pool_prep(_ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)), _ptr(f(bg_q_emb)),
+                                        _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(lora_q), b, c, _stream()),
+          "ada_pool_prep")
+    return lora_q
+
+
+@ada_pool_prep.register_fake
+def _(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q):
+    return to_k_weight.new_empty((bg_q_emb.shape[0], 2, to_k_weight.shape[0] // 8), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::ada_pool", mutates_args=())
+def ada_pool(x: Tensor, q: Tensor, lora_q: Tensor, lora_to_k: Tensor, key_mask: Optional[Tensor],
+             want_attn: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """AttentionalPooler main pass (embedding_manager.py:146-321): x, q bf16 [B,N,C] -> fg_out, bg_out fp32 [B,C]
+    and, when want_attn, attn_fg/attn_bg fp32 [B*8, 1, N] (empty tensors otherwise)."""
+    _need_cuda(x, q, lora_q, lora_to_k, key_mask)
+    if x.dtype != torch.bfloat16 or q.dtype != torch.bfloat16 or not x.is_contiguous() or not q.is_contiguous():
+        raise ValueError("ada_pool: contiguous bf16 x and q expected")
+    b, n, c = x.shape
+    lib = _lib.load()
+    dev = x.device
+    ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
+    fg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    bg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    a_fg = torch.empty((b * 8, 1, n) if want_attn else (0,), dtype=torch.float32, device=dev)
+    a_bg = torch.empty((b * 8, 1, n) if want_attn else (0,), dtype=torch.float32, device=dev)
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
+    wk = lora_to_k.to(torch.float32).contiguous()
+    check(lib.afb_ada_pool(_ptr(x), _ptr(q), _ptr(lora_q.contiguous()), _ptr(wk), _ptr(key_mask), _ptr(fg), _ptr(bg),
+                           _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c,
+                           _stream()), "ada_pool")
+    return fg, bg, a_fg, a_bg
+
+
+@ada_pool.register_fake
+def _(x, q, lora_q, lora_to_k, key_mask, want_attn):
+    b, n, c = x.shape
+    shape = (b * 8, 1, n) if want_attn else (0,)
+    f = lambda s: x.new_empty(s, dtype=torch.float32)
+    return f((b, c)), f((b, c)), f(shape), f(shape)
+
+
+@torch.library.custom_op("adaface_b200::ada_head", mutates_args=())
+def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor,
+             basis: Tensor, bias: Optional[Tensor]) -> Tensor:
+    """AdaEmbedding head (embedding_manager.py:847-893): -> out fp32 [B, K, 768]."""
+    _need_cuda(infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias)
+    b, c = infeat_fg.shape
+    k, r, d = basis.shape
+    f = lambda t: None if t is None else t.to(torch.float32).contiguous()
+    infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias = map(
+        f, (infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias))
+    if coeff_w.shape != (k * r, 2 * c + td):
+        raise ValueError(f"ada_head: coefficient map {tuple(coeff_w.shape)} does not match ({k * r}, {2 * c + td})")
+    out = torch.empty((b, k, d), dtype=torch.float32, device=infeat_fg.device)
+    check(_lib.load().afb_ada_head(_ptr(infeat_fg), _ptr(infeat_bg), _ptr(time_emb), time_emb.stride(0), _ptr(coeff_w),
+                                   _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), b, c, td, k, r, d, _stream()),
+          "ada_head")
+    return out
+
+
+@ada_head.register_fake
+def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias):
+    return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[0], basis.shape[2]), dtype=torch.float32)
+
+
+# ------------------------------------------------------------------------------------------- casts
+@torch.library.custom_op("adaface_b200::to_bf16", mutates_args=())
+def to_bf16(x: Tensor) -> Tensor:
+    _need_cuda(x)
+    if x.dtype != torch.float32:
+        raise ValueError("to_bf16: fp32 input expected")
+    x = x.contiguous()
+    y = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().afb_cast_f32_to_bf16(_ptr(x), _ptr(y), x.numel(), _stream()), "cast_f32_to_bf16")
+    return y
+
+
+@to_bf16.register_fake
+def _(x):
+    return x.new_empty(x.shape, dtype=torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::to_f32", mutates_args=())
+def to_f32(x: Tensor) -> Tensor:
+    _need_cuda(x)
+    if x.dtype != torch.bfloat16:
+        raise ValueError("to_f32: bf16 input expected")
+    x = x.contiguous()
+    y = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    check(_lib.load().afb_cast_bf16_to_f32(_ptr(x), _ptr(y), x.numel(), _stream()), "cast_bf16_to_f32")
+    return y
+
+
+@to_f32.register_fake
+def _(x):
+    return x.new_empty(x.shape, dtype=torch.float32)

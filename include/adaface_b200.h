@@ -1,0 +1,132 @@
+/*
+ * adaface_b200 C ABI -- the drop-in boundary of the B200-native AdaPrompt U-Net transformer path.
+ *
+ * The reference (zyt334/AdaFace) is pure Python/PyTorch and has no FFI layer: its boundary for this
+ * path is the nn.Module contract of ldm/modules/attention.py (CrossAttention :147, BasicTransformerBlock
+ * :260, SpatialTransformer :287), ldm/modules/embedding_manager.py (AttentionalPooler :100, AdaEmbedding
+ * :539) and DDIMSampler.p_sample_ddim (ldm/models/diffusion/ddim.py:222).  The Python host side in
+ * adaface_b200/ keeps those signatures; below it, every kernel group is reachable through the
+ * stateless extern "C" entry points declared here (plain device pointers and sizes, no torch types),
+ * which is what a maintainer binds with ctypes / torch.library.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated; the caller owns all buffers and workspaces;
+ *     kernels never allocate or free; all launches go to `stream` and are CUDA-graph capturable;
+ *   - `bf16` buffers are raw uint16 bfloat16; activations are token-major [rows, C] unless stated;
+ *   - return 0 on success; non-zero = error, message via afb_last_error() (thread-local);
+ *     2 = unsupported shape/argument, 3 = CUDA runtime error;
+ *   - there is no CPU fallback: on a machine without an sm_100 device every entry point returns 3.
+ */
+#ifndef ADAFACE_B200_H_
+#define ADAFACE_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* afb_stream_t;   /* cudaStream_t */
+typedef uint16_t afb_bf16;
+
+const char* afb_last_error(void);
+int afb_abi_version(void);
+/* Number of kernels launched through this library by the calling process since load (bench.py's gpu_launches). */
+int64_t afb_launch_count(void);
+
+/* ---- K14: CFG combine + DDIM update.  Replaces ldm/models/diffusion/ddim.py:252-296 ------------------
+ * e = e_u + s (e_c - e_u); pred_x0 = (x - sqrt(1-a_t) e)/sqrt(a_t); x_prev = sqrt(a_prev) pred_x0 +
+ * sqrt(1 - a_prev - sigma^2) e + sigma * noise * temperature.  fp32 in/out, n = number of elements of x.
+ * `noise` may be NULL when sigma_t == 0. */
+int afb_cfg_ddim_step(const float* x, const float* e_cond, const float* e_uncond, const float* noise,
+                      float* x_prev, float* pred_x0, int64_t n, float guidance_scale, float a_t, float a_prev,
+                      float sigma_t, float sqrt_one_minus_at, float temperature, afb_stream_t stream);
+
+/* ---- K1: GroupNorm(32, C, eps) -> token-major bf16.  Replaces attention.py:71-72,325 (+ the layout change
+ * of :327).  x_layout 0: x is fp32 [B,C,HW] (NCHW contiguous); 1: x is bf16 [B,HW,C] (channels-last).
+ * stats_ws: fp32 workspace of afb_groupnorm_ws_floats(B, HW, groups) floats.  y: bf16 [B*HW, C]. */
+int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups);
+int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
+                         float* stats_ws, int batch, int channels, int hw, int groups, float eps,
+                         afb_stream_t stream);
+
+/* ---- K3: LayerNorm over the last dim, bf16 in / bf16 out, fp32 statistics.  attention.py:267-269,277-283.
+ * gamma/beta may be NULL (no affine; embedding_manager.py:111-113). */
+int afb_layernorm_bf16(const afb_bf16* x, const float* gamma, const float* beta, afb_bf16* y, int64_t rows,
+                       int channels, float eps, afb_stream_t stream);
+
+/* ---- K2/K4/K6/K7/K9/K10/K11: Y = epilogue(A[M,K] * W[N,K]^T), bf16 operands, fp32 accumulation in TMEM.
+ * Replaces every nn.Linear / 1x1 nn.Conv2d on the path (attention.py:35,55,157-165,302-317). */
+enum afb_gemm_epilogue {
+  AFB_EPI_STORE = 0,  /* out[m,n] = acc + bias[n] (+ residual[m,n]); row-major, out_dtype selects bf16/fp32 */
+  AFB_EPI_GEGLU = 1,  /* W rows interleaved (16 value rows, 16 gate rows, ...): out[m,j] = a * gelu_erf(g), */
+                      /* out is bf16 [M, N/2] (attention.py:32-39)                                           */
+  AFB_EPI_NCHW = 2    /* out fp32 [B, N, HW] with m = b*HW + t: out = acc + bias + residual (same layout)     */
+                      /* (proj_out + 'b (h w) c -> b c h w' + x_in: attention.py:335-341)                    */
+};
+enum afb_dtype { AFB_BF16 = 0, AFB_F32 = 1 };
+
+typedef struct afb_gemm_args {
+  const afb_bf16* a;        /* [M, K] row-major, lda elements (K contiguous); 16-byte aligned, lda % 8 == 0 */
+  const afb_bf16* w;        /* [N, K] row-major (nn.Linear weight layout), ldw elements                     */
+  void* out;                /* see epilogue                                                                  */
+  const float* bias;        /* [N] fp32 or NULL                                                              */
+  const void* residual;     /* NULL, or same shape/layout as out with dtype residual_dtype                   */
+  int64_t m, n, k;
+  int64_t lda, ldw, ldo, ldr;   /* leading dimensions in elements (ldo/ldr unused for AFB_EPI_NCHW)         */
+  int epilogue;             /* enum afb_gemm_epilogue */
+  int out_dtype;            /* enum afb_dtype (STORE only; GEGLU is bf16, NCHW is fp32)                      */
+  int residual_dtype;       /* enum afb_dtype */
+  int hw;                   /* tokens per sample, AFB_EPI_NCHW only                                          */
+} afb_gemm_args;
+int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
+
+/* ---- K5/K8: fused softmax(Q K^T * scale) V, online softmax, S/O accumulators in TMEM.
+ * Replaces attention.py:198-242 (self-attention with optional key mask, and cross-attention over the
+ * 77-token context).  q/k/v are bf16 with heads concatenated along the channel dim: element (b, t, h, i)
+ * of q is q[(b*q_len + t)*ldq + h*head_dim + i], likewise k/v with kv_len and ldk/ldv; out is bf16
+ * [B*q_len, ldo] in the same head-concatenated layout.  head_dim in {40, 80, 160}.
+ * key_mask: NULL or uint8 [B, kv_len], 0 = masked key (attention.py:223-232). */
+typedef struct afb_attn_args {
+  const afb_bf16* q;
+  const afb_bf16* k;
+  const afb_bf16* v;
+  afb_bf16* out;
+  const uint8_t* key_mask;
+  int batch, heads, head_dim;
+  int q_len, kv_len;
+  int64_t ldq, ldk, ldv, ldo;
+  float scale;
+} afb_attn_args;
+int afb_attention_fwd(const afb_attn_args* args, afb_stream_t stream);
+
+/* ---- K12: AttentionalPooler.forward, eval mode.  Replaces embedding_manager.py:146-321.
+ * afb_ada_pool_prep (step-invariant, :186-235): fg_q/bg_q = to_k(query embedding) with the layer's attn2.to_k
+ *   weight fp32 [C, ctx_dim]; fg_q_emb fp32 [ctx_dim] (shared by the batch), bg_q_emb fp32 [B, ctx_dim];
+ *   LayerNorm; grouped 1x1 convs lora_to_fg_q / lora_to_bg_q (fp32 [C/8, C/8], 8 groups) -> lora_q fp32 [B,2,C/8].
+ * afb_ada_pool: x, q bf16 [B, N, C] (block input x1 and attn2.to_q(norm2(x1))); lora_to_k fp32 [C/8, C/8];
+ *   key_mask NULL or uint8 [B, N] (0 = masked).  Outputs fp32: fg_out, bg_out [B, C]; attn_fg, attn_bg
+ *   [B, 8, N] (both NULL to skip).  ws: fp32 workspace of afb_ada_pool_ws_floats(B, N, C) floats. */
+int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels);
+int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
+                      const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, int batch, int channels,
+                      afb_stream_t stream);
+int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* lora_q, const float* lora_to_k,
+                 const uint8_t* key_mask, float* fg_out, float* bg_out, float* attn_fg, float* attn_bg, float* ws,
+                 int batch, int n_tokens, int channels, afb_stream_t stream);
+
+/* ---- K13: AdaEmbedding head.  Replaces embedding_manager.py:847-893.
+ * infeat_fg/bg fp32 [B, C]; time_emb fp32 [B, time_ld] (first TD = C/4 used); coeff_w fp32 [K*r, 2C+TD],
+ * coeff_b [K*r]; basis fp32 [K, r, D]; bias fp32 [K, D] or NULL; out fp32 [B, K, D]. */
+int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
+                 const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
+                 int batch, int channels, int td, int num_vectors, int r, int out_dim, afb_stream_t stream);
+
+/* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */
+int afb_cast_f32_to_bf16(const float* src, afb_bf16* dst, int64_t n, afb_stream_t stream);
+int afb_cast_bf16_to_f32(const afb_bf16* src, float* dst, int64_t n, afb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ADAFACE_B200_H_ */
