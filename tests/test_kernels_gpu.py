@@ -1,0 +1,221 @@
+"""Kernel-level parity on the B200: every C-ABI entry point against the CPU oracle (oracle/port.py) or the
+plain fp32 formula of the same op, on seeded inputs.  Run with `-m gpu`."""
+import math
+
+import pytest
+import torch
+
+from conftest import rel_l2
+from oracle import params as P
+from oracle import port
+
+pytestmark = pytest.mark.gpu
+
+BF16_TOL = 1e-2          # north_star: per-block relative L2 <= 1e-2 in bf16
+
+
+@pytest.fixture(scope="module")
+def ops(cuda_device):
+    from adaface_b200 import ops as o
+    return o
+
+
+def _r(key, shape, scale=1.0, seed=101):
+    return P.randn(key, shape, seed, scale)
+
+
+# ---------------------------------------------------------------------------------------------- K14
+@pytest.mark.parametrize("n", [(8, 4, 64, 64), (3, 4, 8, 8), (1, 1, 1, 7)])
+@pytest.mark.parametrize("sigma", [0.0, 0.3])
+def test_cfg_ddim_step_bit_exact(ops, cuda_device, n, sigma):
+    x, ec, eu, nz = (_r(f"ddim.{k}", n) for k in ("x", "ec", "eu", "nz"))
+    a_t, a_prev, s1m = 0.0413, 0.0521, math.sqrt(1 - 0.0413)
+    a_t, a_prev, s1m = (float(torch.tensor(v, dtype=torch.float32)) for v in (a_t, a_prev, s1m))
+    ref_prev, ref_x0 = port.cfg_ddim_update(x, ec, eu, 7.5, a_t, a_prev, sigma, s1m, nz if sigma else None)
+    d = cuda_device
+    got_prev, got_x0 = ops.cfg_ddim_step(x.to(d), ec.to(d), eu.to(d), nz.to(d) if sigma else None, 7.5, a_t, a_prev,
+                                         sigma, s1m, 1.0)
+    assert torch.equal(got_x0.cpu(), ref_x0)
+    assert torch.equal(got_prev.cpu(), ref_prev)
+
+
+# ---------------------------------------------------------------------------------------------- K1 / K3
+@pytest.mark.parametrize("c,hw", [(320, 16), (640, 8), (1280, 8), (320, 12)])
+def test_groupnorm_tokens_both_layouts(ops, cuda_device, c, hw):
+    b = 2
+    x = _r("gn.x", (b, c, hw, hw)) * 1.5 + 0.7
+    g, be = 1 + 0.1 * _r("gn.g", (c,)), 0.1 * _r("gn.b", (c,))
+    ref = port.group_norm(x, g, be, 32, 1e-6).reshape(b, c, hw * hw).transpose(1, 2)
+    d = cuda_device
+    y0 = ops.groupnorm_tokens(x.to(d), g.to(d), be.to(d), 32, 1e-6)
+    assert rel_l2(y0.float(), ref) < 4e-3                 # bf16 output rounding only
+    xb = x.to(d).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ref1 = port.group_norm(xb.float().cpu(), g, be, 32, 1e-6).reshape(b, c, hw * hw).transpose(1, 2)
+    y1 = ops.groupnorm_tokens(xb, g.to(d), be.to(d), 32, 1e-6)
+    assert rel_l2(y1.float(), ref1) < 4e-3
+
+
+@pytest.mark.parametrize("c", [320, 640, 1280, 2880])
+def test_layernorm(ops, cuda_device, c):
+    rows = 77
+    x = (_r("ln.x", (rows, c)) * 2 + 0.3).to(torch.bfloat16)
+    g, be = 1 + 0.1 * _r("ln.g", (c,)), 0.1 * _r("ln.b", (c,))
+    d = cuda_device
+    ref = port.layer_norm(x.float(), g, be)
+    assert rel_l2(ops.layernorm(x.to(d), g.to(d), be.to(d), 1e-5).float(), ref) < 4e-3
+    ref = port.layer_norm(x.float())
+    assert rel_l2(ops.layernorm(x.to(d), None, None, 1e-5).float(), ref) < 4e-3
+
+
+# ---------------------------------------------------------------------------------------------- GEMM
+@pytest.mark.parametrize("m,n,k", [(128, 160, 64), (256, 320, 320), (512, 960, 320), (200, 640, 768),
+                                   (1024, 1280, 5120), (64, 1280, 1280), (4096, 320, 1280), (154, 128, 768)])
+def test_linear_store(ops, cuda_device, m, n, k):
+    a = _r("g.a", (m, k)).to(torch.bfloat16)
+    w = _r("g.w", (n, k), k ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("g.b", (n,))
+    res = _r("g.r", (m, n)).to(torch.bfloat16)
+    ref = a.float() @ w.float().t() + bias
+    d = cuda_device
+    out = ops.linear(a.to(d), w.to(d), bias.to(d), None, False)
+    assert rel_l2(out.float(), ref) < 4e-3
+    out = ops.linear(a.to(d), w.to(d), None, res.to(d), True)
+    assert rel_l2(out, ref - bias + res.float()) < 1e-4          # fp32 out: only accumulation-order error
+    out = ops.linear(a.to(d), w.to(d), bias.to(d), res.float().to(d), False)
+    assert rel_l2(out.float(), ref + res.float()) < 4e-3
+
+
+def test_linear_strided_views(ops, cuda_device):
+    """A operand and residual as column slices of wider buffers (lda/ldr != K/N)."""
+    m, n, k = 256, 320, 320
+    big = _r("g.big", (m, 3 * k)).to(torch.bfloat16).to(cuda_device)
+    w = _r("g.w2", (n, k), k ** -0.5).to(torch.bfloat16).to(cuda_device)
+    a = big[:, k:2 * k]
+    out = ops.linear(a, w, None, None, True)
+    assert rel_l2(out, a.float() @ w.float().t()) < 1e-4
+
+
+@pytest.mark.parametrize("m,c", [(256, 320), (128, 640), (77, 1280)])
+def test_linear_geglu(ops, cuda_device, m, c):
+    a = _r("gg.a", (m, c)).to(torch.bfloat16)
+    w = _r("gg.w", (8 * c, c), c ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("gg.b", (8 * c,))
+    h = a.float() @ w.float().t() + bias
+    val, gate = h.chunk(2, dim=-1)
+    ref = val * port.gelu_erf(gate)
+    d = cuda_device
+    wi, bi = ops.interleave_geglu(w.to(d), bias.to(d))
+    out = ops.linear_geglu(a.to(d), wi, bi)
+    assert out.shape == (m, 4 * c)
+    assert rel_l2(out.float(), ref) < 5e-3
+
+
+@pytest.mark.parametrize("b,c,hw", [(2, 320, 16), (3, 640, 8), (2, 1280, 8)])
+def test_linear_nchw(ops, cuda_device, b, c, hw):
+    n_tok = hw * hw
+    a = _r("gn.a", (b * n_tok, c)).to(torch.bfloat16)
+    w = _r("gn.w", (c, c), c ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("gn.bias", (c,))
+    x_in = _r("gn.xin", (b, c, hw, hw))
+    ref = (a.float() @ w.float().t() + bias).reshape(b, n_tok, c).transpose(1, 2).reshape(b, c, hw, hw) + x_in
+    d = cuda_device
+    out = ops.linear_nchw(a.to(d), w.to(d), bias.to(d), x_in.to(d))
+    assert rel_l2(out, ref) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------- attention
+def _attn_ref(q, k, v, heads, scale, mask=None):
+    b, nq, c = q.shape
+    d = c // heads
+    sim = port.attention_scores(q, k, heads, scale)
+    if mask is not None:
+        sim = sim.masked_fill(~mask.bool()[:, None, None, :], -torch.finfo(sim.dtype).max)
+    attn = sim.softmax(dim=-1)
+    vh = v.reshape(b, -1, heads, d).permute(0, 2, 1, 3)
+    return torch.matmul(attn, vh).permute(0, 2, 1, 3).reshape(b, nq, c)
+
+
+@pytest.mark.parametrize("c,nq,nk", [(320, 256, 256), (320, 1024, 1024), (320, 256, 77), (640, 256, 256),
+                                     (640, 64, 77), (1280, 64, 64), (1280, 256, 77), (320, 144, 144), (320, 4096, 4096)])
+def test_attention_matches_oracle(ops, cuda_device, c, nq, nk):
+    b, heads = 2, 8
+    q = _r("at.q", (b, nq, c)).to(torch.bfloat16)
+    k = _r("at.k", (b, nk, c)).to(torch.bfloat16)
+    v = _r("at.v", (b, nk, c)).to(torch.bfloat16)
+    scale = (c // heads) ** -0.5
+    ref = _attn_ref(q.float(), k.float(), v.float(), heads, scale)
+    d = cuda_device
+    out = ops.attention(q.to(d), k.to(d), v.to(d), heads, scale, None)
+    assert rel_l2(out.float(), ref) < BF16_TOL
+
+
+def test_attention_fused_qkv_views_and_sharp_softmax(ops, cuda_device):
+    """q/k/v as column slices of one [B,N,3C] buffer; large logits exercise the lazy-rescale path."""
+    b, n, c, heads = 2, 512, 320, 8
+    qkv = _r("at.qkv", (b, n, 3 * c), 3.0).to(torch.bfloat16)
+    q, k, v = qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:]
+    scale = (c // heads) ** -0.5
+    ref = _attn_ref(q.float(), k.float(), v.float(), heads, scale)
+    qd = qkv.to(cuda_device)
+    out = ops.attention(qd[..., :c], qd[..., c:2 * c], qd[..., 2 * c:], heads, scale, None)
+    assert rel_l2(out.float(), ref) < BF16_TOL
+
+
+@pytest.mark.parametrize("c,n", [(320, 256), (640, 256), (1280, 64)])
+def test_attention_key_mask(ops, cuda_device, c, n):
+    b, heads = 2, 8
+    q = _r("am.q", (b, n, c)).to(torch.bfloat16)
+    k = _r("am.k", (b, n, c)).to(torch.bfloat16)
+    v = _r("am.v", (b, n, c)).to(torch.bfloat16)
+    mask = (_r("am.m", (b, n)) > -0.3)
+    mask[1, :] = False                                   # a fully masked sample: uniform average, like the reference
+    scale = (c // heads) ** -0.5
+    ref = _attn_ref(q.float(), k.float(), v.float(), heads, scale, mask)
+    d = cuda_device
+    out = ops.attention(q.to(d), k.to(d), v.to(d), heads, scale, mask.to(d))
+    assert rel_l2(out.float(), ref) < BF16_TOL
+
+
+# ---------------------------------------------------------------------------------------------- K12 / K13
+@pytest.mark.parametrize("ca_idx,n", [(0, 256), (2, 64), (4, 64), (0, 4096)])
+def test_ada_pool_and_head(ops, cuda_device, ca_idx, n):
+    seed, b, K, r = 15, 2, 9, 12
+    sd = P.init_ada_embedding(seed, K, r, 2)
+    c = P.CA_INFEAT_DIMS[ca_idx]
+    x = P.randn(f"adag.{ca_idx}.x", (b, n, c), seed).to(torch.bfloat16)
+    q = P.randn(f"adag.{ca_idx}.q", (b, n, c), seed, 2.0).to(torch.bfloat16)
+    to_k = P.draw(f"adag.{ca_idx}.to_k", (c, 768), seed)
+    time_emb = P.randn("adag.time_emb", (b, 1280), seed)
+    probe = P.randn(f"adag.{ca_idx}.probe", (768,), seed, 0.5)
+    extra = P.randn(f"adag.{ca_idx}.extra", (b, 768), seed, 0.5)
+    ref_out, ref_pool = port.ada_embedding(sd, ca_idx, x.float(), q.float(), to_k, time_emb, probe, extra, K, r)
+    d = cuda_device
+    g = lambda key: sd[key].to(d)
+    lora_q = ops.ada_pool_prep(to_k.to(d), probe.to(d), extra.to(d), g(f"poolers.{ca_idx}.lora_to_fg_q.weight").squeeze(-1),
+                               g(f"poolers.{ca_idx}.lora_to_bg_q.weight").squeeze(-1))
+    fg, bg, a_fg, a_bg = ops.ada_pool(x.to(d), q.to(d), lora_q, g(f"poolers.{ca_idx}.lora_to_k.weight").squeeze(-1), None, True)
+    assert rel_l2(fg, ref_pool["fg_out"]) < 2e-3
+    assert rel_l2(bg, ref_pool["bg_out"]) < 2e-3
+    assert rel_l2(a_fg, ref_pool["attn_fg"]) < 2e-3
+    assert rel_l2(a_bg, ref_pool["attn_bg"]) < 2e-3
+    basis = torch.cat([sd["pre_vecs"], sd["basis_vecs"]], dim=1).to(d)
+    out = ops.ada_head(fg, bg, time_emb.to(d), int(0.25 * c), g(f"layer_coeff_maps.{ca_idx}.weight"),
+                       g(f"layer_coeff_maps.{ca_idx}.bias"), basis, sd["bias"][ca_idx].to(d))
+    assert rel_l2(out, ref_out) < 5e-3
+
+
+def test_casts_round_trip(ops, cuda_device):
+    x = _r("cast.x", (3, 1001)).to(cuda_device)
+    y = ops.to_bf16(x)
+    assert torch.equal(y, x.to(torch.bfloat16))
+    assert torch.equal(ops.to_f32(y), y.float())
+
+
+def test_unsupported_arguments_raise(ops, cuda_device):
+    from adaface_b200._lib import AdafaceB200Error
+    d = cuda_device
+    q = torch.zeros((1, 64, 8 * 24), dtype=torch.bfloat16, device=d)
+    with pytest.raises(AdafaceB200Error):
+        ops.attention(q, q, q, 8, 1.0, None)                     # head_dim 24 is not an SD-1.5 head size
+    with pytest.raises(AdafaceB200Error):
+        ops.linear(torch.zeros((8, 64), dtype=torch.bfloat16), torch.zeros((32, 64), dtype=torch.bfloat16), None, None, False)
