@@ -1,0 +1,219 @@
+"""Host-side mirror of the per-layer adaptive subject embedding (reference:
+ldm/modules/embedding_manager.py - LNCat3 :38-58, AttentionalPooler :100-321, AdaEmbedding :539-910).
+
+Constructor arguments, `forward` signatures, return values and state_dict keys follow the reference.  The
+arithmetic runs in two kernel groups (adaface_b200/csrc/ada.cu): K12, one streaming pass over the layer's
+`x` and `q` with an online joint softmax over the (fg | bg) x token axis, and K13, the coefficient map +
+basis combination + per-vector LayerNorm head.  Eval-mode semantics (the pooler's Dropout(0.1) is
+train-only); fp32 statistics on bf16 activations, i.e. the fp32 restatement of the reference rather than
+its forced CPU-bf16 autocast.
+
+In the reference snapshot AdaEmbedding is defined but not wired into the U-Net; the wiring
+offered here (`AdaPromptContext` in adaface_b200/unet.py) reconstructs the removed call site from the
+class's own contract.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from . import ops
+from .attention import _PackedWeights, _f32, as_bf16_tokens
+
+Tensor = torch.Tensor
+
+CA_INFEAT_DIMS = [320, 320, 640, 640, 1280, 1280, 1280, 1280, 1280, 1280, 640, 640, 640, 320, 320, 320]
+LAYER_IDX2CA_LAYER_IDX = {1: 0, 2: 1, 4: 2, 5: 3, 7: 4, 8: 5, 12: 6, 16: 7,
+                          17: 8, 18: 9, 19: 10, 20: 11, 21: 12, 22: 13, 23: 14, 24: 15}
+
+
+class LNCat3(nn.Module):
+    """embedding_manager.py:38-58.  Parameter-free (both LayerNorms are non-affine); its arithmetic is part
+    of the K13 kernel, the module exists for structural parity."""
+
+    def __init__(self, chan1: int, chan2: int, chan3: int = 0):
+        super().__init__()
+        self.chan1, self.chan2, self.chan3 = chan1, chan2, chan3
+
+
+class AttentionalPooler(nn.Module, _PackedWeights):
+    """embedding_manager.py:100-321."""
+
+    def __init__(self, layer_idx: int, feat_dim: int, feat_reduction_ratio: int = 8, infeat_grad_scale: float = 0.5):
+        super().__init__()
+        self.n_heads = 8
+        self.layer_inner_dim = feat_dim
+        self.lora_dim = int(feat_dim / feat_reduction_ratio)
+        if self.lora_dim * 8 != feat_dim:
+            raise NotImplementedError("adaface_b200.AttentionalPooler: feat_reduction_ratio must be 8 (kernel layout)")
+        conv = lambda: nn.Conv1d(feat_dim, self.lora_dim, kernel_size=1, groups=self.n_heads, bias=False)
+        self.lora_to_k, self.lora_to_fg_q, self.lora_to_bg_q = conv(), conv(), conv()
+        self.conv1d_extra_scale = self.n_heads ** -0.5
+        self.layer_idx = layer_idx
+        self.infeat_grad_scale = infeat_grad_scale
+        self.is_fgbg_competitive = True
+        self.attn_drop = nn.Dropout(0.1)
+        self.out_drop = nn.Dropout(0.1)
+
+    def _build_pack(self):
+        return {k: _f32(getattr(self, k).weight.squeeze(-1)) for k in ("lora_to_k", "lora_to_fg_q", "lora_to_bg_q")}
+
+    def forward(self, layer_attn_components: Dict, fg_q_emb: Tensor, bg_q_emb: Tensor, img_mask: Optional[Tensor] = None,
+                debug: bool = False, want_attn: bool = True):
+        if self.training:
+            raise NotImplementedError("adaface_b200.AttentionalPooler: the kernel path implements eval mode "
+                                      "(Dropout(0.1) on the attention is train-only); call .eval()")
+        x, q = layer_attn_components["x"], layer_attn_components["q"]
+        to_k = layer_attn_components["to_k"]
+        infeat_size = layer_attn_components.get("infeat_size")
+        b, n, c = x.shape
+        p = self.packed()
+        if bg_q_emb.dim() == 1:
+            bg_q_emb = bg_q_emb[None].expand(b, -1)
+        lora_q = ops.ada_pool_prep(to_k.weight.detach(), fg_q_emb.reshape(-1), bg_q_emb.reshape(b, -1),
+                                   p["lora_to_fg_q"], p["lora_to_bg_q"])                       # :186-235
+        key_mask = None
+        if img_mask is not None:                                                                # :259-269
+            m = F.interpolate(img_mask.float(), size=infeat_size, mode="nearest").reshape(b, -1)
+            key_mask = m.bool().to(torch.uint8).contiguous()
+        fg, bg, a_fg, a_bg = ops.ada_pool(as_bf16_tokens(x), as_bf16_tokens(q), lora_q, p["lora_to_k"], key_mask,
+                                          want_attn)
+        out = {"fg_out": fg, "bg_out": bg}
+        if want_attn:
+            out["attn_fg"], out["attn_bg"] = a_fg, a_bg
+        return out
+
+
+class AdaEmbedding(nn.Module, _PackedWeights):
+    """embedding_manager.py:539-910.  Built for the attention-pooler variant in its two-stream (H = 2)
+    configuration - the only one in which the reference's own forward is self-consistent -
+    plus the bg-token variant that reuses a cached bg pooling (`use_cached_bg`)."""
+
+    def __init__(self, num_layers: int = 16, num_vectors_per_subj_token: int = 1, fg_emb_count: int = 1,
+                 bg_emb_count: int = 0, use_cached_bg: bool = False, out_emb_dim: int = 768, r: int = 12,
+                 init_string=None, init_vecs: Optional[Tensor] = None, ca_infeat_dims=CA_INFEAT_DIMS,
+                 layer_idx2ca_layer_idx=LAYER_IDX2CA_LAYER_IDX, has_bias: bool = True, use_attn_pooler: bool = True,
+                 attn_pooler_feat_reduction_ratio: int = 8, token_string: str = "", placeholder_is_bg: bool = False,
+                 do_zero_shot: bool = False, device_type: str = "cuda"):
+        super().__init__()
+        if not use_attn_pooler:
+            raise NotImplementedError("adaface_b200.AdaEmbedding: only use_attn_pooler=True is built")
+        if do_zero_shot and not has_bias:
+            raise ValueError("Zero-shot AdaEmbedding must set has_bias=True")
+        if num_layers != len(layer_idx2ca_layer_idx):
+            raise ValueError(f"num_layers={num_layers} != len(layer_idx2ca_layer_idx)={len(layer_idx2ca_layer_idx)}")
+        self.do_zero_shot = do_zero_shot
+        self.token_string = token_string
+        self.num_layers = num_layers
+        self.out_emb_dim = out_emb_dim
+        self.K = K = num_vectors_per_subj_token
+        self.fg_emb_count, self.bg_emb_count = fg_emb_count, bg_emb_count
+        if fg_emb_count + bg_emb_count > K:
+            raise ValueError(f"fg_emb_count={fg_emb_count} + bg_emb_count={bg_emb_count} > num_vectors_per_subj_token={K}")
+        self.placeholder_is_bg = placeholder_is_bg
+        self.use_cached_bg = use_cached_bg
+        if use_cached_bg:
+            self.cached_bg_weight = nn.Parameter(torch.tensor(0.5), requires_grad=True)
+        self.is_fg_only = fg_emb_count == K
+        self.is_bg_only = bg_emb_count == K
+        self.is_one_stream_only = self.is_fg_only or self.is_bg_only
+        self.r = r
+        self.use_attn_pooler = use_attn_pooler
+        self.attn_pooler_feat_reduction_ratio = attn_pooler_feat_reduction_ratio
+        self.emb_infeat_types = [0] * fg_emb_count + [1] * bg_emb_count + [2] * (K - fg_emb_count - bg_emb_count)
+        self.device_type = device_type
+        self.layer_idx2ca_layer_idx = dict(layer_idx2ca_layer_idx)
+        self.ca_layer_idx2layer_idx = {v: k for k, v in self.layer_idx2ca_layer_idx.items()}
+        self.H = H = 1 if self.is_one_stream_only else 2
+        time_h = max([2 if t == 2 else 1 for t in self.emb_infeat_types] or [1])
+        self.TD_frac = 0.25 * time_h
+
+        if init_vecs is not None:
+            if init_vecs.shape[1] != out_emb_dim or init_vecs.shape[0] > num_layers:
+                raise ValueError(f"AdaEmbedding LoRA init vectors shape {tuple(init_vecs.shape)} must be "
+                                 f"(<={num_layers}, {out_emb_dim})")
+            self.N = n0 = init_vecs.shape[0]
+            self.pre_vecs = None if do_zero_shot else nn.Parameter(init_vecs.unsqueeze(0).repeat(K, 1, 1))
+        else:
+            self.N = n0 = 0
+            self.pre_vecs = None
+        if not do_zero_shot:
+            basis = F.normalize(torch.randn(K, r - n0, out_emb_dim), dim=-1) / 4.
+            basis[:, -1] = 0
+            self.basis_vecs = nn.Parameter(basis)
+        else:
+            self.basis_vecs = None
+
+        self.ca_infeat_dims = list(ca_infeat_dims)
+        self.poolers = nn.ModuleList([AttentionalPooler(i, self.ca_infeat_dims[i], attn_pooler_feat_reduction_ratio, 1)
+                                      for i in range(num_layers)])
+        self.TDs = [int(self.TD_frac * d) for d in self.ca_infeat_dims]
+        self.layer_coeff_maps = nn.ModuleList([nn.Linear(d * H + td, r * K, bias=True)
+                                               for d, td in zip(self.ca_infeat_dims, self.TDs)])
+        self.layers_out_lns = nn.ModuleList([nn.ModuleList([nn.LayerNorm(out_emb_dim, elementwise_affine=False)
+                                                            for _ in range(K)]) for _ in range(num_layers)])
+        self.layer_lncat3s = nn.ModuleList([LNCat3(d * H, td) for d, td in zip(self.ca_infeat_dims, self.TDs)])
+        self.reduce_fg_bg_cross_weights()
+        self.has_bias = has_bias
+        self.bias = nn.Parameter(torch.zeros(num_layers, K, out_emb_dim)) if (has_bias and not do_zero_shot) else None
+        self.call_count = 0
+        self.debug = False
+
+    @torch.no_grad()
+    def reduce_fg_bg_cross_weights(self, reduced_layer_idx: Optional[int] = None):
+        """embedding_manager.py:719-773 (init-time): caps the cross-stream weights of the coefficient maps -
+        bg->fg-embedding and fg->bg-embedding blocks - at 1 % of the matching in-stream mean magnitude."""
+        if self.H == 1:
+            return
+        max_ratio = 0.01
+        layers = range(self.num_layers) if reduced_layer_idx is None else [reduced_layer_idx]
+        for li in layers:
+            d = self.ca_infeat_dims[li]
+            w = self.layer_coeff_maps[li].weight.data.view(self.K, self.r, -1)
+            for k, kind in enumerate(self.emb_infeat_types):
+                if kind == 2:
+                    continue
+                own, cross = (slice(0, d), slice(d, 2 * d)) if kind == 0 else (slice(d, 2 * d), slice(0, d))
+                own_mean = w[k][:, own].abs().mean().item()
+                cross_mean = w[k][:, cross].abs().mean().item()
+                w[k][:, cross] *= min(1, max_ratio * own_mean / (cross_mean + 1e-6))
+
+    def _pack_key(self):
+        ps = [p for p in (self.pre_vecs, self.basis_vecs, self.bias) if p is not None]
+        ps += [p for m in self.layer_coeff_maps for p in m.parameters()]
+        return tuple((p.data_ptr(), p._version, p.dtype) for p in ps)
+
+    def _build_pack(self):
+        out = {}
+        if self.basis_vecs is not None:
+            basis = self.basis_vecs if self.pre_vecs is None else torch.cat([self.pre_vecs, self.basis_vecs], dim=1)
+            out["basis"] = _f32(basis)                                                          # :874
+        for i, m in enumerate(self.layer_coeff_maps):
+            out[f"cw{i}"], out[f"cb{i}"] = _f32(m.weight), _f32(m.bias)
+        if self.bias is not None:
+            out["bias"] = _f32(self.bias)
+        return out
+
+    def forward(self, layer_idx: int, layer_attn_components: Dict, time_emb: Tensor, layer_subj_emb_probe: Tensor,
+                layer_static_extra_emb_mean: Tensor, img_mask: Optional[Tensor] = None,
+                cached_pooler_bg_out: Optional[Tensor] = None, zs_basis_vecs: Optional[Tensor] = None):
+        ca = self.layer_idx2ca_layer_idx[layer_idx]
+        if self.H != 2:
+            # the reference concatenates fg and bg features unconditionally (:831) into a Linear sized for one
+            # stream when H == 1, and raises
+            raise RuntimeError("AdaEmbedding.forward needs both fg and bg embeddings (fg_emb_count, bg_emb_count > 0)")
+        if self.use_cached_bg and cached_pooler_bg_out is None:
+            raise ValueError("AdaEmbedding(use_cached_bg=True) needs cached_pooler_bg_out")             # :789-792
+        if self.do_zero_shot:
+            raise NotImplementedError("adaface_b200.AdaEmbedding: per-instance zero-shot basis vectors are not built yet")
+        pooled = self.poolers[ca](layer_attn_components, layer_subj_emb_probe, layer_static_extra_emb_mean,
+                                  img_mask=img_mask, want_attn=getattr(self, "want_pooler_attn", True))   # :815-819
+        infeat_fg = pooled.pop("fg_out")                                                        # :823-829
+        infeat_bg = cached_pooler_bg_out if self.use_cached_bg else pooled["bg_out"]
+        p = self.packed()
+        out = ops.ada_head(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"], p["basis"],
+                           None if self.bias is None else p["bias"][ca])                        # :847-893
+        return out, pooled

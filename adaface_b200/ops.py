@@ -7,7 +7,7 @@ fallback - a non-CUDA tensor or a missing library raises.
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional, Tuple
+from typing import Dict, List, Optional, Tuple
 
 import torch
 
@@ -31,6 +31,35 @@ def _ptr(t: Optional[Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+# Optional per-launch timing (bench.py's kernel breakdown / roofline): CUDA events on the launching stream
+# around every C-ABI call, with the call's algorithmic FLOPs and bytes.  Off (None) on the normal path.
+_TIMING: Optional[List[tuple]] = None
+
+
+def start_timing() -> None:
+    global _TIMING
+    _TIMING = []
+
+
+def stop_timing() -> List[Dict]:
+    """Returns one record per C-ABI call since start_timing(): name, shape tag, ms, flops, bytes."""
+    global _TIMING
+    recs, _TIMING = _TIMING or [], None
+    torch.cuda.synchronize()
+    return [{"name": n, "tag": tag, "ms": e0.elapsed_time(e1), "flops": fl, "bytes": by} for n, tag, fl, by, e0, e1 in recs]
+
+
+def _run(name: str, fn, *args, flops: float = 0.0, nbytes: float = 0.0, tag: str = "") -> None:
+    if _TIMING is None:
+        check(fn(*args), name)
+        return
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    check(fn(*args), name)
+    e1.record()
+    _TIMING.append((name, tag, flops, nbytes, e0, e1))
+
+
 # ------------------------------------------------------------------------------------------- K14
 @torch.library.custom_op("adaface_b200::cfg_ddim_step", mutates_args=())
 def cfg_ddim_step(x: Tensor, e_cond: Tensor, e_uncond: Tensor, noise: Optional[Tensor], guidance_scale: float,
@@ -44,9 +73,9 @@ def cfg_ddim_step(x: Tensor, e_cond: Tensor, e_uncond: Tensor, noise: Optional[T
     x, e_cond, e_uncond = x.contiguous(), e_cond.contiguous(), e_uncond.contiguous()
     noise = None if noise is None else noise.contiguous()
     x_prev, pred_x0 = torch.empty_like(x), torch.empty_like(x)
-    check(_lib.load().afb_cfg_ddim_step(_ptr(x), _ptr(e_cond), _ptr(e_uncond), _ptr(noise), _ptr(x_prev),
-                                        _ptr(pred_x0), x.numel(), guidance_scale, a_t, a_prev, sigma_t,
-                                        sqrt_one_minus_at, temperature, _stream()), "cfg_ddim_step")
+    _run("cfg_ddim_step", _lib.load().afb_cfg_ddim_step, _ptr(x), _ptr(e_cond), _ptr(e_uncond), _ptr(noise),
+         _ptr(x_prev), _ptr(pred_x0), x.numel(), guidance_scale, a_t, a_prev, sigma_t, sqrt_one_minus_at, temperature,
+         _stream(), nbytes=4.0 * x.numel() * (5 + (noise is not None)))
     return x_prev, pred_x0
 
 
@@ -72,8 +101,8 @@ def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: f
     lib = _lib.load()
     ws = torch.empty(int(lib.afb_groupnorm_ws_floats(b, hw, groups)), dtype=torch.float32, device=x.device)
     y = torch.empty((b, hw, c), dtype=torch.bfloat16, device=x.device)
-    check(lib.afb_groupnorm_tokens(_ptr(x), layout, _ptr(gamma), _ptr(beta), _ptr(y), _ptr(ws), b, c, hw, groups,
-                                   eps, _stream()), "groupnorm_tokens")
+    _run("groupnorm_tokens", lib.afb_groupnorm_tokens, _ptr(x), layout, _ptr(gamma), _ptr(beta), _ptr(y), _ptr(ws), b, c,
+         hw, groups, eps, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"C{c}")
     return y
 
 
@@ -91,8 +120,8 @@ def layernorm(x: Tensor, gamma: Optional[Tensor], beta: Optional[Tensor], eps: f
         raise ValueError("layernorm: contiguous bf16 input expected")
     y = torch.empty_like(x)
     c = x.shape[-1]
-    check(_lib.load().afb_layernorm_bf16(_ptr(x), _ptr(gamma), _ptr(beta), _ptr(y), x.numel() // c, c, eps,
-                                         _stream()), "layernorm")
+    _run("layernorm", _lib.load().afb_layernorm_bf16, _ptr(x), _ptr(gamma), _ptr(beta), _ptr(y), x.numel() // c, c, eps,
+         _stream(), nbytes=4.0 * x.numel(), tag=f"C{c}")
     return y
 
 
@@ -114,7 +143,9 @@ def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: O
                     epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
                     residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
                     else _lib.DT_BF16, hw=hw)
-    check(_lib.load().afb_gemm_bf16(C.byref(args), _stream()), "gemm_bf16")
+    m, n, k = a.shape[0], w.shape[0], a.shape[1]
+    _run("gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
+         nbytes=2.0 * (m * k + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}")
 
 
 @torch.library.custom_op("adaface_b200::linear", mutates_args=())
@@ -197,7 +228,8 @@ def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float, key_mas
     args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=_ptr(key_mask), batch=b, heads=heads,
                     head_dim=c // heads, q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"),
                     ldo=c, scale=scale)
-    check(_lib.load().afb_attention_fwd(C.byref(args), _stream()), "attention_fwd")
+    _run("attention_fwd", _lib.load().afb_attention_fwd, C.byref(args), _stream(), flops=4.0 * b * nq * nk * c,
+         nbytes=2.0 * b * c * (2 * nq + 2 * nk), tag=f"b{b}q{nq}k{nk}d{c // heads}")
     return out
 
 
@@ -216,9 +248,9 @@ def ada_pool_prep(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_
     b = bg_q_emb.shape[0]
     f = lambda t: t.to(torch.float32).contiguous()
     lora_q = torch.empty((b, 2, c // 8), dtype=torch.float32, device=to_k_weight.device)
-    check(_lib.load().afb_ada_pool_prep(_ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)), _ptr(f(bg_q_emb)),
-                                        _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(lora_q), b, c, _stream()),
-          "ada_pool_prep")
+    _run("ada_pool_prep", _lib.load().afb_ada_pool_prep, _ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)),
+         _ptr(f(bg_q_emb)), _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(lora_q), b, c, _stream(),
+         nbytes=4.0 * c * ctx_dim)
     return lora_q
 
 
@@ -246,9 +278,9 @@ def ada_pool(x: Tensor, q: Tensor, lora_q: Tensor, lora_to_k: Tensor, key_mask: 
     if key_mask is not None:
         key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
     wk = lora_to_k.to(torch.float32).contiguous()
-    check(lib.afb_ada_pool(_ptr(x), _ptr(q), _ptr(lora_q.contiguous()), _ptr(wk), _ptr(key_mask), _ptr(fg), _ptr(bg),
-                           _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c,
-                           _stream()), "ada_pool")
+    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(lora_q.contiguous()), _ptr(wk), _ptr(key_mask), _ptr(fg),
+         _ptr(bg), _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c, _stream(),
+         nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     return fg, bg, a_fg, a_bg
 
 
@@ -273,9 +305,9 @@ def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, co
     if coeff_w.shape != (k * r, 2 * c + td):
         raise ValueError(f"ada_head: coefficient map {tuple(coeff_w.shape)} does not match ({k * r}, {2 * c + td})")
     out = torch.empty((b, k, d), dtype=torch.float32, device=infeat_fg.device)
-    check(_lib.load().afb_ada_head(_ptr(infeat_fg), _ptr(infeat_bg), _ptr(time_emb), time_emb.stride(0), _ptr(coeff_w),
-                                   _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), b, c, td, k, r, d, _stream()),
-          "ada_head")
+    _run("ada_head", _lib.load().afb_ada_head, _ptr(infeat_fg), _ptr(infeat_bg), _ptr(time_emb), time_emb.stride(0),
+         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), b, c, td, k, r, d, _stream(),
+         nbytes=4.0 * (coeff_w.numel() + basis.numel()))
     return out
 
 
@@ -292,7 +324,8 @@ def to_bf16(x: Tensor) -> Tensor:
         raise ValueError("to_bf16: fp32 input expected")
     x = x.contiguous()
     y = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
-    check(_lib.load().afb_cast_f32_to_bf16(_ptr(x), _ptr(y), x.numel(), _stream()), "cast_f32_to_bf16")
+    _run("cast_f32_to_bf16", _lib.load().afb_cast_f32_to_bf16, _ptr(x), _ptr(y), x.numel(), _stream(),
+         nbytes=6.0 * x.numel())
     return y
 
 
@@ -308,7 +341,8 @@ def to_f32(x: Tensor) -> Tensor:
         raise ValueError("to_f32: bf16 input expected")
     x = x.contiguous()
     y = torch.empty(x.shape, dtype=torch.float32, device=x.device)
-    check(_lib.load().afb_cast_bf16_to_f32(_ptr(x), _ptr(y), x.numel(), _stream()), "cast_bf16_to_f32")
+    _run("cast_bf16_to_f32", _lib.load().afb_cast_bf16_to_f32, _ptr(x), _ptr(y), x.numel(), _stream(),
+         nbytes=6.0 * x.numel())
     return y
 
 

@@ -1,0 +1,72 @@
+"""Multi-GPU sampling: shard the sample / prompt axis across ranks, one process per GPU.
+
+The reference samples on a single GPU (scripts/stable_txt2img.py:238,342); each sample's DDIM trajectory
+depends only on its own x_T and context, so the path shards with NO collective inside the step loop
+(SURVEY.md 8e).  The only exchange is one all-gather of the final latents (NCCL over NVLink on the GPU box,
+gloo in the CPU tests).  A sample's CFG pair (cond, uncond) always stays on one rank.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+Tensor = torch.Tensor
+
+
+def shard_bounds(n_items: int, world_size: int) -> List[Tuple[int, int]]:
+    """Contiguous, balanced [lo, hi) ranges; the first n_items % world_size ranks hold one extra item."""
+    if n_items < 0 or world_size <= 0:
+        raise ValueError("shard_bounds: n_items >= 0 and world_size > 0 expected")
+    base, extra = divmod(n_items, world_size)
+    out, lo = [], 0
+    for r in range(world_size):
+        hi = lo + base + (1 if r < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def shard_layerwise_context(context: Tensor, lo: int, hi: int, n_items: int) -> Tensor:
+    """context [16*n, T, D] is instance-major / layer-minor (embedding_manager.py:1345-1349) or [n, T, D]."""
+    if context.shape[0] % n_items:
+        raise ValueError(f"context batch {context.shape[0]} is not a multiple of the sample count {n_items}")
+    per = context.shape[0] // n_items
+    return context[lo * per:hi * per]
+
+
+def all_gather_samples(local: Tensor, bounds: Sequence[Tuple[int, int]], group=None) -> Tensor:
+    """Gathers per-rank [n_r, ...] latents into [n, ...] on every rank (ranks may hold unequal counts)."""
+    world = len(bounds)
+    if world == 1 or not (dist.is_available() and dist.is_initialized()):
+        return local
+    counts = [hi - lo for lo, hi in bounds]
+    width = max(counts)
+    item_shape = tuple(local.shape[1:])
+    padded = local.new_zeros((width,) + item_shape)
+    padded[:local.shape[0]] = local
+    bufs = [torch.empty_like(padded) for _ in range(world)]
+    dist.all_gather(bufs, padded.contiguous(), group=group)
+    return torch.cat([b[:c] for b, c in zip(bufs, counts)], dim=0)
+
+
+def sample_sharded(run_local: Callable[[Tensor, Tensor, Tensor], Tensor], x_T: Tensor, c_cond: Tensor,
+                   c_uncond: Tensor, rank: Optional[int] = None, world_size: Optional[int] = None,
+                   gather: bool = True, group=None) -> Tensor:
+    """Runs `run_local(x_T_shard, c_cond_shard, c_uncond_shard) -> latents_shard` on this rank's slice of the
+    samples and all-gathers the result.  x_T [n, 4, h, w] must be the SAME tensor on every rank (drawn from one
+    seed), so that the union over ranks equals the single-GPU run sample for sample."""
+    if world_size is None:
+        world_size = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    if rank is None:
+        rank = dist.get_rank(group) if dist.is_available() and dist.is_initialized() else 0
+    n = x_T.shape[0]
+    bounds = shard_bounds(n, world_size)
+    lo, hi = bounds[rank]
+    if hi > lo:
+        out = run_local(x_T[lo:hi], shard_layerwise_context(c_cond, lo, hi, n),
+                        shard_layerwise_context(c_uncond, lo, hi, n))
+    else:
+        out = x_T[:0].clone()
+    return all_gather_samples(out, bounds, group) if gather else out

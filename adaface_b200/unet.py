@@ -1,0 +1,406 @@
+"""Minimal SD-1.5 U-Net shell around the hot path, so that one full DDIM step can run and be timed on the GPU
+box (reference: ldm/modules/diffusionmodules/openaimodel.py - UNetModel :417-1052, ResBlock :167-281,
+Upsample/Downsample :95-165, TimestepEmbedSequential :76-92; timestep_embedding diffusionmodules/util.py:154).
+
+What is product here: the 16 `SpatialTransformer`s (adaface_b200.attention), the per-layer context plumbing
+(`get_layer_context`, openaimodel.py:863-920) and the AdaEmbedding wiring (`AdaPromptContext`).  The ResBlock /
+up / down-sample convolutions are deliberately left on torch (cuDNN, bf16 channels-last) - `north_star` keeps them
+outside the scope and reports them separately; this file only wraps them.  State-dict keys equal the reference's
+UNetModel, so an SD-1.5 checkpoint (`model.diffusion_model.*`) loads unchanged.
+
+Activations between blocks are bf16 channels-last: a [B, C, H, W] channels-last tensor IS the token-major
+[B, H*W, C] layout the transformer kernels use, so no transposition happens at a SpatialTransformer's edges.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from . import ops
+from .attention import SpatialTransformer, _PackedWeights
+from .embedding import LAYER_IDX2CA_LAYER_IDX, AdaEmbedding
+
+Tensor = torch.Tensor
+CL = torch.channels_last
+
+
+def timestep_embedding(timesteps: Tensor, dim: int, max_period: int = 10000) -> Tensor:
+    """diffusionmodules/util.py:154-174 (fp32 sinusoid, cos first)."""
+    half = dim // 2
+    freqs = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32, device=timesteps.device) / half)
+    args = timesteps[:, None].float() * freqs[None]
+    emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+    if dim % 2:
+        emb = torch.cat([emb, torch.zeros_like(emb[:, :1])], dim=-1)
+    return emb
+
+
+class TimestepBlock(nn.Module):
+    pass
+
+
+class GroupNorm32(nn.GroupNorm):
+    """diffusionmodules/util.py:217-219 (eps 1e-5).  fp32 statistics on the bf16 activation."""
+
+    def forward(self, x):
+        return F.group_norm(x, self.num_groups, self.weight, self.bias, self.eps)
+
+
+class _Bf16Conv(nn.Conv2d):
+    """nn.Conv2d holding fp32 master weights (state-dict compatible) and convolving in bf16 channels-last."""
+
+    def _w(self):
+        key = (self.weight.data_ptr(), self.weight._version)
+        c = self.__dict__.get("_bf16_cache")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                w = self.weight.detach().to(torch.bfloat16).contiguous(memory_format=CL)
+                b = None if self.bias is None else self.bias.detach().to(torch.bfloat16)
+            c = (key, w, b)
+            self.__dict__["_bf16_cache"] = c
+        return c[1], c[2]
+
+    def forward(self, x):
+        w, b = self._w()
+        return F.conv2d(x, w, b, self.stride, self.padding)
+
+
+class Upsample(nn.Module):
+    def __init__(self, channels: int, use_conv: bool, dims: int = 2, out_channels: Optional[int] = None, padding: int = 1):
+        super().__init__()
+        self.channels, self.out_channels, self.use_conv = channels, out_channels or channels, use_conv
+        if use_conv:
+            self.conv = _Bf16Conv(channels, self.out_channels, 3, padding=padding)
+
+    def forward(self, x):
+        x = F.interpolate(x, scale_factor=2, mode="nearest")
+        return self.conv(x) if self.use_conv else x
+
+
+class Downsample(nn.Module):
+    def __init__(self, channels: int, use_conv: bool, dims: int = 2, out_channels: Optional[int] = None, padding: int = 1):
+        super().__init__()
+        self.channels, self.out_channels, self.use_conv = channels, out_channels or channels, use_conv
+        self.op = _Bf16Conv(channels, self.out_channels, 3, stride=2, padding=padding) if use_conv \
+            else nn.AvgPool2d(kernel_size=2, stride=2)
+
+    def forward(self, x):
+        return self.op(x)
+
+
+class ResBlock(TimestepBlock):
+    """openaimodel.py:167-281 without up/down and scale-shift norm (SD-1.5 uses neither).  torch path."""
+
+    def __init__(self, channels: int, emb_channels: int, dropout: float, out_channels: Optional[int] = None, **_):
+        super().__init__()
+        self.channels, self.out_channels = channels, out_channels or channels
+        oc = self.out_channels
+        self.in_layers = nn.Sequential(GroupNorm32(32, channels), nn.SiLU(), _Bf16Conv(channels, oc, 3, padding=1))
+        self.emb_layers = nn.Sequential(nn.SiLU(), nn.Linear(emb_channels, oc))
+        self.out_layers = nn.Sequential(GroupNorm32(32, oc), nn.SiLU(), nn.Dropout(p=dropout),
+                                        _Bf16Conv(oc, oc, 3, padding=1))
+        self.skip_connection = nn.Identity() if oc == channels else _Bf16Conv(channels, oc, 1)
+
+    def forward(self, x, emb):
+        h = self.in_layers(x)
+        e = self.emb_layers(emb).to(h.dtype)
+        h = h + e[:, :, None, None]
+        h = self.out_layers(h)
+        return self.skip_connection(x) + h
+
+
+class TimestepEmbedSequential(nn.Sequential, TimestepBlock):
+    """openaimodel.py:76-92."""
+
+    def forward(self, x, emb, context=None, mask=None):
+        for layer in self:
+            if isinstance(layer, TimestepBlock):
+                x = layer(x, emb)
+            elif isinstance(layer, SpatialTransformer):
+                x = layer(x, context, mask=mask)
+            else:
+                x = layer(x)
+        return x
+
+
+class AdaSubject:
+    """One subject token's per-step conditioning: an AdaEmbedding, the K token positions its
+    vectors occupy in the 77-token prompt, the per-layer static probe [16, ctx_dim] (fg pooling query) and the
+    per-layer static extra-embedding mean [16, n_instances, ctx_dim] (bg pooling query)."""
+
+    def __init__(self, embedder: AdaEmbedding, token_positions: Sequence[int], layer_probes: Tensor,
+                 layer_extra_means: Tensor, n_instances: int, cached_bg_from: Optional[int] = None):
+        self.embedder = embedder
+        self.token_positions = list(token_positions)
+        self.layer_probes = layer_probes
+        self.layer_extra_means = layer_extra_means
+        self.n_instances = n_instances          # the first n instances of the batch hold the subject (cond half: F8)
+        self.cached_bg_from = cached_bg_from    # index of the fg subject whose bg pooling this (bg) token reuses
+        if len(self.token_positions) != embedder.K:
+            raise ValueError(f"AdaSubject: {len(self.token_positions)} token positions for K={embedder.K} vectors")
+
+
+class AdaPromptContext:
+    """Reconstruction of the removed `get_layer_ada_conditioning()` call site (embedding_manager.py:1754,
+    SURVEY.md F1/3.2): at every cross-attention layer and every step, after attn2.to_q and before to_k/to_v, each
+    subject's AdaEmbedding turns the layer's pooled features into K vectors that overwrite the subject's token
+    rows of that layer's context."""
+
+    def __init__(self, subjects: Sequence[AdaSubject], img_mask: Optional[Tensor] = None):
+        self.subjects = list(subjects)
+        self.img_mask = img_mask
+        self._pos = {}
+
+    def positions(self, i: int, device) -> Tensor:
+        key = (i, str(device))
+        if key not in self._pos:
+            self._pos[key] = torch.tensor(self.subjects[i].token_positions, dtype=torch.long, device=device)
+        return self._pos[key]
+
+    def apply(self, layer_idx: int, comps: Dict, layer_ctx: Tensor, time_emb: Tensor) -> Tensor:
+        """layer_ctx bf16 [B, T, ctx_dim] (this call's private copy) is updated in place and returned."""
+        ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
+        bg_cache: Dict[int, Tensor] = {}
+        for i, s in enumerate(self.subjects):
+            n = s.n_instances
+            sub = {"x": comps["x"][:n], "q": comps["q"][:n], "to_k": comps["to_k"], "infeat_size": comps["infeat_size"]}
+            cached = bg_cache.get(s.cached_bg_from) if s.cached_bg_from is not None else None
+            mask = None if self.img_mask is None else self.img_mask[:n]
+            vecs, pooled = s.embedder(layer_idx, sub, time_emb[:n], s.layer_probes[ca], s.layer_extra_means[ca][:n],
+                                      img_mask=mask, cached_pooler_bg_out=cached)
+            bg_cache[i] = pooled["bg_out"]
+            layer_ctx[:n, self.positions(i, layer_ctx.device)] = vecs.to(layer_ctx.dtype)
+        return layer_ctx
+
+
+class UNetModel(nn.Module):
+    """openaimodel.py:417-1052, restricted to what SD-1.5 instantiates (v1-inference-ada.yaml:35-51):
+    use_spatial_transformer=True, conv_resample=True, no class conditioning, no scale-shift norm."""
+
+    def __init__(self, image_size: int = 32, in_channels: int = 4, model_channels: int = 320, out_channels: int = 4,
+                 num_res_blocks: int = 2, attention_resolutions: Sequence[int] = (4, 2, 1), dropout: float = 0,
+                 channel_mult: Sequence[int] = (1, 2, 4, 4), conv_resample: bool = True, dims: int = 2,
+                 num_classes=None, use_checkpoint: bool = False, use_fp16: bool = False, num_heads: int = 8,
+                 num_head_channels: int = -1, num_heads_upsample: int = -1, use_scale_shift_norm: bool = False,
+                 resblock_updown: bool = False, use_new_attention_order: bool = False,
+                 use_spatial_transformer: bool = True, transformer_depth: int = 1, context_dim: int = 768,
+                 n_embed=None, legacy: bool = False):
+        super().__init__()
+        if not use_spatial_transformer or dims != 2 or num_classes is not None or use_scale_shift_norm \
+                or resblock_updown or not conv_resample:
+            raise NotImplementedError("adaface_b200.UNetModel builds the SD-1.5 configuration only")
+        if isinstance(context_dim, (list, tuple)):
+            context_dim = context_dim[0]
+        self.image_size, self.in_channels, self.model_channels = image_size, in_channels, model_channels
+        self.out_channels, self.num_res_blocks = out_channels, num_res_blocks
+        self.attention_resolutions, self.channel_mult = tuple(attention_resolutions), tuple(channel_mult)
+        self.num_heads, self.num_head_channels = num_heads, num_head_channels
+        self.num_classes = None
+        self.dtype = torch.bfloat16
+        mc = model_channels
+        ted = mc * 4
+        self.time_embed = nn.Sequential(nn.Linear(mc, ted), nn.SiLU(), nn.Linear(ted, ted))
+
+        def transformer(ch):
+            if num_head_channels == -1:
+                heads, dim_head = num_heads, ch // num_heads
+            else:
+                heads, dim_head = ch // num_head_channels, num_head_channels
+            if legacy:
+                dim_head = ch // heads
+            return SpatialTransformer(ch, heads, dim_head, depth=transformer_depth, context_dim=context_dim)
+
+        self.input_blocks = nn.ModuleList([TimestepEmbedSequential(_Bf16Conv(in_channels, mc, 3, padding=1))])
+        chans, ch, ds = [mc], mc, 1
+        for level, mult in enumerate(self.channel_mult):
+            for _ in range(num_res_blocks):
+                layers: List[nn.Module] = [ResBlock(ch, ted, dropout, out_channels=mult * mc)]
+                ch = mult * mc
+                if ds in self.attention_resolutions:
+                    layers.append(transformer(ch))
+                self.input_blocks.append(TimestepEmbedSequential(*layers))
+                chans.append(ch)
+            if level != len(self.channel_mult) - 1:
+                self.input_blocks.append(TimestepEmbedSequential(Downsample(ch, True, out_channels=ch)))
+                chans.append(ch)
+                ds *= 2
+        self.middle_block = TimestepEmbedSequential(ResBlock(ch, ted, dropout), transformer(ch), ResBlock(ch, ted, dropout))
+        self.output_blocks = nn.ModuleList([])
+        for level, mult in list(enumerate(self.channel_mult))[::-1]:
+            for i in range(num_res_blocks + 1):
+                layers = [ResBlock(ch + chans.pop(), ted, dropout, out_channels=mult * mc)]
+                ch = mult * mc
+                if ds in self.attention_resolutions:
+                    layers.append(transformer(ch))
+                if level and i == num_res_blocks:
+                    layers.append(Upsample(ch, True, out_channels=ch))
+                    ds //= 2
+                self.output_blocks.append(TimestepEmbedSequential(*layers))
+        self.out = nn.Sequential(GroupNorm32(32, ch), nn.SiLU(), _Bf16Conv(mc, out_channels, 3, padding=1))
+
+    # ---------------------------------------------------------------------------------------------------------
+    def spatial_transformers(self):
+        """(layer_idx, module) of the 16 conditioned layers, in execution order (openaimodel.py:876-877)."""
+        blocks = list(self.input_blocks) + [self.middle_block] + list(self.output_blocks)
+        return [(i, m) for i, blk in enumerate(blocks) for m in blk if isinstance(m, SpatialTransformer)]
+
+    def set_cross_attn_flags(self, ca_flag_dict: Dict, ca_layer_indices=None):
+        """openaimodel.py:723-824 (the part the sampling path uses): pushes flags into every attn2's __dict__;
+        a key 'name:layerwise' carries one value per cross-attention layer."""
+        old = {}
+        for layer_idx, st in self.spatial_transformers():
+            if ca_layer_indices is not None and layer_idx not in ca_layer_indices:
+                continue
+            ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
+            attn2 = st.transformer_blocks[0].attn2
+            for k, v in ca_flag_dict.items():
+                name, _, kind = k.partition(":")
+                old.setdefault(k, {})[layer_idx] = attn2.__dict__.get(name)
+                attn2.__dict__[name] = v[ca] if kind == "layerwise" else v
+        return old
+
+    def forward(self, x: Tensor, timesteps: Optional[Tensor] = None, context: Optional[Tensor] = None, y=None,
+                context_in=None, extra_info: Optional[Dict] = None, **kwargs) -> Tensor:
+        """x [B, 4, H, W]; context [16*B, T, 768] instance-major / layer-minor (embedding_manager.py:1345-1349) when
+        extra_info['use_layerwise_context'] (the only mode in which the reference U-Net works), else
+        [B, T, 768] shared by all layers.  Returns eps in x's dtype."""
+        extra_info = extra_info or {}
+        layerwise = extra_info.get("use_layerwise_context", False)
+        ks = extra_info.get("use_conv_attn_kernel_size", None)
+        placeholder2indices = extra_info.get("placeholder2indices", None)
+        img_mask = extra_info.get("img_mask", None)
+        ada: Optional[AdaPromptContext] = extra_info.get("ada_prompt", None)
+        b = x.shape[0]
+
+        emb = self.time_embed(timestep_embedding(timesteps, self.model_channels))                 # :846-847
+        if layerwise:                                                                             # :863-866
+            t, d = context.shape[1], context.shape[2]
+            ctx = torch.empty((16, b, t, d), dtype=torch.bfloat16, device=x.device)
+            ctx.copy_(context.reshape(b, 16, t, d).permute(1, 0, 2, 3))
+        else:
+            ctx = context.to(torch.bfloat16)
+
+        ks_layers = [(-1 if ks is None else int(ks))] * 16
+        if ks is not None and ks > 0:
+            ks_layers[6:11] = [1] * 5                                                             # :922-932
+        self.set_cross_attn_flags({"use_conv_attn_kernel_size:layerwise": ks_layers,
+                                   "is_training": extra_info.get("is_training", False)})
+
+        def layer_context(layer_idx):
+            if layer_idx not in LAYER_IDX2CA_LAYER_IDX:
+                return None
+            lc = ctx[LAYER_IDX2CA_LAYER_IDX[layer_idx]] if layerwise else ctx
+            if ada is None:
+                return lambda: ((lc, lc), placeholder2indices)                                   # :894-896,920
+
+            def with_ada(comps):
+                new = ada.apply(layer_idx, comps, lc, emb)
+                return (new, new), placeholder2indices
+            with_ada.wants_layer_attn_components = True
+            return with_ada
+
+        hs = []
+        h = x.to(torch.bfloat16).contiguous(memory_format=CL)
+        layer_idx = 0
+        for module in self.input_blocks:
+            h = module(h, emb, layer_context(layer_idx), mask=img_mask)
+            hs.append(h)
+            layer_idx += 1
+        h = self.middle_block(h, emb, layer_context(layer_idx), mask=img_mask)
+        layer_idx += 1
+        for module in self.output_blocks:
+            h = torch.cat([h, hs.pop()], dim=1).contiguous(memory_format=CL)
+            h = module(h, emb, layer_context(layer_idx), mask=img_mask)
+            layer_idx += 1
+        return self.out(h).to(x.dtype).contiguous()
+
+
+class DiffusionModel:
+    """What DDIMSampler needs from the reference's LatentDiffusion (ldm/models/diffusion/ddpm.py:244-265 schedule
+    buffers, :2292 apply_model -> DiffusionWrapper.forward :5495-5505 for conditioning_key='crossattn'), with the
+    U-Net call optionally replayed from a CUDA graph (static shapes; launch overhead of ~600 kernels per step)."""
+
+    def __init__(self, unet: UNetModel, timesteps: int = 1000, linear_start: float = 0.00085, linear_end: float = 0.012,
+                 device=None, use_cuda_graph: bool = False):
+        import numpy as np
+        self.unet = unet
+        self.device = torch.device(device) if device is not None else next(unet.parameters()).device
+        betas = np.linspace(linear_start ** 0.5, linear_end ** 0.5, timesteps, dtype=np.float64) ** 2   # util.py:22-25
+        ac = np.cumprod(1.0 - betas, axis=0)
+        f32 = lambda a: torch.tensor(a, dtype=torch.float32, device=self.device)
+        self.num_timesteps = timesteps
+        self.betas, self.alphas_cumprod = f32(betas), f32(ac)
+        self.alphas_cumprod_prev = f32(np.append(1.0, ac[:-1]))
+        self.sqrt_alphas_cumprod, self.sqrt_one_minus_alphas_cumprod = f32(np.sqrt(ac)), f32(np.sqrt(1.0 - ac))
+        self.parameterization = "eps"
+        self.use_cuda_graph = use_cuda_graph
+        self._graphs = {}
+
+    def q_sample(self, x_start, t, noise=None):
+        noise = torch.randn_like(x_start) if noise is None else noise
+        shape = (x_start.shape[0],) + (1,) * (x_start.dim() - 1)
+        return self.sqrt_alphas_cumprod[t].reshape(shape) * x_start + \
+            self.sqrt_one_minus_alphas_cumprod[t].reshape(shape) * noise
+
+    def _run(self, x, t, ctx, extra_info):
+        return self.unet(x, t, context=ctx, context_in=None, extra_info=extra_info)
+
+    @torch.no_grad()
+    def apply_model(self, x_noisy: Tensor, t: Tensor, cond):
+        if isinstance(cond, tuple):
+            ctx, _ctx_in, extra_info = cond
+        else:
+            ctx, extra_info = cond, {"use_layerwise_context": cond.shape[0] == 16 * x_noisy.shape[0]}
+        if not self.use_cuda_graph:
+            return self._run(x_noisy, t, ctx, extra_info)
+        key = (tuple(x_noisy.shape), tuple(ctx.shape), id(extra_info))
+        g = self._graphs.get(key)
+        if g is None:
+            sx, st, sc = x_noisy.clone(), t.clone(), ctx.clone()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):                       # warm-up: builds the packed weights, sets kernel attributes
+                    self._run(sx, st, sc, extra_info)
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = self._run(sx, st, sc, extra_info)
+            g = (graph, sx, st, sc, out, extra_info)
+            self._graphs[key] = g
+        graph, sx, st, sc, out, _ = g
+        sx.copy_(x_noisy)
+        st.copy_(t)
+        if sc.data_ptr() != ctx.data_ptr():
+            sc.copy_(ctx)
+        graph.replay()
+        return out
+
+
+SD15_UNET_CONFIG = dict(image_size=32, in_channels=4, out_channels=4, model_channels=320, attention_resolutions=[4, 2, 1],
+                        num_res_blocks=2, channel_mult=[1, 2, 4, 4], num_heads=8, use_spatial_transformer=True,
+                        transformer_depth=1, context_dim=768, use_checkpoint=True, legacy=False)
+
+
+@torch.no_grad()
+def init_random_(module: nn.Module, seed: int = 0) -> nn.Module:
+    """Synthetic "random-init weights" for benchmarks: matrices / conv kernels ~ N(0, 1/fan_in), norm scales
+    ~ 1 + 0.1 N, biases ~ 0.05 N - INCLUDING the modules the reference zero-initialises (SpatialTransformer.proj_out,
+    ResBlock.out_layers[3], UNetModel.out[2]); with those left at zero every block is the identity and the U-Net
+    returns zeros, which would make a benchmark or a parity test vacuous."""
+    dev = next(module.parameters()).device
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    for name, p in module.named_parameters():
+        if p.dim() >= 2:
+            fan_in = p[0].numel()
+            p.copy_(torch.randn(p.shape, generator=g, device=dev, dtype=torch.float32) / math.sqrt(fan_in))
+        elif name.endswith("weight"):
+            p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g, device=dev, dtype=torch.float32))
+        else:
+            p.copy_(0.05 * torch.randn(p.shape, generator=g, device=dev, dtype=torch.float32))
+    return module

@@ -1,0 +1,220 @@
+"""CPU-side checks of the host layer: the C-ABI library loads and exports every symbol the header declares,
+module state-dict keys equal the reference's, the DDIM schedule equals the reference's golden values, the
+product path fails loudly without CUDA, and the sample sharding works at world_size 2 over gloo."""
+import os
+import re
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT, load_golden
+from oracle import params as P
+from oracle import port
+
+
+# ------------------------------------------------------------------------------------------- C ABI
+def _header_functions():
+    text = open(os.path.join(ROOT, "include", "adaface_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(afb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_builds_loads_and_exports_every_declared_symbol():
+    import ctypes
+    from adaface_b200 import _lib, build
+    path = build.build()
+    assert os.path.exists(path)
+    lib = ctypes.CDLL(path)
+    declared = _header_functions()
+    assert len(declared) >= 14
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/adaface_b200.h but not exported"
+    assert sorted(_lib.EXPORTED_SYMBOLS) == declared, "ctypes signature table and header disagree"
+    lib.afb_abi_version.restype = ctypes.c_int
+    assert lib.afb_abi_version() >= 1
+
+
+def test_sass_contains_blackwell_tensor_and_tma_instructions():
+    """The GEMM / attention kernels must be tcgen05 + TMA code (UTC*MMA, UTMALDG in SASS), not mma.sync."""
+    import shutil
+    import subprocess
+    from adaface_b200 import build
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.run(["cuobjdump", "-sass", build.build()], capture_output=True, text=True).stdout
+    assert "UTCHMMA" in sass or "UTCMMA" in sass
+    assert "UTMALDG" in sass
+    assert "LDTM" in sass
+    assert "HMMA.16816" not in sass
+
+
+# ------------------------------------------------------------------------------------------- state dicts
+def test_spatial_transformer_state_dict_matches_reference_keys():
+    from adaface_b200 import SpatialTransformer
+    for c in (320, 640, 1280):
+        st = SpatialTransformer(c, 8, c // 8, depth=1, context_dim=768)
+        have = {k: tuple(v.shape) for k, v in st.state_dict().items()}
+        assert have == dict(P.spatial_transformer_spec(c))
+        # the reference zero-initialises proj_out (attention.py:313-317)
+        assert float(st.proj_out.weight.abs().max()) == 0.0 and float(st.proj_out.bias.abs().max()) == 0.0
+        attn2 = st.transformer_blocks[0].attn2
+        for attr in ("heads", "scale", "save_attn_vars", "cached_activations", "use_conv_attn_kernel_size",
+                     "infeat_size", "is_training"):
+            assert hasattr(attn2, attr)
+        assert attn2.scale == (c // 8) ** -0.5 and attn2.heads == 8
+
+
+def test_unet_state_dict_matches_reference_keys():
+    from adaface_b200.unet import SD15_UNET_CONFIG, UNetModel
+    with torch.device("meta"):
+        unet = UNetModel(**SD15_UNET_CONFIG)
+    have = {k: tuple(v.shape) for k, v in unet.state_dict().items()}
+    want = dict(P.unet_spec())
+    assert set(have) == set(want)
+    assert have == want
+    layers = [i for i, _ in unet.spatial_transformers()]
+    assert layers == sorted(port.LAYER_IDX2CA)                 # openaimodel.py:876-877
+    assert sum(v.numel() for v in unet.state_dict().values()) == 859_520_964
+
+
+def test_ada_embedding_state_dict_and_cross_weight_reduction():
+    from adaface_b200 import AdaEmbedding
+    torch.manual_seed(0)
+    ada = AdaEmbedding(num_vectors_per_subj_token=9, fg_emb_count=5, bg_emb_count=4, r=12,
+                       init_vecs=torch.zeros(2, 768), device_type="cpu")
+    have = {k: tuple(v.shape) for k, v in ada.state_dict().items()}
+    assert have == dict(P.ada_embedding_spec(9, 12, 2))
+    assert ada.H == 2 and ada.TDs == [int(0.25 * c) for c in P.CA_INFEAT_DIMS]
+    # embedding_manager.py:719-773: cross-stream blocks are at most 1 % of the in-stream mean magnitude
+    w = ada.layer_coeff_maps[0].weight.view(9, 12, -1)
+    d = 320
+    assert float(w[0][:, d:2 * d].abs().mean()) <= 0.0101 * float(w[0][:, :d].abs().mean())
+    assert float(w[8][:, :d].abs().mean()) <= 0.0101 * float(w[8][:, d:2 * d].abs().mean())
+    one = AdaEmbedding(num_vectors_per_subj_token=1, fg_emb_count=1, bg_emb_count=0, device_type="cpu")
+    with pytest.raises(RuntimeError):                          # H == 1 is not self-consistent
+        one(1, {}, None, None, None)
+
+
+# ------------------------------------------------------------------------------------------- DDIM host logic
+class _Model:
+    def __init__(self):
+        betas = port.make_beta_schedule_linear()
+        ac = np.cumprod(1.0 - betas)
+        self.num_timesteps = 1000
+        self.betas = torch.tensor(betas, dtype=torch.float32)
+        self.alphas_cumprod = torch.tensor(ac, dtype=torch.float32)
+        self.alphas_cumprod_prev = torch.tensor(np.append(1.0, ac[:-1]), dtype=torch.float32)
+        self.device = torch.device("cpu")
+
+    def apply_model(self, x, t, c):
+        return torch.tanh(x)
+
+
+def test_ddim_schedule_matches_reference_golden():
+    from adaface_b200 import DDIMSampler
+    from adaface_b200.ddim import guidance_schedule
+    g = load_golden("ddim")
+    s = DDIMSampler(_Model())
+    s.make_schedule(50, ddim_eta=0.0)
+    assert np.array_equal(s.ddim_timesteps, g["timesteps"])
+    assert list(s.ddim_timesteps[:3]) == [1, 21, 41] and s.ddim_timesteps[-1] == 981        # ddim.py:30-36
+    for mine, key in ((s.ddim_alphas, "alphas"), (s.ddim_alphas_prev, "alphas_prev"), (s.ddim_sigmas, "sigmas"),
+                      (s.ddim_sqrt_one_minus_alphas, "sqrt_one_minus_alphas")):
+        np.testing.assert_allclose(mine, g[key], rtol=2e-6, atol=0, err_msg=key)
+    s.make_schedule(50, ddim_eta=0.5)
+    np.testing.assert_allclose(s.ddim_sigmas, g["sigmas_eta05"], rtol=2e-6)
+    sc = guidance_schedule([10.0, 4.0], 50)
+    assert sc == port.guidance_schedule((10.0, 4.0), 50)
+    assert sc[0] == 10.0 and abs(sc[-1] - 4.0) < 1e-9
+    assert guidance_schedule(7.5, 3) == [7.5, 7.5, 7.5]
+
+
+def test_product_path_fails_loudly_on_cpu():
+    from adaface_b200 import CrossAttention, DDIMSampler, SpatialTransformer
+    from adaface_b200._lib import AdafaceB200Error
+    st = SpatialTransformer(320, 8, 40, depth=1, context_dim=768).eval()
+    with pytest.raises(AdafaceB200Error):
+        st(torch.zeros(1, 320, 8, 8), context=torch.zeros(1, 77, 768))
+    with pytest.raises(AdafaceB200Error):
+        CrossAttention(320, 768, 8, 40)(torch.zeros(1, 64, 320), context=torch.zeros(1, 77, 768))
+    s = DDIMSampler(_Model())
+    s.make_schedule(50)
+    x = torch.zeros(1, 4, 8, 8)
+    with pytest.raises(AdafaceB200Error):
+        s.p_sample_ddim(x, torch.zeros(1, 77, 768), torch.full((1,), 981), index=49, guidance_scale=2.0,
+                        unconditional_conditioning=torch.zeros(1, 77, 768))
+
+
+def test_product_package_does_not_import_the_oracle():
+    import subprocess
+    code = ("import sys; import adaface_b200, adaface_b200.unet, adaface_b200.sampling; "
+            "bad = [m for m in sys.modules if m == 'oracle' or m.startswith('oracle.')]; "
+            "assert not bad, bad")
+    subprocess.run([sys.executable, "-c", code], check=True, cwd=ROOT)
+    for fn in os.listdir(os.path.join(ROOT, "adaface_b200")):
+        if fn.endswith(".py"):
+            src = open(os.path.join(ROOT, "adaface_b200", fn)).read()
+            assert "import oracle" not in src and "from oracle" not in src, fn
+
+
+def test_geglu_interleave_is_a_row_permutation():
+    from adaface_b200.ops import interleave_geglu
+    w = torch.arange(64 * 3, dtype=torch.float32).reshape(64, 3)
+    b = torch.arange(64, dtype=torch.float32)
+    wi, bi = interleave_geglu(w, b)
+    # rows 0..15 are value rows 0..15, rows 16..31 their gate rows (32..47), then value 16..31, gate 48..63
+    assert bi.tolist() == list(range(0, 16)) + list(range(32, 48)) + list(range(16, 32)) + list(range(48, 64))
+    assert torch.equal(wi[:, 0] / 3, bi)
+
+
+# ------------------------------------------------------------------------------------------- sharding
+def test_shard_bounds_and_context_slicing():
+    from adaface_b200.sampling import shard_bounds, shard_layerwise_context
+    assert shard_bounds(8, 2) == [(0, 4), (4, 8)]
+    assert shard_bounds(10, 4) == [(0, 3), (3, 6), (6, 8), (8, 10)]
+    assert shard_bounds(1, 4) == [(0, 1), (1, 1), (1, 1), (1, 1)]
+    ctx = torch.arange(6 * 16).reshape(6 * 16, 1, 1)
+    part = shard_layerwise_context(ctx, 2, 4, 6)
+    assert part.shape[0] == 32 and int(part[0]) == 32 and int(part[-1]) == 63
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port_no, n, out_dir):
+    import torch.distributed as dist
+    from adaface_b200.sampling import sample_sharded
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port_no}", rank=rank, world_size=world)
+    g = torch.Generator().manual_seed(42)
+    x_T = torch.randn((n, 4, 8, 8), generator=g)                       # same tensor on every rank
+    c = torch.randn((n * 16, 77, 8), generator=g)
+    uc = torch.randn((16, 77, 8), generator=g).repeat(n, 1, 1)
+    seen = []
+
+    def run_local(x, cc, cu):
+        seen.append((x.shape[0], cc.shape[0], cu.shape[0]))
+        return x * 2.0 + cc.reshape(x.shape[0], 16, -1).mean(dim=(1, 2)).reshape(-1, 1, 1, 1)
+
+    out = sample_sharded(run_local, x_T, c, uc)
+    ref = x_T * 2.0 + c.reshape(n, 16, -1).mean(dim=(1, 2)).reshape(-1, 1, 1, 1)
+    assert torch.allclose(out, ref), "gathered result differs from the single-process result"
+    assert seen[0][1] == 16 * seen[0][0] and seen[0][2] == 16 * seen[0][0]
+    torch.save({"n_local": seen[0][0]}, os.path.join(out_dir, f"r{rank}.pt"))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [8, 5])
+def test_sample_sharded_world_size_2_gloo(tmp_path, n):
+    import torch.multiprocessing as mp
+    port_no = _free_port()
+    mp.spawn(_worker, args=(2, port_no, n, str(tmp_path)), nprocs=2, join=True)
+    counts = [torch.load(os.path.join(tmp_path, f"r{r}.pt"))["n_local"] for r in range(2)]
+    assert sum(counts) == n and abs(counts[0] - counts[1]) <= 1
