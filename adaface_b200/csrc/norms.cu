@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(512) gn_stats_nchw_kernel(const float* __restr
 // y[b, t, c] = (x[b, c, t] - mean) * rstd * gamma[c] + beta[c]; 32 tokens x 64 channels per block
 __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restrict__ x, const float* __restrict__ stats,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                            __nv_bfloat16* __restrict__ y, int C, int HW, int cpg) {
+                                                            __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int act) {
   __shared__ float tile[64][33];
   const int b = blockIdx.z, c0 = blockIdx.y * 64, t0 = blockIdx.x * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restr
       const int g = c / cpg;
       const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
       v = (x[(static_cast<long long>(b) * C + c) * HW + t] - mean) * rstd * gamma[c] + beta[c];
+      if (act == 1) v = v / (1.0f + __expf(-v));
     }
     tile[ty + 8 * i][tx] = v;
   }
@@ -91,22 +92,44 @@ __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restr
   }
 }
 
-// ---- layout 1: x bf16 [B, HW, C]; thread = channel pair, block = (chunk of 64 tokens, b) ---------------
+// ---- layout 1: x bf16 [B, HW, C]; thread = V adjacent channels (V = 2 or 4), block = (chunk of 64 tokens, b) ----
 // partial[((b*groups + g)*nchunks + chunk)*2] = (chunk mean, chunk M2)
+template <int V>
+__device__ __forceinline__ void load_bf16_vec(const __nv_bfloat16* p, float (&v)[V]) {
+  if constexpr (V == 2) {
+    const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(p));
+    v[0] = a.x; v[1] = a.y;
+  } else {
+    const uint2 u = *reinterpret_cast<const uint2*>(p);
+    const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+  }
+}
+template <int V>
+__device__ __forceinline__ void store_bf16_vec(__nv_bfloat16* p, const float (&v)[V]) {
+  if constexpr (V == 2) {
+    *reinterpret_cast<uint32_t*>(p) = pack_bf16x2(v[0], v[1]);
+  } else {
+    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+  }
+}
+
+template <int V>
 __global__ void gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, int C, int HW,
                                       int cpg, int nchunks) {
-  extern __shared__ float sh[];   // [C/2] per-thread sums, then [groups] means
+  extern __shared__ float sh[];   // [C/V] per-thread sums, then [groups] means
   const int b = blockIdx.y, chunk = blockIdx.x;
   const int t0 = chunk * kGnChunkTokens;
   const int nt = min(kGnChunkTokens, HW - t0);
-  const int groups = C / cpg, tpg = cpg >> 1;   // threads per group
-  float* gmean = sh + (C >> 1);
-  const uint32_t* xp = reinterpret_cast<const uint32_t*>(x + (static_cast<long long>(b) * HW + t0) * C) + threadIdx.x;
-  const int row = C >> 1;
+  const int groups = C / cpg, tpg = cpg / V;   // threads per group
+  float* gmean = sh + C / V;
+  const __nv_bfloat16* xp = x + (static_cast<long long>(b) * HW + t0) * C + V * threadIdx.x;
   float s = 0.f;
   for (int t = 0; t < nt; ++t) {
-    const float2 v = unpack_bf16x2(xp[static_cast<long long>(t) * row]);
-    s += v.x + v.y;
+    float v[V];
+    load_bf16_vec<V>(xp + static_cast<long long>(t) * C, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) s += v[j];
   }
   sh[threadIdx.x] = s;
   __syncthreads();
@@ -119,9 +142,13 @@ __global__ void gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, float
   const float mean = gmean[threadIdx.x / tpg];
   float m2 = 0.f;
   for (int t = 0; t < nt; ++t) {
-    const float2 v = unpack_bf16x2(xp[static_cast<long long>(t) * row]);
-    const float a = v.x - mean, c = v.y - mean;
-    m2 += a * a + c * c;
+    float v[V];
+    load_bf16_vec<V>(xp + static_cast<long long>(t) * C, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float d = v[j] - mean;
+      m2 += d * d;
+    }
   }
   __syncthreads();
   sh[threadIdx.x] = m2;
@@ -158,6 +185,9 @@ __global__ void gn_finalize_kernel(const float* __restrict__ partial, float* __r
   stats[2 * i + 1] = rsqrtf(m2 / tot + eps);
 }
 
+__device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
+
+template <int V, bool kSilu>
 __global__ void gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                     __nv_bfloat16* __restrict__ y, int C, int HW, int cpg) {
@@ -165,15 +195,25 @@ __global__ void gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const f
   const int t0 = blockIdx.x * kGnChunkTokens;
   const int nt = min(kGnChunkTokens, HW - t0);
   const int groups = C / cpg;
-  const int c = 2 * threadIdx.x;
+  const int c = V * threadIdx.x;
   const int g = c / cpg;
   const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
-  const float s0 = rstd * gamma[c], s1 = rstd * gamma[c + 1];
-  const float o0 = beta[c] - mean * s0, o1 = beta[c + 1] - mean * s1;
+  float sc[V], of[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    sc[j] = rstd * gamma[c + j];
+    of[j] = beta[c + j] - mean * sc[j];
+  }
   const long long base = (static_cast<long long>(b) * HW + t0) * C + c;
   for (int t = 0; t < nt; ++t) {
-    const float2 v = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(x + base + static_cast<long long>(t) * C));
-    *reinterpret_cast<uint32_t*>(y + base + static_cast<long long>(t) * C) = pack_bf16x2(v.x * s0 + o0, v.y * s1 + o1);
+    float v[V];
+    load_bf16_vec<V>(x + base + static_cast<long long>(t) * C, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      v[j] = v[j] * sc[j] + of[j];
+      if (kSilu) v[j] = silu(v[j]);
+    }
+    store_bf16_vec<V>(y + base + static_cast<long long>(t) * C, v);
   }
 }
 
@@ -251,7 +291,7 @@ extern "C" int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups) {
 }
 
 extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
-                                    float* stats_ws, int batch, int channels, int hw, int groups, float eps,
+                                    float* stats_ws, int batch, int channels, int hw, int groups, float eps, int act,
                                     afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -260,6 +300,7 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
   AFB_REQUIRE(channels % groups == 0, "afb_groupnorm_tokens: channels %d not divisible by groups %d", channels, groups);
   const int cpg = channels / groups;
   AFB_REQUIRE(cpg % 2 == 0 && channels % 64 == 0, "afb_groupnorm_tokens: need channels %% 64 == 0 and even channels/group");
+  AFB_REQUIRE(act == 0 || act == 1, "afb_groupnorm_tokens: act must be 0 (none) or 1 (SiLU)");
   __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(y);
   if (x_layout == 0) {
     AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (static_cast<long long>(cpg) * hw) % 4 == 0,
@@ -267,21 +308,33 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
     gn_stats_nchw_kernel<<<batch * groups, 512, 0, stream>>>(static_cast<const float*>(x), stats_ws, cpg * hw, eps);
     count_launch();
     dim3 grid((hw + 31) / 32, channels / 64, batch);
-    gn_apply_nchw_kernel<<<grid, 256, 0, stream>>>(static_cast<const float*>(x), stats_ws, gamma, beta, yb, channels, hw, cpg);
+    gn_apply_nchw_kernel<<<grid, 256, 0, stream>>>(static_cast<const float*>(x), stats_ws, gamma, beta, yb, channels, hw, cpg, act);
     count_launch();
   } else if (x_layout == 1) {
-    AFB_REQUIRE(channels / 2 <= 1024, "afb_groupnorm_tokens: channels %d too large", channels);
+    const int V = (channels / 2 <= 1024) ? 2 : 4;
+    AFB_REQUIRE(channels / V <= 1024 && cpg % V == 0 && groups <= channels / V,
+                "afb_groupnorm_tokens: channels %d / groups %d not supported by the token-major kernel", channels, groups);
+    AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 7) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0,
+                "afb_groupnorm_tokens: buffers must be 8-byte aligned");
     const int nchunks = (hw + kGnChunkTokens - 1) / kGnChunkTokens;
     float* partial = stats_ws + 2ll * batch * groups;
     const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
     dim3 grid(nchunks, batch);
-    const size_t sh = (channels / 2 + groups) * sizeof(float);
-    gn_partial_tok_kernel<<<grid, channels / 2, sh, stream>>>(xb, partial, channels, hw, cpg, nchunks);
+    const int threads = channels / V;
+    const size_t sh = (threads + groups) * sizeof(float);
+    if (V == 2) gn_partial_tok_kernel<2><<<grid, threads, sh, stream>>>(xb, partial, channels, hw, cpg, nchunks);
+    else gn_partial_tok_kernel<4><<<grid, threads, sh, stream>>>(xb, partial, channels, hw, cpg, nchunks);
     count_launch();
     const int n_bg = batch * groups;
     gn_finalize_kernel<<<(n_bg + 127) / 128, 128, 0, stream>>>(partial, stats_ws, n_bg, nchunks, hw, cpg, eps);
     count_launch();
-    gn_apply_tok_kernel<<<grid, channels / 2, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
+    if (V == 2) {
+      if (act) gn_apply_tok_kernel<2, true><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
+      else gn_apply_tok_kernel<2, false><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
+    } else {
+      if (act) gn_apply_tok_kernel<4, true><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
+      else gn_apply_tok_kernel<4, false><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
+    }
     count_launch();
   } else {
     AFB_FAIL(2, "afb_groupnorm_tokens: unknown x_layout %d", x_layout);

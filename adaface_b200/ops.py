@@ -86,9 +86,10 @@ def _(x, e_cond, e_uncond, noise, guidance_scale, a_t, a_prev, sigma_t, sqrt_one
 
 # ------------------------------------------------------------------------------------------- K1 / K3
 @torch.library.custom_op("adaface_b200::groupnorm_tokens", mutates_args=())
-def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: float) -> Tensor:
+def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: float, act: int = 0) -> Tensor:
     """GroupNorm over x [B,C,h,w] -> normalised tokens bf16 [B, h*w, C] (attention.py:325-327).
-    fp32 NCHW-contiguous and bf16 channels-last inputs are consumed in place; anything else is rejected."""
+    fp32 NCHW-contiguous and bf16 channels-last inputs are consumed in place; anything else is rejected.
+    act = 1 fuses SiLU after the affine (the U-Net ResBlocks' GroupNorm32 -> SiLU)."""
     _need_cuda(x, gamma, beta)
     b, c, h, w = x.shape
     hw = h * w
@@ -102,12 +103,12 @@ def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: f
     ws = torch.empty(int(lib.afb_groupnorm_ws_floats(b, hw, groups)), dtype=torch.float32, device=x.device)
     y = torch.empty((b, hw, c), dtype=torch.bfloat16, device=x.device)
     _run("groupnorm_tokens", lib.afb_groupnorm_tokens, _ptr(x), layout, _ptr(gamma), _ptr(beta), _ptr(y), _ptr(ws), b, c,
-         hw, groups, eps, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"C{c}")
+         hw, groups, eps, act, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"C{c}")
     return y
 
 
 @groupnorm_tokens.register_fake
-def _(x, gamma, beta, groups, eps):
+def _(x, gamma, beta, groups, eps, act=0):
     b, c, h, w = x.shape
     return x.new_empty((b, h * w, c), dtype=torch.bfloat16)
 

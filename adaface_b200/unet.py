@@ -44,10 +44,20 @@ class TimestepBlock(nn.Module):
 
 
 class GroupNorm32(nn.GroupNorm):
-    """diffusionmodules/util.py:217-219 (eps 1e-5).  fp32 statistics on the bf16 activation."""
+    """diffusionmodules/util.py:217-219 (eps 1e-5): parameter holder.  Every GroupNorm32 of the U-Net is followed by
+    SiLU (openaimodel.py:201-205, 233-236, 693-695); `gn_silu` runs the pair as the K1 kernel with fused SiLU on the
+    bf16 channels-last activation (fp32 statistics), so no NCHW round trip is made."""
 
     def forward(self, x):
-        return F.group_norm(x, self.num_groups, self.weight, self.bias, self.eps)
+        raise RuntimeError("GroupNorm32 is applied through gn_silu() together with the SiLU that follows it")
+
+
+def gn_silu(gn: nn.GroupNorm, x: Tensor) -> Tensor:
+    """x bf16 channels-last [B, C, H, W] -> SiLU(GroupNorm(x)), same format."""
+    b, c, h, w = x.shape
+    x = x.contiguous(memory_format=CL)
+    y = ops.groupnorm_tokens(x, gn.weight.detach(), gn.bias.detach(), gn.num_groups, gn.eps, 1)
+    return y.view(b, h, w, c).permute(0, 3, 1, 2)
 
 
 class _Bf16Conv(nn.Conv2d):
@@ -106,10 +116,12 @@ class ResBlock(TimestepBlock):
         self.skip_connection = nn.Identity() if oc == channels else _Bf16Conv(channels, oc, 1)
 
     def forward(self, x, emb):
-        h = self.in_layers(x)
+        h = self.in_layers[2](gn_silu(self.in_layers[0], x))
         e = self.emb_layers(emb).to(h.dtype)
         h = h + e[:, :, None, None]
-        h = self.out_layers(h)
+        if self.training and self.out_layers[2].p > 0:
+            raise NotImplementedError("adaface_b200.ResBlock: dropout > 0 in training mode is not supported")
+        h = self.out_layers[3](gn_silu(self.out_layers[0], h))
         return self.skip_connection(x) + h
 
 
@@ -316,7 +328,7 @@ class UNetModel(nn.Module):
             h = torch.cat([h, hs.pop()], dim=1).contiguous(memory_format=CL)
             h = module(h, emb, layer_context(layer_idx), mask=img_mask)
             layer_idx += 1
-        return self.out(h).to(x.dtype).contiguous()
+        return self.out[2](gn_silu(self.out[0], h)).to(x.dtype).contiguous()
 
 
 class DiffusionModel:

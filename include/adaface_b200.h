@@ -44,10 +44,12 @@ int afb_cfg_ddim_step(const float* x, const float* e_cond, const float* e_uncond
 
 /* ---- K1: GroupNorm(32, C, eps) -> token-major bf16.  Replaces attention.py:71-72,325 (+ the layout change
  * of :327).  x_layout 0: x is fp32 [B,C,HW] (NCHW contiguous); 1: x is bf16 [B,HW,C] (channels-last).
- * stats_ws: fp32 workspace of afb_groupnorm_ws_floats(B, HW, groups) floats.  y: bf16 [B*HW, C]. */
+ * stats_ws: fp32 workspace of afb_groupnorm_ws_floats(B, HW, groups) floats.  y: bf16 [B*HW, C].
+ * act 0: none; 1: SiLU fused after the affine (the GroupNorm32 -> SiLU pairs of the U-Net's ResBlocks,
+ * openaimodel.py:201-205,233-236 - the first "next" row after the transformer path). */
 int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups);
 int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
-                         float* stats_ws, int batch, int channels, int hw, int groups, float eps,
+                         float* stats_ws, int batch, int channels, int hw, int groups, float eps, int act,
                          afb_stream_t stream);
 
 /* ---- K3: LayerNorm over the last dim, bf16 in / bf16 out, fp32 statistics.  attention.py:267-269,277-283.

@@ -40,7 +40,7 @@ def test_cfg_ddim_step_bit_exact(ops, cuda_device, n, sigma):
 
 
 # ---------------------------------------------------------------------------------------------- K1 / K3
-@pytest.mark.parametrize("c,hw", [(320, 16), (640, 8), (1280, 8), (320, 12)])
+@pytest.mark.parametrize("c,hw", [(320, 16), (640, 8), (1280, 8), (320, 12), (2560, 8), (1920, 8), (960, 16)])
 def test_groupnorm_tokens_both_layouts(ops, cuda_device, c, hw):
     b = 2
     x = _r("gn.x", (b, c, hw, hw)) * 1.5 + 0.7
@@ -53,6 +53,12 @@ def test_groupnorm_tokens_both_layouts(ops, cuda_device, c, hw):
     ref1 = port.group_norm(xb.float().cpu(), g, be, 32, 1e-6).reshape(b, c, hw * hw).transpose(1, 2)
     y1 = ops.groupnorm_tokens(xb, g.to(d), be.to(d), 32, 1e-6)
     assert rel_l2(y1.float(), ref1) < 4e-3
+    # fused SiLU (the ResBlocks' GroupNorm32 -> SiLU), both layouts
+    silu = torch.nn.functional.silu
+    assert rel_l2(ops.groupnorm_tokens(x.to(d), g.to(d), be.to(d), 32, 1e-5, 1).float(),
+                  silu(port.group_norm(x, g, be, 32, 1e-5)).reshape(b, c, hw * hw).transpose(1, 2)) < 4e-3
+    assert rel_l2(ops.groupnorm_tokens(xb, g.to(d), be.to(d), 32, 1e-5, 1).float(),
+                  silu(port.group_norm(xb.float().cpu(), g, be, 32, 1e-5)).reshape(b, c, hw * hw).transpose(1, 2)) < 4e-3
 
 
 @pytest.mark.parametrize("c", [320, 640, 1280, 2880])
