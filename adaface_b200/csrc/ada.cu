@@ -36,45 +36,78 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
   return red[0];
 }
 
-// ---- prep: lora_q[b][i][g*lg + o], i = 0 (fg), 1 (bg); includes the 8^-1/2 * 8^-1/2 factor (:235) -----------
-__global__ void __launch_bounds__(kPoolThreads) ada_pool_prep_kernel(
+// ---- prep, kernel 1: proj[s][c] = to_k(query embedding s)[c] (:193, :203); s = 0 is the shared fg probe, s = 1 + b
+// the bg query of sample b.  One warp per output channel: the weight row is read once and dotted with all B + 1
+// query vectors (staged in shared memory), so the [C, ctx_dim] weight streams through exactly once per call.
+constexpr int kPrepMaxSrc = 16;    // sources handled per pass (B + 1 <= 16 in one pass; more -> extra passes)
+__global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
     const float* __restrict__ to_k_w, const float* __restrict__ fg_q_emb, const float* __restrict__ bg_q_emb,
-    const float* __restrict__ w_fg, const float* __restrict__ w_bg, float* __restrict__ lora_q, int C, int ctx_dim) {
-  extern __shared__ float sh[];      // [2][C] projected queries
-  __shared__ float red[32];
-  const int b = blockIdx.x;
-  const int dg = C / kHeads, lg = dg / kHeads;
+    float* __restrict__ proj, int C, int ctx_dim, int n_src) {
+  extern __shared__ float sh[];      // [min(n_src, kPrepMaxSrc)][ctx_dim]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = 0; i < 2; ++i) {
-    const float* emb = (i == 0) ? fg_q_emb : bg_q_emb + static_cast<long long>(b) * ctx_dim;
-    for (int c = warp; c < C; c += (kPoolThreads >> 5)) {                       // to_k(emb): :193, :203
-      const float* wr = to_k_w + static_cast<long long>(c) * ctx_dim;
-      float a = 0.f;
-      for (int k = lane; k < ctx_dim; k += 32) a += wr[k] * emb[k];
-      a = warp_sum(a);
-      if (lane == 0) sh[i * C + c] = a;
-    }
-  }
-  __syncthreads();
-  for (int i = 0; i < 2; ++i) {                                                 // LayerNorm, no affine: :208-209
-    float s = 0.f;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) s += sh[i * C + c];
-    const float mean = block_sum_256(s, red) / C;
-    float m2 = 0.f;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      const float d = sh[i * C + c] - mean;
-      m2 += d * d;
-    }
-    const float rstd = rsqrtf(block_sum_256(m2, red) / C + 1e-5f);
-    for (int c = threadIdx.x; c < C; c += blockDim.x) sh[i * C + c] = (sh[i * C + c] - mean) * rstd;
+  const int c = blockIdx.x * (kPoolThreads >> 5) + warp;
+  for (int s0 = 0; s0 < n_src; s0 += kPrepMaxSrc) {
+    const int ns = min(kPrepMaxSrc, n_src - s0);
     __syncthreads();
+    for (int idx = threadIdx.x; idx < ns * ctx_dim; idx += blockDim.x) {
+      const int s = s0 + idx / ctx_dim, k = idx % ctx_dim;
+      sh[idx] = (s == 0) ? fg_q_emb[k] : bg_q_emb[static_cast<long long>(s - 1) * ctx_dim + k];
+    }
+    __syncthreads();
+    if (c < C) {
+      float acc[kPrepMaxSrc];
+#pragma unroll
+      for (int i = 0; i < kPrepMaxSrc; ++i) acc[i] = 0.f;
+      const float* wr = to_k_w + static_cast<long long>(c) * ctx_dim;
+      for (int k = lane; k < ctx_dim; k += 32) {
+        const float w = wr[k];
+#pragma unroll
+        for (int i = 0; i < kPrepMaxSrc; ++i)
+          if (i < ns) acc[i] += w * sh[i * ctx_dim + k];
+      }
+#pragma unroll
+      for (int i = 0; i < kPrepMaxSrc; ++i) {
+        if (i < ns) {
+          const float a = warp_sum(acc[i]);
+          if (lane == 0) proj[static_cast<long long>(s0 + i) * C + c] = a;
+        }
+      }
+    }
   }
-  for (int idx = threadIdx.x; idx < 2 * dg; idx += blockDim.x) {                // grouped conv: :219, :222, :235
-    const int i = idx / dg, j = idx % dg;       // j = g*lg + o
+}
+
+// ---- prep, kernel 2: block (b, i): LayerNorm (no affine, :208-209) of the projected query, grouped 1x1 conv
+// (:219, :222) and the 8^-1/2 * 8^-1/2 factor (:235) -> lora_q[b][i][g*lg + o]; i = 0 (fg), 1 (bg).
+__global__ void __launch_bounds__(kPoolThreads) ada_qfinish_kernel(const float* __restrict__ proj,
+                                                                  const float* __restrict__ w_fg,
+                                                                  const float* __restrict__ w_bg,
+                                                                  float* __restrict__ lora_q, int C) {
+  extern __shared__ float sh[];      // [C]
+  __shared__ float red[32];
+  const int b = blockIdx.x, i = blockIdx.y;
+  const int dg = C / kHeads, lg = dg / kHeads;
+  const float* src = proj + static_cast<long long>(i == 0 ? 0 : 1 + b) * C;
+  float s = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float v = src[c];
+    sh[c] = v;
+    s += v;
+  }
+  const float mean = block_sum_256(s, red) / C;
+  float m2 = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float d = sh[c] - mean;
+    m2 += d * d;
+  }
+  const float rstd = rsqrtf(block_sum_256(m2, red) / C + 1e-5f);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) sh[c] = (sh[c] - mean) * rstd;
+  __syncthreads();
+  const float* wsel = (i == 0) ? w_fg : w_bg;
+  for (int j = threadIdx.x; j < dg; j += blockDim.x) {      // j = g*lg + o
     const int g = j / lg;
-    const float* w = ((i == 0) ? w_fg : w_bg) + static_cast<long long>(j) * dg;
+    const float* w = wsel + static_cast<long long>(j) * dg;
     float a = 0.f;
-    for (int k = 0; k < dg; ++k) a += w[k] * sh[i * C + g * dg + k];
+    for (int k = 0; k < dg; ++k) a += w[k] * sh[g * dg + k];
     lora_q[(static_cast<long long>(b) * 2 + i) * dg + j] = a * kInvSqrt8 * kInvSqrt8;
   }
 }
@@ -319,18 +352,21 @@ __global__ void __launch_bounds__(256) ada_pool_probs_kernel(const float* __rest
 }
 
 // ---- K13 ------------------------------------------------------------------------------------------------
+// Block (k, b): LNCat of the pooled features and the time slice (recomputed per block, 2C + TD values), the r
+// coefficients of vector k (r dot products of length 2C + TD, one warp each), the basis combination, the
+// per-vector LayerNorm, 1/sqrt(D) and the bias.  B * K blocks instead of B.
 __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__ infeat_fg, const float* __restrict__ infeat_bg,
                                                        const float* __restrict__ time_emb, int time_ld,
                                                        const float* __restrict__ coeff_w, const float* __restrict__ coeff_b,
                                                        const float* __restrict__ basis, const float* __restrict__ bias,
                                                        float* __restrict__ out, int C, int TD, int K, int R, int D) {
-  extern __shared__ float sh[];    // feat [2C + TD], coeffs [K*R], vec [D]
+  extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D]
   __shared__ float red[32];
-  const int b = blockIdx.x;
+  const int k = blockIdx.x, b = blockIdx.y;
   const int F = 2 * C + TD;
   float* feat = sh;
   float* coeffs = feat + F;
-  float* vec = coeffs + K * R;
+  float* vec = coeffs + R;
   for (int i = threadIdx.x; i < F; i += blockDim.x) {
     float v;
     if (i < C) v = infeat_fg[static_cast<long long>(b) * C + i];
@@ -354,39 +390,36 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
     for (int i = threadIdx.x; i < n; i += blockDim.x) feat[lo + i] = (feat[lo + i] - mean) * rstd;
     __syncthreads();
   }
-  // basis_dyn_coeffs = Linear(feat) (:858), one warp per output
+  // basis_dyn_coeffs[k] = Linear(feat)[k*R : (k+1)*R] (:858), one warp per output
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int o = warp; o < K * R; o += (blockDim.x >> 5)) {
-    const float* w = coeff_w + static_cast<long long>(o) * F;
+  for (int o = warp; o < R; o += (blockDim.x >> 5)) {
+    const float* w = coeff_w + static_cast<long long>(k * R + o) * F;
     float a = 0.f;
     for (int i = lane; i < F; i += 32) a += w[i] * feat[i];
     a = warp_sum(a);
-    if (lane == 0) coeffs[o] = a + coeff_b[o];
+    if (lane == 0) coeffs[o] = a + coeff_b[k * R + o];
   }
   __syncthreads();
   // out[k] = LN(coeffs[k] @ basis[k]) / sqrt(D) + bias[k]  (:881-893)
   const float inv_sqrt_d = rsqrtf(static_cast<float>(D));
-  for (int k = 0; k < K; ++k) {
-    float s = 0.f;
-    for (int d = threadIdx.x; d < D; d += blockDim.x) {
-      float a = 0.f;
-      for (int r = 0; r < R; ++r) a += coeffs[k * R + r] * basis[(static_cast<long long>(k) * R + r) * D + d];
-      vec[d] = a;
-      s += a;
-    }
-    const float mean = block_sum_256(s, red) / D;
-    float m2 = 0.f;
-    for (int d = threadIdx.x; d < D; d += blockDim.x) {
-      const float dd = vec[d] - mean;
-      m2 += dd * dd;
-    }
-    const float rstd = rsqrtf(block_sum_256(m2, red) / D + 1e-5f);
-    for (int d = threadIdx.x; d < D; d += blockDim.x) {
-      float v = (vec[d] - mean) * rstd * inv_sqrt_d;
-      if (bias != nullptr) v += bias[static_cast<long long>(k) * D + d];
-      out[(static_cast<long long>(b) * K + k) * D + d] = v;
-    }
-    __syncthreads();
+  float s = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float a = 0.f;
+    for (int r = 0; r < R; ++r) a += coeffs[r] * basis[(static_cast<long long>(k) * R + r) * D + d];
+    vec[d] = a;
+    s += a;
+  }
+  const float mean = block_sum_256(s, red) / D;
+  float m2 = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    const float dd = vec[d] - mean;
+    m2 += dd * dd;
+  }
+  const float rstd = rsqrtf(block_sum_256(m2, red) / D + 1e-5f);
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float v = (vec[d] - mean) * rstd * inv_sqrt_d;
+    if (bias != nullptr) v += bias[static_cast<long long>(k) * D + d];
+    out[(static_cast<long long>(b) * K + k) * D + d] = v;
   }
 }
 
@@ -410,16 +443,34 @@ extern "C" int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels)
          + static_cast<int64_t>(batch) * kHeads * 2;                // merged (max, sum)
 }
 
+extern "C" int64_t afb_ada_pool_prep_ws_floats(int batch, int channels) {
+  return (static_cast<int64_t>(batch) + 1) * channels;
+}
+
 extern "C" int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
-                                 const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, int batch,
+                                 const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, float* ws, int batch,
                                  int channels, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  AFB_REQUIRE(to_k_weight && fg_q_emb && bg_q_emb && lora_to_fg_q && lora_to_bg_q && lora_q, "afb_ada_pool_prep: NULL argument");
+  AFB_REQUIRE(to_k_weight && fg_q_emb && bg_q_emb && lora_to_fg_q && lora_to_bg_q && lora_q && ws,
+              "afb_ada_pool_prep: NULL argument");
   AFB_REQUIRE(batch > 0 && ctx_dim > 0, "afb_ada_pool_prep: empty input");
   AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool_prep: channels %d must be a multiple of 64, <= 1280", channels);
-  ada_pool_prep_kernel<<<batch, kPoolThreads, 2 * channels * sizeof(float), stream>>>(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q,
-                                                                                    lora_to_bg_q, lora_q, channels, ctx_dim);
+  const int n_src = batch + 1;
+  const int src_in_smem = n_src < kPrepMaxSrc ? n_src : kPrepMaxSrc;
+  const size_t sh1 = static_cast<size_t>(src_in_smem) * ctx_dim * sizeof(float);
+  AFB_REQUIRE(sh1 <= 96 * 1024, "afb_ada_pool_prep: ctx_dim %d too large", ctx_dim);
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(ada_qproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set = true;
+  }
+  const int warps = kPoolThreads >> 5;
+  ada_qproj_kernel<<<(channels + warps - 1) / warps, kPoolThreads, sh1, stream>>>(to_k_weight, fg_q_emb, bg_q_emb, ws,
+                                                                                 channels, ctx_dim, n_src);
+  count_launch();
+  ada_qfinish_kernel<<<dim3(batch, 2), kPoolThreads, channels * sizeof(float), stream>>>(ws, lora_to_fg_q, lora_to_bg_q,
+                                                                                        lora_q, channels);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -452,15 +503,18 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* l
   const int chunks_per_lane = (C / 8 + 31) / 32;
   if (chunks_per_lane <= 2) {
     auto kern = ada_pool_main_kernel<2>;
-    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main)));
+    static size_t set_for = 0;
+    if (set_for < sh_main) { AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); set_for = sh_main; }
     kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
   } else if (chunks_per_lane <= 3) {
     auto kern = ada_pool_main_kernel<3>;
-    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main)));
+    static size_t set_for = 0;
+    if (set_for < sh_main) { AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); set_for = sh_main; }
     kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
   } else {
     auto kern = ada_pool_main_kernel<kMaxChunksPerLane>;
-    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main)));
+    static size_t set_for = 0;
+    if (set_for < sh_main) { AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); set_for = sh_main; }
     kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
   }
   count_launch();
@@ -485,9 +539,9 @@ extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, cons
   AFB_REQUIRE(infeat_fg && infeat_bg && time_emb && coeff_w && coeff_b && basis && out, "afb_ada_head: NULL argument");
   AFB_REQUIRE(batch > 0 && channels > 0 && td > 0 && td <= time_ld && num_vectors > 0 && r > 0 && out_dim > 0,
               "afb_ada_head: bad sizes");
-  const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>(num_vectors) * r + out_dim) * sizeof(float);
+  const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>(r) + out_dim) * sizeof(float);
   AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head: feature vector too large for one block (%zu bytes)", sh);
-  ada_head_kernel<<<batch, 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias, out,
+  ada_head_kernel<<<dim3(num_vectors, batch), 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias, out,
                                               channels, td, num_vectors, r, out_dim);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());

@@ -9,7 +9,6 @@ namespace afb {
 void count_launch();
 namespace {
 
-constexpr int kGnChunkTokens = 64;
 
 __device__ __forceinline__ float block_sum(float v, float* red) {
   v = warp_sum(v);
@@ -92,129 +91,188 @@ __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restr
   }
 }
 
-// ---- layout 1: x bf16 [B, HW, C]; thread = V adjacent channels (V = 2 or 4), block = (chunk of 64 tokens, b) ----
-// partial[((b*groups + g)*nchunks + chunk)*2] = (chunk mean, chunk M2)
-template <int V>
-__device__ __forceinline__ void load_bf16_vec(const __nv_bfloat16* p, float (&v)[V]) {
-  if constexpr (V == 2) {
-    const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(p));
-    v[0] = a.x; v[1] = a.y;
-  } else {
-    const uint2 u = *reinterpret_cast<const uint2*>(p);
-    const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
-    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
-  }
-}
-template <int V>
-__device__ __forceinline__ void store_bf16_vec(__nv_bfloat16* p, const float (&v)[V]) {
-  if constexpr (V == 2) {
-    *reinterpret_cast<uint32_t*>(p) = pack_bf16x2(v[0], v[1]);
-  } else {
-    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
-  }
+// ---- layout 1: x bf16 [B, HW, C] (token-major = channels-last) -------------------------------------------------
+// A chunk of T consecutive tokens is one contiguous T*C*2-byte span.  Thread = 8 adjacent channels (one 16-byte
+// vector) x up to kGnTpt tokens held in registers (all loads in flight at once); a block covers T tokens with
+// R = blockDim / (C/8) token rows.  Per-group reductions go through shared-memory atomics (32 groups).
+//   gn_partial_tok   chunk (mean, M2) per (b, group, chunk): two passes over the REGISTER copy, one read of x
+//   gn_finalize      exact (Chan) merge of the chunk partials -> (mean, rstd) per (b, group)
+//   gn_apply_tok     normalise + affine (+ SiLU) with 16-byte loads / stores
+constexpr int kGnTpt = 8;           // tokens per thread
+constexpr int kGnMaxGroups = 64;
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&v)[8]) {
+  const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
 }
 
-template <int V>
-__global__ void gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, int C, int HW,
-                                      int cpg, int nchunks) {
-  extern __shared__ float sh[];   // [C/V] per-thread sums, then [groups] means
+// adds the 8 per-channel values of this thread into their groups' shared-memory slots (runs of equal group merged)
+__device__ __forceinline__ void group_accumulate(float* slots, const float (&s)[8], int c0, int cpg) {
+  int cur = c0 / cpg;
+  float acc = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / cpg;
+    if (g != cur) {
+      atomicAdd(&slots[cur], acc);
+      acc = 0.f;
+      cur = g;
+    }
+    acc += s[j];
+  }
+  atomicAdd(&slots[cur], acc);
+}
+
+__global__ void __launch_bounds__(320) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial,
+                                                             int C, int HW, int cpg, int T, int nchunks) {
+  __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
   const int b = blockIdx.y, chunk = blockIdx.x;
-  const int t0 = chunk * kGnChunkTokens;
-  const int nt = min(kGnChunkTokens, HW - t0);
-  const int groups = C / cpg, tpg = cpg / V;   // threads per group
-  float* gmean = sh + C / V;
-  const __nv_bfloat16* xp = x + (static_cast<long long>(b) * HW + t0) * C + V * threadIdx.x;
-  float s = 0.f;
-  for (int t = 0; t < nt; ++t) {
-    float v[V];
-    load_bf16_vec<V>(xp + static_cast<long long>(t) * C, v);
-#pragma unroll
-    for (int j = 0; j < V; ++j) s += v[j];
-  }
-  sh[threadIdx.x] = s;
+  const int t0 = chunk * T;
+  const int nt = min(T, HW - t0);
+  const int vpr = C >> 3;                       // 16-byte vectors per token row
+  const int R = blockDim.x / vpr;               // token rows covered per pass
+  const int vec = threadIdx.x % vpr, row = threadIdx.x / vpr;
+  const int c0 = vec * 8;
+  const int groups = C / cpg;
+  for (int i = threadIdx.x; i < groups; i += blockDim.x) g_sum[i] = g_m2[i] = 0.f;
   __syncthreads();
-  if (threadIdx.x < groups) {
-    float a = 0.f;
-    for (int i = 0; i < tpg; ++i) a += sh[threadIdx.x * tpg + i];
-    gmean[threadIdx.x] = a / static_cast<float>(nt * cpg);
-  }
-  __syncthreads();
-  const float mean = gmean[threadIdx.x / tpg];
-  float m2 = 0.f;
-  for (int t = 0; t < nt; ++t) {
-    float v[V];
-    load_bf16_vec<V>(xp + static_cast<long long>(t) * C, v);
+  const uint4* xp = reinterpret_cast<const uint4*>(x + (static_cast<long long>(b) * HW + t0) * C) + vec;
+  uint4 data[kGnTpt];
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      const float d = v[j] - mean;
-      m2 += d * d;
+  for (int i = 0; i < kGnTpt; ++i) {
+    const int t = row + i * R;
+    data[i] = (t < nt) ? xp[static_cast<long long>(t) * vpr] : make_uint4(0, 0, 0, 0);
+  }
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+#pragma unroll
+  for (int i = 0; i < kGnTpt; ++i) {
+    float v[8];
+    unpack8(data[i], v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += v[j];   // rows beyond nt hold zeros
+  }
+  group_accumulate(g_sum, s, c0, cpg);
+  __syncthreads();
+  const float inv_n = 1.0f / static_cast<float>(nt * cpg);
+  float mean[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) mean[j] = g_sum[(c0 + j) / cpg] * inv_n;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+#pragma unroll
+  for (int i = 0; i < kGnTpt; ++i) {
+    if (row + i * R < nt) {
+      float v[8];
+      unpack8(data[i], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[j] - mean[j];
+        s[j] += d * d;
+      }
     }
   }
+  group_accumulate(g_m2, s, c0, cpg);
   __syncthreads();
-  sh[threadIdx.x] = m2;
-  __syncthreads();
-  if (threadIdx.x < groups) {
-    float a = 0.f;
-    for (int i = 0; i < tpg; ++i) a += sh[threadIdx.x * tpg + i];
-    float* out = partial + (static_cast<long long>(b * groups + threadIdx.x) * nchunks + chunk) * 2;
-    out[0] = gmean[threadIdx.x];
-    out[1] = a;
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+    float* out = partial + (static_cast<long long>(b * groups + g) * nchunks + chunk) * 2;
+    out[0] = g_sum[g] * inv_n;
+    out[1] = g_m2[g];
   }
 }
 
-// exact (Chan) merge of the chunk partials; one thread per (b, group)
+// exact (Chan) merge of the chunk partials; one warp per (b, group)
 __global__ void gn_finalize_kernel(const float* __restrict__ partial, float* __restrict__ stats, int n_bg, int nchunks,
-                                   int HW, int cpg, float eps) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+                                   int HW, int cpg, int T, float eps) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (i >= n_bg) return;
   const float* p = partial + static_cast<long long>(i) * nchunks * 2;
   float tot = 0.f, wsum = 0.f;
-  for (int c = 0; c < nchunks; ++c) {
-    const float n = static_cast<float>(min(kGnChunkTokens, HW - c * kGnChunkTokens) * cpg);
+  for (int c = lane; c < nchunks; c += 32) {
+    const float n = static_cast<float>(min(T, HW - c * T) * cpg);
     wsum += n * p[2 * c];
     tot += n;
   }
-  const float mean = wsum / tot;
+  tot = warp_sum(tot);
+  const float mean = warp_sum(wsum) / tot;
   float m2 = 0.f;
-  for (int c = 0; c < nchunks; ++c) {
-    const float n = static_cast<float>(min(kGnChunkTokens, HW - c * kGnChunkTokens) * cpg);
+  for (int c = lane; c < nchunks; c += 32) {
+    const float n = static_cast<float>(min(T, HW - c * T) * cpg);
     const float d = p[2 * c] - mean;
     m2 += p[2 * c + 1] + n * d * d;
   }
-  stats[2 * i] = mean;
-  stats[2 * i + 1] = rsqrtf(m2 / tot + eps);
+  m2 = warp_sum(m2);
+  if (lane == 0) {
+    stats[2 * i] = mean;
+    stats[2 * i + 1] = rsqrtf(m2 / tot + eps);
+  }
 }
 
 __device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
 
-template <int V, bool kSilu>
-__global__ void gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
-                                    const float* __restrict__ gamma, const float* __restrict__ beta,
-                                    __nv_bfloat16* __restrict__ y, int C, int HW, int cpg) {
+template <bool kSilu>
+__global__ void __launch_bounds__(320) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int T) {
   const int b = blockIdx.y;
-  const int t0 = blockIdx.x * kGnChunkTokens;
-  const int nt = min(kGnChunkTokens, HW - t0);
+  const int t0 = blockIdx.x * T;
+  const int nt = min(T, HW - t0);
+  const int vpr = C >> 3;
+  const int R = blockDim.x / vpr;
+  const int vec = threadIdx.x % vpr, row = threadIdx.x / vpr;
+  const int c0 = vec * 8;
   const int groups = C / cpg;
-  const int c = V * threadIdx.x;
-  const int g = c / cpg;
-  const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
-  float sc[V], of[V];
+  float sc[8], of[8];
 #pragma unroll
-  for (int j = 0; j < V; ++j) {
-    sc[j] = rstd * gamma[c + j];
-    of[j] = beta[c + j] - mean * sc[j];
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / cpg;
+    const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
+    sc[j] = rstd * gamma[c0 + j];
+    of[j] = beta[c0 + j] - mean * sc[j];
   }
-  const long long base = (static_cast<long long>(b) * HW + t0) * C + c;
-  for (int t = 0; t < nt; ++t) {
-    float v[V];
-    load_bf16_vec<V>(x + base + static_cast<long long>(t) * C, v);
+  const long long base = (static_cast<long long>(b) * HW + t0) * vpr + vec;
+  const uint4* xp = reinterpret_cast<const uint4*>(x) + base;
+  uint4* yp = reinterpret_cast<uint4*>(y) + base;
+  uint4 data[kGnTpt];
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      v[j] = v[j] * sc[j] + of[j];
-      if (kSilu) v[j] = silu(v[j]);
+  for (int i = 0; i < kGnTpt; ++i) {
+    const int t = row + i * R;
+    if (t < nt) data[i] = xp[static_cast<long long>(t) * vpr];
+  }
+#pragma unroll
+  for (int i = 0; i < kGnTpt; ++i) {
+    const int t = row + i * R;
+    if (t < nt) {
+      float v[8];
+      unpack8(data[i], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[j] = v[j] * sc[j] + of[j];
+        if (kSilu) v[j] = silu(v[j]);
+      }
+      yp[static_cast<long long>(t) * vpr] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                        pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
     }
-    store_bf16_vec<V>(y + base + static_cast<long long>(t) * C, v);
   }
+}
+
+// launch geometry of the token-major kernels: threads per block, token rows per pass, tokens per block
+struct GnTokGeom {
+  int threads, rows, T, nchunks;
+};
+inline GnTokGeom gn_tok_geom(int batch, int channels, int hw) {
+  GnTokGeom g;
+  const int vpr = channels / 8;
+  g.rows = 256 / vpr > 0 ? 256 / vpr : 1;
+  g.threads = g.rows * vpr;
+  g.T = g.rows * kGnTpt;
+  // keep at least ~2 waves of blocks on the GPU when the tensor is small
+  while (g.T > g.rows && static_cast<long long>(batch) * ((hw + g.T - 1) / g.T) < 2ll * num_sms()) g.T -= g.rows;
+  if (g.T > hw) g.T = ((hw + g.rows - 1) / g.rows) * g.rows;
+  g.nchunks = (hw + g.T - 1) / g.T;
+  return g;
 }
 
 // ---- LayerNorm: one warp per row, row kept in registers (C <= 8*32*kMaxChunks) -------------------------
@@ -286,8 +344,8 @@ __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const __nv_bfloat16
 }  // namespace afb
 
 extern "C" int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups) {
-  const int64_t nchunks = (hw + afb::kGnChunkTokens - 1) / afb::kGnChunkTokens;
-  return 2ll * batch * groups * (nchunks + 1);
+  // worst case of gn_tok_geom: one token row per chunk
+  return 2ll * batch * groups * (static_cast<int64_t>(hw) + 1);
 }
 
 extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
@@ -311,30 +369,21 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
     gn_apply_nchw_kernel<<<grid, 256, 0, stream>>>(static_cast<const float*>(x), stats_ws, gamma, beta, yb, channels, hw, cpg, act);
     count_launch();
   } else if (x_layout == 1) {
-    const int V = (channels / 2 <= 1024) ? 2 : 4;
-    AFB_REQUIRE(channels / V <= 1024 && cpg % V == 0 && groups <= channels / V,
+    AFB_REQUIRE(channels / 8 <= 320 && groups <= kGnMaxGroups,
                 "afb_groupnorm_tokens: channels %d / groups %d not supported by the token-major kernel", channels, groups);
-    AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 7) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0,
-                "afb_groupnorm_tokens: buffers must be 8-byte aligned");
-    const int nchunks = (hw + kGnChunkTokens - 1) / kGnChunkTokens;
+    AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0,
+                "afb_groupnorm_tokens: buffers must be 16-byte aligned");
+    const GnTokGeom geo = gn_tok_geom(batch, channels, hw);
     float* partial = stats_ws + 2ll * batch * groups;
     const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
-    dim3 grid(nchunks, batch);
-    const int threads = channels / V;
-    const size_t sh = (threads + groups) * sizeof(float);
-    if (V == 2) gn_partial_tok_kernel<2><<<grid, threads, sh, stream>>>(xb, partial, channels, hw, cpg, nchunks);
-    else gn_partial_tok_kernel<4><<<grid, threads, sh, stream>>>(xb, partial, channels, hw, cpg, nchunks);
+    dim3 grid(geo.nchunks, batch);
+    gn_partial_tok_kernel<<<grid, geo.threads, 0, stream>>>(xb, partial, channels, hw, cpg, geo.T, geo.nchunks);
     count_launch();
     const int n_bg = batch * groups;
-    gn_finalize_kernel<<<(n_bg + 127) / 128, 128, 0, stream>>>(partial, stats_ws, n_bg, nchunks, hw, cpg, eps);
+    gn_finalize_kernel<<<(n_bg * 32 + 255) / 256, 256, 0, stream>>>(partial, stats_ws, n_bg, geo.nchunks, hw, cpg, geo.T, eps);
     count_launch();
-    if (V == 2) {
-      if (act) gn_apply_tok_kernel<2, true><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
-      else gn_apply_tok_kernel<2, false><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
-    } else {
-      if (act) gn_apply_tok_kernel<4, true><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
-      else gn_apply_tok_kernel<4, false><<<grid, threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg);
-    }
+    if (act) gn_apply_tok_kernel<true><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg, geo.T);
+    else gn_apply_tok_kernel<false><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg, geo.T);
     count_launch();
   } else {
     AFB_FAIL(2, "afb_groupnorm_tokens: unknown x_layout %d", x_layout);

@@ -249,8 +249,10 @@ def ada_pool_prep(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_
     b = bg_q_emb.shape[0]
     f = lambda t: t.to(torch.float32).contiguous()
     lora_q = torch.empty((b, 2, c // 8), dtype=torch.float32, device=to_k_weight.device)
-    _run("ada_pool_prep", _lib.load().afb_ada_pool_prep, _ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)),
-         _ptr(f(bg_q_emb)), _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(lora_q), b, c, _stream(),
+    lib = _lib.load()
+    ws = torch.empty(int(lib.afb_ada_pool_prep_ws_floats(b, c)), dtype=torch.float32, device=to_k_weight.device)
+    _run("ada_pool_prep", lib.afb_ada_pool_prep, _ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)),
+         _ptr(f(bg_q_emb)), _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(lora_q), _ptr(ws), b, c, _stream(),
          nbytes=4.0 * c * ctx_dim)
     return lora_q
 

@@ -303,6 +303,16 @@ def run_ours(args):
         recs = ops.stop_timing()
         model.use_cuda_graph = not args.no_graph
 
+    if args.dump_kernels and rank == 0:
+        by_tag = {}
+        for r in recs:
+            e = by_tag.setdefault((r["name"], r["tag"]), {"ms": 0.0, "flops": 0.0, "bytes": 0.0, "n": 0})
+            e["ms"] += r["ms"]; e["flops"] += r["flops"]; e["bytes"] += r["bytes"]; e["n"] += 1
+        with open(args.dump_kernels, "w") as fh:
+            fh.write("kernel,shape,launches,total_ms,avg_us,tflops,gbs\n")
+            for (n, tag), e in sorted(by_tag.items(), key=lambda kv: -kv[1]["ms"]):
+                fh.write(f"{n},{tag},{e['n']},{e['ms']:.4f},{1e3 * e['ms'] / e['n']:.1f},"
+                         f"{e['flops'] / (e['ms'] * 1e-3) / 1e12:.1f},{e['bytes'] / (e['ms'] * 1e-3) / 1e9:.0f}\n")
     groups = {}
     for r in recs:
         gk = groups.setdefault(r["name"], {"ms": 0.0, "flops": 0.0, "bytes": 0.0, "launches": 0})
@@ -362,6 +372,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dump-kernels", default=None, help="write the per-shape kernel breakdown of one step as CSV")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

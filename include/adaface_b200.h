@@ -105,14 +105,16 @@ int afb_attention_fwd(const afb_attn_args* args, afb_stream_t stream);
 /* ---- K12: AttentionalPooler.forward, eval mode.  Replaces embedding_manager.py:146-321.
  * afb_ada_pool_prep (step-invariant, :186-235): fg_q/bg_q = to_k(query embedding) with the layer's attn2.to_k
  *   weight fp32 [C, ctx_dim]; fg_q_emb fp32 [ctx_dim] (shared by the batch), bg_q_emb fp32 [B, ctx_dim];
- *   LayerNorm; grouped 1x1 convs lora_to_fg_q / lora_to_bg_q (fp32 [C/8, C/8], 8 groups) -> lora_q fp32 [B,2,C/8].
+ *   LayerNorm; grouped 1x1 convs lora_to_fg_q / lora_to_bg_q (fp32 [C/8, C/8], 8 groups) -> lora_q fp32 [B,2,C/8];
+ *   prep_ws: fp32 workspace of afb_ada_pool_prep_ws_floats(B, C) floats.
  * afb_ada_pool: x, q bf16 [B, N, C] (block input x1 and attn2.to_q(norm2(x1))); lora_to_k fp32 [C/8, C/8];
  *   key_mask NULL or uint8 [B, N] (0 = masked).  Outputs fp32: fg_out, bg_out [B, C]; attn_fg, attn_bg
  *   [B, 8, N] (both NULL to skip).  ws: fp32 workspace of afb_ada_pool_ws_floats(B, N, C) floats. */
 int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels);
+int64_t afb_ada_pool_prep_ws_floats(int batch, int channels);
 int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
-                      const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, int batch, int channels,
-                      afb_stream_t stream);
+                      const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, float* prep_ws, int batch,
+                      int channels, afb_stream_t stream);
 int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* lora_q, const float* lora_to_k,
                  const uint8_t* key_mask, float* fg_out, float* bg_out, float* attn_fg, float* attn_bg, float* ws,
                  int batch, int n_tokens, int channels, afb_stream_t stream);
