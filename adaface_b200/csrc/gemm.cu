@@ -1,12 +1,19 @@
 // Persistent, warp-specialised BF16 GEMM for sm_100a:  Y = epilogue(A[M,K] * W[N,K]^T).
 //
+// Hot variant (bf16 out, optional bf16 residual, plain or GEGLU epilogue) - gemm_bf16_tma_kernel, 384 threads:
 //   warp 0 (one lane)  TMA producer: A tile 128x64 and W tile BNx64 (both K-major, SWIZZLE_128B) into a
 //                      kStages-deep shared-memory ring, mbarrier complete_tx signalling
 //   warp 1 (one lane)  tcgen05.mma issuer: 128 x BN x 16 UMMAs, fp32 accumulators in TMEM, two
 //                      accumulator buffers so the epilogue of tile i overlaps the main loop of tile i+1
 //   warp 2             TMEM allocator
-//   warps 4..7         epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> bias / residual / GEGLU /
-//                      NCHW transposition -> global
+//   warp 3 (one lane)  staging manager: when the output staging buffer of tile i is free again, TMA-loads the
+//                      RESIDUAL tile of tile i into it (one tile ahead of the epilogue, so DRAM latency is hidden)
+//   warps 4..11        epilogue, 2 warps per TMEM lane quarter: tcgen05.ld 32 columns -> + bias (+ residual read
+//                      in place from the staging box) [GEGLU: value * gelu(gate)] -> bf16 -> staging box
+//                      ([128 rows x 32 cols], SWIZZLE_64B, conflict-free 16-byte accesses) -> TMA store (fully
+//                      coalesced writes, clipped at the M / N edges by the tensor map)
+// Cold variants (fp32 out, fp32 residual, NCHW-transposing epilogue of the fp32 drop-in path) -
+// gemm_bf16_kernel, 256 threads, registers -> global directly.
 //
 // Replaces the nn.Linear / 1x1 Conv2d calls of ldm/modules/attention.py (:35, :55, :157-165, :302-317).
 #include "common.cuh"
@@ -216,18 +223,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                                    pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
             }
           }
-        } else if constexpr (EPI == AFB_EPI_GEGLU) {
-          // columns [0,16) of the chunk are the value rows, [16,32) the gate rows of the same 16 outputs
-          if (row_ok) {
-            float o[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) o[j] = v[j] * gelu_erf(v[16 + j]);
-            uint4* o4 = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + static_cast<long long>(m) * p.ldo + (n0 >> 1));
-#pragma unroll
-            for (int j = 0; j < 2; ++j)
-              o4[j] = make_uint4(pack_bf16x2(o[8 * j], o[8 * j + 1]), pack_bf16x2(o[8 * j + 2], o[8 * j + 3]),
-                                 pack_bf16x2(o[8 * j + 4], o[8 * j + 5]), pack_bf16x2(o[8 * j + 6], o[8 * j + 7]));
-          }
         } else {  // AFB_EPI_NCHW: out[b][n][t] fp32, lanes run along t (coalesced)
           if (row_ok) {
             const int b = m / p.hw;
@@ -257,6 +252,344 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc<C::kTmemCols>(tmem_base);
+}
+
+// ============================================================================================
+// Hot variant: TMA-staged epilogue
+// ============================================================================================
+constexpr int kTmaThreads = 384;
+constexpr int kBoxBytes = kBM * 32 * 2;      // one staging box: 128 rows x 32 bf16 columns
+
+template <int BN, bool GEGLU>
+struct TCfg {
+  static constexpr int kABytes = kBM * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kOutChunks = GEGLU ? BN / 64 : BN / 32;        // 32-column output boxes per tile
+  static constexpr int kStagingBytes = 2 * kOutChunks * kBoxBytes;     // double-buffered
+  static constexpr int kBarrierBytes = 512;
+  static constexpr int kStages = (227 * 1024 - 1024 - kBarrierBytes - kStagingBytes) / kStageBytes;
+  static constexpr int kTmemCols = (2 * BN <= 256) ? 256 : 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 + kBarrierBytes;
+  static_assert(kBBytes % 1024 == 0, "W tile must keep 1024B alignment of the next stage");
+  static_assert(kStages >= 3 && kStages <= 12, "pipeline depth");
+  static_assert(GEGLU ? BN % 64 == 0 : BN % 32 == 0, "tile width vs output boxes");
+};
+
+struct GemmTmaDev {
+  const float* bias;
+  int M, N, K;
+  int has_res;
+  int num_m_blocks, num_n_blocks, num_k_blocks;
+};
+
+template <int BN, bool GEGLU>
+__global__ void __launch_bounds__(kTmaThreads, 1)
+gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
+                     const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_res,
+                     const GemmTmaDev p) {
+  using C = TCfg<BN, GEGLU>;
+  constexpr int NC = C::kOutChunks;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + C::kStages * C::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::kStagingBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + C::kStages;
+  uint64_t* tmem_full = bars + 2 * C::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint64_t* out_free = tmem_empty + 2;     // staging buffer b: its TMA stores have finished reading shared memory
+  uint64_t* res_full = out_free + 2;       // staging buffer b: residual landed (or: buffer handed to the epilogue)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_a);
+    tma_prefetch_desc(&tm_w);
+    tma_prefetch_desc(&tm_out);
+    if (p.has_res) tma_prefetch_desc(&tm_res);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 8);
+      mbar_init(&out_free[i], 2);
+      mbar_init(&res_full[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ operand producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile / p.num_n_blocks;
+        const int n_blk = tile % p.num_n_blocks;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          uint8_t* sb = sa + C::kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+          tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+          tma_load_2d(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN, kEvictLast);
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint64_t da = umma_desc_kmajor_sw128(sa);
+          const uint64_t db = umma_desc_kmajor_sw128(sa + C::kABytes);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          umma_commit(&empty_bar[stage]);
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ------------------------------------------------------------------ staging manager
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int sb = it & 1;
+        const uint32_t use = static_cast<uint32_t>(it >> 1);
+        mbar_wait(&out_free[sb], (use & 1) ^ 1);
+        if (p.has_res) {
+          const int m_blk = tile / p.num_n_blocks;
+          const int n_blk = tile % p.num_n_blocks;
+          int valid = 0;
+#pragma unroll
+          for (int ch = 0; ch < NC; ++ch)
+            if (n_blk * BN + ch * 32 < p.N) ++valid;
+          mbar_arrive_expect_tx(&res_full[sb], valid * kBoxBytes);
+#pragma unroll
+          for (int ch = 0; ch < NC; ++ch) {
+            const int n0 = n_blk * BN + ch * 32;
+            if (n0 < p.N) tma_load_2d(&tm_res, &res_full[sb], staging + (sb * NC + ch) * kBoxBytes, n0, m_blk * kBM, kEvictFirst);
+          }
+        } else {
+          mbar_arrive(&res_full[sb]);
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue
+    const int q = warp & 3;                         // TMEM lane quarter
+    const int grp = (warp - 4) >> 2;                // column group 0 / 1
+    constexpr int kSplit = (NC + 1) / 2;
+    const int ch_lo = grp == 0 ? 0 : kSplit;
+    const int ch_hi = grp == 0 ? kSplit : NC;
+    const bool leader = (q == 0) && (lane == 0);    // issues this group's TMA stores
+    const int row = q * 32 + lane;
+    const uint32_t sw = static_cast<uint32_t>((row >> 1) & 3);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m_blk = tile / p.num_n_blocks;
+      const int n_blk = tile % p.num_n_blocks;
+      const int sb = it & 1;
+      const uint32_t use = static_cast<uint32_t>(it >> 1);
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      if (leader) {
+        // the stores of the previous tile (other staging buffer) have certainly been issued: once they have
+        // finished reading shared memory, hand that buffer back to the staging manager
+        bulk_wait_group_read<0>();
+        if (it > 0) mbar_arrive(&out_free[sb ^ 1]);
+      }
+      mbar_wait(&res_full[sb], use & 1);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      bool released = false;
+#pragma unroll 1
+      for (int ch = ch_lo; ch < ch_hi; ++ch) {
+        const int n_out0 = (GEGLU ? n_blk * (BN / 2) : n_blk * BN) + ch * 32;     // first output column of this box
+        const int n_acc0 = GEGLU ? n_blk * BN + ch * 64 : n_out0;                  // first accumulator column
+        if (n_acc0 >= p.N) break;
+        float v[32];
+        if constexpr (GEGLU) {
+          uint32_t ra[32], rg[32];
+          tmem_ld32(taddr + ch * 64, ra);
+          tmem_ld32(taddr + ch * 64 + 32, rg);
+          tmem_ld_wait();
+          if (ch == ch_hi - 1 || n_acc0 + 64 >= p.N) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            released = true;
+          }
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_acc0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 ba = __ldg(b4 + j), bg = __ldg(b4 + 8 + j);
+            v[4 * j + 0] = (__uint_as_float(ra[4 * j + 0]) + ba.x) * gelu_erf(__uint_as_float(rg[4 * j + 0]) + bg.x);
+            v[4 * j + 1] = (__uint_as_float(ra[4 * j + 1]) + ba.y) * gelu_erf(__uint_as_float(rg[4 * j + 1]) + bg.y);
+            v[4 * j + 2] = (__uint_as_float(ra[4 * j + 2]) + ba.z) * gelu_erf(__uint_as_float(rg[4 * j + 2]) + bg.z);
+            v[4 * j + 3] = (__uint_as_float(ra[4 * j + 3]) + ba.w) * gelu_erf(__uint_as_float(rg[4 * j + 3]) + bg.w);
+          }
+        } else {
+          uint32_t r[32];
+          tmem_ld32(taddr + ch * 32, r);
+          tmem_ld_wait();
+          if (ch == ch_hi - 1 || n_acc0 + 32 >= p.N) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            released = true;
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (p.bias != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_acc0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = __ldg(b4 + j);
+              v[4 * j + 0] += b.x;
+              v[4 * j + 1] += b.y;
+              v[4 * j + 2] += b.z;
+              v[4 * j + 3] += b.w;
+            }
+          }
+        }
+        // staging box [128 rows][32 cols] bf16, 64-byte rows, SWIZZLE_64B: 16-byte chunk c of row r sits at c ^ ((r >> 1) & 3)
+        uint8_t* brow = staging + (sb * NC + ch) * kBoxBytes + row * 64;
+        if (!GEGLU && p.has_res) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const uint4 t = *reinterpret_cast<const uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4));
+            const float2 a = unpack_bf16x2(t.x), b = unpack_bf16x2(t.y), cc = unpack_bf16x2(t.z), d = unpack_bf16x2(t.w);
+            v[8 * c + 0] += a.x;
+            v[8 * c + 1] += a.y;
+            v[8 * c + 2] += b.x;
+            v[8 * c + 3] += b.y;
+            v[8 * c + 4] += cc.x;
+            v[8 * c + 5] += cc.y;
+            v[8 * c + 6] += d.x;
+            v[8 * c + 7] += d.y;
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4)) =
+              make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
+                         pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+        fence_proxy_async_smem();
+        named_bar_sync(1 + grp, 128);
+        if (leader) tma_store_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
+      }
+      if (!released) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      }
+      if (leader) bulk_commit_group();
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (leader) bulk_wait_group_read<0>();      // shared memory must outlive the last stores' reads
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<C::kTmemCols>(tmem_base);
+}
+
+int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows, int64_t ld) {
+  const uint64_t dims[2] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(rows)};
+  const uint64_t strides[1] = {static_cast<uint64_t>(ld) * 2};
+  const uint32_t box[2] = {32, kBM};
+  return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, Swizzle::B64);
+}
+
+template <int BN, bool GEGLU>
+int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
+  using C = TCfg<BN, GEGLU>;
+  CUtensorMap tm_a, tm_w, tm_out, tm_res;
+  {
+    const uint64_t dims[2] = {static_cast<uint64_t>(a.k), static_cast<uint64_t>(a.m)};
+    const uint64_t strides[1] = {static_cast<uint64_t>(a.lda) * 2};
+    const uint32_t box[2] = {kBK, kBM};
+    if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.a, dims, strides, box, Swizzle::B128))
+      return rc;
+  }
+  {
+    const uint64_t dims[2] = {static_cast<uint64_t>(a.k), static_cast<uint64_t>(a.n)};
+    const uint64_t strides[1] = {static_cast<uint64_t>(a.ldw) * 2};
+    const uint32_t box[2] = {kBK, BN};
+    if (int rc = make_tensor_map(&tm_w, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.w, dims, strides, box, Swizzle::B128))
+      return rc;
+  }
+  const int64_t n_out = GEGLU ? a.n / 2 : a.n;
+  if (int rc = make_box_map(&tm_out, a.out, n_out, a.m, a.ldo)) return rc;
+  if (a.residual != nullptr) {
+    if (int rc = make_box_map(&tm_res, a.residual, n_out, a.m, a.ldr)) return rc;
+  } else {
+    tm_res = tm_out;
+  }
+  GemmTmaDev p;
+  p.bias = a.bias;
+  p.M = static_cast<int>(a.m);
+  p.N = static_cast<int>(a.n);
+  p.K = static_cast<int>(a.k);
+  p.has_res = a.residual != nullptr;
+  p.num_m_blocks = static_cast<int>((a.m + kBM - 1) / kBM);
+  p.num_n_blocks = static_cast<int>((a.n + BN - 1) / BN);
+  p.num_k_blocks = static_cast<int>((a.k + kBK - 1) / kBK);
+  auto kern = gemm_bf16_tma_kernel<BN, GEGLU>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_set = true;
+  }
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, kTmaThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, tm_out, tm_res, p);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 template <int BN, int EPI>
@@ -338,11 +671,16 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
         AFB_REQUIRE(a.ldr >= a.n && a.ldr % 8 == 0, "afb_gemm_bf16: ldr must be >= N and a multiple of 8");
         AFB_REQUIRE((reinterpret_cast<uintptr_t>(a.residual) & 15) == 0, "afb_gemm_bf16: residual must be 16-byte aligned");
       }
+      if (a.out_dtype == AFB_BF16 && (a.residual == nullptr || a.residual_dtype == AFB_BF16)) {
+        if (a.n % 160 == 0) return launch_tma<160, false>(a, stream);
+        return launch_tma<128, false>(a, stream);
+      }
       return dispatch_bn<AFB_EPI_STORE>(a, stream);
     case AFB_EPI_GEGLU:
       AFB_REQUIRE(a.ldo >= a.n / 2 && a.ldo % 8 == 0, "afb_gemm_bf16: GEGLU ldo must be >= N/2 and a multiple of 8");
       AFB_REQUIRE(a.residual == nullptr, "afb_gemm_bf16: GEGLU epilogue takes no residual");
-      return dispatch_bn<AFB_EPI_GEGLU>(a, stream);
+      AFB_REQUIRE(a.n % 64 == 0 && a.bias != nullptr, "afb_gemm_bf16: GEGLU needs N %% 64 == 0 and a bias");
+      return launch_tma<128, true>(a, stream);
     case AFB_EPI_NCHW:
       AFB_REQUIRE(a.hw > 0 && a.m % a.hw == 0, "afb_gemm_bf16: NCHW epilogue needs hw > 0 dividing M");
       return dispatch_bn<AFB_EPI_NCHW>(a, stream);

@@ -197,12 +197,12 @@ def _(a, w, bias, residual):
 
 
 def interleave_geglu(weight: Tensor, bias: Tensor) -> Tuple[Tensor, Tensor]:
-    """Reorders GEGLU.proj rows [value(4C); gate(4C)] into 16-row groups (16 value rows, their 16 gate rows, ...)
-    so that one 32-column accumulator chunk of the GEMM epilogue holds both halves of 16 outputs."""
+    """Reorders GEGLU.proj rows [value(4C); gate(4C)] into 32-row groups (32 value rows, their 32 gate rows, ...)
+    so that two adjacent 32-column accumulator chunks of the GEMM epilogue hold both halves of 32 outputs."""
     half = weight.shape[0] // 2
-    if half % 16:
-        raise ValueError("interleave_geglu: inner dim must be a multiple of 16")
-    idx = torch.arange(half, device=weight.device).reshape(-1, 16)
+    if half % 32:
+        raise ValueError("interleave_geglu: inner dim must be a multiple of 32")
+    idx = torch.arange(half, device=weight.device).reshape(-1, 32)
     order = torch.cat([idx, idx + half], dim=1).reshape(-1)
     return weight[order].contiguous(), bias[order].contiguous()
 

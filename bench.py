@@ -181,6 +181,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback (use --impl reference)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    torch.backends.cudnn.benchmark = True       # the torch ResBlock convolutions pick their fastest cuDNN algorithm
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 

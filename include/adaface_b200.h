@@ -61,8 +61,8 @@ int afb_layernorm_bf16(const afb_bf16* x, const float* gamma, const float* beta,
  * Replaces every nn.Linear / 1x1 nn.Conv2d on the path (attention.py:35,55,157-165,302-317). */
 enum afb_gemm_epilogue {
   AFB_EPI_STORE = 0,  /* out[m,n] = acc + bias[n] (+ residual[m,n]); row-major, out_dtype selects bf16/fp32 */
-  AFB_EPI_GEGLU = 1,  /* W rows interleaved (16 value rows, 16 gate rows, ...): out[m,j] = a * gelu_erf(g), */
-                      /* out is bf16 [M, N/2] (attention.py:32-39)                                           */
+  AFB_EPI_GEGLU = 1,  /* W / bias rows interleaved (32 value rows, their 32 gate rows, ...), N % 64 == 0:       */
+                      /* out[m,j] = a * gelu_erf(g), out is bf16 [M, N/2] (attention.py:32-39)               */
   AFB_EPI_NCHW = 2    /* out fp32 [B, N, HW] with m = b*HW + t: out = acc + bias + residual (same layout)     */
                       /* (proj_out + 'b (h w) c -> b c h w' + x_in: attention.py:335-341)                    */
 };

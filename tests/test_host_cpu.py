@@ -165,8 +165,11 @@ def test_geglu_interleave_is_a_row_permutation():
     w = torch.arange(64 * 3, dtype=torch.float32).reshape(64, 3)
     b = torch.arange(64, dtype=torch.float32)
     wi, bi = interleave_geglu(w, b)
-    # rows 0..15 are value rows 0..15, rows 16..31 their gate rows (32..47), then value 16..31, gate 48..63
-    assert bi.tolist() == list(range(0, 16)) + list(range(32, 48)) + list(range(16, 32)) + list(range(48, 64))
+    w = torch.arange(128 * 3, dtype=torch.float32).reshape(128, 3)
+    b = torch.arange(128, dtype=torch.float32)
+    wi, bi = interleave_geglu(w, b)
+    # rows 0..31 are value rows 0..31, rows 32..63 their gate rows (64..95), then value 32..63, gate 96..127
+    assert bi.tolist() == list(range(0, 32)) + list(range(64, 96)) + list(range(32, 64)) + list(range(96, 128))
     assert torch.equal(wi[:, 0] / 3, bi)
 
 
