@@ -40,15 +40,16 @@ _SIGNATURES = {
     "afb_launch_count": (_I64, []),
     "afb_cfg_ddim_step": (_I, [_P, _P, _P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _F, _P]),
     "afb_groupnorm_ws_floats": (_I64, [_I, _I, _I]),
-    "afb_groupnorm_tokens": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _P]),
+    "afb_groupnorm_tokens": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _P, _I, _P]),
+    "afb_add_bias_residual": (_I, [_P, _P, _P, _P, _I64, _I, _P]),
     "afb_layernorm_bf16": (_I, [_P, _P, _P, _P, _I64, _I, _F, _P]),
     "afb_gemm_bf16": (_I, [C.POINTER(GemmArgs), _P]),
     "afb_attention_fwd": (_I, [C.POINTER(AttnArgs), _P]),
     "afb_ada_pool_ws_floats": (_I64, [_I, _I, _I]),
     "afb_ada_pool_prep_ws_floats": (_I64, [_I, _I]),
-    "afb_ada_pool_prep": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
-    "afb_ada_pool": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
-    "afb_ada_head": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "afb_ada_pool_prep": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
+    "afb_ada_pool": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "afb_ada_head": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I64, _I, _I, _I, _I, _I, _I, _P]),
     "afb_cast_f32_to_bf16": (_I, [_P, _P, _I64, _P]),
     "afb_cast_bf16_to_f32": (_I, [_P, _P, _I64, _P]),
 }

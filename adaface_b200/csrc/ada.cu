@@ -1,13 +1,22 @@
 // K12/K13: AttentionalPooler + AdaEmbedding head (ldm/modules/embedding_manager.py:100-321, 539-910).
 //
-// K12 streams the layer's x and q ([B,N,C] bf16) exactly once (HBM-bound: 2*N*C*2 bytes per sample):
-//   prep    per sample: fg_q/bg_q = to_k(query embedding), LayerNorm, grouped 1x1 conv -> lora_q [2, C/8]
-//   main    one warp per token: LN(q), v = (x + LN(q))/sqrt(8), grouped 1x1 conv -> lora_k [C/8], the two
-//           per-head scores, head-average smoothing, then a flash-style online softmax over the joint
-//           (fg|bg) x token axis accumulating the fg- and bg-weighted sums of v; per-block partials
-//   combine per sample: exact merge of the block partials -> fg_out, bg_out [B, C] (+ softmax stats)
+// K12 streams the layer's x and q ([B,N,C] bf16) exactly once (HBM-bound: 2*N*C*2 bytes per sample).
+//
+// Algebra used (exact, eval mode).  With v_t = (x_t + LN(q_t)) / sqrt(8) (:160-178), the reference computes
+// lora_k_t = conv_g(v_t) / sqrt(8) (:227, grouped 1x1 conv, 8 groups, C/8 -> C/64 per group) and the per-head
+// scores <lora_q[i][g], lora_k_t[g]> (:247).  The conv is linear, so the score of query i and head g is
+//      s[i][g][t] = sum_{c in head g} u[i][c] * v_t[c],   u[i][c] = sum_o lora_q[i][g][o] * W_k[g][o][c] / sqrt(8)
+// i.e. TWO DOT PRODUCTS per head per token against a per-sample vector u that the step-invariant prep computes once.
+//
+//   prep    ada_qproj:   proj[s] = to_k(query embedding s), one warp per output channel, weight read once
+//           ada_qfinish: LayerNorm, grouped conv of the queries (:208-235), then the fold through lora_to_k -> u [B,2,C]
+//   main    one warp per token: LN(q), v, the 16 head dots, head-average smoothing (:251-257), then a flash-style
+//           online softmax over the joint (fg|bg) x token axis (:273-286) accumulating the fg- and bg-weighted
+//           sums of v; per-block partials
+//   combine exact log-sum-exp merge of the block partials -> fg_out, bg_out [B, C] (+ softmax stats)
 //   probs   optional: attn_fg/attn_bg [B, 8, N] from the stored scores and the merged stats
-// K13 is one block per sample: LNCat, Linear -> K*r coefficients, basis combination, per-vector LN, bias.
+// K13: block (k, b): LNCat, the r coefficients of vector k, basis combination, per-vector LN, bias; optionally
+// writes the vector as bf16 straight into the layer's context rows (the subject-token splice).
 #include "common.cuh"
 #include "../../include/adaface_b200.h"
 
@@ -17,6 +26,7 @@ namespace {
 
 constexpr int kHeads = 8;
 constexpr int kPoolThreads = 256;          // 8 warps
+constexpr int kPoolWarps = kPoolThreads / 32;
 constexpr int kMaxChunksPerLane = 5;       // C <= 1280: C/8 16-byte chunks spread over 32 lanes
 constexpr float kInvSqrt8 = 0.35355339059327373f;
 constexpr float kPoolMasked = -3.0e38f;
@@ -37,15 +47,16 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 }
 
 // ---- prep, kernel 1: proj[s][c] = to_k(query embedding s)[c] (:193, :203); s = 0 is the shared fg probe, s = 1 + b
-// the bg query of sample b.  One warp per output channel: the weight row is read once and dotted with all B + 1
-// query vectors (staged in shared memory), so the [C, ctx_dim] weight streams through exactly once per call.
-constexpr int kPrepMaxSrc = 16;    // sources handled per pass (B + 1 <= 16 in one pass; more -> extra passes)
+// the bg query of sample b.  One warp per output channel: the weight row is read once (float4, all loads in flight)
+// and dotted with all query vectors (staged in shared memory).
+constexpr int kPrepMaxSrc = 9;     // sources per pass (B + 1 = 9 for 8 samples); more -> extra passes
 __global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
     const float* __restrict__ to_k_w, const float* __restrict__ fg_q_emb, const float* __restrict__ bg_q_emb,
     float* __restrict__ proj, int C, int ctx_dim, int n_src) {
   extern __shared__ float sh[];      // [min(n_src, kPrepMaxSrc)][ctx_dim]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int c = blockIdx.x * (kPoolThreads >> 5) + warp;
+  const int c = blockIdx.x * kPoolWarps + warp;
+  const int n4 = ctx_dim >> 2;
   for (int s0 = 0; s0 < n_src; s0 += kPrepMaxSrc) {
     const int ns = min(kPrepMaxSrc, n_src - s0);
     __syncthreads();
@@ -58,12 +69,17 @@ __global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
       float acc[kPrepMaxSrc];
 #pragma unroll
       for (int i = 0; i < kPrepMaxSrc; ++i) acc[i] = 0.f;
-      const float* wr = to_k_w + static_cast<long long>(c) * ctx_dim;
-      for (int k = lane; k < ctx_dim; k += 32) {
-        const float w = wr[k];
+      const float4* wr = reinterpret_cast<const float4*>(to_k_w + static_cast<long long>(c) * ctx_dim);
+#pragma unroll 2
+      for (int k4 = lane; k4 < n4; k4 += 32) {
+        const float4 w = __ldg(wr + k4);
 #pragma unroll
-        for (int i = 0; i < kPrepMaxSrc; ++i)
-          if (i < ns) acc[i] += w * sh[i * ctx_dim + k];
+        for (int i = 0; i < kPrepMaxSrc; ++i) {
+          if (i < ns) {
+            const float4 e = *reinterpret_cast<const float4*>(sh + i * ctx_dim + 4 * k4);
+            acc[i] += w.x * e.x + w.y * e.y + w.z * e.z + w.w * e.w;
+          }
+        }
       }
 #pragma unroll
       for (int i = 0; i < kPrepMaxSrc; ++i) {
@@ -77,38 +93,52 @@ __global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
 }
 
 // ---- prep, kernel 2: block (b, i): LayerNorm (no affine, :208-209) of the projected query, grouped 1x1 conv
-// (:219, :222) and the 8^-1/2 * 8^-1/2 factor (:235) -> lora_q[b][i][g*lg + o]; i = 0 (fg), 1 (bg).
+// (:219, :222) with the 8^-1/2 * 8^-1/2 factor (:235) -> lora_q [dg], then the fold through lora_to_k:
+// u[b][i][c] = 8^-1/2 * sum_o lora_q[g*lg + o] * W_k[g*lg + o][c - g*dg]     (g = c / dg)
 __global__ void __launch_bounds__(kPoolThreads) ada_qfinish_kernel(const float* __restrict__ proj,
                                                                   const float* __restrict__ w_fg,
                                                                   const float* __restrict__ w_bg,
-                                                                  float* __restrict__ lora_q, int C) {
-  extern __shared__ float sh[];      // [C]
+                                                                  const float* __restrict__ w_k,
+                                                                  float* __restrict__ u, int C) {
+  extern __shared__ float sh[];      // [C] normalised query, [dg] lora_q
   __shared__ float red[32];
   const int b = blockIdx.x, i = blockIdx.y;
   const int dg = C / kHeads, lg = dg / kHeads;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* s_q = sh;
+  float* s_lq = sh + C;
   const float* src = proj + static_cast<long long>(i == 0 ? 0 : 1 + b) * C;
   float s = 0.f;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const float v = src[c];
-    sh[c] = v;
+    s_q[c] = v;
     s += v;
   }
   const float mean = block_sum_256(s, red) / C;
   float m2 = 0.f;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float d = sh[c] - mean;
+    const float d = s_q[c] - mean;
     m2 += d * d;
   }
   const float rstd = rsqrtf(block_sum_256(m2, red) / C + 1e-5f);
-  for (int c = threadIdx.x; c < C; c += blockDim.x) sh[c] = (sh[c] - mean) * rstd;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) s_q[c] = (s_q[c] - mean) * rstd;
   __syncthreads();
   const float* wsel = (i == 0) ? w_fg : w_bg;
-  for (int j = threadIdx.x; j < dg; j += blockDim.x) {      // j = g*lg + o
+  for (int j = warp; j < dg; j += kPoolWarps) {      // j = g*lg + o; one warp per output, coalesced weight row
     const int g = j / lg;
     const float* w = wsel + static_cast<long long>(j) * dg;
     float a = 0.f;
-    for (int k = 0; k < dg; ++k) a += w[k] * sh[g * dg + k];
-    lora_q[(static_cast<long long>(b) * 2 + i) * dg + j] = a * kInvSqrt8 * kInvSqrt8;
+    for (int k = lane; k < dg; k += 32) a += w[k] * s_q[g * dg + k];
+    a = warp_sum(a);
+    if (lane == 0) s_lq[j] = a * kInvSqrt8 * kInvSqrt8;
+  }
+  __syncthreads();
+  float* out = u + (static_cast<long long>(b) * 2 + i) * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / dg, k = c - g * dg;
+    float a = 0.f;
+    for (int o = 0; o < lg; ++o) a += s_lq[g * lg + o] * w_k[static_cast<long long>(g * lg + o) * dg + k];
+    out[c] = a * kInvSqrt8;
   }
 }
 
@@ -117,28 +147,18 @@ __host__ __device__ inline long long pool_partial_floats(int C) { return 16 + 2l
 
 template <int kChunks>
 __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
-    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ lora_q,
-    const float* __restrict__ w_k, const uint8_t* __restrict__ key_mask, float* __restrict__ scores,
-    float* __restrict__ partials, int N, int C, int tokens_per_block) {
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
+    const uint8_t* __restrict__ key_mask, float* __restrict__ scores, float* __restrict__ partials, int N, int C,
+    int tokens_per_block) {
   extern __shared__ float sh[];
-  const int dg = C / kHeads, lg = dg / kHeads;          // per-head in / out channels of the grouped conv
-  const int nout = dg;                                  // = 8 * lg outputs
-  float* s_wt = sh;                                     // [8][dg][lg]  transposed lora_to_k weights
-  float* s_lq = s_wt + kHeads * dg * lg;                // [2][nout]
-  float* s_v = s_lq + 2 * nout;                         // [8 warps][C]
-  float* s_lk = s_v + 8 * C;                            // [8 warps][nout]
-  float* s_red = sh;                                    // [8 warps][16 + 2C], reuses the buffers above after the token loop
+  float* s_u = sh;                                      // [2][C] folded queries of this sample
+  float* s_part = s_u + 2 * C;                          // [8 warps][2][kChunks * 32] per-chunk dots
+  float* s_red = sh;                                    // [8 warps][16 + 2C], reuses the buffers after the token loop
 
+  const int dg = C / kHeads;
   const int b = blockIdx.y, blk = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int idx = threadIdx.x; idx < kHeads * dg * lg; idx += blockDim.x) {
-    // w_k is [nout][dg] (row j = g*lg + o); store as [g][i][o]
-    const int j = idx / dg, i = idx % dg;
-    const int g = j / lg, o = j % lg;
-    s_wt[(g * dg + i) * lg + o] = w_k[idx];
-  }
-  for (int idx = threadIdx.x; idx < 2 * nout; idx += blockDim.x)
-    s_lq[idx] = lora_q[static_cast<long long>(b) * 2 * nout + idx];
+  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) s_u[idx] = u[static_cast<long long>(b) * 2 * C + idx];
   __syncthreads();
 
   const int nchunks = C >> 3;
@@ -148,33 +168,39 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
   for (int i = 0; i < kChunks; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc_fg[i][j] = acc_bg[i][j] = 0.f;
-  // lanes 0..7 carry the running max / sum of head g = lane
+  // every lane tracks the running max / sum of head lane & 7 (lanes 0..7 are the ones written out)
   float m_run = -INFINITY, l_run = 0.f;
 
-  float* my_v = s_v + warp * C;
-  float* my_lk = s_lk + warp * nout;
+  float* my_part = s_part + warp * 2 * (kChunks * 32);
   const int t_begin = blk * tokens_per_block;
   const int t_end = min(N, t_begin + tokens_per_block);
-  for (int t = t_begin + warp; t < t_end; t += 8) {
+  for (int t = t_begin + warp; t < t_end; t += kPoolWarps) {
     const long long rowoff = (static_cast<long long>(b) * N + t) * C;
     const uint4* xr = reinterpret_cast<const uint4*>(x + rowoff);
     const uint4* qr = reinterpret_cast<const uint4*>(q + rowoff);
-    float xv[kChunks][8], qv[kChunks][8];
-    float s = 0.f;
+    uint4 ux[kChunks], uq[kChunks];
 #pragma unroll
     for (int i = 0; i < kChunks; ++i) {
       const int ch = lane + 32 * i;
       if (ch < nchunks) {
-        const uint4 ux = xr[ch], uq = qr[ch];
+        ux[i] = xr[ch];
+        uq[i] = qr[ch];
+      }
+    }
+    float xv[kChunks][8], qv[kChunks][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      if (lane + 32 * i < nchunks) {
         float2 a;
-        a = unpack_bf16x2(ux.x); xv[i][0] = a.x; xv[i][1] = a.y;
-        a = unpack_bf16x2(ux.y); xv[i][2] = a.x; xv[i][3] = a.y;
-        a = unpack_bf16x2(ux.z); xv[i][4] = a.x; xv[i][5] = a.y;
-        a = unpack_bf16x2(ux.w); xv[i][6] = a.x; xv[i][7] = a.y;
-        a = unpack_bf16x2(uq.x); qv[i][0] = a.x; qv[i][1] = a.y;
-        a = unpack_bf16x2(uq.y); qv[i][2] = a.x; qv[i][3] = a.y;
-        a = unpack_bf16x2(uq.z); qv[i][4] = a.x; qv[i][5] = a.y;
-        a = unpack_bf16x2(uq.w); qv[i][6] = a.x; qv[i][7] = a.y;
+        a = unpack_bf16x2(ux[i].x); xv[i][0] = a.x; xv[i][1] = a.y;
+        a = unpack_bf16x2(ux[i].y); xv[i][2] = a.x; xv[i][3] = a.y;
+        a = unpack_bf16x2(ux[i].z); xv[i][4] = a.x; xv[i][5] = a.y;
+        a = unpack_bf16x2(ux[i].w); xv[i][6] = a.x; xv[i][7] = a.y;
+        a = unpack_bf16x2(uq[i].x); qv[i][0] = a.x; qv[i][1] = a.y;
+        a = unpack_bf16x2(uq[i].y); qv[i][2] = a.x; qv[i][3] = a.y;
+        a = unpack_bf16x2(uq[i].z); qv[i][4] = a.x; qv[i][5] = a.y;
+        a = unpack_bf16x2(uq[i].w); qv[i][6] = a.x; qv[i][7] = a.y;
 #pragma unroll
         for (int j = 0; j < 8; ++j) s += qv[i][j];
       }
@@ -194,30 +220,30 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
     for (int i = 0; i < kChunks; ++i) {
       const int ch = lane + 32 * i;
       if (ch < nchunks) {
+        const float4* uf = reinterpret_cast<const float4*>(s_u + ch * 8);
+        const float4* ub = reinterpret_cast<const float4*>(s_u + C + ch * 8);
+        const float4 f0 = uf[0], f1 = uf[1], g0 = ub[0], g1 = ub[1];
+        const float fu[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+        const float bu[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        float d_fg = 0.f, d_bg = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xv[i][j] = (xv[i][j] + (qv[i][j] - mean) * rstd) * kInvSqrt8;       // v = (x + k_ln) * 8^-1/2 : :178
-          my_v[ch * 8 + j] = xv[i][j];
+          d_fg += fu[j] * xv[i][j];
+          d_bg += bu[j] * xv[i][j];
         }
+        my_part[ch] = d_fg;
+        my_part[kChunks * 32 + ch] = d_bg;
       }
     }
     __syncwarp();
-    // lora_k[j] = 8^-1/2 * sum_i W[g][o][i] v[g*dg + i]  (:227); product with both queries right away
-    for (int j = lane; j < nout; j += 32) {
-      const int g = j / lg, o = j % lg;
-      const float* wt = s_wt + g * dg * lg + o;
-      const float* vv = my_v + g * dg;
-      float a = 0.f;
-      for (int i = 0; i < dg; ++i) a += wt[i * lg] * vv[i];
-      my_lk[j] = a * kInvSqrt8;
-    }
-    __syncwarp();
-    // lanes 0..15: (i = lane>>3, g = lane&7) score = sum_o lora_q[i][g][o] * lora_k[g][o]  (:247)
+    // lanes 0..15: (i = lane >> 3, g = lane & 7): score = sum of the chunk dots of head g  (:247 after the fold)
     float sc = 0.f;
     if (lane < 16) {
-      const int i = lane >> 3, g = lane & 7;
-      for (int o = 0; o < lg; ++o) sc += s_lq[i * nout + g * lg + o] * my_lk[g * lg + o];
+      const float* pp = my_part + (lane >> 3) * (kChunks * 32) + (lane & 7) * chunks_per_group;
+      for (int k = 0; k < chunks_per_group; ++k) sc += pp[k];
     }
+    __syncwarp();
     // smooth with the head average (:251-257): mean over the 8 lanes of each i
     float tot = sc;
     tot += __shfl_xor_sync(0xffffffffu, tot, 1);
@@ -225,8 +251,9 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
     tot += __shfl_xor_sync(0xffffffffu, tot, 4);
     sc = 0.5f * sc + 0.5f * (tot * 0.125f);
     if (key_mask != nullptr && key_mask[static_cast<long long>(b) * N + t] == 0) sc = kPoolMasked;   // :259-269
-    if (lane < 16) scores[((static_cast<long long>(b) * kHeads + (lane & 7)) * 2 + (lane >> 3)) * N + t] = sc;
-    // online joint softmax over (fg|bg) x tokens, per head g (lanes 0..7 own the state)
+    if (scores != nullptr && lane < 16)
+      scores[((static_cast<long long>(b) * kHeads + (lane & 7)) * 2 + (lane >> 3)) * N + t] = sc;
+    // online joint softmax over (fg|bg) x tokens, per head g = lane & 7
     const float s_fg = __shfl_sync(0xffffffffu, sc, lane & 7);
     const float s_bg = __shfl_sync(0xffffffffu, sc, 8 + (lane & 7));
     const float m_new = fmaxf(m_run, fmaxf(s_fg, s_bg));
@@ -234,7 +261,7 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
     const float e_fg = __expf(s_fg - m_new), e_bg = __expf(s_bg - m_new);
     l_run = l_run * corr + e_fg + e_bg;
     m_run = m_new;
-    // every lane (all lanes computed the state of head lane&7) scales its channel chunks by their head's factors
+    // every lane scales its channel chunks by their head's factors
 #pragma unroll
     for (int i = 0; i < kChunks; ++i) {
       const int ch = lane + 32 * i;
@@ -251,7 +278,6 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
         }
       }
     }
-    __syncwarp();
   }
 
   // ---- merge the 8 warps of the block (exact log-sum-exp merge), then write the block partial
@@ -273,7 +299,7 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
   }
   __syncthreads();
   float* out = partials + (static_cast<long long>(b) * gridDim.x + blk) * pool_partial_floats(C);
-  __shared__ float s_m[8], s_scale[8][8];
+  __shared__ float s_scale[8][8];
   if (threadIdx.x < 8) {
     const int g = threadIdx.x;
     float m = -INFINITY;
@@ -281,11 +307,10 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
     float l = 0.f;
     for (int w = 0; w < 8; ++w) {
       const float mw = s_red[w * (16 + 2 * C) + g];
-      const float sc = (mw == -INFINITY) ? 0.f : __expf(mw - m);
-      s_scale[w][g] = sc;
-      l += sc * s_red[w * (16 + 2 * C) + 8 + g];
+      const float scl = (mw == -INFINITY) ? 0.f : __expf(mw - m);
+      s_scale[w][g] = scl;
+      l += scl * s_red[w * (16 + 2 * C) + 8 + g];
     }
-    s_m[g] = m;
     out[g] = m;
     out[8 + g] = l;
   }
@@ -294,38 +319,48 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
     const int c = idx % C;
     const int g = c / dg;
     float a = 0.f;
+#pragma unroll
     for (int w = 0; w < 8; ++w) a += s_scale[w][g] * s_red[w * (16 + 2 * C) + 16 + idx];
     out[16 + idx] = a;
   }
 }
 
+// grid (B, ceil(2C / 256)): every block recomputes the 8 heads' merge factors (nblocks exps each), then one thread
+// per pooled channel sums its nblocks partials
 __global__ void __launch_bounds__(256) ada_pool_combine_kernel(const float* __restrict__ partials, int nblocks, int C,
                                                                float* __restrict__ fg_out, float* __restrict__ bg_out,
                                                                float* __restrict__ stats) {
   extern __shared__ float sh[];     // [nblocks][8] scales
-  __shared__ float s_m[8], s_l[8];
+  __shared__ float s_l[8];
   const int b = blockIdx.x;
   const int dg = C / kHeads;
   const long long rec = pool_partial_floats(C);
   const float* base = partials + static_cast<long long>(b) * nblocks * rec;
-  if (threadIdx.x < 8) {
-    const int g = threadIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  {
+    const int g = warp;               // 8 warps = 8 heads
     float m = -INFINITY;
-    for (int k = 0; k < nblocks; ++k) m = fmaxf(m, base[k * rec + g]);
+    for (int k = lane; k < nblocks; k += 32) m = fmaxf(m, base[k * rec + g]);
+    m = warp_max(m);
     float l = 0.f;
-    for (int k = 0; k < nblocks; ++k) {
+    for (int k = lane; k < nblocks; k += 32) {
       const float mk = base[k * rec + g];
-      const float sc = (mk == -INFINITY) ? 0.f : __expf(mk - m);
-      sh[k * 8 + g] = sc;
-      l += sc * base[k * rec + 8 + g];
+      const float scl = (mk == -INFINITY) ? 0.f : __expf(mk - m);
+      sh[k * 8 + g] = scl;
+      l += scl * base[k * rec + 8 + g];
     }
-    s_m[g] = m;
-    s_l[g] = l;
-    stats[(static_cast<long long>(b) * 8 + g) * 2] = m;
-    stats[(static_cast<long long>(b) * 8 + g) * 2 + 1] = l;
+    l = warp_sum(l);
+    if (lane == 0) {
+      s_l[g] = l;
+      if (blockIdx.y == 0) {
+        stats[(static_cast<long long>(b) * 8 + g) * 2] = m;
+        stats[(static_cast<long long>(b) * 8 + g) * 2 + 1] = l;
+      }
+    }
   }
   __syncthreads();
-  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) {
+  const int idx = blockIdx.y * blockDim.x + threadIdx.x;
+  if (idx < 2 * C) {
     const int c = idx % C, g = c / dg;
     float a = 0.f;
     for (int k = 0; k < nblocks; ++k) a += sh[k * 8 + g] * base[k * rec + 16 + idx];
@@ -353,20 +388,23 @@ __global__ void __launch_bounds__(256) ada_pool_probs_kernel(const float* __rest
 
 // ---- K13 ------------------------------------------------------------------------------------------------
 // Block (k, b): LNCat of the pooled features and the time slice (recomputed per block, 2C + TD values), the r
-// coefficients of vector k (r dot products of length 2C + TD, one warp each), the basis combination, the
-// per-vector LayerNorm, 1/sqrt(D) and the bias.  B * K blocks instead of B.
+// coefficients of vector k (r dot products of length 2C + TD, one warp each, float4 loads), the basis combination,
+// the per-vector LayerNorm, 1/sqrt(D) and the bias.  When ctx_out is given the vector is also written as bf16 into
+// row token_pos[k] of sample b's context (the splice of the subject rows).
 __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__ infeat_fg, const float* __restrict__ infeat_bg,
                                                        const float* __restrict__ time_emb, int time_ld,
                                                        const float* __restrict__ coeff_w, const float* __restrict__ coeff_b,
                                                        const float* __restrict__ basis, const float* __restrict__ bias,
-                                                       float* __restrict__ out, int C, int TD, int K, int R, int D) {
+                                                       float* __restrict__ out, __nv_bfloat16* __restrict__ ctx_out,
+                                                       const int* __restrict__ token_pos, long long ctx_sample_stride,
+                                                       int C, int TD, int K, int R, int D) {
   extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D]
   __shared__ float red[32];
   const int k = blockIdx.x, b = blockIdx.y;
   const int F = 2 * C + TD;
   float* feat = sh;
   float* coeffs = feat + F;
-  float* vec = coeffs + R;
+  float* vec = coeffs + ((R + 3) & ~3);
   for (int i = threadIdx.x; i < F; i += blockDim.x) {
     float v;
     if (i < C) v = infeat_fg[static_cast<long long>(b) * C + i];
@@ -392,10 +430,16 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
   }
   // basis_dyn_coeffs[k] = Linear(feat)[k*R : (k+1)*R] (:858), one warp per output
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int F4 = F >> 2;
   for (int o = warp; o < R; o += (blockDim.x >> 5)) {
-    const float* w = coeff_w + static_cast<long long>(k * R + o) * F;
+    const float4* w = reinterpret_cast<const float4*>(coeff_w + static_cast<long long>(k * R + o) * F);
     float a = 0.f;
-    for (int i = lane; i < F; i += 32) a += w[i] * feat[i];
+#pragma unroll 4
+    for (int i = lane; i < F4; i += 32) {
+      const float4 ww = __ldg(w + i);
+      const float4 ff = *reinterpret_cast<const float4*>(feat + 4 * i);
+      a += ww.x * ff.x + ww.y * ff.y + ww.z * ff.z + ww.w * ff.w;
+    }
     a = warp_sum(a);
     if (lane == 0) coeffs[o] = a + coeff_b[k * R + o];
   }
@@ -405,7 +449,7 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
   float s = 0.f;
   for (int d = threadIdx.x; d < D; d += blockDim.x) {
     float a = 0.f;
-    for (int r = 0; r < R; ++r) a += coeffs[r] * basis[(static_cast<long long>(k) * R + r) * D + d];
+    for (int r = 0; r < R; ++r) a += coeffs[r] * __ldg(basis + (static_cast<long long>(k) * R + r) * D + d);
     vec[d] = a;
     s += a;
   }
@@ -416,10 +460,14 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
     m2 += dd * dd;
   }
   const float rstd = rsqrtf(block_sum_256(m2, red) / D + 1e-5f);
+  __nv_bfloat16* crow = ctx_out == nullptr ? nullptr
+                                           : ctx_out + static_cast<long long>(b) * ctx_sample_stride +
+                                                 static_cast<long long>(token_pos[k]) * D;
   for (int d = threadIdx.x; d < D; d += blockDim.x) {
     float v = (vec[d] - mean) * rstd * inv_sqrt_d;
     if (bias != nullptr) v += bias[static_cast<long long>(k) * D + d];
     out[(static_cast<long long>(b) * K + k) * D + d] = v;
+    if (crow != nullptr) crow[d] = __float2bfloat16_rn(v);
   }
 }
 
@@ -448,14 +496,15 @@ extern "C" int64_t afb_ada_pool_prep_ws_floats(int batch, int channels) {
 }
 
 extern "C" int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
-                                 const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, float* ws, int batch,
-                                 int channels, afb_stream_t stream_) {
+                                 const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k, float* pool_q,
+                                 float* ws, int batch, int channels, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  AFB_REQUIRE(to_k_weight && fg_q_emb && bg_q_emb && lora_to_fg_q && lora_to_bg_q && lora_q && ws,
+  AFB_REQUIRE(to_k_weight && fg_q_emb && bg_q_emb && lora_to_fg_q && lora_to_bg_q && lora_to_k && pool_q && ws,
               "afb_ada_pool_prep: NULL argument");
-  AFB_REQUIRE(batch > 0 && ctx_dim > 0, "afb_ada_pool_prep: empty input");
+  AFB_REQUIRE(batch > 0 && ctx_dim > 0 && ctx_dim % 4 == 0, "afb_ada_pool_prep: ctx_dim must be a positive multiple of 4");
   AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool_prep: channels %d must be a multiple of 64, <= 1280", channels);
+  AFB_REQUIRE((reinterpret_cast<uintptr_t>(to_k_weight) & 15) == 0, "afb_ada_pool_prep: to_k weight must be 16-byte aligned");
   const int n_src = batch + 1;
   const int src_in_smem = n_src < kPrepMaxSrc ? n_src : kPrepMaxSrc;
   const size_t sh1 = static_cast<size_t>(src_in_smem) * ctx_dim * sizeof(float);
@@ -465,60 +514,60 @@ extern "C" int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const fl
     AFB_CHECK_CUDA(cudaFuncSetAttribute(ada_qproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
     attr_set = true;
   }
-  const int warps = kPoolThreads >> 5;
-  ada_qproj_kernel<<<(channels + warps - 1) / warps, kPoolThreads, sh1, stream>>>(to_k_weight, fg_q_emb, bg_q_emb, ws,
-                                                                                 channels, ctx_dim, n_src);
+  ada_qproj_kernel<<<(channels + kPoolWarps - 1) / kPoolWarps, kPoolThreads, sh1, stream>>>(to_k_weight, fg_q_emb, bg_q_emb, ws,
+                                                                                           channels, ctx_dim, n_src);
   count_launch();
-  ada_qfinish_kernel<<<dim3(batch, 2), kPoolThreads, channels * sizeof(float), stream>>>(ws, lora_to_fg_q, lora_to_bg_q,
-                                                                                        lora_q, channels);
+  const size_t sh2 = (static_cast<size_t>(channels) + channels / kHeads) * sizeof(float);
+  ada_qfinish_kernel<<<dim3(batch, 2), kPoolThreads, sh2, stream>>>(ws, lora_to_fg_q, lora_to_bg_q, lora_to_k, pool_q, channels);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* lora_q, const float* lora_to_k,
-                            const uint8_t* key_mask, float* fg_out, float* bg_out, float* attn_fg, float* attn_bg, float* ws,
-                            int batch, int n_tokens, int channels, afb_stream_t stream_) {
+extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, float* fg_out,
+                            float* bg_out, float* attn_fg, float* attn_bg, float* ws, int batch, int n_tokens, int channels,
+                            afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  AFB_REQUIRE(x && q && lora_q && lora_to_k && fg_out && bg_out && ws, "afb_ada_pool: NULL argument");
+  AFB_REQUIRE(x && q && pool_q && fg_out && bg_out && ws, "afb_ada_pool: NULL argument");
   AFB_REQUIRE(batch > 0 && n_tokens > 0, "afb_ada_pool: empty input");
   AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool: channels %d must be a multiple of 64, <= 1280", channels);
   AFB_REQUIRE((attn_fg == nullptr) == (attn_bg == nullptr), "afb_ada_pool: attn_fg and attn_bg must both be given or both NULL");
   AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) & 15) == 0, "afb_ada_pool: x/q must be 16-byte aligned");
-  const int C = channels, dg = C / kHeads, lg = dg / kHeads;
+  const int C = channels;
   const int nblocks = pool_blocks_per_sample(batch, n_tokens);
   const int tokens_per_block = (n_tokens + nblocks - 1) / nblocks;
   const int grid_x = (n_tokens + tokens_per_block - 1) / tokens_per_block;
   float* scores = ws;
   float* partials = scores + static_cast<long long>(batch) * kHeads * 2 * n_tokens;
   float* stats = partials + static_cast<long long>(batch) * grid_x * pool_partial_floats(C);
+  float* scores_arg = attn_fg != nullptr ? scores : nullptr;
 
-  const size_t sh_a = (static_cast<size_t>(kHeads) * dg * lg + 2 * dg + 8 * C + 8 * dg) * sizeof(float);
-  const size_t sh_b = 8 * (16 + 2 * static_cast<size_t>(C)) * sizeof(float);
-  const size_t sh_main = sh_a > sh_b ? sh_a : sh_b;
   const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
   const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(q);
   dim3 grid(grid_x, batch);
   const int chunks_per_lane = (C / 8 + 31) / 32;
-  if (chunks_per_lane <= 2) {
-    auto kern = ada_pool_main_kernel<2>;
-    static size_t set_for = 0;
-    if (set_for < sh_main) { AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); set_for = sh_main; }
-    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
-  } else if (chunks_per_lane <= 3) {
-    auto kern = ada_pool_main_kernel<3>;
-    static size_t set_for = 0;
-    if (set_for < sh_main) { AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); set_for = sh_main; }
-    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
-  } else {
-    auto kern = ada_pool_main_kernel<kMaxChunksPerLane>;
-    static size_t set_for = 0;
-    if (set_for < sh_main) { AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); set_for = sh_main; }
-    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, lora_q, lora_to_k, key_mask, scores, partials, n_tokens, C, tokens_per_block);
+  const size_t sh_b = kPoolWarps * (16 + 2 * static_cast<size_t>(C)) * sizeof(float);
+#define AFB_LAUNCH_POOL(KCH)                                                                                              \
+  {                                                                                                                       \
+    auto kern = ada_pool_main_kernel<KCH>;                                                                                \
+    const size_t sh_a = (2 * static_cast<size_t>(C) + kPoolWarps * 2 * (KCH * 32)) * sizeof(float);                       \
+    const size_t sh_main = sh_a > sh_b ? sh_a : sh_b;                                                                     \
+    static size_t set_for = 0;                                                                                            \
+    if (set_for < sh_main) {                                                                                              \
+      AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); \
+      set_for = sh_main;                                                                                                  \
+    }                                                                                                                     \
+    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, pool_q, key_mask, scores_arg, partials, n_tokens, C,            \
+                                                  tokens_per_block);                                                      \
   }
+  if (chunks_per_lane <= 2) AFB_LAUNCH_POOL(2)
+  else if (chunks_per_lane <= 3) AFB_LAUNCH_POOL(3)
+  else AFB_LAUNCH_POOL(kMaxChunksPerLane)
+#undef AFB_LAUNCH_POOL
   count_launch();
-  ada_pool_combine_kernel<<<batch, 256, grid_x * 8 * sizeof(float), stream>>>(partials, grid_x, C, fg_out, bg_out, stats);
+  ada_pool_combine_kernel<<<dim3(batch, (2 * C + 255) / 256), 256, grid_x * 8 * sizeof(float), stream>>>(partials, grid_x, C, fg_out,
+                                                                                                         bg_out, stats);
   count_launch();
   if (attn_fg != nullptr) {
     const long long total = static_cast<long long>(batch) * kHeads * 2 * n_tokens;
@@ -533,16 +582,21 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* l
 
 extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
                             const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
-                            int batch, int channels, int td, int num_vectors, int r, int out_dim, afb_stream_t stream_) {
+                            afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int batch, int channels,
+                            int td, int num_vectors, int r, int out_dim, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(infeat_fg && infeat_bg && time_emb && coeff_w && coeff_b && basis && out, "afb_ada_head: NULL argument");
   AFB_REQUIRE(batch > 0 && channels > 0 && td > 0 && td <= time_ld && num_vectors > 0 && r > 0 && out_dim > 0,
               "afb_ada_head: bad sizes");
-  const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>(r) + out_dim) * sizeof(float);
+  AFB_REQUIRE((2 * channels + td) % 4 == 0 && (reinterpret_cast<uintptr_t>(coeff_w) & 15) == 0,
+              "afb_ada_head: coefficient map rows must be 16-byte aligned (2C + TD multiple of 4)");
+  AFB_REQUIRE((ctx_out == nullptr) == (token_pos == nullptr), "afb_ada_head: ctx_out and token_pos go together");
+  const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>((r + 3) & ~3) + out_dim) * sizeof(float);
   AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head: feature vector too large for one block (%zu bytes)", sh);
-  ada_head_kernel<<<dim3(num_vectors, batch), 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias, out,
-                                              channels, td, num_vectors, r, out_dim);
+  ada_head_kernel<<<dim3(num_vectors, batch), 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias,
+                                                                 out, reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos,
+                                                                 ctx_sample_stride, channels, td, num_vectors, r, out_dim);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

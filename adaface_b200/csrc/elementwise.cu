@@ -80,6 +80,37 @@ __global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16*
     dst[i] = __bfloat162float(src[i]);
 }
 
+// out[r][c] = a[r][c] + b[r][c] + bias[c]; 8 channels (16 bytes) per thread
+__global__ void __launch_bounds__(256) add_bias_residual_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
+                                                                const float* __restrict__ bias, uint4* __restrict__ out,
+                                                                long long nvec, int vpr) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const uint4 ua = a[i];
+    float v[8];
+    float2 t;
+    t = unpack_bf16x2(ua.x); v[0] = t.x; v[1] = t.y;
+    t = unpack_bf16x2(ua.y); v[2] = t.x; v[3] = t.y;
+    t = unpack_bf16x2(ua.z); v[4] = t.x; v[5] = t.y;
+    t = unpack_bf16x2(ua.w); v[6] = t.x; v[7] = t.y;
+    if (b != nullptr) {
+      const uint4 ub = b[i];
+      t = unpack_bf16x2(ub.x); v[0] += t.x; v[1] += t.y;
+      t = unpack_bf16x2(ub.y); v[2] += t.x; v[3] += t.y;
+      t = unpack_bf16x2(ub.z); v[4] += t.x; v[5] += t.y;
+      t = unpack_bf16x2(ub.w); v[6] += t.x; v[7] += t.y;
+    }
+    if (bias != nullptr) {
+      const int c0 = static_cast<int>(i % vpr) * 8;
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c0));
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + c0 + 4));
+      v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+      v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+    }
+    out[i] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+}
+
 inline unsigned stream_grid(long long work_items) {
   const long long blocks = (work_items + 255) / 256;
   const long long cap = static_cast<long long>(num_sms()) * 8;
@@ -141,6 +172,23 @@ extern "C" int afb_cast_bf16_to_f32(const afb_bf16* src, float* dst, int64_t n, 
               "afb_cast_bf16_to_f32: buffers must be 16-byte aligned");
   cast_bf16_f32_kernel<<<stream_grid((n + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
       reinterpret_cast<const __nv_bfloat16*>(src), dst, n);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_add_bias_residual(const afb_bf16* a, const afb_bf16* b, const float* bias, afb_bf16* out, int64_t rows,
+                                     int channels, afb_stream_t stream_) {
+  using namespace afb;
+  AFB_REQUIRE(a && out && rows >= 0 && channels > 0, "afb_add_bias_residual: bad argument");
+  AFB_REQUIRE(channels % 8 == 0, "afb_add_bias_residual: channels %d must be a multiple of 8", channels);
+  if (rows == 0) return 0;
+  const uintptr_t all = reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(out) |
+                        reinterpret_cast<uintptr_t>(bias);
+  AFB_REQUIRE((all & 15) == 0, "afb_add_bias_residual: buffers must be 16-byte aligned");
+  const long long nvec = static_cast<long long>(rows) * (channels / 8);
+  add_bias_residual_kernel<<<stream_grid(nvec), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), bias, reinterpret_cast<uint4*>(out), nvec, channels / 8);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -5,6 +5,8 @@
 #include "common.cuh"
 #include "../../include/adaface_b200.h"
 
+#include <atomic>
+
 namespace afb {
 void count_launch();
 namespace {
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restr
       const int g = c / cpg;
       const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
       v = (x[(static_cast<long long>(b) * C + c) * HW + t] - mean) * rstd * gamma[c] + beta[c];
-      if (act == 1) v = v / (1.0f + __expf(-v));
+      if (act == 1) v = __fdividef(v, 1.0f + __expf(-v));
     }
     tile[ty + 8 * i][tx] = v;
   }
@@ -95,8 +97,8 @@ __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restr
 // A chunk of T consecutive tokens is one contiguous T*C*2-byte span.  Thread = 8 adjacent channels (one 16-byte
 // vector) x up to kGnTpt tokens held in registers (all loads in flight at once); a block covers T tokens with
 // R = blockDim / (C/8) token rows.  Per-group reductions go through shared-memory atomics (32 groups).
-//   gn_partial_tok   chunk (mean, M2) per (b, group, chunk): two passes over the REGISTER copy, one read of x
-//   gn_finalize      exact (Chan) merge of the chunk partials -> (mean, rstd) per (b, group)
+//   gn_partial_tok   chunk (mean, M2) per (b, group, chunk): two passes over the REGISTER copy, one read of x; the
+//                    last block of each sample merges the chunk partials (exact Chan merge) -> (mean, rstd)
 //   gn_apply_tok     normalise + affine (+ SiLU) with 16-byte loads / stores
 constexpr int kGnTpt = 8;           // tokens per thread
 constexpr int kGnMaxGroups = 64;
@@ -123,9 +125,22 @@ __device__ __forceinline__ void group_accumulate(float* slots, const float (&s)[
   atomicAdd(&slots[cur], acc);
 }
 
-__global__ void __launch_bounds__(320) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial,
-                                                             int C, int HW, int cpg, int T, int nchunks) {
+// Tickets for the "last block of a sample finalises its statistics" pattern: self-resetting, one row of kGnMaxBatch
+// counters per in-flight launch slot (the host rotates over kGnTicketSlots slots, so launches that overlap on
+// different streams do not share counters unless more than kGnTicketSlots are in flight at once).
+constexpr int kGnMaxBatch = 1024;
+constexpr int kGnTicketSlots = 16;
+__device__ unsigned int g_gn_tickets[kGnTicketSlots * kGnMaxBatch];
+
+// pre_add (optional, fp32 [B, C] with row stride pre_add_ld): a per-(sample, channel) vector added to x BEFORE the
+// statistics and the normalisation - the conv bias + time-embedding add that precedes out_layers' GroupNorm in a
+// ResBlock (openaimodel.py:259-279), folded in so that no separate elementwise pass is needed.
+__global__ void __launch_bounds__(320, 2) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ pre_add,
+                                                             int pre_add_ld, float* __restrict__ partial,
+                                                             float* __restrict__ stats, int C, int HW, int cpg, int T,
+                                                             int nchunks, float eps, int ticket_slot) {
   __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
+  __shared__ unsigned int s_ticket;
   const int b = blockIdx.y, chunk = blockIdx.x;
   const int t0 = chunk * T;
   const int nt = min(T, HW - t0);
@@ -143,9 +158,21 @@ __global__ void __launch_bounds__(320) gn_partial_tok_kernel(const __nv_bfloat16
     const int t = row + i * R;
     data[i] = (t < nt) ? xp[static_cast<long long>(t) * vpr] : make_uint4(0, 0, 0, 0);
   }
+  float add[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) add[j] = 0.f;
+  int my_rows = 0;                               // token rows this thread really holds
+#pragma unroll
+  for (int i = 0; i < kGnTpt; ++i) my_rows += (row + i * R < nt) ? 1 : 0;
+  if (pre_add != nullptr) {
+    const float4* ap = reinterpret_cast<const float4*>(pre_add + static_cast<long long>(b) * pre_add_ld + c0);
+    const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+    add[0] = a0.x; add[1] = a0.y; add[2] = a0.z; add[3] = a0.w;
+    add[4] = a1.x; add[5] = a1.y; add[6] = a1.z; add[7] = a1.w;
+  }
   float s[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  for (int j = 0; j < 8; ++j) s[j] = static_cast<float>(my_rows) * add[j];
 #pragma unroll
   for (int i = 0; i < kGnTpt; ++i) {
     float v[8];
@@ -158,7 +185,7 @@ __global__ void __launch_bounds__(320) gn_partial_tok_kernel(const __nv_bfloat16
   const float inv_n = 1.0f / static_cast<float>(nt * cpg);
   float mean[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) mean[j] = g_sum[(c0 + j) / cpg] * inv_n;
+  for (int j = 0; j < 8; ++j) mean[j] = g_sum[(c0 + j) / cpg] * inv_n - add[j];   // (x + add) - mean = x - (mean - add)
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = 0.f;
 #pragma unroll
@@ -180,41 +207,46 @@ __global__ void __launch_bounds__(320) gn_partial_tok_kernel(const __nv_bfloat16
     out[0] = g_sum[g] * inv_n;
     out[1] = g_m2[g];
   }
+  // ---- the last block of sample b to get here merges the chunk partials (exact Chan merge) into (mean, rstd)
+  __threadfence();
+  __syncthreads();
+  unsigned int* ticket = &g_gn_tickets[ticket_slot * kGnMaxBatch + b];
+  if (threadIdx.x == 0) s_ticket = atomicAdd(ticket, 1u);
+  __syncthreads();
+  if (s_ticket != static_cast<unsigned int>(nchunks - 1)) return;
+  __threadfence();
+  if (threadIdx.x == 0) *ticket = 0u;            // self-reset for the next launch that uses this slot
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int g = warp; g < groups; g += nwarps) {
+    const volatile float* p = partial + static_cast<long long>(b * groups + g) * nchunks * 2;
+    float tot = 0.f, wsum = 0.f;
+    for (int c = lane; c < nchunks; c += 32) {
+      const float n = static_cast<float>(min(T, HW - c * T) * cpg);
+      wsum += n * p[2 * c];
+      tot += n;
+    }
+    tot = warp_sum(tot);
+    const float gmean = warp_sum(wsum) / tot;
+    float m2 = 0.f;
+    for (int c = lane; c < nchunks; c += 32) {
+      const float n = static_cast<float>(min(T, HW - c * T) * cpg);
+      const float d = p[2 * c] - gmean;
+      m2 += p[2 * c + 1] + n * d * d;
+    }
+    m2 = warp_sum(m2);
+    if (lane == 0) {
+      stats[2 * (b * groups + g)] = gmean;
+      stats[2 * (b * groups + g) + 1] = rsqrtf(m2 / tot + eps);
+    }
+  }
 }
 
-// exact (Chan) merge of the chunk partials; one warp per (b, group)
-__global__ void gn_finalize_kernel(const float* __restrict__ partial, float* __restrict__ stats, int n_bg, int nchunks,
-                                   int HW, int cpg, int T, float eps) {
-  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (i >= n_bg) return;
-  const float* p = partial + static_cast<long long>(i) * nchunks * 2;
-  float tot = 0.f, wsum = 0.f;
-  for (int c = lane; c < nchunks; c += 32) {
-    const float n = static_cast<float>(min(T, HW - c * T) * cpg);
-    wsum += n * p[2 * c];
-    tot += n;
-  }
-  tot = warp_sum(tot);
-  const float mean = warp_sum(wsum) / tot;
-  float m2 = 0.f;
-  for (int c = lane; c < nchunks; c += 32) {
-    const float n = static_cast<float>(min(T, HW - c * T) * cpg);
-    const float d = p[2 * c] - mean;
-    m2 += p[2 * c + 1] + n * d * d;
-  }
-  m2 = warp_sum(m2);
-  if (lane == 0) {
-    stats[2 * i] = mean;
-    stats[2 * i + 1] = rsqrtf(m2 / tot + eps);
-  }
-}
-
-__device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
+__device__ __forceinline__ float silu(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
 template <bool kSilu>
-__global__ void __launch_bounds__(320) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
+__global__ void __launch_bounds__(320, 3) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           const float* __restrict__ pre_add, int pre_add_ld,
                                                            __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int T) {
   const int b = blockIdx.y;
   const int t0 = blockIdx.x * T;
@@ -229,8 +261,9 @@ __global__ void __launch_bounds__(320) gn_apply_tok_kernel(const __nv_bfloat16* 
   for (int j = 0; j < 8; ++j) {
     const int g = (c0 + j) / cpg;
     const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
+    const float add = pre_add != nullptr ? pre_add[static_cast<long long>(b) * pre_add_ld + c0 + j] : 0.f;
     sc[j] = rstd * gamma[c0 + j];
-    of[j] = beta[c0 + j] - mean * sc[j];
+    of[j] = beta[c0 + j] + (add - mean) * sc[j];
   }
   const long long base = (static_cast<long long>(b) * HW + t0) * vpr + vec;
   const uint4* xp = reinterpret_cast<const uint4*>(x) + base;
@@ -350,7 +383,7 @@ extern "C" int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups) {
 
 extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
                                     float* stats_ws, int batch, int channels, int hw, int groups, float eps, int act,
-                                    afb_stream_t stream_) {
+                                    const float* pre_add, int pre_add_ld, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && gamma && beta && y && stats_ws, "afb_groupnorm_tokens: NULL argument");
@@ -361,6 +394,7 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
   AFB_REQUIRE(act == 0 || act == 1, "afb_groupnorm_tokens: act must be 0 (none) or 1 (SiLU)");
   __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(y);
   if (x_layout == 0) {
+    AFB_REQUIRE(pre_add == nullptr, "afb_groupnorm_tokens: pre_add is only supported for the token-major layout");
     AFB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (static_cast<long long>(cpg) * hw) % 4 == 0,
                 "afb_groupnorm_tokens: NCHW input must be 16-byte aligned with (C/groups)*HW %% 4 == 0");
     gn_stats_nchw_kernel<<<batch * groups, 512, 0, stream>>>(static_cast<const float*>(x), stats_ws, cpg * hw, eps);
@@ -377,13 +411,16 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
     float* partial = stats_ws + 2ll * batch * groups;
     const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
     dim3 grid(geo.nchunks, batch);
-    gn_partial_tok_kernel<<<grid, geo.threads, 0, stream>>>(xb, partial, channels, hw, cpg, geo.T, geo.nchunks);
+    AFB_REQUIRE(batch <= kGnMaxBatch, "afb_groupnorm_tokens: batch %d > %d", batch, kGnMaxBatch);
+    AFB_REQUIRE(pre_add == nullptr || (pre_add_ld >= channels && pre_add_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(pre_add) & 15) == 0),
+                "afb_groupnorm_tokens: pre_add must be 16-byte aligned fp32 [B, C] with a row stride that is a multiple of 4");
+    static std::atomic<unsigned int> launch_seq{0};
+    const int slot = static_cast<int>(launch_seq.fetch_add(1, std::memory_order_relaxed) % kGnTicketSlots);
+    gn_partial_tok_kernel<<<grid, geo.threads, 0, stream>>>(xb, pre_add, pre_add_ld, partial, stats_ws, channels, hw, cpg, geo.T,
+                                                           geo.nchunks, eps, slot);
     count_launch();
-    const int n_bg = batch * groups;
-    gn_finalize_kernel<<<(n_bg * 32 + 255) / 256, 256, 0, stream>>>(partial, stats_ws, n_bg, geo.nchunks, hw, cpg, geo.T, eps);
-    count_launch();
-    if (act) gn_apply_tok_kernel<true><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg, geo.T);
-    else gn_apply_tok_kernel<false><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, yb, channels, hw, cpg, geo.T);
+    if (act) gn_apply_tok_kernel<true><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T);
+    else gn_apply_tok_kernel<false><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T);
     count_launch();
   } else {
     AFB_FAIL(2, "afb_groupnorm_tokens: unknown x_layout %d", x_layout);

@@ -73,14 +73,13 @@ class AttentionalPooler(nn.Module, _PackedWeights):
         p = self.packed()
         if bg_q_emb.dim() == 1:
             bg_q_emb = bg_q_emb[None].expand(b, -1)
-        lora_q = ops.ada_pool_prep(to_k.weight.detach(), fg_q_emb.reshape(-1), bg_q_emb.reshape(b, -1),
-                                   p["lora_to_fg_q"], p["lora_to_bg_q"])                       # :186-235
+        pool_q = ops.ada_pool_prep(to_k.weight.detach(), fg_q_emb.reshape(-1), bg_q_emb.reshape(b, -1),
+                                   p["lora_to_fg_q"], p["lora_to_bg_q"], p["lora_to_k"])       # :186-235, :227
         key_mask = None
         if img_mask is not None:                                                                # :259-269
             m = F.interpolate(img_mask.float(), size=infeat_size, mode="nearest").reshape(b, -1)
             key_mask = m.bool().to(torch.uint8).contiguous()
-        fg, bg, a_fg, a_bg = ops.ada_pool(as_bf16_tokens(x), as_bf16_tokens(q), lora_q, p["lora_to_k"], key_mask,
-                                          want_attn)
+        fg, bg, a_fg, a_bg = ops.ada_pool(as_bf16_tokens(x), as_bf16_tokens(q), pool_q, key_mask, want_attn)
         out = {"fg_out": fg, "bg_out": bg}
         if want_attn:
             out["attn_fg"], out["attn_bg"] = a_fg, a_bg
@@ -199,7 +198,11 @@ class AdaEmbedding(nn.Module, _PackedWeights):
 
     def forward(self, layer_idx: int, layer_attn_components: Dict, time_emb: Tensor, layer_subj_emb_probe: Tensor,
                 layer_static_extra_emb_mean: Tensor, img_mask: Optional[Tensor] = None,
-                cached_pooler_bg_out: Optional[Tensor] = None, zs_basis_vecs: Optional[Tensor] = None):
+                cached_pooler_bg_out: Optional[Tensor] = None, zs_basis_vecs: Optional[Tensor] = None,
+                splice_into: Optional[Tensor] = None, splice_positions: Optional[Tensor] = None):
+        """Reference signature plus two optional arguments used by the U-Net wiring: `splice_into` (bf16 [B, T, 768]
+        layer context) and `splice_positions` (int32 [K]) make the head kernel write the K vectors straight into the
+        subject-token rows of the context, instead of a separate cast + index_put."""
         ca = self.layer_idx2ca_layer_idx[layer_idx]
         if self.H != 2:
             # the reference concatenates fg and bg features unconditionally (:831) into a Linear sized for one
@@ -214,6 +217,11 @@ class AdaEmbedding(nn.Module, _PackedWeights):
         infeat_fg = pooled.pop("fg_out")                                                        # :823-829
         infeat_bg = cached_pooler_bg_out if self.use_cached_bg else pooled["bg_out"]
         p = self.packed()
-        out = ops.ada_head(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"], p["basis"],
-                           None if self.bias is None else p["bias"][ca])                        # :847-893
+        bias = None if self.bias is None else p["bias"][ca]
+        if splice_into is None:
+            out = ops.ada_head(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"], p["basis"],
+                               bias)                                                            # :847-893
+        else:
+            out = ops.ada_head_splice(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"],
+                                      p["basis"], bias, splice_into, splice_positions)
         return out, pooled

@@ -86,10 +86,12 @@ def _(x, e_cond, e_uncond, noise, guidance_scale, a_t, a_prev, sigma_t, sqrt_one
 
 # ------------------------------------------------------------------------------------------- K1 / K3
 @torch.library.custom_op("adaface_b200::groupnorm_tokens", mutates_args=())
-def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: float, act: int = 0) -> Tensor:
+def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: float, act: int = 0,
+                     pre_add: Optional[Tensor] = None) -> Tensor:
     """GroupNorm over x [B,C,h,w] -> normalised tokens bf16 [B, h*w, C] (attention.py:325-327).
     fp32 NCHW-contiguous and bf16 channels-last inputs are consumed in place; anything else is rejected.
-    act = 1 fuses SiLU after the affine (the U-Net ResBlocks' GroupNorm32 -> SiLU)."""
+    act = 1 fuses SiLU after the affine (the U-Net ResBlocks' GroupNorm32 -> SiLU); pre_add (fp32 [B, C], rows may be
+    strided) is added to x before the statistics (a ResBlock's conv bias + time-embedding add)."""
     _need_cuda(x, gamma, beta)
     b, c, h, w = x.shape
     hw = h * w
@@ -102,13 +104,18 @@ def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: f
     lib = _lib.load()
     ws = torch.empty(int(lib.afb_groupnorm_ws_floats(b, hw, groups)), dtype=torch.float32, device=x.device)
     y = torch.empty((b, hw, c), dtype=torch.bfloat16, device=x.device)
+    add_ld = 0
+    if pre_add is not None:
+        if pre_add.dtype != torch.float32 or pre_add.shape != (b, c) or pre_add.stride(1) != 1:
+            raise ValueError("groupnorm_tokens: pre_add must be fp32 [B, C] with contiguous rows")
+        add_ld = pre_add.stride(0)
     _run("groupnorm_tokens", lib.afb_groupnorm_tokens, _ptr(x), layout, _ptr(gamma), _ptr(beta), _ptr(y), _ptr(ws), b, c,
-         hw, groups, eps, act, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"C{c}")
+         hw, groups, eps, act, _ptr(pre_add), add_ld, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"C{c}")
     return y
 
 
 @groupnorm_tokens.register_fake
-def _(x, gamma, beta, groups, eps, act=0):
+def _(x, gamma, beta, groups, eps, act=0, pre_add=None):
     b, c, h, w = x.shape
     return x.new_empty((b, h * w, c), dtype=torch.bfloat16)
 
@@ -242,35 +249,38 @@ def _(q, k, v, heads, scale, key_mask):
 # ------------------------------------------------------------------------------------------- K12 / K13
 @torch.library.custom_op("adaface_b200::ada_pool_prep", mutates_args=())
 def ada_pool_prep(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_to_fg_q: Tensor,
-                  lora_to_bg_q: Tensor) -> Tensor:
-    """Step-invariant part of AttentionalPooler (embedding_manager.py:186-235) -> lora_q fp32 [B, 2, C/8]."""
-    _need_cuda(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q)
+                  lora_to_bg_q: Tensor, lora_to_k: Tensor) -> Tensor:
+    """Step-invariant part of AttentionalPooler (embedding_manager.py:186-235) folded through lora_to_k (:227):
+    -> pooling queries pool_q fp32 [B, 2, C]."""
+    _need_cuda(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k)
     c, ctx_dim = to_k_weight.shape
     b = bg_q_emb.shape[0]
     f = lambda t: t.to(torch.float32).contiguous()
-    lora_q = torch.empty((b, 2, c // 8), dtype=torch.float32, device=to_k_weight.device)
+    pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=to_k_weight.device)
     lib = _lib.load()
     ws = torch.empty(int(lib.afb_ada_pool_prep_ws_floats(b, c)), dtype=torch.float32, device=to_k_weight.device)
     _run("ada_pool_prep", lib.afb_ada_pool_prep, _ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)),
-         _ptr(f(bg_q_emb)), _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(lora_q), _ptr(ws), b, c, _stream(),
-         nbytes=4.0 * c * ctx_dim)
-    return lora_q
+         _ptr(f(bg_q_emb)), _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(f(lora_to_k)), _ptr(pool_q), _ptr(ws), b, c,
+         _stream(), nbytes=4.0 * c * ctx_dim)
+    return pool_q
 
 
 @ada_pool_prep.register_fake
-def _(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q):
-    return to_k_weight.new_empty((bg_q_emb.shape[0], 2, to_k_weight.shape[0] // 8), dtype=torch.float32)
+def _(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k):
+    return to_k_weight.new_empty((bg_q_emb.shape[0], 2, to_k_weight.shape[0]), dtype=torch.float32)
 
 
 @torch.library.custom_op("adaface_b200::ada_pool", mutates_args=())
-def ada_pool(x: Tensor, q: Tensor, lora_q: Tensor, lora_to_k: Tensor, key_mask: Optional[Tensor],
+def ada_pool(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor],
              want_attn: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """AttentionalPooler main pass (embedding_manager.py:146-321): x, q bf16 [B,N,C] -> fg_out, bg_out fp32 [B,C]
     and, when want_attn, attn_fg/attn_bg fp32 [B*8, 1, N] (empty tensors otherwise)."""
-    _need_cuda(x, q, lora_q, lora_to_k, key_mask)
+    _need_cuda(x, q, pool_q, key_mask)
     if x.dtype != torch.bfloat16 or q.dtype != torch.bfloat16 or not x.is_contiguous() or not q.is_contiguous():
         raise ValueError("ada_pool: contiguous bf16 x and q expected")
     b, n, c = x.shape
+    if pool_q.shape != (b, 2, c) or pool_q.dtype != torch.float32:
+        raise ValueError("ada_pool: pool_q must be fp32 [B, 2, C] (from ada_pool_prep)")
     lib = _lib.load()
     dev = x.device
     ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
@@ -280,26 +290,22 @@ def ada_pool(x: Tensor, q: Tensor, lora_q: Tensor, lora_to_k: Tensor, key_mask: 
     a_bg = torch.empty((b * 8, 1, n) if want_attn else (0,), dtype=torch.float32, device=dev)
     if key_mask is not None:
         key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
-    wk = lora_to_k.to(torch.float32).contiguous()
-    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(lora_q.contiguous()), _ptr(wk), _ptr(key_mask), _ptr(fg),
+    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q.contiguous()), _ptr(key_mask), _ptr(fg),
          _ptr(bg), _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c, _stream(),
          nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     return fg, bg, a_fg, a_bg
 
 
 @ada_pool.register_fake
-def _(x, q, lora_q, lora_to_k, key_mask, want_attn):
+def _(x, q, pool_q, key_mask, want_attn):
     b, n, c = x.shape
     shape = (b * 8, 1, n) if want_attn else (0,)
     f = lambda s: x.new_empty(s, dtype=torch.float32)
     return f((b, c)), f((b, c)), f(shape), f(shape)
 
 
-@torch.library.custom_op("adaface_b200::ada_head", mutates_args=())
-def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor,
-             basis: Tensor, bias: Optional[Tensor]) -> Tensor:
-    """AdaEmbedding head (embedding_manager.py:847-893): -> out fp32 [B, K, 768]."""
-    _need_cuda(infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias)
+def _ada_head_impl(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out, token_pos):
+    _need_cuda(infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias, ctx_out, token_pos)
     b, c = infeat_fg.shape
     k, r, d = basis.shape
     f = lambda t: None if t is None else t.to(torch.float32).contiguous()
@@ -307,16 +313,66 @@ def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, co
         f, (infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias))
     if coeff_w.shape != (k * r, 2 * c + td):
         raise ValueError(f"ada_head: coefficient map {tuple(coeff_w.shape)} does not match ({k * r}, {2 * c + td})")
+    stride = 0
+    if ctx_out is not None:
+        if token_pos is None or token_pos.dtype != torch.int32 or token_pos.numel() != k:
+            raise ValueError("ada_head: token_pos must be int32 [K] when ctx_out is given")
+        if ctx_out.dtype != torch.bfloat16 or ctx_out.dim() != 3 or ctx_out.shape[2] != d or ctx_out.stride(2) != 1 \
+                or ctx_out.stride(1) != d or ctx_out.shape[0] < b:
+            raise ValueError("ada_head: ctx_out must be bf16 [B, T, D] with contiguous rows")
+        stride = ctx_out.stride(0)
     out = torch.empty((b, k, d), dtype=torch.float32, device=infeat_fg.device)
     _run("ada_head", _lib.load().afb_ada_head, _ptr(infeat_fg), _ptr(infeat_bg), _ptr(time_emb), time_emb.stride(0),
-         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), b, c, td, k, r, d, _stream(),
-         nbytes=4.0 * (coeff_w.numel() + basis.numel()))
+         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), _ptr(ctx_out), _ptr(token_pos), stride, b, c, td,
+         k, r, d, _stream(), nbytes=4.0 * (coeff_w.numel() + basis.numel()))
     return out
+
+
+@torch.library.custom_op("adaface_b200::ada_head", mutates_args=())
+def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor,
+             basis: Tensor, bias: Optional[Tensor]) -> Tensor:
+    """AdaEmbedding head (embedding_manager.py:847-893): -> out fp32 [B, K, 768]."""
+    return _ada_head_impl(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, None, None)
 
 
 @ada_head.register_fake
 def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias):
     return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[0], basis.shape[2]), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::ada_head_splice", mutates_args=("ctx_out",))
+def ada_head_splice(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor,
+                    basis: Tensor, bias: Optional[Tensor], ctx_out: Tensor, token_pos: Tensor) -> Tensor:
+    """ada_head that also writes the K vectors, as bf16, into rows token_pos (int32 [K]) of ctx_out (bf16 [B', T, 768],
+    B' >= B) - the splice of the subject-token rows into the layer's context."""
+    return _ada_head_impl(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out, token_pos)
+
+
+@ada_head_splice.register_fake
+def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out, token_pos):
+    return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[0], basis.shape[2]), dtype=torch.float32)
+
+
+# ------------------------------------------------------------------------------------------- elementwise
+@torch.library.custom_op("adaface_b200::add_bias_residual", mutates_args=())
+def add_bias_residual(a: Tensor, b: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:
+    """a + b + bias over bf16 token-major [..., C] tensors (b, bias optional; bias fp32 [C])."""
+    _need_cuda(a, b, bias)
+    if a.dtype != torch.bfloat16 or not a.is_contiguous() or (b is not None and (b.dtype != a.dtype or b.shape != a.shape
+                                                                                 or not b.is_contiguous())):
+        raise ValueError("add_bias_residual: contiguous bf16 tensors of one shape expected")
+    c = a.shape[-1]
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != c):
+        raise ValueError("add_bias_residual: bias must be fp32 [C]")
+    out = torch.empty_like(a)
+    _run("add_bias_residual", _lib.load().afb_add_bias_residual, _ptr(a), _ptr(b), _ptr(bias), _ptr(out), a.numel() // c, c,
+         _stream(), nbytes=2.0 * a.numel() * (2 + (b is not None)))
+    return out
+
+
+@add_bias_residual.register_fake
+def _(a, b, bias):
+    return torch.empty_like(a)
 
 
 # ------------------------------------------------------------------------------------------- casts

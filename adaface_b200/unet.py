@@ -52,12 +52,27 @@ class GroupNorm32(nn.GroupNorm):
         raise RuntimeError("GroupNorm32 is applied through gn_silu() together with the SiLU that follows it")
 
 
-def gn_silu(gn: nn.GroupNorm, x: Tensor) -> Tensor:
-    """x bf16 channels-last [B, C, H, W] -> SiLU(GroupNorm(x)), same format."""
+def gn_silu(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Tensor:
+    """x bf16 channels-last [B, C, H, W] -> SiLU(GroupNorm(x + pre_add[:, :, None, None])), same format."""
     b, c, h, w = x.shape
     x = x.contiguous(memory_format=CL)
-    y = ops.groupnorm_tokens(x, gn.weight.detach(), gn.bias.detach(), gn.num_groups, gn.eps, 1)
+    y = ops.groupnorm_tokens(x, gn.weight.detach(), gn.bias.detach(), gn.num_groups, gn.eps, 1, pre_add)
     return y.view(b, h, w, c).permute(0, 3, 1, 2)
+
+
+def add_cl(a: Tensor, b: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:
+    """a + b + bias[None, :, None, None] on bf16 channels-last [B, C, H, W] tensors, one vectorised pass."""
+    a = a.contiguous(memory_format=CL)
+    bt = None if b is None else b.contiguous(memory_format=CL).permute(0, 2, 3, 1)
+    return ops.add_bias_residual(a.permute(0, 2, 3, 1), bt, bias).permute(0, 3, 1, 2)
+
+
+class EmbBundle:
+    """The time embedding plus every ResBlock's `emb_layers(emb) + conv1.bias` vector, computed by ONE batched Linear
+    at the top of UNetModel.forward instead of 22 small ones (the time embedding is the same for all blocks)."""
+
+    def __init__(self, emb: Tensor, per_block: Dict[int, Tensor]):
+        self.emb, self.per_block = emb, per_block
 
 
 class _Bf16Conv(nn.Conv2d):
@@ -74,9 +89,16 @@ class _Bf16Conv(nn.Conv2d):
             self.__dict__["_bf16_cache"] = c
         return c[1], c[2]
 
-    def forward(self, x):
+    def forward(self, x, with_bias: bool = True):
         w, b = self._w()
-        return F.conv2d(x, w, b, self.stride, self.padding)
+        return F.conv2d(x, w, b if with_bias else None, self.stride, self.padding)
+
+    def conv_add(self, x):
+        """conv(x) + bias with the bias added by one vectorised pass (torch adds a cuDNN conv's bias with a slow
+        broadcasting elementwise kernel)."""
+        if self.bias is None:
+            return self.forward(x, False)
+        return add_cl(self.forward(x, False), None, self.bias.detach())
 
 
 class Upsample(nn.Module):
@@ -88,7 +110,7 @@ class Upsample(nn.Module):
 
     def forward(self, x):
         x = F.interpolate(x, scale_factor=2, mode="nearest")
-        return self.conv(x) if self.use_conv else x
+        return self.conv.conv_add(x) if self.use_conv else x
 
 
 class Downsample(nn.Module):
@@ -99,7 +121,7 @@ class Downsample(nn.Module):
             else nn.AvgPool2d(kernel_size=2, stride=2)
 
     def forward(self, x):
-        return self.op(x)
+        return self.op.conv_add(x) if self.use_conv else self.op(x)
 
 
 class ResBlock(TimestepBlock):
@@ -115,14 +137,30 @@ class ResBlock(TimestepBlock):
                                         _Bf16Conv(oc, oc, 3, padding=1))
         self.skip_connection = nn.Identity() if oc == channels else _Bf16Conv(channels, oc, 1)
 
+    def out_bias(self) -> Tensor:
+        """conv2.bias (+ skip conv bias): added together with the skip tensor in one pass."""
+        ps = [self.out_layers[3].bias] + ([] if isinstance(self.skip_connection, nn.Identity) else [self.skip_connection.bias])
+        key = tuple((p.data_ptr(), p._version) for p in ps)
+        c = self.__dict__.get("_out_bias")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                c = (key, sum(p.detach().float() for p in ps).contiguous())
+            self.__dict__["_out_bias"] = c
+        return c[1]
+
     def forward(self, x, emb):
-        h = self.in_layers[2](gn_silu(self.in_layers[0], x))
-        e = self.emb_layers(emb).to(h.dtype)
-        h = h + e[:, :, None, None]
+        """openaimodel.py:259-279.  The conv1 bias and the time-embedding add are folded into out_layers' GroupNorm
+        (pre_add), conv2's bias and the skip add are one vectorised pass."""
         if self.training and self.out_layers[2].p > 0:
             raise NotImplementedError("adaface_b200.ResBlock: dropout > 0 in training mode is not supported")
-        h = self.out_layers[3](gn_silu(self.out_layers[0], h))
-        return self.skip_connection(x) + h
+        h = self.in_layers[2](gn_silu(self.in_layers[0], x), False)
+        if isinstance(emb, EmbBundle):
+            pre = emb.per_block[id(self)]
+        else:
+            pre = self.emb_layers(emb).float() + self.in_layers[2].bias.detach().float()
+        h = self.out_layers[3](gn_silu(self.out_layers[0], h, pre), False)
+        skip = x if isinstance(self.skip_connection, nn.Identity) else self.skip_connection(x, False)
+        return add_cl(h, skip, self.out_bias())
 
 
 class TimestepEmbedSequential(nn.Sequential, TimestepBlock):
@@ -170,7 +208,7 @@ class AdaPromptContext:
     def positions(self, i: int, device) -> Tensor:
         key = (i, str(device))
         if key not in self._pos:
-            self._pos[key] = torch.tensor(self.subjects[i].token_positions, dtype=torch.long, device=device)
+            self._pos[key] = torch.tensor(self.subjects[i].token_positions, dtype=torch.int32, device=device)
         return self._pos[key]
 
     def apply(self, layer_idx: int, comps: Dict, layer_ctx: Tensor, time_emb: Tensor) -> Tensor:
@@ -182,10 +220,10 @@ class AdaPromptContext:
             sub = {"x": comps["x"][:n], "q": comps["q"][:n], "to_k": comps["to_k"], "infeat_size": comps["infeat_size"]}
             cached = bg_cache.get(s.cached_bg_from) if s.cached_bg_from is not None else None
             mask = None if self.img_mask is None else self.img_mask[:n]
-            vecs, pooled = s.embedder(layer_idx, sub, time_emb[:n], s.layer_probes[ca], s.layer_extra_means[ca][:n],
-                                      img_mask=mask, cached_pooler_bg_out=cached)
+            _, pooled = s.embedder(layer_idx, sub, time_emb[:n], s.layer_probes[ca], s.layer_extra_means[ca][:n],
+                                   img_mask=mask, cached_pooler_bg_out=cached, splice_into=layer_ctx,
+                                   splice_positions=self.positions(i, layer_ctx.device))
             bg_cache[i] = pooled["bg_out"]
-            layer_ctx[:n, self.positions(i, layer_ctx.device)] = vecs.to(layer_ctx.dtype)
         return layer_ctx
 
 
@@ -227,6 +265,7 @@ class UNetModel(nn.Module):
             return SpatialTransformer(ch, heads, dim_head, depth=transformer_depth, context_dim=context_dim)
 
         self.input_blocks = nn.ModuleList([TimestepEmbedSequential(_Bf16Conv(in_channels, mc, 3, padding=1))])
+        self.__dict__["_emb_pack"] = None
         chans, ch, ds = [mc], mc, 1
         for level, mult in enumerate(self.channel_mult):
             for _ in range(num_res_blocks):
@@ -275,6 +314,28 @@ class UNetModel(nn.Module):
                 attn2.__dict__[name] = v[ca] if kind == "layerwise" else v
         return old
 
+    def emb_bundle(self, emb: Tensor) -> EmbBundle:
+        """One Linear for all ResBlocks: rows = concatenated emb_layers[1] weights, bias = emb_layers[1].bias +
+        in_layers[2].bias (the conv1 bias rides along into the GroupNorm pre-add)."""
+        blocks = [m for m in self.modules() if isinstance(m, ResBlock)]
+        ps = [p for rb in blocks for p in (rb.emb_layers[1].weight, rb.emb_layers[1].bias, rb.in_layers[2].bias)]
+        key = tuple((p.data_ptr(), p._version) for p in ps)
+        pack = self.__dict__.get("_emb_pack")
+        if pack is None or pack[0] != key:
+            with torch.no_grad():
+                w = torch.cat([rb.emb_layers[1].weight.detach().float() for rb in blocks], dim=0).contiguous()
+                b = torch.cat([rb.emb_layers[1].bias.detach().float() + rb.in_layers[2].bias.detach().float()
+                               for rb in blocks]).contiguous()
+            offs, o = [], 0
+            for rb in blocks:
+                offs.append((id(rb), o, rb.out_channels))
+                o += rb.out_channels
+            pack = (key, w, b, offs)
+            self.__dict__["_emb_pack"] = pack
+        _, w, b, offs = pack
+        e_all = F.linear(F.silu(emb), w, b)
+        return EmbBundle(emb, {i: e_all[:, o:o + n] for i, o, n in offs})
+
     def forward(self, x: Tensor, timesteps: Optional[Tensor] = None, context: Optional[Tensor] = None, y=None,
                 context_in=None, extra_info: Optional[Dict] = None, **kwargs) -> Tensor:
         """x [B, 4, H, W]; context [16*B, T, 768] instance-major / layer-minor (embedding_manager.py:1345-1349) when
@@ -315,18 +376,20 @@ class UNetModel(nn.Module):
             with_ada.wants_layer_attn_components = True
             return with_ada
 
+        bundle = self.emb_bundle(emb)
         hs = []
-        h = x.to(torch.bfloat16).contiguous(memory_format=CL)
-        layer_idx = 0
-        for module in self.input_blocks:
-            h = module(h, emb, layer_context(layer_idx), mask=img_mask)
+        h = self.input_blocks[0][0](x.to(torch.bfloat16).contiguous(memory_format=CL))
+        hs.append(h)
+        layer_idx = 1
+        for module in list(self.input_blocks)[1:]:
+            h = module(h, bundle, layer_context(layer_idx), mask=img_mask)
             hs.append(h)
             layer_idx += 1
-        h = self.middle_block(h, emb, layer_context(layer_idx), mask=img_mask)
+        h = self.middle_block(h, bundle, layer_context(layer_idx), mask=img_mask)
         layer_idx += 1
         for module in self.output_blocks:
             h = torch.cat([h, hs.pop()], dim=1).contiguous(memory_format=CL)
-            h = module(h, emb, layer_context(layer_idx), mask=img_mask)
+            h = module(h, bundle, layer_context(layer_idx), mask=img_mask)
             layer_idx += 1
         return self.out[2](gn_silu(self.out[0], h)).to(x.dtype).contiguous()
 

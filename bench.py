@@ -253,6 +253,16 @@ def run_ours(args):
         launches_per_step = _lib.launch_count() - n0
         model.use_cuda_graph = not args.no_graph
 
+        if args.profile_step:
+            # for `ncu --profile-from-start off`: exactly one eager (non-graph) step between cudaProfilerStart/Stop
+            model.use_cuda_graph = False
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
+            ddim_step(x_d, 0)
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
+            model.use_cuda_graph = not args.no_graph
+
         # ---- timed region: device-resident inputs
         clocks = ClockSampler(local)
         barrier()
@@ -373,6 +383,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="bracket one eager step with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     ap.add_argument("--dump-kernels", default=None, help="write the per-shape kernel breakdown of one step as CSV")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -46,11 +46,18 @@ int afb_cfg_ddim_step(const float* x, const float* e_cond, const float* e_uncond
  * of :327).  x_layout 0: x is fp32 [B,C,HW] (NCHW contiguous); 1: x is bf16 [B,HW,C] (channels-last).
  * stats_ws: fp32 workspace of afb_groupnorm_ws_floats(B, HW, groups) floats.  y: bf16 [B*HW, C].
  * act 0: none; 1: SiLU fused after the affine (the GroupNorm32 -> SiLU pairs of the U-Net's ResBlocks,
- * openaimodel.py:201-205,233-236 - the first "next" row after the transformer path). */
+ * openaimodel.py:201-205,233-236 - the first "next" row after the transformer path).
+ * pre_add: NULL, or fp32 [B, C] with row stride pre_add_ld (x_layout 1 only): a per-(sample, channel) vector added
+ * to x before the statistics and the normalisation (a ResBlock's conv bias + time-embedding add, :259-279). */
 int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups);
 int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
                          float* stats_ws, int batch, int channels, int hw, int groups, float eps, int act,
-                         afb_stream_t stream);
+                         const float* pre_add, int pre_add_ld, afb_stream_t stream);
+
+/* ---- out = a + b + bias (elementwise, bf16 [rows, C] token-major; b and bias optional).  The residual / bias adds
+ * around the ResBlock convolutions (openaimodel.py:279) as one vectorised pass instead of two broadcast adds. */
+int afb_add_bias_residual(const afb_bf16* a, const afb_bf16* b, const float* bias, afb_bf16* out, int64_t rows,
+                          int channels, afb_stream_t stream);
 
 /* ---- K3: LayerNorm over the last dim, bf16 in / bf16 out, fp32 statistics.  attention.py:267-269,277-283.
  * gamma/beta may be NULL (no affine; embedding_manager.py:111-113). */
@@ -105,26 +112,31 @@ int afb_attention_fwd(const afb_attn_args* args, afb_stream_t stream);
 /* ---- K12: AttentionalPooler.forward, eval mode.  Replaces embedding_manager.py:146-321.
  * afb_ada_pool_prep (step-invariant, :186-235): fg_q/bg_q = to_k(query embedding) with the layer's attn2.to_k
  *   weight fp32 [C, ctx_dim]; fg_q_emb fp32 [ctx_dim] (shared by the batch), bg_q_emb fp32 [B, ctx_dim];
- *   LayerNorm; grouped 1x1 convs lora_to_fg_q / lora_to_bg_q (fp32 [C/8, C/8], 8 groups) -> lora_q fp32 [B,2,C/8];
- *   prep_ws: fp32 workspace of afb_ada_pool_prep_ws_floats(B, C) floats.
- * afb_ada_pool: x, q bf16 [B, N, C] (block input x1 and attn2.to_q(norm2(x1))); lora_to_k fp32 [C/8, C/8];
- *   key_mask NULL or uint8 [B, N] (0 = masked).  Outputs fp32: fg_out, bg_out [B, C]; attn_fg, attn_bg
- *   [B, 8, N] (both NULL to skip).  ws: fp32 workspace of afb_ada_pool_ws_floats(B, N, C) floats. */
+ *   LayerNorm; grouped 1x1 convs lora_to_fg_q / lora_to_bg_q (fp32 [C/8, C/8], 8 groups); the result is folded
+ *   through lora_to_k (fp32 [C/8, C/8]; the grouped conv applied to every token at :227 is linear) into the
+ *   pooling queries pool_q fp32 [B, 2, C].  prep_ws: fp32 workspace of afb_ada_pool_prep_ws_floats(B, C) floats.
+ * afb_ada_pool: x, q bf16 [B, N, C] (block input x1 and attn2.to_q(norm2(x1))); key_mask NULL or uint8 [B, N]
+ *   (0 = masked).  Outputs fp32: fg_out, bg_out [B, C]; attn_fg, attn_bg [B, 8, N] (both NULL to skip).
+ *   ws: fp32 workspace of afb_ada_pool_ws_floats(B, N, C) floats. */
 int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels);
 int64_t afb_ada_pool_prep_ws_floats(int batch, int channels);
 int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
-                      const float* lora_to_fg_q, const float* lora_to_bg_q, float* lora_q, float* prep_ws, int batch,
-                      int channels, afb_stream_t stream);
-int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* lora_q, const float* lora_to_k,
-                 const uint8_t* key_mask, float* fg_out, float* bg_out, float* attn_fg, float* attn_bg, float* ws,
-                 int batch, int n_tokens, int channels, afb_stream_t stream);
+                      const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k, float* pool_q,
+                      float* prep_ws, int batch, int channels, afb_stream_t stream);
+int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, float* fg_out,
+                 float* bg_out, float* attn_fg, float* attn_bg, float* ws, int batch, int n_tokens, int channels,
+                 afb_stream_t stream);
 
 /* ---- K13: AdaEmbedding head.  Replaces embedding_manager.py:847-893.
  * infeat_fg/bg fp32 [B, C]; time_emb fp32 [B, time_ld] (first TD = C/4 used); coeff_w fp32 [K*r, 2C+TD],
- * coeff_b [K*r]; basis fp32 [K, r, D]; bias fp32 [K, D] or NULL; out fp32 [B, K, D]. */
+ * coeff_b [K*r]; basis fp32 [K, r, D]; bias fp32 [K, D] or NULL; out fp32 [B, K, D].
+ * Optional splice of the subject rows into the layer's context: ctx_out bf16 with sample stride
+ * ctx_sample_stride elements and rows of D elements, token_pos int32 [K] (device) - vector k of sample b is also
+ * written, as bf16, to ctx_out[b * ctx_sample_stride + token_pos[k] * D ...].  Both NULL to skip. */
 int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
                  const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
-                 int batch, int channels, int td, int num_vectors, int r, int out_dim, afb_stream_t stream);
+                 afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int batch, int channels, int td,
+                 int num_vectors, int r, int out_dim, afb_stream_t stream);
 
 /* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */
 int afb_cast_f32_to_bf16(const float* src, afb_bf16* dst, int64_t n, afb_stream_t stream);

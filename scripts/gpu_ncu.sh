@@ -1,11 +1,15 @@
 #!/bin/bash
-# ncu evidence: (1) launch list with device time of every kernel of two eager steps, (2) --set full of the top kernels.
-# The same command runs first without ncu (B200_PROFILING.md).  Outputs in gpurun_out/.
+# ncu evidence: (1) launch list with the device time of every kernel of ONE eager DDIM step (cudaProfilerStart/Stop
+# bracket), (2) optionally --set full of selected kernels of that step.  The same command runs first without ncu
+# (B200_PROFILING.md).  Usage: gpu_ncu.sh [tag] [kernel-regex for the full capture] [count]
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --no-graph --no-cpu-baseline"
-$CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
-ncu --metrics gpu__time_duration.sum --clock-control none -s 3500 -c 1300 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
-echo "launch list rc=$?"; tail -2 gpurun_out/ncu1.log
-$CMD > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"attention_fwd_kernel|gemm_bf16_tma_kernel|gn_partial_tok|gn_apply_tok|ada_pool_main|layernorm_bf16" -s 600 -c 40 -o gpurun_out/prof_r01 $CMD > gpurun_out/ncu2.log 2>&1
-echo "full rc=$?"; tail -2 gpurun_out/ncu2.log; ls -la gpurun_out/
+TAG=${1:-r01}
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --profile-step"
+$CMD > gpurun_out/plain_${TAG}.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain_${TAG}.log; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches_${TAG}.csv $CMD > gpurun_out/ncu1_${TAG}.log 2>&1
+echo "launch list rc=$?"
+if [ -n "$2" ]; then
+  ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"$2" -c ${3:-30} -o gpurun_out/prof_${TAG} $CMD > gpurun_out/ncu2_${TAG}.log 2>&1
+  echo "full rc=$?"; tail -2 gpurun_out/ncu2_${TAG}.log
+fi
+ls -la gpurun_out/ | tail -8

@@ -61,6 +61,27 @@ def test_groupnorm_tokens_both_layouts(ops, cuda_device, c, hw):
                   silu(port.group_norm(xb.float().cpu(), g, be, 32, 1e-5)).reshape(b, c, hw * hw).transpose(1, 2)) < 4e-3
 
 
+def test_groupnorm_pre_add_and_add_bias_residual(ops, cuda_device):
+    """The ResBlock folds: GroupNorm(x + pre_add[b, c]) with SiLU, and a + b + bias in one pass."""
+    b, c, hw = 3, 640, 12
+    d = cuda_device
+    x = (_r("gnp.x", (b, c, hw, hw)) * 1.5 + 0.3).to(torch.bfloat16)
+    g, be = 1 + 0.1 * _r("gnp.g", (c,)), 0.1 * _r("gnp.b", (c,))
+    big = _r("gnp.add", (b, 3 * c)).to(d)
+    add = big[:, c:2 * c]                                        # strided rows
+    xb = x.to(d).contiguous(memory_format=torch.channels_last)
+    ref = torch.nn.functional.silu(port.group_norm(x.float() + add.cpu()[:, :, None, None], g, be, 32, 1e-5))
+    y = ops.groupnorm_tokens(xb, g.to(d), be.to(d), 32, 1e-5, 1, add)
+    assert rel_l2(y.float(), ref.reshape(b, c, hw * hw).transpose(1, 2)) < 4e-3
+    a2 = _r("abr.a", (b, hw * hw, c)).to(torch.bfloat16)
+    b2 = _r("abr.b", (b, hw * hw, c)).to(torch.bfloat16)
+    bias = _r("abr.bias", (c,))
+    out = ops.add_bias_residual(a2.to(d), b2.to(d), bias.to(d))
+    assert rel_l2(out.float(), a2.float() + b2.float() + bias) < 3e-3
+    out = ops.add_bias_residual(a2.to(d), None, None)
+    assert torch.equal(out.cpu(), a2)
+
+
 @pytest.mark.parametrize("c", [320, 640, 1280, 2880])
 def test_layernorm(ops, cuda_device, c):
     rows = 77
@@ -197,9 +218,10 @@ def test_ada_pool_and_head(ops, cuda_device, ca_idx, n):
     ref_out, ref_pool = port.ada_embedding(sd, ca_idx, x.float(), q.float(), to_k, time_emb, probe, extra, K, r)
     d = cuda_device
     g = lambda key: sd[key].to(d)
-    lora_q = ops.ada_pool_prep(to_k.to(d), probe.to(d), extra.to(d), g(f"poolers.{ca_idx}.lora_to_fg_q.weight").squeeze(-1),
-                               g(f"poolers.{ca_idx}.lora_to_bg_q.weight").squeeze(-1))
-    fg, bg, a_fg, a_bg = ops.ada_pool(x.to(d), q.to(d), lora_q, g(f"poolers.{ca_idx}.lora_to_k.weight").squeeze(-1), None, True)
+    pool_q = ops.ada_pool_prep(to_k.to(d), probe.to(d), extra.to(d), g(f"poolers.{ca_idx}.lora_to_fg_q.weight").squeeze(-1),
+                               g(f"poolers.{ca_idx}.lora_to_bg_q.weight").squeeze(-1),
+                               g(f"poolers.{ca_idx}.lora_to_k.weight").squeeze(-1))
+    fg, bg, a_fg, a_bg = ops.ada_pool(x.to(d), q.to(d), pool_q, None, True)
     assert rel_l2(fg, ref_pool["fg_out"]) < 2e-3
     assert rel_l2(bg, ref_pool["bg_out"]) < 2e-3
     assert rel_l2(a_fg, ref_pool["attn_fg"]) < 2e-3
@@ -208,6 +230,14 @@ def test_ada_pool_and_head(ops, cuda_device, ca_idx, n):
     out = ops.ada_head(fg, bg, time_emb.to(d), int(0.25 * c), g(f"layer_coeff_maps.{ca_idx}.weight"),
                        g(f"layer_coeff_maps.{ca_idx}.bias"), basis, sd["bias"][ca_idx].to(d))
     assert rel_l2(out, ref_out) < 5e-3
+    # splice: the head kernel writes the K vectors as bf16 into the given rows of a [B, 77, 768] context
+    ctx = torch.zeros((b + 1, 77, 768), dtype=torch.bfloat16, device=d)
+    pos = torch.arange(5, 5 + K, dtype=torch.int32, device=d)
+    out2 = ops.ada_head_splice(fg, bg, time_emb.to(d), int(0.25 * c), g(f"layer_coeff_maps.{ca_idx}.weight"),
+                               g(f"layer_coeff_maps.{ca_idx}.bias"), basis, sd["bias"][ca_idx].to(d), ctx, pos)
+    assert torch.equal(out2, out)
+    assert torch.equal(ctx[:b, 5:5 + K], out.to(torch.bfloat16))
+    assert float(ctx[:b, :5].abs().max()) == 0 and float(ctx[b].abs().max()) == 0 and float(ctx[:b, 5 + K:].abs().max()) == 0
 
 
 def test_casts_round_trip(ops, cuda_device):
