@@ -1,16 +1,21 @@
 // Fused attention forward for sm_100a:  O = softmax(Q K^T * scale [+ key mask]) V, online softmax.
 //
-// One CTA per (128-query tile, head, sample); 192 threads:
-//   warp 0 (one lane)  TMA producer: Q once, then K/V tiles of kBlockKV keys into a kStages ring
+// One CTA per (kQTiles x 128 query rows, head, sample); the query tiles share every K/V tile.  One CTA per SM
+// (it owns all 512 TMEM columns); 64 + kQTiles*128 threads:
+//   warp 0 (one lane)  TMA producer: Q tiles once, then K and V tiles of 64 keys in two separate rings
 //                      (64-column boxes, SWIZZLE_128B; the head is a column slice of the [B, N, ld] buffer)
-//   warp 1 (one lane)  tcgen05.mma issuer: S = Q K^T (128 x kBlockKV, fp32 in TMEM), then O += P V
-//                      (128 x d, fp32 in TMEM; V is the MN-major B operand straight from its [key][d] layout)
-//   warps 2..5         softmax: one query row per thread. tcgen05.ld S -> registers, scale/mask, running max
-//                      with lazy rescaling of O in TMEM (only when the max grows by > 2^8), exp2, row sum,
-//                      P -> bf16 -> shared memory in the canonical K-major 128B-swizzled layout; final
-//                      O / l -> bf16 -> global.
-// Two CTAs are resident per SM for head_dim 40/80 (112 KB smem, 256 TMEM columns each), so one CTA's
-// softmax overlaps the other's MMAs.
+//   warp 1 (one lane)  tcgen05.mma issuer, event driven: S_t = Q_t K_j^T (128 x 64 fp32 in TMEM) is issued one KV
+//                      tile AHEAD of the softmax (the S columns are free as soon as the scores sit in registers),
+//                      O_t += P_t V_j as soon as P_t is published (V is the MN-major B operand straight from its
+//                      [key][d] layout); whichever tile is ready first goes first
+//   warps 2 + 4t + q   softmax of query tile t, TMEM lane quarter q, one query row per thread: tcgen05.ld S ->
+//                      registers, running max with lazy rescaling of O in TMEM (only when the max grows by > 2^8),
+//                      exp2, row sum, P -> bf16 -> shared memory (canonical K-major 128B-swizzled);
+//                      final O / l -> bf16 -> global.
+// Head dim 40 is bound by the MUFU unit (one ex2 per 80 tensor FLOPs), not by the tensor cores, so the kernel is
+// organised around keeping MUFU fed: kQTiles = 4 puts four independent softmax warps on every SM sub-partition,
+// so that while some wait for scores, take the row max or publish P, others are in their exponential phase.  The
+// exponential phase is FFMA2 (scale and max folded) -> MUFU.EX2 -> FADD2 -> F2FP, the row max FMNMX3 on raw scores.
 //
 // Replaces attention.py:198-242 (einsum QK^T, masked_fill, softmax, einsum PV, head merge) without ever
 // materialising the [8B, N, N] score tensor.
@@ -21,8 +26,8 @@ namespace afb {
 void count_launch();
 namespace {
 
-constexpr int kBlockQ = 128;
-constexpr int kAttnThreads = 192;
+constexpr int kBlockQ = 128;                // rows of one query tile (= TMEM lanes)
+constexpr int kBlockKV = 64;                // keys per tile (= one 128-byte swizzle atom of P)
 constexpr float kMaskedScore = -1.0e30f;   // finite: a fully masked row degrades to a uniform average,
                                            // like masked_fill(-finfo.max) + softmax in the reference
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
@@ -33,73 +38,91 @@ struct AttnDev {
   int q_len, kv_len, heads;
   long long ldo;
   float scale_log2;
+#ifdef AFB_ATTN_PROFILE
+  long long* prof;          // [prof_blocks][16 softmax warps][8 phases] clock64 sums (tools/attn_probe.cu)
+  int prof_blocks;
+#endif
 };
+
+#ifdef AFB_ATTN_PROFILE
+#define AFB_PROF(idx)                   \
+  do {                                  \
+    const long long _now = clock64();   \
+    prof_acc[idx] += _now - prof_prev;  \
+    prof_prev = _now;                   \
+  } while (0)
+#else
+#define AFB_PROF(idx) do { } while (0)
+#endif
 
 template <int D>
 struct AttnCfg {
+  static constexpr int kQTiles = (D <= 40) ? 4 : 2;            // query tiles (= softmax warps per sub-partition)
+  static constexpr int kThreads = 64 + kQTiles * 128;
   static constexpr int kAtoms = (D + 63) / 64;                 // 64-column (128-byte) swizzle atoms per row
-  static constexpr int kBlockKV = (D <= 40) ? 128 : 64;
-  static constexpr int kStages = 2;
-  static constexpr int kDPad = (D + 15) / 16 * 16;             // UMMA N / K granularity
-  static constexpr int kQBytes = kAtoms * kBlockQ * 128;
+  static constexpr int kDPadK = (D + 15) / 16 * 16;            // K extent of S = Q K^T (UMMA K step 16)
+  static constexpr int kDPadN = (D + 7) / 8 * 8;               // N extent of O += P V (UMMA N step 8)
+  static constexpr int kQTileBytes = kAtoms * kBlockQ * 128;   // one query tile: atom a at a * 16 KB
   static constexpr int kKVTileBytes = kAtoms * kBlockKV * 128;  // one of K or V
-  static constexpr int kPAtoms = kBlockKV / 64;
-  static constexpr int kPBytes = kPAtoms * kBlockQ * 128;
-  static constexpr int kSmemBytes = kQBytes + kStages * 2 * kKVTileBytes + kPBytes;   // barriers are static smem
-  static constexpr int kTmemCols = 256;
-  static constexpr int kTmemS = 0;
-  static constexpr int kTmemO = kBlockKV;                       // O accumulator starts after S
-  // 228 KB per SM, 1 KB reserved per CTA, dynamic smem starts at a 1 KB boundary after the static barriers
-  static constexpr int kMinBlocks = (kSmemBytes <= 112 * 1024) ? 2 : 1;
-  static_assert(kBlockKV + kDPad <= kTmemCols, "TMEM budget");
+  static constexpr int kPBytes = kBlockQ * 128;                 // one query tile's P (64 keys = one atom)
+  static constexpr int kStages = (D <= 40) ? 4 : (D <= 80 ? 3 : 2);
+  static constexpr int kSmemBytes = kQTiles * (kQTileBytes + kPBytes) + kStages * 2 * kKVTileBytes;
+  static constexpr int kTmemCols = 512;                          // one CTA per SM owns all of TMEM
+  static constexpr int kTmemS = 0;                               // S_t: 64 columns each
+  static constexpr int kTmemO = kQTiles * kBlockKV;              // O_t: kDPadN columns each
+  static_assert(kQTiles * (kBlockKV + kDPadN) <= kTmemCols, "TMEM budget");
+  static_assert(kSmemBytes <= 226 * 1024, "shared memory budget");
+  static_assert(kSmemBytes > 114 * 1024, "two resident CTAs would deadlock on the 512-column TMEM allocation");
 };
 
-__device__ __forceinline__ float fast_exp2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
 template <int D, bool kHasMask>
-__global__ void __launch_bounds__(kAttnThreads, AttnCfg<D>::kMinBlocks)
+__global__ void __launch_bounds__(AttnCfg<D>::kThreads, 1)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                      const __grid_constant__ CUtensorMap tm_v, const AttnDev p) {
   using C = AttnCfg<D>;
-  constexpr int BKV = C::kBlockKV;
+  constexpr int BKV = kBlockKV;
+  constexpr int NS = C::kStages;
+  constexpr int NT = C::kQTiles;
   extern __shared__ __align__(1024) uint8_t smem[];     // SWIZZLE_128B atoms need 1024-byte alignment
-  __shared__ __align__(8) uint64_t bars[5 + 2 * C::kStages + 1];
-  uint8_t* sQ = smem;
-  uint8_t* sKV = sQ + C::kQBytes;                       // stage s: K at sKV + s*2*tile, V right after
-  uint8_t* sP = sKV + C::kStages * 2 * C::kKVTileBytes;
+  __shared__ __align__(8) uint64_t bars[2 + 4 * NT + 4 * NS + 1];
+  uint8_t* sQ = smem;                                   // [NT] query tiles
+  uint8_t* sK = sQ + NT * C::kQTileBytes;               // [NS] K tiles
+  uint8_t* sV = sK + NS * C::kKVTileBytes;              // [NS] V tiles
+  uint8_t* sP = sV + NS * C::kKVTileBytes;              // [NT] P tiles
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint64_t* q_full = bars + 0;
   uint64_t* q_ready = bars + 1;
-  uint64_t* s_full = bars + 2;
-  uint64_t* p_ready = bars + 3;
-  uint64_t* pv_done = bars + 4;
-  uint64_t* kv_full = bars + 5;                          // [kStages]
-  uint64_t* kv_empty = kv_full + C::kStages;             // [kStages]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(kv_empty + C::kStages);
+  uint64_t* s_full = bars + 2;                           // [t] S_j of tile t is in TMEM
+  uint64_t* s_free = s_full + NT;                        // [t] S_j is in registers: the S columns may be overwritten
+  uint64_t* p_ready = s_free + NT;                       // [t] P_j is in shared memory (and O rescaled if needed)
+  uint64_t* pv_done = p_ready + NT;                      // [t] O += P_j V_j finished: P buffer and O are free
+  uint64_t* k_full = pv_done + NT;
+  uint64_t* k_empty = k_full + NS;
+  uint64_t* v_full = k_empty + NS;
+  uint64_t* v_empty = v_full + NS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(v_empty + NS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int q_tile = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
+  const int q_block = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
+  const int q0 = q_block * (NT * kBlockQ);
   const int num_kv_tiles = (p.kv_len + BKV - 1) / BKV;
   const int col0 = head * D;                             // first column of this head in the row
+  const int n_tiles = min(NT, (p.q_len - q0 + kBlockQ - 1) / kBlockQ);   // query tiles with at least one valid row
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
     mbar_init(q_full, 1);
-    mbar_init(q_ready, 128);
-    mbar_init(s_full, 1);
-    mbar_init(p_ready, 128);
-    mbar_init(pv_done, 1);
-    for (int i = 0; i < C::kStages; ++i) {
-      mbar_init(&kv_full[i], 1);
-      mbar_init(&kv_empty[i], 1);
+    mbar_init(q_ready, 4 * n_tiles);
+    for (int t = 0; t < NT; ++t) {
+      mbar_init(&s_full[t], 1);
+      mbar_init(&s_free[t], 4);
+      mbar_init(&p_ready[t], 4);
+      mbar_init(&pv_done[t], 1);
     }
+    for (int i = 0; i < 4 * NS; ++i) mbar_init(&k_full[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<C::kTmemCols>(tmem_slot);
@@ -111,23 +134,30 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      mbar_arrive_expect_tx(q_full, C::kQBytes);
+      mbar_arrive_expect_tx(q_full, n_tiles * C::kQTileBytes);
+      for (int t = 0; t < n_tiles; ++t)
 #pragma unroll
-      for (int a = 0; a < C::kAtoms; ++a)
-        tma_load_3d(&tm_q, q_full, sQ + a * kBlockQ * 128, col0 + a * 64, q_tile * kBlockQ, b, kEvictFirst);
+        for (int a = 0; a < C::kAtoms; ++a)     // rows past q_len are zero-filled by TMA
+          tma_load_3d(&tm_q, q_full, sQ + t * C::kQTileBytes + a * (kBlockQ * 128), col0 + a * 64,
+                      q0 + t * kBlockQ, b, kEvictFirst);
       int stage = 0;
       uint32_t phase = 0;
       for (int j = 0; j < num_kv_tiles; ++j) {
-        mbar_wait(&kv_empty[stage], phase ^ 1);
-        uint8_t* sk = sKV + stage * 2 * C::kKVTileBytes;
-        uint8_t* sv = sk + C::kKVTileBytes;
-        mbar_arrive_expect_tx(&kv_full[stage], 2 * C::kKVTileBytes);
+        // K and V travel in separate rings: K_j is released as soon as S_j exists (the score MMA runs one tile
+        // ahead of the softmax), V_j only after O += P_j V_j.
+        mbar_wait(&k_empty[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&k_full[stage], C::kKVTileBytes);
 #pragma unroll
-        for (int a = 0; a < C::kAtoms; ++a) {
-          tma_load_3d(&tm_k, &kv_full[stage], sk + a * BKV * 128, col0 + a * 64, j * BKV, b, kEvictLast);
-          tma_load_3d(&tm_v, &kv_full[stage], sv + a * BKV * 128, col0 + a * 64, j * BKV, b, kEvictLast);
-        }
-        if (++stage == C::kStages) {
+        for (int a = 0; a < C::kAtoms; ++a)
+          tma_load_3d(&tm_k, &k_full[stage], sK + stage * C::kKVTileBytes + a * BKV * 128, col0 + a * 64, j * BKV, b,
+                      kEvictLast);
+        mbar_wait(&v_empty[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&v_full[stage], C::kKVTileBytes);
+#pragma unroll
+        for (int a = 0; a < C::kAtoms; ++a)
+          tma_load_3d(&tm_v, &v_full[stage], sV + stage * C::kKVTileBytes + a * BKV * 128, col0 + a * 64, j * BKV, b,
+                      kEvictLast);
+        if (++stage == NS) {
           stage = 0;
           phase ^= 1;
         }
@@ -135,170 +165,271 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // The whole warp runs this loop converged (barrier polls are made warp-uniform); one elected lane issues the
+    // tcgen05 instructions.  Converged control flow lets the descriptors live in uniform registers and avoids the
+    // per-instruction election loop the compiler emits around tcgen05.mma in divergent code.
+    {
       constexpr uint32_t idesc_qk = umma_idesc_bf16(kBlockQ, BKV, 0, 0);
-      constexpr uint32_t idesc_pv = umma_idesc_bf16(kBlockQ, C::kDPad, 0, 1);   // B (= V) is MN-major
-      const uint32_t tmem_s = tmem_base + C::kTmemS;
-      const uint32_t tmem_o = tmem_base + C::kTmemO;
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(kBlockQ, C::kDPadN, 0, 1);   // B (= V) is MN-major
       const uint32_t q_addr = smem_u32(sQ);
       const uint32_t p_addr = smem_u32(sP);
+      const bool leader = elect_one();
+      // S_t = Q_t K_j^T : K-steps of 16 over the (padded) head dim
+      auto issue_qk = [&](int t, int stage) {
+        if (leader) {
+          const uint32_t k_addr = smem_u32(sK + stage * C::kKVTileBytes);
+          const uint32_t tmem_s = tmem_base + C::kTmemS + t * BKV;
+#pragma unroll
+          for (int kk = 0; kk < C::kDPadK / 16; ++kk) {
+            const uint32_t qa = q_addr + t * C::kQTileBytes + (kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32;
+            const uint32_t ka = k_addr + (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
+            umma_ss(tmem_s, umma_desc_kmajor_sw128(qa), umma_desc_kmajor_sw128(ka), idesc_qk, kk != 0);
+          }
+          umma_commit(&s_full[t]);
+        }
+      };
+      // O_t += P_t V_j : K-steps of 16 keys; V tile is [key][64 cols] per atom -> MN-major, LBO = atom stride
+      auto issue_pv = [&](int t, int stage, bool first) {
+        if (leader) {
+          const uint32_t v_addr = smem_u32(sV + stage * C::kKVTileBytes);
+          const uint32_t tmem_o = tmem_base + C::kTmemO + t * C::kDPadN;
+#pragma unroll
+          for (int kk = 0; kk < BKV / 16; ++kk) {
+            const uint32_t pa = p_addr + t * C::kPBytes + kk * 32;
+            const uint32_t va = v_addr + kk * (16 * 128);
+            umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
+                    !(first && kk == 0));
+          }
+          umma_commit(&pv_done[t]);
+        }
+      };
+#ifdef AFB_ATTN_PROFILE
+      long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      long long prof_prev = clock64();
+#endif
       mbar_wait(q_full, 0);
       mbar_wait(q_ready, 0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      for (int t = 0; t < n_tiles; ++t) issue_qk(t, 0);
+      if (leader) umma_commit(&k_empty[0]);
       int stage = 0;
       uint32_t phase = 0;
+      const uint32_t all = (1u << n_tiles) - 1u;
       for (int j = 0; j < num_kv_tiles; ++j) {
-        mbar_wait(&kv_full[stage], phase);
-        tc_fence_after();
-        const uint32_t k_addr = smem_u32(sKV + stage * 2 * C::kKVTileBytes);
-        const uint32_t v_addr = k_addr + C::kKVTileBytes;
-        // S = Q K^T : K-steps of 16 over the (padded) head dim
+        int nstage = stage + 1;
+        uint32_t nphase = phase;
+        if (nstage == NS) {
+          nstage = 0;
+          nphase ^= 1;
+        }
+        const bool more = j + 1 < num_kv_tiles;
+        AFB_PROF(3);
+        if (more) mbar_wait(&k_full[nstage], nphase);
+        mbar_wait(&v_full[stage], phase);
+        AFB_PROF(0);                                      // wait for K/V tiles
+        // events of this round: bit t = "S_t(j+1) may be issued" (scores j are in registers),
+        //                       bit NT + t = "O_t += P_t(j) V_j may be issued" (P_t(j) is published)
+        uint32_t pending = (more ? all : 0u) | (all << NT);
+        const uint32_t par = j & 1;
+        while (pending != 0u) {
 #pragma unroll
-        for (int kk = 0; kk < C::kDPad / 16; ++kk) {
-          const uint32_t qa = q_addr + (kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32;
-          const uint32_t ka = k_addr + (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-          umma_ss(tmem_s, umma_desc_kmajor_sw128(qa), umma_desc_kmajor_sw128(ka), idesc_qk, kk != 0);
+          for (int t = 0; t < NT; ++t) {
+            if ((pending >> t) & 1u) {
+              if (__all_sync(0xffffffffu, mbar_test_wait(&s_free[t], par))) {
+                AFB_PROF(1);                              // polling
+                tc_fence_after();
+                issue_qk(t, nstage);
+                pending &= ~(1u << t);
+                if ((pending & all) == 0u && leader) umma_commit(&k_empty[nstage]);
+                AFB_PROF(2);                              // issuing
+              }
+            }
+            if ((pending >> (NT + t)) & 1u) {
+              if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[t], par))) {
+                AFB_PROF(1);
+                tc_fence_after();
+                issue_pv(t, stage, j == 0);
+                pending &= ~(1u << (NT + t));
+                AFB_PROF(2);
+              }
+            }
+          }
         }
-        umma_commit(s_full);
-        // wait for P_j (and the O rescale) from the softmax warps
-        mbar_wait(p_ready, j & 1);
-        tc_fence_after();
-        // O += P V : K-steps of 16 keys; V tile is [key][64 cols] per atom -> MN-major, LBO = atom stride
-#pragma unroll
-        for (int kk = 0; kk < BKV / 16; ++kk) {
-          const uint32_t pa = p_addr + (kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32;
-          const uint32_t va = v_addr + kk * (16 * 128);
-          umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
-                  (j | kk) != 0);
-        }
-        umma_commit(&kv_empty[stage]);
-        umma_commit(pv_done);
-        if (++stage == C::kStages) {
-          stage = 0;
-          phase ^= 1;
-        }
+        if (leader) umma_commit(&v_empty[stage]);
+        stage = nstage;
+        phase = nphase;
       }
+#ifdef AFB_ATTN_PROFILE
+      {
+        const int blk = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+        if (lane == 0 && blk < p.prof_blocks)
+          for (int i = 0; i < 8; ++i) p.prof[(blk * 17 + 16) * 8 + i] = prof_acc[i];
+      }
+#endif
     }
-  } else {
+  } else if (warp < 2 + 4 * n_tiles) {
     // ------------------------------------------------------------------ softmax / correction / epilogue
-    const int quarter = warp & 3;                         // TMEM lane quarter this warp may access
+    const int t = (warp - 2) >> 2;                        // query tile
+    const int quarter = warp & 3;                         // TMEM lane quarter this warp may access (= its SMSP)
     const int row = quarter * 32 + lane;                  // query row inside the tile
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
-    const uint32_t tmem_s = tmem_base + lane_addr + C::kTmemS;
-    const uint32_t tmem_o = tmem_base + lane_addr + C::kTmemO;
+    const uint32_t tmem_s = tmem_base + lane_addr + C::kTmemS + t * BKV;
+    const uint32_t tmem_o = tmem_base + lane_addr + C::kTmemO + t * C::kDPadN;
+    uint8_t* prow = sP + t * C::kPBytes + row * 128;
+#ifdef AFB_ATTN_PROFILE
+    long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long prof_prev = clock64();
+#endif
 
     mbar_wait(q_full, 0);
     if constexpr (D % 16 != 0) {
       // head_dim 40: K-step 2 covers columns 32..47; zero this row's columns 40..47 of Q (one 16-byte chunk,
       // swizzled position) so that whatever K holds there (the next head's data) contributes nothing.
       constexpr int chunk = D / 8;                        // 16-byte chunk index inside the 128-byte row
-      uint8_t* dst = sQ + (C::kAtoms - 1) * kBlockQ * 128 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+      uint8_t* dst = sQ + t * C::kQTileBytes + (C::kAtoms - 1) * (kBlockQ * 128) + row * 128 +
+                     (((chunk & 7) ^ (row & 7)) << 4);
       *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
       fence_proxy_async_smem();
     }
-    mbar_arrive(q_ready);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(q_ready);
 
-    float m_used = 0.f;      // max (log2 domain) the exponentials are currently referenced to
+    // Scores stay raw (unscaled) in registers; the softmax scale (times log2 e) is folded into the one FFMA that
+    // also subtracts the reference max:  p = 2^(s * scale_log2 - m_used).
+    float m_used = 0.f;      // max (scaled log2 domain) the exponentials are currently referenced to
     float l_run = 0.f;       // running row sum
+    const float sc = p.scale_log2;
+    const uint64_t sc2 = pack_f32x2(sc, sc);
     const uint8_t* mask_row = kHasMask ? p.key_mask + static_cast<long long>(b) * p.kv_len : nullptr;
 
     for (int j = 0; j < num_kv_tiles; ++j) {
-      mbar_wait(s_full, j & 1);
+      AFB_PROF(7);
+      mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
-      float s[BKV];
+      AFB_PROF(0);                                        // wait for S
+      uint32_t r[BKV];
 #pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(tmem_s + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]) * p.scale_log2;
-      }
+      for (int c = 0; c < BKV / 32; ++c) tmem_ld32p(tmem_s + c * 32, &r[c * 32]);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_free[t]);             // the MMA warp may start S_{j+1}
+      AFB_PROF(1);                                        // TMEM load
+
       const int kv0 = j * BKV;
       if (kHasMask) {
+        // masked keys get a large finite negative IN THE SCALED DOMAIN (like the reference's masked_fill after the
+        // scaling): a fully masked row then cancels exactly to exp2(0) and averages uniformly
 #pragma unroll
-        for (int i = 0; i < BKV; ++i)
-          if (kv0 + i < p.kv_len && mask_row[kv0 + i] == 0) s[i] = kMaskedScore;
+        for (int i = 0; i < BKV; ++i) {
+          float v = __uint_as_float(r[i]) * sc;
+          if (kv0 + i < p.kv_len && mask_row[kv0 + i] == 0) v = kMaskedScore;
+          r[i] = __float_as_uint(v);
+        }
       }
       if (kv0 + BKV > p.kv_len) {
 #pragma unroll
         for (int i = 0; i < BKV; ++i)
-          if (kv0 + i >= p.kv_len) s[i] = -INFINITY;
+          if (kv0 + i >= p.kv_len) r[i] = 0xff800000u;    // -inf
       }
-      float m_tile = s[0];
+      float mx[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
 #pragma unroll
-      for (int i = 1; i < BKV; ++i) m_tile = fmaxf(m_tile, s[i]);
-
-      // P buffer and O are free once PV(j-1) has completed
-      if (j > 0) {
-        mbar_wait(pv_done, (j - 1) & 1);
-        tc_fence_after();
+      for (int i = 4; i < BKV; i += 8) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (i + 2 * c + 1 < BKV)
+            mx[c] = fmax3(mx[c], __uint_as_float(r[i + 2 * c]), __uint_as_float(r[i + 2 * c + 1]));
       }
-      bool need = (j == 0) || (m_tile > m_used + kRescaleThreshold);
+      const float m_raw = fmaxf(fmax3(mx[0], mx[1], mx[2]), mx[3]);
+      const float m_tile = kHasMask ? m_raw : m_raw * sc;   // scale > 0
+
+      const bool need = (j == 0) || (m_tile > m_used + kRescaleThreshold);
       if (j == 0) {
         m_used = m_tile;
       } else if (__any_sync(0xffffffffu, need)) {
+        // rare after the first tiles: O must be rescaled, which needs O += P_{j-1} V_{j-1} to have finished
+        mbar_wait(&pv_done[t], (j - 1) & 1);
+        tc_fence_after();
         const float m_new = need ? m_tile : m_used;
-        const float alpha = fast_exp2(m_used - m_new);   // 1 for rows that keep their reference max
+        const float alpha = ex2_approx(m_used - m_new);  // 1 for rows that keep their reference max
         m_used = m_new;
         l_run *= alpha;
 #pragma unroll
-        for (int c = 0; c < C::kDPad / 16; ++c) {
-          uint32_t r[16];
-          tmem_ld16(tmem_o + c * 16, r);
+        for (int c = 0; c < C::kDPadN / 8; ++c) {
+          uint32_t o[8];
+          tmem_ld8(tmem_o + c * 8, o);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st16(tmem_o + c * 16, r);
+          for (int i = 0; i < 8; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st8(tmem_o + c * 8, o);
         }
         tmem_st_wait();
       }
-      float l_tile = 0.f;
+      AFB_PROF(2);                                        // max (+ rare rescale)
+
+      // exponentials: FFMA2 (scale, subtract max) -> 2 x MUFU.EX2 -> FADD2 (row sum) -> F2FP (bf16x2), in place
+      const uint64_t nm2 = pack_f32x2(-m_used, -m_used);
+      uint64_t acc0 = 0ull, acc1 = 0ull;                 // two packed partial sums
 #pragma unroll
-      for (int i = 0; i < BKV; ++i) {
-        s[i] = fast_exp2(s[i] - m_used);
-        l_tile += s[i];
+      for (int i = 0; i < BKV / 2; ++i) {
+        uint64_t x = pack_f32x2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+        x = kHasMask ? fadd2(x, nm2) : ffma2(x, sc2, nm2);
+        float lo, hi;
+        unpack_f32x2(x, lo, hi);
+        lo = ex2_approx(lo);
+        hi = ex2_approx(hi);
+        const uint64_t e = pack_f32x2(lo, hi);
+        if (i & 1) acc1 = fadd2(acc1, e); else acc0 = fadd2(acc0, e);
+        r[i] = cvt_bf16x2(lo, hi);
       }
-      l_run += l_tile;
-      // P -> bf16, canonical K-major SW128 layout: atom a = 64 keys, row pitch 128 B, 16-byte chunk c at c ^ (row & 7)
-#pragma unroll
-      for (int a = 0; a < C::kPAtoms; ++a) {
-        uint8_t* prow = sP + a * (kBlockQ * 128) + row * 128;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const float* sv = &s[a * 64 + c * 8];
-          const uint4 pk = make_uint4(pack_bf16x2(sv[0], sv[1]), pack_bf16x2(sv[2], sv[3]),
-                                      pack_bf16x2(sv[4], sv[5]), pack_bf16x2(sv[6], sv[7]));
-          *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = pk;
-        }
+      {
+        float a, bb;
+        unpack_f32x2(fadd2(acc0, acc1), a, bb);
+        l_run += a + bb;
       }
+      AFB_PROF(4);                                        // exponentials
+
+      // the P buffer is free once O += P_{j-1} V_{j-1} has completed (long ago in steady state)
+      if (j > 0) mbar_wait(&pv_done[t], (j - 1) & 1);
+      AFB_PROF(5);                                        // wait for the P buffer
+      // P -> canonical K-major SW128 layout: row pitch 128 B, 16-byte chunk c at c ^ (row & 7)
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) =
+            make_uint4(r[c * 4], r[c * 4 + 1], r[c * 4 + 2], r[c * 4 + 3]);
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(p_ready);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_ready[t]);
+      AFB_PROF(6);                                        // P store
     }
+#ifdef AFB_ATTN_PROFILE
+    {
+      const int blk = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+      if (lane == 0 && blk < p.prof_blocks)
+        for (int i = 0; i < 8; ++i) p.prof[(blk * 17 + (warp - 2)) * 8 + i] = prof_acc[i];
+    }
+#endif
 
     // ---- epilogue: O / l -> bf16 -> out[b, q, head*D : head*D + D]
-    mbar_wait(pv_done, (num_kv_tiles - 1) & 1);
+    mbar_wait(&pv_done[t], (num_kv_tiles - 1) & 1);
     tc_fence_after();
-    const int q_idx = q_tile * kBlockQ + row;
+    const int q_idx = q0 + t * kBlockQ + row;
     const float inv_l = 1.0f / l_run;
     __nv_bfloat16* orow = p.out + (static_cast<long long>(b) * p.q_len + q_idx) * p.ldo + col0;
 #pragma unroll
-    for (int c = 0; c < C::kDPad / 16; ++c) {
-      uint32_t r[16];
-      tmem_ld16(tmem_o + c * 16, r);
+    for (int c = 0; c < D / 8; ++c) {
+      uint32_t o[8];
+      tmem_ld8(tmem_o + c * 8, o);
       tmem_ld_wait();
       if (q_idx < p.q_len) {
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          if (c * 16 + h * 8 < D) {
-            const uint4 pk = make_uint4(
-                pack_bf16x2(__uint_as_float(r[8 * h + 0]) * inv_l, __uint_as_float(r[8 * h + 1]) * inv_l),
-                pack_bf16x2(__uint_as_float(r[8 * h + 2]) * inv_l, __uint_as_float(r[8 * h + 3]) * inv_l),
-                pack_bf16x2(__uint_as_float(r[8 * h + 4]) * inv_l, __uint_as_float(r[8 * h + 5]) * inv_l),
-                pack_bf16x2(__uint_as_float(r[8 * h + 6]) * inv_l, __uint_as_float(r[8 * h + 7]) * inv_l));
-            *reinterpret_cast<uint4*>(orow + c * 16 + h * 8) = pk;
-          }
-        }
+        const uint4 pk = make_uint4(
+            pack_bf16x2(__uint_as_float(o[0]) * inv_l, __uint_as_float(o[1]) * inv_l),
+            pack_bf16x2(__uint_as_float(o[2]) * inv_l, __uint_as_float(o[3]) * inv_l),
+            pack_bf16x2(__uint_as_float(o[4]) * inv_l, __uint_as_float(o[5]) * inv_l),
+            pack_bf16x2(__uint_as_float(o[6]) * inv_l, __uint_as_float(o[7]) * inv_l));
+        *reinterpret_cast<uint4*>(orow + c * 8) = pk;
       }
     }
   }
@@ -308,11 +439,30 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   if (warp == 1) tmem_dealloc<C::kTmemCols>(tmem_base);
 }
 
+#ifdef AFB_ATTN_PROFILE
+long long* g_attn_prof = nullptr;
+int g_attn_prof_blocks = 0;
+#endif
+
 int make_qkv_map(CUtensorMap* map, const void* ptr, int width, int len, int batch, long long ld, int box_rows) {
   const uint64_t dims[3] = {static_cast<uint64_t>(width), static_cast<uint64_t>(len), static_cast<uint64_t>(batch)};
   const uint64_t strides[2] = {static_cast<uint64_t>(ld) * 2, static_cast<uint64_t>(ld) * 2 * static_cast<uint64_t>(len)};
   const uint32_t box[3] = {64, static_cast<uint32_t>(box_rows), 1};
   return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ptr, dims, strides, box, Swizzle::B128);
+}
+
+template <int D, bool kHasMask>
+int launch_attn_kernel(const CUtensorMap& tm_q, const CUtensorMap& tm_k, const CUtensorMap& tm_v, const AttnDev& p,
+                       dim3 grid, cudaStream_t stream) {
+  using C = AttnCfg<D>;
+  auto kern = attention_fwd_kernel<D, kHasMask>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_set = true;
+  }
+  kern<<<grid, C::kThreads, C::kSmemBytes, stream>>>(tm_q, tm_k, tm_v, p);
+  return 0;
 }
 
 template <int D>
@@ -321,8 +471,8 @@ int launch_attn(const afb_attn_args& a, cudaStream_t stream) {
   CUtensorMap tm_q, tm_k, tm_v;
   const int width = a.heads * a.head_dim;
   if (int rc = make_qkv_map(&tm_q, a.q, width, a.q_len, a.batch, a.ldq, kBlockQ)) return rc;
-  if (int rc = make_qkv_map(&tm_k, a.k, width, a.kv_len, a.batch, a.ldk, C::kBlockKV)) return rc;
-  if (int rc = make_qkv_map(&tm_v, a.v, width, a.kv_len, a.batch, a.ldv, C::kBlockKV)) return rc;
+  if (int rc = make_qkv_map(&tm_k, a.k, width, a.kv_len, a.batch, a.ldk, kBlockKV)) return rc;
+  if (int rc = make_qkv_map(&tm_v, a.v, width, a.kv_len, a.batch, a.ldv, kBlockKV)) return rc;
   AttnDev p;
   p.out = reinterpret_cast<__nv_bfloat16*>(a.out);
   p.key_mask = a.key_mask;
@@ -331,24 +481,15 @@ int launch_attn(const afb_attn_args& a, cudaStream_t stream) {
   p.heads = a.heads;
   p.ldo = a.ldo;
   p.scale_log2 = a.scale * 1.4426950408889634f;
-  dim3 grid((a.q_len + kBlockQ - 1) / kBlockQ, a.heads, a.batch);
-  if (a.key_mask != nullptr) {
-    auto kern = attention_fwd_kernel<D, true>;
-    static bool attr_set = false;
-    if (!attr_set) {
-      AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-      attr_set = true;
-    }
-    kern<<<grid, kAttnThreads, C::kSmemBytes, stream>>>(tm_q, tm_k, tm_v, p);
-  } else {
-    auto kern = attention_fwd_kernel<D, false>;
-    static bool attr_set = false;
-    if (!attr_set) {
-      AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-      attr_set = true;
-    }
-    kern<<<grid, kAttnThreads, C::kSmemBytes, stream>>>(tm_q, tm_k, tm_v, p);
-  }
+#ifdef AFB_ATTN_PROFILE
+  p.prof = g_attn_prof;
+  p.prof_blocks = g_attn_prof_blocks;
+#endif
+  constexpr int rows_per_cta = C::kQTiles * kBlockQ;
+  dim3 grid((a.q_len + rows_per_cta - 1) / rows_per_cta, a.heads, a.batch);
+  const int rc = a.key_mask != nullptr ? launch_attn_kernel<D, true>(tm_q, tm_k, tm_v, p, grid, stream)
+                                       : launch_attn_kernel<D, false>(tm_q, tm_k, tm_v, p, grid, stream);
+  if (rc) return rc;
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
