@@ -111,8 +111,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // converged warp, one elected issuer (see gemm_bf16_tma_kernel)
       constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, 0, 0);
+      const bool leader = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -124,21 +125,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
-          const uint64_t da = umma_desc_kmajor_sw128(sa);
-          const uint64_t db = umma_desc_kmajor_sw128(sa + C::kABytes);
+          if (leader) {
+            const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+            const uint64_t da = umma_desc_kmajor_sw128(sa);
+            const uint64_t db = umma_desc_kmajor_sw128(sa + C::kABytes);
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the 128B swizzle atom: +2 in the >>4 address field
-            umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < kBK / 16; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the 128B swizzle atom: +2 in the >>4 address field
+              umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            }
+            umma_commit(&empty_bar[stage]);
           }
-          umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tmem_full[acc]);
+        if (leader) umma_commit(&tmem_full[acc]);
+        __syncwarp();
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -356,8 +361,12 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // The whole warp walks the loop converged and one elected lane issues: in divergent code (if (lane == 0)) the
+    // compiler wraps every tcgen05 instruction in an election loop and keeps the descriptors in vector registers,
+    // ~10 extra instructions per MMA on the one thread that must never fall behind the tensor pipe.
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, 0, 0);
+      const bool leader = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -369,18 +378,22 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
-          const uint64_t da = umma_desc_kmajor_sw128(sa);
-          const uint64_t db = umma_desc_kmajor_sw128(sa + C::kABytes);
+          if (leader) {
+            const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+            const uint64_t da = umma_desc_kmajor_sw128(sa);
+            const uint64_t db = umma_desc_kmajor_sw128(sa + C::kABytes);
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(&empty_bar[stage]);
+            for (int k = 0; k < kBK / 16; ++k) umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            umma_commit(&empty_bar[stage]);
+          }
+          __syncwarp();
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tmem_full[acc]);
+        if (leader) umma_commit(&tmem_full[acc]);
+        __syncwarp();
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
