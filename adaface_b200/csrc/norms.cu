@@ -5,7 +5,8 @@
 #include "common.cuh"
 #include "../../include/adaface_b200.h"
 
-#include <atomic>
+#include <cooperative_groups.h>
+
 
 namespace afb {
 void count_launch();
@@ -95,13 +96,11 @@ __global__ void __launch_bounds__(256) gn_apply_nchw_kernel(const float* __restr
 
 // ---- layout 1: x bf16 [B, HW, C] (token-major = channels-last) -------------------------------------------------
 // A chunk of T consecutive tokens is one contiguous T*C*2-byte span.  Thread = 8 adjacent channels (one 16-byte
-// vector) x up to kGnTpt tokens held in registers (all loads in flight at once); a block covers T tokens with
-// R = blockDim / (C/8) token rows.  Per-group reductions go through shared-memory atomics (32 groups).
-//   gn_partial_tok   chunk (mean, M2) per (b, group, chunk): two passes over the REGISTER copy, one read of x; the
-//                    last block of each sample merges the chunk partials (exact Chan merge) -> (mean, rstd)
-//   gn_apply_tok     normalise + affine (+ SiLU) with 16-byte loads / stores
-constexpr int kGnTpt = 8;           // tokens per thread
+// vector); a block covers its T tokens in passes of R = blockDim / (C/8) token rows.  Per-group reductions go
+// through shared-memory atomics (32 groups), once per block.
 constexpr int kGnMaxGroups = 64;
+constexpr int kGnUnroll = 4;        // token rows in flight per thread (16-byte loads)
+constexpr int kGnMaxChunks = 32;    // chunk partials per sample: merged by one warp lane each in the apply kernel
 
 __device__ __forceinline__ void unpack8(const uint4& u, float (&v)[8]) {
   const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
@@ -125,22 +124,21 @@ __device__ __forceinline__ void group_accumulate(float* slots, const float (&s)[
   atomicAdd(&slots[cur], acc);
 }
 
-// Tickets for the "last block of a sample finalises its statistics" pattern: self-resetting, one row of kGnMaxBatch
-// counters per in-flight launch slot (the host rotates over kGnTicketSlots slots, so launches that overlap on
-// different streams do not share counters unless more than kGnTicketSlots are in flight at once).
-constexpr int kGnMaxBatch = 1024;
-constexpr int kGnTicketSlots = 16;
-__device__ unsigned int g_gn_tickets[kGnTicketSlots * kGnMaxBatch];
-
+// Token-major GroupNorm, two kernels, each block streaming a long run of tokens (T = HW / nchunks, nchunks <= 32 per
+// sample) with kGnUnroll 16-byte loads in flight per thread and no block-wide synchronisation inside the stream:
+//   gn_partial_tok   every thread owns 8 channels and walks its token rows accumulating SHIFTED sums
+//                    sum(x - p), sum((x - p)^2) with p = its first value of that channel (one pass, no cancellation
+//                    problem: p is a sample of the distribution); at the end per-channel (n, mean, M2) are merged into
+//                    per-(sample, group, chunk) (mean, M2) with Chan's formula through two shared-memory reductions.
+//   gn_apply_tok     prologue: one warp per group merges the <= 32 chunk partials of its sample (Chan) -> mean, rstd;
+//                    then normalise + affine (+ SiLU) over the same token run.
 // pre_add (optional, fp32 [B, C] with row stride pre_add_ld): a per-(sample, channel) vector added to x BEFORE the
 // statistics and the normalisation - the conv bias + time-embedding add that precedes out_layers' GroupNorm in a
 // ResBlock (openaimodel.py:259-279), folded in so that no separate elementwise pass is needed.
-__global__ void __launch_bounds__(320, 2) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ pre_add,
-                                                             int pre_add_ld, float* __restrict__ partial,
-                                                             float* __restrict__ stats, int C, int HW, int cpg, int T,
-                                                             int nchunks, float eps, int ticket_slot) {
+__global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ pre_add,
+                                                             int pre_add_ld, float* __restrict__ partial, int C, int HW,
+                                                             int cpg, int T, int nchunks) {
   __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
-  __shared__ unsigned int s_ticket;
   const int b = blockIdx.y, chunk = blockIdx.x;
   const int t0 = chunk * T;
   const int nt = min(T, HW - t0);
@@ -150,104 +148,81 @@ __global__ void __launch_bounds__(320, 2) gn_partial_tok_kernel(const __nv_bfloa
   const int c0 = vec * 8;
   const int groups = C / cpg;
   for (int i = threadIdx.x; i < groups; i += blockDim.x) g_sum[i] = g_m2[i] = 0.f;
-  __syncthreads();
   const uint4* xp = reinterpret_cast<const uint4*>(x + (static_cast<long long>(b) * HW + t0) * C) + vec;
-  uint4 data[kGnTpt];
+  float piv[8], s1[8], s2[8];
 #pragma unroll
-  for (int i = 0; i < kGnTpt; ++i) {
-    const int t = row + i * R;
-    data[i] = (t < nt) ? xp[static_cast<long long>(t) * vpr] : make_uint4(0, 0, 0, 0);
+  for (int j = 0; j < 8; ++j) piv[j] = s1[j] = s2[j] = 0.f;
+  int n_mine = 0;
+  if (row < nt) unpack8(xp[static_cast<long long>(row) * vpr], piv);
+  for (int t = row; t < nt; t += R * kGnUnroll) {
+    uint4 data[kGnUnroll];
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int tt = t + u * R;
+      if (tt < nt) data[u] = xp[static_cast<long long>(tt) * vpr];
+    }
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) {
+      if (t + u * R < nt) {
+        float v[8];
+        unpack8(data[u], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[j] - piv[j];
+          s1[j] += d;
+          s2[j] = fmaf(d, d, s2[j]);
+        }
+        ++n_mine;
+      }
+    }
   }
+  // per-channel (n, mean, M2) of this thread's rows; pre_add shifts the mean only
   float add[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) add[j] = 0.f;
-  int my_rows = 0;                               // token rows this thread really holds
-#pragma unroll
-  for (int i = 0; i < kGnTpt; ++i) my_rows += (row + i * R < nt) ? 1 : 0;
   if (pre_add != nullptr) {
     const float4* ap = reinterpret_cast<const float4*>(pre_add + static_cast<long long>(b) * pre_add_ld + c0);
     const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
     add[0] = a0.x; add[1] = a0.y; add[2] = a0.z; add[3] = a0.w;
     add[4] = a1.x; add[5] = a1.y; add[6] = a1.z; add[7] = a1.w;
   }
-  float s[8];
+  const float n = static_cast<float>(n_mine);
+  const float inv = n_mine > 0 ? 1.0f / n : 0.f;
+  float mean_c[8], wsum[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = static_cast<float>(my_rows) * add[j];
-#pragma unroll
-  for (int i = 0; i < kGnTpt; ++i) {
-    float v[8];
-    unpack8(data[i], v);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s[j] += v[j];   // rows beyond nt hold zeros
+  for (int j = 0; j < 8; ++j) {
+    const float dm = s1[j] * inv;
+    mean_c[j] = piv[j] + dm + add[j];
+    s2[j] = fmaxf(s2[j] - s1[j] * dm, 0.f);     // M2 about this thread's own channel mean
+    wsum[j] = n * mean_c[j];
   }
-  group_accumulate(g_sum, s, c0, cpg);
+  __syncthreads();
+  group_accumulate(g_sum, wsum, c0, cpg);
   __syncthreads();
   const float inv_n = 1.0f / static_cast<float>(nt * cpg);
-  float mean[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) mean[j] = g_sum[(c0 + j) / cpg] * inv_n - add[j];   // (x + add) - mean = x - (mean - add)
-#pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = 0.f;
-#pragma unroll
-  for (int i = 0; i < kGnTpt; ++i) {
-    if (row + i * R < nt) {
-      float v[8];
-      unpack8(data[i], v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float d = v[j] - mean[j];
-        s[j] += d * d;
-      }
-    }
+  for (int j = 0; j < 8; ++j) {
+    const float d = mean_c[j] - g_sum[(c0 + j) / cpg] * inv_n;
+    s2[j] = fmaf(n * d, d, s2[j]);
   }
-  group_accumulate(g_m2, s, c0, cpg);
+  group_accumulate(g_m2, s2, c0, cpg);
   __syncthreads();
   for (int g = threadIdx.x; g < groups; g += blockDim.x) {
     float* out = partial + (static_cast<long long>(b * groups + g) * nchunks + chunk) * 2;
     out[0] = g_sum[g] * inv_n;
     out[1] = g_m2[g];
   }
-  // ---- the last block of sample b to get here merges the chunk partials (exact Chan merge) into (mean, rstd)
-  __threadfence();
-  __syncthreads();
-  unsigned int* ticket = &g_gn_tickets[ticket_slot * kGnMaxBatch + b];
-  if (threadIdx.x == 0) s_ticket = atomicAdd(ticket, 1u);
-  __syncthreads();
-  if (s_ticket != static_cast<unsigned int>(nchunks - 1)) return;
-  __threadfence();
-  if (threadIdx.x == 0) *ticket = 0u;            // self-reset for the next launch that uses this slot
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  for (int g = warp; g < groups; g += nwarps) {
-    const volatile float* p = partial + static_cast<long long>(b * groups + g) * nchunks * 2;
-    float tot = 0.f, wsum = 0.f;
-    for (int c = lane; c < nchunks; c += 32) {
-      const float n = static_cast<float>(min(T, HW - c * T) * cpg);
-      wsum += n * p[2 * c];
-      tot += n;
-    }
-    tot = warp_sum(tot);
-    const float gmean = warp_sum(wsum) / tot;
-    float m2 = 0.f;
-    for (int c = lane; c < nchunks; c += 32) {
-      const float n = static_cast<float>(min(T, HW - c * T) * cpg);
-      const float d = p[2 * c] - gmean;
-      m2 += p[2 * c + 1] + n * d * d;
-    }
-    m2 = warp_sum(m2);
-    if (lane == 0) {
-      stats[2 * (b * groups + g)] = gmean;
-      stats[2 * (b * groups + g) + 1] = rsqrtf(m2 / tot + eps);
-    }
-  }
 }
 
 __device__ __forceinline__ float silu(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
 template <bool kSilu>
-__global__ void __launch_bounds__(320, 3) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
+__global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ partial,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            const float* __restrict__ pre_add, int pre_add_ld,
-                                                           __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int T) {
+                                                           __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int T,
+                                                           int nchunks, float eps) {
+  __shared__ float s_mean[kGnMaxGroups], s_rstd[kGnMaxGroups];
   const int b = blockIdx.y;
   const int t0 = blockIdx.x * T;
   const int nt = min(T, HW - t0);
@@ -256,39 +231,243 @@ __global__ void __launch_bounds__(320, 3) gn_apply_tok_kernel(const __nv_bfloat1
   const int vec = threadIdx.x % vpr, row = threadIdx.x / vpr;
   const int c0 = vec * 8;
   const int groups = C / cpg;
+  const long long base = (static_cast<long long>(b) * HW + t0) * vpr + vec;
+  const uint4* xp = reinterpret_cast<const uint4*>(x) + base;
+  uint4* yp = reinterpret_cast<uint4*>(y) + base;
+  // first loads go out before the statistics merge so their latency overlaps it
+  uint4 data[kGnUnroll];
+#pragma unroll
+  for (int u = 0; u < kGnUnroll; ++u) {
+    const int tt = row + u * R;
+    if (tt < nt) data[u] = xp[static_cast<long long>(tt) * vpr];
+  }
+  {
+    // merge the chunk partials of sample b: lane c holds chunk c (nchunks <= 32), exact Chan merge
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int g = warp; g < groups; g += nwarps) {
+      const float* pp = partial + static_cast<long long>(b * groups + g) * nchunks * 2;
+      float nk = 0.f, mk = 0.f, m2k = 0.f;
+      if (lane < nchunks) {
+        nk = static_cast<float>(min(T, HW - lane * T) * cpg);
+        mk = pp[2 * lane];
+        m2k = pp[2 * lane + 1];
+      }
+      const float tot = warp_sum(nk);
+      const float gmean = warp_sum(nk * mk) / tot;
+      const float d = mk - gmean;
+      const float m2 = warp_sum(m2k + nk * d * d);
+      if (lane == 0) {
+        s_mean[g] = gmean;
+        s_rstd[g] = rsqrtf(m2 / tot + eps);
+      }
+    }
+  }
+  __syncthreads();
   float sc[8], of[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int g = (c0 + j) / cpg;
-    const float mean = stats[2 * (b * groups + g)], rstd = stats[2 * (b * groups + g) + 1];
     const float add = pre_add != nullptr ? pre_add[static_cast<long long>(b) * pre_add_ld + c0 + j] : 0.f;
-    sc[j] = rstd * gamma[c0 + j];
-    of[j] = beta[c0 + j] + (add - mean) * sc[j];
+    sc[j] = s_rstd[g] * gamma[c0 + j];
+    of[j] = beta[c0 + j] + (add - s_mean[g]) * sc[j];
   }
-  const long long base = (static_cast<long long>(b) * HW + t0) * vpr + vec;
-  const uint4* xp = reinterpret_cast<const uint4*>(x) + base;
-  uint4* yp = reinterpret_cast<uint4*>(y) + base;
-  uint4 data[kGnTpt];
+  for (int t = row; t < nt; t += R * kGnUnroll) {
+    uint4 next[kGnUnroll];
 #pragma unroll
-  for (int i = 0; i < kGnTpt; ++i) {
-    const int t = row + i * R;
-    if (t < nt) data[i] = xp[static_cast<long long>(t) * vpr];
-  }
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int tt = t + (kGnUnroll + u) * R;
+      if (tt < nt) next[u] = xp[static_cast<long long>(tt) * vpr];
+    }
 #pragma unroll
-  for (int i = 0; i < kGnTpt; ++i) {
-    const int t = row + i * R;
-    if (t < nt) {
-      float v[8];
-      unpack8(data[i], v);
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int tt = t + u * R;
+      if (tt < nt) {
+        float v[8];
+        unpack8(data[u], v);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        v[j] = v[j] * sc[j] + of[j];
-        if (kSilu) v[j] = silu(v[j]);
+        for (int j = 0; j < 8; ++j) {
+          v[j] = v[j] * sc[j] + of[j];
+          if (kSilu) v[j] = silu(v[j]);
+        }
+        yp[static_cast<long long>(tt) * vpr] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                           pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
       }
-      yp[static_cast<long long>(t) * vpr] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
-                                                        pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    }
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) data[u] = next[u];
+  }
+}
+
+// ---- single-launch variant for samples that fit the shared memory of one thread-block cluster ------------------
+// One cluster of kGnCluster CTAs per sample; CTA r stages its T = ceil(HW / kGnCluster) tokens in shared memory while
+// accumulating the shifted sums, the CTAs exchange their per-group (mean, M2) partials through distributed shared
+// memory, every CTA merges them (Chan) and normalises its tokens straight out of shared memory: x is read from
+// global memory once, one launch instead of two.
+constexpr int kGnCluster = 8;
+constexpr int kGnClusterMaxSmem = 200 * 1024;
+
+template <bool kSilu>
+__global__ void __launch_bounds__(320, 1) gn_cluster_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, const float* __restrict__ pre_add,
+                                                             int pre_add_ld, __nv_bfloat16* __restrict__ y, int C, int HW,
+                                                             int cpg, int T, float eps) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ __align__(128) uint8_t gn_smem[];
+  __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
+  __shared__ float s_part[2 * kGnMaxGroups];            // this CTA's (mean, M2) per group, read by the whole cluster
+  __shared__ float s_mean[kGnMaxGroups], s_rstd[kGnMaxGroups];
+  __shared__ __align__(8) uint64_t load_bar;
+  uint4* tile = reinterpret_cast<uint4*>(gn_smem);
+  const int b = blockIdx.y, rank = static_cast<int>(cluster.block_rank());
+  const int t0 = rank * T;
+  const int nt = max(0, min(T, HW - t0));
+  const int vpr = C >> 3;
+  const int R = blockDim.x / vpr;
+  const int vec = threadIdx.x % vpr, row = threadIdx.x / vpr;
+  const int c0 = vec * 8;
+  const int groups = C / cpg;
+  const long long span0 = (static_cast<long long>(b) * HW + t0) * C;      // first element of this CTA's span
+  const uint32_t span_bytes = static_cast<uint32_t>(nt) * C * 2;
+  constexpr uint32_t kPiece = 32 * 1024;
+  if (threadIdx.x == 0) {
+    mbar_init(&load_bar, 1);
+    fence_barrier_init();
+    if (span_bytes > 0) {
+      mbar_arrive_expect_tx(&load_bar, span_bytes);
+      for (uint32_t off = 0; off < span_bytes; off += kPiece)
+        bulk_load_1d(gn_smem + off, reinterpret_cast<const uint8_t*>(x + span0) + off, min(kPiece, span_bytes - off),
+                     &load_bar);
     }
   }
+  for (int i = threadIdx.x; i < groups; i += blockDim.x) g_sum[i] = g_m2[i] = 0.f;
+  float add[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) add[j] = 0.f;
+  if (pre_add != nullptr) {
+    const float4* ap = reinterpret_cast<const float4*>(pre_add + static_cast<long long>(b) * pre_add_ld + c0);
+    const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+    add[0] = a0.x; add[1] = a0.y; add[2] = a0.z; add[3] = a0.w;
+    add[4] = a1.x; add[5] = a1.y; add[6] = a1.z; add[7] = a1.w;
+  }
+  __syncthreads();                                       // barrier initialised, accumulators zeroed
+  if (span_bytes > 0) mbar_wait(&load_bar, 0);
+  float piv[8], s1[8], s2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) piv[j] = s1[j] = s2[j] = 0.f;
+  int n_mine = 0;
+  if (row < nt) unpack8(tile[row * vpr + vec], piv);
+  for (int t = row; t < nt; t += R) {
+    float v[8];
+    unpack8(tile[t * vpr + vec], v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = v[j] - piv[j];
+      s1[j] += d;
+      s2[j] = fmaf(d, d, s2[j]);
+    }
+    ++n_mine;
+  }
+  const float n = static_cast<float>(n_mine);
+  const float inv = n_mine > 0 ? 1.0f / n : 0.f;
+  float mean_c[8], wsum[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float dm = s1[j] * inv;
+    mean_c[j] = piv[j] + dm + add[j];
+    s2[j] = fmaxf(s2[j] - s1[j] * dm, 0.f);
+    wsum[j] = n * mean_c[j];
+  }
+  group_accumulate(g_sum, wsum, c0, cpg);
+  __syncthreads();
+  const float inv_n = nt > 0 ? 1.0f / static_cast<float>(nt * cpg) : 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float d = mean_c[j] - g_sum[(c0 + j) / cpg] * inv_n;
+    s2[j] = fmaf(n * d, d, s2[j]);
+  }
+  group_accumulate(g_m2, s2, c0, cpg);
+  __syncthreads();
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+    s_part[2 * g] = g_sum[g] * inv_n;
+    s_part[2 * g + 1] = g_m2[g];
+  }
+  cluster.sync();
+  {
+    // lane r reads CTA r's partial of group g over DSMEM; exact Chan merge
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int g = warp; g < groups; g += nwarps) {
+      float nk = 0.f, mk = 0.f, m2k = 0.f;
+      if (lane < kGnCluster) {
+        const float* remote = cluster.map_shared_rank(s_part, lane);
+        nk = static_cast<float>(max(0, min(T, HW - lane * T)) * cpg);
+        mk = remote[2 * g];
+        m2k = remote[2 * g + 1];
+      }
+      const float tot = warp_sum(nk);
+      const float gmean = warp_sum(nk * mk) / tot;
+      const float d = mk - gmean;
+      const float m2 = warp_sum(m2k + nk * d * d);
+      if (lane == 0) {
+        s_mean[g] = gmean;
+        s_rstd[g] = rsqrtf(m2 / tot + eps);
+      }
+    }
+  }
+  cluster.sync();                                        // nobody leaves while its partials are being read
+  float sc[8], of[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / cpg;
+    sc[j] = s_rstd[g] * gamma[c0 + j];
+    of[j] = beta[c0 + j] + (add[j] - s_mean[g]) * sc[j];
+  }
+  // normalise in place in shared memory, then stream the span out with bulk stores
+  for (int t = row; t < nt; t += R) {
+    float v[8];
+    unpack8(tile[t * vpr + vec], v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[j] = v[j] * sc[j] + of[j];
+      if (kSilu) v[j] = silu(v[j]);
+    }
+    tile[t * vpr + vec] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                                     pack_bf16x2(v[6], v[7]));
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0 && span_bytes > 0) {
+    for (uint32_t off = 0; off < span_bytes; off += kPiece)
+      bulk_store_1d(reinterpret_cast<uint8_t*>(y + span0) + off, gn_smem + off, min(kPiece, span_bytes - off));
+    bulk_commit_group();
+    bulk_wait_group_read<0>();
+  }
+}
+
+template <bool kSilu>
+int launch_gn_cluster(const __nv_bfloat16* x, const float* gamma, const float* beta, const float* pre_add, int pre_add_ld,
+                      __nv_bfloat16* y, int batch, int C, int HW, int cpg, int T, int threads, size_t smem, float eps,
+                      cudaStream_t stream) {
+  auto kern = gn_cluster_tok_kernel<kSilu>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGnClusterMaxSmem));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(kGnCluster, batch, 1);
+  cfg.blockDim = dim3(threads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kGnCluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  AFB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, x, gamma, beta, pre_add, pre_add_ld, y, C, HW, cpg, T, eps));
+  return 0;
 }
 
 // launch geometry of the token-major kernels: threads per block, token rows per pass, tokens per block
@@ -300,10 +479,12 @@ inline GnTokGeom gn_tok_geom(int batch, int channels, int hw) {
   const int vpr = channels / 8;
   g.rows = 256 / vpr > 0 ? 256 / vpr : 1;
   g.threads = g.rows * vpr;
-  g.T = g.rows * kGnTpt;
-  // keep at least ~2 waves of blocks on the GPU when the tensor is small
-  while (g.T > g.rows && static_cast<long long>(batch) * ((hw + g.T - 1) / g.T) < 2ll * num_sms()) g.T -= g.rows;
-  if (g.T > hw) g.T = ((hw + g.rows - 1) / g.rows) * g.rows;
+  // about four blocks per SM over the whole launch, at most kGnMaxChunks chunks per sample, at least one pass of rows
+  int want = (4 * num_sms() + batch - 1) / batch;
+  if (want > kGnMaxChunks) want = kGnMaxChunks;
+  if (want < 1) want = 1;
+  g.T = (hw + want - 1) / want;
+  g.T = ((g.T + g.rows - 1) / g.rows) * g.rows;
   g.nchunks = (hw + g.T - 1) / g.T;
   return g;
 }
@@ -411,16 +592,25 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
     float* partial = stats_ws + 2ll * batch * groups;
     const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
     dim3 grid(geo.nchunks, batch);
-    AFB_REQUIRE(batch <= kGnMaxBatch, "afb_groupnorm_tokens: batch %d > %d", batch, kGnMaxBatch);
+    AFB_REQUIRE(batch <= 65535, "afb_groupnorm_tokens: batch %d exceeds the grid limit", batch);
     AFB_REQUIRE(pre_add == nullptr || (pre_add_ld >= channels && pre_add_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(pre_add) & 15) == 0),
                 "afb_groupnorm_tokens: pre_add must be 16-byte aligned fp32 [B, C] with a row stride that is a multiple of 4");
-    static std::atomic<unsigned int> launch_seq{0};
-    const int slot = static_cast<int>(launch_seq.fetch_add(1, std::memory_order_relaxed) % kGnTicketSlots);
-    gn_partial_tok_kernel<<<grid, geo.threads, 0, stream>>>(xb, pre_add, pre_add_ld, partial, stats_ws, channels, hw, cpg, geo.T,
-                                                           geo.nchunks, eps, slot);
+    // samples that fit the shared memory of an 8-CTA cluster: one launch, x read once
+    const int Tc = (hw + kGnCluster - 1) / kGnCluster;
+    const size_t cluster_smem = static_cast<size_t>(Tc) * channels * 2;
+    // (measured on B200: wins for the small late-stage tensors; at 1 MB+ per sample the two-kernel path is faster,
+    //  sixteen 8-CTA clusters with ~160 KB of shared memory each do not all fit the GPCs at once)
+    if (cluster_smem <= static_cast<size_t>(kGnClusterMaxSmem) && static_cast<long long>(hw) * channels <= 512 * 1024) {
+      const int rc = act ? launch_gn_cluster<true>(xb, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, Tc, geo.threads, cluster_smem, eps, stream)
+                         : launch_gn_cluster<false>(xb, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, Tc, geo.threads, cluster_smem, eps, stream);
+      if (rc) return rc;
+      count_launch();
+      return 0;
+    }
+    gn_partial_tok_kernel<<<grid, geo.threads, 0, stream>>>(xb, pre_add, pre_add_ld, partial, channels, hw, cpg, geo.T, geo.nchunks);
     count_launch();
-    if (act) gn_apply_tok_kernel<true><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T);
-    else gn_apply_tok_kernel<false><<<grid, geo.threads, 0, stream>>>(xb, stats_ws, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T);
+    if (act) gn_apply_tok_kernel<true><<<grid, geo.threads, 0, stream>>>(xb, partial, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T, geo.nchunks, eps);
+    else gn_apply_tok_kernel<false><<<grid, geo.threads, 0, stream>>>(xb, partial, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T, geo.nchunks, eps);
     count_launch();
   } else {
     AFB_FAIL(2, "afb_groupnorm_tokens: unknown x_layout %d", x_layout);

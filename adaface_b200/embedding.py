@@ -61,6 +61,14 @@ class AttentionalPooler(nn.Module, _PackedWeights):
     def _build_pack(self):
         return {k: _f32(getattr(self, k).weight.squeeze(-1)) for k in ("lora_to_k", "lora_to_fg_q", "lora_to_bg_q")}
 
+    def prepare_queries(self, to_k: nn.Module, fg_q_emb: Tensor, bg_q_emb: Tensor, batch: int) -> Tensor:
+        """fg / bg pooling queries [B, 2, C] folded through lora_to_k (embedding_manager.py:186-235, :227)."""
+        p = self.packed()
+        if bg_q_emb.dim() == 1:
+            bg_q_emb = bg_q_emb[None].expand(batch, -1)
+        return ops.ada_pool_prep(to_k.weight.detach(), fg_q_emb.reshape(-1), bg_q_emb.reshape(batch, -1),
+                                 p["lora_to_fg_q"], p["lora_to_bg_q"], p["lora_to_k"])
+
     def forward(self, layer_attn_components: Dict, fg_q_emb: Tensor, bg_q_emb: Tensor, img_mask: Optional[Tensor] = None,
                 debug: bool = False, want_attn: bool = True):
         if self.training:
@@ -70,11 +78,11 @@ class AttentionalPooler(nn.Module, _PackedWeights):
         to_k = layer_attn_components["to_k"]
         infeat_size = layer_attn_components.get("infeat_size")
         b, n, c = x.shape
-        p = self.packed()
-        if bg_q_emb.dim() == 1:
-            bg_q_emb = bg_q_emb[None].expand(b, -1)
-        pool_q = ops.ada_pool_prep(to_k.weight.detach(), fg_q_emb.reshape(-1), bg_q_emb.reshape(b, -1),
-                                   p["lora_to_fg_q"], p["lora_to_bg_q"], p["lora_to_k"])       # :186-235, :227
+        # the pooling queries depend on the prompt and the weights only, not on the layer features: a caller may
+        # have computed them ahead (prepare_queries, e.g. on a side stream) and passes them along
+        pool_q = layer_attn_components.get("pool_q")
+        if pool_q is None:
+            pool_q = self.prepare_queries(to_k, fg_q_emb, bg_q_emb, b)
         key_mask = None
         if img_mask is not None:                                                                # :259-269
             m = F.interpolate(img_mask.float(), size=infeat_size, mode="nearest").reshape(b, -1)

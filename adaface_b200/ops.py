@@ -110,7 +110,7 @@ def groupnorm_tokens(x: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: f
             raise ValueError("groupnorm_tokens: pre_add must be fp32 [B, C] with contiguous rows")
         add_ld = pre_add.stride(0)
     _run("groupnorm_tokens", lib.afb_groupnorm_tokens, _ptr(x), layout, _ptr(gamma), _ptr(beta), _ptr(y), _ptr(ws), b, c,
-         hw, groups, eps, act, _ptr(pre_add), add_ld, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"C{c}")
+         hw, groups, eps, act, _ptr(pre_add), add_ld, _stream(), nbytes=float(x.numel()) * (x.element_size() + 2), tag=f"b{b}n{hw}C{c}")
     return y
 
 

@@ -211,13 +211,38 @@ class AdaPromptContext:
             self._pos[key] = torch.tensor(self.subjects[i].token_positions, dtype=torch.int32, device=device)
         return self._pos[key]
 
+    def prepare_queries(self, layers) -> None:
+        """The fg/bg pooling queries of every (layer, subject) depend on the prompt and on weights only, so one U-Net
+        call computes all of them up front on a side stream, concurrently with the first convolutions; `apply` joins
+        the stream before the first pooling.  `layers`: [(layer_idx, SpatialTransformer)]."""
+        main = torch.cuda.current_stream()
+        if self.__dict__.get("_side") is None:
+            self._side = torch.cuda.Stream()
+        self._pool_q, self._joined = {}, False
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            for layer_idx, st in layers:
+                ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
+                to_k = st.transformer_blocks[0].attn2.to_k
+                for i, s in enumerate(self.subjects):
+                    n = s.n_instances
+                    pq = s.embedder.poolers[ca].prepare_queries(to_k, s.layer_probes[ca], s.layer_extra_means[ca][:n], n)
+                    pq.record_stream(main)
+                    self._pool_q[(layer_idx, i)] = pq
+
     def apply(self, layer_idx: int, comps: Dict, layer_ctx: Tensor, time_emb: Tensor) -> Tensor:
         """layer_ctx bf16 [B, T, ctx_dim] (this call's private copy) is updated in place and returned."""
         ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
         bg_cache: Dict[int, Tensor] = {}
+        pool_q = self.__dict__.get("_pool_q") or {}
+        if pool_q and not self._joined:
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._joined = True
         for i, s in enumerate(self.subjects):
             n = s.n_instances
             sub = {"x": comps["x"][:n], "q": comps["q"][:n], "to_k": comps["to_k"], "infeat_size": comps["infeat_size"]}
+            if (layer_idx, i) in pool_q:
+                sub["pool_q"] = pool_q[(layer_idx, i)]
             cached = bg_cache.get(s.cached_bg_from) if s.cached_bg_from is not None else None
             mask = None if self.img_mask is None else self.img_mask[:n]
             _, pooled = s.embedder(layer_idx, sub, time_emb[:n], s.layer_probes[ca], s.layer_extra_means[ca][:n],
@@ -376,6 +401,8 @@ class UNetModel(nn.Module):
             with_ada.wants_layer_attn_components = True
             return with_ada
 
+        if ada is not None and x.is_cuda:
+            ada.prepare_queries(self.spatial_transformers())
         bundle = self.emb_bundle(emb)
         hs = []
         h = self.input_blocks[0][0](x.to(torch.bfloat16).contiguous(memory_format=CL))
@@ -391,6 +418,10 @@ class UNetModel(nn.Module):
             h = torch.cat([h, hs.pop()], dim=1).contiguous(memory_format=CL)
             h = module(h, bundle, layer_context(layer_idx), mask=img_mask)
             layer_idx += 1
+        if ada is not None:
+            if ada.__dict__.get("_pool_q") and not ada._joined:        # no conditioned layer ran: still join the stream
+                torch.cuda.current_stream().wait_stream(ada._side)
+            ada.__dict__["_pool_q"] = None
         return self.out[2](gn_silu(self.out[0], h)).to(x.dtype).contiguous()
 
 
