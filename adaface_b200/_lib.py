@@ -20,7 +20,9 @@ class GemmArgs(C.Structure):
     _fields_ = [("a", C.c_void_p), ("w", C.c_void_p), ("out", C.c_void_p), ("bias", C.c_void_p),
                 ("residual", C.c_void_p), ("m", C.c_int64), ("n", C.c_int64), ("k", C.c_int64),
                 ("lda", C.c_int64), ("ldw", C.c_int64), ("ldo", C.c_int64), ("ldr", C.c_int64),
-                ("epilogue", C.c_int), ("out_dtype", C.c_int), ("residual_dtype", C.c_int), ("hw", C.c_int)]
+                ("epilogue", C.c_int), ("out_dtype", C.c_int), ("residual_dtype", C.c_int), ("hw", C.c_int),
+                ("row_stats_out", C.c_void_p), ("ln_stats", C.c_void_p), ("ln_colsum", C.c_void_p),
+                ("ln_parts", C.c_int), ("ln_eps", C.c_float)]
 
 
 class AttnArgs(C.Structure):
@@ -44,6 +46,7 @@ _SIGNATURES = {
     "afb_add_bias_residual": (_I, [_P, _P, _P, _P, _I64, _I, _P]),
     "afb_layernorm_bf16": (_I, [_P, _P, _P, _P, _I64, _I, _F, _P]),
     "afb_gemm_bf16": (_I, [C.POINTER(GemmArgs), _P]),
+    "afb_gemm_stats_parts": (_I, [_I64]),
     "afb_attention_fwd": (_I, [C.POINTER(AttnArgs), _P]),
     "afb_ada_pool_ws_floats": (_I64, [_I, _I, _I]),
     "afb_ada_pool_prep_ws_floats": (_I64, [_I, _I]),

@@ -220,12 +220,28 @@ class CrossAttention(nn.Module, _PackedWeights):
                           key_mask)
         return ops.linear(a.view(b * n, inner), p["wo"], p["bo"], residual, False)
 
+    def out_projection(self, a2d: Tensor, residual: Optional[Tensor], want_stats: bool = False):
+        """to_out[0] (+ residual); with want_stats also the row partials a LayerNorm-folded consumer needs."""
+        p = self.packed()
+        if want_stats:
+            return ops.linear_stats(a2d, p["wo"], p["bo"], residual)
+        return ops.linear(a2d, p["wo"], p["bo"], residual, False)
+
+    def attend_fused_qkv(self, qkv: Tensor, key_mask: Optional[Tensor]) -> Tensor:
+        """qkv bf16 [B, N, 3*inner] (q | k | v column blocks) -> softmax(q k^T * scale) v as [B*N, inner]."""
+        self._check_modes(None, False)
+        b, n, w3 = qkv.shape
+        inner = w3 // 3
+        a = ops.attention(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
+                          key_mask)
+        return a.view(b * n, inner)
+
     def project_query(self, x: Tensor) -> Tensor:
         b, n, c = x.shape
         return ops.linear(x.view(b * n, c), self.packed()["wq"], None, None, False).view(b, n, -1)
 
     def cross_attention_tokens(self, q: Tensor, v_context: Tensor, k_context: Tensor,
-                               residual: Optional[Tensor]) -> Tensor:
+                               residual: Optional[Tensor], want_stats: bool = False):
         """q bf16 [B, N, C] (already projected); contexts [B, T, ctx_dim] -> to_out(attn) (+ residual)."""
         b, n, inner = q.shape
         p = self.packed()
@@ -239,7 +255,7 @@ class CrossAttention(nn.Module, _PackedWeights):
             k = ops.linear(kc.view(-1, kc.shape[2]), p["wk"], None, None, False).view(b, kc.shape[1], inner)
             v = ops.linear(vc.view(-1, vc.shape[2]), p["wv"], None, None, False).view(b, vc.shape[1], inner)
         a = ops.attention(q, k, v, self.heads, self.scale, None)
-        return ops.linear(a.view(b * n, inner), p["wo"], p["bo"], residual, False)
+        return self.out_projection(a.view(b * n, inner), residual, want_stats)
 
     def forward(self, x: Tensor, context=None, mask: Optional[Tensor] = None) -> Tensor:
         b, n, c = x.shape
@@ -275,33 +291,72 @@ class BasicTransformerBlock(nn.Module, _PackedWeights):
         self.checkpoint = checkpoint
 
     def _pack_key(self):
-        return tuple((p.data_ptr(), p._version, p.dtype) for n in (self.norm1, self.norm2, self.norm3)
-                     for p in n.parameters())
+        ps = [p for n in (self.norm1, self.norm2, self.norm3) for p in n.parameters()]
+        ps += [self.attn1.to_q.weight, self.attn1.to_k.weight, self.attn1.to_v.weight, self.attn2.to_q.weight]
+        ps += list(self.ff.net[0].proj.parameters())
+        return tuple((p.data_ptr(), p._version, p.dtype) for p in ps)
+
+    @staticmethod
+    def _fold(weight: Tensor, bias: Optional[Tensor], norm: nn.LayerNorm):
+        """LayerNorm folded into the Linear that consumes it:  LN(x) W^T + b = rstd (x W'^T - mean s) + t with
+        W' = W diag(gamma) (bf16, what the tensor cores multiply), s = row sums of that bf16 W', t = W beta + b."""
+        w = weight.detach().float()
+        wg = (w * norm.weight.detach().float()[None, :]).to(torch.bfloat16).contiguous()
+        t = w @ norm.bias.detach().float()
+        if bias is not None:
+            t = t + bias.detach().float()
+        return wg, t.contiguous()
 
     def _build_pack(self):
         out = {}
         for i, n in enumerate((self.norm1, self.norm2, self.norm3), 1):
             out[f"g{i}"], out[f"b{i}"] = _f32(n.weight), _f32(n.bias)
+        a1 = self.attn1
+        if a1.to_q.weight.shape[1] == a1.to_k.weight.shape[1]:
+            wqkv = torch.cat([a1.to_q.weight, a1.to_k.weight, a1.to_v.weight], dim=0)
+            out["qkv_w"], out["qkv_t"] = self._fold(wqkv, None, self.norm1)
+            out["qkv_s"] = out["qkv_w"].float().sum(dim=1).contiguous()
+        out["q2_w"], out["q2_t"] = self._fold(self.attn2.to_q.weight, None, self.norm2)
+        out["q2_s"] = out["q2_w"].float().sum(dim=1).contiguous()
+        proj = self.ff.net[0].proj
+        wg, t = self._fold(proj.weight, proj.bias, self.norm3)
+        out["ff_w"], out["ff_t"] = ops.interleave_geglu(wg, t)
+        out["ff_s"] = out["ff_w"].float().sum(dim=1).contiguous()
         return out
 
-    def forward_tokens(self, x: Tensor, context=None, key_mask: Optional[Tensor] = None) -> Tensor:
-        """x bf16 [B, N, C] -> bf16 [B, N, C]; residual adds ride in the GEMM epilogues."""
+    def forward_tokens(self, x: Tensor, context=None, key_mask: Optional[Tensor] = None,
+                       x_stats: Optional[Tensor] = None) -> Tensor:
+        """x bf16 [B, N, C] -> bf16 [B, N, C].  Residual adds ride in the GEMM epilogues; the three LayerNorms are
+        folded into the GEMMs that consume them: the GEMM that PRODUCES the residual stream emits per-row sum /
+        sum-of-squares partials in its epilogue (`x_stats` for the incoming x, from proj_in), and the consumer applies
+        rstd * (acc - mean * colsum) + t.  No LayerNorm kernel, no normalised copy of the activations."""
         b, n, c = x.shape
         p = self.packed()
         x2d = x.view(b * n, c)
-        n1 = ops.layernorm(x2d, p["g1"], p["b1"], self.norm1.eps)
-        x1 = self.attn1.self_attention_tokens(n1.view(b, n, c), key_mask, x2d)                  # :277
-        n2 = ops.layernorm(x1, p["g2"], p["b2"], self.norm2.eps)
+        a1, a2 = self.attn1, self.attn2
+        # ---- x1 = attn1(norm1(x)) + x                                                             :277
+        if x_stats is not None and "qkv_w" in p:
+            qkv = ops.linear_ln(x2d, x_stats, p["qkv_w"], p["qkv_s"], p["qkv_t"], self.norm1.eps)
+        else:
+            n1 = ops.layernorm(x2d, p["g1"], p["b1"], self.norm1.eps)
+            qkv = ops.linear(n1, a1.packed()["wqkv"], None, None, False)
+        x1, st1 = a1.out_projection(a1.attend_fused_qkv(qkv.view(b, n, -1), key_mask), x2d, True)
+        # ---- x2 = attn2(norm2(x1), context) + x1                                                  :280-281
         if exists(context):
-            q = self.attn2.project_query(n2.view(b, n, c))
-            comps = {"x": x1.view(b, n, c), "q": q, "to_k": self.attn2.to_k, "infeat_size": self.attn2.infeat_size}
+            q = ops.linear_ln(x1, st1, p["q2_w"], p["q2_s"], p["q2_t"], self.norm2.eps).view(b, n, -1)
+            comps = {"x": x1.view(b, n, c), "q": q, "to_k": a2.to_k, "infeat_size": a2.infeat_size}
             v_context, k_context, placeholder2indices = resolve_context(context, comps)
-            self.attn2._check_modes(placeholder2indices, True)
-            x2 = self.attn2.cross_attention_tokens(q, v_context, k_context, x1)                 # :280-281
+            a2._check_modes(placeholder2indices, True)
+            x2, st2 = a2.cross_attention_tokens(q, v_context, k_context, x1, True)
         else:                                                                                   # attn2 degenerates to self-attention
-            x2 = self.attn2.self_attention_tokens(n2.view(b, n, c), None, x1)
-        n3 = ops.layernorm(x2, p["g3"], p["b3"], self.norm3.eps)
-        return self.ff.forward_tokens(n3, x2).view(b, n, c)                                     # :283
+            n2 = ops.layernorm(x1, p["g2"], p["b2"], self.norm2.eps)
+            qkv2 = ops.linear(n2, a2.packed()["wqkv"], None, None, False)
+            x2, st2 = a2.out_projection(a2.attend_fused_qkv(qkv2.view(b, n, -1), None), x1, True)
+        # ---- ff(norm3(x2)) + x2                                                                   :283
+        self.ff._check_dropout()
+        g = ops.linear_ln_geglu(x2, st2, p["ff_w"], p["ff_s"], p["ff_t"], self.norm3.eps)
+        fp = self.ff.packed()
+        return ops.linear(g, fp["w2"], fp["b2"], x2, False).view(b, n, c)
 
     def forward(self, x: Tensor, context=None, mask: Optional[Tensor] = None) -> Tensor:
         b, n, _ = x.shape
@@ -354,7 +409,7 @@ class SpatialTransformer(nn.Module, _PackedWeights):
         else:
             x_in = x.float().contiguous()                                                        # fp32 NCHW
         t = ops.groupnorm_tokens(x_in, p["gn_g"], p["gn_b"], self.norm.num_groups, self.norm.eps)   # :325
-        t = ops.linear(t.view(b * n, c), p["wi"], p["bi"], None, False)                          # :326-327
+        t, t_stats = ops.linear_stats(t.view(b * n, c), p["wi"], p["bi"], None)                  # :326-327
         inner = t.shape[1]
         t = t.view(b, n, inner)
         key_mask = None
@@ -363,7 +418,8 @@ class SpatialTransformer(nn.Module, _PackedWeights):
             key_mask = key_mask_from_image_mask(mask2, b, n)
         for block in self.transformer_blocks:
             block.attn2.infeat_size = (h, w)                                                     # :330
-            t = block.forward_tokens(t, context, key_mask)
+            t = block.forward_tokens(t, context, key_mask, t_stats)
+            t_stats = None                                   # deeper blocks (depth > 1) normalise their own input
         if self.save_feat:                                                                       # :337-338
             self.feat = t.view(b, h, w, inner).permute(0, 3, 1, 2)
         t2d = t.view(b * n, inner)

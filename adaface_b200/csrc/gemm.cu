@@ -286,9 +286,14 @@ struct GemmTmaDev {
   int M, N, K;
   int has_res;
   int num_m_blocks, num_n_blocks, num_k_blocks;
+  float* stats_out;          // [M][2 * num_n_blocks][2] or NULL
+  const float* ln_stats;     // [M][ln_parts][2] or NULL
+  const float* ln_colsum;    // [N]
+  int ln_parts;
+  float ln_eps;
 };
 
-template <int BN, bool GEGLU>
+template <int BN, bool GEGLU, bool kLn, bool kStats>
 __global__ void __launch_bounds__(kTmaThreads, 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_res,
@@ -444,6 +449,24 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       const int n_blk = tile % p.num_n_blocks;
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
+      const int m_row = m_blk * kBM + row;
+      float ln_mean = 0.f, ln_rstd = 1.f;
+      if (kLn && m_row < p.M) {
+        // LayerNorm statistics of row m of A from the producer GEMM's partial sums; read BEFORE waiting for the
+        // accumulator so that the latency hides behind this tile's MMAs (parts is even: two partials per 16 bytes)
+        const float4* sp = reinterpret_cast<const float4*>(p.ln_stats + static_cast<long long>(m_row) * p.ln_parts * 2);
+        float s1 = 0.f, s2 = 0.f;
+        const int nq = p.ln_parts >> 1;
+#pragma unroll 4
+        for (int i = 0; i < nq; ++i) {
+          const float4 t = __ldg(sp + i);
+          s1 += t.x + t.z;
+          s2 += t.y + t.w;
+        }
+        const float inv_k = 1.0f / static_cast<float>(p.K);
+        ln_mean = s1 * inv_k;
+        ln_rstd = rsqrtf(fmaxf(s2 * inv_k - ln_mean * ln_mean, 0.f) + p.ln_eps);
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       if (leader) {
@@ -455,6 +478,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       mbar_wait(&res_full[sb], use & 1);
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
       bool released = false;
+      const float ln_nm = -ln_mean * ln_rstd;      // rstd * (acc - mean * cs) = rstd * acc + ln_nm * cs
+      float st_s1 = 0.f, st_s2 = 0.f;
 #pragma unroll 1
       for (int ch = ch_lo; ch < ch_hi; ++ch) {
         const int n_out0 = (GEGLU ? n_blk * (BN / 2) : n_blk * BN) + ch * 32;     // first output column of this box
@@ -473,13 +498,28 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             released = true;
           }
           const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_acc0);
+          if constexpr (kLn) {
+            const float4* c4 = reinterpret_cast<const float4*>(p.ln_colsum + n_acc0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 ca = __ldg(c4 + j), cg = __ldg(c4 + 8 + j);
+              ra[4 * j + 0] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 0]), ln_nm * ca.x));
+              ra[4 * j + 1] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 1]), ln_nm * ca.y));
+              ra[4 * j + 2] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 2]), ln_nm * ca.z));
+              ra[4 * j + 3] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 3]), ln_nm * ca.w));
+              rg[4 * j + 0] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 0]), ln_nm * cg.x));
+              rg[4 * j + 1] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 1]), ln_nm * cg.y));
+              rg[4 * j + 2] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 2]), ln_nm * cg.z));
+              rg[4 * j + 3] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 3]), ln_nm * cg.w));
+            }
+          }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 ba = __ldg(b4 + j), bg = __ldg(b4 + 8 + j);
-            v[4 * j + 0] = (__uint_as_float(ra[4 * j + 0]) + ba.x) * gelu_erf(__uint_as_float(rg[4 * j + 0]) + bg.x);
-            v[4 * j + 1] = (__uint_as_float(ra[4 * j + 1]) + ba.y) * gelu_erf(__uint_as_float(rg[4 * j + 1]) + bg.y);
-            v[4 * j + 2] = (__uint_as_float(ra[4 * j + 2]) + ba.z) * gelu_erf(__uint_as_float(rg[4 * j + 2]) + bg.z);
-            v[4 * j + 3] = (__uint_as_float(ra[4 * j + 3]) + ba.w) * gelu_erf(__uint_as_float(rg[4 * j + 3]) + bg.w);
+            v[4 * j + 0] = (__uint_as_float(ra[4 * j + 0]) + ba.x) * gelu_erf_fast(__uint_as_float(rg[4 * j + 0]) + bg.x);
+            v[4 * j + 1] = (__uint_as_float(ra[4 * j + 1]) + ba.y) * gelu_erf_fast(__uint_as_float(rg[4 * j + 1]) + bg.y);
+            v[4 * j + 2] = (__uint_as_float(ra[4 * j + 2]) + ba.z) * gelu_erf_fast(__uint_as_float(rg[4 * j + 2]) + bg.z);
+            v[4 * j + 3] = (__uint_as_float(ra[4 * j + 3]) + ba.w) * gelu_erf_fast(__uint_as_float(rg[4 * j + 3]) + bg.w);
           }
         } else {
           uint32_t r[32];
@@ -493,6 +533,17 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           }
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if constexpr (kLn) {
+            const float4* c4 = reinterpret_cast<const float4*>(p.ln_colsum + n_acc0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 cs = __ldg(c4 + j);
+              v[4 * j + 0] = fmaf(ln_rstd, v[4 * j + 0], ln_nm * cs.x);
+              v[4 * j + 1] = fmaf(ln_rstd, v[4 * j + 1], ln_nm * cs.y);
+              v[4 * j + 2] = fmaf(ln_rstd, v[4 * j + 2], ln_nm * cs.z);
+              v[4 * j + 3] = fmaf(ln_rstd, v[4 * j + 3], ln_nm * cs.w);
+            }
+          }
           if (p.bias != nullptr) {
             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_acc0);
 #pragma unroll
@@ -523,10 +574,18 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           }
         }
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
-          *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4)) =
-              make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
-                         pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+        for (int c = 0; c < 4; ++c) {
+          const uint4 pk = make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
+                                      pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+          *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4)) = pk;
+          if constexpr (!GEGLU && kStats) {
+            // statistics of exactly what the consumer will read: the bf16-rounded values
+            const float2 a = unpack_bf16x2(pk.x), b = unpack_bf16x2(pk.y), cc = unpack_bf16x2(pk.z), d = unpack_bf16x2(pk.w);
+            st_s1 += ((a.x + a.y) + (b.x + b.y)) + ((cc.x + cc.y) + (d.x + d.y));
+            st_s2 = fmaf(a.x, a.x, st_s2); st_s2 = fmaf(a.y, a.y, st_s2); st_s2 = fmaf(b.x, b.x, st_s2); st_s2 = fmaf(b.y, b.y, st_s2);
+            st_s2 = fmaf(cc.x, cc.x, st_s2); st_s2 = fmaf(cc.y, cc.y, st_s2); st_s2 = fmaf(d.x, d.x, st_s2); st_s2 = fmaf(d.y, d.y, st_s2);
+          }
+        }
         fence_proxy_async_smem();
         named_bar_sync(1 + grp, 128);
         if (leader) tma_store_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
@@ -536,6 +595,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       }
+      if (!GEGLU && kStats && m_row < p.M)
+        reinterpret_cast<float2*>(p.stats_out)[static_cast<long long>(m_row) * (2 * p.num_n_blocks) + 2 * n_blk + grp] =
+            make_float2(st_s1, st_s2);
       if (leader) bulk_commit_group();
       if (++acc == 2) {
         acc = 0;
@@ -557,8 +619,8 @@ int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows,
   return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, Swizzle::B64);
 }
 
-template <int BN, bool GEGLU>
-int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
+template <int BN, bool GEGLU, bool kLn, bool kStats>
+int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   using C = TCfg<BN, GEGLU>;
   CUtensorMap tm_a, tm_w, tm_out, tm_res;
   {
@@ -591,7 +653,12 @@ int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
   p.num_m_blocks = static_cast<int>((a.m + kBM - 1) / kBM);
   p.num_n_blocks = static_cast<int>((a.n + BN - 1) / BN);
   p.num_k_blocks = static_cast<int>((a.k + kBK - 1) / kBK);
-  auto kern = gemm_bf16_tma_kernel<BN, GEGLU>;
+  p.stats_out = a.row_stats_out;
+  p.ln_stats = a.ln_stats;
+  p.ln_colsum = a.ln_colsum;
+  p.ln_parts = a.ln_parts;
+  p.ln_eps = a.ln_eps;
+  auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats>;
   static bool attr_set = false;
   if (!attr_set) {
     AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -603,6 +670,19 @@ int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+template <int BN, bool GEGLU>
+int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
+  const bool ln = a.ln_stats != nullptr, st = a.row_stats_out != nullptr;
+  if constexpr (GEGLU) {
+    return ln ? launch_tma_impl<BN, true, true, false>(a, stream) : launch_tma_impl<BN, true, false, false>(a, stream);
+  } else {
+    if (ln && st) AFB_FAIL(2, "afb_gemm_bf16: folded LayerNorm and row statistics in one GEMM are not built");
+    if (ln) return launch_tma_impl<BN, false, true, false>(a, stream);
+    if (st) return launch_tma_impl<BN, false, false, true>(a, stream);
+    return launch_tma_impl<BN, false, false, false>(a, stream);
+  }
 }
 
 template <int BN, int EPI>
@@ -677,6 +757,14 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
   AFB_REQUIRE(a.n % 32 == 0, "afb_gemm_bf16: N=%lld must be a multiple of 32", (long long)a.n);
   AFB_REQUIRE((reinterpret_cast<uintptr_t>(a.out) & 15) == 0, "afb_gemm_bf16: out must be 16-byte aligned");
   AFB_REQUIRE(a.bias == nullptr || (reinterpret_cast<uintptr_t>(a.bias) & 15) == 0, "afb_gemm_bf16: bias must be 16-byte aligned");
+  if (a.ln_stats != nullptr) {
+    AFB_REQUIRE(a.ln_colsum != nullptr && a.ln_parts > 0 && a.ln_parts <= 64, "afb_gemm_bf16: folded LayerNorm needs ln_colsum and 1..64 ln_parts");
+    AFB_REQUIRE(a.ln_parts % 2 == 0 && (reinterpret_cast<uintptr_t>(a.ln_stats) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(a.ln_colsum) & 15) == 0,
+                "afb_gemm_bf16: ln_parts must be even, ln_stats and ln_colsum 16-byte aligned");
+  }
+  AFB_REQUIRE(a.row_stats_out == nullptr || (reinterpret_cast<uintptr_t>(a.row_stats_out) & 7) == 0,
+              "afb_gemm_bf16: row_stats_out must be 8-byte aligned");
   switch (a.epilogue) {
     case AFB_EPI_STORE:
       AFB_REQUIRE(a.ldo >= a.n && a.ldo % 8 == 0, "afb_gemm_bf16: ldo must be >= N and a multiple of 8");
@@ -688,16 +776,26 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
         if (a.n % 160 == 0) return launch_tma<160, false>(a, stream);
         return launch_tma<128, false>(a, stream);
       }
+      AFB_REQUIRE(a.row_stats_out == nullptr && a.ln_stats == nullptr,
+                  "afb_gemm_bf16: row statistics / folded LayerNorm need bf16 output and a bf16 (or no) residual");
       return dispatch_bn<AFB_EPI_STORE>(a, stream);
     case AFB_EPI_GEGLU:
       AFB_REQUIRE(a.ldo >= a.n / 2 && a.ldo % 8 == 0, "afb_gemm_bf16: GEGLU ldo must be >= N/2 and a multiple of 8");
       AFB_REQUIRE(a.residual == nullptr, "afb_gemm_bf16: GEGLU epilogue takes no residual");
       AFB_REQUIRE(a.n % 64 == 0 && a.bias != nullptr, "afb_gemm_bf16: GEGLU needs N %% 64 == 0 and a bias");
+      AFB_REQUIRE(a.row_stats_out == nullptr, "afb_gemm_bf16: the GEGLU epilogue does not emit row statistics");
       return launch_tma<128, true>(a, stream);
     case AFB_EPI_NCHW:
       AFB_REQUIRE(a.hw > 0 && a.m % a.hw == 0, "afb_gemm_bf16: NCHW epilogue needs hw > 0 dividing M");
+      AFB_REQUIRE(a.row_stats_out == nullptr && a.ln_stats == nullptr,
+                  "afb_gemm_bf16: row statistics / folded LayerNorm are not available with the NCHW epilogue");
       return dispatch_bn<AFB_EPI_NCHW>(a, stream);
     default:
       AFB_FAIL(2, "afb_gemm_bf16: unknown epilogue %d", a.epilogue);
   }
+}
+
+extern "C" int afb_gemm_stats_parts(int64_t n) {
+  const int64_t bn = (n % 160 == 0) ? 160 : 128;      // the tile width afb_gemm_bf16 picks for a STORE epilogue
+  return static_cast<int>(2 * ((n + bn - 1) / bn));
 }

@@ -140,8 +140,14 @@ def _(x, gamma, beta, eps):
 
 # ------------------------------------------------------------------------------------------- GEMMs
 def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], epilogue: int,
-          ldo: int, ldr: int, hw: int = 0) -> None:
-    _need_cuda(a, w, out, bias, residual)
+          ldo: int, ldr: int, hw: int = 0, stats_out: Optional[Tensor] = None, ln_stats: Optional[Tensor] = None,
+          ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0) -> None:
+    _need_cuda(a, w, out, bias, residual, stats_out, ln_stats, ln_colsum)
+    if ln_stats is not None:
+        if ln_colsum is None or ln_stats.dtype != torch.float32 or ln_colsum.dtype != torch.float32 \
+                or not ln_stats.is_contiguous() or ln_stats.dim() != 3 or ln_stats.shape[0] != a.shape[0] \
+                or ln_stats.shape[2] != 2 or ln_colsum.numel() != w.shape[0]:
+            raise ValueError("gemm: ln_stats must be fp32 [M, parts, 2] and ln_colsum fp32 [N]")
     if a.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or a.stride(-1) != 1 or w.stride(-1) != 1:
         raise ValueError("gemm: bf16 operands with contiguous K expected")
     if bias is not None and bias.dtype != torch.float32:
@@ -150,10 +156,12 @@ def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: O
                     m=a.shape[0], n=w.shape[0], k=a.shape[1], lda=a.stride(0), ldw=w.stride(0), ldo=ldo, ldr=ldr,
                     epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
                     residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
-                    else _lib.DT_BF16, hw=hw)
+                    else _lib.DT_BF16, hw=hw, row_stats_out=_ptr(stats_out), ln_stats=_ptr(ln_stats),
+                    ln_colsum=_ptr(ln_colsum), ln_parts=0 if ln_stats is None else ln_stats.shape[1], ln_eps=ln_eps)
     m, n, k = a.shape[0], w.shape[0], a.shape[1]
     _run("gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
-         nbytes=2.0 * (m * k + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}")
+         nbytes=2.0 * (m * k + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
+         + ("r" if residual is not None else ""))
 
 
 @torch.library.custom_op("adaface_b200::linear", mutates_args=())
@@ -171,6 +179,60 @@ def linear(a: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Tens
 @linear.register_fake
 def _(a, w, bias, residual, out_fp32):
     return a.new_empty((a.shape[0], w.shape[0]), dtype=torch.float32 if out_fp32 else torch.bfloat16)
+
+
+def stats_parts(n: int) -> int:
+    """Partials per row that `linear_stats` emits for n output columns (afb_gemm_stats_parts)."""
+    return int(_lib.load().afb_gemm_stats_parts(int(n)))
+
+
+@torch.library.custom_op("adaface_b200::linear_stats", mutates_args=())
+def linear_stats(a: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    """`linear` with bf16 output that also returns the per-row (sum, sum of squares) partials of what it stored,
+    fp32 [M, parts, 2]: the LayerNorm statistics of the output, for a consumer GEMM with the LayerNorm folded in."""
+    out = torch.empty((a.shape[0], w.shape[0]), dtype=torch.bfloat16, device=a.device)
+    if residual is not None and (residual.shape != out.shape or residual.stride(-1) != 1 or residual.dtype != torch.bfloat16):
+        raise ValueError("linear_stats: residual must be bf16 [M,N] with contiguous rows")
+    stats = torch.empty((a.shape[0], stats_parts(w.shape[0]), 2), dtype=torch.float32, device=a.device)
+    _gemm(a, w, out, bias, residual, _lib.EPI_STORE, out.stride(0), 0 if residual is None else residual.stride(0),
+          stats_out=stats)
+    return out, stats
+
+
+@linear_stats.register_fake
+def _(a, w, bias, residual):
+    n = w.shape[0]
+    parts = 2 * ((n + 159) // 160) if n % 160 == 0 else 2 * ((n + 127) // 128)
+    return a.new_empty((a.shape[0], n), dtype=torch.bfloat16), a.new_empty((a.shape[0], parts, 2), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::linear_ln", mutates_args=())
+def linear_ln(a: Tensor, stats: Tensor, w_gamma: Tensor, colsum: Tensor, bias: Tensor, eps: float) -> Tensor:
+    """LayerNorm(a) @ W^T + b with the LayerNorm folded into the GEMM: w_gamma = W * gamma (bf16), colsum[n] =
+    sum_k w_gamma[n,k], bias[n] = sum_k W[n,k] * beta[k] + b[n]; `stats` are a's row partials from `linear_stats`.
+    out = rstd * (a @ w_gamma^T - mean * colsum) + bias (attention.py:269-283 + :157-159)."""
+    out = torch.empty((a.shape[0], w_gamma.shape[0]), dtype=torch.bfloat16, device=a.device)
+    _gemm(a, w_gamma, out, bias, None, _lib.EPI_STORE, out.stride(0), 0, ln_stats=stats, ln_colsum=colsum, ln_eps=eps)
+    return out
+
+
+@linear_ln.register_fake
+def _(a, stats, w_gamma, colsum, bias, eps):
+    return a.new_empty((a.shape[0], w_gamma.shape[0]), dtype=torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::linear_ln_geglu", mutates_args=())
+def linear_ln_geglu(a: Tensor, stats: Tensor, w_interleaved: Tensor, colsum: Tensor, bias: Tensor, eps: float) -> Tensor:
+    """GEGLU(LayerNorm(a)) with the LayerNorm folded in (rows, colsum and bias interleaved by `interleave_geglu`)."""
+    out = torch.empty((a.shape[0], w_interleaved.shape[0] // 2), dtype=torch.bfloat16, device=a.device)
+    _gemm(a, w_interleaved, out, bias, None, _lib.EPI_GEGLU, out.stride(0), 0, ln_stats=stats, ln_colsum=colsum,
+          ln_eps=eps)
+    return out
+
+
+@linear_ln_geglu.register_fake
+def _(a, stats, w_interleaved, colsum, bias, eps):
+    return a.new_empty((a.shape[0], w_interleaved.shape[0] // 2), dtype=torch.bfloat16)
 
 
 @torch.library.custom_op("adaface_b200::linear_geglu", mutates_args=())

@@ -87,8 +87,23 @@ typedef struct afb_gemm_args {
   int out_dtype;            /* enum afb_dtype (STORE only; GEGLU is bf16, NCHW is fp32)                      */
   int residual_dtype;       /* enum afb_dtype */
   int hw;                   /* tokens per sample, AFB_EPI_NCHW only                                          */
+  /* LayerNorm folded around the GEMM (attention.py:269-283: norm1/2/3 feed to_q/k/v and the GEGLU projection).
+   * Producer side (STORE epilogue, bf16 out): row_stats_out != NULL makes the epilogue emit, per output row and per
+   * (column block, column half), the sum and the sum of squares of the bf16 values it stores:
+   * row_stats_out[m][afb_gemm_stats_parts(n)][2] fp32.
+   * Consumer side (STORE with bf16 out, or GEGLU): ln_stats != NULL points at such an array for the rows of A
+   * (ln_parts partials per row, rows of A have k elements); with W' = W * gamma (given as w),
+   * ln_colsum[n] = sum_k W'[n,k] and bias[n] = sum_k W[n,k] * beta[k] (+ the layer's bias), the epilogue computes
+   * rstd[m] * (acc - mean[m] * ln_colsum[n]) + bias[n] == LayerNorm(A)[m,:] . W[n,:] + bias. */
+  float* row_stats_out;
+  const float* ln_stats;
+  const float* ln_colsum;
+  int ln_parts;
+  float ln_eps;
 } afb_gemm_args;
 int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
+/* number of (sum, sum of squares) partials per row that a STORE GEMM with n output columns emits */
+int afb_gemm_stats_parts(int64_t n);
 
 /* ---- K5/K8: fused softmax(Q K^T * scale) V, online softmax, S/O accumulators in TMEM.
  * Replaces attention.py:198-242 (self-attention with optional key mask, and cross-attention over the

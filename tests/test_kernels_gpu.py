@@ -137,6 +137,39 @@ def test_linear_geglu(ops, cuda_device, m, c):
     assert rel_l2(out.float(), ref) < 5e-3
 
 
+@pytest.mark.parametrize("m,c", [(256, 320), (200, 640), (77, 1280)])
+def test_linear_layernorm_fold(ops, cuda_device, m, c):
+    """LayerNorm folded around the GEMMs (attention.py:269-283): the producer GEMM emits per-row sum / sum of squares
+    of the bf16 values it stores, the consumer applies rstd * (acc - mean * colsum) + t.  Checked against
+    torch.layer_norm + matmul in fp32 on the SAME bf16 activations."""
+    d = cuda_device
+    a0 = _r("lnf.a0", (m, c)).to(torch.bfloat16)
+    w0 = _r("lnf.w0", (c, c), c ** -0.5).to(torch.bfloat16)
+    b0 = 0.5 + 0.2 * _r("lnf.b0", (c,))                                  # a non-zero row mean on purpose
+    res = _r("lnf.res", (m, c)).to(torch.bfloat16)
+    x, stats = ops.linear_stats(a0.to(d), w0.to(d), b0.to(d), res.to(d))
+    assert stats.shape == (m, ops.stats_parts(c), 2)
+    xf = x.float().cpu()
+    assert rel_l2(x, a0.float() @ w0.float().t() + b0 + res.float()) < 5e-3
+    assert torch.allclose(stats[..., 0].sum(1).cpu(), xf.sum(-1), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(stats[..., 1].sum(1).cpu(), (xf * xf).sum(-1), rtol=1e-4, atol=1e-2)
+
+    gamma, beta, eps = 1.0 + 0.3 * _r("lnf.g", (c,)), 0.2 * _r("lnf.be", (c,)), 1e-5
+    ln = torch.nn.functional.layer_norm(xf, (c,), gamma, beta, eps)
+    # plain consumer (to_q / to_k / to_v)
+    w = _r("lnf.w", (3 * c, c), c ** -0.5)
+    wg = (w * gamma[None, :]).to(torch.bfloat16)
+    out = ops.linear_ln(x, stats, wg.to(d), wg.float().sum(1).to(d), (w @ beta).to(d), eps)
+    assert rel_l2(out.float(), ln @ w.t()) < 6e-3
+    # gated consumer (GEGLU projection)
+    w2, bias2 = _r("lnf.w2", (8 * c, c), c ** -0.5), 0.1 * _r("lnf.b2", (8 * c,))
+    wg2 = (w2 * gamma[None, :]).to(torch.bfloat16)
+    wi, ti = ops.interleave_geglu(wg2.to(d), (w2 @ beta + bias2).to(d))
+    out2 = ops.linear_ln_geglu(x, stats, wi, wi.float().sum(1).contiguous(), ti, eps)
+    val, gate = (ln @ w2.t() + bias2).chunk(2, dim=-1)
+    assert rel_l2(out2.float(), val * port.gelu_erf(gate)) < 8e-3
+
+
 @pytest.mark.parametrize("b,c,hw", [(2, 320, 16), (3, 640, 8), (2, 1280, 8)])
 def test_linear_nchw(ops, cuda_device, b, c, hw):
     n_tok = hw * hw
