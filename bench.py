@@ -331,15 +331,28 @@ def run_ours(args):
     st_ms = sum(v["ms"] for v in groups.values())
     pk = peaks()
     st_alg_flops = unet_st_flops() * 2 * b
-    top = max((k for k in groups if groups[k]["flops"] > 0), key=lambda k: groups[k]["ms"])
-    tg = groups[top]
+    # dominant kernel = the single launch configuration (kernel, shape) with the most device time in a step among
+    # the tensor-bound ones; all its launches are identical, so "average launch duration" is well defined
+    by_shape = {}
+    for r in recs:
+        if r["flops"] > 0:
+            e = by_shape.setdefault((r["name"], r["tag"]), {"ms": 0.0, "flops": 0.0, "n": 0})
+            e["ms"] += r["ms"]; e["flops"] += r["flops"]; e["n"] += 1
+    (top, top_tag), tg = max(by_shape.items(), key=lambda kv: kv[1]["ms"])
     achieved = tg["flops"] / (tg["ms"] * 1e-3) / 1e12
-    roofline = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops_sustained"],
-                "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops_sustained"], "traffic": None,
+    traffic = None
+    try:    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_dram_traffic.json"))).get(f"{top}:{top_tag}")
+    except Exception:
+        pass
+    roofline = {"kernel": f"{top}[{top_tag}]", "bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops_sustained"],
+                "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops_sustained"], "traffic": traffic,
+                "traffic_unit": "bytes per launch (ncu dram read + write)" if traffic is not None else None,
                 "peak_source": f"{pk['source']} (MEASURED_PEAKS.json bf16_tflops_sustained: kernel timed inside a long step)",
-                "launches_per_step": tg["launches"], "ms_per_step": tg["ms"],
-                "flops_per_step": tg["flops"], "note": "algorithmic FLOPs (unpadded head dim / context) of the launches of "
-                "this kernel in one step / their CUDA-event time in one instrumented eager step"}
+                "launches_per_step": tg["n"], "avg_launch_us": 1e3 * tg["ms"] / tg["n"], "ms_per_step": tg["ms"],
+                "flops_per_launch": tg["flops"] / tg["n"],
+                "note": "algorithmic FLOPs (unpadded head dim / context) of one launch / its average CUDA-event time "
+                        "in one instrumented eager step; per-group figures for every kernel are under 'kernels'"}
     breakdown = {k: {"ms": round(v["ms"], 4), "launches": v["launches"],
                      "tflops": (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["flops"] else None,
                      "gbs": (v["bytes"] / (v["ms"] * 1e-3) / 1e9) if not v["flops"] else None} for k, v in groups.items()}
