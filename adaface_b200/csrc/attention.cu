@@ -66,6 +66,10 @@ struct AttnCfg {
   static constexpr int kKVTileBytes = kAtoms * kBlockKV * 128;  // one of K or V
   static constexpr int kPBytes = kBlockQ * 128;                 // one query tile's P (64 keys = one atom)
   static constexpr int kStages = (D <= 40) ? 4 : (D <= 80 ? 3 : 2);
+#ifndef AFB_ATTN_POLY_EVERY
+#define AFB_ATTN_POLY_EVERY 6
+#endif
+  static constexpr int kPolyEvery = (D <= 40) ? AFB_ATTN_POLY_EVERY : 0;          // every kPolyEvery-th pair of exponentials on the FMA pipe
   static constexpr int kSmemBytes = kQTiles * (kQTileBytes + kPBytes) + kStages * 2 * kKVTileBytes;
   static constexpr int kTmemCols = 512;                          // one CTA per SM owns all of TMEM
   static constexpr int kTmemS = 0;                               // S_t: 64 columns each
@@ -74,6 +78,29 @@ struct AttnCfg {
   static_assert(kSmemBytes <= 226 * 1024, "shared memory budget");
   static_assert(kSmemBytes > 114 * 1024, "two resident CTAs would deadlock on the 512-column TMEM allocation");
 };
+
+// 2^x for a packed pair on the FMA / ALU pipes instead of MUFU (x <= ~8; anything below -126 flushes towards 2^-126):
+// round-to-nearest split x = n + f, |f| <= 0.5, via the 1.5 * 2^23 magic constant; 2^f by a degree-3 minimax
+// polynomial (relative error 7.5e-5, far below the bf16 rounding of P); 2^n by adding n to the exponent field.
+// The d = 40 kernel is MUFU-bound (one ex2 per 80 tensor FLOPs), so a fixed share of the exponentials goes this way.
+__device__ __forceinline__ uint64_t exp2_poly_x2(uint64_t x2) {
+  float lo, hi;
+  unpack_f32x2(x2, lo, hi);
+  x2 = pack_f32x2(fmaxf(lo, -126.0f), fmaxf(hi, -126.0f));
+  const uint64_t magic = pack_f32x2(12582912.0f, 12582912.0f);
+  const uint64_t t2 = fadd2(x2, magic);
+  const uint64_t n2 = fadd2(t2, pack_f32x2(-12582912.0f, -12582912.0f));
+  const uint64_t f2 = ffma2(n2, pack_f32x2(-1.0f, -1.0f), x2);
+  uint64_t p2 = ffma2(f2, pack_f32x2(0.0551716648f, 0.0551716648f), pack_f32x2(0.2426111251f, 0.2426111251f));
+  p2 = ffma2(p2, f2, pack_f32x2(0.6932609677f, 0.6932609677f));
+  p2 = ffma2(p2, f2, pack_f32x2(0.9999280572f, 0.9999280572f));
+  float tl, th, pl, ph;
+  unpack_f32x2(t2, tl, th);
+  unpack_f32x2(p2, pl, ph);
+  const float rl = __int_as_float(__float_as_int(pl) + (__float_as_int(tl) << 23));
+  const float rh = __int_as_float(__float_as_int(ph) + (__float_as_int(th) << 23));
+  return pack_f32x2(rl, rh);
+}
 
 template <int D, bool kHasMask>
 __global__ void __launch_bounds__(AttnCfg<D>::kThreads, 1)
@@ -376,10 +403,16 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         uint64_t x = pack_f32x2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
         x = kHasMask ? fadd2(x, nm2) : ffma2(x, sc2, nm2);
         float lo, hi;
-        unpack_f32x2(x, lo, hi);
-        lo = ex2_approx(lo);
-        hi = ex2_approx(hi);
-        const uint64_t e = pack_f32x2(lo, hi);
+        uint64_t e;
+        if (C::kPolyEvery > 0 && (i % (C::kPolyEvery > 0 ? C::kPolyEvery : 1)) == 1) {
+          e = exp2_poly_x2(x);                            // FMA-pipe exponentials: relieves MUFU
+          unpack_f32x2(e, lo, hi);
+        } else {
+          unpack_f32x2(x, lo, hi);
+          lo = ex2_approx(lo);
+          hi = ex2_approx(hi);
+          e = pack_f32x2(lo, hi);
+        }
         if (i & 1) acc1 = fadd2(acc1, e); else acc0 = fadd2(acc0, e);
         r[i] = cvt_bf16x2(lo, hi);
       }

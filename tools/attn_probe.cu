@@ -27,9 +27,11 @@ int main(int argc, char** argv) {
   cudaMemcpy(k, h.data(), nelem_k * 2, cudaMemcpyHostToDevice);
   cudaMemcpy(v, h.data(), nelem_k * 2, cudaMemcpyHostToDevice);
   const int prof_blocks = 4;
+#ifdef AFB_ATTN_PROFILE
   cudaMalloc(&afb::g_attn_prof, prof_blocks * 136 * sizeof(long long));
   cudaMemset(afb::g_attn_prof, 0, prof_blocks * 136 * sizeof(long long));
   afb::g_attn_prof_blocks = prof_blocks;
+#endif
   afb_attn_args a{};
   a.q = (const afb_bf16*)q; a.k = (const afb_bf16*)k; a.v = (const afb_bf16*)v; a.out = (afb_bf16*)o; a.key_mask = nullptr;
   a.batch = batch; a.heads = heads; a.q_len = nq; a.kv_len = nk; a.head_dim = d;
@@ -49,6 +51,9 @@ int main(int argc, char** argv) {
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   const double flops = 4.0 * batch * heads * (double)nq * nk * d;
   printf("d=%d q=%d k=%d b=%d: %.1f us / launch, %.1f TF/s\n", d, nq, nk, batch, ms / iters * 1e3, flops / (ms / iters * 1e-3) / 1e12);
+#ifndef AFB_ATTN_PROFILE
+  return 0;
+#else
   std::vector<long long> prof(prof_blocks * 136);
   cudaMemcpy(prof.data(), afb::g_attn_prof, prof.size() * sizeof(long long), cudaMemcpyDeviceToHost);
   const char* names[8] = {"wait S", "ldtm", "max", "token", "exp", "wait P buf", "P store", "loop"};
@@ -67,4 +72,5 @@ int main(int argc, char** argv) {
            m[1] / kv_tiles, m[2] / kv_tiles, m[3] / kv_tiles);
   }
   return 0;
+#endif
 }
