@@ -48,6 +48,9 @@ _SIGNATURES = {
     "afb_gemm_bf16": (_I, [C.POINTER(GemmArgs), _P]),
     "afb_gemm_stats_parts": (_I, [_I64]),
     "afb_attention_fwd": (_I, [C.POINTER(AttnArgs), _P]),
+    "afb_cross_scores": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I64, _I64, _F, _P]),
+    "afb_conv_attn_rows": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I64, _I64, _I, _I, _F, _P]),
+    "afb_softmax_pv": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I64, _I64, _P]),
     "afb_ada_pool_ws_floats": (_I64, [_I, _I, _I]),
     "afb_ada_pool_prep_ws_floats": (_I64, [_I, _I]),
     "afb_ada_pool_prep": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),

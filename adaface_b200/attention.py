@@ -201,12 +201,29 @@ class CrossAttention(nn.Module, _PackedWeights):
     def _check_modes(self, placeholder2indices, context_provided: bool):
         if self.training and self.to_out[1].p > 0:
             raise NotImplementedError("adaface_b200: dropout > 0 in training mode is not supported on the kernel path")
-        if context_provided and placeholder2indices is not None and self.use_conv_attn_kernel_size > 1:
-            # attention.py:208-216 / ldm/util.py:701-879; optional mode, off by default
-            raise NotImplementedError("adaface_b200: conv-attention rows (use_conv_attn_kernel_size > 1) are not built yet")
-        if self.save_attn_vars:
-            # attention.py:245-255; training-only capture of q / attn / attnscore
-            raise NotImplementedError("adaface_b200: save_attn_vars capture is not built yet")
+        if self.save_attn_vars and not context_provided:
+            # attention.py:245-255 on a self-attention layer would cache a [B, 8, N, N] matrix (8.6 GB at 64x64);
+            # the reference only ever reads the cross-attention layers' activations (openaimodel.py:985-1000)
+            raise NotImplementedError("adaface_b200: save_attn_vars is built for cross-attention layers only")
+
+    def _conv_attn_subjects(self, placeholder2indices):
+        """attention.py:208-216: [(inst_batch int32 [I], tok int32 [I, ks*ks])] per subject string, or []."""
+        ks = int(self.use_conv_attn_kernel_size or -1)
+        if placeholder2indices is None or ks <= 1:          # ks == 1 is a no-op in the reference (ldm/util.py:720)
+            return []
+        if ks > 4:
+            raise ValueError("use_conv_attn_kernel_size must be 2, 3 or 4 (ldm/util.py:735-744)")
+        out = []
+        for subj_string in placeholder2indices:
+            idx_b, idx_n = [torch.as_tensor(t) for t in placeholder2indices[subj_string]]
+            n_inst = int(torch.unique(idx_b).numel())
+            per = idx_b.numel() // n_inst
+            if per < ks * ks:
+                raise ValueError(f"conv attention with ks={ks} needs {ks * ks} subject tokens, the prompt has {per}")
+            inst = idx_b.reshape(n_inst, per)[:, 0]
+            tok = idx_n.reshape(n_inst, per)[:, :ks * ks]
+            out.append((inst.to(torch.int32), tok.to(torch.int32).contiguous()))
+        return out
 
     # ---- fused token-level paths used by BasicTransformerBlock (bf16 [B, N, C] in, bf16 [B*N, C] out) ----
     def self_attention_tokens(self, x: Tensor, key_mask: Optional[Tensor], residual: Optional[Tensor]) -> Tensor:
@@ -241,7 +258,7 @@ class CrossAttention(nn.Module, _PackedWeights):
         return ops.linear(x.view(b * n, c), self.packed()["wq"], None, None, False).view(b, n, -1)
 
     def cross_attention_tokens(self, q: Tensor, v_context: Tensor, k_context: Tensor,
-                               residual: Optional[Tensor], want_stats: bool = False):
+                               residual: Optional[Tensor], want_stats: bool = False, placeholder2indices=None):
         """q bf16 [B, N, C] (already projected); contexts [B, T, ctx_dim] -> to_out(attn) (+ residual)."""
         b, n, inner = q.shape
         p = self.packed()
@@ -254,7 +271,21 @@ class CrossAttention(nn.Module, _PackedWeights):
             kc, vc = as_bf16_tokens(k_context), as_bf16_tokens(v_context)
             k = ops.linear(kc.view(-1, kc.shape[2]), p["wk"], None, None, False).view(b, kc.shape[1], inner)
             v = ops.linear(vc.view(-1, vc.shape[2]), p["wv"], None, None, False).view(b, vc.shape[1], inner)
-        a = ops.attention(q, k, v, self.heads, self.scale, None)
+        subjects = self._conv_attn_subjects(placeholder2indices)
+        if self.save_attn_vars or subjects:
+            # optional modes that need the score matrix itself: explicit scores -> row replacement -> softmax . v
+            sim = ops.cross_scores(q, k, self.heads, self.scale)                                # :199
+            for inst, tok in subjects:                                                          # :208-216
+                ops.conv_attn_rows(sim, q, k, inst.to(q.device), tok.to(q.device), self.infeat_size[0],
+                                   self.infeat_size[1], int(self.use_conv_attn_kernel_size), self.scale)
+            a, attn = ops.softmax_pv(sim, v, self.save_attn_vars)                               # :238-242
+            if self.save_attn_vars:                                                             # :245-255
+                d = inner // self.heads
+                self.cached_activations = {
+                    "q": q.view(b, n, self.heads, d).permute(0, 2, 1, 3).float() * math.sqrt(self.scale),
+                    "attn": attn, "attnscore": sim}
+        else:
+            a = ops.attention(q, k, v, self.heads, self.scale, None)
         return self.out_projection(a.view(b * n, inner), residual, want_stats)
 
     def forward(self, x: Tensor, context=None, mask: Optional[Tensor] = None) -> Tensor:
@@ -271,7 +302,7 @@ class CrossAttention(nn.Module, _PackedWeights):
                 # the reference would mask whole key columns of the 77-token context (NaN hazard noted at
                 # attention.py:218-222); a key mask is only meaningful for self-attention
                 raise ValueError("CrossAttention: mask is only supported for self-attention (context=None)")
-            out = self.cross_attention_tokens(q, v_context, k_context, None)
+            out = self.cross_attention_tokens(q, v_context, k_context, None, False, placeholder2indices)
         return like_input(out, x).view(b, n, -1)
 
 
@@ -347,7 +378,7 @@ class BasicTransformerBlock(nn.Module, _PackedWeights):
             comps = {"x": x1.view(b, n, c), "q": q, "to_k": a2.to_k, "infeat_size": a2.infeat_size}
             v_context, k_context, placeholder2indices = resolve_context(context, comps)
             a2._check_modes(placeholder2indices, True)
-            x2, st2 = a2.cross_attention_tokens(q, v_context, k_context, x1, True)
+            x2, st2 = a2.cross_attention_tokens(q, v_context, k_context, x1, True, placeholder2indices)
         else:                                                                                   # attn2 degenerates to self-attention
             n2 = ops.layernorm(x1, p["g2"], p["b2"], self.norm2.eps)
             qkv2 = ops.linear(n2, a2.packed()["wqkv"], None, None, False)

@@ -308,6 +308,68 @@ def _(q, k, v, heads, scale, key_mask):
     return q.new_empty(q.shape, dtype=torch.bfloat16)
 
 
+# ------------------------------------------------------------------------------------------- K8b (explicit cross-attention)
+@torch.library.custom_op("adaface_b200::cross_scores", mutates_args=())
+def cross_scores(q: Tensor, k: Tensor, heads: int, scale: float) -> Tensor:
+    """sim fp32 [B, heads, Nq, Nk] = scale * q k^T per head (attention.py:199), q/k bf16 [B, L, heads*d]."""
+    _need_cuda(q, k)
+    ldq, ldk = _ld3(q, "q"), _ld3(k, "k")
+    b, nq, c = q.shape
+    sim = torch.empty((b, heads, nq, k.shape[1]), dtype=torch.float32, device=q.device)
+    _run("cross_scores", _lib.load().afb_cross_scores, _ptr(q), _ptr(k), _ptr(sim), b, heads, c // heads, nq, k.shape[1],
+         ldq, ldk, scale, _stream(), flops=2.0 * b * nq * k.shape[1] * c, tag=f"b{b}q{nq}k{k.shape[1]}d{c // heads}")
+    return sim
+
+
+@cross_scores.register_fake
+def _(q, k, heads, scale):
+    return q.new_empty((q.shape[0], heads, q.shape[1], k.shape[1]), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::conv_attn_rows", mutates_args=("sim",))
+def conv_attn_rows(sim: Tensor, q: Tensor, k: Tensor, inst_batch: Tensor, tok: Tensor, h: int, w: int, ks: int,
+                   scale: float) -> None:
+    """replace_rows_by_conv_attn (ldm/util.py:701-879) in place on sim [B, heads, h*w, Nk]: inst_batch int32 [I] are
+    the samples that hold the subject, tok int32 [I, ks*ks] its first ks*ks token positions."""
+    _need_cuda(sim, q, k, inst_batch, tok)
+    if sim.dtype != torch.float32 or not sim.is_contiguous() or sim.dim() != 4:
+        raise ValueError("conv_attn_rows: sim must be contiguous fp32 [B, heads, N, T]")
+    if inst_batch.dtype != torch.int32 or tok.dtype != torch.int32 or not tok.is_contiguous() \
+            or tok.shape != (inst_batch.numel(), ks * ks):
+        raise ValueError("conv_attn_rows: inst_batch int32 [I] and tok int32 [I, ks*ks] expected")
+    b, heads, n, t = sim.shape
+    if n != h * w:
+        raise ValueError("conv_attn_rows: sim rows do not match the feature map size")
+    ldq, ldk = _ld3(q, "q"), _ld3(k, "k")
+    ws = torch.empty((inst_batch.numel(), heads, n), dtype=torch.float32, device=sim.device)
+    _run("conv_attn_rows", _lib.load().afb_conv_attn_rows, _ptr(sim), _ptr(q), _ptr(k), _ptr(inst_batch), _ptr(tok), _ptr(ws),
+         b, heads, q.shape[2] // heads, h, w, t, ldq, ldk, inst_batch.numel(), ks, scale, _stream(),
+         flops=2.0 * inst_batch.numel() * n * ks * ks * q.shape[2], tag=f"i{inst_batch.numel()}n{n}ks{ks}")
+
+
+@torch.library.custom_op("adaface_b200::softmax_pv", mutates_args=())
+def softmax_pv(sim: Tensor, v: Tensor, want_attn: bool) -> Tuple[Tensor, Tensor]:
+    """(out bf16 [B, Nq, heads*d], attn fp32 [B, heads, Nq, Nk] or an empty tensor): softmax over the keys and
+    attn . v (attention.py:238-242)."""
+    _need_cuda(sim, v)
+    if sim.dtype != torch.float32 or not sim.is_contiguous() or sim.dim() != 4:
+        raise ValueError("softmax_pv: sim must be contiguous fp32 [B, heads, N, T]")
+    ldv = _ld3(v, "v")
+    b, heads, nq, t = sim.shape
+    out = torch.empty((b, nq, v.shape[2]), dtype=torch.bfloat16, device=sim.device)
+    attn = torch.empty_like(sim) if want_attn else torch.empty((0,), dtype=torch.float32, device=sim.device)
+    _run("softmax_pv", _lib.load().afb_softmax_pv, _ptr(sim), _ptr(v), _ptr(attn) if want_attn else None, _ptr(out), b, heads,
+         v.shape[2] // heads, nq, t, ldv, out.stride(1), _stream(), flops=2.0 * b * nq * t * v.shape[2],
+         tag=f"b{b}q{nq}k{t}d{v.shape[2] // heads}")
+    return out, attn
+
+
+@softmax_pv.register_fake
+def _(sim, v, want_attn):
+    out = sim.new_empty((sim.shape[0], sim.shape[2], v.shape[2]), dtype=torch.bfloat16)
+    return out, (torch.empty_like(sim) if want_attn else sim.new_empty((0,)))
+
+
 # ------------------------------------------------------------------------------------------- K12 / K13
 @torch.library.custom_op("adaface_b200::ada_pool_prep", mutates_args=())
 def ada_pool_prep(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_to_fg_q: Tensor,

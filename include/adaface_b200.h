@@ -124,6 +124,24 @@ typedef struct afb_attn_args {
 } afb_attn_args;
 int afb_attention_fwd(const afb_attn_args* args, afb_stream_t stream);
 
+/* ---- K8b: explicit (materialised) 77-token cross-attention for the optional modes of CrossAttention.forward that
+ * need the score matrix: save_attn_vars (attention.py:245-255) and the convolutional-attention row replacement
+ * (attention.py:208-216 -> ldm/util.py:701-879).  sim / attn are fp32 [B, heads, q_len, kv_len] (the reference's
+ * '(b h) i j' with b major); q/k/v/out use the head-concatenated bf16 layout of afb_attention_fwd. */
+/* sim[b,h,n,t] = scale * q[b,n,h,:] . k[b,t,h,:]   (attention.py:199) */
+int afb_cross_scores(const afb_bf16* q, const afb_bf16* k, float* sim, int batch, int heads, int head_dim, int q_len,
+                     int kv_len, int64_t ldq, int64_t ldk, float scale, afb_stream_t stream);
+/* replace_rows_by_conv_attn (ldm/util.py:701-879) with conv_attn_mix_weight = 1 and shifted attention maps, in place
+ * on sim: for instance i (sample inst_batch[i]) the ks*ks subject tokens tok[i*ks*ks + m] act as a ks x ks filter on
+ * the query image [h, w]; column tok[.. + m] of sim receives the conv output shifted by that tap's offset.
+ * conv_ws: n_inst * heads * h * w floats.  scale = the attention scale (d^-1/2); ks in {2, 3, 4}. */
+int afb_conv_attn_rows(float* sim, const afb_bf16* q, const afb_bf16* k, const int* inst_batch, const int* tok,
+                       float* conv_ws, int batch, int heads, int head_dim, int h, int w, int kv_len, int64_t ldq,
+                       int64_t ldk, int n_inst, int ks, float scale, afb_stream_t stream);
+/* attn = softmax_t(sim) (written when attn != NULL), out[b,n,h,:] = attn . v[b,:,h,:]   (attention.py:238-242) */
+int afb_softmax_pv(const float* sim, const afb_bf16* v, float* attn, afb_bf16* out, int batch, int heads, int head_dim,
+                   int q_len, int kv_len, int64_t ldv, int64_t ldo, afb_stream_t stream);
+
 /* ---- K12: AttentionalPooler.forward, eval mode.  Replaces embedding_manager.py:146-321.
  * afb_ada_pool_prep (step-invariant, :186-235): fg_q/bg_q = to_k(query embedding) with the layer's attn2.to_k
  *   weight fp32 [C, ctx_dim]; fg_q_emb fp32 [ctx_dim] (shared by the batch), bg_q_emb fp32 [B, ctx_dim];

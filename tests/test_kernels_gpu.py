@@ -237,6 +237,57 @@ def test_attention_key_mask(ops, cuda_device, c, n):
 
 
 # ---------------------------------------------------------------------------------------------- K12 / K13
+def test_explicit_cross_attention_matches_fused(ops, cuda_device):
+    """cross_scores + softmax_pv (the materialised path used by save_attn_vars / conv attention) against the oracle
+    and against the fused tcgen05 kernel."""
+    d = cuda_device
+    for c, n in ((320, 256), (640, 100), (1280, 64)):
+        b, t, heads = 2, 77, 8
+        q = _r("xa.q", (b, n, c)).to(torch.bfloat16)
+        k = _r("xa.k", (b, t, c)).to(torch.bfloat16)
+        v = _r("xa.v", (b, t, c)).to(torch.bfloat16)
+        scale = (c // heads) ** -0.5
+        sim = ops.cross_scores(q.to(d), k.to(d), heads, scale)
+        ref_sim = port.attention_scores(q.float(), k.float(), heads, scale)
+        assert sim.shape == (b, heads, n, t) and rel_l2(sim, ref_sim) < 1e-5
+        out, attn = ops.softmax_pv(sim, v.to(d), True)
+        ref_attn = ref_sim.softmax(dim=-1)
+        assert rel_l2(attn, ref_attn) < 1e-5
+        vh = v.float().reshape(b, t, heads, c // heads).permute(0, 2, 1, 3)
+        ref_out = torch.matmul(ref_attn, vh).permute(0, 2, 1, 3).reshape(b, n, c)
+        assert rel_l2(out.float(), ref_out) < 4e-3
+        fused = ops.attention(q.to(d), k.to(d), v.to(d), heads, scale, None)
+        assert rel_l2(out.float(), fused.float()) < 6e-3
+        out2, empty = ops.softmax_pv(sim, v.to(d), False)
+        assert empty.numel() == 0 and torch.equal(out2, out)
+
+
+@pytest.mark.parametrize("ks", [2, 3])
+def test_conv_attn_rows_vs_reference_golden(ops, cuda_device, ks):
+    """replace_rows_by_conv_attn (ldm/util.py:701-879) against the output of the reference function itself."""
+    from conftest import load_golden
+    name = "conv_attn"
+    g = load_golden(name)
+    heads, dh, hw, b, t, seed = [int(v) for v in g["meta"]]
+    n = hw * hw
+    q = P.randn(f"{name}.q", (b * heads, n, dh), seed)
+    k = P.randn(f"{name}.k", (b * heads, t, dh), seed)
+    sim = P.randn(f"{name}.sim", (b * heads, n, t), seed)
+    inst = torch.tensor([0, 2], dtype=torch.int32)
+    tok = torch.tensor([list(range(6, 6 + ks * ks))] * 2, dtype=torch.int32)
+    d = cuda_device
+    tokens = lambda x, l: x.reshape(b, heads, l, dh).permute(0, 2, 1, 3).reshape(b, l, heads * dh).to(torch.bfloat16).to(d)
+    s = sim.reshape(b, heads, n, t).to(d).contiguous()
+    ops.conv_attn_rows(s, tokens(q, n), tokens(k, t), inst.to(d), tok.to(d), hw, hw, ks, dh ** -0.5)
+    ref = torch.as_tensor(g[f"out_ks{ks}"]).reshape(b, heads, n, t)
+    s = s.cpu()
+    replaced = torch.zeros(b, t, dtype=torch.bool)
+    replaced[inst.long()[:, None], tok.long()] = True
+    keep = ~replaced[:, None, None, :].expand_as(ref)
+    assert torch.equal(s[keep], ref[keep])                      # untouched columns / samples are untouched
+    assert rel_l2(s[~keep], ref[~keep]) < 6e-3                  # q, k rounded to bf16
+
+
 @pytest.mark.parametrize("ca_idx,n", [(0, 256), (2, 64), (4, 64), (0, 4096)])
 def test_ada_pool_and_head(ops, cuda_device, ca_idx, n):
     seed, b, K, r = 15, 2, 9, 12

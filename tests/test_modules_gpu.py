@@ -139,10 +139,68 @@ def test_basic_transformer_block_and_self_attention(afb, cuda_device):
 def test_unsupported_modes_raise(afb, cuda_device):
     ca = afb.CrossAttention(320, context_dim=768, heads=8, dim_head=40).to(cuda_device).eval()
     x = torch.zeros((1, 64, 320), device=cuda_device)
-    ctx = torch.zeros((1, 77, 768), device=cuda_device)
     ca.save_attn_vars = True
+    with pytest.raises(NotImplementedError):                 # the capture exists for cross-attention layers only
+        ca(x)
+    ff = afb.FeedForward(320, glu=True)
     with pytest.raises(NotImplementedError):
-        ca(x, context=ctx)
+        afb.FeedForward(320, glu=False)
+    assert ff is not None
+
+
+def test_cross_attention_save_attn_vars_vs_reference_golden(afb, cuda_device):
+    """attention.py:245-255: cached q * d^-1/4, attn and attnscore as [B, 8, N, 77], against the reference module."""
+    g = load_golden("attn_vars")
+    c, n, b, seed = [int(v) for v in g["meta"]]
+    name = "attn_vars"
+    ca = afb.CrossAttention(c, context_dim=768, heads=8, dim_head=c // 8)
+    sd = {k: P.draw(f"{name}.{k}", tuple(v.shape), seed) for k, v in ca.state_dict().items()}
+    ca.load_state_dict(sd)
+    ca = ca.to(cuda_device).eval()
+    ca.save_attn_vars = True
+    x = P.randn(f"{name}.x", (b, n, c), seed)
+    ctx = P.randn(f"{name}.ctx", (b, 77, 768), seed)
+    with torch.no_grad():
+        out = ca(x.to(cuda_device), context=ctx.to(cuda_device))
+    assert rel_l2(out, g["out"]) < BLOCK_TOL
+    act = ca.cached_activations
+    assert set(act) == {"q", "attn", "attnscore"}
+    for k in ("q", "attn", "attnscore"):
+        assert tuple(act[k].shape) == tuple(g[k].shape), k
+        assert rel_l2(act[k], g[k]) < BLOCK_TOL, k
+
+
+@pytest.mark.parametrize("ks", [2, 3])
+def test_cross_attention_conv_attn_rows(afb, cuda_device, ks):
+    """attention.py:208-216 through CrossAttention.forward: a callable context that returns placeholder2indices turns
+    on the convolutional-attention row replacement for the subject tokens (ks*ks of them) of the listed samples."""
+    c, hw, b, seed = 320, 8, 3, 31
+    n, heads = hw * hw, 8
+    ca = afb.CrossAttention(c, context_dim=768, heads=heads, dim_head=c // heads)
+    sd = {k: P.draw(f"cva.{k}", tuple(v.shape), seed) for k, v in ca.state_dict().items()}
+    ca.load_state_dict(sd)
+    ca = ca.to(cuda_device).eval()
+    ca.use_conv_attn_kernel_size, ca.infeat_size = ks, (hw, hw)
+    x = P.randn("cva.x", (b, n, c), seed)
+    ctx = P.randn("cva.ctx", (b, 77, 768), seed)
+    idx_b = torch.tensor([0] * 9 + [2] * 9)
+    idx_n = torch.tensor(list(range(4, 13)) * 2)
+    p2i = {"z": (idx_b, idx_n)}
+    cd = ctx.to(cuda_device)
+    with torch.no_grad():
+        out = ca(x.to(cuda_device), context=lambda: ((cd, cd), p2i))
+        plain = ca(x.to(cuda_device), context=cd)
+    # oracle: scores -> row replacement -> softmax -> . v -> to_out
+    d = c // heads
+    q, k, v = x @ sd["to_q.weight"].t(), ctx @ sd["to_k.weight"].t(), ctx @ sd["to_v.weight"].t()
+    sim = port.attention_scores(q, k, heads, d ** -0.5)
+    split = lambda t_: t_.reshape(b, t_.shape[1], heads, d).permute(0, 2, 1, 3).reshape(b * heads, t_.shape[1], d)
+    sim = port.replace_rows_by_conv_attn(sim.reshape(b * heads, n, 77), split(q), split(k), (idx_b, idx_n), (hw, hw), ks,
+                                         heads, d ** -0.5).reshape(b, heads, n, 77)
+    o = torch.matmul(sim.softmax(dim=-1), v.reshape(b, 77, heads, d).permute(0, 2, 1, 3)).permute(0, 2, 1, 3).reshape(b, n, c)
+    ref = o @ sd["to_out.0.weight"].t() + sd["to_out.0.bias"]
+    assert rel_l2(out, ref) < BLOCK_TOL
+    assert rel_l2(out[1], plain[1]) < 6e-3 and rel_l2(out[0], plain[0]) > 1e-2     # sample 1 has no subject (explicit vs fused path: bf16 P)
 
 
 # ------------------------------------------------------------------------------------------- AdaEmbedding
