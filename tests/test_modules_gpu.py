@@ -203,6 +203,98 @@ def test_cross_attention_conv_attn_rows(afb, cuda_device, ks):
     assert rel_l2(out[1], plain[1]) < 6e-3 and rel_l2(out[0], plain[0]) > 1e-2     # sample 1 has no subject (explicit vs fused path: bf16 P)
 
 
+# ------------------------------------------------------------------------------------------- configs 3 and 5
+def test_spatial_transformer_two_subjects_ada_wiring(afb, cuda_device):
+    """BASELINE.json configs[2] structure ('a z hugging a y'): two subjects with their own AdaEmbedding weights, K = 9
+    rows each at positions 2..10 and 13..21, recomputed from this layer's features and spliced into the context of
+    the first n_instances samples (the cond half); the remaining samples keep the static context.  Oracle: the port's
+    functions composed along the reconstructed call site."""
+    from adaface_b200.unet import AdaPromptContext, AdaSubject
+    c, hw, b, n_inst, seed, K, r, layer_idx, ca = 320, 16, 4, 2, 33, 9, 12, 1, 0
+    n = hw * hw
+    d = cuda_device
+    sd = P.init_spatial_transformer(c, seed)
+    st = _st_module(afb, c, sd, d)
+    x = P.randn("ms.x", (b, c, hw, hw), seed)
+    ctx = P.randn("ms.ctx", (b, 77, 768), seed)
+    time_emb = P.randn("ms.time_emb", (b, 1280), seed)
+    subjects, oracle_subjects = [], []
+    for si, pos in enumerate((list(range(2, 11)), list(range(13, 22)))):
+        asd = P.init_ada_embedding(seed + 10 * si, K, r, 2)
+        ada = afb.AdaEmbedding(num_vectors_per_subj_token=K, fg_emb_count=5, bg_emb_count=4, r=r, init_vecs=torch.zeros(2, 768))
+        ada.load_state_dict(asd, strict=True)
+        ada = ada.to(d).eval()
+        probes = P.randn(f"ms.{si}.probes", (16, 768), seed, 0.5)
+        extra = P.randn(f"ms.{si}.extra", (16, n_inst, 768), seed, 0.5)
+        subjects.append(AdaSubject(ada, pos, probes.to(d), extra.to(d), n_instances=n_inst))
+        oracle_subjects.append((asd, pos, probes[ca], extra[ca]))
+    ada_ctx = AdaPromptContext(subjects)
+    lc = ctx.to(d).to(torch.bfloat16)
+
+    def with_ada(comps):
+        new = ada_ctx.apply(layer_idx, comps, lc, time_emb.to(d))
+        return (new, new), None
+    with_ada.wants_layer_attn_components = True
+    with torch.no_grad():
+        y = st(x.to(d), context=with_ada)
+
+    # ---- oracle
+    pre = "transformer_blocks.0."
+    t = port.group_norm(x, sd["norm.weight"], sd["norm.bias"])
+    t = t.reshape(b, c, n).transpose(1, 2) @ sd["proj_in.weight"].reshape(c, c).t() + sd["proj_in.bias"]
+    n1 = port.layer_norm(t, sd[pre + "norm1.weight"], sd[pre + "norm1.bias"])
+    x1 = port.cross_attention(n1, sd, pre + "attn1.") + t
+    n2 = port.layer_norm(x1, sd[pre + "norm2.weight"], sd[pre + "norm2.bias"])
+    q = n2 @ sd[pre + "attn2.to_q.weight"].t()
+    ctx2 = ctx.clone()
+    for asd, pos, probe, extra in oracle_subjects:
+        vecs, _ = port.ada_embedding(asd, ca, x1[:n_inst], q[:n_inst], sd[pre + "attn2.to_k.weight"], time_emb[:n_inst],
+                                     probe, extra, K, r, infeat_size=(hw, hw))
+        ctx2[:n_inst, pos] = vecs
+    x2 = x1 + port.cross_attention(n2, sd, pre + "attn2.", ctx2)
+    n3 = port.layer_norm(x2, sd[pre + "norm3.weight"], sd[pre + "norm3.bias"])
+    x3 = port.geglu_feedforward(n3, sd, pre + "ff.") + x2
+    ref = (x3 @ sd["proj_out.weight"].reshape(c, c).t() + sd["proj_out.bias"]).transpose(1, 2).reshape(b, c, hw, hw) + x
+    assert rel_l2(y, ref) < BLOCK_TOL
+    assert rel_l2(y.cpu() - x, ref - x) < 2 * BLOCK_TOL
+    # the spliced rows really changed the result for the conditioned samples only
+    with torch.no_grad():
+        y_static = st(x.to(d), context=ctx.to(d))
+    assert rel_l2(y[n_inst:], y_static[n_inst:]) < 1e-6 and rel_l2((y - y_static)[:n_inst].cpu(), torch.zeros(1)) > 0
+
+
+def test_config5_shapes_96x96_latent(afb, cuda_device):
+    """BASELINE.json configs[4]: 768x768 images = 96x96 latents, N = 9216 / 2304 tokens.  The eager score tensor is
+    2.7 GB per sample per layer, so the full-size self-attention is checked (a) against the oracle on a slice of the
+    query rows and (b) through its invariance to how the queries are chunked; the second-level block (48x48, C = 640)
+    is compared in full."""
+    from adaface_b200 import ops
+    d = cuda_device
+    b, n, c, heads = 2, 96 * 96, 320, 8
+    qkv = P.randn("c5.qkv", (b, n, 3 * c), 41, 1.5).to(torch.bfloat16)
+    qd = qkv.to(d)
+    scale = (c // heads) ** -0.5
+    full = ops.attention(qd[..., :c], qd[..., c:2 * c], qd[..., 2 * c:], heads, scale, None)
+    rows = torch.arange(1000, 1000 + 384)
+    qf, kf, vf = qkv[..., :c].float(), qkv[..., c:2 * c].float(), qkv[..., 2 * c:].float()
+    sim = port.attention_scores(qf[:, rows], kf, heads, scale)
+    ref = torch.matmul(sim.softmax(-1), vf.reshape(b, n, heads, c // heads).permute(0, 2, 1, 3)).permute(0, 2, 1, 3)
+    assert rel_l2(full[:, rows].float(), ref.reshape(b, len(rows), c)) < 6e-3
+    part = torch.cat([ops.attention(qd[:, lo:hi, :c].contiguous(), qd[..., c:2 * c], qd[..., 2 * c:], heads, scale, None)
+                      for lo, hi in ((0, 512), (512, 5000), (5000, n))], dim=1)
+    assert torch.equal(part, full)
+    # second level of the 96x96 ladder: 48x48 tokens, C = 640, with the 16 identity tokens of the Arc2Face slot (4..19)
+    c2, hw2, seed = 640, 48, 42
+    sd = P.init_spatial_transformer(c2, seed)
+    st = _st_module(afb, c2, sd, d)
+    x = P.randn("c5.x", (1, c2, hw2, hw2), seed)
+    ctx = P.randn("c5.ctx", (1, 77, 768), seed)
+    ctx[:, 4:20] = P.randn("c5.id", (1, 16, 768), seed, 0.7)
+    with torch.no_grad():
+        y = st(x.to(d), context=ctx.to(d))
+    assert rel_l2(y, port.spatial_transformer(x, sd, ctx)) < BLOCK_TOL
+
+
 # ------------------------------------------------------------------------------------------- AdaEmbedding
 def test_ada_embedding_module_vs_reference_golden(afb, cuda_device):
     """All 16 layers against the reference class called standalone (H=2: K=9, fg 5 / bg 4, r=12; eval; fp32
