@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
                                                        const float* __restrict__ basis, const float* __restrict__ bias,
                                                        float* __restrict__ out, __nv_bfloat16* __restrict__ ctx_out,
                                                        const int* __restrict__ token_pos, long long ctx_sample_stride,
-                                                       int C, int TD, int K, int R, int D) {
+                                                       long long basis_sample_stride, int C, int TD, int K, int R, int D) {
   extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D]
   __shared__ float red[32];
   const int k = blockIdx.x, b = blockIdx.y;
@@ -449,7 +449,9 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
   float s = 0.f;
   for (int d = threadIdx.x; d < D; d += blockDim.x) {
     float a = 0.f;
-    for (int r = 0; r < R; ++r) a += coeffs[r] * __ldg(basis + (static_cast<long long>(k) * R + r) * D + d);
+    // basis_sample_stride = 0: shared basis [K, R, D]; > 0: per-instance zero-shot basis [B, K, R, D] (:860-868)
+    const float* bk = basis + static_cast<long long>(b) * basis_sample_stride + static_cast<long long>(k) * R * D;
+    for (int r = 0; r < R; ++r) a += coeffs[r] * __ldg(bk + static_cast<long long>(r) * D + d);
     vec[d] = a;
     s += a;
   }
@@ -582,8 +584,9 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
 
 extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
                             const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
-                            afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int batch, int channels,
-                            int td, int num_vectors, int r, int out_dim, afb_stream_t stream_) {
+                            afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride,
+                            int64_t basis_sample_stride, int batch, int channels, int td, int num_vectors, int r,
+                            int out_dim, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(infeat_fg && infeat_bg && time_emb && coeff_w && coeff_b && basis && out, "afb_ada_head: NULL argument");
@@ -596,7 +599,8 @@ extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, cons
   AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head: feature vector too large for one block (%zu bytes)", sh);
   ada_head_kernel<<<dim3(num_vectors, batch), 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias,
                                                                  out, reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos,
-                                                                 ctx_sample_stride, channels, td, num_vectors, r, out_dim);
+                                                                 ctx_sample_stride, basis_sample_stride, channels, td, num_vectors, r,
+                                                                 out_dim);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

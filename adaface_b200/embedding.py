@@ -218,18 +218,25 @@ class AdaEmbedding(nn.Module, _PackedWeights):
             raise RuntimeError("AdaEmbedding.forward needs both fg and bg embeddings (fg_emb_count, bg_emb_count > 0)")
         if self.use_cached_bg and cached_pooler_bg_out is None:
             raise ValueError("AdaEmbedding(use_cached_bg=True) needs cached_pooler_bg_out")             # :789-792
-        if self.do_zero_shot:
-            raise NotImplementedError("adaface_b200.AdaEmbedding: per-instance zero-shot basis vectors are not built yet")
+        if self.do_zero_shot and zs_basis_vecs is None:
+            raise ValueError("Zero-shot AdaEmbedding requires zs_basis_vecs")                       # :861
         pooled = self.poolers[ca](layer_attn_components, layer_subj_emb_probe, layer_static_extra_emb_mean,
                                   img_mask=img_mask, want_attn=getattr(self, "want_pooler_attn", True))   # :815-819
         infeat_fg = pooled.pop("fg_out")                                                        # :823-829
         infeat_bg = cached_pooler_bg_out if self.use_cached_bg else pooled["bg_out"]
         p = self.packed()
-        bias = None if self.bias is None else p["bias"][ca]
+        if self.do_zero_shot:
+            # per-instance basis [B, K, r, 768] from the subject basis generator, no bias; the coefficient scaler
+            # (gen_gradient_scaler, :656,868) is the identity in the forward pass                   :860-868,886-890
+            if zs_basis_vecs.dim() != 4 or tuple(zs_basis_vecs.shape[1:]) != (self.K, self.r, self.out_emb_dim):
+                raise ValueError(f"zs_basis_vecs must be [B, {self.K}, {self.r}, {self.out_emb_dim}]")
+            basis, bias = zs_basis_vecs[:infeat_fg.shape[0]], None
+        else:
+            basis, bias = p["basis"], (None if self.bias is None else p["bias"][ca])
         if splice_into is None:
-            out = ops.ada_head(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"], p["basis"],
+            out = ops.ada_head(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"], basis,
                                bias)                                                            # :847-893
         else:
             out = ops.ada_head_splice(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"],
-                                      p["basis"], bias, splice_into, splice_positions)
+                                      basis, bias, splice_into, splice_positions)
         return out, pooled

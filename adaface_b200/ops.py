@@ -431,7 +431,14 @@ def _(x, q, pool_q, key_mask, want_attn):
 def _ada_head_impl(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out, token_pos):
     _need_cuda(infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias, ctx_out, token_pos)
     b, c = infeat_fg.shape
-    k, r, d = basis.shape
+    if basis.dim() == 4:                      # zero-shot: per-instance basis vectors [B, K, r, D] (:860-868)
+        if basis.shape[0] != b:
+            raise ValueError("ada_head: per-instance basis must be [B, K, r, D]")
+        k, r, d = basis.shape[1:]
+        basis_stride = k * r * d
+    else:
+        k, r, d = basis.shape
+        basis_stride = 0
     f = lambda t: None if t is None else t.to(torch.float32).contiguous()
     infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias = map(
         f, (infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, bias))
@@ -447,8 +454,8 @@ def _ada_head_impl(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, 
         stride = ctx_out.stride(0)
     out = torch.empty((b, k, d), dtype=torch.float32, device=infeat_fg.device)
     _run("ada_head", _lib.load().afb_ada_head, _ptr(infeat_fg), _ptr(infeat_bg), _ptr(time_emb), time_emb.stride(0),
-         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), _ptr(ctx_out), _ptr(token_pos), stride, b, c, td,
-         k, r, d, _stream(), nbytes=4.0 * (coeff_w.numel() + basis.numel()))
+         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), _ptr(ctx_out), _ptr(token_pos), stride,
+         basis_stride, b, c, td, k, r, d, _stream(), nbytes=4.0 * (coeff_w.numel() + basis.numel()))
     return out
 
 
@@ -461,7 +468,7 @@ def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, co
 
 @ada_head.register_fake
 def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias):
-    return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[0], basis.shape[2]), dtype=torch.float32)
+    return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[-3], basis.shape[-1]), dtype=torch.float32)
 
 
 @torch.library.custom_op("adaface_b200::ada_head_splice", mutates_args=("ctx_out",))
@@ -474,7 +481,7 @@ def ada_head_splice(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: 
 
 @ada_head_splice.register_fake
 def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out, token_pos):
-    return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[0], basis.shape[2]), dtype=torch.float32)
+    return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[-3], basis.shape[-1]), dtype=torch.float32)
 
 
 # ------------------------------------------------------------------------------------------- elementwise

@@ -165,10 +165,12 @@ int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* pool_q, cons
  * coeff_b [K*r]; basis fp32 [K, r, D]; bias fp32 [K, D] or NULL; out fp32 [B, K, D].
  * Optional splice of the subject rows into the layer's context: ctx_out bf16 with sample stride
  * ctx_sample_stride elements and rows of D elements, token_pos int32 [K] (device) - vector k of sample b is also
- * written, as bf16, to ctx_out[b * ctx_sample_stride + token_pos[k] * D ...].  Both NULL to skip. */
+ * written, as bf16, to ctx_out[b * ctx_sample_stride + token_pos[k] * D ...].  Both NULL to skip.
+ * basis_sample_stride: 0 for the shared basis [K, r, D]; K*r*D for per-instance zero-shot basis vectors
+ * [B, K, r, D] (embedding_manager.py:860-868, no bias in that mode). */
 int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
                  const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
-                 afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int batch, int channels, int td,
+                 afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int64_t basis_sample_stride, int batch, int channels, int td,
                  int num_vectors, int r, int out_dim, afb_stream_t stream);
 
 /* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */

@@ -343,6 +343,45 @@ def test_ada_embedding_module_vs_reference_golden(afb, cuda_device):
     print(f"AdaEmbedding worst layer rel-L2 {worst:.2e}")
 
 
+def test_ada_embedding_zero_shot_basis(afb, cuda_device):
+    """embedding_manager.py:860-868,886-890: do_zero_shot takes per-instance basis vectors [B, K, r, 768] and no bias.
+    Pinned through the golden-checked slow path: with every instance given the slow model's own basis the two must
+    agree exactly, and instance i with its own basis must equal the slow model run with that basis."""
+    seed, b, K, r, ca_idx = 35, 3, 9, 12, 2
+    d = cuda_device
+    sd = P.init_ada_embedding(seed, K, r, 2)
+    slow = afb.AdaEmbedding(num_vectors_per_subj_token=K, fg_emb_count=5, bg_emb_count=4, r=r, init_vecs=torch.zeros(2, 768))
+    slow.load_state_dict(sd, strict=True)
+    with torch.no_grad():
+        slow.bias.zero_()
+    slow = slow.to(d).eval()
+    zs = afb.AdaEmbedding(num_vectors_per_subj_token=K, fg_emb_count=5, bg_emb_count=4, r=r, do_zero_shot=True)
+    zs.load_state_dict({k: v for k, v in sd.items() if k in zs.state_dict()}, strict=True)
+    zs = zs.to(d).eval()
+    assert zs.basis_vecs is None and zs.bias is None and zs.pre_vecs is None
+    c = P.CA_INFEAT_DIMS[ca_idx]
+    layer_idx = {v: k for k, v in port.LAYER_IDX2CA.items()}[ca_idx]
+    to_k = torch.nn.Linear(768, c, bias=False).to(d)
+    comps = {"x": P.randn("zs.x", (b, 64, c), seed).to(d), "q": P.randn("zs.q", (b, 64, c), seed, 2.0).to(d), "to_k": to_k,
+             "infeat_size": (8, 8)}
+    args = (P.randn("zs.t", (b, 1280), seed).to(d), P.randn("zs.probe", (768,), seed, 0.5).to(d),
+            P.randn("zs.extra", (b, 768), seed, 0.5).to(d))
+    shared = torch.cat([slow.pre_vecs, slow.basis_vecs], dim=1).detach()                       # [K, r, 768]
+    with torch.no_grad():
+        ref, _ = slow(layer_idx, comps, *args)
+        out, _ = zs(layer_idx, comps, *args, zs_basis_vecs=shared[None].expand(b, -1, -1, -1).contiguous())
+        assert torch.equal(out, ref)
+        per_inst = shared[None] + 0.1 * P.randn("zs.basis", (b, K, r, 768), seed).to(d)
+        out2, _ = zs(layer_idx, comps, *args, zs_basis_vecs=per_inst)
+        for i in range(b):
+            slow.pre_vecs.copy_(per_inst[i, :, :2])
+            slow.basis_vecs.copy_(per_inst[i, :, 2:])
+            ref_i, _ = slow(layer_idx, comps, *args)
+            assert torch.equal(out2[i], ref_i[i])
+        with pytest.raises(ValueError):
+            zs(layer_idx, comps, *args)
+
+
 # ------------------------------------------------------------------------------------------- DDIM
 def _toy(x, t, c):
     return torch.tanh(x * 0.7 + c.mean(dim=(1, 2)).reshape(-1, 1, 1, 1)) * (1.0 + t.reshape(-1, 1, 1, 1) / 1000.0)
