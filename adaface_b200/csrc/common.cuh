@@ -108,6 +108,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+__device__ __forceinline__ float4 lds128(uint32_t smem_addr) {   // explicit LDS.128 (no generic-address load)
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_addr));
+  return v;
+}
+
 // ---- proxies / fences -------------------------------------------------------------------------
 // generic-proxy smem writes -> visible to the async proxy (TMA / tcgen05.mma operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -253,6 +259,82 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                : "memory");
 }
 
+// ---- CTA pair (cta_group::2): two CTAs of one cluster, ranks 2i / 2i+1, drive one 256-row MMA ------------------
+// Bit 24 of a shared::cluster address selects the CTA of the pair; clearing it names the even ("leader") CTA.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// Every thread of every CTA of the cluster.  Execution barrier only (relaxed arrive: no MEMBAR.ALL.GPU): barrier
+// initialisation is published by fence.mbarrier_init.release.cluster, nothing else crosses CTAs through memory.
+__device__ __forceinline__ void cluster_sync_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Release/acquire form: everything this CTA sent to its peers (remote barrier arrives included) has been performed
+// before any peer leaves the barrier -- the one to use before a CTA of the cluster may exit.
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster.  Default (.release.cta)
+// semantics on purpose: .release.cluster costs MEMBAR.ALL.GPU + ERRBAR per arrive, and the users order TMEM
+// accesses (tcgen05 fences), not generic-proxy memory, across the pair.
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(rank)
+      : "memory");
+}
+// TMA load into THIS CTA's shared memory whose bytes are counted on the LEADER CTA's barrier
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint64_t* bar, void* smem, int c0, int c1,
+                                                 uint64_t hint = kEvictNormal) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "l"(hint)
+      : "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem) {   // one warp in EACH CTA of the pair
+  static_assert(kCols >= 32 && kCols <= 512 && (kCols & (kCols - 1)) == 0, "TMEM columns: power of 2 in [32,512]");
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// D[tmem of both CTAs, 256 rows] (+)= A[smem, 128 rows per CTA] * B[smem, N/2 rows per CTA]; leader CTA only
+__device__ __forceinline__ void umma_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this offset in both CTAs once the pair's MMAs issued so far have completed
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+
 // ---- TMEM <-> registers (32 lanes x 32-bit, N columns; warp w touches lanes 32*(w%4)..+31) ------
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
@@ -375,6 +457,33 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
   const float erf_abs = fmaf(-poly, e, 1.0f);
   return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+}
+// v * gelu(x) on two packed lanes, same approximation as gelu_erf_fast with the constants folded:
+// gelu(x) = x * Phi(x), Phi(x) = (x < 0 ? q : 1 - q), q = 0.5 * erfc(|x| / sqrt 2) = (b1 t + .. + b5 t^5) * 2^(-(c x)^2),
+// t = 1 / (1 + (p / sqrt 2) |x|), b_i = a_i / 2, c = sqrt(log2(e) / 2).  13 FMA-pipe + 4 MUFU issues per PAIR.
+__device__ __forceinline__ uint64_t geglu_x2(uint64_t v, uint64_t x) {
+  float x0, x1;
+  unpack_f32x2(x, x0, x1);
+  float d0, d1;
+  unpack_f32x2(ffma2(pack_f32x2(0.23164189f, 0.23164189f), pack_f32x2(fabsf(x0), fabsf(x1)), pack_f32x2(1.0f, 1.0f)), d0, d1);
+  float t0, t1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  const uint64_t t = pack_f32x2(t0, t1);
+  uint64_t poly = ffma2(pack_f32x2(0.5307027145f, 0.5307027145f), t, pack_f32x2(-0.7265760135f, -0.7265760135f));
+  poly = ffma2(poly, t, pack_f32x2(0.7107068705f, 0.7107068705f));
+  poly = ffma2(poly, t, pack_f32x2(-0.142248368f, -0.142248368f));
+  poly = ffma2(poly, t, pack_f32x2(0.127414796f, 0.127414796f));
+  poly = fmul2(poly, t);
+  const uint64_t xs = fmul2(x, pack_f32x2(0.8493218003f, 0.8493218003f));
+  float s0, s1;
+  unpack_f32x2(fmul2(xs, xs), s0, s1);
+  const uint64_t q = fmul2(poly, pack_f32x2(ex2_approx(-s0), ex2_approx(-s1)));
+  float q0, q1, r0, r1;
+  unpack_f32x2(q, q0, q1);
+  unpack_f32x2(ffma2(q, pack_f32x2(-1.0f, -1.0f), pack_f32x2(1.0f, 1.0f)), r0, r1);
+  const uint64_t h = pack_f32x2(x0 < 0.f ? q0 : r0, x1 < 0.f ? q1 : r1);
+  return fmul2(fmul2(v, x), h);
 }
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -265,19 +265,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 constexpr int kTmaThreads = 384;
 constexpr int kBoxBytes = kBM * 32 * 2;      // one staging box: 128 rows x 32 bf16 columns
 
-template <int BN, bool GEGLU>
+// kPair: two CTAs of a cluster (one TPC) compute a 256 x BN tile with cta_group::2 MMAs; each stages its own 128
+// rows of A and HALF of the W tile, so the operand bytes an SM pulls from L2 per output drop by 25-30%.
+template <int BN, bool GEGLU, bool kPair = false>
 struct TCfg {
   static constexpr int kABytes = kBM * kBK * 2;
-  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kBRows = kPair ? BN / 2 : BN;
+  static constexpr int kBBytes = kBRows * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kOutChunks = GEGLU ? BN / 64 : BN / 32;        // 32-column output boxes per tile
   static constexpr int kStagingBytes = 2 * kOutChunks * kBoxBytes;     // double-buffered
+  static constexpr int kParamBytes = 2 * 2 * BN * 4;                   // {bias, colsum} of a tile's columns, double-buffered
   static constexpr int kBarrierBytes = 512;
-  static constexpr int kStages = (227 * 1024 - 1024 - kBarrierBytes - kStagingBytes) / kStageBytes;
+  static constexpr int kStages = (227 * 1024 - 1024 - kBarrierBytes - kStagingBytes - kParamBytes) / kStageBytes;
   static constexpr int kTmemCols = (2 * BN <= 256) ? 256 : 512;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 + kBarrierBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kParamBytes + 1024 + kBarrierBytes;
   static_assert(kBBytes % 1024 == 0, "W tile must keep 1024B alignment of the next stage");
-  static_assert(kStages >= 3 && kStages <= 12, "pipeline depth");
+  static_assert(kStages >= 3 && kStages <= 16, "pipeline depth");
+  static_assert(!kPair || BN % 32 == 0, "pair mode: each CTA stages BN/2 rows of W, MMA N must be a multiple of 16");
   static_assert(GEGLU ? BN % 64 == 0 : BN % 32 == 0, "tile width vs output boxes");
 };
 
@@ -293,17 +298,18 @@ struct GemmTmaDev {
   float ln_eps;
 };
 
-template <int BN, bool GEGLU, bool kLn, bool kStats>
+template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
 __global__ void __launch_bounds__(kTmaThreads, 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_res,
                      const GemmTmaDev p) {
-  using C = TCfg<BN, GEGLU>;
+  using C = TCfg<BN, GEGLU, kPair>;
   constexpr int NC = C::kOutChunks;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + C::kStages * C::kStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::kStagingBytes);
+  float* params = reinterpret_cast<float*>(staging + C::kStagingBytes);      // [2 buffers][bias BN | colsum BN]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::kStagingBytes + C::kParamBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + C::kStages;
   uint64_t* tmem_full = bars + 2 * C::kStages;
@@ -314,6 +320,11 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // work unit: one CTA (kPair: one CTA pair); a unit's tile is kBM (kPair: 2 * kBM) rows by BN columns
+  const int cta_rank = kPair ? static_cast<int>(cluster_ctarank()) : 0;
+  const int unit = kPair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int num_units = kPair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int num_m_units = kPair ? (p.num_m_blocks + 1) >> 1 : p.num_m_blocks;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_a);
@@ -328,35 +339,48 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 8);
+      mbar_init(&tmem_empty[i], kPair ? 16 : 8);      // pair: the leader's barrier collects both CTAs' epilogue warps
       mbar_init(&out_free[i], 2);
       mbar_init(&res_full[i], 1);
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
+  if (warp == 2) {
+    if constexpr (kPair) tmem_alloc_pair<C::kTmemCols>(tmem_slot);
+    else tmem_alloc<C::kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
   __syncthreads();
+  if constexpr (kPair) cluster_sync_relaxed();  // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_tiles = num_m_units * p.num_n_blocks;
+  auto tile_m_blk = [&](int tile) { return kPair ? 2 * (tile / p.num_n_blocks) + cta_rank : tile / p.num_n_blocks; };
 
   if (warp == 0) {
     // ------------------------------------------------------------------ operand producer
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile / p.num_n_blocks;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        const int m_blk = tile_m_blk(tile);
         const int n_blk = tile % p.num_n_blocks;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + C::kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
-          tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
-          tma_load_2d(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN, kEvictLast);
+          if constexpr (kPair) {
+            // both CTAs' bytes are counted on the leader's barrier; the peer's may land before the leader arms the
+            // phase (the pending arrival keeps it open), never before the previous phase closed (empty_bar)
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
+            tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            tma_load_2d_pair(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN + cta_rank * C::kBRows, kEvictLast);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+            tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            tma_load_2d(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN, kEvictLast);
+          }
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
@@ -369,14 +393,14 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     // The whole warp walks the loop converged and one elected lane issues: in divergent code (if (lane == 0)) the
     // compiler wraps every tcgen05 instruction in an election loop and keeps the descriptors in vector registers,
     // ~10 extra instructions per MMA on the one thread that must never fall behind the tensor pipe.
-    {
-      constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, 0, 0);
+    if (cta_rank == 0) {      // pair: the even CTA issues for both
+      constexpr uint32_t idesc = umma_idesc_bf16(kPair ? 2 * kBM : kBM, BN, 0, 0);
       const bool leader = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -388,8 +412,12 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             const uint64_t da = umma_desc_kmajor_sw128(sa);
             const uint64_t db = umma_desc_kmajor_sw128(sa + C::kABytes);
 #pragma unroll
-            for (int k = 0; k < kBK / 16; ++k) umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-            umma_commit(&empty_bar[stage]);
+            for (int k = 0; k < kBK / 16; ++k) {
+              if constexpr (kPair) umma_ss_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+              else umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            }
+            if constexpr (kPair) umma_commit_pair(&empty_bar[stage]);
+            else umma_commit(&empty_bar[stage]);
           }
           __syncwarp();
           if (++stage == C::kStages) {
@@ -397,7 +425,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             phase ^= 1;
           }
         }
-        if (leader) umma_commit(&tmem_full[acc]);
+        if (leader) {
+          if constexpr (kPair) umma_commit_pair(&tmem_full[acc]);
+          else umma_commit(&tmem_full[acc]);
+        }
         __syncwarp();
         if (++acc == 2) {
           acc = 0;
@@ -407,14 +438,32 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     }
   } else if (warp == 3) {
     // ------------------------------------------------------------------ staging manager
-    if (lane == 0) {
-      int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int sb = it & 1;
-        const uint32_t use = static_cast<uint32_t>(it >> 1);
-        mbar_wait(&out_free[sb], (use & 1) ^ 1);
+    // One tile ahead of the epilogue: copies the tile's column parameters (bias, LayerNorm column sums) into shared
+    // memory -- every epilogue thread needs all of them, and 16-32 uniform LDG.128 per thread per box were its top
+    // stall -- and prefetches the residual boxes by TMA.
+    int it = 0;
+    for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
+      const int sb = it & 1;
+      const uint32_t use = static_cast<uint32_t>(it >> 1);
+      mbar_wait(&out_free[sb], (use & 1) ^ 1);
+      {
+        const int n_blk = tile % p.num_n_blocks;
+        float4* pb = reinterpret_cast<float4*>(params + sb * 2 * BN);
+        for (int i = lane; i < BN / 4; i += 32) {
+          const int n0 = n_blk * BN + 4 * i;
+          float4 b = make_float4(0.f, 0.f, 0.f, 0.f), c = b;
+          if (n0 < p.N) {
+            if (p.bias != nullptr) b = __ldg(reinterpret_cast<const float4*>(p.bias + n0));
+            if constexpr (kLn) c = __ldg(reinterpret_cast<const float4*>(p.ln_colsum + n0));
+          }
+          pb[i] = b;
+          if constexpr (kLn) pb[BN / 4 + i] = c;
+        }
+        __syncwarp();      // lane 0's arrive below publishes the whole warp's writes
+      }
+      if (lane == 0) {
         if (p.has_res) {
-          const int m_blk = tile / p.num_n_blocks;
+          const int m_blk = tile_m_blk(tile);
           const int n_blk = tile % p.num_n_blocks;
           int valid = 0;
 #pragma unroll
@@ -430,6 +479,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           mbar_arrive(&res_full[sb]);
         }
       }
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ epilogue
@@ -444,8 +494,12 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     int acc = 0;
     uint32_t acc_phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int m_blk = tile / p.num_n_blocks;
+    auto release_acc = [&](int a) {      // this warp has drained accumulator a
+      if constexpr (kPair) mbar_arrive_cluster(&tmem_empty[a], 0);
+      else mbar_arrive(&tmem_empty[a]);
+    };
+    for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
+      const int m_blk = tile_m_blk(tile);
       const int n_blk = tile % p.num_n_blocks;
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
@@ -485,6 +539,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         const int n_out0 = (GEGLU ? n_blk * (BN / 2) : n_blk * BN) + ch * 32;     // first output column of this box
         const int n_acc0 = GEGLU ? n_blk * BN + ch * 64 : n_out0;                  // first accumulator column
         if (n_acc0 >= p.N) break;
+        // this box's column parameters (shared memory, same address in every lane: broadcast reads)
+        const uint32_t pbias = smem_u32(params + sb * 2 * BN + (n_acc0 - n_blk * BN));
+        const uint32_t pcs = pbias + BN * 4;
+        uint32_t pk[16];                                // the box row: 32 bf16
         float v[32];
         if constexpr (GEGLU) {
           uint32_t ra[32], rg[32];
@@ -494,32 +552,35 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           if (ch == ch_hi - 1 || n_acc0 + 64 >= p.N) {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (lane == 0) release_acc(acc);
             released = true;
           }
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_acc0);
-          if constexpr (kLn) {
-            const float4* c4 = reinterpret_cast<const float4*>(p.ln_colsum + n_acc0);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 ca = __ldg(c4 + j), cg = __ldg(c4 + 8 + j);
-              ra[4 * j + 0] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 0]), ln_nm * ca.x));
-              ra[4 * j + 1] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 1]), ln_nm * ca.y));
-              ra[4 * j + 2] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 2]), ln_nm * ca.z));
-              ra[4 * j + 3] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(ra[4 * j + 3]), ln_nm * ca.w));
-              rg[4 * j + 0] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 0]), ln_nm * cg.x));
-              rg[4 * j + 1] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 1]), ln_nm * cg.y));
-              rg[4 * j + 2] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 2]), ln_nm * cg.z));
-              rg[4 * j + 3] = __float_as_uint(fmaf(ln_rstd, __uint_as_float(rg[4 * j + 3]), ln_nm * cg.w));
-            }
-          }
+          const uint64_t rstd2 = pack_f32x2(ln_rstd, ln_rstd), nm2 = pack_f32x2(ln_nm, ln_nm);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 ba = __ldg(b4 + j), bg = __ldg(b4 + 8 + j);
-            v[4 * j + 0] = (__uint_as_float(ra[4 * j + 0]) + ba.x) * gelu_erf_fast(__uint_as_float(rg[4 * j + 0]) + bg.x);
-            v[4 * j + 1] = (__uint_as_float(ra[4 * j + 1]) + ba.y) * gelu_erf_fast(__uint_as_float(rg[4 * j + 1]) + bg.y);
-            v[4 * j + 2] = (__uint_as_float(ra[4 * j + 2]) + ba.z) * gelu_erf_fast(__uint_as_float(rg[4 * j + 2]) + bg.z);
-            v[4 * j + 3] = (__uint_as_float(ra[4 * j + 3]) + ba.w) * gelu_erf_fast(__uint_as_float(rg[4 * j + 3]) + bg.w);
+            const float4 ba = lds128(pbias + 16 * j), bg = lds128(pbias + 16 * (8 + j));
+            uint64_t a01 = pack_f32x2(__uint_as_float(ra[4 * j + 0]), __uint_as_float(ra[4 * j + 1]));
+            uint64_t a23 = pack_f32x2(__uint_as_float(ra[4 * j + 2]), __uint_as_float(ra[4 * j + 3]));
+            uint64_t g01 = pack_f32x2(__uint_as_float(rg[4 * j + 0]), __uint_as_float(rg[4 * j + 1]));
+            uint64_t g23 = pack_f32x2(__uint_as_float(rg[4 * j + 2]), __uint_as_float(rg[4 * j + 3]));
+            if constexpr (kLn) {
+              // rstd * (acc - mean * colsum) + bias = rstd * acc + (ln_nm * colsum + bias)
+              const float4 ca = lds128(pcs + 16 * j), cg = lds128(pcs + 16 * (8 + j));
+              a01 = ffma2(rstd2, a01, ffma2(nm2, pack_f32x2(ca.x, ca.y), pack_f32x2(ba.x, ba.y)));
+              a23 = ffma2(rstd2, a23, ffma2(nm2, pack_f32x2(ca.z, ca.w), pack_f32x2(ba.z, ba.w)));
+              g01 = ffma2(rstd2, g01, ffma2(nm2, pack_f32x2(cg.x, cg.y), pack_f32x2(bg.x, bg.y)));
+              g23 = ffma2(rstd2, g23, ffma2(nm2, pack_f32x2(cg.z, cg.w), pack_f32x2(bg.z, bg.w)));
+            } else {
+              a01 = fadd2(a01, pack_f32x2(ba.x, ba.y));
+              a23 = fadd2(a23, pack_f32x2(ba.z, ba.w));
+              g01 = fadd2(g01, pack_f32x2(bg.x, bg.y));
+              g23 = fadd2(g23, pack_f32x2(bg.z, bg.w));
+            }
+            float o0, o1, o2, o3;
+            unpack_f32x2(geglu_x2(a01, g01), o0, o1);
+            unpack_f32x2(geglu_x2(a23, g23), o2, o3);
+            pk[2 * j] = cvt_bf16x2(o0, o1);
+            pk[2 * j + 1] = cvt_bf16x2(o2, o3);
           }
         } else {
           uint32_t r[32];
@@ -528,32 +589,25 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           if (ch == ch_hi - 1 || n_acc0 + 32 >= p.N) {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (lane == 0) release_acc(acc);
             released = true;
           }
+          const uint64_t rstd2 = pack_f32x2(ln_rstd, ln_rstd), nm2 = pack_f32x2(ln_nm, ln_nm);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if constexpr (kLn) {
-            const float4* c4 = reinterpret_cast<const float4*>(p.ln_colsum + n_acc0);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 cs = __ldg(c4 + j);
-              v[4 * j + 0] = fmaf(ln_rstd, v[4 * j + 0], ln_nm * cs.x);
-              v[4 * j + 1] = fmaf(ln_rstd, v[4 * j + 1], ln_nm * cs.y);
-              v[4 * j + 2] = fmaf(ln_rstd, v[4 * j + 2], ln_nm * cs.z);
-              v[4 * j + 3] = fmaf(ln_rstd, v[4 * j + 3], ln_nm * cs.w);
+          for (int j = 0; j < 8; ++j) {
+            uint64_t v01 = pack_f32x2(__uint_as_float(r[4 * j + 0]), __uint_as_float(r[4 * j + 1]));
+            uint64_t v23 = pack_f32x2(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+            if constexpr (kLn) {
+              const float4 b = lds128(pbias + 16 * j), cs = lds128(pcs + 16 * j);
+              v01 = ffma2(rstd2, v01, ffma2(nm2, pack_f32x2(cs.x, cs.y), pack_f32x2(b.x, b.y)));
+              v23 = ffma2(rstd2, v23, ffma2(nm2, pack_f32x2(cs.z, cs.w), pack_f32x2(b.z, b.w)));
+            } else if (p.bias != nullptr) {
+              const float4 b = lds128(pbias + 16 * j);
+              v01 = fadd2(v01, pack_f32x2(b.x, b.y));
+              v23 = fadd2(v23, pack_f32x2(b.z, b.w));
             }
-          }
-          if (p.bias != nullptr) {
-            const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_acc0);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 b = __ldg(b4 + j);
-              v[4 * j + 0] += b.x;
-              v[4 * j + 1] += b.y;
-              v[4 * j + 2] += b.z;
-              v[4 * j + 3] += b.w;
-            }
+            unpack_f32x2(v01, v[4 * j + 0], v[4 * j + 1]);
+            unpack_f32x2(v23, v[4 * j + 2], v[4 * j + 3]);
           }
         }
         // staging box [128 rows][32 cols] bf16, 64-byte rows, SWIZZLE_64B: 16-byte chunk c of row r sits at c ^ ((r >> 1) & 3)
@@ -573,14 +627,17 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             v[8 * c + 7] += d.y;
           }
         }
+        if constexpr (!GEGLU) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) pk[j] = cvt_bf16x2(v[2 * j], v[2 * j + 1]);
+        }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          const uint4 pk = make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
-                                      pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
-          *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4)) = pk;
+          const uint4 pq = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+          *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4)) = pq;
           if constexpr (!GEGLU && kStats) {
             // statistics of exactly what the consumer will read: the bf16-rounded values
-            const float2 a = unpack_bf16x2(pk.x), b = unpack_bf16x2(pk.y), cc = unpack_bf16x2(pk.z), d = unpack_bf16x2(pk.w);
+            const float2 a = unpack_bf16x2(pq.x), b = unpack_bf16x2(pq.y), cc = unpack_bf16x2(pq.z), d = unpack_bf16x2(pq.w);
             st_s1 += ((a.x + a.y) + (b.x + b.y)) + ((cc.x + cc.y) + (d.x + d.y));
             st_s2 = fmaf(a.x, a.x, st_s2); st_s2 = fmaf(a.y, a.y, st_s2); st_s2 = fmaf(b.x, b.x, st_s2); st_s2 = fmaf(b.y, b.y, st_s2);
             st_s2 = fmaf(cc.x, cc.x, st_s2); st_s2 = fmaf(cc.y, cc.y, st_s2); st_s2 = fmaf(d.x, d.x, st_s2); st_s2 = fmaf(d.y, d.y, st_s2);
@@ -593,7 +650,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       if (!released) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) release_acc(acc);
       }
       if (!GEGLU && kStats && m_row < p.M)
         reinterpret_cast<float2*>(p.stats_out)[static_cast<long long>(m_row) * (2 * p.num_n_blocks) + 2 * n_blk + grp] =
@@ -609,7 +666,11 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<C::kTmemCols>(tmem_base);
+  if constexpr (kPair) cluster_sync_all();      // neither CTA may exit (or free TMEM) while the other can still signal it
+  if (warp == 2) {
+    if constexpr (kPair) tmem_dealloc_pair<C::kTmemCols>(tmem_base);
+    else tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
 }
 
 int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows, int64_t ld) {
@@ -619,9 +680,9 @@ int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows,
   return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, Swizzle::B64);
 }
 
-template <int BN, bool GEGLU, bool kLn, bool kStats>
+template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
 int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
-  using C = TCfg<BN, GEGLU>;
+  using C = TCfg<BN, GEGLU, kPair>;
   CUtensorMap tm_a, tm_w, tm_out, tm_res;
   {
     const uint64_t dims[2] = {static_cast<uint64_t>(a.k), static_cast<uint64_t>(a.m)};
@@ -633,7 +694,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   {
     const uint64_t dims[2] = {static_cast<uint64_t>(a.k), static_cast<uint64_t>(a.n)};
     const uint64_t strides[1] = {static_cast<uint64_t>(a.ldw) * 2};
-    const uint32_t box[2] = {kBK, BN};
+    const uint32_t box[2] = {kBK, static_cast<uint32_t>(C::kBRows)};
     if (int rc = make_tensor_map(&tm_w, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.w, dims, strides, box, Swizzle::B128))
       return rc;
   }
@@ -658,31 +719,66 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   p.ln_colsum = a.ln_colsum;
   p.ln_parts = a.ln_parts;
   p.ln_eps = a.ln_eps;
-  auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats>;
+  auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats, kPair>;
   static bool attr_set = false;
   if (!attr_set) {
     AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
-  const int tiles = p.num_m_blocks * p.num_n_blocks;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kTmaThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, tm_out, tm_res, p);
+  if constexpr (kPair) {
+    const int tiles = ((p.num_m_blocks + 1) / 2) * p.num_n_blocks;
+    const int pairs = tiles < num_sms() / 2 ? tiles : num_sms() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(kTmaThreads);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AFB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_a, tm_w, tm_out, tm_res, p));
+  } else {
+    const int tiles = p.num_m_blocks * p.num_n_blocks;
+    const int grid = tiles < num_sms() ? tiles : num_sms();
+    kern<<<grid, kTmaThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, tm_out, tm_res, p);
+  }
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-template <int BN, bool GEGLU>
-int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
+// AFB_GEMM_PAIR=0 keeps every GEMM on single-CTA tiles (A/B measurement); read once
+bool pair_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_GEMM_PAIR");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
+template <int BN, bool GEGLU, bool kPair>
+int launch_tma_mode(const afb_gemm_args& a, cudaStream_t stream) {
   const bool ln = a.ln_stats != nullptr, st = a.row_stats_out != nullptr;
   if constexpr (GEGLU) {
-    return ln ? launch_tma_impl<BN, true, true, false>(a, stream) : launch_tma_impl<BN, true, false, false>(a, stream);
+    return ln ? launch_tma_impl<BN, true, true, false, kPair>(a, stream)
+              : launch_tma_impl<BN, true, false, false, kPair>(a, stream);
   } else {
     if (ln && st) AFB_FAIL(2, "afb_gemm_bf16: folded LayerNorm and row statistics in one GEMM are not built");
-    if (ln) return launch_tma_impl<BN, false, true, false>(a, stream);
-    if (st) return launch_tma_impl<BN, false, false, true>(a, stream);
-    return launch_tma_impl<BN, false, false, false>(a, stream);
+    if (ln) return launch_tma_impl<BN, false, true, false, kPair>(a, stream);
+    if (st) return launch_tma_impl<BN, false, false, true, kPair>(a, stream);
+    return launch_tma_impl<BN, false, false, false, kPair>(a, stream);
   }
+}
+
+template <int BN, bool GEGLU>
+int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
+  // a CTA pair needs two row blocks to share one W tile
+  if (a.m > kBM && pair_enabled()) return launch_tma_mode<BN, GEGLU, true>(a, stream);
+  return launch_tma_mode<BN, GEGLU, false>(a, stream);
 }
 
 template <int BN, int EPI>
@@ -784,6 +880,9 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
       AFB_REQUIRE(a.residual == nullptr, "afb_gemm_bf16: GEGLU epilogue takes no residual");
       AFB_REQUIRE(a.n % 64 == 0 && a.bias != nullptr, "afb_gemm_bf16: GEGLU needs N %% 64 == 0 and a bias");
       AFB_REQUIRE(a.row_stats_out == nullptr, "afb_gemm_bf16: the GEGLU epilogue does not emit row statistics");
+      // pair mode takes 256-wide tiles: per SM and k-block 32 KB staged for 128 x 256 outputs instead of 32 KB for
+      // 128 x 128, which is what the shared-memory port (TMA fill + UMMA operand reads) can sustain
+      if (a.m > kBM && a.n % 256 == 0 && pair_enabled()) return launch_tma_mode<256, true, true>(a, stream);
       return launch_tma<128, true>(a, stream);
     case AFB_EPI_NCHW:
       AFB_REQUIRE(a.hw > 0 && a.m % a.hw == 0, "afb_gemm_bf16: NCHW epilogue needs hw > 0 dividing M");
