@@ -366,6 +366,15 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
                : "r"(taddr)
                : "memory");
 }
+// tcgen05.wait::ld that also names the registers of the load it completes: arithmetic on them cannot be scheduled
+// above the wait (needed when another load is already in flight behind it and plain program order is all there is)
+__device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&a)[8], uint32_t (&b)[8]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                 "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7])
+               :
+               : "memory");
+}
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -483,6 +492,30 @@ __device__ __forceinline__ uint64_t geglu_x2(uint64_t v, uint64_t x) {
   unpack_f32x2(q, q0, q1);
   unpack_f32x2(ffma2(q, pack_f32x2(-1.0f, -1.0f), pack_f32x2(1.0f, 1.0f)), r0, r1);
   const uint64_t h = pack_f32x2(x0 < 0.f ? q0 : r0, x1 < 0.f ? q1 : r1);
+  return fmul2(fmul2(v, x), h);
+}
+// v * gelu(x) on two packed lanes without the XU pipe: Phi(x) - 1/2 is odd, so on the clamped argument
+// xc = clamp(x, -4.5, 4.5) it is xc * R(xc^2) with R a degree-9 polynomial (weighted Chebyshev fit of
+// (Phi(x) - 1/2) / x on [0, 4.5], fp32 Horner; |gelu error| <= 4.6e-5 everywhere, <= 2.1e-5 for |x| <= 4 -- below
+// half a bf16 ulp of any result larger than 0.012).  13 FMA-pipe + 4 ALU issues per PAIR, no MUFU: at four GEGLU
+// epilogue warps per scheduler the rcp/ex2 form above is bound by the 4-lane XU (8 cycles per warp instruction).
+__device__ __forceinline__ uint64_t geglu_poly_x2(uint64_t v, uint64_t x) {
+  float x0, x1;
+  unpack_f32x2(x, x0, x1);
+  const uint64_t xc = pack_f32x2(fminf(fmaxf(x0, -4.5f), 4.5f), fminf(fmaxf(x1, -4.5f), 4.5f));
+  const uint64_t u = fmul2(xc, xc);
+#define AFB_C2(c) pack_f32x2(c, c)
+  uint64_t r = ffma2(AFB_C2(-1.654012864e-12f), u, AFB_C2(1.952931983e-10f));
+  r = ffma2(r, u, AFB_C2(-1.028583085e-08f));
+  r = ffma2(r, u, AFB_C2(3.216686082e-07f));
+  r = ffma2(r, u, AFB_C2(-6.731901976e-06f));
+  r = ffma2(r, u, AFB_C2(1.010839987e-04f));
+  r = ffma2(r, u, AFB_C2(-1.139682252e-03f));
+  r = ffma2(r, u, AFB_C2(9.884112515e-03f));
+  r = ffma2(r, u, AFB_C2(-6.641189009e-02f));
+  r = ffma2(r, u, AFB_C2(3.989217281e-01f));
+  const uint64_t h = ffma2(xc, r, AFB_C2(0.5f));
+#undef AFB_C2
   return fmul2(fmul2(v, x), h);
 }
 __device__ __forceinline__ float warp_sum(float v) {

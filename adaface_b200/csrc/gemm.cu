@@ -262,7 +262,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 // ============================================================================================
 // Hot variant: TMA-staged epilogue
 // ============================================================================================
-constexpr int kTmaThreads = 384;
 constexpr int kBoxBytes = kBM * 32 * 2;      // one staging box: 128 rows x 32 bf16 columns
 
 // kPair: two CTAs of a cluster (one TPC) compute a 256 x BN tile with cta_group::2 MMAs; each stages its own 128
@@ -274,8 +273,16 @@ struct TCfg {
   static constexpr int kBBytes = kBRows * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kOutChunks = GEGLU ? BN / 64 : BN / 32;        // 32-column output boxes per tile
+  // warps 0-3: TMA producer, MMA issuer, TMEM allocator, staging manager; then the epilogue warps, four (one per TMEM
+  // lane quarter) per column group.  The GEGLU epilogue is ~35 issue slots per output element: it needs four warps
+  // per scheduler to keep up with the tensor pipe at K = 320.
+  static constexpr int kEpiWarps = GEGLU ? 16 : 8;
+  static constexpr int kGroups = kEpiWarps / 4;
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kStagingBytes = 2 * kOutChunks * kBoxBytes;     // double-buffered
-  static constexpr int kParamBytes = 2 * 2 * BN * 4;                   // {bias, colsum} of a tile's columns, double-buffered
+  static constexpr int kColParamBytes = 2 * 2 * BN * 4;                // {bias, colsum} of a tile's columns, double-buffered
+  static constexpr int kRowParamBytes = 2 * kBM * 8;                   // {rstd, -mean * rstd} of a tile's rows, double-buffered
+  static constexpr int kParamBytes = kColParamBytes + kRowParamBytes;
   static constexpr int kBarrierBytes = 512;
   static constexpr int kStages = (227 * 1024 - 1024 - kBarrierBytes - kStagingBytes - kParamBytes) / kStageBytes;
   static constexpr int kTmemCols = (2 * BN <= 256) ? 256 : 512;
@@ -284,6 +291,35 @@ struct TCfg {
   static_assert(kStages >= 3 && kStages <= 16, "pipeline depth");
   static_assert(!kPair || BN % 32 == 0, "pair mode: each CTA stages BN/2 rows of W, MMA N must be a multiple of 16");
   static_assert(GEGLU ? BN % 64 == 0 : BN % 32 == 0, "tile width vs output boxes");
+};
+
+#ifdef AFB_GEMM_PROFILE
+// developer probe (tools/gemm_probe.cu): cycles the MMA issuer and one epilogue warp of the first CTAs spend per phase
+__device__ long long* g_gemm_prof = nullptr;
+#define AFB_GPROF_DECL long long gp_t = clock64(); long long gp_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define AFB_GPROF(i) { const long long gp_n = clock64(); gp_acc[i] += gp_n - gp_t; gp_t = gp_n; }
+#define AFB_GPROF_FLUSH(slot) if (lane == 0 && g_gemm_prof != nullptr && blockIdx.x < 4) { for (int gi = 0; gi < 8; ++gi) g_gemm_prof[(blockIdx.x * 4 + (slot)) * 8 + gi] = gp_acc[gi]; }
+#else
+#define AFB_GPROF_DECL
+#define AFB_GPROF(i)
+#define AFB_GPROF_FLUSH(slot)
+#endif
+
+// tile = unit + i * num_units walked as (m_unit, n_blk): one division pair at the start instead of one per tile in
+// every warp role (~300 cycles per tile of the epilogue's serial path)
+struct TileWalk {
+  int tile, m_unit, n_blk, dq, dr, nnb, step;
+  __device__ TileWalk(int unit, int num_units, int nnb_)
+      : tile(unit), m_unit(unit / nnb_), n_blk(unit % nnb_), dq(num_units / nnb_), dr(num_units % nnb_), nnb(nnb_), step(num_units) {}
+  __device__ void next() {
+    tile += step;
+    m_unit += dq;
+    n_blk += dr;
+    if (n_blk >= nnb) {
+      n_blk -= nnb;
+      ++m_unit;
+    }
+  }
 };
 
 struct GemmTmaDev {
@@ -299,7 +335,7 @@ struct GemmTmaDev {
 };
 
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
-__global__ void __launch_bounds__(kTmaThreads, 1)
+__global__ void __launch_bounds__((TCfg<BN, GEGLU, kPair>::kThreads), 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_res,
                      const GemmTmaDev p) {
@@ -309,6 +345,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + C::kStages * C::kStageBytes;
   float* params = reinterpret_cast<float*>(staging + C::kStagingBytes);      // [2 buffers][bias BN | colsum BN]
+  float2* row_params = reinterpret_cast<float2*>(staging + C::kStagingBytes + C::kColParamBytes);   // [2 buffers][kBM]
   uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::kStagingBytes + C::kParamBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + C::kStages;
@@ -339,8 +376,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], kPair ? 16 : 8);      // pair: the leader's barrier collects both CTAs' epilogue warps
-      mbar_init(&out_free[i], 2);
+      mbar_init(&tmem_empty[i], (kPair ? 2 : 1) * C::kEpiWarps);      // pair: the leader collects both CTAs' epilogue warps
+      mbar_init(&out_free[i], C::kGroups);
       mbar_init(&res_full[i], 1);
     }
     fence_barrier_init();
@@ -356,16 +393,16 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   const uint32_t tmem_base = *tmem_slot;
 
   const int num_tiles = num_m_units * p.num_n_blocks;
-  auto tile_m_blk = [&](int tile) { return kPair ? 2 * (tile / p.num_n_blocks) + cta_rank : tile / p.num_n_blocks; };
+  auto walk_m_blk = [&](const TileWalk& t) { return kPair ? 2 * t.m_unit + cta_rank : t.m_unit; };
 
   if (warp == 0) {
     // ------------------------------------------------------------------ operand producer
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
-        const int m_blk = tile_m_blk(tile);
-        const int n_blk = tile % p.num_n_blocks;
+      for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next()) {
+        const int m_blk = walk_m_blk(t);
+        const int n_blk = t.n_blk;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
@@ -400,13 +437,16 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      AFB_GPROF_DECL
       for (int tile = unit; tile < num_tiles; tile += num_units) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
+        AFB_GPROF(0)
         const uint32_t tmem_d = tmem_base + acc * BN;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          AFB_GPROF(1)
           if (leader) {
             const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
             const uint64_t da = umma_desc_kmajor_sw128(sa);
@@ -420,6 +460,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             else umma_commit(&empty_bar[stage]);
           }
           __syncwarp();
+          AFB_GPROF(2)
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
@@ -435,36 +476,85 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           acc_phase ^= 1;
         }
       }
+      AFB_GPROF_FLUSH(0)
     }
   } else if (warp == 3) {
     // ------------------------------------------------------------------ staging manager
     // One tile ahead of the epilogue: copies the tile's column parameters (bias, LayerNorm column sums) into shared
     // memory -- every epilogue thread needs all of them, and 16-32 uniform LDG.128 per thread per box were its top
-    // stall -- and prefetches the residual boxes by TMA.
+    // stall --, reduces the producer GEMM's partial row sums to the LayerNorm (rstd, -mean * rstd) of the tile's rows
+    // (a dependent-load chain of ~2000 cycles per tile when the epilogue warps did it), and prefetches the residual
+    // boxes by TMA.
     int it = 0;
-    for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
+    for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next(), ++it) {
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
+      // global loads first -- they do not depend on the staging buffer and run ahead of the wait for it
+      constexpr int kColVecs = (BN / 4 + 31) / 32;           // float4 per lane covering the tile's BN columns
+      const int n_blk = t.n_blk;
+      float4 cb[kColVecs], cc[kColVecs];
+#pragma unroll
+      for (int u = 0; u < kColVecs; ++u) {
+        const int i = lane + 32 * u;
+        const int n0 = n_blk * BN + 4 * i;
+        cb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        cc[u] = cb[u];
+        if (i < BN / 4 && n0 < p.N) {
+          if (p.bias != nullptr) cb[u] = __ldg(reinterpret_cast<const float4*>(p.bias + n0));
+          if constexpr (kLn) cc[u] = __ldg(reinterpret_cast<const float4*>(p.ln_colsum + n0));
+        }
+      }
+      float2 rp[4];                                            // four rows per lane
+      if constexpr (kLn) {
+        const int m0 = walk_m_blk(t) * kBM;
+        const int nq = p.ln_parts >> 1;                        // parts is even: two (sum, sum of squares) partials per 16 bytes
+        const float inv_k = 1.0f / static_cast<float>(p.K);
+        float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int i0 = 0; i0 < nq; i0 += 4) {
+          float4 t[4][4];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const int m_row = min(m0 + r * 32 + lane, p.M - 1);
+            const float4* sp = reinterpret_cast<const float4*>(p.ln_stats + static_cast<long long>(m_row) * p.ln_parts * 2);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) t[r][i] = (i0 + i < nq) ? __ldg(sp + i0 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              s1[r] += t[r][i].x + t[r][i].z;
+              s2[r] += t[r][i].y + t[r][i].w;
+            }
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float mean = s1[r] * inv_k;
+          const float rstd = rsqrtf(fmaxf(s2[r] * inv_k - mean * mean, 0.f) + p.ln_eps);
+          rp[r] = make_float2(rstd, -mean * rstd);
+        }
+      }
       mbar_wait(&out_free[sb], (use & 1) ^ 1);
       {
-        const int n_blk = tile % p.num_n_blocks;
         float4* pb = reinterpret_cast<float4*>(params + sb * 2 * BN);
-        for (int i = lane; i < BN / 4; i += 32) {
-          const int n0 = n_blk * BN + 4 * i;
-          float4 b = make_float4(0.f, 0.f, 0.f, 0.f), c = b;
-          if (n0 < p.N) {
-            if (p.bias != nullptr) b = __ldg(reinterpret_cast<const float4*>(p.bias + n0));
-            if constexpr (kLn) c = __ldg(reinterpret_cast<const float4*>(p.ln_colsum + n0));
+#pragma unroll
+        for (int u = 0; u < kColVecs; ++u) {
+          const int i = lane + 32 * u;
+          if (i < BN / 4) {
+            pb[i] = cb[u];
+            if constexpr (kLn) pb[BN / 4 + i] = cc[u];
           }
-          pb[i] = b;
-          if constexpr (kLn) pb[BN / 4 + i] = c;
+        }
+        if constexpr (kLn) {
+#pragma unroll
+          for (int r = 0; r < 4; ++r) row_params[sb * kBM + r * 32 + lane] = rp[r];
         }
         __syncwarp();      // lane 0's arrive below publishes the whole warp's writes
       }
       if (lane == 0) {
         if (p.has_res) {
-          const int m_blk = tile_m_blk(tile);
-          const int n_blk = tile % p.num_n_blocks;
+          const int m_blk = walk_m_blk(t);
           int valid = 0;
 #pragma unroll
           for (int ch = 0; ch < NC; ++ch)
@@ -484,10 +574,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ epilogue
     const int q = warp & 3;                         // TMEM lane quarter
-    const int grp = (warp - 4) >> 2;                // column group 0 / 1
-    constexpr int kSplit = (NC + 1) / 2;
-    const int ch_lo = grp == 0 ? 0 : kSplit;
-    const int ch_hi = grp == 0 ? kSplit : NC;
+    const int grp = (warp - 4) >> 2;                // column group
+    const int ch_lo = (grp * NC) / C::kGroups;
+    const int ch_hi = ((grp + 1) * NC) / C::kGroups;
     const bool leader = (q == 0) && (lane == 0);    // issues this group's TMA stores
     const int row = q * 32 + lane;
     const uint32_t sw = static_cast<uint32_t>((row >> 1) & 3);
@@ -498,41 +587,35 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       if constexpr (kPair) mbar_arrive_cluster(&tmem_empty[a], 0);
       else mbar_arrive(&tmem_empty[a]);
     };
-    for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
-      const int m_blk = tile_m_blk(tile);
-      const int n_blk = tile % p.num_n_blocks;
+    AFB_GPROF_DECL
+    for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next(), ++it) {
+      const int m_blk = walk_m_blk(t);
+      const int n_blk = t.n_blk;
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       const int m_row = m_blk * kBM + row;
-      float ln_mean = 0.f, ln_rstd = 1.f;
-      if (kLn && m_row < p.M) {
-        // LayerNorm statistics of row m of A from the producer GEMM's partial sums; read BEFORE waiting for the
-        // accumulator so that the latency hides behind this tile's MMAs (parts is even: two partials per 16 bytes)
-        const float4* sp = reinterpret_cast<const float4*>(p.ln_stats + static_cast<long long>(m_row) * p.ln_parts * 2);
-        float s1 = 0.f, s2 = 0.f;
-        const int nq = p.ln_parts >> 1;
-#pragma unroll 4
-        for (int i = 0; i < nq; ++i) {
-          const float4 t = __ldg(sp + i);
-          s1 += t.x + t.z;
-          s2 += t.y + t.w;
-        }
-        const float inv_k = 1.0f / static_cast<float>(p.K);
-        ln_mean = s1 * inv_k;
-        ln_rstd = rsqrtf(fmaxf(s2 * inv_k - ln_mean * ln_mean, 0.f) + p.ln_eps);
-      }
+      AFB_GPROF(0)
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
+      AFB_GPROF(1)
       if (leader) {
         // the stores of the previous tile (other staging buffer) have certainly been issued: once they have
         // finished reading shared memory, hand that buffer back to the staging manager
         bulk_wait_group_read<0>();
         if (it > 0) mbar_arrive(&out_free[sb ^ 1]);
       }
+      AFB_GPROF(2)
       mbar_wait(&res_full[sb], use & 1);
+      AFB_GPROF(3)
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
       bool released = false;
-      const float ln_nm = -ln_mean * ln_rstd;      // rstd * (acc - mean * cs) = rstd * acc + ln_nm * cs
+      // LayerNorm fold: rstd * (acc - mean * colsum) = rstd * acc + ln_nm * colsum
+      float ln_rstd = 1.f, ln_nm = 0.f;
+      if constexpr (kLn) {
+        const float2 rp = row_params[sb * kBM + row];
+        ln_rstd = rp.x;
+        ln_nm = rp.y;
+      }
       float st_s1 = 0.f, st_s2 = 0.f;
 #pragma unroll 1
       for (int ch = ch_lo; ch < ch_hi; ++ch) {
@@ -542,45 +625,60 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         // this box's column parameters (shared memory, same address in every lane: broadcast reads)
         const uint32_t pbias = smem_u32(params + sb * 2 * BN + (n_acc0 - n_blk * BN));
         const uint32_t pcs = pbias + BN * 4;
+        // staging box [128 rows][32 cols] bf16, 64-byte rows, SWIZZLE_64B: 16-byte chunk c of row r sits at c ^ ((r >> 1) & 3)
+        uint8_t* brow = staging + (sb * NC + ch) * kBoxBytes + row * 64;
         uint32_t pk[16];                                // the box row: 32 bf16
         float v[32];
         if constexpr (GEGLU) {
-          uint32_t ra[32], rg[32];
-          tmem_ld32(taddr + ch * 64, ra);
-          tmem_ld32(taddr + ch * 64 + 32, rg);
-          tmem_ld_wait();
-          if (ch == ch_hi - 1 || n_acc0 + 64 >= p.N) {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) release_acc(acc);
-            released = true;
-          }
           const uint64_t rstd2 = pack_f32x2(ln_rstd, ln_rstd), nm2 = pack_f32x2(ln_nm, ln_nm);
+          // Eight output columns at a time, the next eight already in flight: the TMEM read port moves 64 B per clock
+          // per SM (2048 cycles for a 128 x 256 fp32 tile), so the loads of all sixteen warps have to overlap the
+          // arithmetic instead of alternating with it.  Two register stages of 8 + 8 fit the 96-register budget.
+          uint32_t ra[2][8], rg[2][8];
+          tmem_ld8(taddr + ch * 64, ra[0]);
+          tmem_ld8(taddr + ch * 64 + 32, rg[0]);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 ba = lds128(pbias + 16 * j), bg = lds128(pbias + 16 * (8 + j));
-            uint64_t a01 = pack_f32x2(__uint_as_float(ra[4 * j + 0]), __uint_as_float(ra[4 * j + 1]));
-            uint64_t a23 = pack_f32x2(__uint_as_float(ra[4 * j + 2]), __uint_as_float(ra[4 * j + 3]));
-            uint64_t g01 = pack_f32x2(__uint_as_float(rg[4 * j + 0]), __uint_as_float(rg[4 * j + 1]));
-            uint64_t g23 = pack_f32x2(__uint_as_float(rg[4 * j + 2]), __uint_as_float(rg[4 * j + 3]));
-            if constexpr (kLn) {
-              // rstd * (acc - mean * colsum) + bias = rstd * acc + (ln_nm * colsum + bias)
-              const float4 ca = lds128(pcs + 16 * j), cg = lds128(pcs + 16 * (8 + j));
-              a01 = ffma2(rstd2, a01, ffma2(nm2, pack_f32x2(ca.x, ca.y), pack_f32x2(ba.x, ba.y)));
-              a23 = ffma2(rstd2, a23, ffma2(nm2, pack_f32x2(ca.z, ca.w), pack_f32x2(ba.z, ba.w)));
-              g01 = ffma2(rstd2, g01, ffma2(nm2, pack_f32x2(cg.x, cg.y), pack_f32x2(bg.x, bg.y)));
-              g23 = ffma2(rstd2, g23, ffma2(nm2, pack_f32x2(cg.z, cg.w), pack_f32x2(bg.z, bg.w)));
-            } else {
-              a01 = fadd2(a01, pack_f32x2(ba.x, ba.y));
-              a23 = fadd2(a23, pack_f32x2(ba.z, ba.w));
-              g01 = fadd2(g01, pack_f32x2(bg.x, bg.y));
-              g23 = fadd2(g23, pack_f32x2(bg.z, bg.w));
+          for (int qt = 0; qt < 4; ++qt) {
+            const int cur = qt & 1;
+            tmem_ld_wait_on(ra[cur], rg[cur]);
+            AFB_GPROF(6)
+            if (qt < 3) {
+              tmem_ld8(taddr + ch * 64 + (qt + 1) * 8, ra[cur ^ 1]);
+              tmem_ld8(taddr + ch * 64 + 32 + (qt + 1) * 8, rg[cur ^ 1]);
+            } else if (ch == ch_hi - 1 || n_acc0 + 64 >= p.N) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) release_acc(acc);
+              released = true;
             }
-            float o0, o1, o2, o3;
-            unpack_f32x2(geglu_x2(a01, g01), o0, o1);
-            unpack_f32x2(geglu_x2(a23, g23), o2, o3);
-            pk[2 * j] = cvt_bf16x2(o0, o1);
-            pk[2 * j + 1] = cvt_bf16x2(o2, o3);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const int jj = qt * 2 + j;
+              const float4 ba = lds128(pbias + 16 * jj), bg = lds128(pbias + 16 * (8 + jj));
+              uint64_t a01 = pack_f32x2(__uint_as_float(ra[cur][4 * j + 0]), __uint_as_float(ra[cur][4 * j + 1]));
+              uint64_t a23 = pack_f32x2(__uint_as_float(ra[cur][4 * j + 2]), __uint_as_float(ra[cur][4 * j + 3]));
+              uint64_t g01 = pack_f32x2(__uint_as_float(rg[cur][4 * j + 0]), __uint_as_float(rg[cur][4 * j + 1]));
+              uint64_t g23 = pack_f32x2(__uint_as_float(rg[cur][4 * j + 2]), __uint_as_float(rg[cur][4 * j + 3]));
+              if constexpr (kLn) {
+                // rstd * (acc - mean * colsum) + bias = rstd * acc + (ln_nm * colsum + bias)
+                const float4 ca = lds128(pcs + 16 * jj), cg = lds128(pcs + 16 * (8 + jj));
+                a01 = ffma2(rstd2, a01, ffma2(nm2, pack_f32x2(ca.x, ca.y), pack_f32x2(ba.x, ba.y)));
+                a23 = ffma2(rstd2, a23, ffma2(nm2, pack_f32x2(ca.z, ca.w), pack_f32x2(ba.z, ba.w)));
+                g01 = ffma2(rstd2, g01, ffma2(nm2, pack_f32x2(cg.x, cg.y), pack_f32x2(bg.x, bg.y)));
+                g23 = ffma2(rstd2, g23, ffma2(nm2, pack_f32x2(cg.z, cg.w), pack_f32x2(bg.z, bg.w)));
+              } else {
+                a01 = fadd2(a01, pack_f32x2(ba.x, ba.y));
+                a23 = fadd2(a23, pack_f32x2(ba.z, ba.w));
+                g01 = fadd2(g01, pack_f32x2(bg.x, bg.y));
+                g23 = fadd2(g23, pack_f32x2(bg.z, bg.w));
+              }
+              float o0, o1, o2, o3;
+              unpack_f32x2(geglu_poly_x2(a01, g01), o0, o1);
+              unpack_f32x2(geglu_poly_x2(a23, g23), o2, o3);
+              pk[2 * j] = cvt_bf16x2(o0, o1);
+              pk[2 * j + 1] = cvt_bf16x2(o2, o3);
+            }
+            *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(qt) ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
           }
         } else {
           uint32_t r[32];
@@ -610,8 +708,6 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             unpack_f32x2(v23, v[4 * j + 2], v[4 * j + 3]);
           }
         }
-        // staging box [128 rows][32 cols] bf16, 64-byte rows, SWIZZLE_64B: 16-byte chunk c of row r sits at c ^ ((r >> 1) & 3)
-        uint8_t* brow = staging + (sb * NC + ch) * kBoxBytes + row * 64;
         if (!GEGLU && p.has_res) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -632,7 +728,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           for (int j = 0; j < 16; ++j) pk[j] = cvt_bf16x2(v[2 * j], v[2 * j + 1]);
         }
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < (GEGLU ? 0 : 4); ++c) {
           const uint4 pq = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
           *reinterpret_cast<uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4)) = pq;
           if constexpr (!GEGLU && kStats) {
@@ -644,8 +740,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           }
         }
         fence_proxy_async_smem();
+        AFB_GPROF(4)
         named_bar_sync(1 + grp, 128);
         if (leader) tma_store_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
+        AFB_GPROF(5)
       }
       if (!released) {
         tc_fence_before();
@@ -653,7 +751,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         if (lane == 0) release_acc(acc);
       }
       if (!GEGLU && kStats && m_row < p.M)
-        reinterpret_cast<float2*>(p.stats_out)[static_cast<long long>(m_row) * (2 * p.num_n_blocks) + 2 * n_blk + grp] =
+        reinterpret_cast<float2*>(p.stats_out)[static_cast<long long>(m_row) * (C::kGroups * p.num_n_blocks) + C::kGroups * n_blk + grp] =
             make_float2(st_s1, st_s2);
       if (leader) bulk_commit_group();
       if (++acc == 2) {
@@ -662,6 +760,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       }
     }
     if (leader) bulk_wait_group_read<0>();      // shared memory must outlive the last stores' reads
+    if (warp == 4) { AFB_GPROF_FLUSH(1) }
+    if (warp == 7) { AFB_GPROF_FLUSH(2) }
   }
 
   tc_fence_before();
@@ -730,7 +830,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
     const int pairs = tiles < num_sms() / 2 ? tiles : num_sms() / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * pairs);
-    cfg.blockDim = dim3(kTmaThreads);
+    cfg.blockDim = dim3(C::kThreads);
     cfg.dynamicSmemBytes = C::kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -744,7 +844,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   } else {
     const int tiles = p.num_m_blocks * p.num_n_blocks;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    kern<<<grid, kTmaThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, tm_out, tm_res, p);
+    kern<<<grid, C::kThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, tm_out, tm_res, p);
   }
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
