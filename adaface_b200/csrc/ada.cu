@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(kPoolThreads) ada_qfinish_kernel(const float* 
 __host__ __device__ inline long long pool_partial_floats(int C) { return 16 + 2ll * C; }
 
 template <int kChunks>
-__global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
+__global__ void __launch_bounds__(kPoolThreads, (kChunks <= 2 ? 2 : 1)) ada_pool_main_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
     const uint8_t* __restrict__ key_mask, float* __restrict__ scores, float* __restrict__ partials, int N, int C,
     int tokens_per_block) {
@@ -174,18 +174,36 @@ __global__ void __launch_bounds__(kPoolThreads) ada_pool_main_kernel(
   float* my_part = s_part + warp * 2 * (kChunks * 32);
   const int t_begin = blk * tokens_per_block;
   const int t_end = min(N, t_begin + tokens_per_block);
-  for (int t = t_begin + warp; t < t_end; t += kPoolWarps) {
+  // The per-token chain (two warp reductions, the head dots through shared memory, the softmax update) is long and
+  // serial, and a warp has one token in flight: the next token's rows are requested before the current one is
+  // processed, or the loop runs at one DRAM latency per token (kChunks == 5 has no registers left for it).
+  constexpr bool kPrefetch = kChunks <= 3;
+  uint4 nx[kChunks], nq[kChunks];
+  auto load_rows = [&](int t, uint4 (&dx)[kChunks], uint4 (&dq)[kChunks]) {
     const long long rowoff = (static_cast<long long>(b) * N + t) * C;
     const uint4* xr = reinterpret_cast<const uint4*>(x + rowoff);
     const uint4* qr = reinterpret_cast<const uint4*>(q + rowoff);
-    uint4 ux[kChunks], uq[kChunks];
 #pragma unroll
     for (int i = 0; i < kChunks; ++i) {
       const int ch = lane + 32 * i;
       if (ch < nchunks) {
-        ux[i] = xr[ch];
-        uq[i] = qr[ch];
+        dx[i] = xr[ch];
+        dq[i] = qr[ch];
       }
+    }
+  };
+  if (kPrefetch && t_begin + warp < t_end) load_rows(t_begin + warp, nx, nq);
+  for (int t = t_begin + warp; t < t_end; t += kPoolWarps) {
+    uint4 ux[kChunks], uq[kChunks];
+    if constexpr (kPrefetch) {
+#pragma unroll
+      for (int i = 0; i < kChunks; ++i) {
+        ux[i] = nx[i];
+        uq[i] = nq[i];
+      }
+      if (t + kPoolWarps < t_end) load_rows(t + kPoolWarps, nx, nq);
+    } else {
+      load_rows(t, ux, uq);
     }
     float xv[kChunks][8], qv[kChunks][8];
     float s = 0.f;
@@ -473,9 +491,12 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
   }
 }
 
-int pool_blocks_per_sample(int batch, int n_tokens) {
-  // ~2 waves of blocks over the GPU, at least 8 tokens (one per warp) per block
-  int want = (2 * num_sms() + batch - 1) / batch;
+int pool_blocks_per_sample(int batch, int n_tokens, int channels) {
+  // ONE wave of blocks over the GPU (the main kernel fits two blocks per SM up to 512 channels, one above: its
+  // registers hold the running sums of all channels), at least 8 tokens (one per warp) per block.  A second wave
+  // would only add block prologues and warp merges: the token loop is latency-bound, not occupancy-bound.
+  const int per_sm = channels <= 512 ? 2 : 1;
+  int want = per_sm * num_sms() / batch;
   int max_blocks = (n_tokens + 7) / 8;
   if (want > max_blocks) want = max_blocks;
   if (want < 1) want = 1;
@@ -537,7 +558,7 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
   AFB_REQUIRE((attn_fg == nullptr) == (attn_bg == nullptr), "afb_ada_pool: attn_fg and attn_bg must both be given or both NULL");
   AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) & 15) == 0, "afb_ada_pool: x/q must be 16-byte aligned");
   const int C = channels;
-  const int nblocks = pool_blocks_per_sample(batch, n_tokens);
+  const int nblocks = pool_blocks_per_sample(batch, n_tokens, channels);
   const int tokens_per_block = (n_tokens + nblocks - 1) / nblocks;
   const int grid_x = (n_tokens + tokens_per_block - 1) / tokens_per_block;
   float* scores = ws;
