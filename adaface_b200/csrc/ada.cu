@@ -154,6 +154,8 @@ __global__ void __launch_bounds__(kPoolThreads, (kChunks <= 2 ? 2 : 1)) ada_pool
   float* s_u = sh;                                      // [2][C] folded queries of this sample
   float* s_part = s_u + 2 * C;                          // [8 warps][2][kChunks * 32] per-chunk dots
   float* s_red = sh;                                    // [8 warps][16 + 2C], reuses the buffers after the token loop
+  pdl_wait();
+  pdl_trigger();
 
   const int dg = C / kHeads;
   const int b = blockIdx.y, blk = blockIdx.x;
@@ -350,6 +352,8 @@ __global__ void __launch_bounds__(256) ada_pool_combine_kernel(const float* __re
                                                                float* __restrict__ stats) {
   extern __shared__ float sh[];     // [nblocks][8] scales
   __shared__ float s_l[8];
+  pdl_wait();
+  pdl_trigger();
   const int b = blockIdx.x;
   const int dg = C / kHeads;
   const long long rec = pool_partial_floats(C);
@@ -418,6 +422,8 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
                                                        long long basis_sample_stride, int C, int TD, int K, int R, int D) {
   extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D]
   __shared__ float red[32];
+  pdl_wait();
+  pdl_trigger();
   const int k = blockIdx.x, b = blockIdx.y;
   const int F = 2 * C + TD;
   float* feat = sh;
@@ -581,16 +587,16 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
       AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh_main))); \
       set_for = sh_main;                                                                                                  \
     }                                                                                                                     \
-    kern<<<grid, kPoolThreads, sh_main, stream>>>(xb, qb, pool_q, key_mask, scores_arg, partials, n_tokens, C,            \
-                                                  tokens_per_block);                                                      \
+    AFB_CHECK_CUDA(launch_pdl(kern, grid, dim3(kPoolThreads), sh_main, stream, 1, xb, qb, pool_q, key_mask, scores_arg,     \
+                              partials, n_tokens, C, tokens_per_block));                                                  \
   }
   if (chunks_per_lane <= 2) AFB_LAUNCH_POOL(2)
   else if (chunks_per_lane <= 3) AFB_LAUNCH_POOL(3)
   else AFB_LAUNCH_POOL(kMaxChunksPerLane)
 #undef AFB_LAUNCH_POOL
   count_launch();
-  ada_pool_combine_kernel<<<dim3(batch, (2 * C + 255) / 256), 256, grid_x * 8 * sizeof(float), stream>>>(partials, grid_x, C, fg_out,
-                                                                                                         bg_out, stats);
+  AFB_CHECK_CUDA(launch_pdl(ada_pool_combine_kernel, dim3(batch, (2 * C + 255) / 256), dim3(256), grid_x * 8 * sizeof(float), stream, 1,
+                            partials, grid_x, C, fg_out, bg_out, stats));
   count_launch();
   if (attn_fg != nullptr) {
     const long long total = static_cast<long long>(batch) * kHeads * 2 * n_tokens;
@@ -618,10 +624,9 @@ extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, cons
   AFB_REQUIRE((ctx_out == nullptr) == (token_pos == nullptr), "afb_ada_head: ctx_out and token_pos go together");
   const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>((r + 3) & ~3) + out_dim) * sizeof(float);
   AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head: feature vector too large for one block (%zu bytes)", sh);
-  ada_head_kernel<<<dim3(num_vectors, batch), 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias,
-                                                                 out, reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos,
-                                                                 ctx_sample_stride, basis_sample_stride, channels, td, num_vectors, r,
-                                                                 out_dim);
+  AFB_CHECK_CUDA(launch_pdl(ada_head_kernel, dim3(num_vectors, batch), dim3(256), sh, stream, 1, infeat_fg, infeat_bg, time_emb,
+                            time_ld, coeff_w, coeff_b, basis, bias, out, reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos,
+                            ctx_sample_stride, basis_sample_stride, channels, td, num_vectors, r, out_dim));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -157,6 +157,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();        // Q/K/V come from the previous kernel; the set-up above overlapped its tail
+  pdl_trigger();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -494,7 +496,7 @@ int launch_attn_kernel(const CUtensorMap& tm_q, const CUtensorMap& tm_k, const C
     AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
-  kern<<<grid, C::kThreads, C::kSmemBytes, stream>>>(tm_q, tm_k, tm_v, p);
+  AFB_CHECK_CUDA(launch_pdl(kern, grid, dim3(C::kThreads), C::kSmemBytes, stream, 1, tm_q, tm_k, tm_v, p));
   return 0;
 }
 

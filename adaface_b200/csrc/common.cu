@@ -1,6 +1,7 @@
 // Host-side plumbing of the C ABI: thread-local error message, device query, launch counter and TMA
 // tensor-map construction through the driver entry point (no link-time dependency on libcuda).
 #include "common.cuh"
+#include <stdlib.h>
 #include "../../include/adaface_b200.h"
 
 #include <atomic>
@@ -40,6 +41,14 @@ void set_error(const char* fmt, ...) {
 }
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
 
 int num_sms() {
   static int sms = 0;

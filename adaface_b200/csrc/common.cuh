@@ -43,6 +43,47 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
 
 #ifdef __CUDACC__
 // ----------------------------------------------------------------------------------------------
+// Host: launches with programmatic dependent launch (PDL).  A kernel launched through launch_pdl may START while
+// its predecessor in the stream is still running (once every predecessor CTA has executed pdl_trigger() or exited);
+// it MUST execute pdl_wait() before it reads or writes global memory -- pdl_wait() returns when the predecessor
+// grid has completed and its writes are visible.  What runs before the wait (barrier init, TMEM allocation,
+// descriptor prefetch, smem carve-up) overlaps the predecessor's tail, and the launch latency disappears from the
+// stream's critical path; inside a captured CUDA graph the edge becomes a programmatic dependency.
+// AFB_PDL=0 in the environment turns the attribute off (plain stream order) for A/B measurements.
+// ----------------------------------------------------------------------------------------------
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster_x,
+                       Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = static_cast<unsigned>(cluster_x);
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// ----------------------------------------------------------------------------------------------
 // Device helpers
 // ----------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

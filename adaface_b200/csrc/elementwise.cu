@@ -84,6 +84,8 @@ __global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16*
 __global__ void __launch_bounds__(256) add_bias_residual_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
                                                                 const float* __restrict__ bias, uint4* __restrict__ out,
                                                                 long long nvec, int vpr) {
+  pdl_wait();
+  pdl_trigger();
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
     const uint4 ua = a[i];
@@ -187,8 +189,9 @@ extern "C" int afb_add_bias_residual(const afb_bf16* a, const afb_bf16* b, const
                         reinterpret_cast<uintptr_t>(bias);
   AFB_REQUIRE((all & 15) == 0, "afb_add_bias_residual: buffers must be 16-byte aligned");
   const long long nvec = static_cast<long long>(rows) * (channels / 8);
-  add_bias_residual_kernel<<<stream_grid(nvec), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), bias, reinterpret_cast<uint4*>(out), nvec, channels / 8);
+  AFB_CHECK_CUDA(launch_pdl(add_bias_residual_kernel, dim3(stream_grid(nvec)), dim3(256), 0, static_cast<cudaStream_t>(stream_), 1,
+                            reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), bias,
+                            reinterpret_cast<uint4*>(out), nvec, channels / 8));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

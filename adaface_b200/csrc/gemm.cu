@@ -86,6 +86,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  pdl_trigger();
 
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;
 
@@ -391,6 +393,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   if constexpr (kPair) cluster_sync_relaxed();  // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above touched only this CTA's shared memory / TMEM and overlapped the previous kernel's tail
+  pdl_wait();
+  pdl_trigger();
 
   const int num_tiles = num_m_units * p.num_n_blocks;
   auto walk_m_blk = [&](const TileWalk& t) { return kPair ? 2 * t.m_unit + cta_rank : t.m_unit; };
@@ -825,27 +830,16 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
     AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
+  int grid;
   if constexpr (kPair) {
     const int tiles = ((p.num_m_blocks + 1) / 2) * p.num_n_blocks;
     const int pairs = tiles < num_sms() / 2 ? tiles : num_sms() / 2;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * pairs);
-    cfg.blockDim = dim3(C::kThreads);
-    cfg.dynamicSmemBytes = C::kSmemBytes;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    AFB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_a, tm_w, tm_out, tm_res, p));
+    grid = 2 * pairs;
   } else {
     const int tiles = p.num_m_blocks * p.num_n_blocks;
-    const int grid = tiles < num_sms() ? tiles : num_sms();
-    kern<<<grid, C::kThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, tm_out, tm_res, p);
+    grid = tiles < num_sms() ? tiles : num_sms();
   }
+  AFB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(C::kThreads), C::kSmemBytes, stream, kPair ? 2 : 1, tm_a, tm_w, tm_out, tm_res, p));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -922,7 +916,7 @@ int launch(const afb_gemm_args& a, cudaStream_t stream) {
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tm_a, tm_w, p);
+  AFB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), C::kSmemBytes, stream, 1, tm_a, tm_w, p));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

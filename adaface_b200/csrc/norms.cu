@@ -139,6 +139,8 @@ __global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloa
                                                              int pre_add_ld, float* __restrict__ partial, int C, int HW,
                                                              int cpg, int T, int nchunks) {
   __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
+  pdl_wait();
+  pdl_trigger();
   const int b = blockIdx.y, chunk = blockIdx.x;
   const int t0 = chunk * T;
   const int nt = min(T, HW - t0);
@@ -230,6 +232,8 @@ __global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat1
                                                            __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int T,
                                                            int nchunks, float eps) {
   __shared__ float s_mean[kGnMaxGroups], s_rstd[kGnMaxGroups];
+  pdl_wait();
+  pdl_trigger();
   const int b = blockIdx.y;
   const int t0 = blockIdx.x * T;
   const int nt = min(T, HW - t0);
@@ -321,6 +325,8 @@ __global__ void __launch_bounds__(320, 1) gn_cluster_tok_kernel(const __nv_bfloa
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   extern __shared__ __align__(128) uint8_t gn_smem[];
+  pdl_wait();
+  pdl_trigger();
   __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
   __shared__ float s_part[2 * kGnMaxGroups];            // this CTA's (mean, M2) per group, read by the whole cluster
   __shared__ float s_mean[kGnMaxGroups], s_rstd[kGnMaxGroups];
@@ -461,19 +467,8 @@ int launch_gn_cluster(const __nv_bfloat16* x, const float* gamma, const float* b
     AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGnClusterMaxSmem));
     attr_set = true;
   }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(kGnCluster, batch, 1);
-  cfg.blockDim = dim3(threads, 1, 1);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kGnCluster;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  AFB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, x, gamma, beta, pre_add, pre_add_ld, y, C, HW, cpg, T, eps));
+  AFB_CHECK_CUDA(launch_pdl(kern, dim3(kGnCluster, batch, 1), dim3(threads, 1, 1), smem, stream, kGnCluster, x, gamma, beta,
+                            pre_add, pre_add_ld, y, C, HW, cpg, T, eps));
   return 0;
 }
 
@@ -627,10 +622,11 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
       count_launch();
       return 0;
     }
-    gn_partial_tok_kernel<<<grid, geo.threads, 0, stream>>>(xb, pre_add, pre_add_ld, partial, channels, hw, cpg, geo.T, geo.nchunks);
+    AFB_CHECK_CUDA(launch_pdl(gn_partial_tok_kernel, grid, dim3(geo.threads), 0, stream, 1, xb, pre_add, pre_add_ld, partial, channels, hw,
+                              cpg, geo.T, geo.nchunks));
     count_launch();
-    if (act) gn_apply_tok_kernel<true><<<grid, geo.threads, 0, stream>>>(xb, partial, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T, geo.nchunks, eps);
-    else gn_apply_tok_kernel<false><<<grid, geo.threads, 0, stream>>>(xb, partial, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T, geo.nchunks, eps);
+    AFB_CHECK_CUDA(launch_pdl(act ? gn_apply_tok_kernel<true> : gn_apply_tok_kernel<false>, grid, dim3(geo.threads), 0, stream, 1, xb,
+                              partial, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T, geo.nchunks, eps));
     count_launch();
   } else {
     AFB_FAIL(2, "afb_groupnorm_tokens: unknown x_layout %d", x_layout);
