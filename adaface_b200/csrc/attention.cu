@@ -55,6 +55,10 @@ struct AttnDev {
 #define AFB_PROF(idx) do { } while (0)
 #endif
 
+#ifndef AFB_ATTN_STAGGER
+#define AFB_ATTN_STAGGER 0
+#endif
+
 template <int D>
 struct AttnCfg {
   static constexpr int kQTiles = (D <= 40) ? 4 : 2;            // query tiles (= softmax warps per sub-partition)
@@ -332,6 +336,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     const uint64_t sc2 = pack_f32x2(sc, sc);
     const uint8_t* mask_row = kHasMask ? p.key_mask + static_cast<long long>(b) * p.kv_len : nullptr;
 
+#if AFB_ATTN_STAGGER > 0
+    // De-phase the query tiles: the four softmax warps of an SM sub-partition (one per tile) would otherwise walk
+    // the KV loop in step -- all in the exponential phase (MUFU saturated) or all outside it (MUFU idle).
+    if (t > 0) {
+      const long long t0 = clock64();
+      while (clock64() - t0 < static_cast<long long>(t) * AFB_ATTN_STAGGER) {}
+    }
+#endif
     for (int j = 0; j < num_kv_tiles; ++j) {
       AFB_PROF(7);
       mbar_wait(&s_full[t], j & 1);

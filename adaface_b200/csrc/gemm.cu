@@ -334,6 +334,9 @@ struct GemmTmaDev {
   const float* ln_colsum;    // [N]
   int ln_parts;
   float ln_eps;
+  // 3x3 convolution as an implicit GEMM: A is the NHWC image [B, H, W, Cin] behind a 4-D tensor map, the K loop
+  // walks (tap, 64-channel block); conv_cblocks = Cin / 64 (0: plain GEMM)
+  int conv_cblocks, conv_h, conv_w;
 };
 
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
@@ -408,6 +411,16 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next()) {
         const int m_blk = walk_m_blk(t);
         const int n_blk = t.n_blk;
+        // convolution: the tile's 128 rows are the pixel box (b0.., h0.., w0..) of the image; tap (dy, dx) of the
+        // filter reads the same box shifted by (dy, dx), out-of-image pixels zero-filled by TMA (= zero padding)
+        int cw0 = 0, ch0 = 0, cb0 = 0, cblk = 0, dy = -1, dx = -1;
+        if (p.conv_cblocks != 0) {
+          const int m0 = m_blk * kBM;
+          const int r = m0 / p.conv_w;
+          cw0 = m0 - r * p.conv_w;
+          cb0 = r / p.conv_h;
+          ch0 = r - cb0 * p.conv_h;
+        }
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
@@ -416,12 +429,21 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             // both CTAs' bytes are counted on the leader's barrier; the peer's may land before the leader arms the
             // phase (the pending arrival keeps it open), never before the previous phase closed (empty_bar)
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
-            tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            if (p.conv_cblocks != 0) tma_load_4d_pair(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
+            else tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
             tma_load_2d_pair(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN + cta_rank * C::kBRows, kEvictLast);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
-            tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            if (p.conv_cblocks != 0) tma_load_4d(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
+            else tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
             tma_load_2d(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN, kEvictLast);
+          }
+          if (p.conv_cblocks != 0 && ++cblk == p.conv_cblocks) {
+            cblk = 0;
+            if (++dx == 2) {
+              dx = -1;
+              ++dy;
+            }
           }
           if (++stage == C::kStages) {
             stage = 0;
@@ -789,7 +811,18 @@ template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
 int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   using C = TCfg<BN, GEGLU, kPair>;
   CUtensorMap tm_a, tm_w, tm_out, tm_res;
-  {
+  if (a.conv_h > 0) {
+    // NHWC image [B, H, W, Cin], pixel stride lda; the box is 128 consecutive pixels in (b, h, w) order
+    const uint64_t cin = static_cast<uint64_t>(a.k / 9), W = static_cast<uint64_t>(a.conv_w), H = static_cast<uint64_t>(a.conv_h);
+    const uint32_t bw = static_cast<uint32_t>(W < kBM ? W : kBM);
+    const uint32_t bh = static_cast<uint32_t>(H < kBM / bw ? H : kBM / bw);
+    const uint64_t dims[4] = {cin, W, H, static_cast<uint64_t>(a.m) / (W * H)};
+    const uint64_t strides[3] = {static_cast<uint64_t>(a.lda) * 2, static_cast<uint64_t>(a.lda) * 2 * W,
+                                 static_cast<uint64_t>(a.lda) * 2 * W * H};
+    const uint32_t box[4] = {kBK, bw, bh, kBM / (bw * bh)};
+    if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.a, dims, strides, box, Swizzle::B128))
+      return rc;
+  } else {
     const uint64_t dims[2] = {static_cast<uint64_t>(a.k), static_cast<uint64_t>(a.m)};
     const uint64_t strides[1] = {static_cast<uint64_t>(a.lda) * 2};
     const uint32_t box[2] = {kBK, kBM};
@@ -824,6 +857,9 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   p.ln_colsum = a.ln_colsum;
   p.ln_parts = a.ln_parts;
   p.ln_eps = a.ln_eps;
+  p.conv_cblocks = a.conv_h > 0 ? static_cast<int>(a.k / 9 / kBK) : 0;
+  p.conv_h = a.conv_h;
+  p.conv_w = a.conv_w;
   auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats, kPair>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -943,7 +979,23 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
   AFB_REQUIRE(a.lda % 8 == 0 && a.ldw % 8 == 0, "afb_gemm_bf16: lda/ldw must be multiples of 8 elements (TMA 16B strides)");
   AFB_REQUIRE((reinterpret_cast<uintptr_t>(a.a) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.w) & 15) == 0,
               "afb_gemm_bf16: operands must be 16-byte aligned");
-  AFB_REQUIRE(a.lda >= a.k && a.ldw >= a.k, "afb_gemm_bf16: leading dimension smaller than K");
+  if (a.conv_h > 0 || a.conv_w > 0) {
+    // 3x3 / stride 1 / zero padding 1 convolution as an implicit GEMM (openaimodel.py:203-205,236-238)
+    const int64_t hw = static_cast<int64_t>(a.conv_h) * a.conv_w;
+    AFB_REQUIRE(a.conv_h > 0 && a.conv_w > 0 && a.m % hw == 0, "afb_gemm_bf16: conv needs conv_h, conv_w > 0 and M = B*H*W");
+    AFB_REQUIRE(a.k % (9 * 64) == 0, "afb_gemm_bf16: conv needs K = 9 * Cin with Cin %% 64 == 0 (K=%lld)", (long long)a.k);
+    AFB_REQUIRE(a.lda >= a.k / 9 && a.ldw >= a.k, "afb_gemm_bf16: conv leading dimension smaller than Cin / K");
+    const int W = a.conv_w, H = a.conv_h;
+    const int bw = W < 128 ? W : 128;
+    AFB_REQUIRE(W < 128 ? 128 % W == 0 : W % 128 == 0, "afb_gemm_bf16: conv width %d does not tile into 128-pixel boxes", W);
+    const int rl = 128 / bw;
+    AFB_REQUIRE(H < rl ? rl % H == 0 : H % rl == 0, "afb_gemm_bf16: conv height %d does not tile into 128-pixel boxes", H);
+    AFB_REQUIRE(a.epilogue == AFB_EPI_STORE && a.out_dtype == AFB_BF16 && (a.residual == nullptr || a.residual_dtype == AFB_BF16) &&
+                    a.ln_stats == nullptr && a.row_stats_out == nullptr,
+                "afb_gemm_bf16: conv mode takes the bf16 STORE epilogue (bias, bf16 residual) only");
+  } else {
+    AFB_REQUIRE(a.lda >= a.k && a.ldw >= a.k, "afb_gemm_bf16: leading dimension smaller than K");
+  }
   AFB_REQUIRE(a.n % 32 == 0, "afb_gemm_bf16: N=%lld must be a multiple of 32", (long long)a.n);
   AFB_REQUIRE((reinterpret_cast<uintptr_t>(a.out) & 15) == 0, "afb_gemm_bf16: out must be 16-byte aligned");
   AFB_REQUIRE(a.bias == nullptr || (reinterpret_cast<uintptr_t>(a.bias) & 15) == 0, "afb_gemm_bf16: bias must be 16-byte aligned");

@@ -141,7 +141,7 @@ def _(x, gamma, beta, eps):
 # ------------------------------------------------------------------------------------------- GEMMs
 def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], epilogue: int,
           ldo: int, ldr: int, hw: int = 0, stats_out: Optional[Tensor] = None, ln_stats: Optional[Tensor] = None,
-          ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0) -> None:
+          ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0, conv_hw: Optional[Tuple[int, int]] = None) -> None:
     _need_cuda(a, w, out, bias, residual, stats_out, ln_stats, ln_colsum)
     if ln_stats is not None:
         if ln_colsum is None or ln_stats.dtype != torch.float32 or ln_colsum.dtype != torch.float32 \
@@ -153,15 +153,37 @@ def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: O
     if bias is not None and bias.dtype != torch.float32:
         raise ValueError("gemm: bias must be fp32")
     args = GemmArgs(a=_ptr(a), w=_ptr(w), out=_ptr(out), bias=_ptr(bias), residual=_ptr(residual),
-                    m=a.shape[0], n=w.shape[0], k=a.shape[1], lda=a.stride(0), ldw=w.stride(0), ldo=ldo, ldr=ldr,
+                    m=a.shape[0], n=w.shape[0], k=w.shape[1] if conv_hw else a.shape[1], lda=a.stride(0), ldw=w.stride(0),
+                    ldo=ldo, ldr=ldr, conv_h=conv_hw[0] if conv_hw else 0, conv_w=conv_hw[1] if conv_hw else 0,
                     epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
                     residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
                     else _lib.DT_BF16, hw=hw, row_stats_out=_ptr(stats_out), ln_stats=_ptr(ln_stats),
                     ln_colsum=_ptr(ln_colsum), ln_parts=0 if ln_stats is None else ln_stats.shape[1], ln_eps=ln_eps)
-    m, n, k = a.shape[0], w.shape[0], a.shape[1]
-    _run("gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
-         nbytes=2.0 * (m * k + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
+    m, n, k = a.shape[0], w.shape[0], w.shape[1] if conv_hw else a.shape[1]
+    _run("conv3x3_bf16" if conv_hw else "gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
+         nbytes=2.0 * (m * a.shape[1] + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
          + ("r" if residual is not None else ""))
+
+
+@torch.library.custom_op("adaface_b200::conv3x3", mutates_args=())
+def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], h: int, width: int) -> Tensor:
+    """3x3 / stride 1 / zero-padding 1 convolution as an implicit GEMM on the tcgen05 GEMM kernel (ResBlock and
+    Upsample convolutions, openaimodel.py:95-123,203-205,236-238).  x: bf16 NHWC pixels [B*h*width, Cin];
+    w: bf16 [Cout, 9*Cin] = the channels-last memory of the Conv2d weight (k = (ky*3 + kx)*Cin + c); bias fp32
+    [Cout]; residual bf16 [B*h*width, Cout].  Returns bf16 [B*h*width, Cout] (NHWC)."""
+    if x.dim() != 2 or w.dim() != 2 or w.shape[1] != 9 * x.shape[1] or x.shape[0] % (h * width) != 0:
+        raise ValueError("conv3x3: x [B*h*w, Cin] and w [Cout, 9*Cin] expected")
+    out = torch.empty((x.shape[0], w.shape[0]), dtype=torch.bfloat16, device=x.device)
+    if residual is not None and (residual.shape != out.shape or residual.stride(-1) != 1 or residual.dtype != torch.bfloat16):
+        raise ValueError("conv3x3: residual must be bf16 [B*h*w, Cout] with contiguous rows")
+    _gemm(x, w, out, bias, residual, _lib.EPI_STORE, out.stride(0), 0 if residual is None else residual.stride(0),
+          conv_hw=(h, width))
+    return out
+
+
+@conv3x3.register_fake
+def _(x, w, bias, residual, h, width):
+    return x.new_empty((x.shape[0], w.shape[0]), dtype=torch.bfloat16)
 
 
 @torch.library.custom_op("adaface_b200::linear", mutates_args=())

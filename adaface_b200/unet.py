@@ -14,6 +14,7 @@ Activations between blocks are bf16 channels-last: a [B, C, H, W] channels-last 
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -26,6 +27,7 @@ from .embedding import LAYER_IDX2CA_LAYER_IDX, AdaEmbedding
 
 Tensor = torch.Tensor
 CL = torch.channels_last
+_NATIVE_CONV = os.environ.get("AFB_CONV", "1") != "0"
 
 
 def timestep_embedding(timesteps: Tensor, dim: int, max_period: int = 10000) -> Tensor:
@@ -89,15 +91,51 @@ class _Bf16Conv(nn.Conv2d):
             self.__dict__["_bf16_cache"] = c
         return c[1], c[2]
 
+    def native_ok(self, x) -> bool:
+        """3x3 / stride 1 / padding 1 with Cin % 64 == 0 on an image that tiles into 128-pixel boxes: runs as an
+        implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3) instead of cuDNN.  AFB_CONV=0 turns it off."""
+        if not _NATIVE_CONV or self.kernel_size != (3, 3) or self.stride != (1, 1) or self.padding != (1, 1) \
+                or self.dilation != (1, 1) or self.groups != 1:
+            return False
+        _, c, h, w = x.shape
+        if c % 64 or self.out_channels % 32 or x.dtype != torch.bfloat16 or not x.is_cuda:
+            return False
+        bw = min(w, 128)
+        rl = 128 // bw
+        return (128 % w == 0 if w < 128 else w % 128 == 0) and (rl % h == 0 if h < rl else h % rl == 0)
+
+    def _w_native(self):
+        """bf16 [Cout, 9*Cin] with k = (ky*3 + kx)*Cin + c: the channels-last memory of the Conv2d weight."""
+        key = (self.weight.data_ptr(), self.weight._version)
+        c = self.__dict__.get("_native_cache")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                w = self.weight.detach().permute(0, 2, 3, 1).reshape(self.out_channels, -1).to(torch.bfloat16).contiguous()
+                b = None if self.bias is None else self.bias.detach().float().contiguous()
+            c = (key, w, b)
+            self.__dict__["_native_cache"] = c
+        return c[1], c[2]
+
+    def native(self, x, bias: Optional[Tensor], residual: Optional[Tensor]):
+        """conv(x) + bias + residual in one kernel: x, residual bf16 channels-last [B, C, H, W]."""
+        b, c, h, w = x.shape
+        wn, _ = self._w_native()
+        xt = x.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b * h * w, c)
+        rt = None if residual is None else residual.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b * h * w, -1)
+        y = ops.conv3x3(xt, wn, bias, rt, h, w)
+        return y.view(b, h, w, self.out_channels).permute(0, 3, 1, 2)
+
     def forward(self, x, with_bias: bool = True):
+        if self.native_ok(x):
+            return self.native(x, self._w_native()[1] if with_bias else None, None)
         w, b = self._w()
         return F.conv2d(x, w, b if with_bias else None, self.stride, self.padding)
 
     def conv_add(self, x):
         """conv(x) + bias with the bias added by one vectorised pass (torch adds a cuDNN conv's bias with a slow
         broadcasting elementwise kernel)."""
-        if self.bias is None:
-            return self.forward(x, False)
+        if self.bias is None or self.native_ok(x):
+            return self.forward(x, True)
         return add_cl(self.forward(x, False), None, self.bias.detach())
 
 
@@ -158,8 +196,11 @@ class ResBlock(TimestepBlock):
             pre = emb.per_block[id(self)]
         else:
             pre = self.emb_layers(emb).float() + self.in_layers[2].bias.detach().float()
-        h = self.out_layers[3](gn_silu(self.out_layers[0], h, pre), False)
         skip = x if isinstance(self.skip_connection, nn.Identity) else self.skip_connection(x, False)
+        h = gn_silu(self.out_layers[0], h, pre)
+        if self.out_layers[3].native_ok(h):      # conv2 + bias (+ skip conv bias) + skip in the GEMM epilogue
+            return self.out_layers[3].native(h, self.out_bias(), skip)
+        h = self.out_layers[3](h, False)
         return add_cl(h, skip, self.out_bias())
 
 

@@ -100,6 +100,13 @@ typedef struct afb_gemm_args {
   const float* ln_colsum;
   int ln_parts;
   float ln_eps;
+  /* 3x3 convolution (stride 1, zero padding 1) as an implicit GEMM - the ResBlock / Upsample convolutions of
+   * openaimodel.py:95-123,203-205,236-238.  conv_h, conv_w > 0: a is the bf16 NHWC image
+   * [B, conv_h, conv_w, Cin] with pixel stride lda, m = B*conv_h*conv_w, k = 9*Cin (Cin % 64 == 0), w is
+   * [N, 9*Cin] with k = (ky*3 + kx)*Cin + c, i.e. the channels-last memory of the Conv2d weight; out / residual are
+   * bf16 [m, N] = NHWC.  STORE epilogue with bf16 out only.  Widths/heights must tile into 128-pixel boxes
+   * (powers of two up to 128 or multiples of 128).  0, 0: plain GEMM. */
+  int conv_h, conv_w;
 } afb_gemm_args;
 int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
 /* number of (sum, sum of squares) partials per row that a STORE GEMM with n output columns emits */

@@ -112,6 +112,41 @@ def test_linear_store(ops, cuda_device, m, n, k):
     assert rel_l2(out.float(), ref + res.float()) < 4e-3
 
 
+@pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (3, 320, 320, 16, 16), (2, 640, 320, 64, 64),
+                                            (16, 1280, 1280, 8, 8), (1, 128, 128, 4, 32), (2, 192, 640, 32, 32),
+                                            (1, 64, 32, 2, 128)])
+def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
+    """3x3 / stride 1 / zero padding 1 convolution (ResBlock / Upsample convs, openaimodel.py:95-123,203-238) on the
+    tcgen05 GEMM kernel against torch's fp32 conv2d of the same bf16-rounded operands."""
+    x = _r("cv.x", (b, cin, h, w)).to(torch.bfloat16)
+    wt = _r("cv.w", (cout, cin, 3, 3), (9 * cin) ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("cv.b", (cout,))
+    res = _r("cv.r", (b, cout, h, w)).to(torch.bfloat16)
+    ref = torch.nn.functional.conv2d(x.float(), wt.float(), bias, padding=1)
+    d = cuda_device
+    xt = x.to(d).permute(0, 2, 3, 1).reshape(b * h * w, cin).contiguous()
+    wp = wt.to(d).permute(0, 2, 3, 1).reshape(cout, 9 * cin).contiguous()
+    rt = res.to(d).permute(0, 2, 3, 1).reshape(b * h * w, cout).contiguous()
+    to_nchw = lambda y: y.float().view(b, h, w, cout).permute(0, 3, 1, 2)
+    assert rel_l2(to_nchw(ops.conv3x3(xt, wp, bias.to(d), None, h, w)), ref) < 4e-3
+    assert rel_l2(to_nchw(ops.conv3x3(xt, wp, None, rt, h, w)), ref - bias[None, :, None, None] + res.float()) < 4e-3
+    # channel slice of a wider NHWC buffer (pixel stride != Cin)
+    wide = torch.cat([xt, xt.flip(1)], dim=1)
+    assert rel_l2(to_nchw(ops.conv3x3(wide[:, :cin], wp, bias.to(d), None, h, w)), ref) < 4e-3
+
+
+def test_conv3x3_unsupported_geometry_raises(ops, cuda_device):
+    from adaface_b200._lib import AdafaceB200Error
+    d = cuda_device
+    x = torch.zeros((96 * 96, 64), dtype=torch.bfloat16, device=d)
+    wp = torch.zeros((32, 9 * 64), dtype=torch.bfloat16, device=d)
+    with pytest.raises(AdafaceB200Error):
+        ops.conv3x3(x, wp, None, None, 96, 96)           # 96-pixel rows do not tile into 128-pixel boxes
+    with pytest.raises(AdafaceB200Error):
+        ops.conv3x3(torch.zeros((64, 48), dtype=torch.bfloat16, device=d),
+                    torch.zeros((32, 9 * 48), dtype=torch.bfloat16, device=d), None, None, 8, 8)   # Cin % 64
+
+
 def test_linear_strided_views(ops, cuda_device):
     """A operand and residual as column slices of wider buffers (lda/ldr != K/N)."""
     m, n, k = 256, 320, 320
