@@ -4,18 +4,20 @@
 // (it owns all 512 TMEM columns); 64 + kQTiles*128 threads:
 //   warp 0 (one lane)  TMA producer: Q tiles once, then K and V tiles of 64 keys in two separate rings
 //                      (64-column boxes, SWIZZLE_128B; the head is a column slice of the [B, N, ld] buffer)
-//   warp 1 (one lane)  tcgen05.mma issuer, event driven: S_t = Q_t K_j^T (128 x 64 fp32 in TMEM) is issued one KV
-//                      tile AHEAD of the softmax (the S columns are free as soon as the scores sit in registers),
-//                      O_t += P_t V_j as soon as P_t is published (V is the MN-major B operand straight from its
-//                      [key][d] layout); whichever tile is ready first goes first
+//   warp 1 (one lane)  tcgen05.mma issuer, event driven: when tile t publishes P_t(j) it issues O_t += P_t(j) V_j
+//                      (A operand = P straight from TMEM, V is the MN-major B operand from its [key][d] layout) and
+//                      then S_t(j+1) = Q_t K_{j+1}^T over the same TMEM columns (the tensor pipe keeps issue order);
+//                      whichever tile is ready first goes first
 //   warps 2 + 4t + q   softmax of query tile t, TMEM lane quarter q, one query row per thread: tcgen05.ld S ->
 //                      registers, running max with lazy rescaling of O in TMEM (only when the max grows by > 2^8),
-//                      exp2, row sum, P -> bf16 -> shared memory (canonical K-major 128B-swizzled);
+//                      exp2, row sum, P -> bf16 pairs -> tcgen05.st over the first 32 columns of the row's own S
+//                      (P never touches shared memory: the smem port carries Q/K/V operand reads only);
 //                      final O / l -> bf16 -> global.
 // Head dim 40 is bound by the MUFU unit (one ex2 per 80 tensor FLOPs), not by the tensor cores, so the kernel is
 // organised around keeping MUFU fed: kQTiles = 4 puts four independent softmax warps on every SM sub-partition,
 // so that while some wait for scores, take the row max or publish P, others are in their exponential phase.  The
-// exponential phase is FFMA2 (scale and max folded) -> MUFU.EX2 -> FADD2 -> F2FP, the row max FMNMX3 on raw scores.
+// exponential phase is FFMA2 (scale and max folded) -> MUFU.EX2 -> FADD2 -> F2FP, the row max FMNMX3 on raw scores;
+// one pair of exponentials in three runs on the FMA pipe instead (degree-3 minimax exp2).
 //
 // Replaces attention.py:198-242 (einsum QK^T, masked_fill, softmax, einsum PV, head merge) without ever
 // materialising the [8B, N, N] score tensor.
@@ -59,6 +61,15 @@ struct AttnDev {
 #define AFB_ATTN_STAGGER 0
 #endif
 
+// P through tensor memory: the softmax warps write P_j (bf16) over the first 32 columns of their own S_j with
+// tcgen05.st and O += P_j V_j takes its A operand from TMEM.  The shared-memory port then carries only Q/K/V operand
+// reads (it was ~75 % busy with the P round trip: 64 KB of P written and 64 KB re-read by the MMAs per 64 keys on top of
+// 88 KB of Q/K/V reads).  S_{j+1} can no longer be issued before P_j has been consumed: it follows O += P_j V_j in
+// the (in-order) tensor pipe.  AFB_ATTN_PTMEM=0 builds the shared-memory P path.
+#ifndef AFB_ATTN_PTMEM
+#define AFB_ATTN_PTMEM 1
+#endif
+
 template <int D>
 struct AttnCfg {
   static constexpr int kQTiles = (D <= 40) ? 4 : 2;            // query tiles (= softmax warps per sub-partition)
@@ -71,10 +82,11 @@ struct AttnCfg {
   static constexpr int kPBytes = kBlockQ * 128;                 // one query tile's P (64 keys = one atom)
   static constexpr int kStages = (D <= 40) ? 4 : (D <= 80 ? 3 : 2);
 #ifndef AFB_ATTN_POLY_EVERY
-#define AFB_ATTN_POLY_EVERY 6
+#define AFB_ATTN_POLY_EVERY 3
 #endif
   static constexpr int kPolyEvery = (D <= 40) ? AFB_ATTN_POLY_EVERY : 0;          // every kPolyEvery-th pair of exponentials on the FMA pipe
   static constexpr int kSmemBytes = kQTiles * (kQTileBytes + kPBytes) + kStages * 2 * kKVTileBytes;
+  static constexpr bool kPTmem = AFB_ATTN_PTMEM != 0;
   static constexpr int kTmemCols = 512;                          // one CTA per SM owns all of TMEM
   static constexpr int kTmemS = 0;                               // S_t: 64 columns each
   static constexpr int kTmemO = kQTiles * kBlockKV;              // O_t: kDPadN columns each
@@ -106,6 +118,8 @@ __device__ __forceinline__ uint64_t exp2_poly_x2(uint64_t x2) {
   return pack_f32x2(rl, rh);
 }
 
+// 576 threads = 18 warps put five warps on two of the SM sub-partitions (16 K registers each): 96 registers per thread
+// is the hardware ceiling for the d = 40 configuration, which ptxas derives from the launch bounds
 template <int D, bool kHasMask>
 __global__ void __launch_bounds__(AttnCfg<D>::kThreads, 1)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -222,18 +236,24 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         }
       };
       // O_t += P_t V_j : K-steps of 16 keys; V tile is [key][64 cols] per atom -> MN-major, LBO = atom stride
-      auto issue_pv = [&](int t, int stage, bool first) {
+      auto issue_pv = [&](int t, int stage, bool first, bool last) {
         if (leader) {
           const uint32_t v_addr = smem_u32(sV + stage * C::kKVTileBytes);
           const uint32_t tmem_o = tmem_base + C::kTmemO + t * C::kDPadN;
 #pragma unroll
           for (int kk = 0; kk < BKV / 16; ++kk) {
-            const uint32_t pa = p_addr + t * C::kPBytes + kk * 32;
             const uint32_t va = v_addr + kk * (16 * 128);
-            umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
-                    !(first && kk == 0));
+            if constexpr (C::kPTmem) {
+              // A = P_t from TMEM: 16 keys = 8 columns of packed bf16 pairs, same lanes as the S rows
+              umma_ts(tmem_o, tmem_base + C::kTmemS + t * BKV + kk * 8, umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
+                      !(first && kk == 0));
+            } else {
+              const uint32_t pa = p_addr + t * C::kPBytes + kk * 32;
+              umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
+                      !(first && kk == 0));
+            }
           }
-          umma_commit(&pv_done[t]);
+          if (!C::kPTmem || last) umma_commit(&pv_done[t]);
         }
       };
 #ifdef AFB_ATTN_PROFILE
@@ -263,11 +283,26 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         AFB_PROF(0);                                      // wait for K/V tiles
         // events of this round: bit t = "S_t(j+1) may be issued" (scores j are in registers),
         //                       bit NT + t = "O_t += P_t(j) V_j may be issued" (P_t(j) is published)
-        uint32_t pending = (more ? all : 0u) | (all << NT);
+        uint32_t pending = (more && !C::kPTmem ? all : 0u) | (all << NT);
         const uint32_t par = j & 1;
         while (pending != 0u) {
 #pragma unroll
           for (int t = 0; t < NT; ++t) {
+            if constexpr (C::kPTmem) {
+              // one event per tile and round: P_t(j) sits in TMEM -> O_t += P_t(j) V_j, then S_t(j+1) = Q_t K_{j+1}^T
+              // over the same columns (the tensor pipe runs them in issue order)
+              if ((pending >> (NT + t)) & 1u) {
+                if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[t], par))) {
+                  AFB_PROF(1);
+                  tc_fence_after();
+                  issue_pv(t, stage, j == 0, !more);
+                  if (more) issue_qk(t, nstage);
+                  pending &= ~(1u << (NT + t));
+                  AFB_PROF(2);
+                }
+              }
+              continue;
+            }
             if ((pending >> t) & 1u) {
               if (__all_sync(0xffffffffu, mbar_test_wait(&s_free[t], par))) {
                 AFB_PROF(1);                              // polling
@@ -282,14 +317,17 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
               if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[t], par))) {
                 AFB_PROF(1);
                 tc_fence_after();
-                issue_pv(t, stage, j == 0);
+                issue_pv(t, stage, j == 0, !more);
                 pending &= ~(1u << (NT + t));
                 AFB_PROF(2);
               }
             }
           }
         }
-        if (leader) umma_commit(&v_empty[stage]);
+        if (leader) {
+          umma_commit(&v_empty[stage]);
+          if (C::kPTmem && more) umma_commit(&k_empty[nstage]);
+        }
         stage = nstage;
         phase = nphase;
       }
@@ -353,9 +391,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 #pragma unroll
       for (int c = 0; c < BKV / 32; ++c) tmem_ld32p(tmem_s + c * 32, &r[c * 32]);
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&s_free[t]);             // the MMA warp may start S_{j+1}
+      if constexpr (!C::kPTmem) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_free[t]);           // the MMA warp may start S_{j+1}
+      }
       AFB_PROF(1);                                        // TMEM load
 
       const int kv0 = j * BKV;
@@ -390,8 +430,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         m_used = m_tile;
       } else if (__any_sync(0xffffffffu, need)) {
         // rare after the first tiles: O must be rescaled, which needs O += P_{j-1} V_{j-1} to have finished
-        mbar_wait(&pv_done[t], (j - 1) & 1);
-        tc_fence_after();
+        // (P through TMEM: S_j was issued behind it and has completed, so it has)
+        if constexpr (!C::kPTmem) {
+          mbar_wait(&pv_done[t], (j - 1) & 1);
+          tc_fence_after();
+        }
         const float m_new = need ? m_tile : m_used;
         const float alpha = ex2_approx(m_used - m_new);  // 1 for rows that keep their reference max
         m_used = m_new;
@@ -437,15 +480,21 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       }
       AFB_PROF(4);                                        // exponentials
 
-      // the P buffer is free once O += P_{j-1} V_{j-1} has completed (long ago in steady state)
-      if (j > 0) mbar_wait(&pv_done[t], (j - 1) & 1);
-      AFB_PROF(5);                                        // wait for the P buffer
-      // P -> canonical K-major SW128 layout: row pitch 128 B, 16-byte chunk c at c ^ (row & 7)
+      if constexpr (C::kPTmem) {
+        // P_j (bf16 pairs, 32 columns) over the first half of this row's S_j columns
+        tmem_st32p(tmem_s, r);
+        tmem_st_wait();
+      } else {
+        // the P buffer is free once O += P_{j-1} V_{j-1} has completed (long ago in steady state)
+        if (j > 0) mbar_wait(&pv_done[t], (j - 1) & 1);
+        AFB_PROF(5);                                        // wait for the P buffer
+        // P -> canonical K-major SW128 layout: row pitch 128 B, 16-byte chunk c at c ^ (row & 7)
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
-        *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) =
-            make_uint4(r[c * 4], r[c * 4 + 1], r[c * 4 + 2], r[c * 4 + 3]);
-      fence_proxy_async_smem();
+        for (int c = 0; c < 8; ++c)
+          *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) =
+              make_uint4(r[c * 4], r[c * 4 + 1], r[c * 4 + 2], r[c * 4 + 3]);
+        fence_proxy_async_smem();
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_ready[t]);
@@ -460,7 +509,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 #endif
 
     // ---- epilogue: O / l -> bf16 -> out[b, q, head*D : head*D + D]
-    mbar_wait(&pv_done[t], (num_kv_tiles - 1) & 1);
+    mbar_wait(&pv_done[t], C::kPTmem ? 0 : ((num_kv_tiles - 1) & 1));
     tc_fence_after();
     const int q_idx = q0 + t * kBlockQ + row;
     const float inv_l = 1.0f / l_run;
