@@ -36,7 +36,7 @@ int num_sms();
 // Host: TMA tensor maps (cuTensorMapEncodeTiled resolved at run time, no libcuda link dependency)
 // ----------------------------------------------------------------------------------------------
 enum class Swizzle { None = 0, B32 = 1, B64 = 2, B128 = 3 };
-// rank <= 4; dims[0] is the contiguous dimension; strides_bytes[i] is the stride of dims[i+1].
+// rank <= 5; dims[0] is the contiguous dimension; strides_bytes[i] is the stride of dims[i+1].
 int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const void* base,
                     const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
                     Swizzle swizzle, CUtensorMapL2promotion l2 = CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
@@ -221,6 +221,13 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void*
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(map)),
                "r"(smem_u32(smem)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap* map, const void* smem, int c0, int c1, int c2, int c3,
+                                             int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }

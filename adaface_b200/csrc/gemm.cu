@@ -337,6 +337,10 @@ struct GemmTmaDev {
   // 3x3 convolution as an implicit GEMM: A is the NHWC image [B, H, W, Cin] behind a 4-D tensor map, the K loop
   // walks (tap, 64-channel block); conv_cblocks = Cin / 64 (0: plain GEMM)
   int conv_cblocks, conv_h, conv_w;
+  // nearest-2x upsampling folded into the convolution (conv_fold != 0): output phase (py, px) = n_blk / nb_per_phase
+  // is a 2x2 convolution of the LOW-resolution image with taps (py - 1 + a, px - 1 + c); its BN-column blocks store to
+  // the pixels (2i + py, 2j + px) of the high-resolution output through a 5-D tensor map; fold_cout = N / 4
+  int conv_fold, nb_per_phase, fold_cout;
 };
 
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
@@ -413,13 +417,20 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         const int n_blk = t.n_blk;
         // convolution: the tile's 128 rows are the pixel box (b0.., h0.., w0..) of the image; tap (dy, dx) of the
         // filter reads the same box shifted by (dy, dx), out-of-image pixels zero-filled by TMA (= zero padding)
-        int cw0 = 0, ch0 = 0, cb0 = 0, cblk = 0, dy = -1, dx = -1;
+        int cw0 = 0, ch0 = 0, cb0 = 0, cblk = 0, dy = -1, dx = -1, dx0 = -1, dx_end = 2;
         if (p.conv_cblocks != 0) {
           const int m0 = m_blk * kBM;
           const int r = m0 / p.conv_w;
           cw0 = m0 - r * p.conv_w;
           cb0 = r / p.conv_h;
           ch0 = r - cb0 * p.conv_h;
+          if (p.conv_fold != 0) {
+            const int phase = n_blk / p.nb_per_phase;
+            dy = (phase >> 1) - 1;
+            dx0 = (phase & 1) - 1;
+            dx = dx0;
+            dx_end = dx0 + 2;
+          }
         }
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -440,8 +451,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
           }
           if (p.conv_cblocks != 0 && ++cblk == p.conv_cblocks) {
             cblk = 0;
-            if (++dx == 2) {
-              dx = -1;
+            if (++dx == dx_end) {
+              dx = dx0;
               ++dy;
             }
           }
@@ -769,7 +780,17 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         fence_proxy_async_smem();
         AFB_GPROF(4)
         named_bar_sync(1 + grp, 128);
-        if (leader) tma_store_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
+        if (leader) {
+          if (p.conv_fold != 0) {
+            const int phase = n_blk / p.nb_per_phase;
+            const int m0 = m_blk * kBM;
+            const int r = m0 / p.conv_w;              // merged (sample, low-res row) index of the tile's first pixel
+            tma_store_5d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0 - phase * p.fold_cout, phase & 1,
+                         m0 - r * p.conv_w, phase >> 1, r);
+          } else {
+            tma_store_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
+          }
+        }
         AFB_GPROF(5)
       }
       if (!released) {
@@ -813,7 +834,8 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   CUtensorMap tm_a, tm_w, tm_out, tm_res;
   if (a.conv_h > 0) {
     // NHWC image [B, H, W, Cin], pixel stride lda; the box is 128 consecutive pixels in (b, h, w) order
-    const uint64_t cin = static_cast<uint64_t>(a.k / 9), W = static_cast<uint64_t>(a.conv_w), H = static_cast<uint64_t>(a.conv_h);
+    const uint64_t cin = static_cast<uint64_t>(a.k / (a.conv_fold != 0 ? 4 : 9)), W = static_cast<uint64_t>(a.conv_w),
+                   H = static_cast<uint64_t>(a.conv_h);
     const uint32_t bw = static_cast<uint32_t>(W < kBM ? W : kBM);
     const uint32_t bh = static_cast<uint32_t>(H < kBM / bw ? H : kBM / bw);
     const uint64_t dims[4] = {cin, W, H, static_cast<uint64_t>(a.m) / (W * H)};
@@ -837,7 +859,20 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
       return rc;
   }
   const int64_t n_out = GEGLU ? a.n / 2 : a.n;
-  if (int rc = make_box_map(&tm_out, a.out, n_out, a.m, a.ldo)) return rc;
+  if (a.conv_fold != 0) {
+    // high-resolution NHWC output [B, 2H, 2W, Cout] seen as [B*H][py][W][px][Cout]; a tile stores its 128 low-res pixels
+    // of one phase: box {32 channels, 1, bw, 1, bh*bb}
+    const uint64_t W = static_cast<uint64_t>(a.conv_w), H = static_cast<uint64_t>(a.conv_h), cout = static_cast<uint64_t>(a.n / 4);
+    const uint64_t ld = static_cast<uint64_t>(a.ldo) * 2;
+    const uint32_t bw = static_cast<uint32_t>(W < kBM ? W : kBM);
+    const uint64_t dims[5] = {cout, 2, W, 2, static_cast<uint64_t>(a.m) / W};
+    const uint64_t strides[4] = {ld, 2 * ld, 2 * W * ld, 4 * W * ld};
+    const uint32_t box[5] = {32, 1, bw, 1, kBM / bw};
+    (void)H;
+    if (int rc = make_tensor_map(&tm_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, a.out, dims, strides, box, Swizzle::B64)) return rc;
+  } else if (int rc = make_box_map(&tm_out, a.out, n_out, a.m, a.ldo)) {
+    return rc;
+  }
   if (a.residual != nullptr) {
     if (int rc = make_box_map(&tm_res, a.residual, n_out, a.m, a.ldr)) return rc;
   } else {
@@ -857,7 +892,11 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   p.ln_colsum = a.ln_colsum;
   p.ln_parts = a.ln_parts;
   p.ln_eps = a.ln_eps;
-  p.conv_cblocks = a.conv_h > 0 ? static_cast<int>(a.k / 9 / kBK) : 0;
+  const int taps = a.conv_fold != 0 ? 4 : 9;
+  p.conv_cblocks = a.conv_h > 0 ? static_cast<int>(a.k / taps / kBK) : 0;
+  p.conv_fold = a.conv_fold;
+  p.fold_cout = static_cast<int>(a.n / 4);
+  p.nb_per_phase = a.conv_fold != 0 ? static_cast<int>(a.n / 4 / BN) : 1;
   p.conv_h = a.conv_h;
   p.conv_w = a.conv_w;
   auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats, kPair>;
@@ -983,8 +1022,15 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
     // 3x3 / stride 1 / zero padding 1 convolution as an implicit GEMM (openaimodel.py:203-205,236-238)
     const int64_t hw = static_cast<int64_t>(a.conv_h) * a.conv_w;
     AFB_REQUIRE(a.conv_h > 0 && a.conv_w > 0 && a.m % hw == 0, "afb_gemm_bf16: conv needs conv_h, conv_w > 0 and M = B*H*W");
-    AFB_REQUIRE(a.k % (9 * 64) == 0, "afb_gemm_bf16: conv needs K = 9 * Cin with Cin %% 64 == 0 (K=%lld)", (long long)a.k);
-    AFB_REQUIRE(a.lda >= a.k / 9 && a.ldw >= a.k, "afb_gemm_bf16: conv leading dimension smaller than Cin / K");
+    const int taps = a.conv_fold != 0 ? 4 : 9;
+    AFB_REQUIRE(a.k % (taps * 64) == 0, "afb_gemm_bf16: conv needs K = %d * Cin with Cin %% 64 == 0 (K=%lld)", taps, (long long)a.k);
+    AFB_REQUIRE(a.lda >= a.k / taps && a.ldw >= a.k, "afb_gemm_bf16: conv leading dimension smaller than Cin / K");
+    if (a.conv_fold != 0) {
+      const int64_t cout = a.n / 4;
+      AFB_REQUIRE(a.n % 4 == 0 && cout % (cout % 160 == 0 ? 160 : 128) == 0 && a.residual == nullptr && a.ldo == cout,
+                  "afb_gemm_bf16: folded upsampling needs N = 4 * Cout with Cout a multiple of the tile width (160 or 128), "
+                  "no residual and a contiguous [B, 2H, 2W, Cout] output");
+    }
     const int W = a.conv_w, H = a.conv_h;
     const int bw = W < 128 ? W : 128;
     AFB_REQUIRE(W < 128 ? 128 % W == 0 : W % 128 == 0, "afb_gemm_bf16: conv width %d does not tile into 128-pixel boxes", W);
@@ -1009,13 +1055,13 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
               "afb_gemm_bf16: row_stats_out must be 8-byte aligned");
   switch (a.epilogue) {
     case AFB_EPI_STORE:
-      AFB_REQUIRE(a.ldo >= a.n && a.ldo % 8 == 0, "afb_gemm_bf16: ldo must be >= N and a multiple of 8");
+      AFB_REQUIRE((a.conv_fold != 0 || a.ldo >= a.n) && a.ldo % 8 == 0, "afb_gemm_bf16: ldo must be >= N and a multiple of 8");
       if (a.residual) {
         AFB_REQUIRE(a.ldr >= a.n && a.ldr % 8 == 0, "afb_gemm_bf16: ldr must be >= N and a multiple of 8");
         AFB_REQUIRE((reinterpret_cast<uintptr_t>(a.residual) & 15) == 0, "afb_gemm_bf16: residual must be 16-byte aligned");
       }
       if (a.out_dtype == AFB_BF16 && (a.residual == nullptr || a.residual_dtype == AFB_BF16)) {
-        if (a.n % 160 == 0) return launch_tma<160, false>(a, stream);
+        if (a.conv_fold != 0 ? (a.n / 4) % 160 == 0 : a.n % 160 == 0) return launch_tma<160, false>(a, stream);
         return launch_tma<128, false>(a, stream);
       }
       AFB_REQUIRE(a.row_stats_out == nullptr && a.ln_stats == nullptr,

@@ -141,7 +141,8 @@ def _(x, gamma, beta, eps):
 # ------------------------------------------------------------------------------------------- GEMMs
 def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], epilogue: int,
           ldo: int, ldr: int, hw: int = 0, stats_out: Optional[Tensor] = None, ln_stats: Optional[Tensor] = None,
-          ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0, conv_hw: Optional[Tuple[int, int]] = None) -> None:
+          ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0, conv_hw: Optional[Tuple[int, int]] = None,
+          conv_fold: bool = False) -> None:
     _need_cuda(a, w, out, bias, residual, stats_out, ln_stats, ln_colsum)
     if ln_stats is not None:
         if ln_colsum is None or ln_stats.dtype != torch.float32 or ln_colsum.dtype != torch.float32 \
@@ -154,13 +155,13 @@ def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: O
         raise ValueError("gemm: bias must be fp32")
     args = GemmArgs(a=_ptr(a), w=_ptr(w), out=_ptr(out), bias=_ptr(bias), residual=_ptr(residual),
                     m=a.shape[0], n=w.shape[0], k=w.shape[1] if conv_hw else a.shape[1], lda=a.stride(0), ldw=w.stride(0),
-                    ldo=ldo, ldr=ldr, conv_h=conv_hw[0] if conv_hw else 0, conv_w=conv_hw[1] if conv_hw else 0,
+                    ldo=ldo, ldr=ldr, conv_h=conv_hw[0] if conv_hw else 0, conv_w=conv_hw[1] if conv_hw else 0, conv_fold=1 if conv_fold else 0,
                     epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
                     residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
                     else _lib.DT_BF16, hw=hw, row_stats_out=_ptr(stats_out), ln_stats=_ptr(ln_stats),
                     ln_colsum=_ptr(ln_colsum), ln_parts=0 if ln_stats is None else ln_stats.shape[1], ln_eps=ln_eps)
     m, n, k = a.shape[0], w.shape[0], w.shape[1] if conv_hw else a.shape[1]
-    _run("conv3x3_bf16" if conv_hw else "gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
+    _run(("conv3x3_up2_bf16" if conv_fold else "conv3x3_bf16") if conv_hw else "gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
          nbytes=2.0 * (m * a.shape[1] + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
          + ("r" if residual is not None else ""))
 
@@ -184,6 +185,42 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Ten
 @conv3x3.register_fake
 def _(x, w, bias, residual, h, width):
     return x.new_empty((x.shape[0], w.shape[0]), dtype=torch.bfloat16)
+
+
+def fold_upsample_weight(weight: Tensor) -> Tensor:
+    """Conv2d weight [Cout, Cin, 3, 3] -> [4*Cout, 4*Cin] fp32 for `conv3x3_up2`: nearest-2x upsampling followed by the
+    3x3 convolution equals, for output phase (py, px), a 2x2 convolution of the low-resolution image whose tap (a, c)
+    (low-res offset (py-1+a, px-1+c)) is the sum of the 3x3 taps that land on that pixel:
+    py = 0: a=0 <- ky {0}, a=1 <- ky {1, 2};  py = 1: a=0 <- ky {0, 1}, a=1 <- ky {2}  (same for px / kx)."""
+    cout, cin = weight.shape[:2]
+    w = weight.detach().float()
+    sel = {0: ([0], [1, 2]), 1: ([0, 1], [2])}
+    out = w.new_zeros((2, 2, cout, 2, 2, cin))
+    for py in (0, 1):
+        for px in (0, 1):
+            for a in (0, 1):
+                for c in (0, 1):
+                    out[py, px, :, a, c, :] = w[:, :, sel[py][a], :][:, :, :, sel[px][c]].sum(dim=(2, 3))
+    return out.reshape(4 * cout, 4 * cin)
+
+
+@torch.library.custom_op("adaface_b200::conv3x3_up2", mutates_args=())
+def conv3x3_up2(x: Tensor, w_folded: Tensor, bias4: Optional[Tensor], h: int, width: int) -> Tensor:
+    """Upsample.forward (openaimodel.py:95-123): conv3x3(interpolate(x, 2x nearest)) + bias without materialising the
+    upsampled image.  x: bf16 NHWC pixels [B*h*width, Cin] of the LOW-resolution image; w_folded bf16 [4*Cout, 4*Cin]
+    (`fold_upsample_weight`); bias4 fp32 [4*Cout] (the bias repeated per phase).  Returns bf16 [B*2h*2width, Cout]."""
+    if x.dim() != 2 or w_folded.dim() != 2 or w_folded.shape[1] != 4 * x.shape[1] or w_folded.shape[0] % 4 \
+            or x.shape[0] % (h * width) != 0:
+        raise ValueError("conv3x3_up2: x [B*h*w, Cin] and w_folded [4*Cout, 4*Cin] expected")
+    cout = w_folded.shape[0] // 4
+    out = torch.empty((4 * x.shape[0], cout), dtype=torch.bfloat16, device=x.device)
+    _gemm(x, w_folded, out, bias4, None, _lib.EPI_STORE, cout, 0, conv_hw=(h, width), conv_fold=True)
+    return out
+
+
+@conv3x3_up2.register_fake
+def _(x, w_folded, bias4, h, width):
+    return x.new_empty((4 * x.shape[0], w_folded.shape[0] // 4), dtype=torch.bfloat16)
 
 
 @torch.library.custom_op("adaface_b200::linear", mutates_args=())

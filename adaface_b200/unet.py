@@ -27,7 +27,11 @@ from .embedding import LAYER_IDX2CA_LAYER_IDX, AdaEmbedding
 
 Tensor = torch.Tensor
 CL = torch.channels_last
-_NATIVE_CONV = os.environ.get("AFB_CONV", "1") != "0"
+# AFB_CONV=1: every eligible 3x3 ResBlock convolution on this repo's implicit-GEMM kernel (default: cuDNN, which is
+# ~0.5 ms per step faster at batch 16 - its kernels reuse the input tile across the nine taps).  AFB_UPSAMPLE_FOLD=0:
+# Upsample as interpolate + conv instead of the folded four-phase 2x2 convolution.
+_NATIVE_CONV = os.environ.get("AFB_CONV", "0") != "0"
+_NATIVE_UPSAMPLE = os.environ.get("AFB_UPSAMPLE_FOLD", "1") != "0"
 
 
 def timestep_embedding(timesteps: Tensor, dim: int, max_period: int = 10000) -> Tensor:
@@ -92,9 +96,13 @@ class _Bf16Conv(nn.Conv2d):
         return c[1], c[2]
 
     def native_ok(self, x) -> bool:
-        """3x3 / stride 1 / padding 1 with Cin % 64 == 0 on an image that tiles into 128-pixel boxes: runs as an
-        implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3) instead of cuDNN.  AFB_CONV=0 turns it off."""
-        if not _NATIVE_CONV or self.kernel_size != (3, 3) or self.stride != (1, 1) or self.padding != (1, 1) \
+        """True when this convolution runs as an implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3)
+        instead of cuDNN: AFB_CONV=1 and a supported geometry."""
+        return _NATIVE_CONV and self.geometry_ok(x)
+
+    def geometry_ok(self, x) -> bool:
+        """3x3 / stride 1 / padding 1 with Cin % 64 == 0 on an image that tiles into 128-pixel boxes."""
+        if self.kernel_size != (3, 3) or self.stride != (1, 1) or self.padding != (1, 1) \
                 or self.dilation != (1, 1) or self.groups != 1:
             return False
         _, c, h, w = x.shape
@@ -146,7 +154,27 @@ class Upsample(nn.Module):
         if use_conv:
             self.conv = _Bf16Conv(channels, self.out_channels, 3, padding=padding)
 
+    def _folded(self):
+        """bf16 [4*Cout, 4*Cin] phase weights + fp32 [4*Cout] bias of the upsample-folded convolution."""
+        conv = self.conv
+        key = (conv.weight.data_ptr(), conv.weight._version, conv.bias._version)
+        c = self.__dict__.get("_fold_cache")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                c = (key, ops.fold_upsample_weight(conv.weight).to(torch.bfloat16).contiguous(),
+                     conv.bias.detach().float().repeat(4).contiguous())
+            self.__dict__["_fold_cache"] = c
+        return c[1], c[2]
+
     def forward(self, x):
+        if self.use_conv and _NATIVE_UPSAMPLE and self.conv.geometry_ok(x) \
+                and (self.out_channels % 160 == 0 or self.out_channels % 128 == 0):
+            # nearest-2x upsampling folded into the convolution: four 2x2 phase convolutions of the low-res image
+            b, c, h, w = x.shape
+            wf, b4 = self._folded()
+            xt = x.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b * h * w, c)
+            y = ops.conv3x3_up2(xt, wf, b4, h, w)
+            return y.view(b, 2 * h, 2 * w, self.out_channels).permute(0, 3, 1, 2)
         x = F.interpolate(x, scale_factor=2, mode="nearest")
         return self.conv.conv_add(x) if self.use_conv else x
 

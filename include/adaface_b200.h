@@ -107,6 +107,14 @@ typedef struct afb_gemm_args {
    * bf16 [m, N] = NHWC.  STORE epilogue with bf16 out only.  Widths/heights must tile into 128-pixel boxes
    * (powers of two up to 128 or multiples of 128).  0, 0: plain GEMM. */
   int conv_h, conv_w;
+  /* conv_fold != 0: nearest-neighbour 2x upsampling folded into the convolution (Upsample.forward,
+   * openaimodel.py:95-123: F.interpolate(scale 2, nearest) then the 3x3 conv).  Output pixel (2i+py, 2j+px) only sees
+   * 2x2 low-resolution pixels, so each of the four output phases is a 2x2 convolution of the LOW-resolution image
+   * a = [B, conv_h, conv_w, Cin] with pre-summed weights: k = 4*Cin, n = 4*Cout, w is [4*Cout, 4*Cin] with row
+   * (py*2+px)*Cout + o and column (a*2+c)*Cin + ch = sum of the 3x3 taps (ky, kx) that land on low-res offset
+   * (py-1+a, px-1+c); bias is [4*Cout] (the conv bias repeated); out is bf16 [B, 2*conv_h, 2*conv_w, Cout], ldo = Cout.
+   * 2.25x fewer FLOPs than convolving the upsampled image, and the upsampled tensor is never written. */
+  int conv_fold;
 } afb_gemm_args;
 int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
 /* number of (sum, sum of squares) partials per row that a STORE GEMM with n output columns emits */

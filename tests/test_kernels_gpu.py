@@ -135,6 +135,37 @@ def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
     assert rel_l2(to_nchw(ops.conv3x3(wide[:, :cin], wp, bias.to(d), None, h, w)), ref) < 4e-3
 
 
+@pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (2, 128, 128, 16, 16), (16, 1280, 1280, 8, 8),
+                                            (1, 640, 640, 32, 32), (3, 64, 320, 4, 32)])
+def test_conv3x3_upsample_fold(ops, cuda_device, b, cin, cout, h, w):
+    """Upsample.forward (openaimodel.py:95-123): nearest 2x + 3x3 conv as four folded 2x2 phase convolutions of the
+    low-resolution image, against torch's fp32 interpolate + conv2d."""
+    x = _r("up.x", (b, cin, h, w)).to(torch.bfloat16)
+    wt = _r("up.w", (cout, cin, 3, 3), (9 * cin) ** -0.5)
+    bias = 0.1 * _r("up.b", (cout,))
+    ref = torch.nn.functional.conv2d(torch.nn.functional.interpolate(x.float(), scale_factor=2, mode="nearest"), wt, bias,
+                                     padding=1)
+    d = cuda_device
+    wf = ops.fold_upsample_weight(wt)
+    # the fold itself is exact in fp32: check it on the CPU against the reference formulation
+    xf = x.float()
+    xp = torch.nn.functional.pad(xf, (1, 1, 1, 1))
+    chk = torch.zeros_like(ref)
+    for py in (0, 1):
+        for px in (0, 1):
+            acc = 0
+            for a in (0, 1):
+                for c in (0, 1):
+                    wt_ac = wf[(py * 2 + px) * cout:(py * 2 + px + 1) * cout, (a * 2 + c) * cin:(a * 2 + c + 1) * cin]
+                    acc = acc + torch.einsum("bchw,oc->bohw", xp[:, :, py + a:py + a + h, px + c:px + c + w], wt_ac)
+            chk[:, :, py::2, px::2] = acc + bias[None, :, None, None]
+    assert rel_l2(chk, ref) < 1e-5
+    xt = x.to(d).permute(0, 2, 3, 1).reshape(b * h * w, cin).contiguous()
+    y = ops.conv3x3_up2(xt, wf.to(torch.bfloat16).to(d), bias.repeat(4).to(d), h, w)
+    y = y.float().view(b, 2 * h, 2 * w, cout).permute(0, 3, 1, 2)
+    assert rel_l2(y, ref) < 5e-3
+
+
 def test_conv3x3_unsupported_geometry_raises(ops, cuda_device):
     from adaface_b200._lib import AdafaceB200Error
     d = cuda_device
