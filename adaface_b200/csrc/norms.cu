@@ -135,7 +135,8 @@ __device__ __forceinline__ void group_accumulate(float* slots, const float (&s)[
 // pre_add (optional, fp32 [B, C] with row stride pre_add_ld): a per-(sample, channel) vector added to x BEFORE the
 // statistics and the normalisation - the conv bias + time-embedding add that precedes out_layers' GroupNorm in a
 // ResBlock (openaimodel.py:259-279), folded in so that no separate elementwise pass is needed.
-__global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ pre_add,
+__global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, int C1,
+                                                             const float* __restrict__ pre_add,
                                                              int pre_add_ld, float* __restrict__ partial, int C, int HW,
                                                              int cpg, int T, int nchunks) {
   __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
@@ -150,18 +151,24 @@ __global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloa
   const int c0 = vec * 8;
   const int groups = C / cpg;
   for (int i = threadIdx.x; i < groups; i += blockDim.x) g_sum[i] = g_m2[i] = 0.f;
-  const uint4* xp = reinterpret_cast<const uint4*>(x + (static_cast<long long>(b) * HW + t0) * C) + vec;
+  // virtual channel concatenation (x2 != NULL): channels [0, C1) live in x [B, HW, C1], channels [C1, C) in
+  // x2 [B, HW, C - C1] -- a thread owns one 8-channel vector, so it reads one of the two sources throughout
+  const bool second = x2 != nullptr && c0 >= C1;
+  const int src_c = x2 == nullptr ? C : (second ? C - C1 : C1);
+  const int src_vpr = src_c >> 3;
+  const uint4* xp = reinterpret_cast<const uint4*>((second ? x2 : x) + (static_cast<long long>(b) * HW + t0) * src_c) +
+                    (second ? vec - (C1 >> 3) : vec);
   float piv[8], s1[8], s2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) piv[j] = s1[j] = s2[j] = 0.f;
   int n_mine = 0;
-  if (row < nt) unpack8(xp[static_cast<long long>(row) * vpr], piv);
+  if (row < nt) unpack8(xp[static_cast<long long>(row) * src_vpr], piv);
   for (int t = row; t < nt; t += R * kGnUnroll) {
     uint4 data[kGnUnroll];
 #pragma unroll
     for (int u = 0; u < kGnUnroll; ++u) {
       const int tt = t + u * R;
-      if (tt < nt) data[u] = xp[static_cast<long long>(tt) * vpr];
+      if (tt < nt) data[u] = xp[static_cast<long long>(tt) * src_vpr];
     }
 #pragma unroll
     for (int u = 0; u < kGnUnroll; ++u) {
@@ -226,7 +233,8 @@ __device__ __forceinline__ float silu(float v) {
 }
 
 template <bool kSilu>
-__global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ partial,
+__global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, int C1,
+                                                           const float* __restrict__ partial,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            const float* __restrict__ pre_add, int pre_add_ld,
                                                            __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int T,
@@ -243,14 +251,17 @@ __global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat1
   const int c0 = vec * 8;
   const int groups = C / cpg;
   const long long base = (static_cast<long long>(b) * HW + t0) * vpr + vec;
-  const uint4* xp = reinterpret_cast<const uint4*>(x) + base;
+  const bool second = x2 != nullptr && c0 >= C1;                     // virtual concatenation, see gn_partial_tok_kernel
+  const int src_vpr = x2 == nullptr ? vpr : ((second ? C - C1 : C1) >> 3);
+  const uint4* xp = reinterpret_cast<const uint4*>(second ? x2 : x) + (static_cast<long long>(b) * HW + t0) * src_vpr +
+                    (second ? vec - (C1 >> 3) : vec);
   uint4* yp = reinterpret_cast<uint4*>(y) + base;
   // first loads go out before the statistics merge so their latency overlaps it
   uint4 data[kGnUnroll];
 #pragma unroll
   for (int u = 0; u < kGnUnroll; ++u) {
     const int tt = row + u * R;
-    if (tt < nt) data[u] = xp[static_cast<long long>(tt) * vpr];
+    if (tt < nt) data[u] = xp[static_cast<long long>(tt) * src_vpr];
   }
   {
     // merge the chunk partials of sample b: lane c holds chunk c (nchunks <= 32), exact Chan merge
@@ -287,7 +298,7 @@ __global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat1
 #pragma unroll
     for (int u = 0; u < kGnUnroll; ++u) {
       const int tt = t + (kGnUnroll + u) * R;
-      if (tt < nt) next[u] = xp[static_cast<long long>(tt) * vpr];
+      if (tt < nt) next[u] = xp[static_cast<long long>(tt) * src_vpr];
     }
 #pragma unroll
     for (int u = 0; u < kGnUnroll; ++u) {
@@ -580,7 +591,21 @@ extern "C" int64_t afb_groupnorm_ws_floats(int batch, int hw, int groups) {
 extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
                                     float* stats_ws, int batch, int channels, int hw, int groups, float eps, int act,
                                     const float* pre_add, int pre_add_ld, afb_stream_t stream_) {
+  return afb_groupnorm_tokens_cat(x, 0, nullptr, x_layout, gamma, beta, y, stats_ws, batch, channels, hw, groups, eps, act,
+                                  pre_add, pre_add_ld, stream_);
+}
+
+extern "C" int afb_groupnorm_tokens_cat(const void* x, int channels1, const afb_bf16* x2, int x_layout, const float* gamma,
+                                        const float* beta, afb_bf16* y, float* stats_ws, int batch, int channels, int hw,
+                                        int groups, float eps, int act, const float* pre_add, int pre_add_ld,
+                                        afb_stream_t stream_) {
   using namespace afb;
+  const __nv_bfloat16* xb2 = reinterpret_cast<const __nv_bfloat16*>(x2);
+  if (x2 != nullptr) {
+    AFB_REQUIRE(x_layout == 1 && channels1 > 0 && channels1 < channels && channels1 % 8 == 0 && (channels - channels1) % 8 == 0 &&
+                    (reinterpret_cast<uintptr_t>(x2) & 15) == 0,
+                "afb_groupnorm_tokens_cat: two token-major bf16 sources with channel counts that are multiples of 8");
+  }
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && gamma && beta && y && stats_ws, "afb_groupnorm_tokens: NULL argument");
   AFB_REQUIRE(batch > 0 && channels > 0 && hw > 0 && groups > 0, "afb_groupnorm_tokens: empty input");
@@ -615,17 +640,17 @@ extern "C" int afb_groupnorm_tokens(const void* x, int x_layout, const float* ga
     const size_t cluster_smem = static_cast<size_t>(Tc) * channels * 2;
     // (measured on B200: wins for the small late-stage tensors; at 1 MB+ per sample the two-kernel path is faster,
     //  sixteen 8-CTA clusters with ~160 KB of shared memory each do not all fit the GPCs at once)
-    if (cluster_smem <= static_cast<size_t>(kGnClusterMaxSmem) && static_cast<long long>(hw) * channels <= 512 * 1024) {
+    if (x2 == nullptr && cluster_smem <= static_cast<size_t>(kGnClusterMaxSmem) && static_cast<long long>(hw) * channels <= 512 * 1024) {
       const int rc = act ? launch_gn_cluster<true>(xb, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, Tc, geo.threads, cluster_smem, eps, stream)
                          : launch_gn_cluster<false>(xb, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, Tc, geo.threads, cluster_smem, eps, stream);
       if (rc) return rc;
       count_launch();
       return 0;
     }
-    AFB_CHECK_CUDA(launch_pdl(gn_partial_tok_kernel, grid, dim3(geo.threads), 0, stream, 1, xb, pre_add, pre_add_ld, partial, channels, hw,
+    AFB_CHECK_CUDA(launch_pdl(gn_partial_tok_kernel, grid, dim3(geo.threads), 0, stream, 1, xb, xb2, channels1, pre_add, pre_add_ld, partial, channels, hw,
                               cpg, geo.T, geo.nchunks));
     count_launch();
-    AFB_CHECK_CUDA(launch_pdl(act ? gn_apply_tok_kernel<true> : gn_apply_tok_kernel<false>, grid, dim3(geo.threads), 0, stream, 1, xb,
+    AFB_CHECK_CUDA(launch_pdl(act ? gn_apply_tok_kernel<true> : gn_apply_tok_kernel<false>, grid, dim3(geo.threads), 0, stream, 1, xb, xb2, channels1,
                               partial, gamma, beta, pre_add, pre_add_ld, yb, channels, hw, cpg, geo.T, geo.nchunks, eps));
     count_launch();
   } else {

@@ -120,6 +120,31 @@ def _(x, gamma, beta, groups, eps, act=0, pre_add=None):
     return x.new_empty((b, h * w, c), dtype=torch.bfloat16)
 
 
+@torch.library.custom_op("adaface_b200::groupnorm_tokens_cat", mutates_args=())
+def groupnorm_tokens_cat(x1: Tensor, x2: Tensor, gamma: Tensor, beta: Tensor, groups: int, eps: float, act: int = 0) -> Tensor:
+    """GroupNorm (+ SiLU) of th.cat([x1, x2], dim=1) without materialising the concatenation (decoder ResBlocks,
+    openaimodel.py:1004-1010): x1 [B,C1,h,w], x2 [B,C2,h,w] bf16 channels-last -> bf16 tokens [B, h*w, C1+C2]."""
+    _need_cuda(x1, x2, gamma, beta)
+    b, c1, h, w = x1.shape
+    c2 = x2.shape[1]
+    if x2.shape != (b, c2, h, w) or x1.dtype != torch.bfloat16 or x2.dtype != torch.bfloat16 \
+            or not x1.permute(0, 2, 3, 1).is_contiguous() or not x2.permute(0, 2, 3, 1).is_contiguous():
+        raise ValueError("groupnorm_tokens_cat: two bf16 channels-last tensors of the same batch and size expected")
+    hw, c = h * w, c1 + c2
+    lib = _lib.load()
+    ws = torch.empty(int(lib.afb_groupnorm_ws_floats(b, hw, groups)), dtype=torch.float32, device=x1.device)
+    y = torch.empty((b, hw, c), dtype=torch.bfloat16, device=x1.device)
+    _run("groupnorm_tokens", lib.afb_groupnorm_tokens_cat, _ptr(x1), c1, _ptr(x2), 1, _ptr(gamma), _ptr(beta), _ptr(y),
+         _ptr(ws), b, c, hw, groups, eps, act, None, 0, _stream(), nbytes=float(b * hw * c) * 4, tag=f"b{b}n{hw}C{c1}+{c2}")
+    return y
+
+
+@groupnorm_tokens_cat.register_fake
+def _(x1, x2, gamma, beta, groups, eps, act=0):
+    b, c1, h, w = x1.shape
+    return x1.new_empty((b, h * w, c1 + x2.shape[1]), dtype=torch.bfloat16)
+
+
 @torch.library.custom_op("adaface_b200::layernorm", mutates_args=())
 def layernorm(x: Tensor, gamma: Optional[Tensor], beta: Optional[Tensor], eps: float) -> Tensor:
     """LayerNorm over the last dim of a contiguous bf16 tensor (attention.py:267-269)."""

@@ -32,6 +32,7 @@ CL = torch.channels_last
 # Upsample as interpolate + conv instead of the folded four-phase 2x2 convolution.
 _NATIVE_CONV = os.environ.get("AFB_CONV", "0") != "0"
 _NATIVE_UPSAMPLE = os.environ.get("AFB_UPSAMPLE_FOLD", "1") != "0"
+_VIRTUAL_CAT = os.environ.get("AFB_CAT", "1") != "0"
 
 
 def timestep_embedding(timesteps: Tensor, dim: int, max_period: int = 10000) -> Tensor:
@@ -64,6 +65,24 @@ def gn_silu(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Te
     x = x.contiguous(memory_format=CL)
     y = ops.groupnorm_tokens(x, gn.weight.detach(), gn.bias.detach(), gn.num_groups, gn.eps, 1, pre_add)
     return y.view(b, h, w, c).permute(0, 3, 1, 2)
+
+
+class CatPair:
+    """th.cat([h, hs.pop()], dim=1) (openaimodel.py:1004-1010) kept as its two halves: the decoder ResBlock that
+    consumes it normalises both sources in one GroupNorm pass (ops.groupnorm_tokens_cat) and applies its 1x1 skip
+    convolution as two chained GEMMs, so large concatenations are never written.  AFB_CAT=0 materialises always."""
+
+    def __init__(self, a: Tensor, b: Tensor):
+        self.a, self.b = a, b
+        self.shape = (a.shape[0], a.shape[1] + b.shape[1], a.shape[2], a.shape[3])
+
+    def virtual(self) -> bool:
+        # small samples take the single-launch cluster GroupNorm, which needs one source tensor
+        _, c, h, w = self.shape
+        return _VIRTUAL_CAT and h * w * c > 512 * 1024 and self.a.shape[1] % 8 == 0 and self.b.shape[1] % 8 == 0
+
+    def cat(self) -> Tensor:
+        return torch.cat([self.a, self.b], dim=1).contiguous(memory_format=CL)
 
 
 def add_cl(a: Tensor, b: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:
@@ -214,17 +233,52 @@ class ResBlock(TimestepBlock):
             self.__dict__["_out_bias"] = c
         return c[1]
 
+    def _skip_pair(self, pair: CatPair) -> Tensor:
+        """1x1 skip convolution of the virtual concatenation: W[:, :C1] . a + W[:, C1:] . b as two chained GEMMs (the
+        second takes the first's output as its residual); bias is added with conv2's (out_bias)."""
+        sc = self.skip_connection
+        c1 = pair.a.shape[1]
+        key = (sc.weight.data_ptr(), sc.weight._version, c1)
+        c = self.__dict__.get("_skip_pair_w")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                w = sc.weight.detach().reshape(sc.out_channels, -1).to(torch.bfloat16)
+                c = (key, w[:, :c1].contiguous(), w[:, c1:].contiguous())
+            self.__dict__["_skip_pair_w"] = c
+        b_, _, h_, w_ = pair.shape
+        at = pair.a.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
+        bt = pair.b.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
+        s = ops.linear(bt, c[2], None, None, False)
+        s = ops.linear(at, c[1], None, s, False)
+        return s.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
+
     def forward(self, x, emb):
         """openaimodel.py:259-279.  The conv1 bias and the time-embedding add are folded into out_layers' GroupNorm
         (pre_add), conv2's bias and the skip add are one vectorised pass."""
         if self.training and self.out_layers[2].p > 0:
             raise NotImplementedError("adaface_b200.ResBlock: dropout > 0 in training mode is not supported")
-        h = self.in_layers[2](gn_silu(self.in_layers[0], x), False)
+        pair = None
+        if isinstance(x, CatPair):
+            if x.virtual() and not isinstance(self.skip_connection, nn.Identity):
+                pair = x
+            else:
+                x = x.cat()
+        if pair is not None:
+            gn = self.in_layers[0]
+            b_, c_, h_, w_ = pair.shape
+            y = ops.groupnorm_tokens_cat(pair.a.contiguous(memory_format=CL), pair.b.contiguous(memory_format=CL),
+                                         gn.weight.detach(), gn.bias.detach(), gn.num_groups, gn.eps, 1)
+            h = self.in_layers[2](y.view(b_, h_, w_, c_).permute(0, 3, 1, 2), False)
+        else:
+            h = self.in_layers[2](gn_silu(self.in_layers[0], x), False)
         if isinstance(emb, EmbBundle):
             pre = emb.per_block[id(self)]
         else:
             pre = self.emb_layers(emb).float() + self.in_layers[2].bias.detach().float()
-        skip = x if isinstance(self.skip_connection, nn.Identity) else self.skip_connection(x, False)
+        if pair is not None:
+            skip = self._skip_pair(pair)
+        else:
+            skip = x if isinstance(self.skip_connection, nn.Identity) else self.skip_connection(x, False)
         h = gn_silu(self.out_layers[0], h, pre)
         if self.out_layers[3].native_ok(h):      # conv2 + bias (+ skip conv bias) + skip in the GEMM epilogue
             return self.out_layers[3].native(h, self.out_bias(), skip)
@@ -484,8 +538,7 @@ class UNetModel(nn.Module):
         h = self.middle_block(h, bundle, layer_context(layer_idx), mask=img_mask)
         layer_idx += 1
         for module in self.output_blocks:
-            h = torch.cat([h, hs.pop()], dim=1).contiguous(memory_format=CL)
-            h = module(h, bundle, layer_context(layer_idx), mask=img_mask)
+            h = module(CatPair(h, hs.pop()), bundle, layer_context(layer_idx), mask=img_mask)
             layer_idx += 1
         if ada is not None:
             if ada.__dict__.get("_pool_q") and not ada._joined:        # no conditioned layer ran: still join the stream

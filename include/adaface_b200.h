@@ -54,6 +54,14 @@ int afb_groupnorm_tokens(const void* x, int x_layout, const float* gamma, const 
                          float* stats_ws, int batch, int channels, int hw, int groups, float eps, int act,
                          const float* pre_add, int pre_add_ld, afb_stream_t stream);
 
+/* Same with the input given as two token-major bf16 tensors that are (virtually) concatenated along the channel dim:
+ * channels [0, channels1) from x [B, HW, channels1], the rest from x2 [B, HW, channels - channels1] - the
+ * th.cat([h, hs.pop()], dim=1) in front of every decoder ResBlock (openaimodel.py:1004-1010) is never materialised
+ * for its GroupNorm.  x2 == NULL: identical to afb_groupnorm_tokens. */
+int afb_groupnorm_tokens_cat(const void* x, int channels1, const afb_bf16* x2, int x_layout, const float* gamma,
+                             const float* beta, afb_bf16* y, float* stats_ws, int batch, int channels, int hw,
+                             int groups, float eps, int act, const float* pre_add, int pre_add_ld, afb_stream_t stream);
+
 /* ---- out = a + b + bias (elementwise, bf16 [rows, C] token-major; b and bias optional).  The residual / bias adds
  * around the ResBlock convolutions (openaimodel.py:279) as one vectorised pass instead of two broadcast adds. */
 int afb_add_bias_residual(const afb_bf16* a, const afb_bf16* b, const float* bias, afb_bf16* out, int64_t rows,

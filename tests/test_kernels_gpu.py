@@ -94,6 +94,24 @@ def test_layernorm(ops, cuda_device, c):
     assert rel_l2(ops.layernorm(x.to(d), None, None, 1e-5).float(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("c1,c2,hw", [(640, 320, 32), (320, 320, 64), (1280, 640, 32), (1280, 1280, 16)])
+def test_groupnorm_virtual_concat(ops, cuda_device, c1, c2, hw):
+    """GroupNorm32 + SiLU of th.cat([h, skip], 1) (decoder ResBlocks, openaimodel.py:1004-1010, 201-205) read from the
+    two sources: identical to the kernel on the materialised concatenation, and within bf16 rounding of the oracle."""
+    b, d = 2, cuda_device
+    x1 = (_r("gnc.x1", (b, c1, hw, hw)) * 1.3 + 0.2).to(torch.bfloat16)
+    x2 = (_r("gnc.x2", (b, c2, hw, hw)) * 0.7 - 0.4).to(torch.bfloat16)
+    g, be = 1 + 0.1 * _r("gnc.g", (c1 + c2,)), 0.1 * _r("gnc.b", (c1 + c2,))
+    cl = torch.channels_last
+    y = ops.groupnorm_tokens_cat(x1.to(d).contiguous(memory_format=cl), x2.to(d).contiguous(memory_format=cl), g.to(d),
+                                 be.to(d), 32, 1e-5, 1)
+    xc = torch.cat([x1, x2], dim=1)
+    y_mat = ops.groupnorm_tokens(xc.to(d).contiguous(memory_format=cl), g.to(d), be.to(d), 32, 1e-5, 1)
+    ref = torch.nn.functional.silu(port.group_norm(xc.float(), g, be, 32, 1e-5)).reshape(b, c1 + c2, hw * hw).transpose(1, 2)
+    assert rel_l2(y.float(), ref) < 4e-3
+    assert rel_l2(y.float(), y_mat.float()) < 2e-3        # (different chunking / kernel variant: not bit-identical)
+
+
 # ---------------------------------------------------------------------------------------------- GEMM
 @pytest.mark.parametrize("m,n,k", [(128, 160, 64), (256, 320, 320), (512, 960, 320), (200, 640, 768),
                                    (1024, 1280, 5120), (64, 1280, 1280), (4096, 320, 1280), (154, 128, 768)])
