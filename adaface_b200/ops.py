@@ -34,6 +34,22 @@ def _ptr(t: Optional[Tensor]) -> Optional[int]:
 # Optional per-launch timing (bench.py's kernel breakdown / roofline): CUDA events on the launching stream
 # around every C-ABI call, with the call's algorithmic FLOPs and bytes.  Off (None) on the normal path.
 _TIMING: Optional[List[tuple]] = None
+# which part of the U-Net a launch belongs to, for the breakdown only: "st" = the SpatialTransformer / AdaEmbedding /
+# CFG-DDIM hot path, "resblock" = the kernels the U-Net shell borrows for ResBlocks, Upsample and the output head
+_SCOPE = "st"
+
+
+class scope:
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        global _SCOPE
+        self.prev, _SCOPE = _SCOPE, self.name
+
+    def __exit__(self, *exc):
+        global _SCOPE
+        _SCOPE = self.prev
 
 
 def start_timing() -> None:
@@ -46,7 +62,8 @@ def stop_timing() -> List[Dict]:
     global _TIMING
     recs, _TIMING = _TIMING or [], None
     torch.cuda.synchronize()
-    return [{"name": n, "tag": tag, "ms": e0.elapsed_time(e1), "flops": fl, "bytes": by} for n, tag, fl, by, e0, e1 in recs]
+    return [{"name": n, "tag": tag, "ms": e0.elapsed_time(e1), "flops": fl, "bytes": by, "scope": sc}
+            for n, tag, fl, by, e0, e1, sc in recs]
 
 
 def _run(name: str, fn, *args, flops: float = 0.0, nbytes: float = 0.0, tag: str = "") -> None:
@@ -57,7 +74,7 @@ def _run(name: str, fn, *args, flops: float = 0.0, nbytes: float = 0.0, tag: str
     e0.record()
     check(fn(*args), name)
     e1.record()
-    _TIMING.append((name, tag, flops, nbytes, e0, e1))
+    _TIMING.append((name, tag, flops, nbytes, e0, e1, _SCOPE))
 
 
 # ------------------------------------------------------------------------------------------- K14

@@ -186,6 +186,10 @@ class Upsample(nn.Module):
         return c[1], c[2]
 
     def forward(self, x):
+        with ops.scope("resblock"):
+            return self._forward(x)
+
+    def _forward(self, x):
         if self.use_conv and _NATIVE_UPSAMPLE and self.conv.geometry_ok(x) \
                 and (self.out_channels % 160 == 0 or self.out_channels % 128 == 0):
             # nearest-2x upsampling folded into the convolution: four 2x2 phase convolutions of the low-res image
@@ -206,7 +210,8 @@ class Downsample(nn.Module):
             else nn.AvgPool2d(kernel_size=2, stride=2)
 
     def forward(self, x):
-        return self.op.conv_add(x) if self.use_conv else self.op(x)
+        with ops.scope("resblock"):
+            return self.op.conv_add(x) if self.use_conv else self.op(x)
 
 
 class ResBlock(TimestepBlock):
@@ -253,6 +258,10 @@ class ResBlock(TimestepBlock):
         return s.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
 
     def forward(self, x, emb):
+        with ops.scope("resblock"):
+            return self._forward(x, emb)
+
+    def _forward(self, x, emb):
         """openaimodel.py:259-279.  The conv1 bias and the time-embedding add are folded into out_layers' GroupNorm
         (pre_add), conv2's bias and the skip add are one vectorised pass."""
         if self.training and self.out_layers[2].p > 0:
@@ -544,7 +553,8 @@ class UNetModel(nn.Module):
             if ada.__dict__.get("_pool_q") and not ada._joined:        # no conditioned layer ran: still join the stream
                 torch.cuda.current_stream().wait_stream(ada._side)
             ada.__dict__["_pool_q"] = None
-        return self.out[2](gn_silu(self.out[0], h)).to(x.dtype).contiguous()
+        with ops.scope("resblock"):
+            return self.out[2](gn_silu(self.out[0], h)).to(x.dtype).contiguous()
 
 
 class DiffusionModel:
