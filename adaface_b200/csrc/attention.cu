@@ -70,13 +70,23 @@ struct AttnDev {
 #define AFB_ATTN_PTMEM 1
 #endif
 
+// Row sums on the tensor pipe: column D of every V tile is overwritten with ones (by the otherwise idle lanes of the
+// MMA warp, once the tile has landed), so O's column D accumulates sum_j P_j -- of the bf16-rounded probabilities, the
+// same values the numerator uses -- and the softmax warps drop one FADD2 per pair of scores (10 % of their
+// instructions; d = 40 only: 560 -> 546 us).  AFB_ATTN_ONES=0 keeps the row sum in registers.
+#ifndef AFB_ATTN_ONES
+#define AFB_ATTN_ONES 1
+#endif
+
 template <int D>
 struct AttnCfg {
   static constexpr int kQTiles = (D <= 40) ? 4 : 2;            // query tiles (= softmax warps per sub-partition)
   static constexpr int kThreads = 64 + kQTiles * 128;
   static constexpr int kAtoms = (D + 63) / 64;                 // 64-column (128-byte) swizzle atoms per row
   static constexpr int kDPadK = (D + 15) / 16 * 16;            // K extent of S = Q K^T (UMMA K step 16)
-  static constexpr int kDPadN = (D + 7) / 8 * 8;               // N extent of O += P V (UMMA N step 8)
+  static constexpr bool kOnes = AFB_ATTN_ONES != 0 && D <= 40;   // d = 80 is tensor-bound: the wider P V costs more there
+  static_assert(D % 8 == 0, "head dim");
+  static constexpr int kDPadN = kOnes ? D + 8 : D;             // N extent of O += P V (UMMA N step 8); column D = row sum
   static constexpr int kQTileBytes = kAtoms * kBlockQ * 128;   // one query tile: atom a at a * 16 KB
   static constexpr int kKVTileBytes = kAtoms * kBlockKV * 128;  // one of K or V
   static constexpr int kPBytes = kBlockQ * 128;                 // one query tile's P (64 keys = one atom)
@@ -280,6 +290,15 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         AFB_PROF(3);
         if (more) mbar_wait(&k_full[nstage], nphase);
         mbar_wait(&v_full[stage], phase);
+        if constexpr (C::kOnes) {
+          // ones into column D of the V tile (atom D / 64, 16-byte chunk (D % 64) / 8 at its swizzled position)
+          uint8_t* vt = sV + stage * C::kKVTileBytes + (D / 64) * (BKV * 128);
+#pragma unroll
+          for (int k = lane; k < BKV; k += 32)
+            *reinterpret_cast<uint16_t*>(vt + k * 128 + (((((D % 64) / 8) ^ (k & 7))) << 4)) = 0x3F80;   // bf16 1.0
+          fence_proxy_async_smem();
+          __syncwarp();
+        }
         AFB_PROF(0);                                      // wait for K/V tiles
         // events of this round: bit t = "S_t(j+1) may be issued" (scores j are in registers),
         //                       bit NT + t = "O_t += P_t(j) V_j may be issued" (P_t(j) is published)
@@ -470,10 +489,12 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           hi = ex2_approx(hi);
           e = pack_f32x2(lo, hi);
         }
-        if (i & 1) acc1 = fadd2(acc1, e); else acc0 = fadd2(acc0, e);
+        if constexpr (!C::kOnes) {
+          if (i & 1) acc1 = fadd2(acc1, e); else acc0 = fadd2(acc0, e);
+        }
         r[i] = cvt_bf16x2(lo, hi);
       }
-      {
+      if constexpr (!C::kOnes) {
         float a, bb;
         unpack_f32x2(fadd2(acc0, acc1), a, bb);
         l_run += a + bb;
@@ -512,6 +533,12 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     mbar_wait(&pv_done[t], C::kPTmem ? 0 : ((num_kv_tiles - 1) & 1));
     tc_fence_after();
     const int q_idx = q0 + t * kBlockQ + row;
+    if constexpr (C::kOnes) {
+      uint32_t o[8];
+      tmem_ld8(tmem_o + D, o);                              // column D of O: the row sum
+      tmem_ld_wait();
+      l_run = __uint_as_float(o[0]);
+    }
     const float inv_l = 1.0f / l_run;
     __nv_bfloat16* orow = p.out + (static_cast<long long>(b) * p.q_len + q_idx) * p.ldo + col0;
 #pragma unroll
