@@ -238,9 +238,27 @@ class ResBlock(TimestepBlock):
             self.__dict__["_out_bias"] = c
         return c[1]
 
-    def _skip_pair(self, pair: CatPair) -> Tensor:
+    def _skip_single(self, x: Tensor, h: Tensor, bias: Tensor) -> Tensor:
+        """skip_connection(x) + h + bias with the 1x1 convolution as one GEMM (residual = h)."""
+        sc = self.skip_connection
+        key = (sc.weight.data_ptr(), sc.weight._version)
+        c = self.__dict__.get("_skip_w")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                c = (key, sc.weight.detach().reshape(sc.out_channels, -1).to(torch.bfloat16).contiguous())
+            self.__dict__["_skip_w"] = c
+        b_, c_, h_, w_ = x.shape
+        if c_ % 8:
+            return add_cl(h, sc(x, False), bias)
+        xt = x.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, c_)
+        ht = h.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
+        out = ops.linear(xt, c[1], bias, ht, False)
+        return out.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
+
+    def _skip_pair(self, pair: CatPair, h: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:
         """1x1 skip convolution of the virtual concatenation: W[:, :C1] . a + W[:, C1:] . b as two chained GEMMs (the
-        second takes the first's output as its residual); bias is added with conv2's (out_bias)."""
+        second takes the first's output as its residual).  With h / bias given the first GEMM's epilogue also adds
+        conv2's output and the biases, so the result is the ResBlock's output."""
         sc = self.skip_connection
         c1 = pair.a.shape[1]
         key = (sc.weight.data_ptr(), sc.weight._version, c1)
@@ -253,7 +271,8 @@ class ResBlock(TimestepBlock):
         b_, _, h_, w_ = pair.shape
         at = pair.a.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
         bt = pair.b.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
-        s = ops.linear(bt, c[2], None, None, False)
+        ht = None if h is None else h.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
+        s = ops.linear(bt, c[2], bias, ht, False)
         s = ops.linear(at, c[1], None, s, False)
         return s.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
 
@@ -284,15 +303,21 @@ class ResBlock(TimestepBlock):
             pre = emb.per_block[id(self)]
         else:
             pre = self.emb_layers(emb).float() + self.in_layers[2].bias.detach().float()
-        if pair is not None:
-            skip = self._skip_pair(pair)
-        else:
-            skip = x if isinstance(self.skip_connection, nn.Identity) else self.skip_connection(x, False)
         h = gn_silu(self.out_layers[0], h, pre)
-        if self.out_layers[3].native_ok(h):      # conv2 + bias (+ skip conv bias) + skip in the GEMM epilogue
-            return self.out_layers[3].native(h, self.out_bias(), skip)
-        h = self.out_layers[3](h, False)
-        return add_cl(h, skip, self.out_bias())
+        conv2 = self.out_layers[3]
+        if isinstance(self.skip_connection, nn.Identity):
+            if conv2.native_ok(h):               # conv2 + bias + skip in the GEMM epilogue
+                return conv2.native(h, self.out_bias(), x)
+            return add_cl(conv2(h, False), x, self.out_bias())
+        if conv2.native_ok(h):                   # conv2 + both biases + skip(x) in the GEMM epilogue
+            skip = self._skip_pair(pair, None, None) if pair is not None else self.skip_connection(x, False)
+            return conv2.native(h, self.out_bias(), skip)
+        # cuDNN conv2: the 1x1 skip convolution runs as a GEMM whose epilogue adds conv2's output and both biases
+        # (skip(x) + conv2(h) + bias in the skip GEMM instead of a separate elementwise pass)
+        h = conv2(h, False)
+        if pair is not None:
+            return self._skip_pair(pair, h, self.out_bias())
+        return self._skip_single(x, h, self.out_bias())
 
 
 class TimestepEmbedSequential(nn.Sequential, TimestepBlock):

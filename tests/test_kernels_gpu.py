@@ -132,7 +132,7 @@ def test_linear_store(ops, cuda_device, m, n, k):
 
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (3, 320, 320, 16, 16), (2, 640, 320, 64, 64),
                                             (16, 1280, 1280, 8, 8), (1, 128, 128, 4, 32), (2, 192, 640, 32, 32),
-                                            (1, 64, 32, 2, 128)])
+                                            (1, 64, 32, 2, 128), (3, 64, 160, 8, 8), (5, 128, 320, 4, 4)])
 def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
     """3x3 / stride 1 / zero padding 1 convolution (ResBlock / Upsample convs, openaimodel.py:95-123,203-238) on the
     tcgen05 GEMM kernel against torch's fp32 conv2d of the same bf16-rounded operands."""
@@ -154,7 +154,8 @@ def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
 
 
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (2, 128, 128, 16, 16), (16, 1280, 1280, 8, 8),
-                                            (1, 640, 640, 32, 32), (3, 64, 320, 4, 32)])
+                                            (1, 640, 640, 32, 32), (3, 64, 320, 4, 32), (3, 128, 128, 8, 8),
+                                            (5, 64, 160, 4, 4)])
 def test_conv3x3_upsample_fold(ops, cuda_device, b, cin, cout, h, w):
     """Upsample.forward (openaimodel.py:95-123): nearest 2x + 3x3 conv as four folded 2x2 phase convolutions of the
     low-resolution image, against torch's fp32 interpolate + conv2d."""
