@@ -31,6 +31,8 @@ CL = torch.channels_last
 # ~0.5 ms per step faster at batch 16 - its kernels reuse the input tile across the nine taps).  AFB_UPSAMPLE_FOLD=0:
 # Upsample as interpolate + conv instead of the folded four-phase 2x2 convolution.
 _NATIVE_CONV = os.environ.get("AFB_CONV", "0") != "0"
+# AFB_CONV_W="64,32": image widths whose 3x3 convolutions take the native kernel when AFB_CONV=1 (default: all)
+_NATIVE_CONV_W = tuple(int(v) for v in os.environ.get("AFB_CONV_W", "").split(",") if v)
 _NATIVE_UPSAMPLE = os.environ.get("AFB_UPSAMPLE_FOLD", "1") != "0"
 _VIRTUAL_CAT = os.environ.get("AFB_CAT", "1") != "0"
 
@@ -117,7 +119,7 @@ class _Bf16Conv(nn.Conv2d):
     def native_ok(self, x) -> bool:
         """True when this convolution runs as an implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3)
         instead of cuDNN: AFB_CONV=1 and a supported geometry."""
-        return _NATIVE_CONV and self.geometry_ok(x)
+        return _NATIVE_CONV and (not _NATIVE_CONV_W or x.shape[3] in _NATIVE_CONV_W) and self.geometry_ok(x)
 
     def geometry_ok(self, x) -> bool:
         """3x3 / stride 1 / padding 1 with Cin % 64 == 0 on an image that tiles into 128-pixel boxes."""

@@ -273,6 +273,30 @@ FAST = ["st_small", "st_c640", "st_c1280", "st_mask_vk", "st_config1", "attn_var
 SLOW = ["unet_step", "ddim10_small", "ddim50"]
 
 
+RESBLOCK_CH_STRIDE = 4
+RESBLOCK_CASES = (("same", 320, 320, 16), ("skip", 320, 640, 16), ("cat", 640, 320, 32), ("cat_small", 2560, 1280, 8))
+
+
+def resblock_inputs(tag, cin, hw, seed, b=2):
+    return P.randn(f"rb.{tag}.x", (b, cin, hw, hw), seed), P.randn(f"rb.{tag}.emb", (b, 1280), seed)
+
+
+def case_resblock(ref, name="resblock", seed=21):
+    """The reference's ResBlock (openaimodel.py:167-281) and Upsample (:95-123) - SURVEY.md 8f N1 - on seeded inputs."""
+    out = {}
+    for tag, cin, cout, hw in RESBLOCK_CASES:
+        rb = ref.openaimodel.ResBlock(cin, 1280, 0.0, out_channels=cout, dims=2, use_checkpoint=False, use_scale_shift_norm=False)
+        rb.load_state_dict(P.init_resblock(cin, cout, seed), strict=True)
+        x, emb = resblock_inputs(tag, cin, hw, seed)
+        with torch.no_grad():
+            out[tag] = rb.eval()(x, emb)[:, ::RESBLOCK_CH_STRIDE]      # every 4th channel keeps the fixture small
+    up = ref.openaimodel.Upsample(640, True, dims=2)
+    up.load_state_dict(P.init_upsample(640, seed), strict=True)
+    with torch.no_grad():
+        out["up"] = up.eval()(P.randn("rb.up.x", (2, 640, 16, 16), seed))[:, ::RESBLOCK_CH_STRIDE]
+    _save(name, **out)
+
+
 def main(argv):
     ref = RH.load()
     torch.set_num_threads(os.cpu_count() or 1)
@@ -301,6 +325,8 @@ def main(argv):
             case_unet_step(ref)
         elif name == "ddim50":
             case_ddim50(ref)
+        elif name == "resblock":
+            case_resblock(ref)
         elif name == "ddim10_small":
             case_ddim50(ref, "ddim10_small", seed=19, hw=16, steps=10)
         else:

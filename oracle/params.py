@@ -148,6 +148,32 @@ def unet_spec(model_channels: int = 320, channel_mult=(1, 2, 4, 4), num_res_bloc
     yield "out.2.bias", (out_ch,)
 
 
+def resblock_spec(cin: int, cout: int, ted: int = 1280, prefix: str = ""):
+    """state_dict keys/shapes of one ResBlock(cin, ted, dropout, out_channels=cout): openaimodel.py:183-257."""
+    yield prefix + "in_layers.0.weight", (cin,)
+    yield prefix + "in_layers.0.bias", (cin,)
+    yield prefix + "in_layers.2.weight", (cout, cin, 3, 3)
+    yield prefix + "in_layers.2.bias", (cout,)
+    yield prefix + "emb_layers.1.weight", (cout, ted)
+    yield prefix + "emb_layers.1.bias", (cout,)
+    yield prefix + "out_layers.0.weight", (cout,)
+    yield prefix + "out_layers.0.bias", (cout,)
+    yield prefix + "out_layers.3.weight", (cout, cout, 3, 3)
+    yield prefix + "out_layers.3.bias", (cout,)
+    if cin != cout:
+        yield prefix + "skip_connection.weight", (cout, cin, 1, 1)
+        yield prefix + "skip_connection.bias", (cout,)
+
+
+def init_resblock(cin: int, cout: int, seed: int, ted: int = 1280) -> Dict[str, torch.Tensor]:
+    return {k: draw(f"rb{cin}x{cout}." + k, s, seed) for k, s in resblock_spec(cin, cout, ted)}
+
+
+def init_upsample(ch: int, seed: int) -> Dict[str, torch.Tensor]:
+    """Upsample(ch, use_conv=True): openaimodel.py:95-123."""
+    return {"conv.weight": draw(f"up{ch}.conv.weight", (ch, ch, 3, 3), seed), "conv.bias": draw(f"up{ch}.conv.bias", (ch,), seed)}
+
+
 def init_unet(seed: int, **cfg) -> Dict[str, torch.Tensor]:
     return {k: draw(k, s, seed) for k, s in unet_spec(**cfg)}
 

@@ -396,6 +396,12 @@ def res_block(x: Tensor, emb: Tensor, p: Params, prefix: str) -> Tensor:
     return x + h
 
 
+def upsample(x: Tensor, p: Params, prefix: str) -> Tensor:
+    """Upsample.forward with use_conv=True: openaimodel.py:113-123."""
+    x = F.interpolate(x, scale_factor=2, mode="nearest")
+    return F.conv2d(x, p[prefix + "conv.weight"], p[prefix + "conv.bias"], padding=1)
+
+
 def unet_forward(p: Params, x: Tensor, timesteps: Tensor, context: Tensor, model_channels: int = 320,
                  channel_mult: Sequence[int] = (1, 2, 4, 4), num_res_blocks: int = 2,
                  attention_resolutions: Sequence[int] = (4, 2, 1), heads: int = 8,

@@ -498,3 +498,38 @@ def test_ddim_full_loop_vs_reference_golden(afb, cuda_device, name):
     cos = cosine(samples.cpu(), g["samples"])
     print(f"{name}: final latent cosine {cos:.5f}, rel-L2 {rel_l2(samples, g['samples']):.3e}")
     assert cos >= 0.995
+
+
+# ---------------------------------------------------------------------------------------------- N1: ResBlock / Upsample
+def test_resblock_and_upsample_vs_reference_golden(afb, cuda_device):
+    """SURVEY.md 8f N1 (openaimodel.py:95-123, 167-281): the U-Net shell's ResBlock (fused GroupNorm+SiLU with the
+    bias / time-embedding fold, skip-GEMM tail) - also fed with the decoder's virtual concatenation - and the
+    upsample-folded Upsample against outputs of the reference's own modules."""
+    from adaface_b200 import unet as U
+    from oracle.gen_golden import RESBLOCK_CASES, RESBLOCK_CH_STRIDE, resblock_inputs
+    g = load_golden("resblock")
+    seed, d, cl = 21, cuda_device, torch.channels_last
+    for tag, cin, cout, hw in RESBLOCK_CASES:
+        rb = U.ResBlock(cin, 1280, 0.0, out_channels=cout)
+        rb.load_state_dict(P.init_resblock(cin, cout, seed), strict=True)
+        rb = rb.to(d).eval()
+        x, emb = resblock_inputs(tag, cin, hw, seed)
+        xb = x.to(d).to(torch.bfloat16).contiguous(memory_format=cl)
+        with torch.no_grad():
+            if tag.startswith("cat"):
+                half = cin // 2
+                pair = U.CatPair(xb[:, :half].contiguous(memory_format=cl), xb[:, half:].contiguous(memory_format=cl))
+                assert pair.virtual() == (tag == "cat")          # the big concatenation stays virtual
+                y = rb(pair, emb.to(d))
+            else:
+                y = rb(xb, emb.to(d))
+        assert y.shape == (2, cout, hw, hw)
+        assert rel_l2(y.float()[:, ::RESBLOCK_CH_STRIDE], g[tag]) < 1e-2, tag
+    up = U.Upsample(640, True)
+    up.load_state_dict(P.init_upsample(640, seed), strict=True)
+    up = up.to(d).eval()
+    x = P.randn("rb.up.x", (2, 640, 16, 16), seed).to(d).to(torch.bfloat16).contiguous(memory_format=cl)
+    with torch.no_grad():
+        y = up(x)
+    assert y.shape == (2, 640, 32, 32)
+    assert rel_l2(y.float()[:, ::RESBLOCK_CH_STRIDE], g["up"]) < 1e-2

@@ -186,3 +186,16 @@ def test_ddim10_small_matches_reference():
         out = port.ddim_sample(lambda x, t, c: port.unet_forward(sd, x, t, c), x_T, c_cond, c_uncond, steps,
                                (10.0, 4.0))
     assert rel_l2(out, g["samples"]) < 1e-3
+
+
+def test_resblock_and_upsample_match_reference():
+    """the port's res_block / upsample against the reference's ResBlock / Upsample modules."""
+    from oracle.gen_golden import RESBLOCK_CASES, RESBLOCK_CH_STRIDE, resblock_inputs
+    g = load_golden("resblock")
+    seed = 21
+    for tag, cin, cout, hw in RESBLOCK_CASES:
+        x, emb = resblock_inputs(tag, cin, hw, seed)
+        y = port.res_block(x, emb, P.init_resblock(cin, cout, seed), "")
+        assert rel_l2(y[:, ::RESBLOCK_CH_STRIDE], g[tag]) < TOL, tag
+    y = port.upsample(P.randn("rb.up.x", (2, 640, 16, 16), seed), P.init_upsample(640, seed), "")
+    assert rel_l2(y[:, ::RESBLOCK_CH_STRIDE], g["up"]) < TOL
