@@ -25,6 +25,12 @@ class GemmArgs(C.Structure):
                 ("ln_parts", C.c_int), ("ln_eps", C.c_float), ("conv_h", C.c_int), ("conv_w", C.c_int), ("conv_fold", C.c_int)]
 
 
+class AdaPrepItem(C.Structure):
+    _fields_ = [("to_k_weight", C.c_void_p), ("fg_q_emb", C.c_void_p), ("bg_q_emb", C.c_void_p),
+                ("lora_to_fg_q", C.c_void_p), ("lora_to_bg_q", C.c_void_p), ("lora_to_k", C.c_void_p),
+                ("pool_q", C.c_void_p), ("ws", C.c_void_p), ("channels", C.c_int), ("reserved", C.c_int)]
+
+
 class AttnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("out", C.c_void_p),
                 ("key_mask", C.c_void_p), ("batch", C.c_int), ("heads", C.c_int), ("head_dim", C.c_int),
@@ -55,6 +61,7 @@ _SIGNATURES = {
     "afb_ada_pool_ws_floats": (_I64, [_I, _I, _I]),
     "afb_ada_pool_prep_ws_floats": (_I64, [_I, _I]),
     "afb_ada_pool_prep": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
+    "afb_ada_pool_prep_batched": (_I, [_P, _I, _I, _I, _I, _P]),
     "afb_ada_pool": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "afb_ada_head": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _I, _I, _I, _I, _I, _I, _P]),
     "afb_cast_f32_to_bf16": (_I, [_P, _P, _I64, _P]),

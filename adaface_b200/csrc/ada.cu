@@ -50,7 +50,7 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 // the bg query of sample b.  One warp per output channel: the weight row is read once (float4, all loads in flight)
 // and dotted with all query vectors (staged in shared memory).
 constexpr int kPrepMaxSrc = 9;     // sources per pass (B + 1 = 9 for 8 samples); more -> extra passes
-__global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
+__device__ __forceinline__ void ada_qproj_body(
     const float* __restrict__ to_k_w, const float* __restrict__ fg_q_emb, const float* __restrict__ bg_q_emb,
     float* __restrict__ proj, int C, int ctx_dim, int n_src) {
   extern __shared__ float sh[];      // [min(n_src, kPrepMaxSrc)][ctx_dim]
@@ -92,14 +92,27 @@ __global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
   }
 }
 
+__global__ void __launch_bounds__(kPoolThreads) ada_qproj_kernel(
+    const float* __restrict__ to_k_w, const float* __restrict__ fg_q_emb, const float* __restrict__ bg_q_emb,
+    float* __restrict__ proj, int C, int ctx_dim, int n_src) {
+  ada_qproj_body(to_k_w, fg_q_emb, bg_q_emb, proj, C, ctx_dim, n_src);
+}
+// all (layer, subject) items of one U-Net call in one launch: blockIdx.y = item (channels differ per item)
+__global__ void __launch_bounds__(kPoolThreads) ada_qproj_batched_kernel(const afb_ada_prep_item* __restrict__ items,
+                                                                        int ctx_dim, int n_src) {
+  const afb_ada_prep_item it = items[blockIdx.y];
+  if (static_cast<int>(blockIdx.x) * kPoolWarps >= it.channels) return;
+  ada_qproj_body(it.to_k_weight, it.fg_q_emb, it.bg_q_emb, it.ws, it.channels, ctx_dim, n_src);
+}
+
 // ---- prep, kernel 2: block (b, i): LayerNorm (no affine, :208-209) of the projected query, grouped 1x1 conv
 // (:219, :222) with the 8^-1/2 * 8^-1/2 factor (:235) -> lora_q [dg], then the fold through lora_to_k:
 // u[b][i][c] = 8^-1/2 * sum_o lora_q[g*lg + o] * W_k[g*lg + o][c - g*dg]     (g = c / dg)
-__global__ void __launch_bounds__(kPoolThreads) ada_qfinish_kernel(const float* __restrict__ proj,
-                                                                  const float* __restrict__ w_fg,
-                                                                  const float* __restrict__ w_bg,
-                                                                  const float* __restrict__ w_k,
-                                                                  float* __restrict__ u, int C) {
+__device__ __forceinline__ void ada_qfinish_body(const float* __restrict__ proj,
+                                                 const float* __restrict__ w_fg,
+                                                 const float* __restrict__ w_bg,
+                                                 const float* __restrict__ w_k,
+                                                 float* __restrict__ u, int C) {
   extern __shared__ float sh[];      // [C] normalised query, [dg] lora_q
   __shared__ float red[32];
   const int b = blockIdx.x, i = blockIdx.y;
@@ -140,6 +153,18 @@ __global__ void __launch_bounds__(kPoolThreads) ada_qfinish_kernel(const float* 
     for (int o = 0; o < lg; ++o) a += s_lq[g * lg + o] * w_k[static_cast<long long>(g * lg + o) * dg + k];
     out[c] = a * kInvSqrt8;
   }
+}
+
+__global__ void __launch_bounds__(kPoolThreads) ada_qfinish_kernel(const float* __restrict__ proj,
+                                                                  const float* __restrict__ w_fg,
+                                                                  const float* __restrict__ w_bg,
+                                                                  const float* __restrict__ w_k,
+                                                                  float* __restrict__ u, int C) {
+  ada_qfinish_body(proj, w_fg, w_bg, w_k, u, C);
+}
+__global__ void __launch_bounds__(kPoolThreads) ada_qfinish_batched_kernel(const afb_ada_prep_item* __restrict__ items) {
+  const afb_ada_prep_item it = items[blockIdx.z];
+  ada_qfinish_body(it.ws, it.lora_to_fg_q, it.lora_to_bg_q, it.lora_to_k, it.pool_q, it.channels);
 }
 
 // partial record per block: m[8], l[8], acc_fg[C], acc_bg[C]
@@ -548,6 +573,33 @@ extern "C" int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const fl
   count_launch();
   const size_t sh2 = (static_cast<size_t>(channels) + channels / kHeads) * sizeof(float);
   ada_qfinish_kernel<<<dim3(batch, 2), kPoolThreads, sh2, stream>>>(ws, lora_to_fg_q, lora_to_bg_q, lora_to_k, pool_q, channels);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_pool_prep_batched(const afb_ada_prep_item* items, int n_items, int max_channels, int ctx_dim,
+                                         int batch, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(items != nullptr && n_items > 0 && n_items <= 65535, "afb_ada_pool_prep_batched: 1..65535 items expected");
+  AFB_REQUIRE(batch > 0 && ctx_dim > 0 && ctx_dim % 4 == 0, "afb_ada_pool_prep_batched: ctx_dim must be a positive multiple of 4");
+  AFB_REQUIRE(max_channels % 64 == 0 && max_channels > 0 && max_channels <= 1280,
+              "afb_ada_pool_prep_batched: max_channels %d must be a multiple of 64, <= 1280", max_channels);
+  const int n_src = batch + 1;
+  const int src_in_smem = n_src < kPrepMaxSrc ? n_src : kPrepMaxSrc;
+  const size_t sh1 = static_cast<size_t>(src_in_smem) * ctx_dim * sizeof(float);
+  AFB_REQUIRE(sh1 <= 96 * 1024, "afb_ada_pool_prep_batched: ctx_dim %d too large", ctx_dim);
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(ada_qproj_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set = true;
+  }
+  ada_qproj_batched_kernel<<<dim3((max_channels + kPoolWarps - 1) / kPoolWarps, n_items), kPoolThreads, sh1, stream>>>(items, ctx_dim,
+                                                                                                                    n_src);
+  count_launch();
+  const size_t sh2 = (static_cast<size_t>(max_channels) + max_channels / kHeads) * sizeof(float);
+  ada_qfinish_batched_kernel<<<dim3(batch, 2, n_items), kPoolThreads, sh2, stream>>>(items);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -495,6 +495,40 @@ def _(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k):
     return to_k_weight.new_empty((bg_q_emb.shape[0], 2, to_k_weight.shape[0]), dtype=torch.float32)
 
 
+class AdaPrepBatch:
+    """All (cross-attention layer, subject) pooling-query preparations of one U-Net call as ONE pair of launches
+    (afb_ada_pool_prep_batched).  The descriptor table is uploaded once; `run()` recomputes every pool_q in place, so
+    the call is CUDA-graph capturable and the outputs (`pool_q[i]`, fp32 [B, 2, C_i]) keep their addresses.
+    items: (to_k_weight [C, ctx], fg_q_emb [ctx], bg_q_emb [B, ctx], lora_to_fg_q, lora_to_bg_q, lora_to_k) fp32."""
+
+    def __init__(self, items, batch: int):
+        lib = _lib.load()
+        f = lambda t: t.detach().to(torch.float32).contiguous()
+        self.keep, self.pool_q, table = [], [], []
+        self.batch, self.ctx_dim, self.max_c = batch, int(items[0][0].shape[1]), 0
+        dev = items[0][0].device
+        for to_k_w, fg, bg, wf, wb, wk in items:
+            _need_cuda(to_k_w, fg, bg, wf, wb, wk)
+            c = int(to_k_w.shape[0])
+            if to_k_w.shape[1] != self.ctx_dim or bg.reshape(batch, -1).shape[1] != self.ctx_dim:
+                raise ValueError("AdaPrepBatch: every item must share ctx_dim and batch")
+            ts = [f(to_k_w), f(fg.reshape(-1)), f(bg.reshape(batch, -1)), f(wf), f(wb), f(wk)]
+            pq = torch.empty((batch, 2, c), dtype=torch.float32, device=dev)
+            ws = torch.empty(int(lib.afb_ada_pool_prep_ws_floats(batch, c)), dtype=torch.float32, device=dev)
+            self.keep.append(ts + [ws])
+            self.pool_q.append(pq)
+            self.max_c = max(self.max_c, c)
+            table.append(_lib.AdaPrepItem(*[t.data_ptr() for t in ts], pq.data_ptr(), ws.data_ptr(), c, 0))
+        raw = bytes(memoryview((_lib.AdaPrepItem * len(table))(*table)).cast("B"))
+        self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        self.n = len(table)
+        self.nbytes = 4.0 * sum(float(t[0].numel()) for t in self.keep)
+
+    def run(self) -> None:
+        _run("ada_pool_prep", _lib.load().afb_ada_pool_prep_batched, _ptr(self.table), self.n, self.max_c, self.ctx_dim,
+             self.batch, _stream(), nbytes=self.nbytes, tag=f"batched{self.n}")
+
+
 @torch.library.custom_op("adaface_b200::ada_pool", mutates_args=())
 def ada_pool(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor],
              want_attn: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:

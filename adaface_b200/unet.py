@@ -377,15 +377,38 @@ class AdaPromptContext:
         main = torch.cuda.current_stream()
         if self.__dict__.get("_side") is None:
             self._side = torch.cuda.Stream()
+        # one descriptor table for every (layer, subject): built once per set of weights / prompt tensors, then the whole
+        # preparation is two launches per U-Net call (afb_ada_pool_prep_batched)
+        items, where, key = [], [], []
+        for layer_idx, st in layers:
+            ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
+            to_k = st.transformer_blocks[0].attn2.to_k
+            for i, s in enumerate(self.subjects):
+                n = s.n_instances
+                pk = s.embedder.poolers[ca].packed()
+                bg = s.layer_extra_means[ca][:n]
+                if bg.dim() == 1:
+                    bg = bg[None].expand(n, -1)
+                items.append((to_k.weight, s.layer_probes[ca], bg, pk["lora_to_fg_q"], pk["lora_to_bg_q"], pk["lora_to_k"]))
+                where.append((layer_idx, i, n))
+                key += [to_k.weight.data_ptr(), to_k.weight._version, s.layer_probes.data_ptr(), s.layer_probes._version,
+                        s.layer_extra_means.data_ptr(), s.layer_extra_means._version, pk["lora_to_k"].data_ptr(), n]
         self._pool_q, self._joined = {}, False
+        if not items:
+            return
+        batches = {}
+        for it, (layer_idx, i, n) in zip(items, where):        # items of one launch share the instance count
+            batches.setdefault(n, []).append((it, layer_idx, i))
+        key = tuple(key)
+        cache = self.__dict__.get("_prep_cache")
+        if cache is None or cache[0] != key:
+            cache = (key, {n: (ops.AdaPrepBatch([e[0] for e in group], n), group) for n, group in batches.items()})
+            self.__dict__["_prep_cache"] = cache
         self._side.wait_stream(main)
         with torch.cuda.stream(self._side):
-            for layer_idx, st in layers:
-                ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
-                to_k = st.transformer_blocks[0].attn2.to_k
-                for i, s in enumerate(self.subjects):
-                    n = s.n_instances
-                    pq = s.embedder.poolers[ca].prepare_queries(to_k, s.layer_probes[ca], s.layer_extra_means[ca][:n], n)
+            for n, (batch, group) in cache[1].items():
+                batch.run()
+                for pq, (_, layer_idx, i) in zip(batch.pool_q, group):
                     pq.record_stream(main)
                     self._pool_q[(layer_idx, i)] = pq
 

@@ -179,6 +179,24 @@ int64_t afb_ada_pool_prep_ws_floats(int batch, int channels);
 int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
                       const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k, float* pool_q,
                       float* prep_ws, int batch, int channels, afb_stream_t stream);
+/* The same for every (cross-attention layer, subject) of one U-Net call in two launches: `items` is a DEVICE array of
+ * n_items descriptors (the caller uploads it once; every pointer inside is a device pointer with the meaning of the
+ * afb_ada_pool_prep argument of the same name; ws holds afb_ada_pool_prep_ws_floats(batch, channels) floats).  All
+ * items share batch and ctx_dim; max_channels = the largest `channels`. */
+typedef struct afb_ada_prep_item {
+  const float* to_k_weight;
+  const float* fg_q_emb;
+  const float* bg_q_emb;
+  const float* lora_to_fg_q;
+  const float* lora_to_bg_q;
+  const float* lora_to_k;
+  float* pool_q;
+  float* ws;
+  int channels;
+  int reserved;
+} afb_ada_prep_item;
+int afb_ada_pool_prep_batched(const afb_ada_prep_item* items, int n_items, int max_channels, int ctx_dim, int batch,
+                              afb_stream_t stream);
 int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, float* fg_out,
                  float* bg_out, float* attn_fg, float* attn_bg, float* ws, int batch, int n_tokens, int channels,
                  afb_stream_t stream);

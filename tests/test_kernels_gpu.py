@@ -409,6 +409,27 @@ def test_ada_pool_and_head(ops, cuda_device, ca_idx, n):
     assert float(ctx[:b, :5].abs().max()) == 0 and float(ctx[b].abs().max()) == 0 and float(ctx[:b, 5 + K:].abs().max()) == 0
 
 
+def test_ada_pool_prep_batched_equals_per_layer(ops, cuda_device):
+    """afb_ada_pool_prep_batched (every layer / subject of a U-Net call in two launches) against the per-layer entry
+    point: same arithmetic, so identical results; a second run() recomputes in place."""
+    d, b = cuda_device, 3
+    items = []
+    for c in (320, 640, 1280, 320):
+        lg = c // 8
+        items.append(tuple(t.to(d) for t in (_r(f"pb.tok{c}", (c, 768), 768 ** -0.5), _r(f"pb.fg{c}", (768,)),
+                                               _r(f"pb.bg{c}", (b, 768)), _r(f"pb.wf{c}", (lg, lg), lg ** -0.5),
+                                               _r(f"pb.wb{c}", (lg, lg), lg ** -0.5), _r(f"pb.wk{c}", (lg, lg), lg ** -0.5))))
+    batch = ops.AdaPrepBatch(items, b)
+    batch.run()
+    for it, pq in zip(items, batch.pool_q):
+        ref = ops.ada_pool_prep(*it)
+        assert pq.shape == ref.shape and torch.equal(pq, ref)
+    for pq in batch.pool_q:
+        pq.zero_()
+    batch.run()
+    assert all(torch.equal(pq, ops.ada_pool_prep(*it)) for it, pq in zip(items, batch.pool_q))
+
+
 def test_casts_round_trip(ops, cuda_device):
     x = _r("cast.x", (3, 1001)).to(cuda_device)
     y = ops.to_bf16(x)
