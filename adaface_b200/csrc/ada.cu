@@ -447,10 +447,23 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
                                                        long long basis_sample_stride, int C, int TD, int K, int R, int D) {
   extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D]
   __shared__ float red[32];
-  pdl_wait();
-  pdl_trigger();
   const int k = blockIdx.x, b = blockIdx.y;
   const int F = 2 * C + TD;
+  {
+    // The coefficient rows and basis vectors of this k are parameters, not outputs of the pooling kernels: pull them
+    // into L2 while the predecessor is still running (programmatic dependent launch), so that the dependent part of
+    // this latency-bound kernel finds them there.
+    auto prefetch = [&](const float* ptr, long long nfloats) {
+      const char* pc = reinterpret_cast<const char*>(ptr);
+      for (long long off = static_cast<long long>(threadIdx.x) * 128; off < nfloats * 4; off += static_cast<long long>(blockDim.x) * 128)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pc + off));
+    };
+    prefetch(coeff_w + static_cast<long long>(k) * R * F, static_cast<long long>(R) * F);
+    prefetch(basis + static_cast<long long>(b) * basis_sample_stride + static_cast<long long>(k) * R * D, static_cast<long long>(R) * D);
+    if (bias != nullptr) prefetch(bias + static_cast<long long>(k) * D, D);
+  }
+  pdl_wait();
+  pdl_trigger();
   float* feat = sh;
   float* coeffs = feat + F;
   float* vec = coeffs + ((R + 3) & ~3);
