@@ -278,7 +278,12 @@ struct TCfg {
   // warps 0-3: TMA producer, MMA issuer, TMEM allocator, staging manager; then the epilogue warps, four (one per TMEM
   // lane quarter) per column group.  The GEGLU epilogue is ~35 issue slots per output element: it needs four warps
   // per scheduler to keep up with the tensor pipe at K = 320.
-  static constexpr int kEpiWarps = GEGLU ? 16 : 8;
+  // (measured: sixteen epilogue warps for the STORE epilogues change nothing -- those GEMMs are bound by the SM <-> L2
+  //  traffic of their operands and outputs, not by the epilogue arithmetic; -DAFB_GEMM_EPI_WARPS=16 rebuilds that way)
+#ifndef AFB_GEMM_EPI_WARPS
+#define AFB_GEMM_EPI_WARPS 8
+#endif
+  static constexpr int kEpiWarps = GEGLU ? 16 : AFB_GEMM_EPI_WARPS;
   static constexpr int kGroups = kEpiWarps / 4;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kStagingBytes = 2 * kOutChunks * kBoxBytes;     // double-buffered
@@ -1088,5 +1093,5 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
 
 extern "C" int afb_gemm_stats_parts(int64_t n) {
   const int64_t bn = (n % 160 == 0) ? 160 : 128;      // the tile width afb_gemm_bf16 picks for a STORE epilogue
-  return static_cast<int>(2 * ((n + bn - 1) / bn));
+  return static_cast<int>((AFB_GEMM_EPI_WARPS / 4) * ((n + bn - 1) / bn));   // one partial per epilogue column group
 }

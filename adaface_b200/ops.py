@@ -303,7 +303,7 @@ def linear_stats(a: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optiona
 @linear_stats.register_fake
 def _(a, w, bias, residual):
     n = w.shape[0]
-    parts = 2 * ((n + 159) // 160) if n % 160 == 0 else 2 * ((n + 127) // 128)
+    parts = stats_parts(n)
     return a.new_empty((a.shape[0], n), dtype=torch.bfloat16), a.new_empty((a.shape[0], parts, 2), dtype=torch.float32)
 
 
