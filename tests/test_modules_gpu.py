@@ -475,6 +475,27 @@ def test_unet_step_vs_reference_golden(afb, cuda_device):
     assert cosine(eps.cpu(), g["eps"]) > 0.999
 
 
+def test_unet_config5_geometry_96x96(afb, cuda_device):
+    """BASELINE.json configs[4] geometry (768x768 -> 96x96 latent, N = 9216 / 2304 / 576 / 144): the full U-Net call runs
+    through the fallback geometry of the shell (no 128-pixel boxes at width 96: cuDNN convolutions, interpolate +
+    conv Upsample) with the virtual concatenations and every path kernel at the large sizes.  No CPU oracle at this size
+    (the eager score tensors need > 20 GB), so the check is batch independence: a two-sample call must
+    equal the two one-sample calls, and the output must be finite and non-trivial."""
+    d = cuda_device
+    unet = _load_unet(afb, 17, d)
+    x = P.randn("cfg5.x", (2, 4, 96, 96), 23).to(d)
+    ctx = P.randn("cfg5.ctx", (32, 77, 768), 23).to(d)
+    info = {"use_layerwise_context": True, "is_training": False, "use_conv_attn_kernel_size": -1, "placeholder2indices": None}
+    t = torch.full((2,), 501, dtype=torch.long, device=d)
+    with torch.no_grad():
+        both = unet(x, t, context=ctx, extra_info=info)
+        one = [unet(x[i:i + 1], t[i:i + 1], context=ctx[16 * i:16 * (i + 1)], extra_info=info) for i in range(2)]
+    assert both.shape == (2, 4, 96, 96) and bool(torch.isfinite(both).all())
+    assert float(both.std()) > 1e-3
+    # (cuDNN may pick different algorithms per batch size: bf16-level agreement, not bit equality)
+    assert rel_l2(both, torch.cat(one)) < 2e-2
+
+
 @pytest.mark.slow
 @pytest.mark.parametrize("name", ["ddim10_small", "ddim50"])
 def test_ddim_full_loop_vs_reference_golden(afb, cuda_device, name):
