@@ -40,7 +40,8 @@ def st_flops(n, c, t=77, d=768):
     return 40.0 * n * c * c + 4.0 * n * n * c + 4.0 * n * t * c + 4.0 * t * d * c
 
 
-def unet_st_flops(hw=LATENT):
+def unet_st_flops(hw=None):
+    hw = LATENT if hw is None else hw
     n = hw * hw
     return sum(k * st_flops(m, c) for m, c, k in ((n, 320, 5), (n // 4, 640, 5), (n // 16, 1280, 5), (n // 64, 1280, 1)))
 
@@ -158,9 +159,12 @@ def run_reference(args):
 
 
 def workload_config(world):
-    return {"workload": "SD-1.5 U-Net DDIM step 512x512 (64x64 latent), n_samples=8 + CFG pair (batch 16) per GPU, "
-                        "guidance (10,4) annealed, 16 AdaEmbedding layers (K=9, fg5/bg4, r=12), layerwise context "
-                        "[16B,77,768], random-init weights (BASELINE.json configs[1])",
+    px = 8 * LATENT
+    which = "BASELINE.json configs[1]" if (LATENT, N_SAMPLES) == (64, 8) else \
+        "geometry and batch of BASELINE.json configs[4] (the ArcFace identity tokens are synthetic context rows like all others)"
+    return {"workload": f"SD-1.5 U-Net DDIM step {px}x{px} ({LATENT}x{LATENT} latent), n_samples={N_SAMPLES} + CFG pair "
+                        f"(batch {2 * N_SAMPLES}) per GPU, guidance (10,4) annealed, 16 AdaEmbedding layers (K=9, fg5/bg4, "
+                        f"r=12), layerwise context [16B,77,768], random-init weights ({which})",
             "n_samples_per_gpu": N_SAMPLES, "batch_incl_cfg_per_gpu": 2 * N_SAMPLES, "latent": [4, LATENT, LATENT],
             "ddim_steps_per_image": DDIM_STEPS, "parallelism": f"samples sharded over {world} GPU(s), no collective "
             "inside the step", "resblocks": "Upsample = nearest-2x folded into four 2x2 phase convolutions on this repo's implicit-GEMM tcgen05 kernel; "
@@ -443,7 +447,13 @@ def main():
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket one eager step with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     ap.add_argument("--dump-kernels", default=None, help="write the per-shape kernel breakdown of one step as CSV")
+    ap.add_argument("--workload", default="config2", choices=["config2", "config5"],
+                    help="config2 (default, the benchmarked one): 64x64 latents, 8 samples + CFG pair; config5: 96x96 "
+                         "latents, 16 samples + CFG pair (BASELINE.json configs[4] geometry; an extra data point)")
     args = ap.parse_args()
+    if args.workload == "config5":
+        global N_SAMPLES, LATENT
+        N_SAMPLES, LATENT = 16, 96
     if args.impl == "reference":
         run_reference(args)
     else:
