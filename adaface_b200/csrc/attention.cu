@@ -228,19 +228,21 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     {
       constexpr uint32_t idesc_qk = umma_idesc_bf16(kBlockQ, BKV, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(kBlockQ, C::kDPadN, 0, 1);   // B (= V) is MN-major
-      const uint32_t q_addr = smem_u32(sQ);
+      const uint64_t q_desc0 = umma_desc_kmajor_sw128(smem_u32(sQ));
       const uint32_t p_addr = smem_u32(sP);
       const bool leader = elect_one();
       // S_t = Q_t K_j^T : K-steps of 16 over the (padded) head dim
       auto issue_qk = [&](int t, int stage) {
         if (leader) {
-          const uint32_t k_addr = smem_u32(sK + stage * C::kKVTileBytes);
+          // one descriptor per operand tile; the K-step offsets are added to its 16-byte address field
+          const uint64_t kd = umma_desc_kmajor_sw128(smem_u32(sK + stage * C::kKVTileBytes));
+          const uint64_t qd = q_desc0 + static_cast<uint64_t>(t * (C::kQTileBytes >> 4));
           const uint32_t tmem_s = tmem_base + C::kTmemS + t * BKV;
 #pragma unroll
           for (int kk = 0; kk < C::kDPadK / 16; ++kk) {
-            const uint32_t qa = q_addr + t * C::kQTileBytes + (kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32;
-            const uint32_t ka = k_addr + (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-            umma_ss(tmem_s, umma_desc_kmajor_sw128(qa), umma_desc_kmajor_sw128(ka), idesc_qk, kk != 0);
+            const uint64_t qoff = static_cast<uint64_t>(((kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32) >> 4);
+            const uint64_t koff = static_cast<uint64_t>(((kk >> 2) * (BKV * 128) + (kk & 3) * 32) >> 4);
+            umma_ss(tmem_s, qd + qoff, kd + koff, idesc_qk, kk != 0);
           }
           umma_commit(&s_full[t]);
         }
@@ -248,19 +250,17 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       // O_t += P_t V_j : K-steps of 16 keys; V tile is [key][64 cols] per atom -> MN-major, LBO = atom stride
       auto issue_pv = [&](int t, int stage, bool first, bool last) {
         if (leader) {
-          const uint32_t v_addr = smem_u32(sV + stage * C::kKVTileBytes);
+          const uint64_t vd = umma_desc_mnmajor_sw128(smem_u32(sV + stage * C::kKVTileBytes), BKV * 128);
           const uint32_t tmem_o = tmem_base + C::kTmemO + t * C::kDPadN;
 #pragma unroll
           for (int kk = 0; kk < BKV / 16; ++kk) {
-            const uint32_t va = v_addr + kk * (16 * 128);
+            const uint64_t voff = static_cast<uint64_t>((kk * (16 * 128)) >> 4);
             if constexpr (C::kPTmem) {
               // A = P_t from TMEM: 16 keys = 8 columns of packed bf16 pairs, same lanes as the S rows
-              umma_ts(tmem_o, tmem_base + C::kTmemS + t * BKV + kk * 8, umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
-                      !(first && kk == 0));
+              umma_ts(tmem_o, tmem_base + C::kTmemS + t * BKV + kk * 8, vd + voff, idesc_pv, !(first && kk == 0));
             } else {
               const uint32_t pa = p_addr + t * C::kPBytes + kk * 32;
-              umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), umma_desc_mnmajor_sw128(va, BKV * 128), idesc_pv,
-                      !(first && kk == 0));
+              umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), vd + voff, idesc_pv, !(first && kk == 0));
             }
           }
           if (!C::kPTmem || last) umma_commit(&pv_done[t]);
