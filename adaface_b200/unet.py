@@ -27,10 +27,14 @@ from .embedding import LAYER_IDX2CA_LAYER_IDX, AdaEmbedding
 
 Tensor = torch.Tensor
 CL = torch.channels_last
-# AFB_CONV=1: every eligible 3x3 ResBlock convolution on this repo's implicit-GEMM kernel (default: cuDNN, which is
-# ~0.5 ms per step faster at batch 16 - its kernels reuse the input tile across the nine taps).  AFB_UPSAMPLE_FOLD=0:
+# AFB_CONV=1: every eligible 3x3 ResBlock convolution on this repo's implicit-GEMM kernel; 0: all on cuDNN; default
+# "auto": the shapes listed in _NATIVE_CONV_AUTO (cuDNN is faster on the others at batch 16 - its kernels reuse the
+# input tile across the nine taps).  AFB_UPSAMPLE_FOLD=0:
 # Upsample as interpolate + conv instead of the folded four-phase 2x2 convolution.
-_NATIVE_CONV = os.environ.get("AFB_CONV", "0") != "0"
+_NATIVE_CONV = os.environ.get("AFB_CONV", "auto")
+# (Cin, Cout, width) of the 3x3 convolutions that are faster on the implicit-GEMM kernel than on cuDNN at batch 16
+# (eager CUDA-event times on B200, tools/trace_aten.py vs the bench's per-shape table): the deep-K decoder shapes
+_NATIVE_CONV_AUTO = {(2560, 1280, 16), (960, 320, 64), (1920, 1280, 16), (640, 1280, 16)}
 # AFB_CONV_W="64,32": image widths whose 3x3 convolutions take the native kernel when AFB_CONV=1 (default: all)
 _NATIVE_CONV_W = tuple(int(v) for v in os.environ.get("AFB_CONV_W", "").split(",") if v)
 _NATIVE_UPSAMPLE = os.environ.get("AFB_UPSAMPLE_FOLD", "1") != "0"
@@ -119,7 +123,11 @@ class _Bf16Conv(nn.Conv2d):
     def native_ok(self, x) -> bool:
         """True when this convolution runs as an implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3)
         instead of cuDNN: AFB_CONV=1 and a supported geometry."""
-        return _NATIVE_CONV and (not _NATIVE_CONV_W or x.shape[3] in _NATIVE_CONV_W) and self.geometry_ok(x)
+        if _NATIVE_CONV == "0":
+            return False
+        if _NATIVE_CONV == "auto":
+            return (self.in_channels, self.out_channels, x.shape[3]) in _NATIVE_CONV_AUTO and self.geometry_ok(x)
+        return (not _NATIVE_CONV_W or x.shape[3] in _NATIVE_CONV_W) and self.geometry_ok(x)
 
     def geometry_ok(self, x) -> bool:
         """3x3 / stride 1 / padding 1 with Cin % 64 == 0 on an image that tiles into 128-pixel boxes."""
@@ -530,7 +538,7 @@ class UNetModel(nn.Module):
         pack = self.__dict__.get("_emb_pack")
         if pack is None or pack[0] != key:
             with torch.no_grad():
-                w = torch.cat([rb.emb_layers[1].weight.detach().float() for rb in blocks], dim=0).contiguous()
+                w = torch.cat([rb.emb_layers[1].weight.detach().float() for rb in blocks], dim=0).to(torch.bfloat16).contiguous()
                 b = torch.cat([rb.emb_layers[1].bias.detach().float() + rb.in_layers[2].bias.detach().float()
                                for rb in blocks]).contiguous()
             offs, o = [], 0
@@ -540,7 +548,12 @@ class UNetModel(nn.Module):
             pack = (key, w, b, offs)
             self.__dict__["_emb_pack"] = pack
         _, w, b, offs = pack
-        e_all = F.linear(F.silu(emb), w, b)
+        # one [B, 1280] x [20160, 1280]^T GEMM on the tcgen05 kernel (bf16 operands, fp32 accumulate and output): the
+        # fp32 cuBLAS path streamed 103 MB of weights per step
+        if emb.is_cuda and w.shape[0] % 32 == 0:
+            e_all = ops.linear(F.silu(emb).to(torch.bfloat16), w, b, None, True)
+        else:
+            e_all = F.linear(F.silu(emb), w.float(), b)
         return EmbBundle(emb, {i: e_all[:, o:o + n] for i, o, n in offs})
 
     def forward(self, x: Tensor, timesteps: Optional[Tensor] = None, context: Optional[Tensor] = None, y=None,
@@ -587,7 +600,7 @@ class UNetModel(nn.Module):
             ada.prepare_queries(self.spatial_transformers())
         bundle = self.emb_bundle(emb)
         hs = []
-        h = self.input_blocks[0][0](x.to(torch.bfloat16).contiguous(memory_format=CL))
+        h = self.input_blocks[0][0].conv_add(x.to(torch.bfloat16).contiguous(memory_format=CL))
         hs.append(h)
         layer_idx = 1
         for module in list(self.input_blocks)[1:]:
