@@ -346,12 +346,15 @@ struct GemmTmaDev {
   // is a 2x2 convolution of the LOW-resolution image with taps (py - 1 + a, px - 1 + c); its BN-column blocks store to
   // the pixels (2i + py, 2j + px) of the high-resolution output through a 5-D tensor map; fold_cout = N / 4
   int conv_fold, nb_per_phase, fold_cout;
+  // A virtually concatenated along K (plain GEMM only): k-blocks [0, k1_blocks) come from tm_a, the rest from tm_a2
+  int k1_blocks;
 };
 
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
 __global__ void __launch_bounds__((TCfg<BN, GEGLU, kPair>::kThreads), 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_res,
+                     const __grid_constant__ CUtensorMap tm_a2,
                      const GemmTmaDev p) {
   using C = TCfg<BN, GEGLU, kPair>;
   constexpr int NC = C::kOutChunks;
@@ -382,6 +385,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_out);
     if (p.has_res) tma_prefetch_desc(&tm_res);
+    if (p.k1_blocks < p.num_k_blocks) tma_prefetch_desc(&tm_a2);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) {
@@ -446,12 +450,14 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             // phase (the pending arrival keeps it open), never before the previous phase closed (empty_bar)
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
             if (p.conv_cblocks != 0) tma_load_4d_pair(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
-            else tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            else if (kb < p.k1_blocks) tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            else tma_load_2d_pair(&tm_a2, &full_bar[stage], sa, (kb - p.k1_blocks) * kBK, m_blk * kBM);
             tma_load_2d_pair(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN + cta_rank * C::kBRows, kEvictLast);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
             if (p.conv_cblocks != 0) tma_load_4d(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
-            else tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            else if (kb < p.k1_blocks) tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
+            else tma_load_2d(&tm_a2, &full_bar[stage], sa, (kb - p.k1_blocks) * kBK, m_blk * kBM);
             tma_load_2d(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN, kEvictLast);
           }
           if (p.conv_cblocks != 0 && ++cblk == p.conv_cblocks) {
@@ -836,7 +842,8 @@ int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows,
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
 int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   using C = TCfg<BN, GEGLU, kPair>;
-  CUtensorMap tm_a, tm_w, tm_out, tm_res;
+  CUtensorMap tm_a, tm_w, tm_out, tm_res, tm_a2;
+  const int64_t k1 = a.a2 != nullptr ? a.k_split : a.k;      // columns of A that come from a.a
   if (a.conv_h > 0) {
     // NHWC image [B, H, W, Cin], pixel stride lda; the box is 128 consecutive pixels in (b, h, w) order
     const uint64_t cin = static_cast<uint64_t>(a.k / (a.conv_fold != 0 ? 4 : 9)), W = static_cast<uint64_t>(a.conv_w),
@@ -850,10 +857,18 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
     if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.a, dims, strides, box, Swizzle::B128))
       return rc;
   } else {
-    const uint64_t dims[2] = {static_cast<uint64_t>(a.k), static_cast<uint64_t>(a.m)};
+    const uint64_t dims[2] = {static_cast<uint64_t>(k1), static_cast<uint64_t>(a.m)};
     const uint64_t strides[1] = {static_cast<uint64_t>(a.lda) * 2};
     const uint32_t box[2] = {kBK, kBM};
     if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.a, dims, strides, box, Swizzle::B128))
+      return rc;
+  }
+  tm_a2 = tm_a;
+  if (a.a2 != nullptr) {
+    const uint64_t dims[2] = {static_cast<uint64_t>(a.k - k1), static_cast<uint64_t>(a.m)};
+    const uint64_t strides[1] = {static_cast<uint64_t>(a.lda2) * 2};
+    const uint32_t box[2] = {kBK, kBM};
+    if (int rc = make_tensor_map(&tm_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.a2, dims, strides, box, Swizzle::B128))
       return rc;
   }
   {
@@ -900,6 +915,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   const int taps = a.conv_fold != 0 ? 4 : 9;
   p.conv_cblocks = a.conv_h > 0 ? static_cast<int>(a.k / taps / kBK) : 0;
   p.conv_fold = a.conv_fold;
+  p.k1_blocks = a.a2 != nullptr ? static_cast<int>(k1 / kBK) : p.num_k_blocks;
   p.fold_cout = static_cast<int>(a.n / 4);
   p.nb_per_phase = a.conv_fold != 0 ? static_cast<int>(a.n / 4 / BN) : 1;
   p.conv_h = a.conv_h;
@@ -919,7 +935,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
     const int tiles = p.num_m_blocks * p.num_n_blocks;
     grid = tiles < num_sms() ? tiles : num_sms();
   }
-  AFB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(C::kThreads), C::kSmemBytes, stream, kPair ? 2 : 1, tm_a, tm_w, tm_out, tm_res, p));
+  AFB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(C::kThreads), C::kSmemBytes, stream, kPair ? 2 : 1, tm_a, tm_w, tm_out, tm_res, tm_a2, p));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -1044,6 +1060,14 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
     AFB_REQUIRE(a.epilogue == AFB_EPI_STORE && a.out_dtype == AFB_BF16 && (a.residual == nullptr || a.residual_dtype == AFB_BF16) &&
                     a.ln_stats == nullptr && a.row_stats_out == nullptr,
                 "afb_gemm_bf16: conv mode takes the bf16 STORE epilogue (bias, bf16 residual) only");
+  } else if (a.a2 != nullptr) {
+    // A = [a | a2] along K: the decoder's 1x1 skip convolution of th.cat([h, hs.pop()], 1) (openaimodel.py:1004-1010, 277)
+    AFB_REQUIRE(a.k_split > 0 && a.k_split < a.k && a.k_split % 64 == 0, "afb_gemm_bf16: k_split must be a multiple of 64 inside (0, K)");
+    AFB_REQUIRE(a.lda >= a.k_split && a.lda2 >= a.k - a.k_split && a.lda2 % 8 == 0 && a.ldw >= a.k &&
+                    (reinterpret_cast<uintptr_t>(a.a2) & 15) == 0,
+                "afb_gemm_bf16: a2 must be 16-byte aligned with lda2 %% 8 == 0 and the leading dimensions must cover their halves");
+    AFB_REQUIRE(a.epilogue == AFB_EPI_STORE && a.out_dtype == AFB_BF16 && (a.residual == nullptr || a.residual_dtype == AFB_BF16),
+                "afb_gemm_bf16: the two-source A operand takes the bf16 STORE epilogue only");
   } else {
     AFB_REQUIRE(a.lda >= a.k && a.ldw >= a.k, "afb_gemm_bf16: leading dimension smaller than K");
   }

@@ -184,7 +184,7 @@ def _(x, gamma, beta, eps):
 def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], epilogue: int,
           ldo: int, ldr: int, hw: int = 0, stats_out: Optional[Tensor] = None, ln_stats: Optional[Tensor] = None,
           ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0, conv_hw: Optional[Tuple[int, int]] = None,
-          conv_fold: bool = False) -> None:
+          conv_fold: bool = False, a2: Optional[Tensor] = None) -> None:
     _need_cuda(a, w, out, bias, residual, stats_out, ln_stats, ln_colsum)
     if ln_stats is not None:
         if ln_colsum is None or ln_stats.dtype != torch.float32 or ln_colsum.dtype != torch.float32 \
@@ -195,16 +195,19 @@ def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: O
         raise ValueError("gemm: bf16 operands with contiguous K expected")
     if bias is not None and bias.dtype != torch.float32:
         raise ValueError("gemm: bias must be fp32")
+    if a2 is not None and (a2.dtype != torch.bfloat16 or a2.stride(-1) != 1 or a2.shape[0] != a.shape[0]):
+        raise ValueError("gemm: a2 must be bf16 [M, K2] with contiguous rows")
     args = GemmArgs(a=_ptr(a), w=_ptr(w), out=_ptr(out), bias=_ptr(bias), residual=_ptr(residual),
-                    m=a.shape[0], n=w.shape[0], k=w.shape[1] if conv_hw else a.shape[1], lda=a.stride(0), ldw=w.stride(0),
+                    a2=_ptr(a2), k_split=a.shape[1] if a2 is not None else 0, lda2=a2.stride(0) if a2 is not None else 0,
+                    m=a.shape[0], n=w.shape[0], k=w.shape[1] if (conv_hw or a2 is not None) else a.shape[1], lda=a.stride(0), ldw=w.stride(0),
                     ldo=ldo, ldr=ldr, conv_h=conv_hw[0] if conv_hw else 0, conv_w=conv_hw[1] if conv_hw else 0, conv_fold=1 if conv_fold else 0,
                     epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
                     residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
                     else _lib.DT_BF16, hw=hw, row_stats_out=_ptr(stats_out), ln_stats=_ptr(ln_stats),
                     ln_colsum=_ptr(ln_colsum), ln_parts=0 if ln_stats is None else ln_stats.shape[1], ln_eps=ln_eps)
-    m, n, k = a.shape[0], w.shape[0], w.shape[1] if conv_hw else a.shape[1]
+    m, n, k = a.shape[0], w.shape[0], w.shape[1] if (conv_hw or a2 is not None) else a.shape[1]
     _run(("conv3x3_up2_bf16" if conv_fold else "conv3x3_bf16") if conv_hw else "gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
-         nbytes=2.0 * (m * a.shape[1] + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
+         nbytes=2.0 * (m * (k if a2 is not None else a.shape[1]) + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("c" if a2 is not None else "") + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
          + ("r" if residual is not None else ""))
 
 
@@ -280,6 +283,24 @@ def linear(a: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Tens
 @linear.register_fake
 def _(a, w, bias, residual, out_fp32):
     return a.new_empty((a.shape[0], w.shape[0]), dtype=torch.float32 if out_fp32 else torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::linear_cat", mutates_args=())
+def linear_cat(a1: Tensor, a2: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Tensor]) -> Tensor:
+    """out[M,N] = cat([a1, a2], 1) @ w[N, K1+K2]^T + bias (+ residual) without materialising the concatenation: the
+    GEMM's K loop reads its first K1 columns from a1 and the rest from a2 (K1 % 64 == 0).  bf16 in / bf16 out."""
+    if a1.dim() != 2 or a2.dim() != 2 or w.dim() != 2 or a1.shape[1] + a2.shape[1] != w.shape[1] or a1.shape[1] % 64:
+        raise ValueError("linear_cat: a1 [M,K1], a2 [M,K2], w [N,K1+K2] with K1 %% 64 == 0 expected")
+    out = torch.empty((a1.shape[0], w.shape[0]), dtype=torch.bfloat16, device=a1.device)
+    if residual is not None and (residual.shape != out.shape or residual.stride(-1) != 1 or residual.dtype != torch.bfloat16):
+        raise ValueError("linear_cat: residual must be bf16 [M,N] with contiguous rows")
+    _gemm(a1, w, out, bias, residual, _lib.EPI_STORE, out.stride(0), 0 if residual is None else residual.stride(0), a2=a2)
+    return out
+
+
+@linear_cat.register_fake
+def _(a1, a2, w, bias, residual):
+    return a1.new_empty((a1.shape[0], w.shape[0]), dtype=torch.bfloat16)
 
 
 def stats_parts(n: int) -> int:

@@ -266,9 +266,9 @@ class ResBlock(TimestepBlock):
         return out.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
 
     def _skip_pair(self, pair: CatPair, h: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:
-        """1x1 skip convolution of the virtual concatenation: W[:, :C1] . a + W[:, C1:] . b as two chained GEMMs (the
-        second takes the first's output as its residual).  With h / bias given the first GEMM's epilogue also adds
-        conv2's output and the biases, so the result is the ResBlock's output."""
+        """1x1 skip convolution of the virtual concatenation as ONE GEMM whose K loop reads its first C1 columns from a
+        and the rest from b (ops.linear_cat; two chained GEMMs when C1 is not a multiple of 64).  With h / bias given the
+        epilogue also adds conv2's output and the biases, so the result is the ResBlock's output."""
         sc = self.skip_connection
         c1 = pair.a.shape[1]
         key = (sc.weight.data_ptr(), sc.weight._version, c1)
@@ -276,14 +276,17 @@ class ResBlock(TimestepBlock):
         if c is None or c[0] != key:
             with torch.no_grad():
                 w = sc.weight.detach().reshape(sc.out_channels, -1).to(torch.bfloat16)
-                c = (key, w[:, :c1].contiguous(), w[:, c1:].contiguous())
+                c = (key, w[:, :c1].contiguous(), w[:, c1:].contiguous(), w.contiguous())
             self.__dict__["_skip_pair_w"] = c
         b_, _, h_, w_ = pair.shape
         at = pair.a.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
         bt = pair.b.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
         ht = None if h is None else h.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
-        s = ops.linear(bt, c[2], bias, ht, False)
-        s = ops.linear(at, c[1], None, s, False)
+        if c1 % 64 == 0:
+            s = ops.linear_cat(at, bt, c[3], bias, ht)
+        else:
+            s = ops.linear(bt, c[2], bias, ht, False)
+            s = ops.linear(at, c[1], None, s, False)
         return s.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
 
     def forward(self, x, emb):

@@ -123,6 +123,11 @@ typedef struct afb_gemm_args {
    * (py-1+a, px-1+c); bias is [4*Cout] (the conv bias repeated); out is bf16 [B, 2*conv_h, 2*conv_w, Cout], ldo = Cout.
    * 2.25x fewer FLOPs than convolving the upsampled image, and the upsampled tensor is never written. */
   int conv_fold;
+  /* a2 != NULL (plain GEMM, bf16 STORE epilogue): the A operand is the virtual concatenation [a | a2] along K -
+   * columns [0, k_split) from a (leading dimension lda), columns [k_split, k) from a2 [M, k - k_split] (leading dimension
+   * lda2); k_split % 64 == 0.  The decoder's 1x1 skip convolution over th.cat([h, hs.pop()], 1) in one GEMM. */
+  const afb_bf16* a2;
+  int64_t k_split, lda2;
 } afb_gemm_args;
 int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
 /* number of (sum, sum of squares) partials per row that a STORE GEMM with n output columns emits */

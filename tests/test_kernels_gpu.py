@@ -197,6 +197,25 @@ def test_conv3x3_unsupported_geometry_raises(ops, cuda_device):
                     torch.zeros((32, 9 * 48), dtype=torch.bfloat16, device=d), None, None, 8, 8)   # Cin % 64
 
 
+@pytest.mark.parametrize("m,n,k1,k2", [(256, 320, 320, 320), (300, 640, 640, 320), (1024, 1280, 1280, 1280), (130, 160, 64, 40)])
+def test_linear_virtual_concat_along_k(ops, cuda_device, m, n, k1, k2):
+    """A = [a1 | a2] along K read from two tensors (the decoder's 1x1 skip convolution over th.cat([h, hs.pop()], 1),
+    openaimodel.py:1004-1010, 277) against the GEMM on the materialised concatenation and the fp32 formula."""
+    d = cuda_device
+    a1 = _r("lc.a1", (m, k1)).to(torch.bfloat16).to(d)
+    a2 = _r("lc.a2", (m, k2)).to(torch.bfloat16).to(d)
+    w = _r("lc.w", (n, k1 + k2), (k1 + k2) ** -0.5).to(torch.bfloat16).to(d)
+    bias = (0.1 * _r("lc.b", (n,))).to(d)
+    res = _r("lc.r", (m, n)).to(torch.bfloat16).to(d)
+    ref = torch.cat([a1, a2], 1).float() @ w.float().t() + bias + res.float()
+    out = ops.linear_cat(a1, a2, w, bias, res)
+    assert rel_l2(out.float(), ref) < 4e-3
+    if (k1 + k2) % 8 == 0:
+        mat = ops.linear(torch.cat([a1, a2], 1).contiguous(), w, bias, res, False)
+        assert torch.equal(out, mat)          # same tiles, same accumulation order
+    assert rel_l2(ops.linear_cat(a1, a2, w, None, None).float(), ref - bias - res.float()) < 4e-3
+
+
 def test_linear_strided_views(ops, cuda_device):
     """A operand and residual as column slices of wider buffers (lda/ldr != K/N)."""
     m, n, k = 256, 320, 320
