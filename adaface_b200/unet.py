@@ -76,7 +76,8 @@ def gn_silu(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Te
 class CatPair:
     """th.cat([h, hs.pop()], dim=1) (openaimodel.py:1004-1010) kept as its two halves: the decoder ResBlock that
     consumes it normalises both sources in one GroupNorm pass (ops.groupnorm_tokens_cat) and applies its 1x1 skip
-    convolution as two chained GEMMs, so large concatenations are never written.  AFB_CAT=0 materialises always."""
+    convolution as one GEMM over both sources (ops.linear_cat), so large concatenations are never written.  AFB_CAT=0
+    materialises always."""
 
     def __init__(self, a: Tensor, b: Tensor):
         self.a, self.b = a, b
