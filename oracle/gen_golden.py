@@ -297,6 +297,46 @@ def case_resblock(ref, name="resblock", seed=21):
     _save(name, **out)
 
 
+STATIC_TOKEN = 49408        # first id past the CLIP vocabulary: what add_tokens gives the placeholder
+
+
+def static_inputs(name, seed, b=3, n=77, K=9):
+    """Token embeddings and token ids of b prompts: prompt 0 holds the placeholder (followed by its K-1 filler
+    slots) at position 5 and once more at 40 (only the first counts, embedding_manager.py:1363-1366), prompt 1 has
+    none, prompt 2 holds it at position 20."""
+    emb = P.randn(f"{name}.embedded_text", (b, n, 768), seed, 0.05)
+    tok = (P.randn(f"{name}.tokens", (b, n), seed).abs() * 1000).long() % 49000 + 1
+    tok[0, 5] = STATIC_TOKEN
+    tok[0, 40] = STATIC_TOKEN
+    tok[2, 20] = STATIC_TOKEN
+    return emb, tok
+
+
+def case_static(ref, name="static_emb", seed=22, K=9, r=12, L=16):
+    """SURVEY 8f N2.  StaticLayerwiseEmbedding.forward run on the unmodified reference class
+    (embedding_manager.py:497-537), and the splice of its rows into the layer-repeated prompt by the reference's own
+    statements of EmbeddingManager.get_static_embedding (the method itself needs a CLIP tokenizer/embedder, absent
+    here): repeat :1350, where :1360, extract_first_index_in_each_instance :1366 (the reference's function,
+    ldm/util.py:2114), per-k assignment :1510-1552 with REAL_OCCURS_IN_BATCH repeats :1546."""
+    sd = P.init_static_embedding(seed, K, r, 2)
+    em = ref.embedding_manager
+    mod = em.StaticLayerwiseEmbedding(num_layers=L, num_vectors_per_subj_token=K, out_emb_dim=768, r=r,
+                                      init_vecs=torch.zeros(2, 768), has_bias=True, device_type="cpu")
+    mod.load_state_dict(sd, strict=True)
+    with torch.no_grad():
+        static = mod.eval()()
+    emb, tok = static_inputs(name, seed, K=K)
+    B, N = tok.shape
+    embedded_text = emb.unsqueeze(1).repeat(1, L, 1, 1).view(B * L, N, -1).clone()
+    tokenized_text = tok.unsqueeze(1).repeat(1, L, 1).view(B * L, N)
+    placeholder_indices = torch.where(tokenized_text == STATIC_TOKEN)
+    first = ref.util.extract_first_index_in_each_instance(placeholder_indices)
+    real_occurs = first[0].numel() // L
+    for k in range(K):
+        embedded_text[(first[0], first[1] + k)] = static[:, k].repeat(real_occurs, 1)
+    _save(name, meta=np.array([seed, K, r, L, STATIC_TOKEN]), static=static, spliced=embedded_text[:, :, ::16])
+
+
 def main(argv):
     ref = RH.load()
     torch.set_num_threads(os.cpu_count() or 1)
@@ -327,6 +367,8 @@ def main(argv):
             case_ddim50(ref)
         elif name == "resblock":
             case_resblock(ref)
+        elif name == "static_emb":
+            case_static(ref)
         elif name == "ddim10_small":
             case_ddim50(ref, "ddim10_small", seed=19, hw=16, steps=10)
         else:

@@ -207,6 +207,31 @@ def init_ada_embedding(seed: int, K: int = 9, r: int = 12, n_init: int = 2) -> D
     return out
 
 
+def static_embedding_spec(K: int = 9, r: int = 12, n_init: int = 2, num_layers: int = 16, out_dim: int = 768):
+    """state_dict keys/shapes of StaticLayerwiseEmbedding(num_layers, K, out_dim, r, init_vecs [n_init, 768],
+    has_bias=True): embedding_manager.py:374-490."""
+    if n_init > 0:
+        yield "pre_vecs", (K, n_init, out_dim)
+    yield "basis_rand_weights", (num_layers, K, r)
+    yield "basis_vecs", (K, r - n_init, out_dim)
+    yield "basis_comm_weights", (1, K, r)
+    yield "bias", (num_layers, K, out_dim)
+
+
+def init_static_embedding(seed: int, K: int = 9, r: int = 12, n_init: int = 2) -> Dict[str, torch.Tensor]:
+    out = {}
+    for k, s in static_embedding_spec(K, r, n_init):
+        if k in ("pre_vecs", "basis_vecs"):
+            out[k] = draw("static." + k, s, seed, "normal", 0.25)
+        elif k == "bias":
+            out[k] = draw("static." + k, s, seed, "normal", 0.02)
+        elif k == "basis_comm_weights":
+            out[k] = draw("static." + k, s, seed, "normal", 0.2) + 1.0 / r
+        else:
+            out[k] = draw("static." + k, s, seed, "normal", 0.1)
+    return out
+
+
 def randn(key: str, shape, seed: int, scale: float = 1.0) -> torch.Tensor:
     """A named synthetic input tensor."""
     return draw(key, tuple(shape), seed, "normal", scale)

@@ -282,6 +282,46 @@ def ada_embedding(p: Params, ca_layer_idx: int, x: Tensor, q: Tensor, to_k_weigh
 
 
 # --------------------------------------------------------------------------------------------
+# StaticLayerwiseEmbedding + the splice of its rows into the layerwise prompt
+# --------------------------------------------------------------------------------------------
+def static_layerwise_embedding(p: Params, out_emb_dim: int = 768) -> Tensor:
+    """StaticLayerwiseEmbedding.forward, not zero-shot: embedding_manager.py:497-537.
+
+    p: basis_rand_weights [L,K,r], basis_comm_weights [1,K,r], basis_vecs [K,r-N,D], optional pre_vecs [K,N,D],
+    bias [L,K,D] (absent = 0).  Returns [L,K,D]."""
+    weights = p["basis_rand_weights"] + p["basis_comm_weights"]                          # :501
+    basis = p["basis_vecs"]
+    if "pre_vecs" in p and p["pre_vecs"] is not None:
+        basis = torch.cat([p["pre_vecs"], basis], dim=1)                                 # :516-518
+    L, K, _ = weights.shape
+    unnorm = torch.einsum("lkr,krd->lkd", weights, basis)                                # :522
+    ln = F.layer_norm(unnorm, (out_emb_dim,), None, None, 1e-5)                          # :529 (no affine)
+    out = ln / math.sqrt(out_emb_dim)                                                    # :530
+    bias = p.get("bias", None)
+    return out if bias is None else out + bias                                           # :534
+
+
+def splice_static_embedding(embedded_text: Tensor, tokenized_text: Tensor, placeholder_token: int,
+                            subj_static_embedding: Tensor, num_layers: int = 16) -> Tensor:
+    """EmbeddingManager.get_static_embedding, inference branch for one placeholder: embedding_manager.py:1341-1352
+    (repeat over the layers, instance-major / layer-minor), :1360-1366 (first occurrence per instance),
+    :1510-1552 (vector k of layer l goes to token position first + k of row b*L + l).
+
+    embedded_text [B,N,D], tokenized_text [B,N] (int), subj_static_embedding [L,K,D].  Returns [B*L,N,D]."""
+    B, N, D = embedded_text.shape
+    L, K = num_layers, subj_static_embedding.shape[1]
+    out = embedded_text.unsqueeze(1).repeat(1, L, 1, 1).reshape(B * L, N, D).clone()
+    for b in range(B):
+        hits = (tokenized_text[b] == placeholder_token).nonzero().flatten()
+        if hits.numel() == 0:
+            continue
+        first = int(hits[0])
+        for k in range(K):
+            out[b * L:(b + 1) * L, first + k] = subj_static_embedding[:, k].to(out.dtype)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
 # DDIM schedule + CFG combine + update (ddim.py:28-68,135-296; diffusionmodules/util.py:21-77)
 # --------------------------------------------------------------------------------------------
 def make_beta_schedule_linear(n_timestep: int = 1000, linear_start: float = 0.00085,

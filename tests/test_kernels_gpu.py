@@ -340,6 +340,28 @@ def test_attention_key_mask(ops, cuda_device, c, n):
     assert rel_l2(out.float(), ref) < BF16_TOL
 
 
+@pytest.mark.parametrize("c,nq,nk,masked", [(320, 4096, 77, False), (320, 200, 1, False), (320, 129, 128, False),
+                                            (640, 1024, 77, False), (640, 130, 65, True), (1280, 256, 77, False),
+                                            (1280, 70, 128, True), (320, 300, 77, True)])
+def test_attention_short_key_sequence(ops, cuda_device, c, nq, nk, masked):
+    """kv_len <= 128 takes the one-query-tile configuration (several CTAs per SM, 128/256 TMEM columns each): ragged
+    query lengths, 1..128 keys (the partial second key tile is masked inside the kernel), optional key mask."""
+    b, heads = 3, 8
+    q = _r("as.q", (b, nq, c)).to(torch.bfloat16)
+    k = _r("as.k", (b, nk, c)).to(torch.bfloat16)
+    v = _r("as.v", (b, nk, c)).to(torch.bfloat16)
+    mask = None
+    if masked:
+        mask = (_r("as.m", (b, nk)) > -0.5)
+        mask[:, 0] = True
+    scale = (c // heads) ** -0.5
+    ref = _attn_ref(q.float(), k.float(), v.float(), heads, scale, mask)
+    d = cuda_device
+    out = ops.attention(q.to(d), k.to(d), v.to(d), heads, scale, None if mask is None else mask.to(d))
+    assert torch.isfinite(out).all()
+    assert rel_l2(out.float(), ref) < BF16_TOL
+
+
 # ---------------------------------------------------------------------------------------------- K12 / K13
 def test_explicit_cross_attention_matches_fused(ops, cuda_device):
     """cross_scores + softmax_pv (the materialised path used by save_attn_vars / conv attention) against the oracle
