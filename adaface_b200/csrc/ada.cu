@@ -535,6 +535,91 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
   }
 }
 
+// ---- N2: StaticLayerwiseEmbedding + splice ------------------------------------------------------------------
+// Block (k, l): coefficients basis_rand_weights[l, k] + basis_comm_weights[0, k] (embedding_manager.py:501), the
+// combination of vector k's basis (pre_vecs | basis_vecs, :516-522), LayerNorm without affine (:529), 1/sqrt(D)
+// (:530) and the layer/vector bias (:534).
+__global__ void __launch_bounds__(256) static_layerwise_kernel(const float* __restrict__ rand_w, const float* __restrict__ comm_w,
+                                                               const float* __restrict__ pre_vecs, int n_pre,
+                                                               const float* __restrict__ basis_vecs,
+                                                               const float* __restrict__ bias, float* __restrict__ out, int K,
+                                                               int R, int D) {
+  extern __shared__ float sh[];    // coeffs [R rounded up to 4], vec [D]
+  __shared__ float red[32];
+  pdl_wait();
+  pdl_trigger();
+  const int k = blockIdx.x, l = blockIdx.y;
+  float* coeffs = sh;
+  float* vec = sh + ((R + 3) & ~3);
+  for (int r = threadIdx.x; r < R; r += blockDim.x)
+    coeffs[r] = rand_w[(static_cast<long long>(l) * K + k) * R + r] + comm_w[static_cast<long long>(k) * R + r];
+  __syncthreads();
+  const float* pre = pre_vecs == nullptr ? nullptr : pre_vecs + static_cast<long long>(k) * n_pre * D;
+  const float* bas = basis_vecs + static_cast<long long>(k) * (R - n_pre) * D;
+  float s = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float a = 0.f;
+    for (int r = 0; r < n_pre; ++r) a += coeffs[r] * __ldg(pre + static_cast<long long>(r) * D + d);
+    for (int r = n_pre; r < R; ++r) a += coeffs[r] * __ldg(bas + static_cast<long long>(r - n_pre) * D + d);
+    vec[d] = a;
+    s += a;
+  }
+  const float mean = block_sum_256(s, red) / D;
+  float m2 = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    const float dd = vec[d] - mean;
+    m2 += dd * dd;
+  }
+  const float rstd = rsqrtf(block_sum_256(m2, red) / D + 1e-5f);
+  const float inv_sqrt_d = rsqrtf(static_cast<float>(D));
+  const long long row = (static_cast<long long>(l) * K + k) * D;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float v = (vec[d] - mean) * rstd * inv_sqrt_d;
+    if (bias != nullptr) v += bias[row + d];
+    out[row + d] = v;
+  }
+}
+
+// one warp per prompt: position of the first occurrence of `token` (-1: none)  (ldm/util.py:2114-2124)
+__global__ void __launch_bounds__(32) first_token_pos_kernel(const long long* __restrict__ tokens, long long token,
+                                                             int* __restrict__ first_pos, int N) {
+  pdl_wait();
+  pdl_trigger();
+  const long long* row = tokens + static_cast<long long>(blockIdx.x) * N;
+  int best = 0x7fffffff;
+  for (int n = threadIdx.x; n < N; n += 32)
+    if (row[n] == token) best = min(best, n);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (threadIdx.x == 0) first_pos[blockIdx.x] = best == 0x7fffffff ? -1 : best;
+}
+
+// Block (n, l, b) writes row n of prompt copy b * L + l (instance-major / layer-minor, :1341-1352): the token
+// embedding, or vector n - first of layer l's static embedding for the K positions that start at the placeholder
+// (:1510-1552).  One float4 per thread and pass.
+__global__ void __launch_bounds__(256) splice_static_kernel(const float* __restrict__ embedded_text, const int* __restrict__ first_pos,
+                                                            const float* __restrict__ static_emb, float* __restrict__ out_f32,
+                                                            __nv_bfloat16* __restrict__ out_bf16, int N, int L, int K, int D) {
+  pdl_wait();
+  pdl_trigger();
+  const int n = blockIdx.x, l = blockIdx.y, b = blockIdx.z;
+  const int first = first_pos[b];
+  const bool subj = first >= 0 && n >= first && n < first + K;
+  const float* src = subj ? static_emb + (static_cast<long long>(l) * K + (n - first)) * D
+                          : embedded_text + (static_cast<long long>(b) * N + n) * D;
+  const long long dst = ((static_cast<long long>(b) * L + l) * N + n) * D;
+  for (int i = threadIdx.x * 4; i < D; i += blockDim.x * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(src + i);
+    if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + dst + i) = v;
+    if (out_bf16 != nullptr) {
+      uint2 pk;
+      pk.x = pack_bf16x2(v.x, v.y);
+      pk.y = pack_bf16x2(v.z, v.w);
+      *reinterpret_cast<uint2*>(out_bf16 + dst + i) = pk;
+    }
+  }
+}
+
 int pool_blocks_per_sample(int batch, int n_tokens, int channels) {
   // ONE wave of blocks over the GPU (the main kernel fits two blocks per SM up to 512 channels, one above: its
   // registers hold the running sums of all channels), at least 8 tokens (one per warp) per block.  A second wave
@@ -692,6 +777,61 @@ extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, cons
   AFB_CHECK_CUDA(launch_pdl(ada_head_kernel, dim3(num_vectors, batch), dim3(256), sh, stream, 1, infeat_fg, infeat_bg, time_emb,
                             time_ld, coeff_w, coeff_b, basis, bias, out, reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos,
                             ctx_sample_stride, basis_sample_stride, channels, td, num_vectors, r, out_dim));
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_static_layerwise_embedding(const float* basis_rand_weights, const float* basis_comm_weights,
+                                              const float* pre_vecs, int n_pre, const float* basis_vecs, const float* bias,
+                                              float* out, int num_layers, int num_vectors, int r, int out_dim,
+                                              afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(basis_rand_weights && basis_comm_weights && basis_vecs && out, "afb_static_layerwise_embedding: NULL argument");
+  AFB_REQUIRE(num_layers > 0 && num_layers <= 65535 && num_vectors > 0 && r > 0 && out_dim > 0,
+              "afb_static_layerwise_embedding: bad sizes");
+  AFB_REQUIRE(n_pre >= 0 && n_pre < r && (n_pre == 0) == (pre_vecs == nullptr),
+              "afb_static_layerwise_embedding: pre_vecs and n_pre go together, and n_pre < r");
+  const size_t sh = (static_cast<size_t>((r + 3) & ~3) + out_dim) * sizeof(float);
+  AFB_REQUIRE(sh <= 48 * 1024, "afb_static_layerwise_embedding: vector too long for one block (%zu bytes)", sh);
+  AFB_CHECK_CUDA(launch_pdl(static_layerwise_kernel, dim3(num_vectors, num_layers), dim3(256), sh, stream, 1, basis_rand_weights,
+                            basis_comm_weights, pre_vecs, n_pre, basis_vecs, bias, out, num_vectors, r, out_dim));
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_first_token_pos(const int64_t* tokens, int64_t token, int* first_pos, int batch, int n_tokens,
+                                   afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(tokens && first_pos, "afb_first_token_pos: NULL argument");
+  AFB_REQUIRE(batch > 0 && n_tokens > 0, "afb_first_token_pos: empty problem");
+  AFB_CHECK_CUDA(launch_pdl(first_token_pos_kernel, dim3(batch), dim3(32), 0, stream, 1,
+                            reinterpret_cast<const long long*>(tokens), static_cast<long long>(token), first_pos, n_tokens));
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_splice_static_embedding(const float* embedded_text, const int* first_pos, const float* static_emb,
+                                           float* out_f32, afb_bf16* out_bf16, int batch, int n_tokens, int num_layers,
+                                           int num_vectors, int dim, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(embedded_text && first_pos && static_emb, "afb_splice_static_embedding: NULL argument");
+  AFB_REQUIRE(out_f32 || out_bf16, "afb_splice_static_embedding: no output given");
+  AFB_REQUIRE(batch > 0 && batch <= 65535 && num_layers > 0 && num_layers <= 65535 && n_tokens > 0 && num_vectors > 0,
+              "afb_splice_static_embedding: bad sizes");
+  AFB_REQUIRE(dim > 0 && dim % 4 == 0, "afb_splice_static_embedding: dim must be a multiple of 4");
+  const uintptr_t all = reinterpret_cast<uintptr_t>(embedded_text) | reinterpret_cast<uintptr_t>(static_emb) |
+                        reinterpret_cast<uintptr_t>(out_f32) | reinterpret_cast<uintptr_t>(out_bf16);
+  AFB_REQUIRE((all & 15) == 0, "afb_splice_static_embedding: buffers must be 16-byte aligned");
+  const int threads = dim / 4 < 256 ? ((dim / 4 + 31) / 32) * 32 : 256;
+  AFB_CHECK_CUDA(launch_pdl(splice_static_kernel, dim3(n_tokens, num_layers, batch), dim3(threads), 0, stream, 1, embedded_text,
+                            first_pos, static_emb, out_f32, reinterpret_cast<__nv_bfloat16*>(out_bf16), n_tokens, num_layers,
+                            num_vectors, dim));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -94,5 +94,5 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
 }  // namespace afb
 
 extern "C" const char* afb_last_error(void) { return afb::g_error; }
-extern "C" int afb_abi_version(void) { return 9; }
+extern "C" int afb_abi_version(void) { return 10; }
 extern "C" int64_t afb_launch_count(void) { return afb::g_launches.load(std::memory_order_relaxed); }

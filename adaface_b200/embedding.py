@@ -240,3 +240,85 @@ class AdaEmbedding(nn.Module, _PackedWeights):
             out = ops.ada_head_splice(infeat_fg, infeat_bg, time_emb, self.TDs[ca], p[f"cw{ca}"], p[f"cb{ca}"],
                                       basis, bias, splice_into, splice_positions)
         return out, pooled
+
+
+class StaticLayerwiseEmbedding(nn.Module):
+    """embedding_manager.py:360-537, the learned ("slow", not zero-shot) form: 16 x K static subject
+    vectors as a low-rank combination of K sets of r basis vectors.  Constructor arguments, parameter names
+    (`pre_vecs`, `basis_rand_weights`, `basis_vecs`, `basis_comm_weights`, `bias`) and their initialisation follow the
+    reference, so its state_dict loads; `forward()` is one kernel (`afb_static_layerwise_embedding`).  The zero-shot form
+    of the reference only reshapes the vectors a subject-basis generator hands it (:504-511) and is a view here."""
+
+    def __init__(self, num_layers: int = 16, num_vectors_per_subj_token: int = 1, out_emb_dim: int = 768, r: int = 6,
+                 init_noise_stds=(0.1, 0.04), init_string=None, init_vecs: Optional[Tensor] = None,
+                 init_vec_weights: Optional[Tensor] = None, has_bias: bool = True, token_string: str = "",
+                 do_zero_shot: bool = False, device_type: str = "cuda"):
+        super().__init__()
+        if r > min(num_layers, out_emb_dim):                                                       # :392-395
+            raise ValueError(f"StaticLayerwiseEmbedding LoRA rank {r} must be less or equal than "
+                             f"{min(num_layers, out_emb_dim)}")
+        self.do_zero_shot, self.token_string, self.num_layers = do_zero_shot, token_string, num_layers
+        self.K, self.out_emb_dim, self.r = num_vectors_per_subj_token, out_emb_dim, r
+        self.has_bias, self.device_type = has_bias, device_type
+        K = self.K
+        if init_vecs is not None:
+            if init_vecs.shape[1] != out_emb_dim or init_vecs.shape[0] > num_layers:               # :398-401
+                raise ValueError(f"StaticLayerwiseEmbedding init vectors shape {tuple(init_vecs.shape)} must be "
+                                 f"(<={num_layers}, {out_emb_dim})")
+            N = self.N = init_vecs.shape[0]
+            self.pre_vecs = None if do_zero_shot else nn.Parameter(init_vecs.unsqueeze(0).repeat(K, 1, 1).clone())
+        else:
+            N = self.N = 0
+            self.pre_vecs = None
+        self.basis_rand_weights = nn.Parameter(torch.randn(num_layers, K, r))                      # :417
+        if not do_zero_shot:
+            bv = F.normalize(torch.randn(K, r - N, out_emb_dim), dim=-1) / 4.0                      # :424-426
+            bv[-1] = 0                                                                             # :428
+            self.basis_vecs = nn.Parameter(bv)
+        else:
+            self.basis_vecs = None
+        self.basis_comm_weights = nn.Parameter(torch.ones(1, K, r) / r)                            # :438
+        if init_vecs is not None:                                                                  # :442-477
+            with torch.no_grad():
+                self.basis_comm_weights.fill_(1.0 / N)
+                self.basis_comm_weights[:, :, N:] *= 0.4
+                if init_vec_weights is not None:
+                    assert len(init_vec_weights) == len(init_vecs)
+                    self.basis_comm_weights[:, :, :N] = init_vec_weights.reshape(1, 1, -1)
+                self.basis_rand_weights[:, :, :N] *= init_noise_stds[1]
+                self.basis_rand_weights[:, :, N:] *= init_noise_stds[0]
+        if has_bias and not do_zero_shot:
+            self.bias = nn.Parameter(torch.zeros(num_layers, K, out_emb_dim))                      # :481-483
+        else:
+            self.bias = 0
+
+    def forward(self, static_zs_embs: Optional[Tensor] = None) -> Tensor:
+        """-> [16, K, 768] fp32 (zero-shot: `static_zs_embs` [B, 16, K, 768] -> [(B 16), K, 768], :504-511)."""
+        if self.do_zero_shot:
+            b, l, k, d = static_zs_embs.shape
+            out = static_zs_embs.reshape(b * l, k, d)
+            self.bias, self.has_bias = out, True
+            return out
+        bias = self.bias if isinstance(self.bias, torch.Tensor) else None
+        return ops.static_layerwise_embedding(self.basis_rand_weights.detach(), self.basis_comm_weights.detach(),
+                                              None if self.pre_vecs is None else self.pre_vecs.detach(),
+                                              self.basis_vecs.detach(), None if bias is None else bias.detach())
+
+
+def splice_static_embedding(embedded_text: Tensor, tokenized_text: Tensor, placeholder_token: int,
+                            subj_static_embedding: Tensor, num_unet_ca_layers: int = 16,
+                            out_dtype: torch.dtype = torch.float32):
+    """The inference branch of EmbeddingManager.get_static_embedding for one placeholder string
+    (embedding_manager.py:1341-1352, 1360-1366, 1510-1552): the prompt's token embeddings `[B, N, 768]` repeated over the
+    16 cross-attention layers (instance-major / layer-minor) with the K static vectors of each layer written at the K
+    positions that start at the FIRST occurrence of the placeholder in each prompt; prompts without it pass through.
+    Returns (embedded_text [B*16, N, 768], tokenized_text [B*16, N]) like the reference.  Two launches, no host sync."""
+    if subj_static_embedding.shape[0] != num_unet_ca_layers:
+        raise ValueError("splice_static_embedding: one static embedding per cross-attention layer expected")
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("splice_static_embedding: fp32 or bf16 output")
+    first = ops.first_token_pos(tokenized_text, int(placeholder_token))
+    out = ops.splice_static_embedding(embedded_text, first, subj_static_embedding, out_dtype == torch.bfloat16)
+    B, N = tokenized_text.shape
+    tok = tokenized_text.unsqueeze(1).expand(B, num_unet_ca_layers, N).reshape(B * num_unet_ca_layers, N)
+    return out, tok

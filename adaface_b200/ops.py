@@ -640,6 +640,83 @@ def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out
     return infeat_fg.new_empty((infeat_fg.shape[0], basis.shape[-3], basis.shape[-1]), dtype=torch.float32)
 
 
+# ------------------------------------------------------------------------------------------- static embedding (N2)
+def _f32c(t: Optional[Tensor], what: str) -> Optional[Tensor]:
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        raise ValueError(f"{what}: fp32 tensor expected")
+    return t.contiguous()
+
+
+@torch.library.custom_op("adaface_b200::static_layerwise_embedding", mutates_args=())
+def static_layerwise_embedding(basis_rand_weights: Tensor, basis_comm_weights: Tensor, pre_vecs: Optional[Tensor],
+                               basis_vecs: Tensor, bias: Optional[Tensor]) -> Tensor:
+    """StaticLayerwiseEmbedding.forward (embedding_manager.py:497-537): rand [L,K,r], comm [1,K,r], pre_vecs
+    [K,N,D] or None, basis_vecs [K,r-N,D], bias [L,K,D] or None -> fp32 [L,K,D]."""
+    _need_cuda(basis_rand_weights, basis_comm_weights, pre_vecs, basis_vecs, bias)
+    rw, cw = _f32c(basis_rand_weights, "basis_rand_weights"), _f32c(basis_comm_weights, "basis_comm_weights")
+    pv, bv, bs = _f32c(pre_vecs, "pre_vecs"), _f32c(basis_vecs, "basis_vecs"), _f32c(bias, "bias")
+    L, K, r = rw.shape
+    n_pre = 0 if pv is None else pv.shape[1]
+    D = bv.shape[-1]
+    if cw.numel() != K * r or bv.shape[0] != K or bv.shape[1] != r - n_pre or (pv is not None and pv.shape != (K, n_pre, D)) \
+            or (bs is not None and bs.shape != (L, K, D)):
+        raise ValueError("static_layerwise_embedding: inconsistent parameter shapes")
+    out = torch.empty((L, K, D), device=rw.device, dtype=torch.float32)
+    _run("static_layerwise_embedding", _lib.load().afb_static_layerwise_embedding, _ptr(rw), _ptr(cw), _ptr(pv), n_pre,
+         _ptr(bv), _ptr(bs), _ptr(out), L, K, r, D, _stream(), nbytes=4.0 * (L * K * D * 2 + K * r * D))
+    return out
+
+
+@static_layerwise_embedding.register_fake
+def _(basis_rand_weights, basis_comm_weights, pre_vecs, basis_vecs, bias):
+    L, K, _ = basis_rand_weights.shape
+    return basis_vecs.new_empty((L, K, basis_vecs.shape[-1]), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::first_token_pos", mutates_args=())
+def first_token_pos(tokens: Tensor, token: int) -> Tensor:
+    """tokens int64 [B,N] -> int32 [B]: first position of `token` in each prompt, -1 if absent (ldm/util.py:2114)."""
+    _need_cuda(tokens)
+    if tokens.dtype != torch.int64 or tokens.dim() != 2:
+        raise ValueError("first_token_pos: int64 [B, N] token ids expected")
+    tokens = tokens.contiguous()
+    out = torch.empty((tokens.shape[0],), device=tokens.device, dtype=torch.int32)
+    _run("first_token_pos", _lib.load().afb_first_token_pos, _ptr(tokens), int(token), _ptr(out), tokens.shape[0],
+         tokens.shape[1], _stream(), nbytes=8.0 * tokens.numel())
+    return out
+
+
+@first_token_pos.register_fake
+def _(tokens, token):
+    return tokens.new_empty((tokens.shape[0],), dtype=torch.int32)
+
+
+@torch.library.custom_op("adaface_b200::splice_static_embedding", mutates_args=())
+def splice_static_embedding(embedded_text: Tensor, first_pos: Tensor, static_emb: Tensor, to_bf16: bool) -> Tensor:
+    """The layer-repeated prompt with the subject rows spliced in (embedding_manager.py:1341-1352, 1510-1552):
+    embedded_text fp32 [B,N,D], first_pos int32 [B], static_emb fp32 [L,K,D] -> [B*L, N, D] fp32 (or bf16)."""
+    _need_cuda(embedded_text, first_pos, static_emb)
+    et, se = _f32c(embedded_text, "embedded_text"), _f32c(static_emb, "static_emb")
+    if first_pos.dtype != torch.int32 or et.dim() != 3 or first_pos.numel() != et.shape[0] or se.dim() != 3 \
+            or se.shape[-1] != et.shape[-1]:
+        raise ValueError("splice_static_embedding: embedded_text [B,N,D], first_pos int32 [B], static_emb [L,K,D] expected")
+    B, N, D = et.shape
+    L, K, _ = se.shape
+    out = torch.empty((B * L, N, D), device=et.device, dtype=torch.bfloat16 if to_bf16 else torch.float32)
+    _run("splice_static_embedding", _lib.load().afb_splice_static_embedding, _ptr(et), _ptr(first_pos.contiguous()), _ptr(se),
+         None if to_bf16 else _ptr(out), _ptr(out) if to_bf16 else None, B, N, L, K, D, _stream(),
+         nbytes=float(B * L * N * D) * (4 + (2 if to_bf16 else 4)))
+    return out
+
+
+@splice_static_embedding.register_fake
+def _(embedded_text, first_pos, static_emb, to_bf16):
+    B, N, D = embedded_text.shape
+    return embedded_text.new_empty((B * static_emb.shape[0], N, D), dtype=torch.bfloat16 if to_bf16 else torch.float32)
+
+
 # ------------------------------------------------------------------------------------------- elementwise
 @torch.library.custom_op("adaface_b200::add_bias_residual", mutates_args=())
 def add_bias_residual(a: Tensor, b: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:

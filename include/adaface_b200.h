@@ -219,6 +219,25 @@ int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* ti
                  afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int64_t basis_sample_stride, int batch, int channels, int td,
                  int num_vectors, int r, int out_dim, afb_stream_t stream);
 
+/* ---- N2: StaticLayerwiseEmbedding and the splice of its rows into the layerwise prompt.
+ * afb_static_layerwise_embedding replaces StaticLayerwiseEmbedding.forward (not zero-shot),
+ *   embedding_manager.py:497-537: out[l, k] = LN(sum_r (rand[l,k,r] + comm[0,k,r]) * basis[k,r]) / sqrt(D) + bias[l,k].
+ *   basis_rand_weights fp32 [L, K, r]; basis_comm_weights [1, K, r]; pre_vecs [K, n_pre, D] or NULL (n_pre = 0);
+ *   basis_vecs [K, r - n_pre, D]; bias [L, K, D] or NULL; out fp32 [L, K, D].
+ * afb_first_token_pos: tokens int64 [B, N] -> first_pos int32 [B], the first position holding `token`, -1 if none
+ *   (extract_first_index_in_each_instance, ldm/util.py:2114-2124).
+ * afb_splice_static_embedding replaces the inference branch of EmbeddingManager.get_static_embedding for one
+ *   placeholder, embedding_manager.py:1341-1352 and 1510-1552: out[b * L + l, n] = static_emb[l, n - first_pos[b]] for
+ *   first_pos[b] <= n < first_pos[b] + K, else embedded_text[b, n]; positions past N are dropped.  embedded_text fp32
+ *   [B, N, D]; static_emb fp32 [L, K, D]; out_f32 fp32 and/or out_bf16 bf16 [B * L, N, D] (either may be NULL). */
+int afb_static_layerwise_embedding(const float* basis_rand_weights, const float* basis_comm_weights, const float* pre_vecs,
+                                   int n_pre, const float* basis_vecs, const float* bias, float* out, int num_layers,
+                                   int num_vectors, int r, int out_dim, afb_stream_t stream);
+int afb_first_token_pos(const int64_t* tokens, int64_t token, int* first_pos, int batch, int n_tokens, afb_stream_t stream);
+int afb_splice_static_embedding(const float* embedded_text, const int* first_pos, const float* static_emb, float* out_f32,
+                                afb_bf16* out_bf16, int batch, int n_tokens, int num_layers, int num_vectors, int dim,
+                                afb_stream_t stream);
+
 /* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */
 int afb_cast_f32_to_bf16(const float* src, afb_bf16* dst, int64_t n, afb_stream_t stream);
 int afb_cast_bf16_to_f32(const afb_bf16* src, float* dst, int64_t n, afb_stream_t stream);

@@ -5,7 +5,7 @@ import math
 import pytest
 import torch
 
-from conftest import rel_l2
+from conftest import load_golden, rel_l2
 from oracle import params as P
 from oracle import port
 
@@ -486,3 +486,55 @@ def test_unsupported_arguments_raise(ops, cuda_device):
         ops.attention(q, q, q, 8, 1.0, None)                     # head_dim 24 is not an SD-1.5 head size
     with pytest.raises(AdafaceB200Error):
         ops.linear(torch.zeros((8, 64), dtype=torch.bfloat16), torch.zeros((32, 64), dtype=torch.bfloat16), None, None, False)
+
+
+# ---------------------------------------------------------------------------------------------- N2 static embedding
+def test_static_layerwise_embedding_vs_reference_golden(ops, cuda_device):
+    """afb_static_layerwise_embedding against the reference StaticLayerwiseEmbedding (golden) and, without pre_vecs /
+    bias and at other sizes, against the port."""
+    from adaface_b200.embedding import StaticLayerwiseEmbedding
+    g = load_golden("static_emb")
+    seed, K, r, L, _ = (int(v) for v in g["meta"])
+    mod = StaticLayerwiseEmbedding(L, K, 768, r, init_vecs=torch.zeros(2, 768))
+    mod.load_state_dict(P.init_static_embedding(seed, K, r, 2), strict=True)
+    out = mod.to(cuda_device)()
+    assert out.shape == (L, K, 768) and out.dtype == torch.float32
+    assert rel_l2(out, torch.from_numpy(g["static"])) < 1e-5
+    for (L2, K2, r2, D2, n_pre, has_bias) in [(16, 1, 6, 768, 0, False), (4, 3, 5, 1024, 1, True), (25, 16, 12, 768, 3, True)]:
+        p = {"basis_rand_weights": _r("se.rw", (L2, K2, r2)), "basis_comm_weights": _r("se.cw", (1, K2, r2)),
+             "basis_vecs": _r("se.bv", (K2, r2 - n_pre, D2))}
+        if n_pre:
+            p["pre_vecs"] = _r("se.pv", (K2, n_pre, D2))
+        if has_bias:
+            p["bias"] = _r("se.b", (L2, K2, D2), 0.02)
+        ref = port.static_layerwise_embedding(p, D2)
+        d = cuda_device
+        got = ops.static_layerwise_embedding(p["basis_rand_weights"].to(d), p["basis_comm_weights"].to(d),
+                                             p["pre_vecs"].to(d) if n_pre else None, p["basis_vecs"].to(d),
+                                             p["bias"].to(d) if has_bias else None)
+        assert rel_l2(got, ref) < 1e-5, (L2, K2, r2)
+
+
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_splice_static_embedding_vs_reference_golden(ops, cuda_device, out_dtype):
+    """first_token_pos + splice_static_embedding: bit-exact copy semantics against the reference's statements (golden)
+    and the port, including a prompt without the placeholder, a repeated placeholder and one at the end of the prompt
+    whose trailing vectors fall off the 77 positions."""
+    from adaface_b200.embedding import splice_static_embedding
+    from oracle.gen_golden import static_inputs
+    g = load_golden("static_emb")
+    seed, K, r, L, token = (int(v) for v in g["meta"])
+    static = torch.from_numpy(g["static"])
+    emb, tok = static_inputs("static_emb", seed, K=K)
+    d = cuda_device
+    out, tok_rep = splice_static_embedding(emb.to(d), tok.to(d), token, static.to(d), L, out_dtype)
+    assert out.dtype == out_dtype and out.shape == (emb.shape[0] * L, 77, 768) and tok_rep.shape == (emb.shape[0] * L, 77)
+    want = torch.from_numpy(g["spliced"])
+    assert torch.equal(out[:, :, ::16].cpu(), want.to(out_dtype))
+    assert torch.equal(out.cpu(), port.splice_static_embedding(emb, tok, token, static, L).to(out_dtype))
+    assert torch.equal(ops.first_token_pos(tok.to(d), token).cpu(), torch.tensor([5, -1, 20], dtype=torch.int32))
+    tok2 = tok.clone()
+    tok2[1, 77 - 3] = token                                  # only 3 of the K vectors fit
+    out2, _ = splice_static_embedding(emb.to(d), tok2.to(d), token, static.to(d), L, out_dtype)
+    assert torch.equal(out2[L:2 * L, 74:77].cpu(), static[:, :3].to(out_dtype))
+    assert torch.equal(out2[L:2 * L, :74].cpu(), emb[1, :74].expand(L, -1, -1).to(out_dtype))

@@ -199,3 +199,21 @@ def test_resblock_and_upsample_match_reference():
         assert rel_l2(y[:, ::RESBLOCK_CH_STRIDE], g[tag]) < TOL, tag
     y = port.upsample(P.randn("rb.up.x", (2, 640, 16, 16), seed), P.init_upsample(640, seed), "")
     assert rel_l2(y[:, ::RESBLOCK_CH_STRIDE], g["up"]) < TOL
+
+
+def test_static_layerwise_embedding_and_splice_match_reference():
+    """the port's StaticLayerwiseEmbedding.forward against the reference class, and its splice against
+    the reference's own get_static_embedding statements (first occurrence per prompt, K rows per layer copy)."""
+    from oracle.gen_golden import STATIC_TOKEN, static_inputs
+    g = load_golden("static_emb")
+    seed, K, r, L, token = (int(v) for v in g["meta"])
+    assert token == STATIC_TOKEN
+    static = port.static_layerwise_embedding(P.init_static_embedding(seed, K, r, 2))
+    assert rel_l2(static, g["static"]) < TOL
+    emb, tok = static_inputs("static_emb", seed, K=K)
+    spliced = port.splice_static_embedding(emb, tok, token, torch.from_numpy(g["static"]), L)
+    assert spliced.shape == (emb.shape[0] * L, emb.shape[1], emb.shape[2])
+    assert torch.equal(spliced[:, :, ::16], torch.from_numpy(g["spliced"]))
+    # prompt 1 holds no placeholder: untouched; prompt 0's second occurrence (position 40) is not a subject row
+    assert torch.equal(spliced[L:2 * L], emb[1].expand(L, -1, -1))
+    assert torch.equal(spliced[0, 40], emb[0, 40])
