@@ -142,14 +142,15 @@ def load_embedding_checkpoint(ckpt_paths: Union[str, Sequence[str]], do_zero_sho
                     continue                                               # :1996-1999: duplicate background, ignored
                 raise ValueError(f"Duplicate key {km}->{km2} in {parts[0]}")
             if scores is not None:
-                out.emb_global_scale_scores[km2] = float(scores[idx])
+                out.emb_global_scale_scores[km2] = float(scores.detach()[idx])
             if km in ckpt_bg:
                 if km2 not in out.background_strings:
                     out.background_strings.append(km2)
             elif km2 not in out.subject_strings:
                 out.subject_strings.append(km2)
             # the token id is the tokenizer's (:2018-2020); the stored one is kept for tokenizers extended the same way
-            out.string_to_token[km2] = ckpt["string_to_token"].get(km)
+            tok = ckpt["string_to_token"].get(km)
+            out.string_to_token[km2] = int(tok) if isinstance(tok, torch.Tensor) else tok
             out.string_to_static_embedder[km2] = _to_static_embedder(ckpt["string_to_static_embedder"][km], do_zero_shot)
             if km in ckpt.get("token2num_vectors", {}):
                 out.token2num_vectors[km2] = ckpt["token2num_vectors"][km]

@@ -337,6 +337,46 @@ def case_static(ref, name="static_emb", seed=22, K=9, r=12, L=16):
     _save(name, meta=np.array([seed, K, r, L, STATIC_TOKEN]), static=static, spliced=embedded_text[:, :, ::16])
 
 
+CKPT_FIXTURE = "embeddings_gs-toy.pt"
+
+
+def case_embeddings_ckpt(ref, name="embeddings_ckpt", seed=23, L=16):
+    """SURVEY 8f N3.  A checkpoint in the reference's own on-disk format: the dict of EmbeddingManager.save
+    (embedding_manager.py:1820-1834) with LIVE reference StaticLayerwiseEmbedding modules (a subject "z", K=4, r=6, two
+    init vectors; a background "y", K=2, r=4, none), written by torch.save, i.e. a pickle naming
+    ldm.modules.embedding_manager.StaticLayerwiseEmbedding.  EmbeddingManager itself cannot be built here (it wants a
+    CLIP embedder), so the dict is assembled by hand with the reference's container types (:986-989, :1215-1216).
+    The .npz holds what the reference modules compute, for the loader's parity test."""
+    from collections import OrderedDict
+    em = ref.embedding_manager
+    specs = {"z": (4, 6, 2), "y": (2, 4, 0)}
+    embedders = torch.nn.ParameterDict()
+    outs = {}
+    for i, (km, (K, r, n_init)) in enumerate(specs.items()):
+        mod = em.StaticLayerwiseEmbedding(num_layers=L, num_vectors_per_subj_token=K, out_emb_dim=768, r=r,
+                                          init_vecs=torch.zeros(n_init, 768) if n_init else None, has_bias=True,
+                                          token_string=km, device_type="cpu")
+        sd = {k: P.draw(f"ckpt.{km}.{k}", tuple(v.shape), seed + i, "normal", 0.2) for k, v in mod.state_dict().items()}
+        mod.load_state_dict(sd, strict=True)
+        embedders[km] = mod
+        with torch.no_grad():
+            outs[f"static_{km}"] = mod.eval()()
+    ckpt = {"string_to_token": OrderedDict(z=torch.tensor(49408), y=torch.tensor(49409)),
+            "string_to_static_embedder": embedders,
+            "string_to_subj_basis_generator_dict": torch.nn.ModuleDict(),
+            "token2num_vectors": {"z": 4, "y": 2},
+            "emb_global_scale_scores": torch.nn.Parameter(torch.tensor([0.3, -0.2])),
+            "use_conv_attn_kernel_size": 3,
+            "placeholder_strings": ["z", "y"], "subject_strings": ["z"], "background_strings": ["y"],
+            "ca_q_bns": torch.nn.ModuleDict({"1": torch.nn.BatchNorm2d(320, affine=False)}),
+            "ca_outfeat_lns": torch.nn.ModuleDict({"1": torch.nn.LayerNorm(320, elementwise_affine=False)}),
+            "do_zero_shot": False}
+    path = os.path.join(GOLDEN_DIR, CKPT_FIXTURE)
+    torch.save(ckpt, path)
+    print(f"wrote {path} ({os.path.getsize(path) // 1024} KiB)")
+    _save(name, meta=np.array([seed, L]), **outs)
+
+
 def main(argv):
     ref = RH.load()
     torch.set_num_threads(os.cpu_count() or 1)
@@ -369,6 +409,8 @@ def main(argv):
             case_resblock(ref)
         elif name == "static_emb":
             case_static(ref)
+        elif name == "embeddings_ckpt":
+            case_embeddings_ckpt(ref)
         elif name == "ddim10_small":
             case_ddim50(ref, "ddim10_small", seed=19, hw=16, steps=10)
         else:

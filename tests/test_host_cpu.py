@@ -221,3 +221,50 @@ def test_sample_sharded_world_size_2_gloo(tmp_path, n):
     mp.spawn(_worker, args=(2, port_no, n, str(tmp_path)), nprocs=2, join=True)
     counts = [torch.load(os.path.join(tmp_path, f"r{r}.pt"))["n_local"] for r in range(2)]
     assert sum(counts) == n and abs(counts[0] - counts[1]) <= 1
+
+
+def test_reference_embedding_checkpoint_loads_without_ldm():
+    """a checkpoint written by torch.save with LIVE reference modules (pickled class path
+    ldm.modules.embedding_manager.StaticLayerwiseEmbedding; fixture made by oracle/gen_golden.py from the imported
+    reference) loads where no `ldm` package exists, into this package's StaticLayerwiseEmbedding, with the bookkeeping of
+    EmbeddingManager.load (renaming, subject/background strings, token2num_vectors, global scales)."""
+    import subprocess
+    import sys
+    fixture = os.path.join(os.path.dirname(__file__), "golden", "embeddings_gs-toy.pt")
+    if not os.path.exists(fixture):
+        pytest.skip("checkpoint fixture not generated")
+    code = f"""
+import sys, torch
+from adaface_b200.checkpoint import load_embedding_checkpoint, OpaqueReferenceModule
+from adaface_b200.embedding import StaticLayerwiseEmbedding
+ck = load_embedding_checkpoint({fixture!r} + ":z-zz")
+assert not any(m == "ldm" or m.startswith("ldm.") for m in sys.modules)
+assert ck.subject_strings == ["zz"] and ck.background_strings == ["y"] and ck.placeholder_strings == ["zz", "y"]
+assert ck.token2num_vectors == {{"zz": 4, "y": 2}} and ck.string_to_token == {{"zz": 49408, "y": 49409}}
+assert ck.use_conv_attn_kernel_size == 3 and ck.do_zero_shot is False
+assert abs(ck.emb_global_scale_scores["zz"] - 0.3) < 1e-6 and abs(ck.emb_global_scales()["y"] - (torch.sigmoid(torch.tensor(-0.2)).item() + 0.5)) < 1e-6
+z, y = ck.string_to_static_embedder["zz"], ck.string_to_static_embedder["y"]
+assert type(z) is StaticLayerwiseEmbedding and (z.K, z.r, z.N, z.num_layers) == (4, 6, 2, 16) and (y.K, y.r, y.N) == (2, 4, 0)
+assert sorted(z.state_dict()) == ["basis_comm_weights", "basis_rand_weights", "basis_vecs", "bias", "pre_vecs"]
+assert sorted(y.state_dict()) == ["basis_comm_weights", "basis_rand_weights", "basis_vecs", "bias"]
+assert set(ck.opaque) == {{"string_to_subj_basis_generator_dict", "ca_q_bns", "ca_outfeat_lns"}}
+try:
+    load_embedding_checkpoint([{fixture!r}, {fixture!r}])
+except ValueError as e:
+    assert "Duplicate key" in str(e)
+else:
+    raise AssertionError("duplicate subject placeholder must raise like the reference")
+print("ok")
+"""
+    env = dict(os.environ, PYTHONPATH=os.path.dirname(os.path.dirname(__file__)))
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+    assert res.returncode == 0 and "ok" in res.stdout, res.stderr[-2000:]
+    # the arithmetic of the loaded parameters, checked on the CPU with the oracle port against the reference's outputs
+    from adaface_b200.checkpoint import load_embedding_checkpoint
+    from conftest import load_golden, rel_l2
+    from oracle import port
+    g = load_golden("embeddings_ckpt")
+    ck = load_embedding_checkpoint(fixture)
+    for km in ("z", "y"):
+        sd = {k: v.detach() for k, v in ck.string_to_static_embedder[km].state_dict().items()}
+        assert rel_l2(port.static_layerwise_embedding(sd), g[f"static_{km}"]) < 1e-5

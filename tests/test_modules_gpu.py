@@ -554,3 +554,38 @@ def test_resblock_and_upsample_vs_reference_golden(afb, cuda_device):
         y = up(x)
     assert y.shape == (2, 640, 32, 32)
     assert rel_l2(y.float()[:, ::RESBLOCK_CH_STRIDE], g["up"]) < 1e-2
+
+
+def test_reference_checkpoint_to_layerwise_prompt(cuda_device):
+    """SURVEY.md 8f N3 + N2 end to end: the reference-format checkpoint fixture (live reference modules, pickled) ->
+    this package's StaticLayerwiseEmbedding on the GPU == what the reference modules computed (golden), then spliced into
+    a batch of prompts == the oracle's splice, bit for bit."""
+    import os
+    from adaface_b200.checkpoint import load_embedding_checkpoint
+    from adaface_b200.embedding import splice_static_embedding
+    from conftest import load_golden
+    fixture = os.path.join(os.path.dirname(__file__), "golden", "embeddings_gs-toy.pt")
+    if not os.path.exists(fixture):
+        pytest.skip("checkpoint fixture not generated")
+    g = load_golden("embeddings_ckpt")
+    ck = load_embedding_checkpoint(fixture)
+    static = ck.static_embeddings(cuda_device)
+    for km in ("z", "y"):
+        assert static[km].shape == (16, ck.token2num_vectors[km], 768)
+        assert rel_l2(static[km], torch.from_numpy(g[f"static_{km}"])) < 1e-5
+    emb = P.randn("ckpt.prompt", (4, 77, 768), 5, 0.05)
+    tok = torch.full((4, 77), 320, dtype=torch.long)
+    tok[0, 3] = ck.string_to_token["z"]
+    tok[2, 70] = ck.string_to_token["z"]
+    tok[2, 75] = ck.string_to_token["z"]
+    tok[3, 76] = ck.string_to_token["z"]                  # last position: one of the four vectors fits
+    out, tok16 = splice_static_embedding(emb.to(cuda_device), tok.to(cuda_device), ck.string_to_token["z"], static["z"], 16,
+                                         torch.bfloat16)
+    # (the oracle's splice writes all K rows and would run off the prompt for sample 3: restated per vector here)
+    want = emb.unsqueeze(1).repeat(1, 16, 1, 1).reshape(64, 77, 768).clone()
+    for b, first in ((0, 3), (2, 70), (3, 76)):
+        for k in range(4):
+            if first + k < 77:
+                want[b * 16:(b + 1) * 16, first + k] = static["z"].cpu()[:, k]
+    assert torch.equal(out.cpu(), want.to(torch.bfloat16))
+    assert tok16.shape == (64, 77) and torch.equal(tok16[16:32].cpu(), tok[1].expand(16, -1))
