@@ -77,6 +77,10 @@ struct AttnDev {
 #ifndef AFB_ATTN_ONES
 #define AFB_ATTN_ONES 1
 #endif
+// AFB_ATTN_SDOUBLE: 0 = one S buffer per query tile everywhere, 1 = two at d = 80 (default), 2 = also at d = 40.
+#ifndef AFB_ATTN_SDOUBLE
+#define AFB_ATTN_SDOUBLE 1
+#endif
 
 // kSmall: the variant for a short key sequence (the 77-token context, the 8x8 image's self-attention): such a CTA is
 // one serial chain (set-up, loads, two score tiles, epilogue) with nothing to pipeline, so instead of four query tiles
@@ -84,11 +88,22 @@ struct AttnDev {
 // share the SM and overlap their chains.
 template <int D, bool kSmall = false>
 struct AttnCfg {
-  static constexpr int kQTiles = kSmall ? 1 : ((D <= 40) ? 4 : 2);   // query tiles (= softmax warps per sub-partition)
+  static constexpr bool kPTmem = AFB_ATTN_PTMEM != 0;
+  // kSDouble: two S buffers per query tile, so S_{j+1} = Q K_{j+1}^T is computed while the softmax warps still work on
+  // S_j: the MMA round trip (publish P_j -> MMA warp reacts -> tensor pipe -> commit -> softmax warp wakes, ~800 cycles
+  // plus queueing behind the other tiles' MMAs) leaves the critical path.  P_j overwrites the first half of ITS S
+  // buffer; S_{j+2} is issued into that buffer behind O += P_j V_j.  d = 80 fits as it is (2 x (128 + 80) = 416 TMEM
+  // columns): 82.2 -> 74.5 us at 1024 x 1024.  d = 40 would pay with one query tile (3 instead of 4: 3 x (128 + 40) =
+  // 504 columns, no room for the ones column) and measured SLOWER, 563 -> 604 us at 4096 x 4096: per query tile the same
+  // ~560 cycles per 64 keys with or without the round trip (three warps per sub-partition at ~60 % MUFU and ~63 % issue
+  // occupancy, i.e. bound by the exponentials' instruction stream, not by the MMA latency), plus an 8 % tail from
+  // 11 CTAs of 384 rows per head (1408 CTAs = 9.5 waves).  AFB_ATTN_SDOUBLE=2 builds it for d = 40 as well.
+  static constexpr bool kSDouble = AFB_ATTN_SDOUBLE != 0 && kPTmem && !kSmall && D <= 80 && (D > 40 || AFB_ATTN_SDOUBLE >= 2);
+  static constexpr int kQTiles = kSmall ? 1 : ((D <= 40) ? (kSDouble ? 3 : 4) : 2);   // query tiles per CTA
   static constexpr int kThreads = 64 + kQTiles * 128;
   static constexpr int kAtoms = (D + 63) / 64;                 // 64-column (128-byte) swizzle atoms per row
   static constexpr int kDPadK = (D + 15) / 16 * 16;            // K extent of S = Q K^T (UMMA K step 16)
-  static constexpr bool kOnes = AFB_ATTN_ONES != 0 && D <= 40;   // d = 80 is tensor-bound: the wider P V costs more there
+  static constexpr bool kOnes = AFB_ATTN_ONES != 0 && D <= 40 && !kSDouble;   // d = 80 is tensor-bound: the wider P V costs more there
   static_assert(D % 8 == 0, "head dim");
   static constexpr int kDPadN = kOnes ? D + 8 : D;             // N extent of O += P V (UMMA N step 8); column D = row sum
   static constexpr int kQTileBytes = kAtoms * kBlockQ * 128;   // one query tile: atom a at a * 16 KB
@@ -99,15 +114,15 @@ struct AttnCfg {
 #define AFB_ATTN_POLY_EVERY 3
 #endif
   static constexpr int kPolyEvery = (D <= 40) ? AFB_ATTN_POLY_EVERY : 0;          // every kPolyEvery-th pair of exponentials on the FMA pipe
-  static constexpr bool kPTmem = AFB_ATTN_PTMEM != 0;
   static constexpr int kSmemBytes =
       kQTiles * (kQTileBytes + ((kSmall && kPTmem) ? 0 : kPBytes)) + kStages * 2 * kKVTileBytes;
-  static constexpr int kTmemNeed = kQTiles * (kBlockKV + kDPadN);
+  static constexpr int kSStride = kSDouble ? 2 * kBlockKV : kBlockKV;     // TMEM columns of one tile's S buffer(s)
+  static constexpr int kTmemNeed = kQTiles * (kSStride + kDPadN);
   // the full-size CTA owns all of TMEM (one per SM); a small one takes the power of two that holds its S and O
   static constexpr int kTmemCols = !kSmall ? 512 : (kTmemNeed <= 128 ? 128 : (kTmemNeed <= 256 ? 256 : 512));
   static constexpr int kMinBlocks = !kSmall ? 1 : (D <= 40 ? 4 : (D <= 80 ? 2 : 1));
-  static constexpr int kTmemS = 0;                               // S_t: 64 columns each
-  static constexpr int kTmemO = kQTiles * kBlockKV;              // O_t: kDPadN columns each
+  static constexpr int kTmemS = 0;                               // S_t: kSStride columns each (buffer b at + 64 b)
+  static constexpr int kTmemO = kQTiles * kSStride;              // O_t: kDPadN columns each
   static_assert(kTmemNeed <= kTmemCols, "TMEM budget");
   static_assert(kSmemBytes <= 226 * 1024, "shared memory budget");
   static_assert(kSmall || kSmemBytes > 114 * 1024, "a second resident CTA would only wait for the 512 TMEM columns");
@@ -148,7 +163,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   constexpr int NS = C::kStages;
   constexpr int NT = C::kQTiles;
   extern __shared__ __align__(1024) uint8_t smem[];     // SWIZZLE_128B atoms need 1024-byte alignment
-  __shared__ __align__(8) uint64_t bars[2 + 4 * NT + 4 * NS + 1];
+  __shared__ __align__(8) uint64_t bars[2 + 6 * NT + 4 * NS + 1];
   uint8_t* sQ = smem;                                   // [NT] query tiles
   uint8_t* sK = sQ + NT * C::kQTileBytes;               // [NS] K tiles
   uint8_t* sV = sK + NS * C::kKVTileBytes;              // [NS] V tiles
@@ -156,10 +171,10 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint64_t* q_full = bars + 0;
   uint64_t* q_ready = bars + 1;
-  uint64_t* s_full = bars + 2;                           // [t] S_j of tile t is in TMEM
-  uint64_t* s_free = s_full + NT;                        // [t] S_j is in registers: the S columns may be overwritten
-  uint64_t* p_ready = s_free + NT;                       // [t] P_j is in shared memory (and O rescaled if needed)
-  uint64_t* pv_done = p_ready + NT;                      // [t] O += P_j V_j finished: P buffer and O are free
+  uint64_t* s_full = bars + 2;                           // [2t + buf] S_j of tile t is in TMEM (buf = j & 1 if kSDouble, else 0)
+  uint64_t* s_free = s_full + 2 * NT;                    // [t] S_j is in registers: the S columns may be overwritten
+  uint64_t* p_ready = s_free + NT;                       // [2t + buf] P_j is published (and O rescaled if needed)
+  uint64_t* pv_done = p_ready + 2 * NT;                  // [t] O += P_j V_j finished: P buffer and O are free
   uint64_t* k_full = pv_done + NT;
   uint64_t* k_empty = k_full + NS;
   uint64_t* v_full = k_empty + NS;
@@ -181,9 +196,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     mbar_init(q_full, 1);
     mbar_init(q_ready, 4 * n_tiles);
     for (int t = 0; t < NT; ++t) {
-      mbar_init(&s_full[t], 1);
-      mbar_init(&s_free[t], 4);
-      mbar_init(&p_ready[t], 4);
+      mbar_init(&s_full[2 * t], 1);
+      mbar_init(&s_full[2 * t + 1], 1);
+      mbar_init(&s_free[t], C::kSDouble ? 1 : 4);
+      mbar_init(&p_ready[2 * t], 4);
+      mbar_init(&p_ready[2 * t + 1], 4);
       mbar_init(&pv_done[t], 1);
     }
     for (int i = 0; i < 4 * NS; ++i) mbar_init(&k_full[i], 1);
@@ -241,23 +258,23 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       const uint32_t p_addr = smem_u32(sP);
       const bool leader = elect_one();
       // S_t = Q_t K_j^T : K-steps of 16 over the (padded) head dim
-      auto issue_qk = [&](int t, int stage) {
+      auto issue_qk = [&](int t, int stage, int buf = 0) {
         if (leader) {
           // one descriptor per operand tile; the K-step offsets are added to its 16-byte address field
           const uint64_t kd = umma_desc_kmajor_sw128(smem_u32(sK + stage * C::kKVTileBytes));
           const uint64_t qd = q_desc0 + static_cast<uint64_t>(t * (C::kQTileBytes >> 4));
-          const uint32_t tmem_s = tmem_base + C::kTmemS + t * BKV;
+          const uint32_t tmem_s = tmem_base + C::kTmemS + t * C::kSStride + buf * BKV;
 #pragma unroll
           for (int kk = 0; kk < C::kDPadK / 16; ++kk) {
             const uint64_t qoff = static_cast<uint64_t>(((kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32) >> 4);
             const uint64_t koff = static_cast<uint64_t>(((kk >> 2) * (BKV * 128) + (kk & 3) * 32) >> 4);
             umma_ss(tmem_s, qd + qoff, kd + koff, idesc_qk, kk != 0);
           }
-          umma_commit(&s_full[t]);
+          umma_commit(&s_full[2 * t + buf]);
         }
       };
       // O_t += P_t V_j : K-steps of 16 keys; V tile is [key][64 cols] per atom -> MN-major, LBO = atom stride
-      auto issue_pv = [&](int t, int stage, bool first, bool last) {
+      auto issue_pv = [&](int t, int stage, bool first, bool last, int buf = 0) {
         if (leader) {
           const uint64_t vd = umma_desc_mnmajor_sw128(smem_u32(sV + stage * C::kKVTileBytes), BKV * 128);
           const uint32_t tmem_o = tmem_base + C::kTmemO + t * C::kDPadN;
@@ -266,13 +283,18 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
             const uint64_t voff = static_cast<uint64_t>((kk * (16 * 128)) >> 4);
             if constexpr (C::kPTmem) {
               // A = P_t from TMEM: 16 keys = 8 columns of packed bf16 pairs, same lanes as the S rows
-              umma_ts(tmem_o, tmem_base + C::kTmemS + t * BKV + kk * 8, vd + voff, idesc_pv, !(first && kk == 0));
+              umma_ts(tmem_o, tmem_base + C::kTmemS + t * C::kSStride + buf * BKV + kk * 8, vd + voff, idesc_pv,
+                      !(first && kk == 0));
             } else {
               const uint32_t pa = p_addr + t * C::kPBytes + kk * 32;
               umma_ss(tmem_o, umma_desc_kmajor_sw128(pa), vd + voff, idesc_pv, !(first && kk == 0));
             }
           }
-          if (!C::kPTmem || last) umma_commit(&pv_done[t]);
+          // double-buffered S: pv_done[t] completes every round (the rare O rescale waits for round j-1 on it), and
+          // the epilogue gets its own one-shot barrier (s_free[t], otherwise unused with P in TMEM): a softmax warp can
+          // finish P(n-1) before round n-2 has completed, and a parity wait cannot tell two phases apart
+          if (!C::kPTmem || C::kSDouble || last) umma_commit(&pv_done[t]);
+          if (C::kSDouble && last) umma_commit(&s_free[t]);
         }
       };
 #ifdef AFB_ATTN_PROFILE
@@ -288,6 +310,48 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t all = (1u << n_tiles) - 1u;
+      if constexpr (C::kSDouble) {
+        // Run-ahead schedule: S(0) and S(1) of every tile up front; in round j, when tile t publishes P_t(j) (in S
+        // buffer j & 1): O_t += P_t(j) V_j, then S_t(j+2) = Q_t K_{j+2}^T into that same buffer (the tensor pipe keeps
+        // issue order, so the overwrite lands behind the read).  The softmax of round j+1 never waits for an MMA.
+        static_assert(NS >= 3, "K ring: tiles j+1 and j+2 are live while j+3 loads");
+        if (num_kv_tiles > 1) {
+          mbar_wait(&k_full[1], 0);
+          tc_fence_after();
+          for (int t = 0; t < n_tiles; ++t) issue_qk(t, 1, 1);
+          if (leader) umma_commit(&k_empty[1]);
+        }
+        for (int j = 0; j < num_kv_tiles; ++j) {
+          const int st = j % NS, st2 = (j + 2) % NS;
+          const bool more = j + 2 < num_kv_tiles;
+          AFB_PROF(3);
+          if (more) mbar_wait(&k_full[st2], ((j + 2) / NS) & 1);
+          mbar_wait(&v_full[st], (j / NS) & 1);
+          AFB_PROF(0);
+          const int buf = j & 1;
+          const uint32_t par = (j >> 1) & 1;
+          uint32_t pending = all;
+          while (pending != 0u) {
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+              if ((pending >> t) & 1u) {
+                if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[2 * t + buf], par))) {
+                  AFB_PROF(1);
+                  tc_fence_after();
+                  issue_pv(t, st, j == 0, j + 1 == num_kv_tiles, buf);
+                  if (more) issue_qk(t, st2, buf);
+                  pending &= ~(1u << t);
+                  AFB_PROF(2);
+                }
+              }
+            }
+          }
+          if (leader) {
+            umma_commit(&v_empty[st]);
+            if (more) umma_commit(&k_empty[st2]);
+          }
+        }
+      } else
       for (int j = 0; j < num_kv_tiles; ++j) {
         int nstage = stage + 1;
         uint32_t nphase = phase;
@@ -320,7 +384,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
               // one event per tile and round: P_t(j) sits in TMEM -> O_t += P_t(j) V_j, then S_t(j+1) = Q_t K_{j+1}^T
               // over the same columns (the tensor pipe runs them in issue order)
               if ((pending >> (NT + t)) & 1u) {
-                if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[t], par))) {
+                if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[2 * t], par))) {
                   AFB_PROF(1);
                   tc_fence_after();
                   issue_pv(t, stage, j == 0, !more);
@@ -342,7 +406,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
               }
             }
             if ((pending >> (NT + t)) & 1u) {
-              if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[t], par))) {
+              if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[2 * t], par))) {
                 AFB_PROF(1);
                 tc_fence_after();
                 issue_pv(t, stage, j == 0, !more);
@@ -373,7 +437,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     const int quarter = warp & 3;                         // TMEM lane quarter this warp may access (= its SMSP)
     const int row = quarter * 32 + lane;                  // query row inside the tile
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
-    const uint32_t tmem_s = tmem_base + lane_addr + C::kTmemS + t * BKV;
+    const uint32_t tmem_s0 = tmem_base + lane_addr + C::kTmemS + t * C::kSStride;
     const uint32_t tmem_o = tmem_base + lane_addr + C::kTmemO + t * C::kDPadN;
     uint8_t* prow = sP + t * C::kPBytes + row * 128;
 #ifdef AFB_ATTN_PROFILE
@@ -412,7 +476,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 #endif
     for (int j = 0; j < num_kv_tiles; ++j) {
       AFB_PROF(7);
-      mbar_wait(&s_full[t], j & 1);
+      const int sbuf = C::kSDouble ? (j & 1) : 0;
+      const uint32_t tmem_s = tmem_s0 + sbuf * BKV;
+      mbar_wait(&s_full[2 * t + sbuf], C::kSDouble ? ((j >> 1) & 1) : (j & 1));
       tc_fence_after();
       AFB_PROF(0);                                        // wait for S
       uint32_t r[BKV];
@@ -459,7 +525,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       } else if (__any_sync(0xffffffffu, need)) {
         // rare after the first tiles: O must be rescaled, which needs O += P_{j-1} V_{j-1} to have finished
         // (P through TMEM: S_j was issued behind it and has completed, so it has)
-        if constexpr (!C::kPTmem) {
+        // (double-buffered S: S_j sits behind O += P_{j-2} V_{j-2} only, so round j-1 is waited for explicitly)
+        if constexpr (!C::kPTmem || C::kSDouble) {
           mbar_wait(&pv_done[t], (j - 1) & 1);
           tc_fence_after();
         }
@@ -527,7 +594,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_ready[t]);
+      if (lane == 0) mbar_arrive(&p_ready[2 * t + sbuf]);
       AFB_PROF(6);                                        // P store
     }
 #ifdef AFB_ATTN_PROFILE
@@ -539,7 +606,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 #endif
 
     // ---- epilogue: O / l -> bf16 -> out[b, q, head*D : head*D + D]
-    mbar_wait(&pv_done[t], C::kPTmem ? 0 : ((num_kv_tiles - 1) & 1));
+    if constexpr (C::kSDouble) mbar_wait(&s_free[t], 0);
+    else mbar_wait(&pv_done[t], C::kPTmem ? 0 : ((num_kv_tiles - 1) & 1));
     tc_fence_after();
     const int q_idx = q0 + t * kBlockQ + row;
     if constexpr (C::kOnes) {
