@@ -33,7 +33,7 @@ def _digest() -> str:
     files.append(os.path.join(os.path.dirname(PKG_DIR), "include", "adaface_b200.h"))
     for f in files:
         with open(f, "rb") as fh:
-            h.update(f.encode())
+            h.update(os.path.basename(f).encode())     # not the absolute path: the checkout moves (GPU box scratch dirs)
             h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())
     return h.hexdigest()
@@ -45,14 +45,30 @@ def is_current() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    """Compiles and links the library if the sources changed.  Safe under concurrent callers (one process per GPU
+    under torchrun): an exclusive file lock serialises them, the late ones find the library current, and the .so is
+    moved into place atomically so that no process can dlopen a half-written file."""
     if not force and is_current():
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
+    import fcntl
+    with open(os.path.join(LIB_DIR, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
     nvcc = _nvcc()
     objs = []
     procs = []
+    tag = f".{os.getpid()}"
     for src in SOURCES:
-        obj = os.path.join(LIB_DIR, src.replace(".cu", ".o"))
+        obj = os.path.join(LIB_DIR, src.replace(".cu", tag + ".o"))
         cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd[1:1] = ["-Xptxas", "-v"]
@@ -68,13 +84,19 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
     if failed:
         raise RuntimeError("adaface_b200 CUDA build failed")
-    link = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB_PATH, *objs, "-lcudart_static",
+    tmp_lib = LIB_PATH + tag + ".tmp"
+    link = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", tmp_lib, *objs, "-lcudart_static",
             "-ldl", "-lrt", "-lpthread"]
     subprocess.run(link, check=True)
     for o in objs:
         os.remove(o)
-    with open(LIB_PATH + ".sha256", "w") as fh:
+    stamp = LIB_PATH + ".sha256"
+    if os.path.exists(stamp):
+        os.remove(stamp)                       # never a current-looking stamp next to a library being replaced
+    os.replace(tmp_lib, LIB_PATH)
+    with open(stamp + tag, "w") as fh:
         fh.write(_digest())
+    os.replace(stamp + tag, stamp)
     return LIB_PATH
 
 

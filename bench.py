@@ -155,7 +155,7 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_RESULT_OUT, flush=True)
 
 
 def workload_config(world):
@@ -430,10 +430,13 @@ def run_ours(args):
                                     "those (x8 extrapolation)"}
         else:
             line["cpu_baseline"] = None
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_RESULT_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+_RESULT_OUT = sys.stdout
 
 
 def main():
@@ -451,6 +454,12 @@ def main():
                     help="config2 (default, the benchmarked one): 64x64 latents, 8 samples + CFG pair; config5: 96x96 "
                          "latents, 16 samples + CFG pair (BASELINE.json configs[4] geometry; an extra data point)")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON result: libraries that chat on file descriptor 1 (NCCL prints
+    # "NCCL version ..." there when NCCL_DEBUG=VERSION is set on the box) are sent to stderr instead
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.workload == "config5":
         global N_SAMPLES, LATENT
         N_SAMPLES, LATENT = 16, 96

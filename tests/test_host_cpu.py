@@ -268,3 +268,27 @@ print("ok")
     for km in ("z", "y"):
         sd = {k: v.detach() for k, v in ck.string_to_static_embedder[km].state_dict().items()}
         assert rel_l2(port.static_layerwise_embedding(sd), g[f"static_{km}"]) < 1e-5
+
+
+def test_built_library_stays_current_when_the_checkout_moves(tmp_path):
+    """The GPU box runs a COPY of the repository under another path with the prebuilt .so inside: the staleness check
+    must not depend on where the checkout lives (a rebuild there, by every rank of a torchrun job at once, once produced
+    a half-linked library), and concurrent build() callers must serialise on the file lock."""
+    import shutil
+    import subprocess
+    import sys
+    from adaface_b200 import build as B
+    if not os.path.exists(B.LIB_PATH):
+        pytest.skip("library not built")
+    assert B.is_current()
+    root = tmp_path / "elsewhere"
+    shutil.copytree(os.path.join(ROOT, "adaface_b200"), root / "adaface_b200", ignore=shutil.ignore_patterns("__pycache__"))
+    shutil.copytree(os.path.join(ROOT, "include"), root / "include")
+    code = ("import sys; from adaface_b200 import build as B; assert B.PKG_DIR.startswith(sys.argv[1]), B.PKG_DIR; "
+            "assert B.is_current(); print(B.build())")
+    procs = [subprocess.Popen([sys.executable, "-c", code, str(root)], cwd=root, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                              text=True, env=dict(os.environ, PYTHONPATH=str(root))) for _ in range(3)]
+    for p in procs:
+        out, err = p.communicate(timeout=600)
+        assert p.returncode == 0, err[-1500:]
+        assert out.strip().endswith("libadaface_b200.so")
