@@ -18,6 +18,9 @@
 // so that while some wait for scores, take the row max or publish P, others are in their exponential phase.  The
 // exponential phase is FFMA2 (scale and max folded) -> MUFU.EX2 -> FADD2 -> F2FP, the row max FMNMX3 on raw scores;
 // one pair of exponentials in three runs on the FMA pipe instead (degree-3 minimax exp2).
+// Two more configurations of the same kernel (AttnCfg): head dim 80 keeps TWO S buffers per query tile so that
+// S(j+1) is computed while the softmax warps work on S(j) (kSDouble), and short key sequences (the 77-token context)
+// run as one-query-tile CTAs with 128 / 256 TMEM columns, several per SM (kSmall).
 //
 // Replaces attention.py:198-242 (einsum QK^T, masked_fill, softmax, einsum PV, head merge) without ever
 // materialising the [8B, N, N] score tensor.
