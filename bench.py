@@ -423,11 +423,13 @@ def run_ours(args):
                                           "default, every 3x3 ResBlock convolution with AFB_CONV=1); part of non_st_ms_per_step"},
                 "kernels": breakdown}
         if world == 1 and not args.no_cpu_baseline:
-            t_pair, threads = cpu_unet_step_time(1, 0)
+            n_cpu = 5 if LATENT <= 64 else 1                     # ~10-15 s of CPU work on the box's host cores
+            t_pair, threads = cpu_unet_step_time(n_cpu, 1)
             line["cpu_baseline"] = {"value": 1.0 / (t_pair * N_SAMPLES), "unit": "steps/s", "cores": threads,
-                                    "kind": "port", "sample": "oracle/port.py fp32: one U-Net call + CFG/DDIM update "
-                                    f"for 1 sample + its CFG pair (batch 2, 64x64) took {t_pair:.2f} s; a step is 8 of "
-                                    "those (x8 extrapolation)"}
+                                    "kind": "port", "sample": f"oracle/port.py fp32 on {threads} host threads: U-Net call + "
+                                    f"CFG/DDIM update for 1 sample + its CFG pair (batch 2, {LATENT}x{LATENT}), mean of "
+                                    f"{n_cpu} calls after 1 warm-up = {t_pair:.2f} s; a step is {N_SAMPLES} of those "
+                                    f"(x{N_SAMPLES} extrapolation)"}
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), file=_RESULT_OUT, flush=True)
