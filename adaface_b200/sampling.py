@@ -70,3 +70,45 @@ def sample_sharded(run_local: Callable[[Tensor, Tensor, Tensor], Tensor], x_T: T
     else:
         out = x_T[:0].clone()
     return all_gather_samples(out, bounds, group) if gather else out
+
+
+class FlatGradAllReduce:
+    """The one collective of inversion mode (BASELINE.json configs[3]): the U-Net is frozen and
+    replicated, only the AdaEmbedding / StaticLayerwiseEmbedding parameters (3.8 M floats = 15 MB) carry gradients,
+    so a data-parallel optimizer step needs ONE all-reduce: every gradient is copied into a persistent flat fp32
+    buffer, summed over the ranks (NCCL over NVLink; gloo in the CPU tests), divided by the world size and copied
+    back - the arithmetic of the reference's Lightning-DDP wrapper (main.py:862) on its trainable set.  Only the
+    collective is built: the backward kernels that would produce these gradients are not.
+    Parameters whose `.grad` is None on a rank contribute zeros (DDP's find_unused_parameters semantics)."""
+
+    def __init__(self, params, group=None):
+        self.params = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("FlatGradAllReduce: no trainable parameters")
+        dev = self.params[0].device
+        if any(p.device != dev for p in self.params):
+            raise ValueError("FlatGradAllReduce: parameters on different devices")
+        self.group = group
+        self.offsets, n = [], 0
+        for p in self.params:
+            self.offsets.append(n)
+            n += p.numel()
+        self.flat = torch.zeros(n, dtype=torch.float32, device=dev)
+
+    @torch.no_grad()
+    def __call__(self) -> Tensor:
+        """Averages the gradients over the ranks in place; returns the flat buffer (a view of what was reduced)."""
+        self.flat.zero_()
+        for p, off in zip(self.params, self.offsets):
+            if p.grad is not None:
+                self.flat[off:off + p.numel()].copy_(p.grad.reshape(-1))
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+            self.flat.div_(dist.get_world_size(self.group))
+        for p, off in zip(self.params, self.offsets):
+            g = self.flat[off:off + p.numel()].view_as(p)
+            if p.grad is None:
+                p.grad = g.clone().to(p.dtype)
+            else:
+                p.grad.copy_(g)
+        return self.flat

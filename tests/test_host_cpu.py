@@ -223,6 +223,35 @@ def test_sample_sharded_world_size_2_gloo(tmp_path, n):
     assert sum(counts) == n and abs(counts[0] - counts[1]) <= 1
 
 
+def _grad_worker(rank, world, port_no, out_dir):
+    import torch.distributed as dist
+    from adaface_b200.sampling import FlatGradAllReduce
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port_no}", rank=rank, world_size=world)
+    torch.manual_seed(0)                                                # same parameters on every rank
+    params = [torch.nn.Parameter(torch.randn(9, 12, 768)), torch.nn.Parameter(torch.randn(108, 720)),
+              torch.nn.Parameter(torch.randn(5)), torch.nn.Parameter(torch.randn(3), requires_grad=False)]
+    g = torch.Generator().manual_seed(100 + rank)                       # different gradients per rank
+    grads = [torch.randn(p.shape, generator=g) for p in params[:3]]
+    params[0].grad, params[1].grad = grads[0].clone(), grads[1].clone()
+    if rank == 0:
+        params[2].grad = grads[2].clone()                               # unused on rank 1: contributes zeros
+    reducer = FlatGradAllReduce(params)
+    flat = reducer()
+    assert flat.numel() == sum(p.numel() for p in params[:3]) and params[3].grad is None
+    torch.save({"grads": [p.grad.clone() for p in params[:3]], "own": grads}, os.path.join(out_dir, f"g{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_inversion_gradient_allreduce_world_size_2_gloo(tmp_path):
+    """SURVEY.md 8e, inversion mode: one flat-buffer all-reduce averages the embedding gradients over the ranks."""
+    import torch.multiprocessing as mp
+    mp.spawn(_grad_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (torch.load(os.path.join(tmp_path, f"g{r}.pt")) for r in range(2))
+    for i in range(3):
+        want = (r0["own"][i] + (r1["own"][i] if i < 2 else 0)) / 2
+        assert torch.allclose(r0["grads"][i], want, atol=1e-6) and torch.equal(r0["grads"][i], r1["grads"][i])
+
+
 def test_reference_embedding_checkpoint_loads_without_ldm():
     """a checkpoint written by torch.save with LIVE reference modules (pickled class path
     ldm.modules.embedding_manager.StaticLayerwiseEmbedding; fixture made by oracle/gen_golden.py from the imported
