@@ -238,7 +238,16 @@ def _grad_worker(rank, world, port_no, out_dir):
     reducer = FlatGradAllReduce(params)
     flat = reducer()
     assert flat.numel() == sum(p.numel() for p in params[:3]) and params[3].grad is None
-    torch.save({"grads": [p.grad.clone() for p in params[:3]], "own": grads}, os.path.join(out_dir, f"g{rank}.pt"))
+    first = [p.grad.clone() for p in params[:3]]
+    # attached mode: the gradients live inside the flat buffer, a call is only the all-reduce
+    params[0].grad, params[1].grad, params[2].grad = grads[0].clone(), grads[1].clone(), None
+    if rank == 0:
+        params[2].grad = grads[2].clone()
+    reducer.attach()
+    assert all(reducer._is_view(p, off) for p, off in zip(reducer.params, reducer.offsets))
+    reducer()
+    assert all(torch.equal(p.grad, f) for p, f in zip(params[:3], first)), "attached mode differs from copy mode"
+    torch.save({"grads": first, "own": grads}, os.path.join(out_dir, f"g{rank}.pt"))
     dist.destroy_process_group()
 
 
