@@ -42,14 +42,18 @@ def main():
     with torch.no_grad():
         gathered = sample_sharded(run_local, x_T, c, uc)
         full = run_local(x_T, c, uc)                      # every rank also runs all samples alone
+    # The two runs use different batch sizes (cuDNN algorithm choice, GroupNorm chunking, GEMM row tiling), so they agree
+    # to bf16 rounding amplified by the random-init U-Net over the steps, not bit for bit: the bar is the north star's
+    # latent cosine >= 0.995, PER SAMPLE (a sharding mistake - a wrong context slice, a misplaced sample - gives ~0).
     rel = float((gathered - full).norm() / full.norm())
-    cos = float(torch.nn.functional.cosine_similarity(gathered.flatten(), full.flatten(), dim=0))
-    same = torch.tensor([1.0 if (gathered.shape == full.shape and rel < 1e-2 and bool(torch.isfinite(gathered).all())) else 0.0],
-                        device=dev)
+    cos = torch.nn.functional.cosine_similarity(gathered.flatten(1), full.flatten(1), dim=1)
+    good = gathered.shape == full.shape and bool(torch.isfinite(gathered).all()) and float(cos.min()) >= 0.995
+    same = torch.tensor([1.0 if good else 0.0], device=dev)
     dist.all_reduce(same, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(json.dumps({"check": "sample_sharded_vs_single_gpu", "world": world, "samples": n, "ddim_steps": STEPS,
-                          "rel_l2": rel, "cosine": cos, "ok": bool(same.item() == 1.0)}), flush=True)
+                          "rel_l2": rel, "cosine_per_sample_min": float(cos.min()), "cosine_per_sample": [round(float(v), 5) for v in cos],
+                          "ok": bool(same.item() == 1.0)}), flush=True)
     dist.destroy_process_group()
     sys.exit(0 if same.item() == 1.0 else 1)
 
