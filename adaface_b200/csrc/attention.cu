@@ -116,7 +116,12 @@ struct AttnCfg {
 #ifndef AFB_ATTN_POLY_EVERY
 #define AFB_ATTN_POLY_EVERY 3
 #endif
-  static constexpr int kPolyEvery = (D <= 40) ? AFB_ATTN_POLY_EVERY : 0;          // every kPolyEvery-th pair of exponentials on the FMA pipe
+// d = 80: no FMA-pipe exponentials (measured 74.7 us without, 75.3 / 76.3 us with one pair in three / four: the
+// kernel is latency-, not MUFU-bound there)
+#ifndef AFB_ATTN_POLY_EVERY_80
+#define AFB_ATTN_POLY_EVERY_80 0
+#endif
+  static constexpr int kPolyEvery = (D <= 40) ? AFB_ATTN_POLY_EVERY : (D <= 80 ? AFB_ATTN_POLY_EVERY_80 : 0);          // every kPolyEvery-th pair of exponentials on the FMA pipe
   static constexpr int kSmemBytes =
       kQTiles * (kQTileBytes + ((kSmall && kPTmem) ? 0 : kPBytes)) + kStages * 2 * kKVTileBytes;
   static constexpr int kSStride = kSDouble ? 2 * kBlockKV : kBlockKV;     // TMEM columns of one tile's S buffer(s)
