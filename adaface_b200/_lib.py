@@ -50,6 +50,8 @@ _SIGNATURES = {
     "afb_groupnorm_ws_floats": (_I64, [_I, _I, _I]),
     "afb_groupnorm_tokens": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _P, _I, _P]),
     "afb_groupnorm_tokens_cat": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _P, _I, _P]),
+    "afb_groupnorm_static_ws_max_floats": (_I64, []),
+    "afb_groupnorm_tokens_static_ws": (_I, [_P, _I, _P, _P, _P, _I, _I, _I, _I, _F, _I, _P, _I, _P]),
     "afb_add_bias_residual": (_I, [_P, _P, _P, _P, _I64, _I, _P]),
     "afb_layernorm_bf16": (_I, [_P, _P, _P, _P, _I64, _I, _F, _P]),
     "afb_gemm_bf16": (_I, [C.POINTER(GemmArgs), _P]),

@@ -7,6 +7,8 @@
 
 #include <cooperative_groups.h>
 
+#include <mutex>
+
 
 namespace afb {
 void count_launch();
@@ -683,4 +685,59 @@ extern "C" int afb_layernorm_bf16(const afb_bf16* x, const float* gamma, const f
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// ---- allocation-free variant: the statistics workspace lives in the library ------------------------------------
+// afb_groupnorm_tokens_static_ws == afb_groupnorm_tokens with `stats_ws` taken from a file-scope device array instead
+// of a caller buffer, for callers that cannot allocate (CUDA graph capture, tight serving loops).  No counterpart in
+// the reference.  Every GPU that loads the library holds the array
+// (kGnStaticWsFloats * 4 bytes = 1 MiB) until the process exits.
+namespace afb {
+namespace {
+constexpr int64_t kGnStaticWsFloats = 256 * 1024;
+static __device__ __align__(256) float g_gn_static_ws[kGnStaticWsFloats];
+
+// In host code `g_gn_static_ws` is only the host-side shadow of the symbol, not a device address: the address a
+// kernel may use is resolved once per device (with that device current) through cudaGetSymbolAddress and cached.
+constexpr int kGnStaticMaxDevices = 64;
+float* g_gn_static_ws_addr[kGnStaticMaxDevices] = {};
+std::mutex g_gn_static_ws_mu;
+
+int gn_static_ws(float** out) {
+  int dev = -1;
+  AFB_CHECK_CUDA(cudaGetDevice(&dev));
+  AFB_REQUIRE(dev >= 0 && dev < kGnStaticMaxDevices, "afb_groupnorm_tokens_static_ws: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_gn_static_ws_mu);
+  if (g_gn_static_ws_addr[dev] == nullptr) {
+    void* p = nullptr;
+    AFB_CHECK_CUDA(cudaGetSymbolAddress(&p, g_gn_static_ws));
+    AFB_REQUIRE(p != nullptr, "afb_groupnorm_tokens_static_ws: cudaGetSymbolAddress returned NULL");
+    g_gn_static_ws_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_gn_static_ws_addr[dev];
+  return 0;
+}
+}  // namespace
+}  // namespace afb
+
+extern "C" int64_t afb_groupnorm_static_ws_max_floats(void) { return afb::kGnStaticWsFloats; }
+
+extern "C" int afb_groupnorm_tokens_static_ws(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
+                                              int batch, int channels, int hw, int groups, float eps, int act,
+                                              const float* pre_add, int pre_add_ld, afb_stream_t stream) {
+  using namespace afb;
+  AFB_REQUIRE(batch > 0 && groups > 0, "afb_groupnorm_tokens_static_ws: empty input");
+  // what the kernels touch: 2*B*G floats of (mean, rstd) + 2*B*G*nchunks chunk partials, nchunks <= kGnMaxChunks
+  const int64_t need = 2ll * batch * groups * (1 + kGnMaxChunks);
+  AFB_REQUIRE(need <= kGnStaticWsFloats,
+              "afb_groupnorm_tokens_static_ws: batch %d x groups %d needs %lld workspace floats, the built-in scratch holds "
+              "%lld (batch * groups <= %lld); use afb_groupnorm_tokens with a caller workspace",
+              batch, groups, static_cast<long long>(need), static_cast<long long>(kGnStaticWsFloats),
+              static_cast<long long>(kGnStaticWsFloats / (2 * (1 + kGnMaxChunks))));
+  float* ws = nullptr;
+  if (const int rc = gn_static_ws(&ws)) return rc;
+  // Nothing in the workspace has to start at zero: the statistics kernel writes every (sample, group, chunk) slot the
+  // apply kernel reads in the same call, so the previous call's contents are never observed.
+  return afb_groupnorm_tokens_cat(x, 0, nullptr, x_layout, gamma, beta, y, ws, batch, channels, hw, groups, eps, act,
+                                  pre_add, pre_add_ld, stream);
 }

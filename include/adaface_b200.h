@@ -62,6 +62,22 @@ int afb_groupnorm_tokens_cat(const void* x, int channels1, const afb_bf16* x2, i
                              const float* beta, afb_bf16* y, float* stats_ws, int batch, int channels, int hw,
                              int groups, float eps, int act, const float* pre_add, int pre_add_ld, afb_stream_t stream);
 
+/* ---- allocation-free variant of afb_groupnorm_tokens.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and results as afb_groupnorm_tokens minus `stats_ws`: the statistics
+ * workspace is a file-scope `static __device__` array inside the library (1 MiB = afb_groupnorm_static_ws_max_floats()
+ * floats per GPU that loads the library, held until the process exits).  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine); the caller still owns x and y.  Limit: 2 * batch * groups * 33 floats must
+ * fit, i.e. batch * groups <= 3971 (batch <= 124 at 32 groups); larger inputs are rejected with code 2 - use
+ * afb_groupnorm_tokens with a caller workspace.  All calls on a device share the one array: calls that overlap on the
+ * GPU (different streams, or graph branches without an edge between them) race on it; calls ordered on one stream are
+ * safe, and nothing needs to be cleared between them (every slot read in a call is written earlier in that call).
+ * The array's device address is resolved once per device on the first call made with that device current. */
+int64_t afb_groupnorm_static_ws_max_floats(void);
+int afb_groupnorm_tokens_static_ws(const void* x, int x_layout, const float* gamma, const float* beta, afb_bf16* y,
+                                   int batch, int channels, int hw, int groups, float eps, int act,
+                                   const float* pre_add, int pre_add_ld, afb_stream_t stream);
+
 /* ---- out = a + b + bias (elementwise, bf16 [rows, C] token-major; b and bias optional).  The residual / bias adds
  * around the ResBlock convolutions (openaimodel.py:279) as one vectorised pass instead of two broadcast adds. */
 int afb_add_bias_residual(const afb_bf16* a, const afb_bf16* b, const float* bias, afb_bf16* out, int64_t rows,
