@@ -45,6 +45,7 @@ _P, _I, _I64, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
 _SIGNATURES = {
     "afb_last_error": (C.c_char_p, []),
     "afb_abi_version": (_I, []),
+    "afb_header_digest": (C.c_char_p, []),
     "afb_launch_count": (_I64, []),
     "afb_cfg_ddim_step": (_I, [_P, _P, _P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _F, _P]),
     "afb_groupnorm_ws_floats": (_I64, [_I, _I, _I]),
@@ -101,6 +102,14 @@ def load():
         fn = getattr(lib, name)          # AttributeError here = ABI mismatch, fail loudly
         fn.restype = res
         fn.argtypes = args
+    # a prebuilt library that could not be rebuilt (no nvcc here) must at least have been built against THIS header:
+    # a changed afb_gemm_args / afb_attn_args layout or argument order would otherwise corrupt kernel arguments silently
+    built_against = (lib.afb_header_digest() or b"").decode()
+    if built_against != _build.header_digest():
+        raise AdafaceB200Error(
+            f"adaface_b200: {path} was built against another revision of include/adaface_b200.h "
+            f"({built_against[:12]}... vs {_build.header_digest()[:12]}...) and could not be rebuilt here; "
+            "run `python -m adaface_b200.build` where nvcc is available")
     _LIB = lib
     return lib
 

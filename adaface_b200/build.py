@@ -39,6 +39,13 @@ def _digest() -> str:
     return h.hexdigest()
 
 
+def header_digest() -> str:
+    """sha256 of include/adaface_b200.h: compiled into the library (afb_header_digest) so that a loader can tell a
+    library built against another revision of the argument structs / signatures from a current one."""
+    with open(os.path.join(os.path.dirname(PKG_DIR), "include", "adaface_b200.h"), "rb") as fh:
+        return hashlib.sha256(fh.read()).hexdigest()
+
+
 def is_current() -> bool:
     stamp = LIB_PATH + ".sha256"
     return os.path.exists(LIB_PATH) and os.path.exists(stamp) and open(stamp).read().strip() == _digest()
@@ -70,6 +77,8 @@ def _build_locked(verbose: bool) -> str:
     for src in SOURCES:
         obj = os.path.join(LIB_DIR, src.replace(".cu", tag + ".o"))
         cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        if src == "common.cu":
+            cmd.insert(1, f'-DAFB_HEADER_DIGEST="{header_digest()}"')
         if verbose:
             cmd[1:1] = ["-Xptxas", "-v"]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

@@ -47,10 +47,26 @@ def _shell(module: str, name: str) -> type:
     return _SHELLS[key]
 
 
+# What an `embeddings_gs-*.pt` legitimately names beside the reference's own classes: torch tensors / parameters /
+# storages and their rebuild helpers, torch.nn modules (the pickled embedders are live nn.Modules), plain containers and
+# numpy scalars / arrays.  Anything else is refused: a pickle from a third party must not be able to import and call
+# arbitrary globals (os.system, builtins.eval, ...) just because this reader runs with weights_only=False.
+_ALLOWED_MODULE_PREFIXES = ("torch", "collections", "numpy", "_codecs")
+_ALLOWED_BUILTINS = {"set", "frozenset", "list", "dict", "tuple", "int", "float", "bool", "str", "bytes", "bytearray",
+                     "complex", "slice", "range", "object"}
+_DENIED = {("torch", "load"), ("torch.serialization", "load"), ("torch.hub", "load"), ("numpy", "load")}
+
+
 class _Unpickler(pickle.Unpickler):
     def find_class(self, module: str, name: str):
         if module.startswith(REFERENCE_PREFIXES):
             return _shell(module, name)
+        root = module.split(".", 1)[0]
+        allowed = (root in _ALLOWED_MODULE_PREFIXES and (module, name) not in _DENIED) or \
+            (module in ("builtins", "__builtin__") and name in _ALLOWED_BUILTINS)
+        if not allowed:
+            raise pickle.UnpicklingError(f"embedding checkpoint names {module}.{name}, which is not on the allow-list of "
+                                         "this reader (torch / torch.nn / collections / numpy / plain containers)")
         return super().find_class(module, name)
 
 

@@ -94,5 +94,9 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
 }  // namespace afb
 
 extern "C" const char* afb_last_error(void) { return afb::g_error; }
-extern "C" int afb_abi_version(void) { return 10; }
+extern "C" int afb_abi_version(void) { return 11; }
+#ifndef AFB_HEADER_DIGEST
+#define AFB_HEADER_DIGEST "unknown"
+#endif
+extern "C" const char* afb_header_digest(void) { return AFB_HEADER_DIGEST; }
 extern "C" int64_t afb_launch_count(void) { return afb::g_launches.load(std::memory_order_relaxed); }

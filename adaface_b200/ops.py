@@ -505,9 +505,14 @@ def ada_pool_prep(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_
     pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=to_k_weight.device)
     lib = _lib.load()
     ws = torch.empty(int(lib.afb_ada_pool_prep_ws_floats(b, c)), dtype=torch.float32, device=to_k_weight.device)
-    _run("ada_pool_prep", lib.afb_ada_pool_prep, _ptr(f(to_k_weight)), ctx_dim, _ptr(f(fg_q_emb)),
-         _ptr(f(bg_q_emb)), _ptr(f(lora_to_fg_q)), _ptr(f(lora_to_bg_q)), _ptr(f(lora_to_k)), _ptr(pool_q), _ptr(ws), b, c,
-         _stream(), nbytes=4.0 * c * ctx_dim)
+    # the converted copies must outlive the launch: a temporary freed right after data_ptr() can be handed out again by
+    # the caching allocator for the next conversion, and the kernel would read overwritten weights
+    w, fg, bg, wf, wb, wk = map(f, (to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k))
+    if fg.numel() != ctx_dim or bg.shape != (b, ctx_dim):
+        raise ValueError("ada_pool_prep: fg_q_emb must hold ctx_dim values and bg_q_emb must be [B, ctx_dim]")
+    _run("ada_pool_prep", lib.afb_ada_pool_prep, _ptr(w), ctx_dim, _ptr(fg), _ptr(bg), _ptr(wf), _ptr(wb), _ptr(wk),
+         _ptr(pool_q), _ptr(ws), b, c, _stream(), nbytes=4.0 * c * ctx_dim)
+    del w, fg, bg, wf, wb, wk      # stream-ordered free: the allocator reuses them only behind the launch
     return pool_q
 
 
@@ -570,7 +575,8 @@ def ada_pool(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor],
     a_bg = torch.empty((b * 8, 1, n) if want_attn else (0,), dtype=torch.float32, device=dev)
     if key_mask is not None:
         key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
-    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q.contiguous()), _ptr(key_mask), _ptr(fg),
+    pool_q = pool_q.contiguous()
+    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg),
          _ptr(bg), _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c, _stream(),
          nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     return fg, bg, a_fg, a_bg
@@ -705,7 +711,8 @@ def splice_static_embedding(embedded_text: Tensor, first_pos: Tensor, static_emb
     B, N, D = et.shape
     L, K, _ = se.shape
     out = torch.empty((B * L, N, D), device=et.device, dtype=torch.bfloat16 if to_bf16 else torch.float32)
-    _run("splice_static_embedding", _lib.load().afb_splice_static_embedding, _ptr(et), _ptr(first_pos.contiguous()), _ptr(se),
+    first_pos = first_pos.contiguous()
+    _run("splice_static_embedding", _lib.load().afb_splice_static_embedding, _ptr(et), _ptr(first_pos), _ptr(se),
          None if to_bf16 else _ptr(out), _ptr(out) if to_bf16 else None, B, N, L, K, D, _stream(),
          nbytes=float(B * L * N * D) * (4 + (2 if to_bf16 else 4)))
     return out

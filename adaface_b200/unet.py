@@ -579,7 +579,9 @@ class UNetModel(nn.Module):
             ctx = torch.empty((16, b, t, d), dtype=torch.bfloat16, device=x.device)
             ctx.copy_(context.reshape(b, 16, t, d).permute(1, 0, 2, 3))
         else:
-            ctx = context.to(torch.bfloat16)
+            # the AdaEmbedding wiring splices subject rows into this call's context in place: never into the caller's
+            # own tensor (it is reused by every DDIM step and by the CFG concatenation)
+            ctx = context.to(torch.bfloat16, copy=ada is not None)
 
         ks_layers = [(-1 if ks is None else int(ks))] * 16
         if ks is not None and ks > 0:
@@ -644,6 +646,53 @@ class DiffusionModel:
         self.parameterization = "eps"
         self.use_cuda_graph = use_cuda_graph
         self._graphs = {}
+        self._param_list = None
+
+    # ---- what a captured graph bakes in beside its input buffers: the packed bf16 weight copies, the AdaEmbedding
+    # descriptor tables and the conditioning objects of extra_info.  The fingerprints below go into the graph key, so
+    # a load_state_dict / optimizer step / .to() or an edited extra_info re-captures instead of replaying stale state.
+    @staticmethod
+    def _tensor_id(t):
+        return (t.data_ptr(), t._version) if isinstance(t, torch.Tensor) else t
+
+    def _weights_fingerprint(self):
+        if self._param_list is None:
+            self._param_list = list(self.unet.parameters())
+        ver = ptr = 0
+        for p in self._param_list:
+            ver += p._version
+            ptr ^= p.data_ptr()
+        return (len(self._param_list), ver, ptr)
+
+    def _conditioning_fingerprint(self, extra_info) -> tuple:
+        out = []
+        for k in sorted(extra_info):
+            v = extra_info[k]
+            if k == "ada_prompt" and v is not None:
+                fp = [id(v), self._tensor_id(v.img_mask)]
+                for s in v.subjects:
+                    ver = ptr = 0
+                    for p in s.embedder.parameters():
+                        ver += p._version
+                        ptr ^= p.data_ptr()
+                    fp += [id(s.embedder), ver, ptr, tuple(s.token_positions), s.n_instances, s.cached_bg_from,
+                           self._tensor_id(s.layer_probes), self._tensor_id(s.layer_extra_means)]
+                out.append((k, tuple(fp)))
+            elif k == "placeholder2indices" and isinstance(v, dict):
+                out.append((k, tuple((name, tuple(self._tensor_id(torch.as_tensor(t)) if not isinstance(t, torch.Tensor)
+                                                  else self._tensor_id(t) for t in pair)) for name, pair in sorted(v.items()))))
+            elif isinstance(v, torch.Tensor):
+                out.append((k, self._tensor_id(v)))
+            elif isinstance(v, (int, float, bool, str, type(None))):
+                out.append((k, v))
+            else:
+                out.append((k, id(v)))
+        return tuple(out)
+
+    def invalidate_graphs(self) -> None:
+        """Drops every captured U-Net graph (the next apply_model re-captures)."""
+        self._graphs.clear()
+        self._param_list = None
 
     def q_sample(self, x_start, t, noise=None):
         noise = torch.randn_like(x_start) if noise is None else noise
@@ -663,7 +712,11 @@ class DiffusionModel:
         if not self.use_cuda_graph:
             return self._run(x_noisy, t, ctx, extra_info)
         key = (tuple(x_noisy.shape), tuple(ctx.shape), id(extra_info))
+        state = (self._weights_fingerprint(), self._conditioning_fingerprint(extra_info))
         g = self._graphs.get(key)
+        if g is not None and g[6] != state:       # weights or conditioning changed since the capture
+            del self._graphs[key]
+            g = None
         if g is None:
             sx, st, sc = x_noisy.clone(), t.clone(), ctx.clone()
             side = torch.cuda.Stream()
@@ -675,9 +728,10 @@ class DiffusionModel:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
                 out = self._run(sx, st, sc, extra_info)
-            g = (graph, sx, st, sc, out, extra_info)
+            # the fingerprint is taken AFTER the capture: warm-up builds the weight packs but touches no parameter
+            g = (graph, sx, st, sc, out, extra_info, state)
             self._graphs[key] = g
-        graph, sx, st, sc, out, _ = g
+        graph, sx, st, sc, out = g[:5]
         sx.copy_(x_noisy)
         st.copy_(t)
         if sc.data_ptr() != ctx.data_ptr():

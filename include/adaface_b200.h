@@ -31,6 +31,9 @@ typedef uint16_t afb_bf16;
 
 const char* afb_last_error(void);
 int afb_abi_version(void);
+/* sha256 (hex) of this header as it was when the library was built: a loader compares it with the header it binds
+ * against and refuses a library whose argument structs / signatures may differ (adaface_b200/_lib.py does). */
+const char* afb_header_digest(void);
 /* Number of kernels launched through this library by the calling process since load (bench.py's gpu_launches). */
 int64_t afb_launch_count(void);
 

@@ -20,6 +20,7 @@ import torch
 
 from . import params as P
 from .port import LAYER_IDX2CA
+from . import port
 from . import ref_harness as RH
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
@@ -269,6 +270,60 @@ def case_ddim50(ref, name="ddim50", seed=18, hw=64, steps=50):
     _save(name, samples=samples, meta=np.array([seed, hw, steps]), **trace)
 
 
+def case_unet_step_b16(ref, name="unet_step_b16", seed=17, hw=64, n_samples=8):
+    """The U-Net call of BASELINE.json configs[1] at its full batch: n_samples = 8 + the CFG pair = 16 samples at 64x64
+    through the UNMODIFIED reference U-Net (~9 GB of fp32 scores per 64x64 self-attention layer).  eps is stored
+    sub-sampled (every other pixel) plus in full for the first cond / uncond pair; per-SpatialTransformer outputs
+    sub-sampled like `unet_step`.  Same weights as `unet_step` (seed 17)."""
+    unet, _ = build_ref_unet(ref, seed)
+    x_T, c_cond, c_uncond = unet_inputs(name, n_samples, hw, seed)
+    x_in = torch.cat([x_T, x_T])
+    t_in = torch.full((2 * n_samples,), 981, dtype=torch.long)
+    ctx = torch.cat([c_cond, c_uncond])
+    arrays, idx = {}, [0]
+
+    def hook(mod, inp, out):
+        arrays[f"st_out_sub_{idx[0]}"] = out[::4, ::8, ::4, ::4]       # samples 0, 4 (cond) and 8, 12 (uncond)
+        idx[0] += 1
+
+    for m in unet.modules():
+        if isinstance(m, ref.attention.SpatialTransformer):
+            m.register_forward_hook(hook)
+    t0 = time.time()
+    with torch.no_grad():
+        eps = unet(x_in, t_in, context=ctx, context_in=None, extra_info=RH.default_extra_info())
+    print(f"reference U-Net forward B={2 * n_samples} {hw}x{hw}: {time.time() - t0:.1f}s")
+    assert idx[0] == 16
+    _save(name, eps_sub=eps[:, :, ::2, ::2], eps_pair0=eps[[0, n_samples]], meta=np.array([seed, hw, n_samples]), **arrays)
+
+
+def case_ddim50_ada(name, n_subjects, seed=18, hw=64, steps=50):
+    """`steps`-step DDIM with the AdaEmbedding call site composed into every conditioned layer (one subject: the
+    benchmarked workload of bench.py at n_samples = 1; two subjects: BASELINE.json configs[2] 'a z hugging a y').
+    The reference has no live call site for AdaEmbedding, so this fixture comes from oracle/port.py -
+    `unet_forward(ada_subjects=...)`, whose parts are pinned to the reference by `unet_step`, `ddim50` and `ada` - and not
+    from the reference modules.  n_samples = 1 + CFG (10, 4), eta = 0; U-Net weights as `ddim50` (seed 18)."""
+    sd = P.init_unet(seed)
+    x_T, c_cond, c_uncond = unet_inputs(name, 1, hw, seed)
+    subjects = P.ada_subject_inputs(name, n_subjects, 1, seed)
+    trace = {}
+    step = [0]
+
+    def apply_model(x_in, t_in, ctx):
+        out = port.unet_forward(sd, x_in, t_in, ctx, ada_subjects=subjects)
+        step[0] += 1
+        return out
+
+    t0 = time.time()
+    with torch.no_grad():
+        samples, tr = port.ddim_sample(apply_model, x_T, c_cond, c_uncond, steps, (10.0, 4.0), return_trace=True)
+    for i in (0, 9, 24, steps - 1):
+        if i < steps:
+            trace[f"x_step{i}"] = tr[i]
+    print(f"port {steps}-step DDIM with {n_subjects} AdaEmbedding subject(s) (B=2, {hw}x{hw}): {time.time() - t0:.1f}s")
+    _save(name, samples=samples, meta=np.array([seed, hw, steps, n_subjects]), **trace)
+
+
 FAST = ["st_small", "st_c640", "st_c1280", "st_mask_vk", "st_config1", "attn_vars", "conv_attn", "ada", "ddim"]
 SLOW = ["unet_step", "ddim10_small", "ddim50"]
 
@@ -411,6 +466,14 @@ def main(argv):
             case_static(ref)
         elif name == "embeddings_ckpt":
             case_embeddings_ckpt(ref)
+        elif name == "unet_step_b16":
+            case_unet_step_b16(ref)
+        elif name == "ddim50_ada1":
+            case_ddim50_ada("ddim50_ada1", 1)
+        elif name == "ddim50_ada2":
+            case_ddim50_ada("ddim50_ada2", 2)
+        elif name == "ddim10_ada2_small":
+            case_ddim50_ada("ddim10_ada2_small", 2, seed=19, hw=16, steps=10)
         elif name == "ddim10_small":
             case_ddim50(ref, "ddim10_small", seed=19, hw=16, steps=10)
         else:

@@ -235,3 +235,18 @@ def init_static_embedding(seed: int, K: int = 9, r: int = 12, n_init: int = 2) -
 def randn(key: str, shape, seed: int, scale: float = 1.0) -> torch.Tensor:
     """A named synthetic input tensor."""
     return draw(key, tuple(shape), seed, "normal", scale)
+
+
+def ada_subject_inputs(name: str, n_subjects: int, n_instances: int, seed: int, K: int = 9, r: int = 12):
+    """Seeded per-subject inputs of the AdaEmbedding wiring (BASELINE.json configs[1] with one subject,
+    configs[2] 'a z hugging a y' with two): an AdaEmbedding state_dict (K = 9 vectors, fg 5 / bg 4, rank r), the K token
+    positions the subject occupies in the 77-token prompt (2..10, then 13..21), the per-layer fg probe [16, 768] and the
+    per-layer bg query [16, n_instances, 768].  Shared by oracle/gen_golden.py, the GPU tests and bench.py's checker."""
+    out = []
+    for si in range(n_subjects):
+        first = 2 + 11 * si
+        out.append({"params": init_ada_embedding(seed + 10 * si, K, r, 2), "positions": list(range(first, first + K)),
+                    "probes": randn(f"{name}.{si}.probes", (16, 768), seed, 0.5),
+                    "extra_means": randn(f"{name}.{si}.extra", (16, n_instances, 768), seed, 0.5),
+                    "K": K, "r": r, "n_instances": n_instances})
+    return out

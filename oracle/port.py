@@ -160,6 +160,48 @@ def spatial_transformer(x: Tensor, p: Params, context=None, mask: Optional[Tenso
     return y.transpose(1, 2).reshape(b, c, h, w) + x_in                            # :341
 
 
+def spatial_transformer_ada(x: Tensor, p: Params, context, ada_subjects, ca_layer_idx: int, time_emb: Tensor,
+                            heads: int = 8, prefix: str = "", io: Optional[dict] = None) -> Tensor:
+    """SpatialTransformer.forward (attention.py:321-341, depth 1) with the per-layer AdaEmbedding call site composed in.
+
+    The reference snapshot defines AdaEmbedding but has no live call site for it (SURVEY.md finding F1: the
+    `get_layer_ada_conditioning` hook at embedding_manager.py:1754 was removed), so this composition is the BUILD'S
+    RECONSTRUCTION of SURVEY.md 3.2, not a restatement of reference lines: after attn2's query projection
+    (attention.py:176) and before its key / value projections (:195-196), every subject's AdaEmbedding
+    (`ada_embedding`, embedding_manager.py:779-910) turns this layer's (x1, q) into K vectors that overwrite the subject's
+    token rows of this layer's context for the first `n_instances` samples (the cond half of the CFG batch, F8).
+
+    ada_subjects: sequence of dicts {params, positions [K], probes [16,768], extra_means [16,n,768], K, r, n_instances,
+    cached_bg_from (optional index of the subject whose bg pooling is reused)}.  `context` as for spatial_transformer
+    (tensor, tuple or callable); a shared (not split) context is assumed."""
+    b, c, h, w = x.shape
+    pre = prefix + "transformer_blocks.0."
+    t = group_norm(x, p[prefix + "norm.weight"], p[prefix + "norm.bias"])                       # :325
+    t = t.reshape(b, c, h * w).transpose(1, 2) @ p[prefix + "proj_in.weight"].reshape(c, c).t() + p[prefix + "proj_in.bias"]
+    n1 = layer_norm(t, p[pre + "norm1.weight"], p[pre + "norm1.bias"])
+    x1 = cross_attention(n1, p, pre + "attn1.", None, None, heads) + t                          # :277
+    n2 = layer_norm(x1, p[pre + "norm2.weight"], p[pre + "norm2.bias"])
+    q = n2 @ p[pre + "attn2.to_q.weight"].t()                                                   # :176
+    v_context, k_context, _ = resolve_context(context)
+    ctx = k_context.clone()
+    bg_cache = {}
+    for i, s in enumerate(ada_subjects):
+        n = s["n_instances"]
+        cached = bg_cache.get(s.get("cached_bg_from")) if s.get("cached_bg_from") is not None else None
+        vecs, pooled = ada_embedding(s["params"], ca_layer_idx, x1[:n], q[:n], p[pre + "attn2.to_k.weight"], time_emb[:n],
+                                     s["probes"][ca_layer_idx], s["extra_means"][ca_layer_idx][:n], s["K"], s["r"],
+                                     infeat_size=(h, w), cached_pooler_bg_out=cached)
+        bg_cache[i] = pooled["bg_out"]
+        ctx[:n, list(s["positions"])] = vecs
+        if io is not None:
+            io.setdefault("ada_vecs", {})[(ca_layer_idx, i)] = vecs
+    x2 = x1 + cross_attention(n2, p, pre + "attn2.", ctx, None, heads)                          # :280-281
+    n3 = layer_norm(x2, p[pre + "norm3.weight"], p[pre + "norm3.bias"])
+    x3 = geglu_feedforward(n3, p, pre + "ff.") + x2                                             # :283
+    y = x3 @ p[prefix + "proj_out.weight"].reshape(c, c).t() + p[prefix + "proj_out.bias"]      # :335-340
+    return y.transpose(1, 2).reshape(b, c, h, w) + x                                            # :341
+
+
 # --------------------------------------------------------------------------------------------
 # Conv-attention rows (ldm/util.py:701-879), optional mode (use_conv_attn_kernel_size > 1)
 # --------------------------------------------------------------------------------------------
@@ -445,11 +487,16 @@ def upsample(x: Tensor, p: Params, prefix: str) -> Tensor:
 def unet_forward(p: Params, x: Tensor, timesteps: Tensor, context: Tensor, model_channels: int = 320,
                  channel_mult: Sequence[int] = (1, 2, 4, 4), num_res_blocks: int = 2,
                  attention_resolutions: Sequence[int] = (4, 2, 1), heads: int = 8,
-                 st_fn: Optional[Callable] = None, block_outputs: Optional[dict] = None) -> Tensor:
+                 st_fn: Optional[Callable] = None, block_outputs: Optional[dict] = None,
+                 ada_subjects=None, block_inputs: Optional[dict] = None) -> Tensor:
     """UNetModel.forward with use_layerwise_context=True, no conv-attn: openaimodel.py:827-1052.
 
     context: [16*B,77,768], instance-major / layer-minor (embedding_manager.py:1345-1349).
     `st_fn(x, params, prefix, layer_context)` defaults to the port's spatial_transformer.
+    `ada_subjects` (see spatial_transformer_ada) composes the per-layer AdaEmbedding call site into every conditioned
+    layer - the build's reconstruction of SURVEY.md 3.2 (F1), the workload bench.py times.  `block_inputs` /
+    `block_outputs` collect every SpatialTransformer's input / output by U-Net block index; block_outputs["emb"] is the
+    time embedding.
     """
     b = x.shape[0]
     ctx = context.reshape(b, 16, -1, context.shape[-1]).permute(1, 0, 2, 3)        # :866
@@ -460,13 +507,20 @@ def unet_forward(p: Params, x: Tensor, timesteps: Tensor, context: Tensor, model
     def run_st(h, prefix, layer_idx):
         lc = ctx[LAYER_IDX2CA[layer_idx]]
         layer_context = lambda: ((lc, lc), None)                                    # :894-896,920
+        if block_inputs is not None:
+            block_inputs[layer_idx] = h
         if st_fn is not None:
             out = st_fn(h, p, prefix, layer_context)
+        elif ada_subjects:
+            out = spatial_transformer_ada(h, p, layer_context, ada_subjects, LAYER_IDX2CA[layer_idx], emb, heads, prefix)
         else:
             out = spatial_transformer(h, p, layer_context, None, heads, prefix)
         if block_outputs is not None:
             block_outputs[layer_idx] = out
         return out
+
+    if block_outputs is not None:
+        block_outputs["emb"] = emb
 
     hs = []
     h = F.conv2d(x, p["input_blocks.0.0.weight"], p["input_blocks.0.0.bias"], padding=1)

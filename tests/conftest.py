@@ -19,7 +19,9 @@ def pytest_configure(config):
 def load_golden(name):
     path = os.path.join(GOLDEN_DIR, name + ".npz")
     if not os.path.exists(path):
-        pytest.skip(f"golden fixture {name}.npz not generated")
+        # every fixture is committed together with the script that made it (oracle/gen_golden.py): a missing one is a
+        # broken checkout, and a parity test must never turn into a silent skip
+        pytest.fail(f"golden fixture tests/golden/{name}.npz is missing (regenerate with `python -m oracle.gen_golden {name}`)")
     return np.load(path)
 
 

@@ -330,3 +330,30 @@ def test_built_library_stays_current_when_the_checkout_moves(tmp_path):
         out, err = p.communicate(timeout=600)
         assert p.returncode == 0, err[-1500:]
         assert out.strip().endswith("libadaface_b200.so")
+
+
+def test_embedding_checkpoint_reader_refuses_globals_outside_its_allow_list(tmp_path):
+    """the reader runs a pickle with weights_only=False; anything that is not a reference class, torch,
+    numpy or a plain container must be refused instead of imported."""
+    import pickle
+    from adaface_b200.checkpoint import load_embedding_checkpoint
+
+    class Evil:
+        def __reduce__(self):
+            return (os.system, ("echo pwned > /dev/null",))
+
+    path = tmp_path / "embeddings_gs-evil.pt"
+    torch.save({"string_to_static_embedder": Evil()}, str(path))
+    with pytest.raises(pickle.UnpicklingError, match="allow-list"):
+        load_embedding_checkpoint(str(path))
+
+
+def test_loader_refuses_a_library_built_against_another_header(monkeypatch):
+    """a prebuilt .so whose argument structs may differ from include/adaface_b200.h must not be loaded."""
+    from adaface_b200 import _lib, build
+    _lib.load()                                     # current library: loads
+    monkeypatch.setattr(_lib, "_LIB", None)
+    monkeypatch.setattr(build, "is_current", lambda: True)
+    monkeypatch.setattr(build, "header_digest", lambda: "0" * 64)
+    with pytest.raises(_lib.AdafaceB200Error, match="another revision"):
+        _lib.load()

@@ -538,3 +538,20 @@ def test_splice_static_embedding_vs_reference_golden(ops, cuda_device, out_dtype
     out2, _ = splice_static_embedding(emb.to(d), tok2.to(d), token, static.to(d), L, out_dtype)
     assert torch.equal(out2[L:2 * L, 74:77].cpu(), static[:, :3].to(out_dtype))
     assert torch.equal(out2[L:2 * L, :74].cpu(), emb[1, :74].expand(L, -1, -1).to(out_dtype))
+
+
+def test_ada_pool_prep_converted_inputs_stay_alive(ops, cuda_device):
+    """a bf16 to_k weight, an expanded 1-D bg query and non-contiguous lora weights all need a converted
+    copy; the copies must outlive the launch (a freed temporary could be handed to the next conversion)."""
+    d, b, c = cuda_device, 4, 640
+    lg = c // 8
+    to_k = _r("pp.tok", (c, 768), 768 ** -0.5).to(d)
+    fg, bg1 = _r("pp.fg", (768,)).to(d), _r("pp.bg", (768,)).to(d)
+    wf, wb, wk = (_r(f"pp.{n}", (lg, lg), lg ** -0.5).to(d) for n in ("wf", "wb", "wk"))
+    to_k_bf16 = to_k.to(torch.bfloat16)
+    ref = ops.ada_pool_prep(to_k_bf16.float(), fg, bg1[None].expand(b, -1).contiguous(), wf, wb, wk)
+    for _ in range(3):          # repeated: the allocator has freed blocks of matching sizes to hand out
+        out = ops.ada_pool_prep(to_k_bf16, fg.double(), bg1[None].expand(b, -1), wf.t().contiguous().t(), wb.double(), wk.half().float().t().t())
+        ref2 = ops.ada_pool_prep(to_k_bf16.float(), fg, bg1[None].expand(b, -1).contiguous(), wf, wb, wk.half().float())
+        assert torch.equal(out, ref2)
+    assert rel_l2(ref, ops.ada_pool_prep(to_k, fg, bg1[None].expand(b, -1).contiguous(), wf, wb, wk)) < 5e-3

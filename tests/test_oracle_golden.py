@@ -217,3 +217,31 @@ def test_static_layerwise_embedding_and_splice_match_reference():
     # prompt 1 holds no placeholder: untouched; prompt 0's second occurrence (position 40) is not a subject row
     assert torch.equal(spliced[L:2 * L], emb[1].expand(L, -1, -1))
     assert torch.equal(spliced[0, 40], emb[0, 40])
+
+
+def test_composed_ada_oracle_reduces_to_the_plain_block_and_reproduces_its_fixture():
+    """port.spatial_transformer_ada (the build's reconstruction of the removed AdaEmbedding call site)
+    with no subject equals port.spatial_transformer, whose parity with the reference is pinned above; with subjects it
+    changes the conditioned samples only; and the composed 10-step DDIM run reproduces its committed fixture."""
+    c, hw, b, seed = 320, 8, 3, 31
+    sd = P.init_spatial_transformer(c, seed)
+    x = P.randn("cada.x", (b, c, hw, hw), seed)
+    ctx = P.randn("cada.ctx", (b, 77, 768), seed)
+    emb = P.randn("cada.emb", (b, 1280), seed)
+    plain = port.spatial_transformer(x, sd, ctx)
+    assert rel_l2(port.spatial_transformer_ada(x, sd, ctx, [], 0, emb), plain) < 1e-6
+    subj = P.ada_subject_inputs("cada", 2, 2, seed)
+    y = port.spatial_transformer_ada(x, sd, ctx, subj, 0, emb)
+    assert rel_l2(y[2:], plain[2:]) < 1e-6 and rel_l2(y[:2], plain[:2]) > 1e-4
+    g = load_golden("ddim10_ada2_small")
+    seed, hw, steps, n_subjects = [int(v) for v in g["meta"]]
+    usd = P.init_unet(seed)
+    name = "ddim10_ada2_small"
+    x_T = P.randn(f"{name}.x_T", (1, 4, hw, hw), seed)
+    c_cond = P.randn(f"{name}.c_cond", (16, 77, 768), seed)
+    c_uncond = P.randn(f"{name}.c_uncond", (16, 77, 768), seed)
+    subjects = P.ada_subject_inputs(name, n_subjects, 1, seed)
+    with torch.no_grad():
+        out = port.ddim_sample(lambda xi, ti, ci: port.unet_forward(usd, xi, ti, ci, ada_subjects=subjects), x_T, c_cond,
+                               c_uncond, steps, (10.0, 4.0))
+    assert rel_l2(out, g["samples"]) < 1e-4
