@@ -84,6 +84,9 @@ struct AttnDev {
 #ifndef AFB_ATTN_SDOUBLE
 #define AFB_ATTN_SDOUBLE 1
 #endif
+#ifndef AFB_ATTN_HALF
+#define AFB_ATTN_HALF 0
+#endif
 
 // kSmall: the variant for a short key sequence (the 77-token context, the 8x8 image's self-attention): such a CTA is
 // one serial chain (set-up, loads, two score tiles, epilogue) with nothing to pipeline, so instead of four query tiles
@@ -101,12 +104,22 @@ struct AttnCfg {
   // ~560 cycles per 64 keys with or without the round trip (three warps per sub-partition at ~60 % MUFU and ~63 % issue
   // occupancy, i.e. bound by the exponentials' instruction stream, not by the MMA latency), plus an 8 % tail from
   // 11 CTAs of 384 rows per head (1408 CTAs = 9.5 waves).  AFB_ATTN_SDOUBLE=2 builds it for d = 40 as well.
-  static constexpr bool kSDouble = AFB_ATTN_SDOUBLE != 0 && kPTmem && !kSmall && D <= 80 && (D > 40 || AFB_ATTN_SDOUBLE >= 2);
-  static constexpr int kQTiles = kSmall ? 1 : ((D <= 40) ? (kSDouble ? 3 : 4) : 2);   // query tiles per CTA
+  // kHalf (d = 40): the two S buffers are the two 32-key HALVES of the tile's 64 score columns, so run-ahead costs no
+  // tensor memory: a round is 32 keys; while the softmax warps work on half h, the tensor pipe runs O += P V and the next
+  // scores of half 1 - h.  All four query tiles and the ones column stay (4 x (64 + 48) = 448 columns).
+  // MEASURED SLOWER (B200, 4096 x 4096, batch 16): 759 us against 560 us for the single-buffered 64-key rounds.  A
+  // tcgen05.mma of 128 x N x 16 costs ~30 clocks of the tensor pipe's issue time whatever N <= 64 is, so ten
+  // instructions per 64 keys (4 for P V, 2 x 3 for the two 32-key score halves) instead of seven take 1258 instead of 812
+  // clocks per 64 keys of the four tiles, and the softmax warps wait for the pipe (2100 instead of 800 clocks per 64
+  // keys) instead of for the round trip.  Off by default; -DAFB_ATTN_HALF=1 builds it.
+  static constexpr bool kHalf = AFB_ATTN_HALF != 0 && kPTmem && !kSmall && D <= 40 && AFB_ATTN_SDOUBLE < 2;
+  static constexpr bool kSDouble = kHalf || (AFB_ATTN_SDOUBLE != 0 && kPTmem && !kSmall && D <= 80 && (D > 40 || AFB_ATTN_SDOUBLE >= 2));
+  static constexpr int kSKeys = kHalf ? 32 : kBlockKV;          // keys per S buffer = keys per softmax round
+  static constexpr int kQTiles = kSmall ? 1 : ((D <= 40) ? ((kSDouble && !kHalf) ? 3 : 4) : 2);   // query tiles per CTA
   static constexpr int kThreads = 64 + kQTiles * 128;
   static constexpr int kAtoms = (D + 63) / 64;                 // 64-column (128-byte) swizzle atoms per row
   static constexpr int kDPadK = (D + 15) / 16 * 16;            // K extent of S = Q K^T (UMMA K step 16)
-  static constexpr bool kOnes = AFB_ATTN_ONES != 0 && D <= 40 && !kSDouble;   // d = 80 is tensor-bound: the wider P V costs more there
+  static constexpr bool kOnes = AFB_ATTN_ONES != 0 && D <= 40 && (!kSDouble || kHalf);   // d = 80 is tensor-bound: the wider P V costs more there
   static_assert(D % 8 == 0, "head dim");
   static constexpr int kDPadN = kOnes ? D + 8 : D;             // N extent of O += P V (UMMA N step 8); column D = row sum
   static constexpr int kQTileBytes = kAtoms * kBlockQ * 128;   // one query tile: atom a at a * 16 KB
@@ -124,7 +137,7 @@ struct AttnCfg {
   static constexpr int kPolyEvery = (D <= 40) ? AFB_ATTN_POLY_EVERY : (D <= 80 ? AFB_ATTN_POLY_EVERY_80 : 0);          // every kPolyEvery-th pair of exponentials on the FMA pipe
   static constexpr int kSmemBytes =
       kQTiles * (kQTileBytes + ((kSmall && kPTmem) ? 0 : kPBytes)) + kStages * 2 * kKVTileBytes;
-  static constexpr int kSStride = kSDouble ? 2 * kBlockKV : kBlockKV;     // TMEM columns of one tile's S buffer(s)
+  static constexpr int kSStride = kSDouble ? 2 * kSKeys : kBlockKV;       // TMEM columns of one tile's S buffer(s)
   static constexpr int kTmemNeed = kQTiles * (kSStride + kDPadN);
   // the full-size CTA owns all of TMEM (one per SM); a small one takes the power of two that holds its S and O
   static constexpr int kTmemCols = !kSmall ? 512 : (kTmemNeed <= 128 ? 128 : (kTmemNeed <= 256 ? 256 : 512));
@@ -260,18 +273,22 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     // tcgen05 instructions.  Converged control flow lets the descriptors live in uniform registers and avoids the
     // per-instruction election loop the compiler emits around tcgen05.mma in divergent code.
     {
-      constexpr uint32_t idesc_qk = umma_idesc_bf16(kBlockQ, BKV, 0, 0);
+      constexpr int BS = C::kSKeys;                         // keys per round
+      constexpr int H = BKV / BS;                           // rounds per K/V tile
+      constexpr uint32_t idesc_qk = umma_idesc_bf16(kBlockQ, BS, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(kBlockQ, C::kDPadN, 0, 1);   // B (= V) is MN-major
       const uint64_t q_desc0 = umma_desc_kmajor_sw128(smem_u32(sQ));
       const uint32_t p_addr = smem_u32(sP);
       const bool leader = elect_one();
       // S_t = Q_t K_j^T : K-steps of 16 over the (padded) head dim
-      auto issue_qk = [&](int t, int stage, int buf = 0) {
+      auto issue_qk = [&](int t, int stage, int buf = 0, int half = 0) {
         if (leader) {
           // one descriptor per operand tile; the K-step offsets are added to its 16-byte address field
-          const uint64_t kd = umma_desc_kmajor_sw128(smem_u32(sK + stage * C::kKVTileBytes));
+          // (half: keys [half * BS, half * BS + BS) of the tile = rows of the K-major K tile, 128 bytes each)
+          const uint64_t kd = umma_desc_kmajor_sw128(smem_u32(sK + stage * C::kKVTileBytes)) +
+                              static_cast<uint64_t>((half * BS * 128) >> 4);
           const uint64_t qd = q_desc0 + static_cast<uint64_t>(t * (C::kQTileBytes >> 4));
-          const uint32_t tmem_s = tmem_base + C::kTmemS + t * C::kSStride + buf * BKV;
+          const uint32_t tmem_s = tmem_base + C::kTmemS + t * C::kSStride + buf * BS;
 #pragma unroll
           for (int kk = 0; kk < C::kDPadK / 16; ++kk) {
             const uint64_t qoff = static_cast<uint64_t>(((kk >> 2) * (kBlockQ * 128) + (kk & 3) * 32) >> 4);
@@ -282,16 +299,16 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         }
       };
       // O_t += P_t V_j : K-steps of 16 keys; V tile is [key][64 cols] per atom -> MN-major, LBO = atom stride
-      auto issue_pv = [&](int t, int stage, bool first, bool last, int buf = 0) {
+      auto issue_pv = [&](int t, int stage, bool first, bool last, int buf = 0, int half = 0) {
         if (leader) {
           const uint64_t vd = umma_desc_mnmajor_sw128(smem_u32(sV + stage * C::kKVTileBytes), BKV * 128);
           const uint32_t tmem_o = tmem_base + C::kTmemO + t * C::kDPadN;
 #pragma unroll
-          for (int kk = 0; kk < BKV / 16; ++kk) {
-            const uint64_t voff = static_cast<uint64_t>((kk * (16 * 128)) >> 4);
+          for (int kk = 0; kk < BS / 16; ++kk) {
+            const uint64_t voff = static_cast<uint64_t>(((half * (BS / 16) + kk) * (16 * 128)) >> 4);
             if constexpr (C::kPTmem) {
               // A = P_t from TMEM: 16 keys = 8 columns of packed bf16 pairs, same lanes as the S rows
-              umma_ts(tmem_o, tmem_base + C::kTmemS + t * C::kSStride + buf * BKV + kk * 8, vd + voff, idesc_pv,
+              umma_ts(tmem_o, tmem_base + C::kTmemS + t * C::kSStride + buf * BS + kk * 8, vd + voff, idesc_pv,
                       !(first && kk == 0));
             } else {
               const uint32_t pa = p_addr + t * C::kPBytes + kk * 32;
@@ -314,30 +331,47 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
       for (int t = 0; t < n_tiles; ++t) issue_qk(t, 0);
-      if (leader) umma_commit(&k_empty[0]);
+      if (H == 1 && leader) umma_commit(&k_empty[0]);      // half rounds: K tile 0 also feeds S(1), released below
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t all = (1u << n_tiles) - 1u;
       if constexpr (C::kSDouble) {
-        // Run-ahead schedule: S(0) and S(1) of every tile up front; in round j, when tile t publishes P_t(j) (in S
-        // buffer j & 1): O_t += P_t(j) V_j, then S_t(j+2) = Q_t K_{j+2}^T into that same buffer (the tensor pipe keeps
-        // issue order, so the overwrite lands behind the read).  The softmax of round j+1 never waits for an MMA.
-        static_assert(NS >= 3, "K ring: tiles j+1 and j+2 are live while j+3 loads");
-        if (num_kv_tiles > 1) {
-          mbar_wait(&k_full[1], 0);
-          tc_fence_after();
-          for (int t = 0; t < n_tiles; ++t) issue_qk(t, 1, 1);
-          if (leader) umma_commit(&k_empty[1]);
+        // Run-ahead schedule over ROUNDS of BS keys (H rounds per K/V tile): S(0) and S(1) of every tile up front; in
+        // round r, when tile t publishes P_t(r) (in S buffer r & 1): O_t += P_t(r) V(r), then S_t(r+2) into that same
+        // buffer (the tensor pipe keeps issue order, so the overwrite lands behind the read).  The softmax of round r+1
+        // never waits for an MMA.
+        static_assert(NS >= 3, "K ring: the tiles of rounds r+1 and r+2 are live while the next one loads");
+        const int num_rounds = (p.kv_len + BS - 1) / BS;
+        if (num_rounds > 1) {
+          if (H == 1) {
+            mbar_wait(&k_full[1], 0);
+            tc_fence_after();
+          }
+          for (int t = 0; t < n_tiles; ++t) issue_qk(t, H == 1 ? 1 : 0, 1, H == 1 ? 0 : 1);
+          if (H == 1 && leader) umma_commit(&k_empty[1]);
         }
-        for (int j = 0; j < num_kv_tiles; ++j) {
-          const int st = j % NS, st2 = (j + 2) % NS;
-          const bool more = j + 2 < num_kv_tiles;
+        if (H == 2 && leader) umma_commit(&k_empty[0]);      // (H == 1: committed above, after S(0))
+        for (int r = 0; r < num_rounds; ++r) {
+          const int j = r / H, h = r % H, st = j % NS;
+          const int r2 = r + 2, j2 = r2 / H, h2 = r2 % H, st2 = j2 % NS;
+          const bool more = r2 < num_rounds;
           AFB_PROF(3);
-          if (more) mbar_wait(&k_full[st2], ((j + 2) / NS) & 1);
-          mbar_wait(&v_full[st], (j / NS) & 1);
+          if (more && h2 == 0) mbar_wait(&k_full[st2], (j2 / NS) & 1);      // first round that reads K tile j2
+          if (h == 0) {
+            mbar_wait(&v_full[st], (j / NS) & 1);
+            if constexpr (C::kOnes) {
+              // ones into column D of the V tile (atom D / 64, 16-byte chunk (D % 64) / 8 at its swizzled position)
+              uint8_t* vt = sV + st * C::kKVTileBytes + (D / 64) * (BKV * 128);
+#pragma unroll
+              for (int k = lane; k < BKV; k += 32)
+                *reinterpret_cast<uint16_t*>(vt + k * 128 + (((((D % 64) / 8) ^ (k & 7))) << 4)) = 0x3F80;   // bf16 1.0
+              fence_proxy_async_smem();
+              __syncwarp();
+            }
+          }
           AFB_PROF(0);
-          const int buf = j & 1;
-          const uint32_t par = (j >> 1) & 1;
+          const int buf = r & 1;
+          const uint32_t par = (r >> 1) & 1;
           uint32_t pending = all;
           while (pending != 0u) {
 #pragma unroll
@@ -346,8 +380,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
                 if (__all_sync(0xffffffffu, mbar_test_wait(&p_ready[2 * t + buf], par))) {
                   AFB_PROF(1);
                   tc_fence_after();
-                  issue_pv(t, st, j == 0, j + 1 == num_kv_tiles, buf);
-                  if (more) issue_qk(t, st2, buf);
+                  issue_pv(t, st, r == 0, r + 1 == num_rounds, buf, h);
+                  if (more) issue_qk(t, st2, buf, h2);
                   pending &= ~(1u << t);
                   AFB_PROF(2);
                 }
@@ -355,8 +389,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
             }
           }
           if (leader) {
-            umma_commit(&v_empty[st]);
-            if (more) umma_commit(&k_empty[st2]);
+            if (h == H - 1 || r + 1 == num_rounds) umma_commit(&v_empty[st]);                    // last round on V tile j
+            if (more && (h2 == H - 1 || r2 + 1 == num_rounds)) umma_commit(&k_empty[st2]);      // last scores from K tile j2
           }
         }
       } else
@@ -482,16 +516,18 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       while (clock64() - t0 < static_cast<long long>(t) * AFB_ATTN_STAGGER) {}
     }
 #endif
-    for (int j = 0; j < num_kv_tiles; ++j) {
+    constexpr int BS = C::kSKeys;                         // keys per round (32: half rounds, else 64)
+    const int num_rounds = (p.kv_len + BS - 1) / BS;
+    for (int j = 0; j < num_rounds; ++j) {                // j counts ROUNDS of BS keys
       AFB_PROF(7);
       const int sbuf = C::kSDouble ? (j & 1) : 0;
-      const uint32_t tmem_s = tmem_s0 + sbuf * BKV;
+      const uint32_t tmem_s = tmem_s0 + sbuf * BS;
       mbar_wait(&s_full[2 * t + sbuf], C::kSDouble ? ((j >> 1) & 1) : (j & 1));
       tc_fence_after();
       AFB_PROF(0);                                        // wait for S
-      uint32_t r[BKV];
+      uint32_t r[BS];
 #pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) tmem_ld32p(tmem_s + c * 32, &r[c * 32]);
+      for (int c = 0; c < BS / 32; ++c) tmem_ld32p(tmem_s + c * 32, &r[c * 32]);
       tmem_ld_wait();
       if constexpr (!C::kPTmem) {
         tc_fence_before();
@@ -500,28 +536,28 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       }
       AFB_PROF(1);                                        // TMEM load
 
-      const int kv0 = j * BKV;
+      const int kv0 = j * BS;
       if (kHasMask) {
         // masked keys get a large finite negative IN THE SCALED DOMAIN (like the reference's masked_fill after the
         // scaling): a fully masked row then cancels exactly to exp2(0) and averages uniformly
 #pragma unroll
-        for (int i = 0; i < BKV; ++i) {
+        for (int i = 0; i < BS; ++i) {
           float v = __uint_as_float(r[i]) * sc;
           if (kv0 + i < p.kv_len && mask_row[kv0 + i] == 0) v = kMaskedScore;
           r[i] = __float_as_uint(v);
         }
       }
-      if (kv0 + BKV > p.kv_len) {
+      if (kv0 + BS > p.kv_len) {
 #pragma unroll
-        for (int i = 0; i < BKV; ++i)
+        for (int i = 0; i < BS; ++i)
           if (kv0 + i >= p.kv_len) r[i] = 0xff800000u;    // -inf
       }
       float mx[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
 #pragma unroll
-      for (int i = 4; i < BKV; i += 8) {
+      for (int i = 4; i < BS; i += 8) {
 #pragma unroll
         for (int c = 0; c < 4; ++c)
-          if (i + 2 * c + 1 < BKV)
+          if (i + 2 * c + 1 < BS)
             mx[c] = fmax3(mx[c], __uint_as_float(r[i + 2 * c]), __uint_as_float(r[i + 2 * c + 1]));
       }
       const float m_raw = fmaxf(fmax3(mx[0], mx[1], mx[2]), mx[3]);
@@ -559,7 +595,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       const uint64_t nm2 = pack_f32x2(-m_used, -m_used);
       uint64_t acc0 = 0ull, acc1 = 0ull;                 // two packed partial sums
 #pragma unroll
-      for (int i = 0; i < BKV / 2; ++i) {
+      for (int i = 0; i < BS / 2; ++i) {
         uint64_t x = pack_f32x2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
         x = kHasMask ? fadd2(x, nm2) : ffma2(x, sc2, nm2);
         float lo, hi;
@@ -586,8 +622,15 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       AFB_PROF(4);                                        // exponentials
 
       if constexpr (C::kPTmem) {
-        // P_j (bf16 pairs, 32 columns) over the first half of this row's S_j columns
-        tmem_st32p(tmem_s, r);
+        // P_j (bf16 pairs, BS / 2 columns) over the first half of this round's S columns
+        if constexpr (BS == 64) {
+          tmem_st32p(tmem_s, r);
+        } else {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = r[i];
+          tmem_st16(tmem_s, pk);
+        }
         tmem_st_wait();
       } else {
         // the P buffer is free once O += P_{j-1} V_{j-1} has completed (long ago in steady state)

@@ -1,0 +1,819 @@
+// Backward kernels of the inversion step (BASELINE.json configs[3]): gradients flow from the block output back through
+// the GEGLU feed-forward, the 77-token cross-attention and its key / value projections into the AdaEmbedding head and
+// the attentional pooler, whose parameters are the only trainable tensors (the U-Net is frozen).
+//
+// The reference has no backward code of its own: torch autograd differentiates the modules of
+// ldm/modules/attention.py (:32-59 GEGLU, :195-243 attention, :269-283 LayerNorm) and
+// ldm/modules/embedding_manager.py (:146-321 AttentionalPooler, :847-893 AdaEmbedding head) under
+// ddpm.py:599 (manual_backward).  Each kernel below is the analytic derivative of the forward kernel it pairs with
+// (gemm.cu GEGLU / LayerNorm-fold epilogues, attention.cu, ada.cu); matrix products against frozen weights reuse the
+// forward GEMM (dA = dC W), so no weight-gradient GEMM exists on the path.
+#include "common.cuh"
+#include "../../include/adaface_b200.h"
+
+namespace afb {
+void count_launch();
+namespace {
+
+constexpr int kHeads = 8;
+constexpr float kInvSqrt8 = 0.35355339059327373f;
+
+__device__ __forceinline__ void unpack8f(const uint4& u, float (&v)[8]) {
+  const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8f(const float (&v)[8]) {
+  return make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+}
+
+__device__ __forceinline__ float block_sum_t(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.f;
+  if (warp == 0) {
+    t = warp_sum(t);
+    if (lane == 0) red[0] = t;
+  }
+  __syncthreads();
+  return red[0];
+}
+
+// ---- GEGLU backward (attention.py:32-39): out = a * gelu(g) with (a, g) the halves of h = proj(x).
+// h is given in the INTERLEAVED column order of the forward GEMM (32 value columns, their 32 gate columns, ...), and dh
+// is produced in the same order, so the dX GEMM that follows multiplies by the same interleaved weight.
+// Thread = 8 output columns.  gelu'(g) = Phi(g) + g phi(g) (exact erf form, like the forward).
+__global__ void __launch_bounds__(256) geglu_bwd_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ dout,
+                                                        __nv_bfloat16* __restrict__ dh, long long rows, int H) {
+  const long long vecs_per_row = H >> 3;
+  const long long total = rows * vecs_per_row;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long m = i / vecs_per_row;
+    const int j0 = static_cast<int>(i % vecs_per_row) * 8;       // first output column
+    const int blk = j0 >> 5, off = j0 & 31;
+    const long long hrow = m * 2 * H + static_cast<long long>(blk) * 64;
+    float a[8], g[8], d[8], da[8], dg[8];
+    unpack8f(*reinterpret_cast<const uint4*>(h + hrow + off), a);
+    unpack8f(*reinterpret_cast<const uint4*>(h + hrow + 32 + off), g);
+    unpack8f(*reinterpret_cast<const uint4*>(dout + m * H + j0), d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float x = g[k];
+      const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
+      const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
+      da[k] = d[k] * x * cdf;
+      dg[k] = d[k] * a[k] * (cdf + x * pdf);
+    }
+    *reinterpret_cast<uint4*>(dh + hrow + off) = pack8f(da);
+    *reinterpret_cast<uint4*>(dh + hrow + 32 + off) = pack8f(dg);
+  }
+}
+
+// ---- LayerNorm backward without affine (the affine part is folded into the consumer's weight, attention.py:269-283):
+// a_hat = (a - mean) * rstd; da = rstd * (g - mean(g) - a_hat * mean(g * a_hat)) (+ add: the gradient that reaches `a`
+// along the residual stream).  One warp per row, the row in registers (C <= 8 * 32 * kMaxChunks).
+template <int kMaxChunks>
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ g,
+                                                            const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ da,
+                                                            long long rows, int C, float eps) {
+  const long long row = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nchunks = C >> 3;
+  const uint4* ar = reinterpret_cast<const uint4*>(a + row * C);
+  const uint4* gr = reinterpret_cast<const uint4*>(g + row * C);
+  float av[kMaxChunks][8], gv[kMaxChunks][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int ch = lane + 32 * i;
+    if (ch < nchunks) {
+      unpack8f(ar[ch], av[i]);
+      unpack8f(gr[ch], gv[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += av[i][j];
+    }
+  }
+  const float mean = warp_sum(s) / C;
+  float m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i)
+    if (lane + 32 * i < nchunks)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = av[i][j] - mean;
+        m2 += d * d;
+      }
+  const float rstd = rsqrtf(warp_sum(m2) / C + eps);
+  float sg = 0.f, sga = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i)
+    if (lane + 32 * i < nchunks)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        av[i][j] = (av[i][j] - mean) * rstd;
+        sg += gv[i][j];
+        sga += gv[i][j] * av[i][j];
+      }
+  const float mg = warp_sum(sg) / C, mga = warp_sum(sga) / C;
+  uint4* outr = reinterpret_cast<uint4*>(da + row * C);
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int ch = lane + 32 * i;
+    if (ch < nchunks) {
+      float o[8], r[8];
+      if (add != nullptr) unpack8f(reinterpret_cast<const uint4*>(add + row * C)[ch], r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = rstd * (gv[i][j] - mg - av[i][j] * mga) + (add != nullptr ? r[j] : 0.f);
+      outr[ch] = pack8f(o);
+    }
+  }
+}
+
+// ---- attention backward for a short key sequence (the 77-token context, attention.py:195-243):
+// S = scale q k^T, P = softmax(S), O = P v;  dV = P^T dO, dP = dO v^T, dS = P * (dP - rowsum(P * dP)),
+// dQ = scale dS k, dK = scale dS^T q.  Block (row chunk, head, sample): K and V of the head live in shared memory as
+// fp32, the block walks its query rows in tiles of 32 rows: scores and probabilities of the tile in shared memory, dQ
+// written per tile, dK / dV accumulated in registers (thread = fixed (key, channel) outputs) over all tiles of the
+// block and added to global memory once at the end (fp32 atomics: dk / dv must be zero on entry).
+constexpr int kAbRows = 32;          // query rows per tile
+constexpr int kAbThreads = 256;
+constexpr int kAbMaxKeys = 128;
+
+template <int D>
+__global__ void __launch_bounds__(kAbThreads) attn_bwd_short_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
+    const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv,
+    int q_len, int kv_len, long long ldq, long long ldk, long long ldv, long long ldo, long long lddq, long long lddk,
+    float scale, int tiles_per_block) {
+  extern __shared__ float sh[];
+  constexpr int DP = D + 1;                                  // padded row: conflict-free column walks
+  const int T = kv_len;
+  float* sK = sh;                                            // [T][DP]
+  float* sV = sK + T * DP;                                   // [T][DP]
+  float* sQ = sV + T * DP;                                   // [32][DP]
+  float* sO = sQ + kAbRows * DP;                             // [32][DP]  dO tile
+  float* sP = sO + kAbRows * DP;                             // [32][T+1] probabilities
+  float* sS = sP + kAbRows * (T + 1);                        // [32][T+1] dS (scaled)
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int col0 = head * D;
+  const int tid = threadIdx.x;
+  for (int idx = tid; idx < T * D; idx += kAbThreads) {
+    const int t = idx / D, i = idx - t * D;
+    sK[t * DP + i] = __bfloat162float(k[(static_cast<long long>(b) * T + t) * ldk + col0 + i]);
+    sV[t * DP + i] = __bfloat162float(v[(static_cast<long long>(b) * T + t) * ldv + col0 + i]);
+  }
+  // outputs owned by this thread for dK / dV: (t, i) pairs idx = tid + n * kAbThreads
+  constexpr int kMaxT = D >= 160 ? 80 : kAbMaxKeys;            // bounds the per-thread accumulators (d = 160: 77 keys)
+  constexpr int kOwnMax = (kMaxT * D + kAbThreads - 1) / kAbThreads;
+  float acc_k[kOwnMax], acc_v[kOwnMax];
+#pragma unroll
+  for (int n = 0; n < kOwnMax; ++n) acc_k[n] = acc_v[n] = 0.f;
+  const int n_own = (T * D + kAbThreads - 1) / kAbThreads;
+
+  const int tile0 = blockIdx.x * tiles_per_block;
+  for (int tile = tile0; tile < tile0 + tiles_per_block; ++tile) {
+    const int r0 = tile * kAbRows;
+    if (r0 >= q_len) break;
+    __syncthreads();
+    for (int idx = tid; idx < kAbRows * D; idx += kAbThreads) {
+      const int r = idx / D, i = idx - r * D;
+      const int row = r0 + r;
+      float qv = 0.f, ov = 0.f;
+      if (row < q_len) {
+        qv = __bfloat162float(q[(static_cast<long long>(b) * q_len + row) * ldq + col0 + i]);
+        ov = __bfloat162float(dout[(static_cast<long long>(b) * q_len + row) * ldo + col0 + i]);
+      }
+      sQ[r * DP + i] = qv;
+      sO[r * DP + i] = ov;
+    }
+    __syncthreads();
+    // scores and dP: thread (r = tid % 32, keys t = tid / 32 + 8 n)
+    {
+      const int r = tid & 31;
+      for (int t = tid >> 5; t < T; t += kAbThreads / 32) {
+        float s = 0.f, dp = 0.f;
+#pragma unroll 8
+        for (int i = 0; i < D; ++i) {
+          s = fmaf(sQ[r * DP + i], sK[t * DP + i], s);
+          dp = fmaf(sO[r * DP + i], sV[t * DP + i], dp);
+        }
+        sP[r * (T + 1) + t] = s * scale;
+        sS[r * (T + 1) + t] = dp;
+      }
+    }
+    __syncthreads();
+    // softmax and dS per row: one warp handles 4 rows
+    {
+      const int warp = tid >> 5, lane = tid & 31;
+      for (int r = warp; r < kAbRows; r += kAbThreads / 32) {
+        float mx = -INFINITY;
+        for (int t = lane; t < T; t += 32) mx = fmaxf(mx, sP[r * (T + 1) + t]);
+        mx = warp_max(mx);
+        float l = 0.f;
+        for (int t = lane; t < T; t += 32) {
+          const float e = __expf(sP[r * (T + 1) + t] - mx);
+          sP[r * (T + 1) + t] = e;
+          l += e;
+        }
+        l = warp_sum(l);
+        const float inv = 1.0f / l;
+        float delta = 0.f;
+        for (int t = lane; t < T; t += 32) {
+          const float pr = sP[r * (T + 1) + t] * inv;
+          sP[r * (T + 1) + t] = pr;
+          delta += pr * sS[r * (T + 1) + t];
+        }
+        delta = warp_sum(delta);
+        const bool live = r0 + r < q_len;
+        for (int t = lane; t < T; t += 32) {
+          const float pr = sP[r * (T + 1) + t];
+          sS[r * (T + 1) + t] = live ? pr * (sS[r * (T + 1) + t] - delta) * scale : 0.f;
+          if (!live) sP[r * (T + 1) + t] = 0.f;
+        }
+      }
+    }
+    __syncthreads();
+    // dQ[r][i] = sum_t dS[r][t] k[t][i]
+    if (dq != nullptr) {
+      for (int idx = tid; idx < kAbRows * D; idx += kAbThreads) {
+        const int r = idx / D, i = idx - r * D;
+        if (r0 + r < q_len) {
+          float a = 0.f;
+          for (int t = 0; t < T; ++t) a = fmaf(sS[r * (T + 1) + t], sK[t * DP + i], a);
+          dq[(static_cast<long long>(b) * q_len + r0 + r) * lddq + col0 + i] = __float2bfloat16_rn(a);
+        }
+      }
+    }
+    // dK[t][i] += sum_r dS[r][t] q[r][i];  dV[t][i] += sum_r P[r][t] dO[r][i]
+#pragma unroll
+    for (int n = 0; n < kOwnMax; ++n) {
+      if (n < n_own) {
+        const int idx = tid + n * kAbThreads;
+        if (idx < T * D) {
+          const int t = idx / D, i = idx - t * D;
+          float ak = 0.f, av = 0.f;
+#pragma unroll 8
+          for (int r = 0; r < kAbRows; ++r) {
+            ak = fmaf(sS[r * (T + 1) + t], sQ[r * DP + i], ak);
+            av = fmaf(sP[r * (T + 1) + t], sO[r * DP + i], av);
+          }
+          acc_k[n] += ak;
+          acc_v[n] += av;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int n = 0; n < kOwnMax; ++n) {
+    if (n < n_own) {
+      const int idx = tid + n * kAbThreads;
+      if (idx < T * D) {
+        const int t = idx / D, i = idx - t * D;
+        const long long o = (static_cast<long long>(b) * T + t) * lddk + col0 + i;
+        atomicAdd(dk + o, acc_k[n]);
+        atomicAdd(dv + o, acc_v[n]);
+      }
+    }
+  }
+}
+
+// ---- AdaEmbedding head backward (embedding_manager.py:847-893), block (k, b) like the forward kernel:
+// recomputes feat = LNCat3(fg, bg, time), coeffs, vec and its LayerNorm, then
+//   dbias[k] += g;  dvec = LN'(g / sqrt(D));  dbasis[k, r] += coeffs[r] dvec;  dcoeffs[r] = <basis[k, r], dvec>;
+//   dcoeff_b[k, r] += dcoeffs[r];  dcoeff_w[k, r, :] += dcoeffs[r] feat;  dfeat[b, :] += sum_r dcoeffs[r] coeff_w[k, r, :]
+// (all sums over the batch and, for dfeat, over k go through fp32 atomics: the gradient buffers must be zero on entry).
+__global__ void __launch_bounds__(256) ada_head_bwd_kernel(
+    const float* __restrict__ infeat_fg, const float* __restrict__ infeat_bg, const float* __restrict__ time_emb, int time_ld,
+    const float* __restrict__ coeff_w, const float* __restrict__ coeff_b, const float* __restrict__ basis,
+    const float* __restrict__ gout, float* __restrict__ d_coeff_w, float* __restrict__ d_coeff_b, float* __restrict__ d_basis,
+    float* __restrict__ d_bias, float* __restrict__ d_feat, int C, int TD, int K, int R, int D) {
+  extern __shared__ float sh[];    // feat [F], coeffs [R4], dcoeffs [R4], vec [D], dvec [D]
+  __shared__ float red[32];
+  const int k = blockIdx.x, b = blockIdx.y;
+  const int F = 2 * C + TD, R4 = (R + 3) & ~3;
+  float* feat = sh;
+  float* coeffs = feat + F;
+  float* dcoeffs = coeffs + R4;
+  float* vec = dcoeffs + R4;
+  float* dvec = vec + D;
+  for (int i = threadIdx.x; i < F; i += blockDim.x) {
+    float v;
+    if (i < C) v = infeat_fg[static_cast<long long>(b) * C + i];
+    else if (i < 2 * C) v = infeat_bg[static_cast<long long>(b) * C + i - C];
+    else v = time_emb[static_cast<long long>(b) * time_ld + i - 2 * C];
+    feat[i] = v;
+  }
+  __syncthreads();
+  for (int part = 0; part < 2; ++part) {
+    const int lo = part == 0 ? 0 : 2 * C, n = part == 0 ? 2 * C : TD;
+    float s = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += feat[lo + i];
+    const float mean = block_sum_t(s, red) / n;
+    float m2 = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const float d = feat[lo + i] - mean;
+      m2 += d * d;
+    }
+    const float rstd = rsqrtf(block_sum_t(m2, red) / n + 1e-5f);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) feat[lo + i] = (feat[lo + i] - mean) * rstd;
+    __syncthreads();
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int o = warp; o < R; o += nwarps) {
+    const float* w = coeff_w + static_cast<long long>(k * R + o) * F;
+    float a = 0.f;
+    for (int i = lane; i < F; i += 32) a += w[i] * feat[i];
+    a = warp_sum(a);
+    if (lane == 0) coeffs[o] = a + coeff_b[k * R + o];
+  }
+  __syncthreads();
+  const float* bk = basis + static_cast<long long>(k) * R * D;
+  float s = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float a = 0.f;
+    for (int r = 0; r < R; ++r) a += coeffs[r] * bk[static_cast<long long>(r) * D + d];
+    vec[d] = a;
+    s += a;
+  }
+  const float mean = block_sum_t(s, red) / D;
+  float m2 = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    const float dd = vec[d] - mean;
+    m2 += dd * dd;
+  }
+  const float rstd = rsqrtf(block_sum_t(m2, red) / D + 1e-5f);
+  const float inv_sqrt_d = rsqrtf(static_cast<float>(D));
+  const float* g = gout + (static_cast<long long>(b) * K + k) * D;
+  // LayerNorm backward: y = (vec - mean) rstd, out = y / sqrt(D) + bias
+  float sg = 0.f, sgy = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    const float gy = g[d] * inv_sqrt_d;
+    const float y = (vec[d] - mean) * rstd;
+    sg += gy;
+    sgy += gy * y;
+    if (d_bias != nullptr) atomicAdd(d_bias + static_cast<long long>(k) * D + d, g[d]);
+  }
+  const float mg = block_sum_t(sg, red) / D;
+  const float mgy = block_sum_t(sgy, red) / D;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    const float gy = g[d] * inv_sqrt_d;
+    const float y = (vec[d] - mean) * rstd;
+    dvec[d] = rstd * (gy - mg - y * mgy);
+  }
+  __syncthreads();
+  for (int r = warp; r < R; r += nwarps) {
+    float a = 0.f;
+    for (int d = lane; d < D; d += 32) {
+      a += bk[static_cast<long long>(r) * D + d] * dvec[d];
+      atomicAdd(d_basis + (static_cast<long long>(k) * R + r) * D + d, coeffs[r] * dvec[d]);
+    }
+    a = warp_sum(a);
+    if (lane == 0) {
+      dcoeffs[r] = a;
+      atomicAdd(d_coeff_b + k * R + r, a);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < F; i += blockDim.x) {
+    float df = 0.f;
+    for (int r = 0; r < R; ++r) {
+      const long long wi = static_cast<long long>(k * R + r) * F + i;
+      df += dcoeffs[r] * coeff_w[wi];
+      atomicAdd(d_coeff_w + wi, dcoeffs[r] * feat[i]);
+    }
+    atomicAdd(d_feat + static_cast<long long>(b) * F + i, df);
+  }
+}
+
+// LNCat3 backward for the pooled-feature part (the time slice carries no trainable parameter): block b,
+// dinfeat = rstd (df - mean(df) - a_hat mean(df a_hat)) over the 2C pooled features -> d_fg [B, C], d_bg [B, C]
+__global__ void __launch_bounds__(256) ada_lncat_bwd_kernel(const float* __restrict__ infeat_fg, const float* __restrict__ infeat_bg,
+                                                            const float* __restrict__ d_feat, float* __restrict__ d_fg,
+                                                            float* __restrict__ d_bg, int C, int F) {
+  __shared__ float red[32];
+  const int b = blockIdx.x, n = 2 * C;
+  auto in = [&](int i) { return i < C ? infeat_fg[static_cast<long long>(b) * C + i] : infeat_bg[static_cast<long long>(b) * C + i - C]; };
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s += in(i);
+  const float mean = block_sum_t(s, red) / n;
+  float m2 = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float d = in(i) - mean;
+    m2 += d * d;
+  }
+  const float rstd = rsqrtf(block_sum_t(m2, red) / n + 1e-5f);
+  float sg = 0.f, sga = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float g = d_feat[static_cast<long long>(b) * F + i], a = (in(i) - mean) * rstd;
+    sg += g;
+    sga += g * a;
+  }
+  const float mg = block_sum_t(sg, red) / n, mga = block_sum_t(sga, red) / n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float g = d_feat[static_cast<long long>(b) * F + i], a = (in(i) - mean) * rstd;
+    const float o = rstd * (g - mg - a * mga);
+    if (i < C) d_fg[static_cast<long long>(b) * C + i] = o;
+    else d_bg[static_cast<long long>(b) * C + i - C] = o;
+  }
+}
+
+// ---- AttentionalPooler backward w.r.t. the folded pooling queries u [B, 2, C] (embedding_manager.py:146-321, eval
+// semantics).  With v_t = (x_t + LN(q_t)) / sqrt(8), raw scores s_i,g[t] = <u_i, v_t>_g, smoothed
+// s' = s / 2 + mean_g(s) / 2, joint softmax p_i,g[t] over (i, t) with the forward's (max, sum) per (sample, head):
+//   dp_i,g[t] = <dout_i, v_t>_g;  ds'_i,g[t] = p (dp - Delta_g),  Delta_g = sum_{c in g} (dfg out_fg + dbg out_bg)[c];
+//   ds_i,g = ds'_i,g / 2 + mean_g'(ds'_i,g') / 2;   du_i[c] += sum_t ds_i,g(c)[t] v_t[c].
+// One warp per token, per-lane channel accumulators, block partials added to du with atomics (du zero on entry).
+// The gradients towards x and q (the layer features) are not produced: the trainable tensors are reached through u.
+constexpr int kPbThreads = 256;
+constexpr int kPbWarps = kPbThreads / 32;
+
+template <int kChunks>
+__global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
+    const uint8_t* __restrict__ key_mask, const float* __restrict__ stats, const float* __restrict__ out_fg,
+    const float* __restrict__ out_bg, const float* __restrict__ d_fg, const float* __restrict__ d_bg, float* __restrict__ du,
+    int N, int C, int tokens_per_block) {
+  extern __shared__ float sh[];
+  float* s_u = sh;                       // [2][C]
+  float* s_d = s_u + 2 * C;              // [2][C] dout
+  float* s_part = s_d + 2 * C;           // [8 warps][4][kChunks * 32]
+  __shared__ float s_delta[kHeads], s_m[kHeads], s_l[kHeads];
+  const int dg = C / kHeads;
+  const int b = blockIdx.y, blk = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) {
+    s_u[idx] = u[static_cast<long long>(b) * 2 * C + idx];
+    s_d[idx] = idx < C ? d_fg[static_cast<long long>(b) * C + idx] : d_bg[static_cast<long long>(b) * C + idx - C];
+  }
+  if (threadIdx.x < kHeads) {
+    s_m[threadIdx.x] = stats[(static_cast<long long>(b) * kHeads + threadIdx.x) * 2];
+    s_l[threadIdx.x] = stats[(static_cast<long long>(b) * kHeads + threadIdx.x) * 2 + 1];
+  }
+  __syncthreads();
+  if (warp < kHeads) {                   // Delta_g
+    float a = 0.f;
+    for (int c = lane; c < dg; c += 32) {
+      const int cc = warp * dg + c;
+      a += s_d[cc] * out_fg[static_cast<long long>(b) * C + cc] + s_d[C + cc] * out_bg[static_cast<long long>(b) * C + cc];
+    }
+    a = warp_sum(a);
+    if (lane == 0) s_delta[warp] = a;
+  }
+  __syncthreads();
+  const int nchunks = C >> 3;
+  const int chunks_per_group = dg >> 3;
+  float acc_fg[kChunks][8], acc_bg[kChunks][8];
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc_fg[i][j] = acc_bg[i][j] = 0.f;
+  float* my_part = s_part + warp * 4 * (kChunks * 32);
+  const int t_begin = blk * tokens_per_block;
+  const int t_end = min(N, t_begin + tokens_per_block);
+  for (int t = t_begin + warp; t < t_end; t += kPbWarps) {
+    const long long rowoff = (static_cast<long long>(b) * N + t) * C;
+    const uint4* xr = reinterpret_cast<const uint4*>(x + rowoff);
+    const uint4* qr = reinterpret_cast<const uint4*>(q + rowoff);
+    float xv[kChunks][8], qv[kChunks][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+        unpack8f(xr[ch], xv[i]);
+        unpack8f(qr[ch], qv[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += qv[i][j];
+      }
+    }
+    const float mean = warp_sum(s) / C;
+    float m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i)
+      if (lane + 32 * i < nchunks)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = qv[i][j] - mean;
+          m2 += d * d;
+        }
+    const float rstd = rsqrtf(warp_sum(m2) / C + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+        float a_fg = 0.f, a_bg = 0.f, p_fg = 0.f, p_bg = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xv[i][j] = (xv[i][j] + (qv[i][j] - mean) * rstd) * kInvSqrt8;     // v
+          a_fg += s_u[ch * 8 + j] * xv[i][j];
+          a_bg += s_u[C + ch * 8 + j] * xv[i][j];
+          p_fg += s_d[ch * 8 + j] * xv[i][j];
+          p_bg += s_d[C + ch * 8 + j] * xv[i][j];
+        }
+        my_part[ch] = a_fg;
+        my_part[kChunks * 32 + ch] = a_bg;
+        my_part[2 * kChunks * 32 + ch] = p_fg;
+        my_part[3 * kChunks * 32 + ch] = p_bg;
+      }
+    }
+    __syncwarp();
+    // lanes 0..15: (i = lane >> 3, g = lane & 7): raw score and dp of head g
+    float sc = 0.f, dp = 0.f;
+    if (lane < 16) {
+      const float* pp = my_part + (lane >> 3) * (kChunks * 32) + (lane & 7) * chunks_per_group;
+      const float* pd = pp + 2 * (kChunks * 32);
+      for (int kk = 0; kk < chunks_per_group; ++kk) {
+        sc += pp[kk];
+        dp += pd[kk];
+      }
+    }
+    __syncwarp();
+    float tot = sc;
+    tot += __shfl_xor_sync(0xffffffffu, tot, 1);
+    tot += __shfl_xor_sync(0xffffffffu, tot, 2);
+    tot += __shfl_xor_sync(0xffffffffu, tot, 4);
+    sc = 0.5f * sc + 0.5f * (tot * 0.125f);
+    const bool masked = key_mask != nullptr && key_mask[static_cast<long long>(b) * N + t] == 0;
+    const int g = lane & 7;
+    float dsp = 0.f;                                              // d s' of (i, g) held by lanes 0..15
+    if (lane < 16 && !masked) dsp = __expf(sc - s_m[g]) / s_l[g] * (dp - s_delta[g]);
+    float dtot = dsp;
+    dtot += __shfl_xor_sync(0xffffffffu, dtot, 1);
+    dtot += __shfl_xor_sync(0xffffffffu, dtot, 2);
+    dtot += __shfl_xor_sync(0xffffffffu, dtot, 4);
+    const float ds = 0.5f * dsp + 0.5f * (dtot * 0.125f);         // d s (raw score) of (i, g)
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      const bool ok = ch < nchunks;
+      const int gg = ok ? ch / chunks_per_group : 0;
+      const float f = __shfl_sync(0xffffffffu, ds, gg);
+      const float bgv = __shfl_sync(0xffffffffu, ds, 8 + gg);
+      if (ok) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          acc_fg[i][j] = fmaf(f, xv[i][j], acc_fg[i][j]);
+          acc_bg[i][j] = fmaf(bgv, xv[i][j], acc_bg[i][j]);
+        }
+      }
+    }
+  }
+  float* dub = du + static_cast<long long>(b) * 2 * C;
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i) {
+    const int ch = lane + 32 * i;
+    if (ch < nchunks)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(dub + ch * 8 + j, acc_fg[i][j]);
+        atomicAdd(dub + C + ch * 8 + j, acc_bg[i][j]);
+      }
+  }
+}
+
+// ---- backward of the pooling-query preparation (ada.cu ada_qfinish: LayerNorm of the projected query, grouped conv
+// lora_to_{fg,bg}_q, fold through lora_to_k) w.r.t. the three grouped-conv weights [C/8, C/8] (8 groups of lg x dg):
+// block (b, i): n = LN(proj_i[b]);  lq[g, o] = <W_i[g, o, :], n_g> / 8;  u[c] = 8^-1/2 sum_o lq[g, o] W_k[g, o, c - g dg]
+//   dW_k[g, o, k'] += 8^-1/2 lq[g, o] du[g dg + k'];  dlq[g, o] = 8^-1/2 <W_k[g, o, :], du_g>;  dW_i[g, o, k] += dlq[g, o] n_g[k] / 8
+// proj [B + 1, C] is the forward's workspace (row 0: the shared fg probe, row 1 + b: sample b's bg query).
+__global__ void __launch_bounds__(256) ada_prep_bwd_kernel(const float* __restrict__ proj, const float* __restrict__ w_fg,
+                                                           const float* __restrict__ w_bg, const float* __restrict__ w_k,
+                                                           const float* __restrict__ du, float* __restrict__ d_w_fg,
+                                                           float* __restrict__ d_w_bg, float* __restrict__ d_w_k, int C) {
+  extern __shared__ float sh[];      // n [C], lq [dg], dlq [dg]
+  __shared__ float red[32];
+  const int b = blockIdx.x, i = blockIdx.y;
+  const int dg = C / kHeads, lg = dg / kHeads;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  float* s_n = sh;
+  float* s_lq = sh + C;
+  float* s_dlq = s_lq + dg;
+  const float* src = proj + static_cast<long long>(i == 0 ? 0 : 1 + b) * C;
+  float s = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    s_n[c] = src[c];
+    s += src[c];
+  }
+  const float mean = block_sum_t(s, red) / C;
+  float m2 = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float d = s_n[c] - mean;
+    m2 += d * d;
+  }
+  const float rstd = rsqrtf(block_sum_t(m2, red) / C + 1e-5f);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) s_n[c] = (s_n[c] - mean) * rstd;
+  __syncthreads();
+  const float* wsel = (i == 0) ? w_fg : w_bg;
+  float* d_wsel = (i == 0) ? d_w_fg : d_w_bg;
+  const float* dub = du + (static_cast<long long>(b) * 2 + i) * C;
+  for (int j = warp; j < dg; j += nwarps) {      // j = g * lg + o
+    const int g = j / lg;
+    float a = 0.f, d = 0.f;
+    for (int k = lane; k < dg; k += 32) {
+      a += wsel[static_cast<long long>(j) * dg + k] * s_n[g * dg + k];
+      d += w_k[static_cast<long long>(j) * dg + k] * dub[g * dg + k];
+    }
+    a = warp_sum(a);
+    d = warp_sum(d);
+    if (lane == 0) {
+      s_lq[j] = a * kInvSqrt8 * kInvSqrt8;
+      s_dlq[j] = d * kInvSqrt8;
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < dg * dg; idx += blockDim.x) {
+    const int j = idx / dg, k = idx - j * dg;
+    const int g = j / lg;
+    atomicAdd(d_w_k + idx, kInvSqrt8 * s_lq[j] * dub[g * dg + k]);
+    atomicAdd(d_wsel + idx, s_dlq[j] * kInvSqrt8 * kInvSqrt8 * s_n[g * dg + k]);
+  }
+}
+
+}  // namespace
+}  // namespace afb
+
+extern "C" int afb_geglu_bwd(const afb_bf16* h, const afb_bf16* dout, afb_bf16* dh, int64_t rows, int hidden, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(h && dout && dh, "afb_geglu_bwd: NULL argument");
+  AFB_REQUIRE(rows > 0 && hidden > 0 && hidden % 32 == 0, "afb_geglu_bwd: hidden %d must be a positive multiple of 32", hidden);
+  const uintptr_t all = reinterpret_cast<uintptr_t>(h) | reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(dh);
+  AFB_REQUIRE((all & 15) == 0, "afb_geglu_bwd: buffers must be 16-byte aligned");
+  const long long total = rows * (hidden / 8);
+  const long long blocks = (total + 255) / 256;
+  const int grid = static_cast<int>(blocks < 8LL * num_sms() ? blocks : 8LL * num_sms());
+  geglu_bwd_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(h), reinterpret_cast<const __nv_bfloat16*>(dout),
+                                            reinterpret_cast<__nv_bfloat16*>(dh), rows, hidden);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_layernorm_bwd(const afb_bf16* a, const afb_bf16* g, const afb_bf16* add, afb_bf16* da, int64_t rows,
+                                 int channels, float eps, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(a && g && da, "afb_layernorm_bwd: NULL argument");
+  AFB_REQUIRE(rows > 0 && channels > 0 && channels % 8 == 0 && channels <= 8 * 32 * 5,
+              "afb_layernorm_bwd: channels %d must be a multiple of 8, <= 1280", channels);
+  const uintptr_t all = reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(add) |
+                        reinterpret_cast<uintptr_t>(da);
+  AFB_REQUIRE((all & 15) == 0, "afb_layernorm_bwd: buffers must be 16-byte aligned");
+  const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(a);
+  const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(g);
+  const __nv_bfloat16* addb = reinterpret_cast<const __nv_bfloat16*>(add);
+  __nv_bfloat16* db = reinterpret_cast<__nv_bfloat16*>(da);
+  const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+  const int cpl = (channels / 8 + 31) / 32;
+  if (cpl <= 2) layernorm_bwd_kernel<2><<<grid, 256, 0, stream>>>(ab, gb, addb, db, rows, channels, eps);
+  else if (cpl <= 3) layernorm_bwd_kernel<3><<<grid, 256, 0, stream>>>(ab, gb, addb, db, rows, channels, eps);
+  else layernorm_bwd_kernel<5><<<grid, 256, 0, stream>>>(ab, gb, addb, db, rows, channels, eps);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+namespace afb {
+namespace {
+template <int D>
+int launch_attn_bwd(const afb_attn_args& a, const __nv_bfloat16* dout, __nv_bfloat16* dq, float* dk, float* dv, long long lddq,
+                    long long lddk, cudaStream_t stream) {
+  const int T = a.kv_len;
+  const size_t sh = (2 * static_cast<size_t>(T) * (D + 1) + 2 * static_cast<size_t>(kAbRows) * (D + 1) +
+                     2 * static_cast<size_t>(kAbRows) * (T + 1)) * sizeof(float);
+  auto kern = attn_bwd_short_kernel<D>;
+  static size_t set_for = 0;
+  if (set_for < sh) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh)));
+    set_for = sh;
+  }
+  const int tiles = (a.q_len + kAbRows - 1) / kAbRows;
+  // about two waves of blocks; every block keeps its dK / dV partial in registers over its tiles
+  int chunks = (2 * num_sms() + a.batch * a.heads - 1) / (a.batch * a.heads);
+  if (chunks > tiles) chunks = tiles;
+  if (chunks < 1) chunks = 1;
+  const int tiles_per_block = (tiles + chunks - 1) / chunks;
+  dim3 grid((tiles + tiles_per_block - 1) / tiles_per_block, a.heads, a.batch);
+  kern<<<grid, kAbThreads, sh, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
+                                         reinterpret_cast<const __nv_bfloat16*>(a.v), dout, dq, dk, dv, a.q_len, a.kv_len, a.ldq,
+                                         a.ldk, a.ldv, a.ldo, lddq, lddk, a.scale, tiles_per_block);
+  return 0;
+}
+}  // namespace
+}  // namespace afb
+
+extern "C" int afb_attention_bwd_short(const afb_attn_args* args, const afb_bf16* dout, afb_bf16* dq, float* dk, float* dv,
+                                       int64_t lddq, int64_t lddk, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(args != nullptr && dout && dk && dv, "afb_attention_bwd_short: NULL argument");
+  const afb_attn_args& a = *args;
+  AFB_REQUIRE(a.q && a.k && a.v, "afb_attention_bwd_short: NULL operand");
+  AFB_REQUIRE(a.key_mask == nullptr, "afb_attention_bwd_short: key masks are a self-attention feature (not built for the backward)");
+  AFB_REQUIRE(a.batch > 0 && a.heads > 0 && a.q_len > 0 && a.kv_len > 0 && a.batch <= 65535 && a.heads <= 65535,
+              "afb_attention_bwd_short: bad sizes");
+  const int max_keys = a.head_dim >= 160 ? 80 : kAbMaxKeys;
+  AFB_REQUIRE(a.kv_len <= max_keys, "afb_attention_bwd_short: kv_len %d > %d: only the short-key (cross-attention) backward is "
+              "built; the self-attention backward is not", a.kv_len, max_keys);
+  const int width = a.heads * a.head_dim;
+  AFB_REQUIRE(a.ldq >= width && a.ldk >= width && a.ldv >= width && a.ldo >= width && lddk >= width && (dq == nullptr || lddq >= width),
+              "afb_attention_bwd_short: leading dimension smaller than heads*head_dim");
+  const __nv_bfloat16* db = reinterpret_cast<const __nv_bfloat16*>(dout);
+  __nv_bfloat16* dqb = reinterpret_cast<__nv_bfloat16*>(dq);
+  int rc;
+  switch (a.head_dim) {
+    case 40: rc = launch_attn_bwd<40>(a, db, dqb, dk, dv, lddq, lddk, stream); break;
+    case 80: rc = launch_attn_bwd<80>(a, db, dqb, dk, dv, lddq, lddk, stream); break;
+    case 160: rc = launch_attn_bwd<160>(a, db, dqb, dk, dv, lddq, lddk, stream); break;
+    default: AFB_FAIL(2, "afb_attention_bwd_short: head_dim %d not supported (SD-1.5 uses 40, 80, 160)", a.head_dim);
+  }
+  if (rc) return rc;
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_head_bwd(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
+                                const float* coeff_w, const float* coeff_b, const float* basis, const float* grad_out,
+                                float* d_coeff_w, float* d_coeff_b, float* d_basis, float* d_bias, float* d_feat_ws,
+                                float* d_infeat_fg, float* d_infeat_bg, int batch, int channels, int td, int num_vectors, int r,
+                                int out_dim, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(infeat_fg && infeat_bg && time_emb && coeff_w && coeff_b && basis && grad_out && d_coeff_w && d_coeff_b && d_basis &&
+                  d_feat_ws && d_infeat_fg && d_infeat_bg,
+              "afb_ada_head_bwd: NULL argument");
+  AFB_REQUIRE(batch > 0 && channels > 0 && td > 0 && td <= time_ld && num_vectors > 0 && r > 0 && out_dim > 0, "afb_ada_head_bwd: bad sizes");
+  const int F = 2 * channels + td;
+  const size_t sh = (static_cast<size_t>(F) + 2 * static_cast<size_t>((r + 3) & ~3) + 2 * static_cast<size_t>(out_dim)) * sizeof(float);
+  AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head_bwd: feature vector too large for one block (%zu bytes)", sh);
+  AFB_CHECK_CUDA(cudaMemsetAsync(d_feat_ws, 0, static_cast<size_t>(batch) * F * sizeof(float), stream));
+  ada_head_bwd_kernel<<<dim3(num_vectors, batch), 256, sh, stream>>>(infeat_fg, infeat_bg, time_emb, time_ld, coeff_w, coeff_b, basis,
+                                                                      grad_out, d_coeff_w, d_coeff_b, d_basis, d_bias, d_feat_ws,
+                                                                      channels, td, num_vectors, r, out_dim);
+  count_launch();
+  ada_lncat_bwd_kernel<<<batch, 256, 0, stream>>>(infeat_fg, infeat_bg, d_feat_ws, d_infeat_fg, d_infeat_bg, channels, F);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
+                                const float* stats, const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg,
+                                float* d_pool_q, int batch, int n_tokens, int channels, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(x && q && pool_q && stats && fg_out && bg_out && d_fg && d_bg && d_pool_q, "afb_ada_pool_bwd: NULL argument");
+  AFB_REQUIRE(batch > 0 && n_tokens > 0 && channels % 64 == 0 && channels <= 1280, "afb_ada_pool_bwd: bad sizes");
+  AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) & 15) == 0, "afb_ada_pool_bwd: x/q must be 16-byte aligned");
+  const int C = channels;
+  int blocks = 2 * num_sms() / batch;
+  const int max_blocks = (n_tokens + 7) / 8;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  const int tokens_per_block = (n_tokens + blocks - 1) / blocks;
+  dim3 grid((n_tokens + tokens_per_block - 1) / tokens_per_block, batch);
+  const int cpl = (C / 8 + 31) / 32;
+  AFB_CHECK_CUDA(cudaMemsetAsync(d_pool_q, 0, static_cast<size_t>(batch) * 2 * C * sizeof(float), stream));
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(q);
+#define AFB_LAUNCH_PB(KCH)                                                                                          \
+  {                                                                                                                 \
+    auto kern = ada_pool_bwd_kernel<KCH>;                                                                           \
+    const size_t shb = (4 * static_cast<size_t>(C) + kPbWarps * 4 * (KCH * 32)) * sizeof(float);                    \
+    static size_t set_for = 0;                                                                                      \
+    if (set_for < shb) {                                                                                            \
+      AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(shb))); \
+      set_for = shb;                                                                                                \
+    }                                                                                                               \
+    kern<<<grid, kPbThreads, shb, stream>>>(xb, qb, pool_q, key_mask, stats, fg_out, bg_out, d_fg, d_bg, d_pool_q, n_tokens, C, \
+                                            tokens_per_block);                                                      \
+  }
+  if (cpl <= 2) AFB_LAUNCH_PB(2)
+  else if (cpl <= 3) AFB_LAUNCH_PB(3)
+  else AFB_LAUNCH_PB(5)
+#undef AFB_LAUNCH_PB
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const float* lora_to_bg_q,
+                                     const float* lora_to_k, const float* d_pool_q, float* d_lora_to_fg_q, float* d_lora_to_bg_q,
+                                     float* d_lora_to_k, int batch, int channels, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(proj_ws && lora_to_fg_q && lora_to_bg_q && lora_to_k && d_pool_q && d_lora_to_fg_q && d_lora_to_bg_q && d_lora_to_k,
+              "afb_ada_pool_prep_bwd: NULL argument");
+  AFB_REQUIRE(batch > 0 && channels % 64 == 0 && channels <= 1280, "afb_ada_pool_prep_bwd: bad sizes");
+  const size_t sh = (static_cast<size_t>(channels) + 2 * static_cast<size_t>(channels / 8)) * sizeof(float);
+  ada_prep_bwd_kernel<<<dim3(batch, 2), 256, sh, stream>>>(proj_ws, lora_to_fg_q, lora_to_bg_q, lora_to_k, d_pool_q, d_lora_to_fg_q,
+                                                            d_lora_to_bg_q, d_lora_to_k, channels);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -589,6 +589,8 @@ def run_ours(args):
 
             # (sample_sharded slices x_T for this rank; the rank's contexts are already resident in c_d / uc_d, the CPU
             #  tensors passed along are only sliced as views)
+            from adaface_b200.sampling import all_gather_samples
+            all_gather_samples(x_d, shard_bounds(total, world))       # untimed warm-up of the collective (NCCL connects lazily)
             barrier()
             t_wall = time.perf_counter()
             e0.record()
@@ -605,10 +607,15 @@ def run_ours(args):
             value = (total / N_SAMPLES) * steps / (job_ms * 1e-3)
             scaling = "strong"
             # the gathered job equals this rank's own result on its slice
-            same = bool(torch.equal(latents[lo:hi], run_local(x_d, None, None))) if args.check_gather else None
+            # the gathered job against this rank's own re-run of its slice (GroupNorm's shared-memory atomics make two runs
+            # agree to rounding, not bit for bit)
+            same = None
+            if args.check_gather:
+                again = run_local(x_d, None, None)
+                same = float((latents[lo:hi] - again).norm() / again.norm())
             extra_keys.update({"job": {"samples": total, "ddim_steps": steps, "ms": job_ms, "allgather_ms": ag_ms,
                                        "allgather_share": ag_ms / job_ms, "allgather_bytes": total * 4 * LATENT * LATENT * 4,
-                                       "per_rank_step_ms": (job_ms - ag_ms) / steps, "gather_equals_local": same,
+                                       "per_rank_step_ms": (job_ms - ag_ms) / steps, "gather_vs_local_rel_l2": same,
                                        "sample_steps_per_s": total * steps / (job_ms * 1e-3)}})
 
             # ---- e2e: the same job from HOST buffers: x_T and both contexts copied from pinned memory at the start of
@@ -693,7 +700,10 @@ def run_ours(args):
             line["cpu_baseline"] = None
         errs = [parity[k] for k in ("oracle_rel_l2", "fixture_rel_l2") if k in parity]
         parity["checked"] = bool(errs)
-        parity["ok"] = bool(errs) and max(errs) < PARITY_BAR and finite
+        parity["ok"] = (max(errs) < PARITY_BAR and finite) if errs else None
+        if not errs:
+            parity["note"] = ("not checked in this run (the oracle leg runs at N = 1; the sharded two-subject job is pinned by "
+                              "tests/test_workload_gpu.py: ddim50_ada2, U-Net call with two subjects)")
         line["parity"] = parity
         print(json.dumps(line), file=_RESULT_OUT, flush=True)
         if errs and not parity["ok"]:

@@ -257,6 +257,42 @@ int afb_splice_static_embedding(const float* embedded_text, const int* first_pos
                                 afb_bf16* out_bf16, int batch, int n_tokens, int num_layers, int num_vectors, int dim,
                                 afb_stream_t stream);
 
+/* ---- Backward of the inversion step (BASELINE.json configs[3]: backward through cross-attention, gradients only on the
+ * AdaEmbedding parameters).  The reference has no backward code: torch autograd differentiates attention.py:32-59,
+ * 195-243, 269-283 and embedding_manager.py:146-321, 847-893 under ddpm.py:599 (manual_backward); these entry points
+ * are the analytic derivatives of the forward kernels above.  Products against the frozen weights reuse afb_gemm_bf16
+ * (dA = dC W with the transposed weight as `w`).  Gradient buffers marked "+=" are accumulated into (zero them first).
+ *
+ * afb_geglu_bwd: h bf16 [rows, 2*hidden] = the GEGLU projection in the forward GEMM's interleaved column order (32 value
+ *   columns, their 32 gate columns, ...), dout bf16 [rows, hidden] -> dh bf16 [rows, 2*hidden], same order.
+ * afb_layernorm_bwd: LayerNorm without affine (the affine part is folded into the consumer's weight): a, g = d(a_hat)
+ *   bf16 [rows, C], add = NULL or bf16 [rows, C] (gradient arriving along the residual stream) -> da bf16.
+ * afb_attention_bwd_short: kv_len <= 128 (d = 160: <= 80), no key mask - the 77-token cross-attention.  args as in
+ *   afb_attention_fwd (`out` unused), dout bf16 [B*q_len, ldo]; dq bf16 [B*q_len, lddq] or NULL; dk, dv fp32
+ *   [B*kv_len, lddk] "+=".  The self-attention backward (long key sequences) is not built: the call fails with code 2.
+ * afb_ada_head_bwd: grad_out fp32 [B, K, D] -> d_coeff_w [K*r, 2C+TD], d_coeff_b [K*r], d_basis [K, r, D], d_bias [K, D]
+ *   or NULL (all "+="), d_infeat_fg / d_infeat_bg fp32 [B, C] (written); d_feat_ws: fp32 workspace [B, 2C+TD].
+ * afb_ada_pool_bwd: gradient of the pooled features w.r.t. the folded pooling queries: stats fp32 [B, 8, 2] = the
+ *   forward's (max, sum) per (sample, head) (tail of afb_ada_pool's workspace), fg_out / bg_out the forward outputs,
+ *   d_fg / d_bg fp32 [B, C] -> d_pool_q fp32 [B, 2, C] (written).  Gradients towards x and q are not produced.
+ * afb_ada_pool_prep_bwd: proj_ws = the forward's workspace (fp32 [(B+1), C]) -> d_lora_to_fg_q, d_lora_to_bg_q,
+ *   d_lora_to_k fp32 [C/8, C/8] ("+="). */
+int afb_geglu_bwd(const afb_bf16* h, const afb_bf16* dout, afb_bf16* dh, int64_t rows, int hidden, afb_stream_t stream);
+int afb_layernorm_bwd(const afb_bf16* a, const afb_bf16* g, const afb_bf16* add, afb_bf16* da, int64_t rows, int channels,
+                      float eps, afb_stream_t stream);
+int afb_attention_bwd_short(const afb_attn_args* args, const afb_bf16* dout, afb_bf16* dq, float* dk, float* dv, int64_t lddq,
+                            int64_t lddk, afb_stream_t stream);
+int afb_ada_head_bwd(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld, const float* coeff_w,
+                     const float* coeff_b, const float* basis, const float* grad_out, float* d_coeff_w, float* d_coeff_b,
+                     float* d_basis, float* d_bias, float* d_feat_ws, float* d_infeat_fg, float* d_infeat_bg, int batch,
+                     int channels, int td, int num_vectors, int r, int out_dim, afb_stream_t stream);
+int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, const float* stats,
+                     const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg, float* d_pool_q, int batch,
+                     int n_tokens, int channels, afb_stream_t stream);
+int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k,
+                          const float* d_pool_q, float* d_lora_to_fg_q, float* d_lora_to_bg_q, float* d_lora_to_k, int batch,
+                          int channels, afb_stream_t stream);
+
 /* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */
 int afb_cast_f32_to_bf16(const float* src, afb_bf16* dst, int64_t n, afb_stream_t stream);
 int afb_cast_bf16_to_f32(const afb_bf16* src, float* dst, int64_t n, afb_stream_t stream);
