@@ -61,9 +61,19 @@ class AttentionalPooler(nn.Module, _PackedWeights):
     def _build_pack(self):
         return {k: _f32(getattr(self, k).weight.squeeze(-1)) for k in ("lora_to_k", "lora_to_fg_q", "lora_to_bg_q")}
 
+    def _differentiated(self) -> bool:
+        """True inside an inversion step: gradients are being recorded and this pooler's grouped-conv weights train."""
+        return torch.is_grad_enabled() and any(getattr(self, k).weight.requires_grad
+                                               for k in ("lora_to_k", "lora_to_fg_q", "lora_to_bg_q"))
+
     def prepare_queries(self, to_k: nn.Module, fg_q_emb: Tensor, bg_q_emb: Tensor, batch: int) -> Tensor:
         """fg / bg pooling queries [B, 2, C] folded through lora_to_k (embedding_manager.py:186-235, :227)."""
-        p = self.packed()
+        if self._differentiated():
+            # the parameters themselves (views, not the detached kernel-layout copies): autograd routes the gradients of
+            # ops.ada_pool_prep (ops.ada_pool_prep_bwd) to them
+            p = {k: getattr(self, k).weight.squeeze(-1) for k in ("lora_to_k", "lora_to_fg_q", "lora_to_bg_q")}
+        else:
+            p = self.packed()
         if bg_q_emb.dim() == 1:
             bg_q_emb = bg_q_emb[None].expand(batch, -1)
         return ops.ada_pool_prep(to_k.weight.detach(), fg_q_emb.reshape(-1), bg_q_emb.reshape(batch, -1),
@@ -87,6 +97,10 @@ class AttentionalPooler(nn.Module, _PackedWeights):
         if img_mask is not None:                                                                # :259-269
             m = F.interpolate(img_mask.float(), size=infeat_size, mode="nearest").reshape(b, -1)
             key_mask = m.bool().to(torch.uint8).contiguous()
+        if self._differentiated():
+            # the pooler differentiates w.r.t. its queries; the gradient towards the layer features is not built, so the
+            # features enter as constants (the reference scales that gradient path by infeat_grad_scale, :128-131)
+            x, q = x.detach(), q.detach()
         fg, bg, a_fg, a_bg = ops.ada_pool(as_bf16_tokens(x), as_bf16_tokens(q), pool_q, key_mask, want_attn)
         out = {"fg_out": fg, "bg_out": bg}
         if want_attn:
@@ -224,6 +238,22 @@ class AdaEmbedding(nn.Module, _PackedWeights):
                                   img_mask=img_mask, want_attn=getattr(self, "want_pooler_attn", True))   # :815-819
         infeat_fg = pooled.pop("fg_out")                                                        # :823-829
         infeat_bg = cached_pooler_bg_out if self.use_cached_bg else pooled["bg_out"]
+        differentiated = torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (
+            self.layer_coeff_maps[ca].weight, self.layer_coeff_maps[ca].bias, self.basis_vecs, self.pre_vecs, self.bias,
+            infeat_fg, infeat_bg))
+        if differentiated and not self.do_zero_shot:
+            # inversion step: hand the parameters themselves to the op (ops.ada_head_bwd produces their gradients) and
+            # write the K rows into a COPY of the context with a differentiable index_copy instead of the in-kernel splice
+            m = self.layer_coeff_maps[ca]
+            basis = self.basis_vecs if self.pre_vecs is None else torch.cat([self.pre_vecs, self.basis_vecs], dim=1)
+            bias = None if self.bias is None else self.bias[ca]
+            out = ops.ada_head(infeat_fg, infeat_bg, time_emb, self.TDs[ca], m.weight, m.bias, basis, bias)
+            if splice_into is not None:
+                ctx_new = splice_into.clone()
+                n = out.shape[0]
+                ctx_new[:n] = ctx_new[:n].index_copy(1, splice_positions.long(), out.to(ctx_new.dtype))
+                pooled["ctx"] = ctx_new
+            return out, pooled
         p = self.packed()
         if self.do_zero_shot:
             # per-instance basis [B, K, r, 768] from the subject basis generator, no bias; the coefficient scaler

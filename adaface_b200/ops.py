@@ -779,3 +779,340 @@ def to_f32(x: Tensor) -> Tensor:
 @to_f32.register_fake
 def _(x):
     return x.new_empty(x.shape, dtype=torch.float32)
+
+
+# =========================================================================================== backward (inversion step)
+# BASELINE.json configs[3]: the U-Net is frozen, the AdaEmbedding parameters are the trainable set.  The reference gets
+# its gradients from torch autograd (ddpm.py:599 manual_backward); here every op on the path from the block output back
+# to those parameters carries an analytic backward built from the kernels of csrc/backward.cu and from the forward GEMM
+# (dA = dC W against the frozen weight).  Not built: the backward of self-attention (long key sequences), of GroupNorm and
+# of the pooler towards the layer features x / q - ops that would need them raise instead of returning wrong gradients.
+_WT_CACHE: Dict[Tuple, Tensor] = {}
+
+
+def _transposed(w: Tensor) -> Tensor:
+    """bf16 [N, K] weight -> contiguous [K, N] (the `w` operand of the dX GEMM), cached per weight tensor."""
+    key = (w.data_ptr(), w._version, tuple(w.shape), tuple(w.stride()))
+    t = _WT_CACHE.get(key)
+    if t is None:
+        if len(_WT_CACHE) > 512:
+            _WT_CACHE.clear()
+        t = w.detach().t().contiguous()
+        _WT_CACHE[key] = t
+    return t
+
+
+def _frozen(*ws: Optional[Tensor]) -> None:
+    for w in ws:
+        if w is not None and w.requires_grad:
+            raise NotImplementedError("adaface_b200: the inversion step trains the embedding parameters only - weight "
+                                      "gradients of the U-Net GEMMs are not built; freeze the U-Net (requires_grad_(False))")
+
+
+def _dx_gemm(dout: Tensor, w: Tensor) -> Tensor:
+    """dA [M, K] = dOut [M, N] @ W [N, K]: the forward GEMM with the transposed weight."""
+    return linear(dout.contiguous(), _transposed(w), None, None, False)
+
+
+@torch.library.custom_op("adaface_b200::geglu_bwd", mutates_args=())
+def geglu_bwd(h: Tensor, dout: Tensor) -> Tensor:
+    """h bf16 [M, 2H] (interleaved value / gate column order of the forward GEMM), dout bf16 [M, H] -> dh bf16 [M, 2H]."""
+    _need_cuda(h, dout)
+    if h.dtype != torch.bfloat16 or dout.dtype != torch.bfloat16 or h.dim() != 2 or dout.shape != (h.shape[0], h.shape[1] // 2):
+        raise ValueError("geglu_bwd: h bf16 [M, 2H] and dout bf16 [M, H] expected")
+    h, dout = h.contiguous(), dout.contiguous()
+    dh = torch.empty_like(h)
+    _run("geglu_bwd", _lib.load().afb_geglu_bwd, _ptr(h), _ptr(dout), _ptr(dh), h.shape[0], dout.shape[1], _stream(),
+         nbytes=2.0 * (2 * h.numel() + dout.numel()))
+    return dh
+
+
+@geglu_bwd.register_fake
+def _(h, dout):
+    return torch.empty_like(h)
+
+
+@torch.library.custom_op("adaface_b200::layernorm_bwd", mutates_args=())
+def layernorm_bwd(a: Tensor, g: Tensor, add: Optional[Tensor], eps: float) -> Tensor:
+    """Backward of the affine-free LayerNorm over the last dim: a, g = d(a_hat) bf16 [M, C] (+ add: the gradient that
+    reaches `a` along the residual stream) -> da bf16 [M, C]."""
+    _need_cuda(a, g, add)
+    if a.dtype != torch.bfloat16 or g.dtype != torch.bfloat16 or a.shape != g.shape or (add is not None and (
+            add.dtype != torch.bfloat16 or add.shape != a.shape)):
+        raise ValueError("layernorm_bwd: bf16 tensors of one shape expected")
+    a, g = a.contiguous(), g.contiguous()
+    add = None if add is None else add.contiguous()
+    da = torch.empty_like(a)
+    c = a.shape[-1]
+    _run("layernorm_bwd", _lib.load().afb_layernorm_bwd, _ptr(a), _ptr(g), _ptr(add), _ptr(da), a.numel() // c, c, eps, _stream(),
+         nbytes=2.0 * a.numel() * (3 + (add is not None)))
+    return da
+
+
+@layernorm_bwd.register_fake
+def _(a, g, add, eps):
+    return torch.empty_like(a)
+
+
+@torch.library.custom_op("adaface_b200::attention_bwd_short", mutates_args=())
+def attention_bwd_short(q: Tensor, k: Tensor, v: Tensor, dout: Tensor, heads: int, scale: float,
+                        want_dq: bool) -> Tuple[Tensor, Tensor, Tensor]:
+    """Backward of `attention` for a short key sequence (the 77-token context): -> (dq bf16 [B,Nq,C] or an empty tensor,
+    dk fp32 [B,Nk,C], dv fp32 [B,Nk,C])."""
+    _need_cuda(q, k, v, dout)
+    b, nq, c = q.shape
+    nk = k.shape[1]
+    dout = dout.contiguous()
+    if dout.dtype != torch.bfloat16 or dout.shape != q.shape:
+        raise ValueError("attention_bwd_short: dout must be bf16 of q's shape")
+    dq = torch.empty((b, nq, c) if want_dq else (0,), dtype=torch.bfloat16, device=q.device)
+    dk = torch.zeros((b, nk, c), dtype=torch.float32, device=q.device)
+    dv = torch.zeros((b, nk, c), dtype=torch.float32, device=q.device)
+    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=None, key_mask=None, batch=b, heads=heads, head_dim=c // heads,
+                    q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"), ldo=c, scale=scale)
+    _run("attention_bwd", _lib.load().afb_attention_bwd_short, C.byref(args), _ptr(dout), _ptr(dq) if want_dq else None, _ptr(dk),
+         _ptr(dv), c, c, _stream(), flops=10.0 * b * nq * nk * c, tag=f"b{b}q{nq}k{nk}d{c // heads}")
+    return dq, dk, dv
+
+
+@attention_bwd_short.register_fake
+def _(q, k, v, dout, heads, scale, want_dq):
+    f = lambda t: t.new_empty(t.shape, dtype=torch.float32)
+    return (torch.empty_like(q) if want_dq else q.new_empty((0,))), f(k), f(v)
+
+
+@torch.library.custom_op("adaface_b200::ada_head_bwd", mutates_args=())
+def ada_head_bwd(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor,
+                 basis: Tensor, grad_out: Tensor, want_bias: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """Backward of `ada_head` (shared basis [K, r, D]): -> (d_coeff_w, d_coeff_b, d_basis, d_bias [K, D] or empty,
+    d_infeat_fg, d_infeat_bg), all fp32."""
+    _need_cuda(infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, grad_out)
+    b, c = infeat_fg.shape
+    if basis.dim() != 3:
+        raise NotImplementedError("ada_head_bwd: the zero-shot per-instance basis has no trainable tensor on this path")
+    k, r, d = basis.shape
+    f = lambda t: t.detach().to(torch.float32).contiguous()
+    infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, grad_out = map(
+        f, (infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis, grad_out))
+    dev = infeat_fg.device
+    z = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+    d_cw, d_cb, d_basis = z(*coeff_w.shape), z(*coeff_b.shape), z(k, r, d)
+    d_bias = z(k, d) if want_bias else z(0)
+    ws = torch.empty((b, 2 * c + td), dtype=torch.float32, device=dev)
+    d_fg, d_bg = torch.empty((b, c), dtype=torch.float32, device=dev), torch.empty((b, c), dtype=torch.float32, device=dev)
+    _run("ada_head_bwd", _lib.load().afb_ada_head_bwd, _ptr(infeat_fg), _ptr(infeat_bg), _ptr(time_emb), time_emb.stride(0),
+         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(grad_out), _ptr(d_cw), _ptr(d_cb), _ptr(d_basis),
+         _ptr(d_bias) if want_bias else None, _ptr(ws), _ptr(d_fg), _ptr(d_bg), b, c, td, k, r, d, _stream(),
+         nbytes=8.0 * (coeff_w.numel() + basis.numel()))
+    return d_cw, d_cb, d_basis, d_bias, d_fg, d_bg
+
+
+@ada_head_bwd.register_fake
+def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, grad_out, want_bias):
+    f = lambda t: t.new_empty(t.shape, dtype=torch.float32)
+    k, _, d = basis.shape
+    return f(coeff_w), f(coeff_b), f(basis), infeat_fg.new_empty((k, d) if want_bias else (0,), dtype=torch.float32), \
+        f(infeat_fg), f(infeat_bg)
+
+
+@torch.library.custom_op("adaface_b200::ada_pool_bwd", mutates_args=())
+def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor, d_bg: Tensor) -> Tensor:
+    """Backward of `ada_pool` w.r.t. the folded pooling queries: re-runs the forward for its softmax statistics and
+    pooled outputs, then one streaming pass over x and q -> d_pool_q fp32 [B, 2, C]."""
+    _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg)
+    b, n, c = x.shape
+    lib = _lib.load()
+    dev = x.device
+    x, q = x.contiguous(), q.contiguous()
+    pool_q = pool_q.detach().to(torch.float32).contiguous()
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
+    ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
+    fg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    bg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
+         b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+    stats = ws[ws.numel() - b * 16:]                     # the forward's merged (max, sum) per (sample, head)
+    d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
+    d_pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=dev)
+    _run("ada_pool_bwd", lib.afb_ada_pool_bwd, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats), _ptr(fg), _ptr(bg),
+         _ptr(d_fg), _ptr(d_bg), _ptr(d_pool_q), b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+    return d_pool_q
+
+
+@ada_pool_bwd.register_fake
+def _(x, q, pool_q, key_mask, d_fg, d_bg):
+    return x.new_empty((x.shape[0], 2, x.shape[2]), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::ada_pool_prep_bwd", mutates_args=())
+def ada_pool_prep_bwd(to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor, lora_to_fg_q: Tensor, lora_to_bg_q: Tensor,
+                      lora_to_k: Tensor, d_pool_q: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """Backward of `ada_pool_prep` w.r.t. the three grouped-conv weights [C/8, C/8] (the to_k projection is frozen, the
+    query embeddings are inputs): re-runs the projection for its workspace, then one small kernel."""
+    _need_cuda(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k, d_pool_q)
+    c, ctx_dim = to_k_weight.shape
+    b = bg_q_emb.shape[0]
+    f = lambda t: t.detach().to(torch.float32).contiguous()
+    w, fg, bg, wf, wb, wk, dq = map(f, (to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k, d_pool_q))
+    lib = _lib.load()
+    dev = w.device
+    pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=dev)
+    ws = torch.empty(int(lib.afb_ada_pool_prep_ws_floats(b, c)), dtype=torch.float32, device=dev)
+    _run("ada_pool_prep", lib.afb_ada_pool_prep, _ptr(w), ctx_dim, _ptr(fg), _ptr(bg), _ptr(wf), _ptr(wb), _ptr(wk), _ptr(pool_q),
+         _ptr(ws), b, c, _stream(), nbytes=4.0 * c * ctx_dim)
+    d_wf, d_wb, d_wk = torch.zeros_like(wf), torch.zeros_like(wb), torch.zeros_like(wk)
+    _run("ada_pool_prep_bwd", lib.afb_ada_pool_prep_bwd, _ptr(ws), _ptr(wf), _ptr(wb), _ptr(wk), _ptr(dq), _ptr(d_wf), _ptr(d_wb),
+         _ptr(d_wk), b, c, _stream(), nbytes=12.0 * wk.numel())
+    return d_wf, d_wb, d_wk
+
+
+@ada_pool_prep_bwd.register_fake
+def _(to_k_weight, fg_q_emb, bg_q_emb, lora_to_fg_q, lora_to_bg_q, lora_to_k, d_pool_q):
+    f = lambda t: t.new_empty(t.shape, dtype=torch.float32)
+    return f(lora_to_fg_q), f(lora_to_bg_q), f(lora_to_k)
+
+
+# ---- autograd formulas (torch.library.register_autograd): dX only against frozen weights -----------------------------
+def _bf16c(g: Tensor) -> Tensor:
+    return g.to(torch.bfloat16).contiguous()
+
+
+def _linear_setup(ctx, inputs, output):
+    a, w, bias, residual, out_fp32 = inputs
+    _frozen(w, bias)
+    ctx.save_for_backward(w)
+    ctx.a_needs, ctx.res_needs = a.requires_grad, residual is not None and residual.requires_grad
+    ctx.a_dtype, ctx.res_dtype = a.dtype, (None if residual is None else residual.dtype)
+
+
+def _linear_backward(ctx, g):
+    (w,) = ctx.saved_tensors
+    gb = _bf16c(g)
+    da = _dx_gemm(gb, w).to(ctx.a_dtype) if ctx.a_needs else None
+    dres = g.to(ctx.res_dtype) if ctx.res_needs else None
+    return da, None, None, dres, None
+
+
+linear.register_autograd(_linear_backward, setup_context=_linear_setup)
+
+
+def _linear_stats_setup(ctx, inputs, output):
+    a, w, bias, residual = inputs
+    _frozen(w, bias)
+    ctx.save_for_backward(w)
+    ctx.a_needs, ctx.res_needs = a.requires_grad, residual is not None and residual.requires_grad
+
+
+def _linear_stats_backward(ctx, g, g_stats):
+    # the row statistics are a side output consumed by the LayerNorm-folded GEMMs, whose backward differentiates the
+    # LayerNorm itself (from the activations): no gradient flows through `stats`
+    (w,) = ctx.saved_tensors
+    gb = _bf16c(g)
+    return (_dx_gemm(gb, w) if ctx.a_needs else None), None, None, (gb if ctx.res_needs else None)
+
+
+linear_stats.register_autograd(_linear_stats_backward, setup_context=_linear_stats_setup)
+
+
+def _linear_ln_setup(ctx, inputs, output):
+    a, stats, w_gamma, colsum, bias, eps = inputs
+    _frozen(w_gamma, colsum, bias)
+    ctx.save_for_backward(a, w_gamma)
+    ctx.eps = eps
+
+
+def _linear_ln_backward(ctx, g):
+    a, w_gamma = ctx.saved_tensors
+    d_hat = _dx_gemm(_bf16c(g), w_gamma)                       # gradient w.r.t. the normalised activations
+    return layernorm_bwd(a, d_hat, None, ctx.eps), None, None, None, None, None
+
+
+linear_ln.register_autograd(_linear_ln_backward, setup_context=_linear_ln_setup)
+
+
+def _linear_ln_geglu_setup(ctx, inputs, output):
+    a, stats, w_interleaved, colsum, bias, eps = inputs
+    _frozen(w_interleaved, colsum, bias)
+    ctx.save_for_backward(a, stats, w_interleaved, colsum, bias)
+    ctx.eps = eps
+
+
+def _linear_ln_geglu_backward(ctx, g):
+    a, stats, w_i, colsum, bias = ctx.saved_tensors
+    # the forward never writes the 8C-wide projection: recompute it (same interleaved column order), then
+    # d(a_hat) = dh W_interleaved and the LayerNorm backward
+    h = linear_ln(a, stats, w_i, colsum, bias, ctx.eps)
+    dh = geglu_bwd(h, _bf16c(g))
+    d_hat = _dx_gemm(dh, w_i)
+    return layernorm_bwd(a, d_hat, None, ctx.eps), None, None, None, None, None
+
+
+linear_ln_geglu.register_autograd(_linear_ln_geglu_backward, setup_context=_linear_ln_geglu_setup)
+
+
+def _attention_setup(ctx, inputs, output):
+    q, k, v, heads, scale, key_mask = inputs
+    if k.shape[1] > 128 or key_mask is not None:
+        raise NotImplementedError("adaface_b200: only the backward of the short-key (77-token cross-) attention is built; "
+                                  "self-attention / masked attention cannot take part in a differentiated graph yet")
+    ctx.save_for_backward(q, k, v)
+    ctx.heads, ctx.scale, ctx.q_needs = heads, scale, q.requires_grad
+
+
+def _attention_backward(ctx, g):
+    q, k, v = ctx.saved_tensors
+    dq, dk, dv = attention_bwd_short(q, k, v, _bf16c(g), ctx.heads, ctx.scale, ctx.q_needs)
+    return (dq if ctx.q_needs else None), dk.to(k.dtype), dv.to(v.dtype), None, None, None
+
+
+attention.register_autograd(_attention_backward, setup_context=_attention_setup)
+
+
+def _ada_head_setup(ctx, inputs, output):
+    infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, bias = inputs
+    ctx.save_for_backward(infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis)
+    ctx.td, ctx.has_bias = td, bias is not None
+
+
+def _ada_head_backward(ctx, g):
+    infeat_fg, infeat_bg, time_emb, coeff_w, coeff_b, basis = ctx.saved_tensors
+    d_cw, d_cb, d_basis, d_bias, d_fg, d_bg = ada_head_bwd(infeat_fg, infeat_bg, time_emb, ctx.td, coeff_w, coeff_b, basis,
+                                                           g.contiguous(), ctx.has_bias)
+    # the time embedding carries no trainable tensor on this path: no gradient is produced for it
+    return d_fg, d_bg, None, None, d_cw, d_cb, d_basis, (d_bias if ctx.has_bias else None)
+
+
+ada_head.register_autograd(_ada_head_backward, setup_context=_ada_head_setup)
+
+
+def _ada_pool_setup(ctx, inputs, output):
+    x, q, pool_q, key_mask, want_attn = inputs
+    if x.requires_grad or q.requires_grad:
+        raise NotImplementedError("adaface_b200: the pooler's backward towards the layer features (x, q) is not built; it "
+                                  "differentiates w.r.t. the pooling queries only (detach x and q)")
+    ctx.save_for_backward(x, q, pool_q, key_mask)
+
+
+def _ada_pool_backward(ctx, g_fg, g_bg, g_afg, g_abg):
+    x, q, pool_q, key_mask = ctx.saved_tensors
+    z = lambda g: torch.zeros((x.shape[0], x.shape[2]), dtype=torch.float32, device=x.device) if g is None else g
+    return None, None, ada_pool_bwd(x, q, pool_q, key_mask, z(g_fg), z(g_bg)), None, None
+
+
+ada_pool.register_autograd(_ada_pool_backward, setup_context=_ada_pool_setup)
+
+
+def _ada_pool_prep_setup(ctx, inputs, output):
+    to_k_weight, fg_q_emb, bg_q_emb, wf, wb, wk = inputs
+    _frozen(to_k_weight)
+    ctx.save_for_backward(to_k_weight, fg_q_emb, bg_q_emb, wf, wb, wk)
+
+
+def _ada_pool_prep_backward(ctx, g):
+    to_k_weight, fg_q_emb, bg_q_emb, wf, wb, wk = ctx.saved_tensors
+    d_wf, d_wb, d_wk = ada_pool_prep_bwd(to_k_weight, fg_q_emb, bg_q_emb, wf, wb, wk, g.contiguous())
+    return None, None, None, d_wf.to(wf.dtype), d_wb.to(wb.dtype), d_wk.to(wk.dtype)
+
+
+ada_pool_prep.register_autograd(_ada_pool_prep_backward, setup_context=_ada_pool_prep_setup)

@@ -443,6 +443,7 @@ class AdaPromptContext:
                                    img_mask=mask, cached_pooler_bg_out=cached, splice_into=layer_ctx,
                                    splice_positions=self.positions(i, layer_ctx.device))
             bg_cache[i] = pooled["bg_out"]
+            layer_ctx = pooled.get("ctx", layer_ctx)      # inversion step: the embedder returns a differentiable copy
         return layer_ctx
 
 
@@ -602,7 +603,9 @@ class UNetModel(nn.Module):
             with_ada.wants_layer_attn_components = True
             return with_ada
 
-        if ada is not None and x.is_cuda:
+        ada_trains = ada is not None and torch.is_grad_enabled() and any(
+            p.requires_grad for s_ in ada.subjects for p in s_.embedder.parameters())
+        if ada is not None and x.is_cuda and not ada_trains:      # (inversion step: per-layer, differentiable preparation)
             ada.prepare_queries(self.spatial_transformers())
         bundle = self.emb_bundle(emb)
         hs = []
