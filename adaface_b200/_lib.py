@@ -35,7 +35,7 @@ class AttnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("out", C.c_void_p),
                 ("key_mask", C.c_void_p), ("batch", C.c_int), ("heads", C.c_int), ("head_dim", C.c_int),
                 ("q_len", C.c_int), ("kv_len", C.c_int), ("ldq", C.c_int64), ("ldk", C.c_int64),
-                ("ldv", C.c_int64), ("ldo", C.c_int64), ("scale", C.c_float)]
+                ("ldv", C.c_int64), ("ldo", C.c_int64), ("scale", C.c_float), ("lse", C.c_void_p)]
 
 
 EPI_STORE, EPI_GEGLU, EPI_NCHW = 0, 1, 2
@@ -76,6 +76,9 @@ _SIGNATURES = {
     "afb_ada_head_bwd": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "afb_ada_pool_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "afb_ada_pool_prep_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
+    "afb_attention_bwd": (_I, [C.POINTER(AttnArgs), _P, _P, _P, _P, _P, _I64, _P]),
+    "afb_groupnorm_tokens_bwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _F, _P]),
+    "afb_ada_pool_bwd_features": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "afb_cast_f32_to_bf16": (_I, [_P, _P, _I64, _P]),
     "afb_cast_bf16_to_f32": (_I, [_P, _P, _I64, _P]),
 }

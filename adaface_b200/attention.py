@@ -233,7 +233,7 @@ class CrossAttention(nn.Module, _PackedWeights):
         p = self.packed()
         inner = p["wq"].shape[0]
         qkv = ops.linear(x.view(b * n, c), p["wqkv"], None, None, False).view(b, n, 3 * inner)
-        a = ops.attention(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
+        a = ops.attention_auto(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
                           key_mask)
         return ops.linear(a.view(b * n, inner), p["wo"], p["bo"], residual, False)
 
@@ -249,7 +249,7 @@ class CrossAttention(nn.Module, _PackedWeights):
         self._check_modes(None, False)
         b, n, w3 = qkv.shape
         inner = w3 // 3
-        a = ops.attention(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
+        a = ops.attention_auto(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
                           key_mask)
         return a.view(b * n, inner)
 
@@ -285,7 +285,7 @@ class CrossAttention(nn.Module, _PackedWeights):
                     "q": q.view(b, n, self.heads, d).permute(0, 2, 1, 3).float() * math.sqrt(self.scale),
                     "attn": attn, "attnscore": sim}
         else:
-            a = ops.attention(q, k, v, self.heads, self.scale, None)
+            a = ops.attention_auto(q, k, v, self.heads, self.scale, None)
         return self.out_projection(a.view(b * n, inner), residual, want_stats)
 
     def forward(self, x: Tensor, context=None, mask: Optional[Tensor] = None) -> Tensor:

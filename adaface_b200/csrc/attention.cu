@@ -39,6 +39,7 @@ constexpr float kRescaleThreshold = 8.0f;  // log2 units
 
 struct AttnDev {
   __nv_bfloat16* out;
+  float* lse;               // optional [B, heads, q_len]: log2-domain log-sum-exp of the scaled scores (for the backward)
   const uint8_t* key_mask;
   int q_len, kv_len, heads;
   long long ldo;
@@ -668,6 +669,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       l_run = __uint_as_float(o[0]);
     }
     const float inv_l = 1.0f / l_run;
+    if (p.lse != nullptr && q_idx < p.q_len)      // P = 2^(s * scale * log2(e) - lse)
+      p.lse[(static_cast<long long>(b) * p.heads + head) * p.q_len + q_idx] = m_used + log2f(l_run);
     __nv_bfloat16* orow = p.out + (static_cast<long long>(b) * p.q_len + q_idx) * p.ldo + col0;
 #pragma unroll
     for (int c = 0; c < D / 8; ++c) {
@@ -736,6 +739,7 @@ int launch_attn(const afb_attn_args& a, cudaStream_t stream) {
   AttnDev p;
   p.out = reinterpret_cast<__nv_bfloat16*>(a.out);
   p.key_mask = a.key_mask;
+  p.lse = a.lse;
   p.q_len = a.q_len;
   p.kv_len = a.kv_len;
   p.heads = a.heads;

@@ -817,3 +817,493 @@ extern "C" int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ================================================================================================================
+// Second stage: the pieces that carry a layer's gradient further down the U-Net - self-attention (long key sequences),
+// GroupNorm, and the pooler's gradient towards the layer features.
+// ================================================================================================================
+namespace afb {
+namespace {
+
+// delta[b, h, q] = sum_i dO[b, q, h d + i] * O[b, q, h d + i]  (= rowsum(P * dP)); one thread per (row, head)
+__global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
+                                                         float* __restrict__ delta, long long rows, int q_len, int heads, int d,
+                                                         long long ldo, long long lddo) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= rows * heads) return;
+  const long long row = idx / heads;
+  const int h = static_cast<int>(idx % heads);
+  const __nv_bfloat16* po = o + row * ldo + h * d;
+  const __nv_bfloat16* pd = dout + row * lddo + h * d;
+  float a = 0.f;
+  for (int i = 0; i < d; i += 8) {
+    float x[8], y[8];
+    unpack8f(*reinterpret_cast<const uint4*>(po + i), x);
+    unpack8f(*reinterpret_cast<const uint4*>(pd + i), y);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a = fmaf(x[j], y[j], a);
+  }
+  const long long b = row / q_len, qi = row % q_len;
+  delta[(b * heads + h) * q_len + qi] = a;
+}
+
+// ---- attention backward for long key sequences (self-attention, attention.py:195-243), flash style:
+// block (key tile of 64, head, sample) keeps K, V of its tile in shared memory and walks the query tiles of 64 rows:
+//   P = 2^(s scale log2e - lse), dP = dO V^T, dS = P (dP - delta) scale,
+//   dV += P^T dO, dK += dS^T Q (register accumulators over all query tiles, written once),
+//   dQ += dS K (fp32 atomics: every key tile adds its share; dq must be zero on entry).
+// fp32 CUDA-core arithmetic with 4 x 4 register tiles: a first, correct version of this kernel - the tensor-core
+// (tcgen05) form of the forward kernel is not built for the backward yet.
+constexpr int kAlT = 64;             // keys per block tile and query rows per step
+constexpr int kAlThreads = 256;
+
+template <int D>
+__global__ void __launch_bounds__(kAlThreads) attn_bwd_long_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
+    const __nv_bfloat16* __restrict__ dout, const float* __restrict__ lse, const float* __restrict__ delta,
+    float* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv, int q_len, int kv_len, int heads, long long ldq,
+    long long ldk, long long ldv, long long ldo, long long ldg, float scale) {
+  extern __shared__ float sh[];
+  constexpr int DP = D + 1;
+  constexpr int TP = kAlT + 1;
+  float* sK = sh;                         // [64][DP]
+  float* sV = sK + kAlT * DP;
+  float* sQ = sV + kAlT * DP;
+  float* sO = sQ + kAlT * DP;             // dO tile
+  float* sP = sO + kAlT * DP;             // [64 rows][TP]
+  float* sS = sP + kAlT * TP;             // dS
+  float* sL = sS + kAlT * TP;             // [64] lse, [64] delta
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int k0 = blockIdx.x * kAlT;
+  const int col0 = head * D;
+  const int tid = threadIdx.x;
+  const float scale_log2 = scale * 1.4426950408889634f;
+  for (int idx = tid; idx < kAlT * D; idx += kAlThreads) {
+    const int t = idx / D, i = idx - t * D;
+    const bool ok = k0 + t < kv_len;
+    sK[t * DP + i] = ok ? __bfloat162float(k[(static_cast<long long>(b) * kv_len + k0 + t) * ldk + col0 + i]) : 0.f;
+    sV[t * DP + i] = ok ? __bfloat162float(v[(static_cast<long long>(b) * kv_len + k0 + t) * ldv + col0 + i]) : 0.f;
+  }
+  // dK / dV outputs of this thread: key t = tid % 64, channels i = (tid / 64) + 4 n
+  constexpr int kOwn = (D + 3) / 4;
+  float acc_k[kOwn], acc_v[kOwn];
+#pragma unroll
+  for (int n = 0; n < kOwn; ++n) acc_k[n] = acc_v[n] = 0.f;
+  const int ty = tid >> 4, tx = tid & 15;       // 4 x 4 micro tile: rows 4 ty.., keys 4 tx..
+  for (int r0 = 0; r0 < q_len; r0 += kAlT) {
+    __syncthreads();
+    for (int idx = tid; idx < kAlT * D; idx += kAlThreads) {
+      const int r = idx / D, i = idx - r * D;
+      const bool ok = r0 + r < q_len;
+      sQ[r * DP + i] = ok ? __bfloat162float(q[(static_cast<long long>(b) * q_len + r0 + r) * ldq + col0 + i]) : 0.f;
+      sO[r * DP + i] = ok ? __bfloat162float(dout[(static_cast<long long>(b) * q_len + r0 + r) * ldo + col0 + i]) : 0.f;
+    }
+    if (tid < kAlT) {
+      const bool ok = r0 + tid < q_len;
+      const long long li = (static_cast<long long>(b) * heads + head) * q_len + r0 + tid;
+      sL[tid] = ok ? lse[li] : 0.f;
+      sL[kAlT + tid] = ok ? delta[li] : 0.f;
+    }
+    __syncthreads();
+    {
+      float s[4][4], dp[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) s[a][c] = dp[a][c] = 0.f;
+#pragma unroll 4
+      for (int i = 0; i < D; ++i) {
+        float qa[4], oa[4], kc[4], vc[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          qa[a] = sQ[(4 * ty + a) * DP + i];
+          oa[a] = sO[(4 * ty + a) * DP + i];
+          kc[a] = sK[(4 * tx + a) * DP + i];
+          vc[a] = sV[(4 * tx + a) * DP + i];
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            s[a][c] = fmaf(qa[a], kc[c], s[a][c]);
+            dp[a][c] = fmaf(oa[a], vc[c], dp[a][c]);
+          }
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int r = 4 * ty + a;
+        const bool row_ok = r0 + r < q_len;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int t = 4 * tx + c;
+          const bool ok = row_ok && k0 + t < kv_len;
+          const float pr = ok ? exp2f(s[a][c] * scale_log2 - sL[r]) : 0.f;
+          sP[r * TP + t] = pr;
+          sS[r * TP + t] = pr * (dp[a][c] - sL[kAlT + r]) * scale;
+        }
+      }
+    }
+    __syncthreads();
+    // dQ[r][i] += sum_t dS[r][t] K[t][i]: thread (r = tid % 64, channels (tid / 64) + 4 n)
+    {
+      const int r = tid & 63, i0 = tid >> 6;
+      if (r0 + r < q_len) {
+        float* dst = dq + (static_cast<long long>(b) * q_len + r0 + r) * ldg + col0;
+        for (int i = i0; i < D; i += 4) {
+          float a = 0.f;
+#pragma unroll 8
+          for (int t = 0; t < kAlT; ++t) a = fmaf(sS[r * TP + t], sK[t * DP + i], a);
+          atomicAdd(dst + i, a);
+        }
+      }
+    }
+    // dK[t][i] += sum_r dS[r][t] Q[r][i];  dV[t][i] += sum_r P[r][t] dO[r][i]
+    {
+      const int t = tid & 63, i0 = tid >> 6;
+#pragma unroll
+      for (int n = 0; n < kOwn; ++n) {
+        const int i = i0 + 4 * n;
+        if (i < D) {
+          float ak = 0.f, av = 0.f;
+#pragma unroll 8
+          for (int r = 0; r < kAlT; ++r) {
+            ak = fmaf(sS[r * TP + t], sQ[r * DP + i], ak);
+            av = fmaf(sP[r * TP + t], sO[r * DP + i], av);
+          }
+          acc_k[n] += ak;
+          acc_v[n] += av;
+        }
+      }
+    }
+  }
+  {
+    const int t = tid & 63, i0 = tid >> 6;
+    if (k0 + t < kv_len) {
+      const long long o = (static_cast<long long>(b) * kv_len + k0 + t) * ldg + col0;
+#pragma unroll
+      for (int n = 0; n < kOwn; ++n) {
+        const int i = i0 + 4 * n;
+        if (i < D) {
+          dk[o + i] = acc_k[n];
+          dv[o + i] = acc_v[n];
+        }
+      }
+    }
+  }
+}
+
+template <int D>
+int launch_attn_bwd_long(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
+                         long long ldg, cudaStream_t stream) {
+  const size_t sh = (4 * static_cast<size_t>(kAlT) * (D + 1) + 2 * static_cast<size_t>(kAlT) * (kAlT + 1) + 2 * kAlT) * sizeof(float);
+  auto kern = attn_bwd_long_kernel<D>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh)));
+    attr_set = true;
+  }
+  dim3 grid((a.kv_len + kAlT - 1) / kAlT, a.heads, a.batch);
+  kern<<<grid, kAlThreads, sh, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
+                                         reinterpret_cast<const __nv_bfloat16*>(a.v), dout, a.lse, delta, dq, dk, dv, a.q_len,
+                                         a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale);
+  return 0;
+}
+
+}  // namespace
+}  // namespace afb
+
+extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout, float* delta_ws, float* dq, float* dk,
+                                 float* dv, int64_t ldg, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(args != nullptr && dout && delta_ws && dq && dk && dv, "afb_attention_bwd: NULL argument");
+  const afb_attn_args& a = *args;
+  AFB_REQUIRE(a.q && a.k && a.v && a.out && a.lse, "afb_attention_bwd: q, k, v, the forward output and its lse are needed");
+  AFB_REQUIRE(a.key_mask == nullptr, "afb_attention_bwd: the backward with a key mask is not built");
+  AFB_REQUIRE(a.batch > 0 && a.heads > 0 && a.q_len > 0 && a.kv_len > 0 && a.batch <= 65535 && a.heads <= 65535,
+              "afb_attention_bwd: bad sizes");
+  const int width = a.heads * a.head_dim;
+  AFB_REQUIRE(a.ldq >= width && a.ldk >= width && a.ldv >= width && a.ldo >= width && ldg >= width,
+              "afb_attention_bwd: leading dimension smaller than heads*head_dim");
+  AFB_REQUIRE(a.head_dim % 8 == 0 && a.ldo % 8 == 0, "afb_attention_bwd: head_dim and ldo must be multiples of 8");
+  const long long rows = static_cast<long long>(a.batch) * a.q_len;
+  const __nv_bfloat16* db = reinterpret_cast<const __nv_bfloat16*>(dout);
+  const long long n = rows * a.heads;
+  // `dout` shares the forward output's row pitch (ldo)
+  attn_delta_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.out), db,
+                                                                                delta_ws, rows, a.q_len, a.heads, a.head_dim,
+                                                                                a.ldo, a.ldo);
+  count_launch();
+  AFB_CHECK_CUDA(cudaMemsetAsync(dq, 0, static_cast<size_t>(rows) * ldg * sizeof(float), stream));
+  int rc;
+  switch (a.head_dim) {
+    case 40: rc = launch_attn_bwd_long<40>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    case 80: rc = launch_attn_bwd_long<80>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    case 160: rc = launch_attn_bwd_long<160>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    default: AFB_FAIL(2, "afb_attention_bwd: head_dim %d not supported (SD-1.5 uses 40, 80, 160)", a.head_dim);
+  }
+  if (rc) return rc;
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+namespace afb {
+namespace {
+
+// ---- GroupNorm backward (attention.py:71-72,325: GroupNorm(32, C, eps) without activation, token-major bf16 in and
+// out): block (group, sample) walks the group's cpg channels of all tokens three times (the slab is L2 resident):
+// statistics of x, then the two means of the LayerNorm-style backward, then
+//   dx = rstd (gamma g - mean(gamma g) - x_hat mean(gamma g x_hat)).
+__global__ void __launch_bounds__(512) gn_bwd_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ g,
+                                                         const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dx, int C,
+                                                         int HW, int cpg, float eps) {
+  __shared__ float red[32];
+  const int grp = blockIdx.x, b = blockIdx.y;
+  const long long base = static_cast<long long>(b) * HW * C + grp * cpg;
+  const int n = HW * cpg;
+  float s = 0.f, s2 = 0.f;
+  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+    const int t = idx / cpg, j = idx - t * cpg;
+    const float v = __bfloat162float(x[base + static_cast<long long>(t) * C + j]);
+    s += v;
+    s2 = fmaf(v, v, s2);
+  }
+  const float mean = block_sum_t(s, red) / n;
+  const float var = fmaxf(block_sum_t(s2, red) / n - mean * mean, 0.f);
+  const float rstd = rsqrtf(var + eps);
+  float sg = 0.f, sgx = 0.f;
+  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+    const int t = idx / cpg, j = idx - t * cpg;
+    const long long o = base + static_cast<long long>(t) * C + j;
+    const float xh = (__bfloat162float(x[o]) - mean) * rstd;
+    const float gg = __bfloat162float(g[o]) * gamma[grp * cpg + j];
+    sg += gg;
+    sgx = fmaf(gg, xh, sgx);
+  }
+  const float mg = block_sum_t(sg, red) / n, mgx = block_sum_t(sgx, red) / n;
+  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+    const int t = idx / cpg, j = idx - t * cpg;
+    const long long o = base + static_cast<long long>(t) * C + j;
+    const float xh = (__bfloat162float(x[o]) - mean) * rstd;
+    const float gg = __bfloat162float(g[o]) * gamma[grp * cpg + j];
+    dx[o] = __float2bfloat16_rn(rstd * (gg - mg - xh * mgx));
+  }
+}
+
+}  // namespace
+}  // namespace afb
+
+extern "C" int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, afb_bf16* dx, int batch,
+                                        int channels, int hw, int groups, float eps, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(x && grad_y && gamma && dx, "afb_groupnorm_tokens_bwd: NULL argument");
+  AFB_REQUIRE(batch > 0 && batch <= 65535 && channels > 0 && hw > 0 && groups > 0 && channels % groups == 0,
+              "afb_groupnorm_tokens_bwd: bad sizes");
+  gn_bwd_tok_kernel<<<dim3(groups, batch), 512, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                             reinterpret_cast<const __nv_bfloat16*>(grad_y), gamma,
+                                                             reinterpret_cast<__nv_bfloat16*>(dx), channels, hw, channels / groups, eps);
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+namespace afb {
+namespace {
+
+// ---- AttentionalPooler backward towards the layer features (embedding_manager.py:146-321): with the quantities of
+// ada_pool_bwd_kernel, dv_t[c] = sum_i (ds_i,g(c)[t] u_i[c] + p_i,g(c)[t] dout_i[c]); v = (x + LN(q)) / sqrt(8), so
+// dx_t = dv_t / sqrt(8) and dq_t = LayerNorm'(dv_t / sqrt(8)) (no affine).  One warp per token, rows written as bf16.
+// (AdaEmbedding builds its poolers with infeat_grad_scale = 1, embedding_manager.py:667: the gradient is not scaled.)
+template <int kChunks>
+__global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_feat_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
+    const uint8_t* __restrict__ key_mask, const float* __restrict__ stats, const float* __restrict__ out_fg,
+    const float* __restrict__ out_bg, const float* __restrict__ d_fg, const float* __restrict__ d_bg,
+    __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dqo, int N, int C, int tokens_per_block) {
+  extern __shared__ float sh[];
+  float* s_u = sh;                       // [2][C]
+  float* s_d = s_u + 2 * C;              // [2][C] dout
+  float* s_part = s_d + 2 * C;           // [8 warps][4][kChunks * 32]
+  __shared__ float s_delta[kHeads], s_m[kHeads], s_l[kHeads];
+  const int dg = C / kHeads;
+  const int b = blockIdx.y, blk = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) {
+    s_u[idx] = u[static_cast<long long>(b) * 2 * C + idx];
+    s_d[idx] = idx < C ? d_fg[static_cast<long long>(b) * C + idx] : d_bg[static_cast<long long>(b) * C + idx - C];
+  }
+  if (threadIdx.x < kHeads) {
+    s_m[threadIdx.x] = stats[(static_cast<long long>(b) * kHeads + threadIdx.x) * 2];
+    s_l[threadIdx.x] = stats[(static_cast<long long>(b) * kHeads + threadIdx.x) * 2 + 1];
+  }
+  __syncthreads();
+  if (warp < kHeads) {
+    float a = 0.f;
+    for (int c = lane; c < dg; c += 32) {
+      const int cc = warp * dg + c;
+      a += s_d[cc] * out_fg[static_cast<long long>(b) * C + cc] + s_d[C + cc] * out_bg[static_cast<long long>(b) * C + cc];
+    }
+    a = warp_sum(a);
+    if (lane == 0) s_delta[warp] = a;
+  }
+  __syncthreads();
+  const int nchunks = C >> 3;
+  const int chunks_per_group = dg >> 3;
+  float* my_part = s_part + warp * 4 * (kChunks * 32);
+  const int t_begin = blk * tokens_per_block;
+  const int t_end = min(N, t_begin + tokens_per_block);
+  for (int t = t_begin + warp; t < t_end; t += kPbWarps) {
+    const long long rowoff = (static_cast<long long>(b) * N + t) * C;
+    const uint4* xr = reinterpret_cast<const uint4*>(x + rowoff);
+    const uint4* qr = reinterpret_cast<const uint4*>(q + rowoff);
+    float vv[kChunks][8], kh[kChunks][8];        // v, then dv / sqrt(8);  q, then LN(q)
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+        unpack8f(xr[ch], vv[i]);
+        unpack8f(qr[ch], kh[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += kh[i][j];
+      }
+    }
+    const float mean = warp_sum(s) / C;
+    float m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i)
+      if (lane + 32 * i < nchunks)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = kh[i][j] - mean;
+          m2 += d * d;
+        }
+    const float rstd = rsqrtf(warp_sum(m2) / C + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+        float a_fg = 0.f, a_bg = 0.f, p_fg = 0.f, p_bg = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          kh[i][j] = (kh[i][j] - mean) * rstd;
+          vv[i][j] = (vv[i][j] + kh[i][j]) * kInvSqrt8;
+          a_fg += s_u[ch * 8 + j] * vv[i][j];
+          a_bg += s_u[C + ch * 8 + j] * vv[i][j];
+          p_fg += s_d[ch * 8 + j] * vv[i][j];
+          p_bg += s_d[C + ch * 8 + j] * vv[i][j];
+        }
+        my_part[ch] = a_fg;
+        my_part[kChunks * 32 + ch] = a_bg;
+        my_part[2 * kChunks * 32 + ch] = p_fg;
+        my_part[3 * kChunks * 32 + ch] = p_bg;
+      }
+    }
+    __syncwarp();
+    float sc = 0.f, dp = 0.f;
+    if (lane < 16) {
+      const float* pp = my_part + (lane >> 3) * (kChunks * 32) + (lane & 7) * chunks_per_group;
+      const float* pd = pp + 2 * (kChunks * 32);
+      for (int kk = 0; kk < chunks_per_group; ++kk) {
+        sc += pp[kk];
+        dp += pd[kk];
+      }
+    }
+    __syncwarp();
+    float tot = sc;
+    tot += __shfl_xor_sync(0xffffffffu, tot, 1);
+    tot += __shfl_xor_sync(0xffffffffu, tot, 2);
+    tot += __shfl_xor_sync(0xffffffffu, tot, 4);
+    sc = 0.5f * sc + 0.5f * (tot * 0.125f);
+    const bool masked = key_mask != nullptr && key_mask[static_cast<long long>(b) * N + t] == 0;
+    const int g = lane & 7;
+    float pr = 0.f;
+    if (lane < 16 && !masked) pr = __expf(sc - s_m[g]) / s_l[g];
+    const float dsp = pr * (dp - s_delta[g]);
+    float dtot = dsp;
+    dtot += __shfl_xor_sync(0xffffffffu, dtot, 1);
+    dtot += __shfl_xor_sync(0xffffffffu, dtot, 2);
+    dtot += __shfl_xor_sync(0xffffffffu, dtot, 4);
+    const float ds = 0.5f * dsp + 0.5f * (dtot * 0.125f);
+    float sg = 0.f, sga = 0.f;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      const bool ok = ch < nchunks;
+      const int gg = ok ? ch / chunks_per_group : 0;
+      const float f_ds = __shfl_sync(0xffffffffu, ds, gg), b_ds = __shfl_sync(0xffffffffu, ds, 8 + gg);
+      const float f_p = __shfl_sync(0xffffffffu, pr, gg), b_p = __shfl_sync(0xffffffffu, pr, 8 + gg);
+      if (ok) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c = ch * 8 + j;
+          const float gx = (f_ds * s_u[c] + b_ds * s_u[C + c] + f_p * s_d[c] + b_p * s_d[C + c]) * kInvSqrt8;
+          vv[i][j] = gx;
+          sg += gx;
+          sga = fmaf(gx, kh[i][j], sga);
+        }
+      }
+    }
+    const float mg = warp_sum(sg) / C, mga = warp_sum(sga) / C;
+#pragma unroll
+    for (int i = 0; i < kChunks; ++i) {
+      const int ch = lane + 32 * i;
+      if (ch < nchunks) {
+        float o[8];
+        reinterpret_cast<uint4*>(dx + rowoff)[ch] = pack8f(vv[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (vv[i][j] - mg - kh[i][j] * mga);
+        reinterpret_cast<uint4*>(dqo + rowoff)[ch] = pack8f(o);
+      }
+    }
+  }
+}
+
+}  // namespace
+}  // namespace afb
+
+extern "C" int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
+                                         const float* stats, const float* fg_out, const float* bg_out, const float* d_fg,
+                                         const float* d_bg, afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels,
+                                         afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(x && q && pool_q && stats && fg_out && bg_out && d_fg && d_bg && dx && dq, "afb_ada_pool_bwd_features: NULL argument");
+  AFB_REQUIRE(batch > 0 && n_tokens > 0 && channels % 64 == 0 && channels <= 1280, "afb_ada_pool_bwd_features: bad sizes");
+  const uintptr_t all = reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(dx) |
+                        reinterpret_cast<uintptr_t>(dq);
+  AFB_REQUIRE((all & 15) == 0, "afb_ada_pool_bwd_features: x / q / dx / dq must be 16-byte aligned");
+  const int C = channels;
+  int blocks = 4 * num_sms() / batch;
+  const int max_blocks = (n_tokens + 7) / 8;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  const int tokens_per_block = (n_tokens + blocks - 1) / blocks;
+  dim3 grid((n_tokens + tokens_per_block - 1) / tokens_per_block, batch);
+  const int cpl = (C / 8 + 31) / 32;
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(q);
+  __nv_bfloat16* dxb = reinterpret_cast<__nv_bfloat16*>(dx);
+  __nv_bfloat16* dqb = reinterpret_cast<__nv_bfloat16*>(dq);
+#define AFB_LAUNCH_PBF(KCH)                                                                                         \
+  {                                                                                                                 \
+    auto kern = ada_pool_bwd_feat_kernel<KCH>;                                                                      \
+    const size_t shb = (4 * static_cast<size_t>(C) + kPbWarps * 4 * (KCH * 32)) * sizeof(float);                    \
+    static size_t set_for = 0;                                                                                      \
+    if (set_for < shb) {                                                                                            \
+      AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(shb))); \
+      set_for = shb;                                                                                                \
+    }                                                                                                               \
+    kern<<<grid, kPbThreads, shb, stream>>>(xb, qb, pool_q, key_mask, stats, fg_out, bg_out, d_fg, d_bg, dxb, dqb, n_tokens, C, \
+                                            tokens_per_block);                                                      \
+  }
+  if (cpl <= 2) AFB_LAUNCH_PBF(2)
+  else if (cpl <= 3) AFB_LAUNCH_PBF(3)
+  else AFB_LAUNCH_PBF(5)
+#undef AFB_LAUNCH_PBF
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -97,10 +97,6 @@ class AttentionalPooler(nn.Module, _PackedWeights):
         if img_mask is not None:                                                                # :259-269
             m = F.interpolate(img_mask.float(), size=infeat_size, mode="nearest").reshape(b, -1)
             key_mask = m.bool().to(torch.uint8).contiguous()
-        if self._differentiated():
-            # the pooler differentiates w.r.t. its queries; the gradient towards the layer features is not built, so the
-            # features enter as constants (the reference scales that gradient path by infeat_grad_scale, :128-131)
-            x, q = x.detach(), q.detach()
         fg, bg, a_fg, a_bg = ops.ada_pool(as_bf16_tokens(x), as_bf16_tokens(q), pool_q, key_mask, want_attn)
         out = {"fg_out": fg, "bg_out": bg}
         if want_attn:

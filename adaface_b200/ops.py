@@ -1086,23 +1086,6 @@ def _ada_head_backward(ctx, g):
 ada_head.register_autograd(_ada_head_backward, setup_context=_ada_head_setup)
 
 
-def _ada_pool_setup(ctx, inputs, output):
-    x, q, pool_q, key_mask, want_attn = inputs
-    if x.requires_grad or q.requires_grad:
-        raise NotImplementedError("adaface_b200: the pooler's backward towards the layer features (x, q) is not built; it "
-                                  "differentiates w.r.t. the pooling queries only (detach x and q)")
-    ctx.save_for_backward(x, q, pool_q, key_mask)
-
-
-def _ada_pool_backward(ctx, g_fg, g_bg, g_afg, g_abg):
-    x, q, pool_q, key_mask = ctx.saved_tensors
-    z = lambda g: torch.zeros((x.shape[0], x.shape[2]), dtype=torch.float32, device=x.device) if g is None else g
-    return None, None, ada_pool_bwd(x, q, pool_q, key_mask, z(g_fg), z(g_bg)), None, None
-
-
-ada_pool.register_autograd(_ada_pool_backward, setup_context=_ada_pool_setup)
-
-
 def _ada_pool_prep_setup(ctx, inputs, output):
     to_k_weight, fg_q_emb, bg_q_emb, wf, wb, wk = inputs
     _frozen(to_k_weight)
@@ -1116,3 +1099,186 @@ def _ada_pool_prep_backward(ctx, g):
 
 
 ada_pool_prep.register_autograd(_ada_pool_prep_backward, setup_context=_ada_pool_prep_setup)
+
+
+# ---- second stage: self-attention, GroupNorm and the pooler's gradient towards the layer features --------------------
+@torch.library.custom_op("adaface_b200::attention_lse", mutates_args=())
+def attention_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float) -> Tuple[Tensor, Tensor]:
+    """`attention` that also returns the log2-domain log-sum-exp of every query row, fp32 [B, heads, Nq] - what the
+    backward needs to rebuild the probabilities.  Used instead of `attention` while gradients are recorded."""
+    _need_cuda(q, k, v)
+    b, nq, c = q.shape
+    nk = k.shape[1]
+    if k.shape != v.shape or k.shape[0] != b or k.shape[2] != c or c % heads:
+        raise ValueError("attention_lse: shape mismatch")
+    out = torch.empty((b, nq, c), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((b, heads, nq), dtype=torch.float32, device=q.device)
+    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=None, batch=b, heads=heads,
+                    head_dim=c // heads, q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"),
+                    ldo=c, scale=scale, lse=_ptr(lse))
+    _run("attention_fwd", _lib.load().afb_attention_fwd, C.byref(args), _stream(), flops=4.0 * b * nq * nk * c,
+         nbytes=2.0 * b * c * (2 * nq + 2 * nk), tag=f"b{b}q{nq}k{nk}d{c // heads}")
+    return out, lse
+
+
+@attention_lse.register_fake
+def _(q, k, v, heads, scale):
+    return q.new_empty(q.shape, dtype=torch.bfloat16), q.new_empty((q.shape[0], heads, q.shape[1]), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::attention_bwd", mutates_args=())
+def attention_bwd(q: Tensor, k: Tensor, v: Tensor, out: Tensor, lse: Tensor, dout: Tensor, heads: int,
+                  scale: float) -> Tuple[Tensor, Tensor, Tensor]:
+    """Backward of `attention_lse` for any key length (self-attention): -> (dq, dk, dv) fp32 [B, L, C]."""
+    _need_cuda(q, k, v, out, lse, dout)
+    b, nq, c = q.shape
+    nk = k.shape[1]
+    out, dout, lse = out.contiguous(), dout.contiguous(), lse.contiguous()
+    if dout.dtype != torch.bfloat16 or dout.shape != q.shape or out.shape != q.shape:
+        raise ValueError("attention_bwd: out / dout must be bf16 of q's shape")
+    dev = q.device
+    dq = torch.empty((b, nq, c), dtype=torch.float32, device=dev)
+    dk = torch.empty((b, nk, c), dtype=torch.float32, device=dev)
+    dv = torch.empty((b, nk, c), dtype=torch.float32, device=dev)
+    ws = torch.empty((b * heads * nq,), dtype=torch.float32, device=dev)
+    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=None, batch=b, heads=heads,
+                    head_dim=c // heads, q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"),
+                    ldo=c, scale=scale, lse=_ptr(lse))
+    _run("attention_bwd", _lib.load().afb_attention_bwd, C.byref(args), _ptr(dout), _ptr(ws), _ptr(dq), _ptr(dk), _ptr(dv), c,
+         _stream(), flops=10.0 * b * nq * nk * c, tag=f"b{b}q{nq}k{nk}d{c // heads}")
+    return dq, dk, dv
+
+
+@attention_bwd.register_fake
+def _(q, k, v, out, lse, dout, heads, scale):
+    f = lambda t: t.new_empty(t.shape, dtype=torch.float32)
+    return f(q), f(k), f(v)
+
+
+def _attention_lse_setup(ctx, inputs, output):
+    q, k, v, heads, scale = inputs
+    out, lse = output
+    ctx.save_for_backward(q, k, v, out, lse)
+    ctx.heads, ctx.scale = heads, scale
+
+
+def _attention_lse_backward(ctx, g, g_lse):
+    q, k, v, out, lse = ctx.saved_tensors
+    dq, dk, dv = attention_bwd(q, k, v, out, lse, _bf16c(g), ctx.heads, ctx.scale)
+    return dq.to(q.dtype), dk.to(k.dtype), dv.to(v.dtype), None, None
+
+
+attention_lse.register_autograd(_attention_lse_backward, setup_context=_attention_lse_setup)
+
+
+def attention_auto(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float, key_mask: Optional[Tensor]) -> Tensor:
+    """`attention`, or - while gradients are recorded through a long key sequence - `attention_lse`, whose backward
+    covers self-attention.  (The short-key backward of `attention` needs no saved statistics.)"""
+    if torch.is_grad_enabled() and k.shape[1] > 128 and (q.requires_grad or k.requires_grad or v.requires_grad):
+        if key_mask is not None:
+            raise NotImplementedError("adaface_b200: the self-attention backward with a key mask is not built")
+        return attention_lse(q, k, v, heads, scale)[0]
+    return attention(q, k, v, heads, scale, key_mask)
+
+
+@torch.library.custom_op("adaface_b200::groupnorm_tokens_bwd", mutates_args=())
+def groupnorm_tokens_bwd(x: Tensor, grad_y: Tensor, gamma: Tensor, groups: int, eps: float) -> Tensor:
+    """Backward of `groupnorm_tokens` (no activation, no pre-add) for a bf16 channels-last x [B,C,h,w] and grad_y bf16
+    [B, h*w, C] -> dx bf16 channels-last [B,C,h,w]."""
+    _need_cuda(x, grad_y, gamma)
+    b, c, h, w = x.shape
+    if x.dtype != torch.bfloat16 or not x.permute(0, 2, 3, 1).is_contiguous():
+        raise NotImplementedError("groupnorm_tokens_bwd: only the bf16 channels-last layout is built")
+    grad_y = _bf16c(grad_y)
+    dx = torch.empty_like(x)                                  # preserves channels-last
+    _run("groupnorm_tokens_bwd", _lib.load().afb_groupnorm_tokens_bwd, _ptr(x), _ptr(grad_y), _ptr(gamma.detach().float().contiguous()),
+         _ptr(dx), b, c, h * w, groups, eps, _stream(), nbytes=6.0 * x.numel(), tag=f"b{b}n{h * w}C{c}")
+    return dx
+
+
+@groupnorm_tokens_bwd.register_fake
+def _(x, grad_y, gamma, groups, eps):
+    return torch.empty_like(x)
+
+
+def _gn_setup(ctx, inputs, output):
+    x, gamma, beta, groups, eps, act, pre_add = inputs
+    _frozen(gamma, beta)
+    if act != 0 or pre_add is not None:
+        raise NotImplementedError("adaface_b200: the backward of the GroupNorm + SiLU / pre-add fusion of the ResBlocks is "
+                                  "not built (ResBlocks take their torch path while gradients are recorded)")
+    ctx.save_for_backward(x, gamma)
+    ctx.groups, ctx.eps = groups, eps
+
+
+def _gn_backward(ctx, g):
+    x, gamma = ctx.saved_tensors
+    return groupnorm_tokens_bwd(x, g, gamma, ctx.groups, ctx.eps), None, None, None, None, None, None
+
+
+groupnorm_tokens.register_autograd(_gn_backward, setup_context=_gn_setup)
+
+
+def _abr_setup(ctx, inputs, output):
+    a, b, bias = inputs
+    _frozen(bias)
+    ctx.b_needs = b is not None and b.requires_grad
+    ctx.a_needs = a.requires_grad
+
+
+def _abr_backward(ctx, g):
+    return (g if ctx.a_needs else None), (g if ctx.b_needs else None), None
+
+
+add_bias_residual.register_autograd(_abr_backward, setup_context=_abr_setup)
+
+
+@torch.library.custom_op("adaface_b200::ada_pool_bwd_features", mutates_args=())
+def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor,
+                          d_bg: Tensor) -> Tuple[Tensor, Tensor]:
+    """Backward of `ada_pool` towards the layer features: -> (dx, dq) bf16 [B, N, C]."""
+    _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg)
+    b, n, c = x.shape
+    lib = _lib.load()
+    dev = x.device
+    x, q = x.contiguous(), q.contiguous()
+    pool_q = pool_q.detach().to(torch.float32).contiguous()
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
+    ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
+    fg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    bg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
+         b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+    stats = ws[ws.numel() - b * 16:]
+    d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
+    dx, dq = torch.empty_like(x), torch.empty_like(q)
+    _run("ada_pool_bwd_features", lib.afb_ada_pool_bwd_features, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats),
+         _ptr(fg), _ptr(bg), _ptr(d_fg), _ptr(d_bg), _ptr(dx), _ptr(dq), b, n, c, _stream(), nbytes=8.0 * b * n * c,
+         tag=f"b{b}n{n}C{c}")
+    return dx, dq
+
+
+@ada_pool_bwd_features.register_fake
+def _(x, q, pool_q, key_mask, d_fg, d_bg):
+    return torch.empty_like(x), torch.empty_like(q)
+
+
+def _ada_pool_setup2(ctx, inputs, output):
+    x, q, pool_q, key_mask, want_attn = inputs
+    ctx.save_for_backward(x, q, pool_q, key_mask)
+    ctx.feat_needs, ctx.q_needs = x.requires_grad or q.requires_grad, pool_q.requires_grad
+
+
+def _ada_pool_backward2(ctx, g_fg, g_bg, g_afg, g_abg):
+    x, q, pool_q, key_mask = ctx.saved_tensors
+    z = lambda g: torch.zeros((x.shape[0], x.shape[2]), dtype=torch.float32, device=x.device) if g is None else g
+    g_fg, g_bg = z(g_fg), z(g_bg)
+    d_pq = ada_pool_bwd(x, q, pool_q, key_mask, g_fg, g_bg) if ctx.q_needs else None
+    dx = dq = None
+    if ctx.feat_needs:
+        dx, dq = ada_pool_bwd_features(x, q, pool_q, key_mask, g_fg, g_bg)
+    return dx, dq, d_pq, None, None
+
+
+ada_pool.register_autograd(_ada_pool_backward2, setup_context=_ada_pool_setup2)

@@ -65,8 +65,26 @@ class GroupNorm32(nn.GroupNorm):
         raise RuntimeError("GroupNorm32 is applied through gn_silu() together with the SiLU that follows it")
 
 
+def _differentiated(*ts) -> bool:
+    """True when gradients are being recorded through one of the tensors (the inversion step, BASELINE.json configs[3]).
+    The ResBlocks, up / down-sampling and the output head - outside the hot path, north_star keeps them on torch - then
+    run as plain differentiable torch ops (fp32 GroupNorm + SiLU, bf16 cuDNN convolutions) instead of this repo's fused
+    forward-only kernels; the SpatialTransformers keep their kernels and use the backward of csrc/backward.cu."""
+    return torch.is_grad_enabled() and any(isinstance(t, torch.Tensor) and t.requires_grad for t in ts)
+
+
+def _gn_silu_torch(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Tensor:
+    h = x.float()
+    if pre_add is not None:
+        h = h + pre_add.float()[:, :, None, None]
+    h = F.silu(F.group_norm(h, gn.num_groups, gn.weight.detach().float(), gn.bias.detach().float(), gn.eps))
+    return h.to(torch.bfloat16).contiguous(memory_format=CL)
+
+
 def gn_silu(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Tensor:
     """x bf16 channels-last [B, C, H, W] -> SiLU(GroupNorm(x + pre_add[:, :, None, None])), same format."""
+    if _differentiated(x):
+        return _gn_silu_torch(gn, x, pre_add)
     b, c, h, w = x.shape
     x = x.contiguous(memory_format=CL)
     y = ops.groupnorm_tokens(x, gn.weight.detach(), gn.bias.detach(), gn.num_groups, gn.eps, 1, pre_add)
@@ -124,7 +142,7 @@ class _Bf16Conv(nn.Conv2d):
     def native_ok(self, x) -> bool:
         """True when this convolution runs as an implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3)
         instead of cuDNN: AFB_CONV=1 and a supported geometry."""
-        if _NATIVE_CONV == "0":
+        if _NATIVE_CONV == "0" or _differentiated(x):      # (the implicit-GEMM convolution has no backward: cuDNN via torch)
             return False
         if _NATIVE_CONV == "auto":
             return (self.in_channels, self.out_channels, x.shape[3]) in _NATIVE_CONV_AUTO and self.geometry_ok(x)
@@ -201,7 +219,7 @@ class Upsample(nn.Module):
             return self._forward(x)
 
     def _forward(self, x):
-        if self.use_conv and _NATIVE_UPSAMPLE and self.conv.geometry_ok(x) \
+        if self.use_conv and _NATIVE_UPSAMPLE and self.conv.geometry_ok(x) and not _differentiated(x) \
                 and (self.out_channels % 160 == 0 or self.out_channels % 128 == 0):
             # nearest-2x upsampling folded into the convolution: four 2x2 phase convolutions of the low-res image
             b, c, h, w = x.shape
@@ -294,11 +312,31 @@ class ResBlock(TimestepBlock):
         with ops.scope("resblock"):
             return self._forward(x, emb)
 
+    def _forward_torch(self, x, emb):
+        """openaimodel.py:259-279 as differentiable torch ops (frozen bf16 weights), used while gradients are recorded."""
+        if isinstance(x, CatPair):
+            x = x.cat()
+        conv1, conv2 = self.in_layers[2], self.out_layers[3]
+        h = F.conv2d(_gn_silu_torch(self.in_layers[0], x), conv1._w()[0], None, conv1.stride, conv1.padding)
+        if isinstance(emb, EmbBundle):
+            pre = emb.per_block[id(self)]
+        else:
+            pre = self.emb_layers(emb).float() + conv1.bias.detach().float()
+        h = _gn_silu_torch(self.out_layers[0], h, pre)
+        w2, b2 = conv2._w()
+        h = F.conv2d(h, w2, b2, conv2.stride, conv2.padding)
+        if not isinstance(self.skip_connection, nn.Identity):
+            ws, bs = self.skip_connection._w()
+            x = F.conv2d(x, ws, bs)
+        return (x + h).contiguous(memory_format=CL)
+
     def _forward(self, x, emb):
         """openaimodel.py:259-279.  The conv1 bias and the time-embedding add are folded into out_layers' GroupNorm
         (pre_add), conv2's bias and the skip add are one vectorised pass."""
         if self.training and self.out_layers[2].p > 0:
             raise NotImplementedError("adaface_b200.ResBlock: dropout > 0 in training mode is not supported")
+        if _differentiated(*((x.a, x.b) if isinstance(x, CatPair) else (x,))):
+            return self._forward_torch(x, emb)
         pair = None
         if isinstance(x, CatPair):
             if x.virtual() and not isinstance(self.skip_connection, nn.Identity):

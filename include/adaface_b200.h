@@ -168,6 +168,9 @@ typedef struct afb_attn_args {
   int q_len, kv_len;
   int64_t ldq, ldk, ldv, ldo;
   float scale;
+  /* optional (NULL to skip): fp32 [B, heads, q_len], the log-sum-exp of the scaled scores of every query row in the
+   * log2 domain, lse = log2(sum_k 2^(scale * log2(e) * s_k)); what afb_attention_bwd needs to rebuild the probabilities */
+  float* lse;
 } afb_attn_args;
 int afb_attention_fwd(const afb_attn_args* args, afb_stream_t stream);
 
@@ -292,6 +295,21 @@ int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const float* pool_q, 
 int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k,
                           const float* d_pool_q, float* d_lora_to_fg_q, float* d_lora_to_bg_q, float* d_lora_to_k, int batch,
                           int channels, afb_stream_t stream);
+
+/* Second stage: what carries a layer's gradient further down the U-Net.
+ * afb_attention_bwd: any key length (self-attention), no key mask.  args as in the forward call that produced args->out
+ *   and args->lse (both required); dout bf16 with the row pitch of out (ldo); delta_ws fp32 [B * heads * q_len];
+ *   dq (zeroed inside), dk, dv fp32 [B * len, ldg].  CUDA-core arithmetic: a first, correct version.
+ * afb_groupnorm_tokens_bwd: GroupNorm without activation, token-major bf16 x / grad_y [B, HW, C] -> dx bf16.
+ * afb_ada_pool_bwd_features: the pooler's gradient towards x and q (bf16 [B, N, C] each); other arguments as
+ *   afb_ada_pool_bwd. */
+int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout, float* delta_ws, float* dq, float* dk, float* dv,
+                      int64_t ldg, afb_stream_t stream);
+int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, afb_bf16* dx, int batch, int channels,
+                             int hw, int groups, float eps, afb_stream_t stream);
+int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
+                              const float* stats, const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg,
+                              afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels, afb_stream_t stream);
 
 /* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */
 int afb_cast_f32_to_bf16(const float* src, afb_bf16* dst, int64_t n, afb_stream_t stream);
