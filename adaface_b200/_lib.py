@@ -63,6 +63,7 @@ _SIGNATURES = {
     "afb_softmax_pv": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I64, _I64, _P]),
     "afb_ada_pool_ws_floats": (_I64, [_I, _I, _I]),
     "afb_ada_pool_prep_ws_floats": (_I64, [_I, _I]),
+    "afb_ada_pool_stats_offset": (_I64, [_I, _I, _I]),
     "afb_ada_pool_prep": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "afb_ada_pool_prep_batched": (_I, [_P, _I, _I, _I, _I, _P]),
     "afb_ada_pool": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),

@@ -643,6 +643,15 @@ extern "C" int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels)
          + static_cast<int64_t>(batch) * kHeads * 2;                // merged (max, sum)
 }
 
+extern "C" int64_t afb_ada_pool_stats_offset(int batch, int n_tokens, int channels) {
+  // where afb_ada_pool leaves the merged softmax statistics [B, 8, 2] inside its workspace (same geometry as the launch)
+  using namespace afb;
+  const int nblocks = pool_blocks_per_sample(batch, n_tokens, channels);
+  const int tokens_per_block = (n_tokens + nblocks - 1) / nblocks;
+  const int grid_x = (n_tokens + tokens_per_block - 1) / tokens_per_block;
+  return static_cast<int64_t>(batch) * kHeads * 2 * n_tokens + static_cast<int64_t>(batch) * grid_x * pool_partial_floats(channels);
+}
+
 extern "C" int64_t afb_ada_pool_prep_ws_floats(int batch, int channels) {
   return (static_cast<int64_t>(batch) + 1) * channels;
 }

@@ -932,7 +932,8 @@ def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor
     bg = torch.empty((b, c), dtype=torch.float32, device=dev)
     _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
          b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
-    stats = ws[ws.numel() - b * 16:]                     # the forward's merged (max, sum) per (sample, head)
+    off = int(lib.afb_ada_pool_stats_offset(b, n, c))       # the forward's merged (max, sum) per (sample, head)
+    stats = ws[off:off + b * 16]
     d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
     d_pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=dev)
     _run("ada_pool_bwd", lib.afb_ada_pool_bwd, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats), _ptr(fg), _ptr(bg),
@@ -1250,7 +1251,8 @@ def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Option
     bg = torch.empty((b, c), dtype=torch.float32, device=dev)
     _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
          b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
-    stats = ws[ws.numel() - b * 16:]
+    off = int(lib.afb_ada_pool_stats_offset(b, n, c))       # the forward's merged (max, sum) per (sample, head)
+    stats = ws[off:off + b * 16]
     d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
     dx, dq = torch.empty_like(x), torch.empty_like(q)
     _run("ada_pool_bwd_features", lib.afb_ada_pool_bwd_features, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats),

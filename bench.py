@@ -715,6 +715,125 @@ def run_ours(args):
         raise SystemExit(3)
 
 
+def run_inversion(args):
+    """--workload config4 (BASELINE.json configs[3], an extra measurement beside the headline metric): one AdaPrompt
+    inversion training step per "step" - batch 8 per GPU at 64x64, no CFG pair, one random timestep per sample,
+    eps = U-Net(q_sample(x_start, t, noise)) with the 16 AdaEmbedding layers wired in, loss = MSE(eps, noise)
+    (ddpm.py:3567-3591 with unit masks), backward through the frozen U-Net to the AdaEmbedding parameters (3.81 M values),
+    ONE flat NCCL all-reduce of those gradients (the design's only training collective, main.py:862 DDP in the
+    reference), AdamW step.  Everything inside the timed region; device time, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    steps = args.steps if args.steps is not None else 10
+    warmup = max(args.warmup if args.warmup is not None else 3, 3)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    torch.backends.cudnn.benchmark = True
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from adaface_b200 import _lib, ops
+    from adaface_b200.sampling import FlatGradAllReduce
+    from adaface_b200.unet import AdaPromptContext, AdaSubject, DiffusionModel
+    b = N_SAMPLES
+    unet, adas = build_modules(1)
+    unet, ada = unet.to(dev).requires_grad_(False), adas[0].to(dev)
+    x_all, c_all, _, probes, extra = synthetic_inputs(b * world, 1, LATENT)
+    lo = rank * b
+    x_start, ctx = x_all[lo:lo + b].to(dev), c_all[16 * lo:16 * (lo + b)].to(dev)
+    ada_ctx = AdaPromptContext([AdaSubject(ada, subject_positions(0), probes[0].to(dev), extra[0][:, lo:lo + b].contiguous().to(dev),
+                                           n_instances=b)])
+    info = {"use_layerwise_context": True, "is_training": True, "use_conv_attn_kernel_size": -1, "placeholder2indices": None,
+            "ada_prompt": ada_ctx}
+    model = DiffusionModel(unet, use_cuda_graph=False)
+    params = [p for p in ada.parameters() if p.requires_grad]
+    reducer = FlatGradAllReduce(params).attach()
+    opt = torch.optim.AdamW(params, lr=1e-5, foreach=True)
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    ar0, ar1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    bw0 = torch.cuda.Event(enable_timing=True)
+
+    def step():
+        t = torch.randint(0, 1000, (b,), device=dev, generator=gen)
+        noise = torch.randn(x_start.shape, device=dev, generator=gen)
+        x_noisy = model.q_sample(x_start, t, noise)
+        eps = unet(x_noisy, t, context=ctx, extra_info=info)
+        loss = ((eps.float() - noise) ** 2).mean()
+        bw0.record()
+        loss.backward()
+        ar0.record()
+        reducer()
+        ar1.record()
+        opt.step()
+        opt.zero_grad(set_to_none=False)
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        tt = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    for _ in range(warmup):
+        loss = step()
+    n0 = _lib.launch_count()
+    step()
+    torch.cuda.synchronize()
+    launches = _lib.launch_count() - n0
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        loss = step()
+    e1.record()
+    barrier()
+    clk = clocks.stop()
+    ms = max_over_ranks(e0.elapsed_time(e1) / steps)
+    ar_ms = max_over_ranks(ar0.elapsed_time(ar1))
+    bw_ms = max_over_ranks(bw0.elapsed_time(ar0))
+    finite = bool(torch.isfinite(loss)) and all(bool(torch.isfinite(p.grad).all()) for p in params)
+    # kernel breakdown of one instrumented step (forward and backward kernels by name)
+    torch.cuda.synchronize()
+    ops.start_timing()
+    step()
+    recs = ops.stop_timing()
+    groups = {}
+    for r_ in recs:
+        gk = groups.setdefault(r_["name"], {"ms": 0.0, "launches": 0})
+        gk["ms"] += r_["ms"]; gk["launches"] += 1
+    if rank == 0:
+        line = {"metric": "inversion_steps_per_s", "value": world * 1e3 / ms, "unit": "steps/s", "n_gpus": world, "steps": steps,
+                "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": f"BASELINE.json configs[3]: AdaPrompt inversion training step, batch {b} per GPU at "
+                                       f"{8 * LATENT}x{8 * LATENT} ({LATENT}x{LATENT} latent), no CFG pair, random timesteps, MSE(eps, noise), "
+                                       f"backward through the frozen SD-1.5 U-Net to the AdaEmbedding parameters "
+                                       f"({sum(p.numel() for p in params)} values), one flat NCCL all-reduce, AdamW; {world} GPU(s)",
+                           "batch_per_gpu": b, "trainable_values": sum(p.numel() for p in params),
+                           "parallelism": f"data parallel over {world} GPU(s): one all-reduce of {4 * reducer.flat.numel()} bytes per step"},
+                "clocks": clk, "finite": finite, "loss": float(loss),
+                "backward_ms": bw_ms, "allreduce_ms": ar_ms, "allreduce_share": ar_ms / ms,
+                "gpu_launches": launches * steps, "gpu_launches_per_step": launches,
+                "kernels": {k: {"ms": round(v["ms"], 3), "launches": v["launches"]} for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])},
+                "note": "parity of this step: tests/test_backward_gpu.py (gradients vs fp32 autograd through the port); the "
+                        "self-attention backward is a first CUDA-core version, which is what dominates the step"}
+        print(json.dumps(line), file=_RESULT_OUT, flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 _RESULT_OUT = sys.stdout
 
 
@@ -733,7 +852,7 @@ def main():
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket one eager step with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     ap.add_argument("--dump-kernels", default=None, help="write the per-shape kernel breakdown of one step as CSV")
-    ap.add_argument("--workload", default=None, choices=["config2", "config3", "config5"],
+    ap.add_argument("--workload", default=None, choices=["config2", "config3", "config4", "config5"],
                     help="config2 (default at N = 1, the benchmarked one): 64x64 latents, 8 samples + CFG pair per GPU; config3 "
                          "(default at N > 1): the 64-sample two-subject job sharded over the ranks; config5: 96x96 latents, 16 "
                          "samples + CFG pair (BASELINE.json configs[4] geometry; an extra data point)")
@@ -750,6 +869,8 @@ def main():
         args.workload = "config2"
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "config4":
+        run_inversion(args)
     else:
         run_ours(args)
 

@@ -203,6 +203,9 @@ int afb_softmax_pv(const float* sim, const afb_bf16* v, float* attn, afb_bf16* o
  *   ws: fp32 workspace of afb_ada_pool_ws_floats(B, N, C) floats. */
 int64_t afb_ada_pool_ws_floats(int batch, int n_tokens, int channels);
 int64_t afb_ada_pool_prep_ws_floats(int batch, int channels);
+/* offset (in floats) inside afb_ada_pool's workspace of the merged softmax statistics fp32 [B, 8, 2] = (max, sum) per
+ * (sample, head) that the call leaves behind - the `stats` argument of afb_ada_pool_bwd / afb_ada_pool_bwd_features */
+int64_t afb_ada_pool_stats_offset(int batch, int n_tokens, int channels);
 int afb_ada_pool_prep(const float* to_k_weight, int ctx_dim, const float* fg_q_emb, const float* bg_q_emb,
                       const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k, float* pool_q,
                       float* prep_ws, int batch, int channels, afb_stream_t stream);

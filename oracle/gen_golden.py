@@ -104,6 +104,20 @@ def case_conv_attn(ref, name="conv_attn", seed=14):
     _save(name, meta=np.array([heads, d, hw, b, t, seed]), **outs)
 
 
+def case_conv_attn_ks4(ref, name="conv_attn_ks4", seed=24):
+    """replace_rows_by_conv_attn with ks = 4 (the asymmetric 1,2,1,2 padding branch, ldm/util.py:754): 16 subject tokens
+    per instance at positions 6..21."""
+    heads, d, hw, b, t = 8, 40, 8, 3, 77
+    n = hw * hw
+    q = P.randn(f"{name}.q", (b * heads, n, d), seed)
+    k = P.randn(f"{name}.k", (b * heads, t, d), seed)
+    sim = P.randn(f"{name}.sim", (b * heads, n, t), seed)
+    idx_b = torch.tensor([0] * 16 + [2] * 16)
+    idx_n = torch.tensor(list(range(6, 22)) * 2)
+    out = ref.util.replace_rows_by_conv_attn(sim, q, k, (idx_b, idx_n), (hw, hw), 4, heads, d ** -0.5)
+    _save(name, meta=np.array([heads, d, hw, b, t, seed]), out_ks4=out)
+
+
 def build_ref_ada(ref, seed, K=9, r=12):
     sd = P.init_ada_embedding(seed, K, r, 2)
     ada = ref.embedding_manager.AdaEmbedding(num_vectors_per_subj_token=K, fg_emb_count=5, bg_emb_count=4,
@@ -452,6 +466,8 @@ def main(argv):
             case_attn_vars(ref)
         elif name == "conv_attn":
             case_conv_attn(ref)
+        elif name == "conv_attn_ks4":
+            case_conv_attn_ks4(ref)
         elif name == "ada":
             case_ada(ref)
         elif name == "ddim":

@@ -119,13 +119,13 @@ def _layer_keys(ca):
              f"layer_coeff_maps.{ca}.weight", f"layer_coeff_maps.{ca}.bias", "pre_vecs", "basis_vecs"])
 
 
-@pytest.mark.parametrize("ca,n", [(0, 400), (3, 256), (6, 64)])
+@pytest.mark.parametrize("ca,n", [(0, 400), (3, 256), (6, 64), (0, 4096)])
 def test_ada_embedding_parameter_gradients(cuda_device, ca, n):
     """AdaEmbedding.forward (pooler + head) at one layer: gradients of every tensor it trains - the three grouped-conv
     pooler weights, the coefficient map, the basis vectors and the bias - against fp32 autograd through the port."""
     import adaface_b200 as afb
     d = cuda_device
-    K, r, b, seed = 9, 12, 3, 71
+    K, r, b, seed = 9, 12, (8 if n >= 4096 else 3), 71     # (8 x 4096: the pooling kernel's one-wave geometry of the bench)
     c = port.CA_INFEAT_DIMS[ca]
     layer_idx = {v: k for k, v in port.LAYER_IDX2CA.items()}[ca]
     asd = P.init_ada_embedding(seed, K, r, 2)

@@ -388,11 +388,11 @@ def test_explicit_cross_attention_matches_fused(ops, cuda_device):
         assert empty.numel() == 0 and torch.equal(out2, out)
 
 
-@pytest.mark.parametrize("ks", [2, 3])
+@pytest.mark.parametrize("ks", [2, 3, 4])
 def test_conv_attn_rows_vs_reference_golden(ops, cuda_device, ks):
     """replace_rows_by_conv_attn (ldm/util.py:701-879) against the output of the reference function itself."""
     from conftest import load_golden
-    name = "conv_attn"
+    name = "conv_attn_ks4" if ks == 4 else "conv_attn"       # ks = 4: its own fixture (16 subject tokens, util.py:754)
     g = load_golden(name)
     heads, dh, hw, b, t, seed = [int(v) for v in g["meta"]]
     n = hw * hw

@@ -170,7 +170,7 @@ def test_cross_attention_save_attn_vars_vs_reference_golden(afb, cuda_device):
         assert rel_l2(act[k], g[k]) < BLOCK_TOL, k
 
 
-@pytest.mark.parametrize("ks", [2, 3])
+@pytest.mark.parametrize("ks", [2, 3, 4])
 def test_cross_attention_conv_attn_rows(afb, cuda_device, ks):
     """attention.py:208-216 through CrossAttention.forward: a callable context that returns placeholder2indices turns
     on the convolutional-attention row replacement for the subject tokens (ks*ks of them) of the listed samples."""
@@ -183,8 +183,9 @@ def test_cross_attention_conv_attn_rows(afb, cuda_device, ks):
     ca.use_conv_attn_kernel_size, ca.infeat_size = ks, (hw, hw)
     x = P.randn("cva.x", (b, n, c), seed)
     ctx = P.randn("cva.ctx", (b, 77, 768), seed)
-    idx_b = torch.tensor([0] * 9 + [2] * 9)
-    idx_n = torch.tensor(list(range(4, 13)) * 2)
+    per = max(9, ks * ks)                                        # ks = 4 needs 16 subject tokens per instance
+    idx_b = torch.tensor([0] * per + [2] * per)
+    idx_n = torch.tensor(list(range(4, 4 + per)) * 2)
     p2i = {"z": (idx_b, idx_n)}
     cd = ctx.to(cuda_device)
     with torch.no_grad():

@@ -71,6 +71,21 @@ def test_conv_attn_rows():
     assert port.replace_rows_by_conv_attn(sim, q, k, (idx_b, idx_n), (hw, hw), 1, heads, d ** -0.5) is sim
 
 
+def test_conv_attn_rows_ks4():
+    """The ks = 4 branch (asymmetric 1,2,1,2 padding, ldm/util.py:754) against the reference function's own output."""
+    name = "conv_attn_ks4"
+    g = load_golden(name)
+    heads, d, hw, b, t, seed = [int(v) for v in g["meta"]]
+    n = hw * hw
+    q = P.randn(f"{name}.q", (b * heads, n, d), seed)
+    k = P.randn(f"{name}.k", (b * heads, t, d), seed)
+    sim = P.randn(f"{name}.sim", (b * heads, n, t), seed)
+    idx_b = torch.tensor([0] * 16 + [2] * 16)
+    idx_n = torch.tensor(list(range(6, 22)) * 2)
+    out = port.replace_rows_by_conv_attn(sim, q, k, (idx_b, idx_n), (hw, hw), 4, heads, d ** -0.5)
+    assert rel_l2(out, g["out_ks4"]) < TOL
+
+
 def _ada_inputs(name, ca_idx, n, b, seed):
     c = P.CA_INFEAT_DIMS[ca_idx]
     return (P.randn(f"{name}.{ca_idx}.x", (b, n, c), seed), P.randn(f"{name}.{ca_idx}.q", (b, n, c), seed, 2.0),
