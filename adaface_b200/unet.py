@@ -83,7 +83,7 @@ def _gn_silu_torch(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None
 
 def gn_silu(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Tensor:
     """x bf16 channels-last [B, C, H, W] -> SiLU(GroupNorm(x + pre_add[:, :, None, None])), same format."""
-    if _differentiated(x):
+    if _differentiated(x, pre_add):
         return _gn_silu_torch(gn, x, pre_add)
     b, c, h, w = x.shape
     x = x.contiguous(memory_format=CL)
@@ -335,7 +335,8 @@ class ResBlock(TimestepBlock):
         (pre_add), conv2's bias and the skip add are one vectorised pass."""
         if self.training and self.out_layers[2].p > 0:
             raise NotImplementedError("adaface_b200.ResBlock: dropout > 0 in training mode is not supported")
-        if _differentiated(*((x.a, x.b) if isinstance(x, CatPair) else (x,))):
+        pre_probe = emb.per_block[id(self)] if isinstance(emb, EmbBundle) else emb
+        if _differentiated(pre_probe, *((x.a, x.b) if isinstance(x, CatPair) else (x,))):
             return self._forward_torch(x, emb)
         pair = None
         if isinstance(x, CatPair):
