@@ -9,6 +9,7 @@
 // (gemm.cu GEGLU / LayerNorm-fold epilogues, attention.cu, ada.cu); matrix products against frozen weights reuse the
 // forward GEMM (dA = dC W), so no weight-gradient GEMM exists on the path.
 #include "common.cuh"
+#include <stdlib.h>
 #include "../../include/adaface_b200.h"
 
 namespace afb {
@@ -992,6 +993,232 @@ __global__ void __launch_bounds__(kAlThreads) attn_bwd_long_kernel(
   }
 }
 
+// ---- the same backward on the tensor cores (warp-level mma.sync m16n8k16, bf16 operands, fp32 accumulation) ------
+// Block = 4 warps, one 64-key tile, walks the 64-row query tiles.  Warp w owns query rows 16w..16w+15 for S = Q K^T,
+// dP = dO V^T and dQ += dS K, and keys 16w..16w+15 of the tile for dV += P^T dO and dK += dS^T Q (accumulators in
+// registers over all query tiles).  Operand tiles live in shared memory as bf16 with padded rows (conflict-free fragment
+// loads); P and dS cross from the score layout to the transposed A operand through shared memory.  kSplit > 1 (d = 160)
+// gives a block only a slice of the output columns to bound the accumulators (the scores are recomputed per slice).
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t ld32(const __nv_bfloat16* p) { return *reinterpret_cast<const uint32_t*>(p); }
+__device__ __forceinline__ uint32_t ld16x2(const __nv_bfloat16* p0, const __nv_bfloat16* p1) {
+  return static_cast<uint32_t>(*reinterpret_cast<const uint16_t*>(p0)) |
+         (static_cast<uint32_t>(*reinterpret_cast<const uint16_t*>(p1)) << 16);
+}
+
+constexpr int kAmThreads = 128;
+constexpr int kAmPS = kAlT + 8;        // row pitch of the P / dS tiles (bf16 elements)
+
+template <int D, int kSplit>
+__global__ void __launch_bounds__(kAmThreads) attn_bwd_mma_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
+    const __nv_bfloat16* __restrict__ dout, const float* __restrict__ lse, const float* __restrict__ delta,
+    float* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv, int q_len, int kv_len, int heads, long long ldq,
+    long long ldk, long long ldv, long long ldo, long long ldg, float scale) {
+  constexpr int DPAD = (D + 15) / 16 * 16;
+  constexpr int LD = DPAD + 8;                   // operand row pitch (bf16 elements)
+  constexpr int CW = DPAD / kSplit;              // output columns of this block
+  constexpr int NT = CW / 8;                     // 8-column accumulator tiles
+  static_assert(CW % 8 == 0, "column slice");
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  __nv_bfloat16* sV = sK + kAlT * LD;
+  __nv_bfloat16* sQ = sV + kAlT * LD;
+  __nv_bfloat16* sO = sQ + kAlT * LD;
+  __nv_bfloat16* sP = sO + kAlT * LD;            // [64][kAmPS]
+  __nv_bfloat16* sS = sP + kAlT * kAmPS;
+  float* sL = reinterpret_cast<float*>(sS + kAlT * kAmPS);     // [64] lse, [64] delta
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int k0 = (blockIdx.x / kSplit) * kAlT;
+  const int cs = (blockIdx.x % kSplit) * CW;     // first output column of this block
+  const int col0 = head * D;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const float scale_log2 = scale * 1.4426950408889634f;
+  const __nv_bfloat16 zero = __float2bfloat16(0.f);
+  // K, V tiles (rows past kv_len and the padding columns are zero)
+  for (int idx = tid; idx < kAlT * (DPAD / 8); idx += kAmThreads) {
+    const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+    uint4 kk = make_uint4(0, 0, 0, 0), vv = kk;
+    if (k0 + r < kv_len && c8 < D) {
+      kk = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * kv_len + k0 + r) * ldk + col0 + c8);
+      vv = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * kv_len + k0 + r) * ldv + col0 + c8);
+    }
+    *reinterpret_cast<uint4*>(sK + r * LD + c8) = kk;
+    *reinterpret_cast<uint4*>(sV + r * LD + c8) = vv;
+  }
+  (void)zero;
+  float acc_k[NT][4], acc_v[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; ++n)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc_k[n][e] = acc_v[n][e] = 0.f;
+
+  for (int r0 = 0; r0 < q_len; r0 += kAlT) {
+    __syncthreads();                              // previous tile fully consumed
+    for (int idx = tid; idx < kAlT * (DPAD / 8); idx += kAmThreads) {
+      const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+      uint4 qq = make_uint4(0, 0, 0, 0), oo = qq;
+      if (r0 + r < q_len && c8 < D) {
+        qq = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * q_len + r0 + r) * ldq + col0 + c8);
+        oo = *reinterpret_cast<const uint4*>(dout + (static_cast<long long>(b) * q_len + r0 + r) * ldo + col0 + c8);
+      }
+      *reinterpret_cast<uint4*>(sQ + r * LD + c8) = qq;
+      *reinterpret_cast<uint4*>(sO + r * LD + c8) = oo;
+    }
+    if (tid < kAlT) {
+      const bool ok = r0 + tid < q_len;
+      const long long li = (static_cast<long long>(b) * heads + head) * q_len + r0 + tid;
+      sL[tid] = ok ? lse[li] : 0.f;
+      sL[kAlT + tid] = ok ? delta[li] : 0.f;
+    }
+    __syncthreads();
+    // ---- S = Q K^T and dP = dO V^T for this warp's 16 rows x 64 keys
+    {
+      float s_acc[8][4], p_acc[8][4];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) s_acc[j][e] = p_acc[j][e] = 0.f;
+      const __nv_bfloat16* qa = sQ + (16 * warp + g) * LD + 2 * t;
+      const __nv_bfloat16* oa = sO + (16 * warp + g) * LD + 2 * t;
+#pragma unroll
+      for (int kk = 0; kk < DPAD / 16; ++kk) {
+        uint32_t aq[4], ao[4];
+        aq[0] = ld32(qa + kk * 16); aq[1] = ld32(qa + 8 * LD + kk * 16); aq[2] = ld32(qa + kk * 16 + 8); aq[3] = ld32(qa + 8 * LD + kk * 16 + 8);
+        ao[0] = ld32(oa + kk * 16); ao[1] = ld32(oa + 8 * LD + kk * 16); ao[2] = ld32(oa + kk * 16 + 8); ao[3] = ld32(oa + 8 * LD + kk * 16 + 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const __nv_bfloat16* kb = sK + (8 * j + g) * LD + kk * 16 + 2 * t;
+          const __nv_bfloat16* vb = sV + (8 * j + g) * LD + kk * 16 + 2 * t;
+          mma_bf16_16816(s_acc[j], aq, ld32(kb), ld32(kb + 8));
+          mma_bf16_16816(p_acc[j], ao, ld32(vb), ld32(vb + 8));
+        }
+      }
+      // P and dS of the rows g and g + 8 of this warp's 16, columns 8 j + 2 t, + 1
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = 16 * warp + g + 8 * half;
+        const bool row_ok = r0 + r < q_len;
+        const float l2 = sL[r], dl = sL[kAlT + r];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c = 8 * j + 2 * t;
+          float pr[2], ds[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const bool ok = row_ok && k0 + c + e < kv_len;
+            pr[e] = ok ? exp2f(s_acc[j][2 * half + e] * scale_log2 - l2) : 0.f;
+            ds[e] = pr[e] * (p_acc[j][2 * half + e] - dl) * scale;
+          }
+          *reinterpret_cast<uint32_t*>(sP + r * kAmPS + c) = pack_bf16x2(pr[0], pr[1]);
+          *reinterpret_cast<uint32_t*>(sS + r * kAmPS + c) = pack_bf16x2(ds[0], ds[1]);
+        }
+      }
+    }
+    __syncwarp();
+    // ---- dQ[16 rows][CW] = dS[16 x 64] K[64 x CW]  (this warp's own rows of dS)
+    {
+      float d_acc[NT][4];
+#pragma unroll
+      for (int n = 0; n < NT; ++n)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) d_acc[n][e] = 0.f;
+      const __nv_bfloat16* sa = sS + (16 * warp + g) * kAmPS + 2 * t;
+#pragma unroll
+      for (int kk = 0; kk < kAlT / 16; ++kk) {
+        uint32_t a[4];
+        a[0] = ld32(sa + kk * 16); a[1] = ld32(sa + 8 * kAmPS + kk * 16); a[2] = ld32(sa + kk * 16 + 8); a[3] = ld32(sa + 8 * kAmPS + kk * 16 + 8);
+        const __nv_bfloat16* kr = sK + (kk * 16 + 2 * t) * LD + cs + g;      // B[k = key][n = column]
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+          mma_bf16_16816(d_acc[n], a, ld16x2(kr + 8 * n, kr + LD + 8 * n), ld16x2(kr + 8 * LD + 8 * n, kr + 9 * LD + 8 * n));
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = r0 + 16 * warp + g + 8 * half;
+        if (r < q_len) {
+          float* dst = dq + (static_cast<long long>(b) * q_len + r) * ldg + col0;
+#pragma unroll
+          for (int n = 0; n < NT; ++n) {
+            const int c = cs + 8 * n + 2 * t;
+            if (c < D) atomicAdd(dst + c, d_acc[n][2 * half]);
+            if (c + 1 < D) atomicAdd(dst + c + 1, d_acc[n][2 * half + 1]);
+          }
+        }
+      }
+    }
+    __syncthreads();                              // every warp's P and dS rows are in shared memory
+    // ---- dV[16 keys][CW] += P^T dO,  dK[16 keys][CW] += dS^T Q  (keys 16 w .. of the tile; A = transposed tiles)
+#pragma unroll
+    for (int kk = 0; kk < kAlT / 16; ++kk) {
+      const __nv_bfloat16* pr = sP + (kk * 16 + 2 * t) * kAmPS + 16 * warp + g;     // A[m = key][k = row] = P[row][key]
+      const __nv_bfloat16* sr = sS + (kk * 16 + 2 * t) * kAmPS + 16 * warp + g;
+      uint32_t ap[4], as[4];
+      ap[0] = ld16x2(pr, pr + kAmPS); ap[1] = ld16x2(pr + 8, pr + kAmPS + 8);
+      ap[2] = ld16x2(pr + 8 * kAmPS, pr + 9 * kAmPS); ap[3] = ld16x2(pr + 8 * kAmPS + 8, pr + 9 * kAmPS + 8);
+      as[0] = ld16x2(sr, sr + kAmPS); as[1] = ld16x2(sr + 8, sr + kAmPS + 8);
+      as[2] = ld16x2(sr + 8 * kAmPS, sr + 9 * kAmPS); as[3] = ld16x2(sr + 8 * kAmPS + 8, sr + 9 * kAmPS + 8);
+      const __nv_bfloat16* orow = sO + (kk * 16 + 2 * t) * LD + cs + g;              // B[k = row][n = column]
+      const __nv_bfloat16* qrow = sQ + (kk * 16 + 2 * t) * LD + cs + g;
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        mma_bf16_16816(acc_v[n], ap, ld16x2(orow + 8 * n, orow + LD + 8 * n), ld16x2(orow + 8 * LD + 8 * n, orow + 9 * LD + 8 * n));
+        mma_bf16_16816(acc_k[n], as, ld16x2(qrow + 8 * n, qrow + LD + 8 * n), ld16x2(qrow + 8 * LD + 8 * n, qrow + 9 * LD + 8 * n));
+      }
+    }
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int key = k0 + 16 * warp + g + 8 * half;
+    if (key < kv_len) {
+      const long long o = (static_cast<long long>(b) * kv_len + key) * ldg + col0;
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        const int c = cs + 8 * n + 2 * t;
+        if (c < D) {
+          dk[o + c] = acc_k[n][2 * half];
+          dv[o + c] = acc_v[n][2 * half];
+        }
+        if (c + 1 < D) {
+          dk[o + c + 1] = acc_k[n][2 * half + 1];
+          dv[o + c + 1] = acc_v[n][2 * half + 1];
+        }
+      }
+    }
+  }
+}
+
+template <int D, int kSplit>
+int launch_attn_bwd_mma(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
+                        long long ldg, cudaStream_t stream) {
+  constexpr int DPAD = (D + 15) / 16 * 16;
+  const size_t sh = (4 * static_cast<size_t>(kAlT) * (DPAD + 8) + 2 * static_cast<size_t>(kAlT) * kAmPS) * 2 + 2 * kAlT * sizeof(float);
+  auto kern = attn_bwd_mma_kernel<D, kSplit>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh)));
+    attr_set = true;
+  }
+  dim3 grid(((a.kv_len + kAlT - 1) / kAlT) * kSplit, a.heads, a.batch);
+  kern<<<grid, kAmThreads, sh, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
+                                         reinterpret_cast<const __nv_bfloat16*>(a.v), dout, a.lse, delta, dq, dk, dv, a.q_len,
+                                         a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale);
+  return 0;
+}
+
+// AFB_ATTN_BWD=simt keeps the CUDA-core version (A/B measurement and cross-check); read once
+bool attn_bwd_mma_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_ATTN_BWD");
+    return e == nullptr || e[0] != 's';
+  }();
+  return on;
+}
+
 template <int D>
 int launch_attn_bwd_long(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
                          long long ldg, cudaStream_t stream) {
@@ -1036,10 +1263,18 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
   count_launch();
   AFB_CHECK_CUDA(cudaMemsetAsync(dq, 0, static_cast<size_t>(rows) * ldg * sizeof(float), stream));
   int rc;
+  // the tensor-core version reads its operands with 16-byte vector loads
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |
+                        reinterpret_cast<uintptr_t>(dout)) & 15) == 0 &&
+                      a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0;
+  const bool mma = attn_bwd_mma_enabled() && vec_ok;
   switch (a.head_dim) {
-    case 40: rc = launch_attn_bwd_long<40>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
-    case 80: rc = launch_attn_bwd_long<80>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
-    case 160: rc = launch_attn_bwd_long<160>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    case 40: rc = mma ? launch_attn_bwd_mma<40, 1>(a, db, delta_ws, dq, dk, dv, ldg, stream)
+                      : launch_attn_bwd_long<40>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    case 80: rc = mma ? launch_attn_bwd_mma<80, 1>(a, db, delta_ws, dq, dk, dv, ldg, stream)
+                      : launch_attn_bwd_long<80>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    case 160: rc = mma ? launch_attn_bwd_mma<160, 2>(a, db, delta_ws, dq, dk, dv, ldg, stream)
+                       : launch_attn_bwd_long<160>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
     default: AFB_FAIL(2, "afb_attention_bwd: head_dim %d not supported (SD-1.5 uses 40, 80, 160)", a.head_dim);
   }
   if (rc) return rc;
