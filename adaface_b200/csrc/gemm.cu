@@ -268,11 +268,19 @@ constexpr int kBoxBytes = kBM * 32 * 2;      // one staging box: 128 rows x 32 b
 
 // kPair: two CTAs of a cluster (one TPC) compute a 256 x BN tile with cta_group::2 MMAs; each stages its own 128
 // rows of A and HALF of the W tile, so the operand bytes an SM pulls from L2 per output drop by 25-30%.
-template <int BN, bool GEGLU, bool kPair = false>
+// kWide (pair mode, STORE epilogues): a unit's tile is 2 * BN columns wide -- every A stage feeds TWO MMAs, one per BN-wide
+// half, so the activation tile crosses the L2 -> SM fabric once per 2 * BN output columns instead of once per BN
+// (operand bytes per CTA and k-block for 2 x 128 x 160 outputs: 16 + 2 * 10 KB instead of 2 * (16 + 10) KB).  The halves
+// are separate accumulators of BN columns rotating through THREE TMEM slots (3 * 160 = 480 of 512 columns): the epilogue
+// and the staging manager keep working on BN-wide half tiles, one slot drains while the other two fill.
+template <int BN, bool GEGLU, bool kPair = false, bool kWide = false>
 struct TCfg {
   static constexpr int kABytes = kBM * kBK * 2;
-  static constexpr int kBRows = kPair ? BN / 2 : BN;
-  static constexpr int kBBytes = kBRows * kBK * 2;
+  static constexpr int kBRows = kPair ? BN / 2 : BN;                  // rows of one W box
+  static constexpr int kBBoxBytes = kBRows * kBK * 2;
+  static constexpr int kHalves = kWide ? 2 : 1;
+  static constexpr int kBBytes = kHalves * kBBoxBytes;
+  static constexpr int kAccSlots = kWide ? 3 : 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kOutChunks = GEGLU ? BN / 64 : BN / 32;        // 32-column output boxes per tile
   // warps 0-3: TMA producer, MMA issuer, TMEM allocator, staging manager; then the epilogue warps, four (one per TMEM
@@ -283,6 +291,10 @@ struct TCfg {
 #ifndef AFB_GEMM_EPI_WARPS
 #define AFB_GEMM_EPI_WARPS 8
 #endif
+  // (wide tiles, measured: the mainloop's operand wait drops by a third, then the MMA issuer waits for a free accumulator
+  //  instead -- a wide tile needs TWO of the three slots, so only one half tile of epilogue overlaps the next mainloop; a
+  //  second team of eight epilogue warps, one per half, changed nothing for that reason: 20.9 vs 19.5 us at
+  //  16384 x 640 x 640, and was removed)
   static constexpr int kEpiWarps = GEGLU ? 16 : AFB_GEMM_EPI_WARPS;
   static constexpr int kGroups = kEpiWarps / 4;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
@@ -292,9 +304,11 @@ struct TCfg {
   static constexpr int kParamBytes = kColParamBytes + kRowParamBytes;
   static constexpr int kBarrierBytes = 512;
   static constexpr int kStages = (227 * 1024 - 1024 - kBarrierBytes - kStagingBytes - kParamBytes) / kStageBytes;
-  static constexpr int kTmemCols = (2 * BN <= 256) ? 256 : 512;
+  static constexpr int kTmemCols = (kAccSlots * BN <= 256) ? 256 : 512;
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kParamBytes + 1024 + kBarrierBytes;
-  static_assert(kBBytes % 1024 == 0, "W tile must keep 1024B alignment of the next stage");
+  static_assert(kAccSlots * BN <= 512, "accumulator slots exceed TMEM");
+  static_assert(!kWide || (kPair && !GEGLU), "wide tiles: pair mode, STORE epilogues");
+  static_assert(kBBoxBytes % 1024 == 0, "W tile must keep 1024B alignment of the next stage");
   static_assert(kStages >= 3 && kStages <= 16, "pipeline depth");
   static_assert(!kPair || BN % 32 == 0, "pair mode: each CTA stages BN/2 rows of W, MMA N must be a multiple of 16");
   static_assert(GEGLU ? BN % 64 == 0 : BN % 32 == 0, "tile width vs output boxes");
@@ -350,14 +364,15 @@ struct GemmTmaDev {
   int k1_blocks;
 };
 
-template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
-__global__ void __launch_bounds__((TCfg<BN, GEGLU, kPair>::kThreads), 1)
+template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair, bool kWide = false>
+__global__ void __launch_bounds__((TCfg<BN, GEGLU, kPair, kWide>::kThreads), 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_res,
                      const __grid_constant__ CUtensorMap tm_a2,
                      const GemmTmaDev p) {
-  using C = TCfg<BN, GEGLU, kPair>;
+  using C = TCfg<BN, GEGLU, kPair, kWide>;
   constexpr int NC = C::kOutChunks;
+  constexpr int kSlots = C::kAccSlots;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + C::kStages * C::kStageBytes;
@@ -367,8 +382,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + C::kStages;
   uint64_t* tmem_full = bars + 2 * C::kStages;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint64_t* out_free = tmem_empty + 2;     // staging buffer b: its TMA stores have finished reading shared memory
+  uint64_t* tmem_empty = tmem_full + 3;
+  uint64_t* out_free = tmem_empty + 3;     // staging buffer b: its TMA stores have finished reading shared memory
   uint64_t* res_full = out_free + 2;       // staging buffer b: residual landed (or: buffer handed to the epilogue)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
 
@@ -392,9 +407,11 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kSlots; ++i) {
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], (kPair ? 2 : 1) * C::kEpiWarps);      // pair: the leader collects both CTAs' epilogue warps
+    }
+    for (int i = 0; i < 2; ++i) {
       mbar_init(&out_free[i], C::kGroups);
       mbar_init(&res_full[i], 1);
     }
@@ -413,7 +430,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   pdl_wait();
   pdl_trigger();
 
-  const int num_tiles = num_m_units * p.num_n_blocks;
+  // tiles of the producer / MMA walk: BN (kWide: 2 * BN) columns wide
+  const int nnb_t = kWide ? p.num_n_blocks >> 1 : p.num_n_blocks;
+  const int num_tiles = num_m_units * nnb_t;
   auto walk_m_blk = [&](const TileWalk& t) { return kPair ? 2 * t.m_unit + cta_rank : t.m_unit; };
 
   if (warp == 0) {
@@ -421,9 +440,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next()) {
+      for (TileWalk t(unit, num_units, nnb_t); t.tile < num_tiles; t.next()) {
         const int m_blk = walk_m_blk(t);
-        const int n_blk = t.n_blk;
+        const int n_blk = kWide ? 2 * t.n_blk : t.n_blk;
         // convolution: the tile's 128 rows are the pixel box (b0.., h0.., w0..) of the image; tap (dy, dx) of the
         // filter reads the same box shifted by (dy, dx), out-of-image pixels zero-filled by TMA (= zero padding)
         int cw0 = 0, ch0 = 0, cb0 = 0, cblk = 0, dy = -1, dx = -1, dx0 = -1, dx_end = 2;
@@ -453,6 +472,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             else if (kb < p.k1_blocks) tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
             else tma_load_2d_pair(&tm_a2, &full_bar[stage], sa, (kb - p.k1_blocks) * kBK, m_blk * kBM);
             tma_load_2d_pair(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN + cta_rank * C::kBRows, kEvictLast);
+            if constexpr (kWide)
+              tma_load_2d_pair(&tm_w, &full_bar[stage], sb + C::kBBoxBytes, kb * kBK, (n_blk + 1) * BN + cta_rank * C::kBRows, kEvictLast);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
             if (p.conv_cblocks != 0) tma_load_4d(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
@@ -489,9 +510,20 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       AFB_GPROF_DECL
       for (int tile = unit; tile < num_tiles; tile += num_units) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        // wide tile: the second half accumulates in the next slot of the ring
+        int acc1 = acc;
+        uint32_t acc1_phase = acc_phase;
+        if constexpr (kWide) {
+          if (++acc1 == kSlots) {
+            acc1 = 0;
+            acc1_phase ^= 1;
+          }
+          mbar_wait(&tmem_empty[acc1], acc1_phase ^ 1);
+        }
+        const uint32_t tmem_d1 = tmem_base + acc1 * BN;
         tc_fence_after();
         AFB_GPROF(0)
-        const uint32_t tmem_d = tmem_base + acc * BN;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -504,6 +536,11 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             for (int k = 0; k < kBK / 16; ++k) {
               if constexpr (kPair) umma_ss_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
               else umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            }
+            if constexpr (kWide) {
+              const uint64_t db1 = umma_desc_kmajor_sw128(sa + C::kABytes + C::kBBoxBytes);
+#pragma unroll
+              for (int k = 0; k < kBK / 16; ++k) umma_ss_pair(tmem_d1, da + 2 * k, db1 + 2 * k, idesc, (kb | k) != 0);
             }
             if constexpr (kPair) umma_commit_pair(&empty_bar[stage]);
             else umma_commit(&empty_bar[stage]);
@@ -518,9 +555,14 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         if (leader) {
           if constexpr (kPair) umma_commit_pair(&tmem_full[acc]);
           else umma_commit(&tmem_full[acc]);
+          if constexpr (kWide) umma_commit_pair(&tmem_full[acc1]);
         }
         __syncwarp();
-        if (++acc == 2) {
+        if constexpr (kWide) {
+          acc = acc1;
+          acc_phase = acc1_phase;
+        }
+        if (++acc == kSlots) {
           acc = 0;
           acc_phase ^= 1;
         }
@@ -535,12 +577,13 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     // (a dependent-load chain of ~2000 cycles per tile when the epilogue warps did it), and prefetches the residual
     // boxes by TMA.
     int it = 0;
-    for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next(), ++it) {
+    for (TileWalk t(unit, num_units, nnb_t); t.tile < num_tiles; t.next())
+    for (int half = 0; half < C::kHalves; ++half, ++it) {      // BN-wide half tiles of a wide tile, in accumulator-slot order
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       // global loads first -- they do not depend on the staging buffer and run ahead of the wait for it
       constexpr int kColVecs = (BN / 4 + 31) / 32;           // float4 per lane covering the tile's BN columns
-      const int n_blk = t.n_blk;
+      const int n_blk = kWide ? 2 * t.n_blk + half : t.n_blk;
       float4 cb[kColVecs], cc[kColVecs];
 #pragma unroll
       for (int u = 0; u < kColVecs; ++u) {
@@ -637,9 +680,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       else mbar_arrive(&tmem_empty[a]);
     };
     AFB_GPROF_DECL
-    for (TileWalk t(unit, num_units, p.num_n_blocks); t.tile < num_tiles; t.next(), ++it) {
+    for (TileWalk t(unit, num_units, nnb_t); t.tile < num_tiles; t.next())
+    for (int half = 0; half < C::kHalves; ++half, ++it) {      // BN-wide half tiles of a wide tile, in accumulator-slot order
       const int m_blk = walk_m_blk(t);
-      const int n_blk = t.n_blk;
+      const int n_blk = kWide ? 2 * t.n_blk + half : t.n_blk;
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       const int m_row = m_blk * kBM + row;
@@ -813,7 +857,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         reinterpret_cast<float2*>(p.stats_out)[static_cast<long long>(m_row) * (C::kGroups * p.num_n_blocks) + C::kGroups * n_blk + grp] =
             make_float2(st_s1, st_s2);
       if (leader) bulk_commit_group();
-      if (++acc == 2) {
+      if (++acc == kSlots) {
         acc = 0;
         acc_phase ^= 1;
       }
@@ -839,9 +883,9 @@ int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows,
   return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, Swizzle::B64);
 }
 
-template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair>
+template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair, bool kWide = false>
 int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
-  using C = TCfg<BN, GEGLU, kPair>;
+  using C = TCfg<BN, GEGLU, kPair, kWide>;
   CUtensorMap tm_a, tm_w, tm_out, tm_res, tm_a2;
   const int64_t k1 = a.a2 != nullptr ? a.k_split : a.k;      // columns of A that come from a.a
   if (a.conv_h > 0) {
@@ -920,7 +964,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   p.nb_per_phase = a.conv_fold != 0 ? static_cast<int>(a.n / 4 / BN) : 1;
   p.conv_h = a.conv_h;
   p.conv_w = a.conv_w;
-  auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats, kPair>;
+  auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats, kPair, kWide>;
   static bool attr_set = false;
   if (!attr_set) {
     AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -928,7 +972,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   }
   int grid;
   if constexpr (kPair) {
-    const int tiles = ((p.num_m_blocks + 1) / 2) * p.num_n_blocks;
+    const int tiles = ((p.num_m_blocks + 1) / 2) * (kWide ? p.num_n_blocks / 2 : p.num_n_blocks);
     const int pairs = tiles < num_sms() / 2 ? tiles : num_sms() / 2;
     grid = 2 * pairs;
   } else {
@@ -950,7 +994,16 @@ bool pair_enabled() {
   return on;
 }
 
-template <int BN, bool GEGLU, bool kPair>
+// AFB_GEMM_WIDE=0 keeps the BN-wide tiles everywhere (A/B measurement); read once
+bool wide_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_GEMM_WIDE");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
+template <int BN, bool GEGLU, bool kPair, bool kWide = false>
 int launch_tma_mode(const afb_gemm_args& a, cudaStream_t stream) {
   const bool ln = a.ln_stats != nullptr, st = a.row_stats_out != nullptr;
   if constexpr (GEGLU) {
@@ -958,16 +1011,30 @@ int launch_tma_mode(const afb_gemm_args& a, cudaStream_t stream) {
               : launch_tma_impl<BN, true, false, false, kPair>(a, stream);
   } else {
     if (ln && st) AFB_FAIL(2, "afb_gemm_bf16: folded LayerNorm and row statistics in one GEMM are not built");
-    if (ln) return launch_tma_impl<BN, false, true, false, kPair>(a, stream);
-    if (st) return launch_tma_impl<BN, false, false, true, kPair>(a, stream);
-    return launch_tma_impl<BN, false, false, false, kPair>(a, stream);
+    if (ln) return launch_tma_impl<BN, false, true, false, kPair, kWide>(a, stream);
+    if (st) return launch_tma_impl<BN, false, false, true, kPair, kWide>(a, stream);
+    return launch_tma_impl<BN, false, false, false, kPair, kWide>(a, stream);
   }
 }
 
 template <int BN, bool GEGLU>
 int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
   // a CTA pair needs two row blocks to share one W tile
-  if (a.m > kBM && pair_enabled()) return launch_tma_mode<BN, GEGLU, true>(a, stream);
+  if (a.m > kBM && pair_enabled()) {
+    // 2 * BN-wide tiles when the columns pair up and there are enough tiles left to fill the pairs of SMs
+    if constexpr (!GEGLU && BN == 160) {
+      // (measured per shape, B200: K >= 1280 gains 2-10 % -- the 3x3 convolutions, FF-out, the C = 1280 projections --,
+      //  K = 640 is even, K = 320 loses 10-15 %: its [65536, 320] activation streams from HBM and the three-stage ring of
+      //  the wide tile is too shallow for that)
+      if (a.n % (2 * BN) == 0 && a.conv_fold == 0 && a.k >= 1280 && wide_enabled()) {
+        // waves x operand KB per CTA and k-block: 16 + 2 * 10 for a wide tile, 16 + 10 for a BN-wide one
+        const int64_t pairs = num_sms() / 2, m_units = (a.m + 2 * kBM - 1) / (2 * kBM);
+        const int64_t wide = (m_units * (a.n / (2 * BN)) + pairs - 1) / pairs * 36, narrow = (m_units * (a.n / BN) + pairs - 1) / pairs * 26;
+        if (wide <= narrow) return launch_tma_mode<BN, GEGLU, true, true>(a, stream);
+      }
+    }
+    return launch_tma_mode<BN, GEGLU, true>(a, stream);
+  }
   return launch_tma_mode<BN, GEGLU, false>(a, stream);
 }
 

@@ -573,14 +573,13 @@ class UNetModel(nn.Module):
                 attn2.__dict__[name] = v[ca] if kind == "layerwise" else v
         return old
 
-    def emb_bundle(self, emb: Tensor) -> EmbBundle:
+    def emb_bundle(self, emb: Tensor, e_all: Optional[Tensor] = None) -> EmbBundle:
         """One Linear for all ResBlocks: rows = concatenated emb_layers[1] weights, bias = emb_layers[1].bias +
         in_layers[2].bias (the conv1 bias rides along into the GroupNorm pre-add)."""
-        blocks = [m for m in self.modules() if isinstance(m, ResBlock)]
-        ps = [p for rb in blocks for p in (rb.emb_layers[1].weight, rb.emb_layers[1].bias, rb.in_layers[2].bias)]
-        key = tuple((p.data_ptr(), p._version) for p in ps)
+        key = self._emb_pack_key()
         pack = self.__dict__.get("_emb_pack")
         if pack is None or pack[0] != key:
+            blocks = self.__dict__["_time_blocks"]
             with torch.no_grad():
                 w = torch.cat([rb.emb_layers[1].weight.detach().float() for rb in blocks], dim=0).to(torch.bfloat16).contiguous()
                 b = torch.cat([rb.emb_layers[1].bias.detach().float() + rb.in_layers[2].bias.detach().float()
@@ -592,13 +591,54 @@ class UNetModel(nn.Module):
             pack = (key, w, b, offs)
             self.__dict__["_emb_pack"] = pack
         _, w, b, offs = pack
+        if e_all is None:
+            e_all = self._emb_project(emb, w, b)
+        return EmbBundle(emb, {i: e_all[:, o:o + n] for i, o, n in offs})
+
+    @staticmethod
+    def _emb_project(emb, w, b):
         # one [B, 1280] x [20160, 1280]^T GEMM on the tcgen05 kernel (bf16 operands, fp32 accumulate and output): the
         # fp32 cuBLAS path streamed 103 MB of weights per step
         if emb.is_cuda and w.shape[0] % 32 == 0:
-            e_all = ops.linear(F.silu(emb).to(torch.bfloat16), w, b, None, True)
-        else:
-            e_all = F.linear(F.silu(emb), w.float(), b)
-        return EmbBundle(emb, {i: e_all[:, o:o + n] for i, o, n in offs})
+            return ops.linear(F.silu(emb).to(torch.bfloat16), w, b, None, True)
+        return F.linear(F.silu(emb), w.float(), b)
+
+    time_table_size = 1000          # LatentDiffusion's num_timesteps (ddpm.py:244-265)
+
+    def time_tables(self):
+        """emb = time_embed(timestep_embedding(t)) (openaimodel.py:846-847) and the ResBlocks' emb_layers projections
+        depend on t alone: both are tabulated once for t = 0..999 (5 + 81 MB of 180 GB) and a U-Net call gathers its rows
+        - two launches instead of the sin/cos + two fp32 GEMMs + SiLU + bf16 GEMM chain of every DDIM step.  Rebuilt
+        when a parameter of time_embed / emb_layers / conv1's bias changes.  Rows are computed by the same kernels as
+        the direct path (row-independent), so the gathered values are the direct path's."""
+        ps = list(self.time_embed.parameters())
+        key = tuple((p.data_ptr(), p._version) for p in ps)
+        tab = self.__dict__.get("_time_tab")
+        if tab is None or tab[0] != key:
+            with torch.no_grad():
+                t_all = torch.arange(self.time_table_size, device=ps[0].device)
+                emb = self.time_embed(timestep_embedding(t_all, self.model_channels)).contiguous()
+                self.emb_bundle(emb[:1])                       # builds / refreshes the packed emb_layers weights
+                _, w, b, _ = self.__dict__["_emb_pack"]
+                tab = (key, emb, self._emb_project(emb, w, b).contiguous(), self.__dict__["_emb_pack"][0])
+            self.__dict__["_time_tab"] = tab
+        elif tab[3] != self._emb_pack_key():
+            self.__dict__["_time_tab"] = None
+            return self.time_tables()
+        return tab[1], tab[2]
+
+    def _time_params(self):
+        """emb_layers[1].weight / .bias and conv1's bias of every ResBlock, then time_embed's four parameters (the list
+        is rebuilt when load_state_dict(assign=True) has replaced the Parameter objects)."""
+        ps = self.__dict__.get("_time_param_list")
+        if ps is None or ps[-1] is not self.time_embed[2].bias or ps[0] is not self.__dict__["_time_blocks"][0].emb_layers[1].weight:
+            blocks = self.__dict__["_time_blocks"] = [m for m in self.modules() if isinstance(m, ResBlock)]
+            ps = [p for rb in blocks for p in (rb.emb_layers[1].weight, rb.emb_layers[1].bias, rb.in_layers[2].bias)]
+            ps = self.__dict__["_time_param_list"] = ps + list(self.time_embed.parameters())
+        return ps
+
+    def _emb_pack_key(self):
+        return tuple((p.data_ptr(), p._version) for p in self._time_params()[:-4])
 
     def forward(self, x: Tensor, timesteps: Optional[Tensor] = None, context: Optional[Tensor] = None, y=None,
                 context_in=None, extra_info: Optional[Dict] = None, **kwargs) -> Tensor:
@@ -613,7 +653,13 @@ class UNetModel(nn.Module):
         ada: Optional[AdaPromptContext] = extra_info.get("ada_prompt", None)
         b = x.shape[0]
 
-        emb = self.time_embed(timestep_embedding(timesteps, self.model_channels))                 # :846-847
+        e_all = None
+        tabulated = x.is_cuda and not timesteps.is_floating_point() and not _differentiated(*self._time_params())
+        if tabulated:                              # rows of the per-timestep tables (t in [0, time_table_size))
+            emb_tab, e_tab = self.time_tables()
+            emb, e_all = emb_tab.index_select(0, timesteps), e_tab.index_select(0, timesteps)
+        else:
+            emb = self.time_embed(timestep_embedding(timesteps, self.model_channels))             # :846-847
         if layerwise:                                                                             # :863-866
             t, d = context.shape[1], context.shape[2]
             ctx = torch.empty((16, b, t, d), dtype=torch.bfloat16, device=x.device)
@@ -646,7 +692,7 @@ class UNetModel(nn.Module):
             p.requires_grad for s_ in ada.subjects for p in s_.embedder.parameters())
         if ada is not None and x.is_cuda and not ada_trains:      # (inversion step: per-layer, differentiable preparation)
             ada.prepare_queries(self.spatial_transformers())
-        bundle = self.emb_bundle(emb)
+        bundle = self.emb_bundle(emb, e_all)
         hs = []
         h = self.input_blocks[0][0].conv_add(x.to(torch.bfloat16).contiguous(memory_format=CL))
         hs.append(h)

@@ -114,7 +114,10 @@ def test_groupnorm_virtual_concat(ops, cuda_device, c1, c2, hw):
 
 # ---------------------------------------------------------------------------------------------- GEMM
 @pytest.mark.parametrize("m,n,k", [(128, 160, 64), (256, 320, 320), (512, 960, 320), (200, 640, 768),
-                                   (1024, 1280, 5120), (64, 1280, 1280), (4096, 320, 1280), (154, 128, 768)])
+                                   (1024, 1280, 5120), (64, 1280, 1280), (4096, 320, 1280), (154, 128, 768),
+                                   # K >= 1280 with enough row blocks: the 320-column wide tiles (csrc/gemm.cu kWide),
+                                   # ragged row tail
+                                   (16384, 640, 1280), (9500, 1280, 1280), (5000, 960, 2560)])
 def test_linear_store(ops, cuda_device, m, n, k):
     a = _r("g.a", (m, k)).to(torch.bfloat16)
     w = _r("g.w", (n, k), k ** -0.5).to(torch.bfloat16)
@@ -241,7 +244,7 @@ def test_linear_geglu(ops, cuda_device, m, c):
     assert rel_l2(out.float(), ref) < 5e-3
 
 
-@pytest.mark.parametrize("m,c", [(256, 320), (200, 640), (77, 1280)])
+@pytest.mark.parametrize("m,c", [(256, 320), (200, 640), (77, 1280), (9500, 1280)])   # the last one: wide tiles
 def test_linear_layernorm_fold(ops, cuda_device, m, c):
     """LayerNorm folded around the GEMMs (attention.py:269-283): the producer GEMM emits per-row sum / sum of squares
     of the bf16 values it stores, the consumer applies rstd * (acc - mean * colsum) + t.  Checked against
