@@ -137,7 +137,7 @@ __device__ __forceinline__ void group_accumulate(float* slots, const float (&s)[
 // pre_add (optional, fp32 [B, C] with row stride pre_add_ld): a per-(sample, channel) vector added to x BEFORE the
 // statistics and the normalisation - the conv bias + time-embedding add that precedes out_layers' GroupNorm in a
 // ResBlock (openaimodel.py:259-279), folded in so that no separate elementwise pass is needed.
-__global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, int C1,
+__global__ void __launch_bounds__(320, 2) gn_partial_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, int C1,
                                                              const float* __restrict__ pre_add,
                                                              int pre_add_ld, float* __restrict__ partial, int C, int HW,
                                                              int cpg, int T, int nchunks) {
@@ -165,12 +165,19 @@ __global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloa
   for (int j = 0; j < 8; ++j) piv[j] = s1[j] = s2[j] = 0.f;
   int n_mine = 0;
   if (row < nt) unpack8(xp[static_cast<long long>(row) * src_vpr], piv);
+  // the next batch of rows is requested before the current one is reduced: the loads never drain
+  uint4 data[kGnUnroll];
+#pragma unroll
+  for (int u = 0; u < kGnUnroll; ++u) {
+    const int tt = row + u * R;
+    if (tt < nt) data[u] = xp[static_cast<long long>(tt) * src_vpr];
+  }
   for (int t = row; t < nt; t += R * kGnUnroll) {
-    uint4 data[kGnUnroll];
+    uint4 next[kGnUnroll];
 #pragma unroll
     for (int u = 0; u < kGnUnroll; ++u) {
-      const int tt = t + u * R;
-      if (tt < nt) data[u] = xp[static_cast<long long>(tt) * src_vpr];
+      const int tt = t + (kGnUnroll + u) * R;
+      if (tt < nt) next[u] = xp[static_cast<long long>(tt) * src_vpr];
     }
 #pragma unroll
     for (int u = 0; u < kGnUnroll; ++u) {
@@ -186,6 +193,8 @@ __global__ void __launch_bounds__(320, 3) gn_partial_tok_kernel(const __nv_bfloa
         ++n_mine;
       }
     }
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) data[u] = next[u];
   }
   // per-channel (n, mean, M2) of this thread's rows; pre_add shifts the mean only
   float add[8];
@@ -322,166 +331,202 @@ __global__ void __launch_bounds__(320, 2) gn_apply_tok_kernel(const __nv_bfloat1
   }
 }
 
-// ---- single-launch variant for samples that fit the shared memory of one thread-block cluster ------------------
-// One cluster of kGnCluster CTAs per sample; CTA r stages its T = ceil(HW / kGnCluster) tokens in shared memory while
-// accumulating the shifted sums, the CTAs exchange their per-group (mean, M2) partials through distributed shared
-// memory, every CTA merges them (Chan) and normalises its tokens straight out of shared memory: x is read from
-// global memory once, one launch instead of two.
-constexpr int kGnCluster = 8;
-constexpr int kGnClusterMaxSmem = 200 * 1024;
+// ---- register-resident slab variant --------------------------------------------------------------------------
+// One CTA = (sample, slab of S = lcm(C/groups, 16) channels = S / cpg WHOLE groups), all HW tokens of the slab held in
+// registers (kItems <= 16 16-byte vectors per thread, <= 320 threads, HW * S * 2 <= 80 KB): x is read once, the variance is the exact two-pass
+// form Sum (x - mean)^2 over the registers, no atomics (deterministic), no second launch, no inter-CTA exchange -- the
+// groups of a slab live in this CTA alone.  A token contributes S * 2 = 160..480 contiguous bytes: whole 32-byte
+// sectors (with S = lcm(cpg, 8) = 40 channels every other slab boundary fell inside a sector, the partial-sector
+// stores made L2 fetch the output lines from DRAM first and the kernel ran at 1.2 TB/s, measured), and the activations
+// of these sizes (<= 21 MB) sit in L2 anyway.
+// Replaces the round-1 8-CTA cluster kernel (span staged in shared memory, partials over DSMEM, two cluster barriers:
+// 10-30 us for 2.6-16 MB tensors against 4.6-11 us here) and the two-kernel path for every tensor whose slab fits.
+constexpr int kGnSlabMaxThreads = 320;
+constexpr int kGnSlabMaxGroups = 8;
 
-template <bool kSilu>
-__global__ void __launch_bounds__(320, 1) gn_cluster_tok_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
-                                                             const float* __restrict__ beta, const float* __restrict__ pre_add,
-                                                             int pre_add_ld, __nv_bfloat16* __restrict__ y, int C, int HW,
-                                                             int cpg, int T, float eps) {
-  namespace cg = cooperative_groups;
-  cg::cluster_group cluster = cg::this_cluster();
-  extern __shared__ __align__(128) uint8_t gn_smem[];
+template <int kItems, bool kSilu>
+__global__ void __launch_bounds__(kGnSlabMaxThreads, 1)
+gn_slab_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, int C1,
+                   const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ pre_add,
+                   int pre_add_ld, __nv_bfloat16* __restrict__ y, int C, int HW, int cpg, int S, int R, float eps) {
+  __shared__ float s_pa[kGnSlabMaxThreads], s_pb[kGnSlabMaxThreads];      // per-thread partials of its (first, second) group
+  __shared__ float s_tot[kGnSlabMaxGroups];
   pdl_wait();
+  const int b = blockIdx.y;
+  const int vps = S >> 3;                               // 16-byte vectors per token of the slab
+  const int vec = threadIdx.x % vps, row = threadIdx.x / vps;
+  const bool valid = row < R;                           // the block is rounded up to whole warps
+  const int c0 = blockIdx.x * S + vec * 8;
+  const int g0 = (blockIdx.x * S) / cpg;                // first group of the slab
+  const int ngroups = S / cpg;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool second = x2 != nullptr && c0 >= C1;        // virtual concatenation: a slab lies in one source (C1 % S == 0)
+  const int src_c = x2 == nullptr ? C : (second ? C - C1 : C1);
+  const __nv_bfloat16* src = (second ? x2 : x) + static_cast<long long>(b) * HW * src_c + (second ? c0 - C1 : c0);
+  uint4 data[kItems];
+#pragma unroll
+  for (int u = 0; u < kItems; ++u) {
+    const int t = row + u * R;
+    if (valid && t < HW) data[u] = *reinterpret_cast<const uint4*>(src + static_cast<long long>(t) * src_c);
+  }
   pdl_trigger();
-  __shared__ float g_sum[kGnMaxGroups], g_m2[kGnMaxGroups];
-  __shared__ float s_part[2 * kGnMaxGroups];            // this CTA's (mean, M2) per group, read by the whole cluster
-  __shared__ float s_mean[kGnMaxGroups], s_rstd[kGnMaxGroups];
-  __shared__ __align__(8) uint64_t load_bar;
-  uint4* tile = reinterpret_cast<uint4*>(gn_smem);
-  const int b = blockIdx.y, rank = static_cast<int>(cluster.block_rank());
-  const int t0 = rank * T;
-  const int nt = max(0, min(T, HW - t0));
-  const int vpr = C >> 3;
-  const int R = blockDim.x / vpr;
-  const int vec = threadIdx.x % vpr, row = threadIdx.x / vpr;
-  const int c0 = vec * 8;
-  const int groups = C / cpg;
-  const long long span0 = (static_cast<long long>(b) * HW + t0) * C;      // first element of this CTA's span
-  const uint32_t span_bytes = static_cast<uint32_t>(nt) * C * 2;
-  constexpr uint32_t kPiece = 32 * 1024;
-  if (threadIdx.x == 0) {
-    mbar_init(&load_bar, 1);
-    fence_barrier_init();
-    if (span_bytes > 0) {
-      mbar_arrive_expect_tx(&load_bar, span_bytes);
-      for (uint32_t off = 0; off < span_bytes; off += kPiece)
-        bulk_load_1d(gn_smem + off, reinterpret_cast<const uint8_t*>(x + span0) + off, min(kPiece, span_bytes - off),
-                     &load_bar);
+  // parameters: requested ahead of the two reduction rounds
+  float add[8], gm[8], bt[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    add[j] = 0.f;
+    gm[j] = 1.f;
+    bt[j] = 0.f;
+  }
+  if (valid) {
+    const float4* gp = reinterpret_cast<const float4*>(gamma + c0);
+    const float4* bp = reinterpret_cast<const float4*>(beta + c0);
+    const float4 ga = __ldg(gp), gb = __ldg(gp + 1), ba = __ldg(bp), bb = __ldg(bp + 1);
+    gm[0] = ga.x; gm[1] = ga.y; gm[2] = ga.z; gm[3] = ga.w; gm[4] = gb.x; gm[5] = gb.y; gm[6] = gb.z; gm[7] = gb.w;
+    bt[0] = ba.x; bt[1] = ba.y; bt[2] = ba.z; bt[3] = ba.w; bt[4] = bb.x; bt[5] = bb.y; bt[6] = bb.z; bt[7] = bb.w;
+    if (pre_add != nullptr) {
+      const float4* ap = reinterpret_cast<const float4*>(pre_add + static_cast<long long>(b) * pre_add_ld + c0);
+      const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+      add[0] = a0.x; add[1] = a0.y; add[2] = a0.z; add[3] = a0.w;
+      add[4] = a1.x; add[5] = a1.y; add[6] = a1.z; add[7] = a1.w;
     }
   }
-  for (int i = threadIdx.x; i < groups; i += blockDim.x) g_sum[i] = g_m2[i] = 0.f;
-  float add[8];
+  // a thread's 8 channels lie in at most two groups (cpg >= 8): channels [0, split) in group ga, the rest in ga + 1
+  const int ga_ = c0 / cpg - g0;
+  const int split = min(8, (g0 + ga_ + 1) * cpg - c0);
+  // block-wide per-group sum of the threads' (first-group, second-group) partials: warp g scans all threads' partials
+  // of group g (thread i's first group follows from i % vps), then one shuffle reduction
+  auto block_group_sum = [&](float pa, float pb) {
+    __syncthreads();                                    // s_tot of the previous round has been read
+    s_pa[threadIdx.x] = valid ? pa : 0.f;
+    s_pb[threadIdx.x] = valid ? pb : 0.f;
+    __syncthreads();
+    for (int g = warp; g < ngroups; g += (blockDim.x >> 5)) {
+      float acc = 0.f;
+      for (int i = lane; i < blockDim.x; i += 32) {
+        const int gi = (blockIdx.x * S + (i % vps) * 8) / cpg - g0;
+        acc += (gi == g ? s_pa[i] : 0.f) + (gi + 1 == g ? s_pb[i] : 0.f);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) s_tot[g] = acc;
+    }
+    __syncthreads();
+  };
+  // ---- mean
+  float s[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) add[j] = 0.f;
-  if (pre_add != nullptr) {
-    const float4* ap = reinterpret_cast<const float4*>(pre_add + static_cast<long long>(b) * pre_add_ld + c0);
-    const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
-    add[0] = a0.x; add[1] = a0.y; add[2] = a0.z; add[3] = a0.w;
-    add[4] = a1.x; add[5] = a1.y; add[6] = a1.z; add[7] = a1.w;
-  }
-  __syncthreads();                                       // barrier initialised, accumulators zeroed
-  if (span_bytes > 0) mbar_wait(&load_bar, 0);
-  float piv[8], s1[8], s2[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) piv[j] = s1[j] = s2[j] = 0.f;
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
   int n_mine = 0;
-  if (row < nt) unpack8(tile[row * vpr + vec], piv);
-  for (int t = row; t < nt; t += R) {
-    float v[8];
-    unpack8(tile[t * vpr + vec], v);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float d = v[j] - piv[j];
-      s1[j] += d;
-      s2[j] = fmaf(d, d, s2[j]);
+  for (int u = 0; u < kItems; ++u) {
+    if (valid && row + u * R < HW) {
+      float v[8];
+      unpack8(data[u], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += v[j];
+      ++n_mine;
     }
-    ++n_mine;
   }
-  const float n = static_cast<float>(n_mine);
-  const float inv = n_mine > 0 ? 1.0f / n : 0.f;
-  float mean_c[8], wsum[8];
+  float pa = 0.f, pb = 0.f;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const float dm = s1[j] * inv;
-    mean_c[j] = piv[j] + dm + add[j];
-    s2[j] = fmaxf(s2[j] - s1[j] * dm, 0.f);
-    wsum[j] = n * mean_c[j];
+    const float v = s[j] + static_cast<float>(n_mine) * add[j];
+    if (j < split) pa += v;
+    else pb += v;
   }
-  group_accumulate(g_sum, wsum, c0, cpg);
-  __syncthreads();
-  const float inv_n = nt > 0 ? 1.0f / static_cast<float>(nt * cpg) : 0.f;
+  block_group_sum(pa, pb);
+  const float inv_n = 1.0f / (static_cast<float>(HW) * static_cast<float>(cpg));
+  const float mean_a = s_tot[ga_] * inv_n, mean_b = split < 8 ? s_tot[ga_ + 1] * inv_n : 0.f;
+  float off[8];                                         // add - mean of the channel's group
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float d = mean_c[j] - g_sum[(c0 + j) / cpg] * inv_n;
-    s2[j] = fmaf(n * d, d, s2[j]);
-  }
-  group_accumulate(g_m2, s2, c0, cpg);
-  __syncthreads();
-  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
-    s_part[2 * g] = g_sum[g] * inv_n;
-    s_part[2 * g + 1] = g_m2[g];
-  }
-  cluster.sync();
-  {
-    // lane r reads CTA r's partial of group g over DSMEM; exact Chan merge
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    for (int g = warp; g < groups; g += nwarps) {
-      float nk = 0.f, mk = 0.f, m2k = 0.f;
-      if (lane < kGnCluster) {
-        const float* remote = cluster.map_shared_rank(s_part, lane);
-        nk = static_cast<float>(max(0, min(T, HW - lane * T)) * cpg);
-        mk = remote[2 * g];
-        m2k = remote[2 * g + 1];
-      }
-      const float tot = warp_sum(nk);
-      const float gmean = warp_sum(nk * mk) / tot;
-      const float d = mk - gmean;
-      const float m2 = warp_sum(m2k + nk * d * d);
-      if (lane == 0) {
-        s_mean[g] = gmean;
-        s_rstd[g] = rsqrtf(m2 / tot + eps);
+  for (int j = 0; j < 8; ++j) off[j] = add[j] - (j < split ? mean_a : mean_b);
+  // ---- variance about the mean
+  pa = 0.f;
+  pb = 0.f;
+#pragma unroll
+  for (int u = 0; u < kItems; ++u) {
+    if (valid && row + u * R < HW) {
+      float v[8];
+      unpack8(data[u], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[j] + off[j];
+        if (j < split) pa = fmaf(d, d, pa);
+        else pb = fmaf(d, d, pb);
       }
     }
   }
-  cluster.sync();                                        // nobody leaves while its partials are being read
+  block_group_sum(pa, pb);
+  if (!valid) return;
+  const float rstd_a = rsqrtf(s_tot[ga_] * inv_n + eps), rstd_b = split < 8 ? rsqrtf(s_tot[ga_ + 1] * inv_n + eps) : 0.f;
   float sc[8], of[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const int g = (c0 + j) / cpg;
-    sc[j] = s_rstd[g] * gamma[c0 + j];
-    of[j] = beta[c0 + j] + (add[j] - s_mean[g]) * sc[j];
+    sc[j] = (j < split ? rstd_a : rstd_b) * gm[j];
+    of[j] = fmaf(off[j], sc[j], bt[j]);
   }
-  // normalise in place in shared memory, then stream the span out with bulk stores
-  for (int t = row; t < nt; t += R) {
-    float v[8];
-    unpack8(tile[t * vpr + vec], v);
+  __nv_bfloat16* dst = y + static_cast<long long>(b) * HW * C + c0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      v[j] = v[j] * sc[j] + of[j];
-      if (kSilu) v[j] = silu(v[j]);
+  for (int u = 0; u < kItems; ++u) {
+    const int t = row + u * R;
+    if (t < HW) {
+      float v[8];
+      unpack8(data[u], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[j] = fmaf(v[j], sc[j], of[j]);
+        if (kSilu) v[j] = silu(v[j]);
+      }
+      *reinterpret_cast<uint4*>(dst + static_cast<long long>(t) * C) =
+          make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
     }
-    tile[t * vpr + vec] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-                                     pack_bf16x2(v[6], v[7]));
-  }
-  fence_proxy_async_smem();
-  __syncthreads();
-  if (threadIdx.x == 0 && span_bytes > 0) {
-    for (uint32_t off = 0; off < span_bytes; off += kPiece)
-      bulk_store_1d(reinterpret_cast<uint8_t*>(y + span0) + off, gn_smem + off, min(kPiece, span_bytes - off));
-    bulk_commit_group();
-    bulk_wait_group_read<0>();
   }
 }
 
-template <bool kSilu>
-int launch_gn_cluster(const __nv_bfloat16* x, const float* gamma, const float* beta, const float* pre_add, int pre_add_ld,
-                      __nv_bfloat16* y, int batch, int C, int HW, int cpg, int T, int threads, size_t smem, float eps,
-                      cudaStream_t stream) {
-  auto kern = gn_cluster_tok_kernel<kSilu>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGnClusterMaxSmem));
-    attr_set = true;
+// AFB_GN_SLAB=0 keeps every tensor on the two-kernel path (A/B measurement); read once
+bool gn_slab_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_GN_SLAB");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
+struct GnSlabGeom {
+  int S, items, R, threads;     // items == 0: the tensor does not fit the slab kernel
+};
+inline GnSlabGeom gn_slab_geom(int batch, int channels, int channels1, bool cat, int hw, int cpg) {
+  GnSlabGeom g{0, 0, 0, 0};
+  int S = cpg;
+  while (S % 16 != 0) S += cpg;                         // lcm(cpg, 16): slabs begin and end on 32-byte sectors
+  if (S > channels || channels % S != 0 || S / cpg > kGnSlabMaxGroups || cpg < 8) return g;
+  if (cat && channels1 % S != 0) return g;
+  if (static_cast<long long>(hw) * S > 40960) return g; // 80 KB of registers per CTA
+  const int vps = S / 8;
+  for (int items = 1; items <= 16; items *= 2) {
+    const int R = (hw + items - 1) / items;
+    const int threads = R * vps;
+    if (threads <= kGnSlabMaxThreads) {
+      // eight and more vectors per thread leave one CTA per SM: beyond two waves the two-kernel path is faster
+      // (measured: [16, 256, 2560] 21.0 vs 19.0 us)
+      if (items >= 8 && static_cast<long long>(channels / S) * batch > 2 * num_sms()) return g;
+      g.S = S;
+      g.items = items;
+      g.R = R;
+      g.threads = (threads + 31) / 32 * 32;
+      return g;
+    }
   }
-  AFB_CHECK_CUDA(launch_pdl(kern, dim3(kGnCluster, batch, 1), dim3(threads, 1, 1), smem, stream, kGnCluster, x, gamma, beta,
-                            pre_add, pre_add_ld, y, C, HW, cpg, T, eps));
+  return g;
+}
+
+template <int kItems>
+int launch_gn_slab(const GnSlabGeom& g, const __nv_bfloat16* x, const __nv_bfloat16* x2, int C1, const float* gamma,
+                   const float* beta, const float* pre_add, int pre_add_ld, __nv_bfloat16* y, int batch, int C, int HW,
+                   int cpg, float eps, int act, cudaStream_t stream) {
+  auto kern = act ? gn_slab_tok_kernel<kItems, true> : gn_slab_tok_kernel<kItems, false>;
+  AFB_CHECK_CUDA(launch_pdl(kern, dim3(C / g.S, batch, 1), dim3(g.threads, 1, 1), 0, stream, 1, x, x2, C1, gamma, beta, pre_add,
+                            pre_add_ld, y, C, HW, cpg, g.S, g.R, eps));
   return 0;
 }
 
@@ -637,17 +682,22 @@ extern "C" int afb_groupnorm_tokens_cat(const void* x, int channels1, const afb_
     AFB_REQUIRE(batch <= 65535, "afb_groupnorm_tokens: batch %d exceeds the grid limit", batch);
     AFB_REQUIRE(pre_add == nullptr || (pre_add_ld >= channels && pre_add_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(pre_add) & 15) == 0),
                 "afb_groupnorm_tokens: pre_add must be 16-byte aligned fp32 [B, C] with a row stride that is a multiple of 4");
-    // samples that fit the shared memory of an 8-CTA cluster: one launch, x read once
-    const int Tc = (hw + kGnCluster - 1) / kGnCluster;
-    const size_t cluster_smem = static_cast<size_t>(Tc) * channels * 2;
-    // (measured on B200: wins for the small late-stage tensors; at 1 MB+ per sample the two-kernel path is faster,
-    //  sixteen 8-CTA clusters with ~160 KB of shared memory each do not all fit the GPCs at once)
-    if (x2 == nullptr && cluster_smem <= static_cast<size_t>(kGnClusterMaxSmem) && static_cast<long long>(hw) * channels <= 512 * 1024) {
-      const int rc = act ? launch_gn_cluster<true>(xb, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, Tc, geo.threads, cluster_smem, eps, stream)
-                         : launch_gn_cluster<false>(xb, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, Tc, geo.threads, cluster_smem, eps, stream);
-      if (rc) return rc;
-      count_launch();
-      return 0;
+    // tensors whose (sample, group-slab) fits the registers of one CTA: one launch, x read once, deterministic
+    if (gn_slab_enabled()) {
+      const GnSlabGeom sg = gn_slab_geom(batch, channels, channels1, x2 != nullptr, hw, cpg);
+      if (sg.items != 0) {
+        int rc = 0;
+        switch (sg.items) {
+          case 1: rc = launch_gn_slab<1>(sg, xb, xb2, channels1, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, eps, act, stream); break;
+          case 2: rc = launch_gn_slab<2>(sg, xb, xb2, channels1, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, eps, act, stream); break;
+          case 4: rc = launch_gn_slab<4>(sg, xb, xb2, channels1, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, eps, act, stream); break;
+          case 8: rc = launch_gn_slab<8>(sg, xb, xb2, channels1, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, eps, act, stream); break;
+          default: rc = launch_gn_slab<16>(sg, xb, xb2, channels1, gamma, beta, pre_add, pre_add_ld, yb, batch, channels, hw, cpg, eps, act, stream); break;
+        }
+        if (rc) return rc;
+        count_launch();
+        return 0;
+      }
     }
     AFB_CHECK_CUDA(launch_pdl(gn_partial_tok_kernel, grid, dim3(geo.threads), 0, stream, 1, xb, xb2, channels1, pre_add, pre_add_ld, partial, channels, hw,
                               cpg, geo.T, geo.nchunks));

@@ -660,10 +660,10 @@ class UNetModel(nn.Module):
             emb, e_all = emb_tab.index_select(0, timesteps), e_tab.index_select(0, timesteps)
         else:
             emb = self.time_embed(timestep_embedding(timesteps, self.model_channels))             # :846-847
-        if layerwise:                                                                             # :863-866
-            t, d = context.shape[1], context.shape[2]
-            ctx = torch.empty((16, b, t, d), dtype=torch.bfloat16, device=x.device)
-            ctx.copy_(context.reshape(b, 16, t, d).permute(1, 0, 2, 3))
+        if isinstance(context, LayerMajorContext):
+            ctx, layerwise = context.ctx, True             # converted ahead by the caller (DiffusionModel, outside its graph)
+        elif layerwise:                                                                           # :863-866
+            ctx = LayerMajorContext.convert(context, b)
         else:
             # the AdaEmbedding wiring splices subject rows into this call's context in place: never into the caller's
             # own tensor (it is reused by every DDIM step and by the CFG concatenation)
@@ -712,6 +712,25 @@ class UNetModel(nn.Module):
             ada.__dict__["_pool_q"] = None
         with ops.scope("resblock"):
             return self.out[2](gn_silu(self.out[0], h)).to(x.dtype).contiguous()
+
+
+class LayerMajorContext:
+    """The layerwise prompt [16*B, T, 768] (instance-major / layer-minor, embedding_manager.py:1345-1349) as the bf16
+    layer-major tensor [16, B, T, 768] the SpatialTransformers read: what UNetModel.forward builds from `context` at
+    every call (openaimodel.py:863-866).  A caller whose prompt does not change between calls converts once and passes
+    this instead (DiffusionModel does, outside its captured graph: 39 us per DDIM step at batch 16).  The AdaEmbedding
+    wiring overwrites the subject-token rows of the cond samples in place at every call - always the same rows, so the
+    tensor can be reused without refreshing."""
+
+    def __init__(self, ctx: Tensor):
+        self.ctx = ctx
+
+    @staticmethod
+    def convert(context: Tensor, b: int) -> Tensor:
+        t, d = context.shape[1], context.shape[2]
+        ctx = torch.empty((16, b, t, d), dtype=torch.bfloat16, device=context.device)
+        ctx.copy_(context.reshape(b, 16, t, d).permute(1, 0, 2, 3))
+        return ctx
 
 
 class DiffusionModel:
@@ -805,8 +824,12 @@ class DiffusionModel:
         if g is not None and g[6] != state:       # weights or conditioning changed since the capture
             del self._graphs[key]
             g = None
+        layerwise = bool(extra_info.get("use_layerwise_context", False))
         if g is None:
-            sx, st, sc = x_noisy.clone(), t.clone(), ctx.clone()
+            sx, st = x_noisy.clone(), t.clone()
+            # layerwise prompts enter the graph already converted to the layer-major bf16 tensor: the conversion runs
+            # outside, and only when the caller's context changed
+            sc = LayerMajorContext(LayerMajorContext.convert(ctx, x_noisy.shape[0])) if layerwise else ctx.clone()
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
@@ -817,13 +840,19 @@ class DiffusionModel:
             with torch.cuda.graph(graph):
                 out = self._run(sx, st, sc, extra_info)
             # the fingerprint is taken AFTER the capture: warm-up builds the weight packs but touches no parameter
-            g = (graph, sx, st, sc, out, extra_info, state)
+            g = (graph, sx, st, sc, out, extra_info, state, [(id(ctx), ctx._version), ctx])
             self._graphs[key] = g
         graph, sx, st, sc, out = g[:5]
         sx.copy_(x_noisy)
         st.copy_(t)
-        if sc.data_ptr() != ctx.data_ptr():
-            sc.copy_(ctx)
+        seen = g[7]                                   # the context last copied in (identity + version), kept alive
+        if seen[0] != (id(ctx), ctx._version):
+            if layerwise:
+                t_, d_ = ctx.shape[1], ctx.shape[2]
+                sc.ctx.copy_(ctx.reshape(x_noisy.shape[0], 16, t_, d_).permute(1, 0, 2, 3))
+            else:
+                sc.copy_(ctx)
+            seen[0], seen[1] = (id(ctx), ctx._version), ctx
         graph.replay()
         return out
 

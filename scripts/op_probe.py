@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""Device time of single ops without host starvation: each case is captured as a CUDA graph of N back-to-back calls and
+the replay is timed with CUDA events.  Usage: python scripts/op_probe.py gn|ada [N]"""
+import sys
+
+import torch
+
+sys.path.insert(0, ".")
+from adaface_b200 import ops  # noqa: E402
+
+
+def timed(fn, n=20, reps=5):
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(n):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / (n * reps)
+
+
+def gn_cases():
+    d = "cuda"
+    for b, hw, c, c2, act in [(16, 4096, 320, 0, 1), (16, 1024, 640, 0, 1), (16, 1024, 320, 0, 1), (16, 256, 1280, 0, 1), (16, 64, 1280, 0, 1),
+                              (16, 64, 2560, 0, 1), (16, 256, 640, 0, 1), (16, 1024, 640, 640, 1), (16, 256, 1280, 1280, 1),
+                              (16, 1024, 640, 320, 1), (16, 256, 1920, 0, 1), (16, 1024, 1280, 0, 0), (16, 256, 1280, 0, 0)]:
+        h = int(hw ** 0.5)
+        ga, be = torch.ones(c + c2, device=d), torch.zeros(c + c2, device=d)
+        x = torch.randn(b, c, h, h, device=d).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        if c2:
+            x2 = torch.randn(b, c2, h, h, device=d).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+            us = timed(lambda: ops.groupnorm_tokens_cat(x, x2, ga, be, 32, 1e-5, act))
+        else:
+            us = timed(lambda: ops.groupnorm_tokens(x, ga, be, 32, 1e-5, act))
+        mb = b * hw * (c + c2) * 4 / 1e6
+        print(f"groupnorm b{b} n{hw} C{c}{'+%d' % c2 if c2 else ''} act{act}: {us:7.2f} us  {mb / us * 1e3 / 1e3:6.2f} TB/s (read + write once)")
+
+
+if __name__ == "__main__":
+    with torch.no_grad():
+        {"gn": gn_cases}[sys.argv[1]]()
