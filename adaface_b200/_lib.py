@@ -22,7 +22,7 @@ class GemmArgs(C.Structure):
                 ("lda", C.c_int64), ("ldw", C.c_int64), ("ldo", C.c_int64), ("ldr", C.c_int64),
                 ("epilogue", C.c_int), ("out_dtype", C.c_int), ("residual_dtype", C.c_int), ("hw", C.c_int),
                 ("row_stats_out", C.c_void_p), ("ln_stats", C.c_void_p), ("ln_colsum", C.c_void_p),
-                ("ln_parts", C.c_int), ("ln_eps", C.c_float), ("conv_h", C.c_int), ("conv_w", C.c_int), ("conv_fold", C.c_int), ("a2", C.c_void_p), ("k_split", C.c_int64), ("lda2", C.c_int64)]
+                ("ln_parts", C.c_int), ("ln_eps", C.c_float), ("conv_h", C.c_int), ("conv_w", C.c_int), ("conv_fold", C.c_int), ("a2", C.c_void_p), ("k_split", C.c_int64), ("lda2", C.c_int64), ("conv_stride", C.c_int)]
 
 
 class AdaPrepItem(C.Structure):

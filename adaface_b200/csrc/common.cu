@@ -61,7 +61,8 @@ int num_sms() {
 }
 
 int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const void* base, const uint64_t* dims,
-                    const uint64_t* strides_bytes, const uint32_t* box, Swizzle swizzle, CUtensorMapL2promotion l2) {
+                    const uint64_t* strides_bytes, const uint32_t* box, Swizzle swizzle, CUtensorMapL2promotion l2,
+                    const uint32_t* element_strides) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) AFB_FAIL(3, "cuTensorMapEncodeTiled is not available (no CUDA driver / device?)");
   cuuint64_t gdims[5];
@@ -71,7 +72,7 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
   for (int i = 0; i < rank; ++i) {
     gdims[i] = dims[i];
     gbox[i] = box[i];
-    estr[i] = 1;
+    estr[i] = element_strides != nullptr ? element_strides[i] : 1;
     if (i + 1 < rank) gstrides[i] = strides_bytes[i];
   }
   CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_NONE;
@@ -94,7 +95,7 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
 }  // namespace afb
 
 extern "C" const char* afb_last_error(void) { return afb::g_error; }
-extern "C" int afb_abi_version(void) { return 11; }
+extern "C" int afb_abi_version(void) { return 12; }
 #ifndef AFB_HEADER_DIGEST
 #define AFB_HEADER_DIGEST "unknown"
 #endif

@@ -39,7 +39,8 @@ enum class Swizzle { None = 0, B32 = 1, B64 = 2, B128 = 3 };
 // rank <= 5; dims[0] is the contiguous dimension; strides_bytes[i] is the stride of dims[i+1].
 int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const void* base,
                     const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
-                    Swizzle swizzle, CUtensorMapL2promotion l2 = CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+                    Swizzle swizzle, CUtensorMapL2promotion l2 = CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    const uint32_t* element_strides = nullptr);   // traversal strides per dimension (NULL: all 1)
 
 #ifdef __CUDACC__
 // ----------------------------------------------------------------------------------------------
@@ -219,6 +220,14 @@ __device__ __forceinline__ void bulk_store_1d(void* gmem, const void* smem, uint
 // TMA store: shared -> global, completion tracked by the issuing thread's bulk async-groups
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem)), "r"(c0), "r"(c1)
+               : "memory");
+}
+// element-wise add of the shared-memory box INTO global memory (the tensor map's data type decides the arithmetic: bf16
+// here): how the K-split partial tiles of one output tile meet without a second pass
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const void* smem, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(map)),
                "r"(smem_u32(smem)), "r"(c0), "r"(c1)
                : "memory");

@@ -356,12 +356,17 @@ struct GemmTmaDev {
   // 3x3 convolution as an implicit GEMM: A is the NHWC image [B, H, W, Cin] behind a 4-D tensor map, the K loop
   // walks (tap, 64-channel block); conv_cblocks = Cin / 64 (0: plain GEMM)
   int conv_cblocks, conv_h, conv_w;
+  int conv_stride;           // 1, or 2: conv_h / conv_w are the OUTPUT size, tap coordinates are 2 * pixel + (dy, dx)
   // nearest-2x upsampling folded into the convolution (conv_fold != 0): output phase (py, px) = n_blk / nb_per_phase
   // is a 2x2 convolution of the LOW-resolution image with taps (py - 1 + a, px - 1 + c); its BN-column blocks store to
   // the pixels (2i + py, 2j + px) of the high-resolution output through a 5-D tensor map; fold_cout = N / 4
   int conv_fold, nb_per_phase, fold_cout;
   // A virtually concatenated along K (plain GEMM only): k-blocks [0, k1_blocks) come from tm_a, the rest from tm_a2
   int k1_blocks;
+  // K split (k_splits > 1): an output tile is computed by k_splits units, each over num_k_blocks / k_splits k-blocks,
+  // and their bf16 partial tiles are ADDED into the pre-zeroed output by TMA reduce-stores; split 0 carries the bias and
+  // the residual.  For launches with fewer tiles than SM pairs and a deep K (the 3x3 convolutions at 8x8: 32 tiles).
+  int k_splits;
 };
 
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair, bool kWide = false>
@@ -431,8 +436,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   pdl_trigger();
 
   // tiles of the producer / MMA walk: BN (kWide: 2 * BN) columns wide
-  const int nnb_t = kWide ? p.num_n_blocks >> 1 : p.num_n_blocks;
+  const int nnb_t = (kWide ? p.num_n_blocks >> 1 : p.num_n_blocks) * p.k_splits;     // the split index is the fastest one
   const int num_tiles = num_m_units * nnb_t;
+  const int kb_per_split = p.num_k_blocks / p.k_splits;
   auto walk_m_blk = [&](const TileWalk& t) { return kPair ? 2 * t.m_unit + cta_rank : t.m_unit; };
 
   if (warp == 0) {
@@ -442,7 +448,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       uint32_t phase = 0;
       for (TileWalk t(unit, num_units, nnb_t); t.tile < num_tiles; t.next()) {
         const int m_blk = walk_m_blk(t);
-        const int n_blk = kWide ? 2 * t.n_blk : t.n_blk;
+        const int split = t.n_blk % p.k_splits, nt_blk = t.n_blk / p.k_splits;
+        const int n_blk = kWide ? 2 * nt_blk : nt_blk;
+        const int kb0 = split * kb_per_split;
         // convolution: the tile's 128 rows are the pixel box (b0.., h0.., w0..) of the image; tap (dy, dx) of the
         // filter reads the same box shifted by (dy, dx), out-of-image pixels zero-filled by TMA (= zero padding)
         int cw0 = 0, ch0 = 0, cb0 = 0, cblk = 0, dy = -1, dx = -1, dx0 = -1, dx_end = 2;
@@ -458,9 +466,14 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             dx0 = (phase & 1) - 1;
             dx = dx0;
             dx_end = dx0 + 2;
+          } else if (kb0 != 0) {                      // a later K split starts inside the tap walk
+            const int tap = kb0 / p.conv_cblocks;
+            cblk = kb0 - tap * p.conv_cblocks;
+            dy = tap / 3 - 1;
+            dx = tap - (tap / 3) * 3 - 1;
           }
         }
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb0 + kb_per_split; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + C::kABytes;
@@ -468,7 +481,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             // both CTAs' bytes are counted on the leader's barrier; the peer's may land before the leader arms the
             // phase (the pending arrival keeps it open), never before the previous phase closed (empty_bar)
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
-            if (p.conv_cblocks != 0) tma_load_4d_pair(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
+            if (p.conv_cblocks != 0) tma_load_4d_pair(&tm_a, &full_bar[stage], sa, cblk * kBK, p.conv_stride * cw0 + dx, p.conv_stride * ch0 + dy, cb0);
             else if (kb < p.k1_blocks) tma_load_2d_pair(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
             else tma_load_2d_pair(&tm_a2, &full_bar[stage], sa, (kb - p.k1_blocks) * kBK, m_blk * kBM);
             tma_load_2d_pair(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN + cta_rank * C::kBRows, kEvictLast);
@@ -476,7 +489,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
               tma_load_2d_pair(&tm_w, &full_bar[stage], sb + C::kBBoxBytes, kb * kBK, (n_blk + 1) * BN + cta_rank * C::kBRows, kEvictLast);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
-            if (p.conv_cblocks != 0) tma_load_4d(&tm_a, &full_bar[stage], sa, cblk * kBK, cw0 + dx, ch0 + dy, cb0);
+            if (p.conv_cblocks != 0) tma_load_4d(&tm_a, &full_bar[stage], sa, cblk * kBK, p.conv_stride * cw0 + dx, p.conv_stride * ch0 + dy, cb0);
             else if (kb < p.k1_blocks) tma_load_2d(&tm_a, &full_bar[stage], sa, kb * kBK, m_blk * kBM);
             else tma_load_2d(&tm_a2, &full_bar[stage], sa, (kb - p.k1_blocks) * kBK, m_blk * kBM);
             tma_load_2d(&tm_w, &full_bar[stage], sb, kb * kBK, n_blk * BN, kEvictLast);
@@ -524,7 +537,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         const uint32_t tmem_d1 = tmem_base + acc1 * BN;
         tc_fence_after();
         AFB_GPROF(0)
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        for (int kb = 0; kb < kb_per_split; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           AFB_GPROF(1)
@@ -583,7 +596,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       // global loads first -- they do not depend on the staging buffer and run ahead of the wait for it
       constexpr int kColVecs = (BN / 4 + 31) / 32;           // float4 per lane covering the tile's BN columns
-      const int n_blk = kWide ? 2 * t.n_blk + half : t.n_blk;
+      const int split = t.n_blk % p.k_splits, nt_blk = t.n_blk / p.k_splits;
+      const int n_blk = kWide ? 2 * nt_blk + half : nt_blk;
+      const bool tile_res = p.has_res && split == 0;      // K split: split 0 carries bias and residual
       float4 cb[kColVecs], cc[kColVecs];
 #pragma unroll
       for (int u = 0; u < kColVecs; ++u) {
@@ -592,7 +607,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         cb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         cc[u] = cb[u];
         if (i < BN / 4 && n0 < p.N) {
-          if (p.bias != nullptr) cb[u] = __ldg(reinterpret_cast<const float4*>(p.bias + n0));
+          if (p.bias != nullptr && split == 0) cb[u] = __ldg(reinterpret_cast<const float4*>(p.bias + n0));
           if constexpr (kLn) cc[u] = __ldg(reinterpret_cast<const float4*>(p.ln_colsum + n0));
         }
       }
@@ -645,7 +660,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         __syncwarp();      // lane 0's arrive below publishes the whole warp's writes
       }
       if (lane == 0) {
-        if (p.has_res) {
+        if (tile_res) {
           const int m_blk = walk_m_blk(t);
           int valid = 0;
 #pragma unroll
@@ -683,7 +698,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
     for (TileWalk t(unit, num_units, nnb_t); t.tile < num_tiles; t.next())
     for (int half = 0; half < C::kHalves; ++half, ++it) {      // BN-wide half tiles of a wide tile, in accumulator-slot order
       const int m_blk = walk_m_blk(t);
-      const int n_blk = kWide ? 2 * t.n_blk + half : t.n_blk;
+      const int split = t.n_blk % p.k_splits, nt_blk = t.n_blk / p.k_splits;
+      const int n_blk = kWide ? 2 * nt_blk + half : nt_blk;
+      const bool tile_res = p.has_res && split == 0;      // K split: split 0 carries bias and residual
       const int sb = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       const int m_row = m_blk * kBM + row;
@@ -801,7 +818,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             unpack_f32x2(v23, v[4 * j + 2], v[4 * j + 3]);
           }
         }
-        if (!GEGLU && p.has_res) {
+        if (!GEGLU && tile_res) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             const uint4 t = *reinterpret_cast<const uint4*>(brow + ((static_cast<uint32_t>(c) ^ sw) << 4));
@@ -842,6 +859,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
             const int r = m0 / p.conv_w;              // merged (sample, low-res row) index of the tile's first pixel
             tma_store_5d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0 - phase * p.fold_cout, phase & 1,
                          m0 - r * p.conv_w, phase >> 1, r);
+          } else if (p.k_splits > 1) {
+            tma_reduce_add_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
           } else {
             tma_store_2d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, m_blk * kBM);
           }
@@ -883,6 +902,22 @@ int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows,
   return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, Swizzle::B64);
 }
 
+// AFB_GEMM_SPLITK=0 never splits K (A/B measurement); read once
+bool splitk_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_GEMM_SPLITK");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
+__global__ void __launch_bounds__(256) zero_bf16_kernel(uint4* __restrict__ p, long long n) {
+  pdl_wait();
+  pdl_trigger();
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 template <int BN, bool GEGLU, bool kLn, bool kStats, bool kPair, bool kWide = false>
 int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   using C = TCfg<BN, GEGLU, kPair, kWide>;
@@ -894,11 +929,16 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
                    H = static_cast<uint64_t>(a.conv_h);
     const uint32_t bw = static_cast<uint32_t>(W < kBM ? W : kBM);
     const uint32_t bh = static_cast<uint32_t>(H < kBM / bw ? H : kBM / bw);
-    const uint64_t dims[4] = {cin, W, H, static_cast<uint64_t>(a.m) / (W * H)};
-    const uint64_t strides[3] = {static_cast<uint64_t>(a.lda) * 2, static_cast<uint64_t>(a.lda) * 2 * W,
-                                 static_cast<uint64_t>(a.lda) * 2 * W * H};
-    const uint32_t box[4] = {kBK, bw, bh, kBM / (bw * bh)};
-    if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.a, dims, strides, box, Swizzle::B128))
+    // stride 2: W, H are the output size; the input image is twice as large and the box walks it with element stride 2
+    const uint32_t cs = a.conv_stride == 2 ? 2u : 1u;
+    const uint64_t Wi = W * cs, Hi = H * cs;
+    const uint64_t dims[4] = {cin, Wi, Hi, static_cast<uint64_t>(a.m) / (W * H)};
+    const uint64_t strides[3] = {static_cast<uint64_t>(a.lda) * 2, static_cast<uint64_t>(a.lda) * 2 * Wi,
+                                 static_cast<uint64_t>(a.lda) * 2 * Wi * Hi};
+    const uint32_t box[4] = {kBK, bw * cs, bh * cs, kBM / (bw * bh)};
+    const uint32_t estr[4] = {1, cs, cs, 1};
+    if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.a, dims, strides, box, Swizzle::B128,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, estr))
       return rc;
   } else {
     const uint64_t dims[2] = {static_cast<uint64_t>(k1), static_cast<uint64_t>(a.m)};
@@ -960,10 +1000,30 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   p.conv_cblocks = a.conv_h > 0 ? static_cast<int>(a.k / taps / kBK) : 0;
   p.conv_fold = a.conv_fold;
   p.k1_blocks = a.a2 != nullptr ? static_cast<int>(k1 / kBK) : p.num_k_blocks;
+  p.k_splits = 1;
+  if constexpr (kPair && !GEGLU && !kLn && !kStats) {
+    // fewer tiles than SM pairs and a deep K: split K so that every pair has work (measured on the 3x3 convolutions at
+    // 8x8, 32 tiles of 180-360 k-blocks on 74 pairs).  The output is zeroed first; partial tiles meet by bf16 reduce-adds.
+    const int tiles = ((p.num_m_blocks + 1) / 2) * (kWide ? p.num_n_blocks / 2 : p.num_n_blocks);
+    const int pairs = num_sms() / 2;
+    if (splitk_enabled() && a.conv_fold == 0 && a.a2 == nullptr && a.residual != a.out && 2 * tiles <= pairs + pairs / 4 && p.num_k_blocks >= 64 &&
+        a.ldo == a.n) {
+      int ks = (pairs + pairs / 4) / tiles;
+      if (ks > 4) ks = 4;
+      while (ks > 1 && p.num_k_blocks % ks != 0) --ks;
+      if (ks > 1) {
+        p.k_splits = ks;
+        AFB_CHECK_CUDA(launch_pdl(zero_bf16_kernel, dim3(static_cast<unsigned>((a.m * a.n / 8 + 255) / 256)), dim3(256), 0, stream, 1,
+                                  reinterpret_cast<uint4*>(a.out), static_cast<long long>(a.m * a.n / 8)));
+        count_launch();
+      }
+    }
+  }
   p.fold_cout = static_cast<int>(a.n / 4);
   p.nb_per_phase = a.conv_fold != 0 ? static_cast<int>(a.n / 4 / BN) : 1;
   p.conv_h = a.conv_h;
   p.conv_w = a.conv_w;
+  p.conv_stride = a.conv_stride == 2 ? 2 : 1;
   auto kern = gemm_bf16_tma_kernel<BN, GEGLU, kLn, kStats, kPair, kWide>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -972,7 +1032,7 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   }
   int grid;
   if constexpr (kPair) {
-    const int tiles = ((p.num_m_blocks + 1) / 2) * (kWide ? p.num_n_blocks / 2 : p.num_n_blocks);
+    const int tiles = ((p.num_m_blocks + 1) / 2) * (kWide ? p.num_n_blocks / 2 : p.num_n_blocks) * p.k_splits;
     const int pairs = tiles < num_sms() / 2 ? tiles : num_sms() / 2;
     grid = 2 * pairs;
   } else {
@@ -1111,6 +1171,8 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
     const int64_t hw = static_cast<int64_t>(a.conv_h) * a.conv_w;
     AFB_REQUIRE(a.conv_h > 0 && a.conv_w > 0 && a.m % hw == 0, "afb_gemm_bf16: conv needs conv_h, conv_w > 0 and M = B*H*W");
     const int taps = a.conv_fold != 0 ? 4 : 9;
+    AFB_REQUIRE(a.conv_stride == 0 || a.conv_stride == 1 || (a.conv_stride == 2 && a.conv_fold == 0),
+                "afb_gemm_bf16: conv_stride must be 1 or 2 (2 not together with conv_fold)");
     AFB_REQUIRE(a.k % (taps * 64) == 0, "afb_gemm_bf16: conv needs K = %d * Cin with Cin %% 64 == 0 (K=%lld)", taps, (long long)a.k);
     AFB_REQUIRE(a.lda >= a.k / taps && a.ldw >= a.k, "afb_gemm_bf16: conv leading dimension smaller than Cin / K");
     if (a.conv_fold != 0) {

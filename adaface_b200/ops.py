@@ -184,7 +184,7 @@ def _(x, gamma, beta, eps):
 def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: Optional[Tensor], epilogue: int,
           ldo: int, ldr: int, hw: int = 0, stats_out: Optional[Tensor] = None, ln_stats: Optional[Tensor] = None,
           ln_colsum: Optional[Tensor] = None, ln_eps: float = 0.0, conv_hw: Optional[Tuple[int, int]] = None,
-          conv_fold: bool = False, a2: Optional[Tensor] = None) -> None:
+          conv_fold: bool = False, a2: Optional[Tensor] = None, conv_stride: int = 1) -> None:
     _need_cuda(a, w, out, bias, residual, stats_out, ln_stats, ln_colsum)
     if ln_stats is not None:
         if ln_colsum is None or ln_stats.dtype != torch.float32 or ln_colsum.dtype != torch.float32 \
@@ -201,11 +201,13 @@ def _gemm(a: Tensor, w: Tensor, out: Tensor, bias: Optional[Tensor], residual: O
                     a2=_ptr(a2), k_split=a.shape[1] if a2 is not None else 0, lda2=a2.stride(0) if a2 is not None else 0,
                     m=a.shape[0], n=w.shape[0], k=w.shape[1] if (conv_hw or a2 is not None) else a.shape[1], lda=a.stride(0), ldw=w.stride(0),
                     ldo=ldo, ldr=ldr, conv_h=conv_hw[0] if conv_hw else 0, conv_w=conv_hw[1] if conv_hw else 0, conv_fold=1 if conv_fold else 0,
-                    epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
+                    conv_stride=conv_stride, epilogue=epilogue, out_dtype=_lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_BF16,
                     residual_dtype=_lib.DT_F32 if (residual is not None and residual.dtype == torch.float32)
                     else _lib.DT_BF16, hw=hw, row_stats_out=_ptr(stats_out), ln_stats=_ptr(ln_stats),
                     ln_colsum=_ptr(ln_colsum), ln_parts=0 if ln_stats is None else ln_stats.shape[1], ln_eps=ln_eps)
-    m, n, k = a.shape[0], w.shape[0], w.shape[1] if (conv_hw or a2 is not None) else a.shape[1]
+    if conv_stride == 2:
+        args.m = a.shape[0] // 4              # output pixels; `a` holds the twice-as-large input image
+    m, n, k = int(args.m), w.shape[0], w.shape[1] if (conv_hw or a2 is not None) else a.shape[1]
     _run(("conv3x3_up2_bf16" if conv_fold else "conv3x3_bf16") if conv_hw else "gemm_bf16", _lib.load().afb_gemm_bf16, C.byref(args), _stream(), flops=2.0 * m * n * k,
          nbytes=2.0 * (m * (k if a2 is not None else a.shape[1]) + n * k) + out.numel() * out.element_size(), tag=f"{m}x{n}x{k}e{epilogue}" + ("c" if a2 is not None else "") + ("s" if stats_out is not None else "") + ("l" if ln_stats is not None else "")
          + ("r" if residual is not None else ""))
@@ -230,6 +232,23 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], residual: Optional[Ten
 @conv3x3.register_fake
 def _(x, w, bias, residual, h, width):
     return x.new_empty((x.shape[0], w.shape[0]), dtype=torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::conv3x3_s2", mutates_args=())
+def conv3x3_s2(x: Tensor, w: Tensor, bias: Optional[Tensor], h: int, width: int) -> Tensor:
+    """3x3 / stride 2 / zero-padding 1 convolution (Downsample.forward, openaimodel.py:138-165) on the same implicit-GEMM
+    kernel: TMA reads tap (dy, dx) of output pixel (i, j) at input pixel (2i + dy, 2j + dx) with an element stride of 2.
+    x: bf16 NHWC pixels [B*h*width, Cin] of the INPUT image (h, width even); returns bf16 [B*(h/2)*(width/2), Cout]."""
+    if x.dim() != 2 or w.dim() != 2 or w.shape[1] != 9 * x.shape[1] or x.shape[0] % (h * width) != 0 or h % 2 or width % 2:
+        raise ValueError("conv3x3_s2: x [B*h*w, Cin] with even h, w and w [Cout, 9*Cin] expected")
+    out = torch.empty((x.shape[0] // 4, w.shape[0]), dtype=torch.bfloat16, device=x.device)
+    _gemm(x, w, out, bias, None, _lib.EPI_STORE, out.stride(0), 0, conv_hw=(h // 2, width // 2), conv_stride=2)
+    return out
+
+
+@conv3x3_s2.register_fake
+def _(x, w, bias, h, width):
+    return x.new_empty((x.shape[0] // 4, w.shape[0]), dtype=torch.bfloat16)
 
 
 def fold_upsample_weight(weight: Tensor) -> Tensor:

@@ -27,13 +27,13 @@ from .embedding import LAYER_IDX2CA_LAYER_IDX, AdaEmbedding
 
 Tensor = torch.Tensor
 CL = torch.channels_last
-# AFB_CONV=1: every eligible 3x3 ResBlock convolution on this repo's implicit-GEMM kernel; 0: all on cuDNN; default
-# "auto": the shapes listed in _NATIVE_CONV_AUTO (cuDNN is faster on the others at batch 16 - its kernels reuse the
-# input tile across the nine taps).  AFB_UPSAMPLE_FOLD=0:
-# Upsample as interpolate + conv instead of the folded four-phase 2x2 convolution.
-_NATIVE_CONV = os.environ.get("AFB_CONV", "auto")
-# (Cin, Cout, width) of the 3x3 convolutions that are faster on the implicit-GEMM kernel than on cuDNN at batch 16
-# (eager CUDA-event times on B200, tools/trace_aten.py vs the bench's per-shape table): the deep-K decoder shapes
+# AFB_CONV=1 (default): every 3x3 convolution with Cin % 64 == 0 - stride 1 and the stride-2 Downsample - on this repo's
+# implicit-GEMM kernel; 0: all on cuDNN; "auto": only the shapes listed in _NATIVE_CONV_AUTO (round 1's default, when
+# cuDNN was faster on the others; with 320-column wide tiles and the K split for the 8x8 images the whole step is even:
+# 15.62 ms all-native vs 15.74 ms "auto", measured).  AFB_UPSAMPLE_FOLD=0: Upsample as interpolate + conv instead of the
+# folded four-phase 2x2 convolution.
+_NATIVE_CONV = os.environ.get("AFB_CONV", "1")
+# (Cin, Cout, width) of the 3x3 convolutions that were faster on the implicit-GEMM kernel than on cuDNN in round 1
 _NATIVE_CONV_AUTO = {(2560, 1280, 16), (960, 320, 64), (1920, 1280, 16), (640, 1280, 16)}
 # AFB_CONV_W="64,32": image widths whose 3x3 convolutions take the native kernel when AFB_CONV=1 (default: all)
 _NATIVE_CONV_W = tuple(int(v) for v in os.environ.get("AFB_CONV_W", "").split(",") if v)
@@ -149,13 +149,17 @@ class _Bf16Conv(nn.Conv2d):
         return (not _NATIVE_CONV_W or x.shape[3] in _NATIVE_CONV_W) and self.geometry_ok(x)
 
     def geometry_ok(self, x) -> bool:
-        """3x3 / stride 1 / padding 1 with Cin % 64 == 0 on an image that tiles into 128-pixel boxes."""
-        if self.kernel_size != (3, 3) or self.stride != (1, 1) or self.padding != (1, 1) \
+        """3x3 / stride 1 or 2 / padding 1 with Cin % 64 == 0 on an (output) image that tiles into 128-pixel boxes."""
+        if self.kernel_size != (3, 3) or self.stride not in ((1, 1), (2, 2)) or self.padding != (1, 1) \
                 or self.dilation != (1, 1) or self.groups != 1:
             return False
         _, c, h, w = x.shape
         if c % 64 or self.out_channels % 32 or x.dtype != torch.bfloat16 or not x.is_cuda:
             return False
+        if self.stride == (2, 2):
+            if h % 2 or w % 2:
+                return False
+            h, w = h // 2, w // 2
         bw = min(w, 128)
         rl = 128 // bw
         return (128 % w == 0 if w < 128 else w % 128 == 0) and (rl % h == 0 if h < rl else h % rl == 0)
@@ -177,6 +181,9 @@ class _Bf16Conv(nn.Conv2d):
         b, c, h, w = x.shape
         wn, _ = self._w_native()
         xt = x.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b * h * w, c)
+        if self.stride == (2, 2):
+            y = ops.conv3x3_s2(xt, wn, bias, h, w)
+            return y.view(b, h // 2, w // 2, self.out_channels).permute(0, 3, 1, 2)
         rt = None if residual is None else residual.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b * h * w, -1)
         y = ops.conv3x3(xt, wn, bias, rt, h, w)
         return y.view(b, h, w, self.out_channels).permute(0, 3, 1, 2)

@@ -147,6 +147,11 @@ typedef struct afb_gemm_args {
    * lda2); k_split % 64 == 0.  The decoder's 1x1 skip convolution over th.cat([h, hs.pop()], 1) in one GEMM. */
   const afb_bf16* a2;
   int64_t k_split, lda2;
+  /* conv_stride = 2 (0 and 1 mean stride 1; conv_fold == 0 only): the stride-2 / padding-1 3x3 convolution of
+   * Downsample.forward (openaimodel.py:138-165).  conv_h, conv_w are then the OUTPUT image size, a is the input image
+   * [B, 2*conv_h, 2*conv_w, Cin], m = B*conv_h*conv_w output pixels; tap (dy, dx) of output pixel (i, j) reads input
+   * pixel (2i + dy, 2j + dx), which TMA fetches with an element stride of 2 along both image axes. */
+  int conv_stride;
 } afb_gemm_args;
 int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
 /* number of (sum, sum of squares) partials per row that a STORE GEMM with n output columns emits */

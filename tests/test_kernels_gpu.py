@@ -156,6 +156,23 @@ def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
     assert rel_l2(to_nchw(ops.conv3x3(wide[:, :cin], wp, bias.to(d), None, h, w)), ref) < 4e-3
 
 
+@pytest.mark.parametrize("b,cin,cout,h,w", [(2, 320, 320, 64, 64), (16, 640, 640, 32, 32), (16, 1280, 1280, 16, 16),
+                                            (3, 64, 160, 16, 16), (1, 128, 128, 8, 64), (5, 64, 32, 8, 8)])
+def test_conv3x3_stride2_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
+    """3x3 / stride 2 / zero padding 1 convolution (Downsample.forward, openaimodel.py:138-165): the same implicit-GEMM
+    kernel with a TMA element stride of 2 on the image axes, against torch's fp32 conv2d."""
+    x = _r("cs.x", (b, cin, h, w)).to(torch.bfloat16)
+    wt = _r("cs.w", (cout, cin, 3, 3), (9 * cin) ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("cs.b", (cout,))
+    ref = torch.nn.functional.conv2d(x.float(), wt.float(), bias, stride=2, padding=1)
+    d = cuda_device
+    xt = x.to(d).permute(0, 2, 3, 1).reshape(b * h * w, cin).contiguous()
+    wp = wt.to(d).permute(0, 2, 3, 1).reshape(cout, 9 * cin).contiguous()
+    y = ops.conv3x3_s2(xt, wp, bias.to(d), h, w)
+    assert y.shape == (b * (h // 2) * (w // 2), cout)
+    assert rel_l2(y.float().view(b, h // 2, w // 2, cout).permute(0, 3, 1, 2), ref) < 4e-3
+
+
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (2, 128, 128, 16, 16), (16, 1280, 1280, 8, 8),
                                             (1, 640, 640, 32, 32), (3, 64, 320, 4, 32), (3, 128, 128, 8, 8),
                                             (5, 64, 160, 4, 4)])
