@@ -57,6 +57,8 @@ _SIGNATURES = {
     "afb_layernorm_bf16": (_I, [_P, _P, _P, _P, _I64, _I, _F, _P]),
     "afb_gemm_bf16": (_I, [C.POINTER(GemmArgs), _P]),
     "afb_gemm_stats_parts": (_I, [_I64]),
+    "afb_im2col3x3_c4": (_I, [_P, _P, _I, _I, _I, _P]),
+    "afb_conv3x3_few_out": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "afb_attention_fwd": (_I, [C.POINTER(AttnArgs), _P]),
     "afb_cross_scores": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I64, _I64, _F, _P]),
     "afb_conv_attn_rows": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I64, _I64, _I, _I, _F, _P]),

@@ -15,7 +15,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_DIR = os.path.join(PKG_DIR, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libadaface_b200.so")
-SOURCES = ["common.cu", "elementwise.cu", "norms.cu", "gemm.cu", "attention.cu", "attn_explicit.cu", "ada.cu", "backward.cu"]
+SOURCES = ["common.cu", "elementwise.cu", "norms.cu", "gemm.cu", "attention.cu", "attn_explicit.cu", "ada.cu", "backward.cu", "conv_small.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-diag-suppress", "550"]
 

@@ -251,6 +251,50 @@ def _(x, w, bias, h, width):
     return x.new_empty((x.shape[0] // 4, w.shape[0]), dtype=torch.bfloat16)
 
 
+@torch.library.custom_op("adaface_b200::conv3x3_c4", mutates_args=())
+def conv3x3_c4(x: Tensor, w64: Tensor, bias: Optional[Tensor], h: int, width: int) -> Tensor:
+    """Conv2d(4, Cout, 3, padding=1) on the latent (the U-Net's first convolution, openaimodel.py:575-579): an im2col
+    into 64-wide rows, then the tcgen05 GEMM.  x: bf16 NHWC pixels [B*h*width, 4]; w64: bf16 [Cout, 64] with column
+    (ky*3 + kx)*4 + c and zeros from 36 on; bias fp32 [Cout].  Returns bf16 [B*h*width, Cout] (NHWC)."""
+    _need_cuda(x, w64, bias)
+    if x.dim() != 2 or x.shape[1] != 4 or x.dtype != torch.bfloat16 or not x.is_contiguous() or w64.shape[1] != 64 \
+            or x.shape[0] % (h * width) != 0:
+        raise ValueError("conv3x3_c4: contiguous bf16 x [B*h*w, 4] and w64 [Cout, 64] expected")
+    cols = torch.empty((x.shape[0], 64), dtype=torch.bfloat16, device=x.device)
+    _run("im2col3x3_c4", _lib.load().afb_im2col3x3_c4, _ptr(x), _ptr(cols), x.shape[0] // (h * width), h, width, _stream(),
+         nbytes=float(x.numel() * 2 * 9 + cols.numel() * 2), tag=f"b{x.shape[0] // (h * width)}h{h}w{width}")
+    out = torch.empty((x.shape[0], w64.shape[0]), dtype=torch.bfloat16, device=x.device)
+    _gemm(cols, w64, out, bias, None, _lib.EPI_STORE, out.stride(0), 0)
+    return out
+
+
+@conv3x3_c4.register_fake
+def _(x, w64, bias, h, width):
+    return x.new_empty((x.shape[0], w64.shape[0]), dtype=torch.bfloat16)
+
+
+@torch.library.custom_op("adaface_b200::conv3x3_few_out", mutates_args=())
+def conv3x3_few_out(x: Tensor, w8: Tensor, bias: Optional[Tensor], cout: int, h: int, width: int) -> Tensor:
+    """Conv2d(C, cout <= 8, 3, padding=1) (the U-Net's last convolution, openaimodel.py:716-720).  x: bf16 NHWC pixels
+    [B*h*width, C], C % 64 == 0; w8: bf16 [8, 9*C] with column (ky*3 + kx)*C + c, rows >= cout zero; bias fp32 [cout].
+    Returns fp32 NCHW [B, cout, h, width]."""
+    _need_cuda(x, w8, bias)
+    if x.dim() != 2 or x.dtype != torch.bfloat16 or not x.is_contiguous() or w8.shape != (8, 9 * x.shape[1]) \
+            or w8.dtype != torch.bfloat16 or not w8.is_contiguous() or x.shape[0] % (h * width) != 0:
+        raise ValueError("conv3x3_few_out: contiguous bf16 x [B*h*w, C] and w8 [8, 9*C] expected")
+    b = x.shape[0] // (h * width)
+    out = torch.empty((b, cout, h, width), dtype=torch.float32, device=x.device)
+    _run("conv3x3_few_out", _lib.load().afb_conv3x3_few_out, _ptr(x), _ptr(w8), _ptr(bias), _ptr(out), b, h, width, x.shape[1],
+         cout, _stream(), flops=2.0 * x.shape[0] * cout * 9 * x.shape[1], nbytes=float(x.numel() * 2 + out.numel() * 4),
+         tag=f"b{b}h{h}w{width}C{x.shape[1]}")
+    return out
+
+
+@conv3x3_few_out.register_fake
+def _(x, w8, bias, cout, h, width):
+    return x.new_empty((x.shape[0] // (h * width), cout, h, width), dtype=torch.float32)
+
+
 def fold_upsample_weight(weight: Tensor) -> Tensor:
     """Conv2d weight [Cout, Cin, 3, 3] -> [4*Cout, 4*Cin] fp32 for `conv3x3_up2`: nearest-2x upsampling followed by the
     3x3 convolution equals, for output phase (py, px), a 2x2 convolution of the low-resolution image whose tap (a, c)

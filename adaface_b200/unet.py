@@ -102,9 +102,9 @@ class CatPair:
         self.shape = (a.shape[0], a.shape[1] + b.shape[1], a.shape[2], a.shape[3])
 
     def virtual(self) -> bool:
-        # small samples take the single-launch cluster GroupNorm, which needs one source tensor
-        _, c, h, w = self.shape
-        return _VIRTUAL_CAT and h * w * c > 512 * 1024 and self.a.shape[1] % 8 == 0 and self.b.shape[1] % 8 == 0
+        # (round 1 materialised small concatenations for its single-source cluster GroupNorm; the slab and two-kernel
+        #  GroupNorms both read two sources)
+        return _VIRTUAL_CAT and self.a.shape[1] % 8 == 0 and self.b.shape[1] % 8 == 0
 
     def cat(self) -> Tensor:
         return torch.cat([self.a, self.b], dim=1).contiguous(memory_format=CL)
@@ -188,7 +188,45 @@ class _Bf16Conv(nn.Conv2d):
         y = ops.conv3x3(xt, wn, bias, rt, h, w)
         return y.view(b, h, w, self.out_channels).permute(0, 3, 1, 2)
 
+    def small_ok(self, x) -> bool:
+        """The two convolutions without a 64-channel side: Conv2d(4, Cout, 3, padding=1) (ops.conv3x3_c4) and
+        Conv2d(C, <= 8, 3, padding=1) (ops.conv3x3_few_out)."""
+        if _NATIVE_CONV == "0" or _differentiated(x) or self.kernel_size != (3, 3) or self.stride != (1, 1) \
+                or self.padding != (1, 1) or self.dilation != (1, 1) or self.groups != 1 or not x.is_cuda \
+                or x.dtype != torch.bfloat16:
+            return False
+        return (self.in_channels == 4 and self.out_channels % 32 == 0) or \
+            (self.in_channels % 64 == 0 and self.out_channels <= 8)
+
+    def _w_small(self):
+        key = (self.weight.data_ptr(), self.weight._version)
+        c = self.__dict__.get("_small_cache")
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                w = self.weight.detach().permute(0, 2, 3, 1).reshape(self.out_channels, -1).float()    # [Cout, 9*Cin]
+                if self.in_channels == 4:
+                    wp = torch.zeros((self.out_channels, 64), dtype=torch.float32, device=w.device)
+                    wp[:, :36] = w
+                else:
+                    wp = torch.zeros((8, w.shape[1]), dtype=torch.float32, device=w.device)
+                    wp[:self.out_channels] = w
+                b = None if self.bias is None else self.bias.detach().float().contiguous()
+            c = (key, wp.to(torch.bfloat16).contiguous(), b)
+            self.__dict__["_small_cache"] = c
+        return c[1], c[2]
+
+    def small(self, x):
+        """x bf16 channels-last [B, C, H, W] -> conv(x) + bias: bf16 channels-last (Cin = 4) or fp32 NCHW (Cout <= 8)."""
+        b, c, h, w = x.shape
+        wp, bias = self._w_small()
+        xt = x.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b * h * w, c)
+        if self.in_channels == 4:
+            return ops.conv3x3_c4(xt, wp, bias, h, w).view(b, h, w, self.out_channels).permute(0, 3, 1, 2)
+        return ops.conv3x3_few_out(xt, wp, bias, self.out_channels, h, w)
+
     def forward(self, x, with_bias: bool = True):
+        if with_bias and self.small_ok(x):
+            return self.small(x)
         if self.native_ok(x):
             return self.native(x, self._w_native()[1] if with_bias else None, None)
         w, b = self._w()
@@ -197,7 +235,7 @@ class _Bf16Conv(nn.Conv2d):
     def conv_add(self, x):
         """conv(x) + bias with the bias added by one vectorised pass (torch adds a cuDNN conv's bias with a slow
         broadcasting elementwise kernel)."""
-        if self.bias is None or self.native_ok(x):
+        if self.bias is None or self.native_ok(x) or self.small_ok(x):
             return self.forward(x, True)
         return add_cl(self.forward(x, False), None, self.bias.detach())
 

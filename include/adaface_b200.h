@@ -154,6 +154,17 @@ typedef struct afb_gemm_args {
   int conv_stride;
 } afb_gemm_args;
 int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream);
+
+/* ---- N1: the two convolutions without a 64-channel side (openaimodel.py:575-579 conv_in, :716-720 conv_out).
+ * afb_im2col3x3_c4: x bf16 NHWC [B, h, w, 4] -> cols bf16 [B*h*w, 64] with cols[p][(ky*3+kx)*4 + c] = the zero-padded
+ * 3x3 neighbourhood of pixel p (columns 36..63 zero); Conv2d(4, Cout, 3, padding=1) is then afb_gemm_bf16 of cols with
+ * the weight as [Cout, 64] (same k order, zero-padded).
+ * afb_conv3x3_few_out: x bf16 NHWC [B, h, w, channels] (channels % 64 == 0), w8 bf16 [8, 9*channels] with
+ * k = (ky*3+kx)*channels + c and rows >= cout zero, bias fp32 [cout] or NULL -> out fp32 NCHW [B, cout, h, w], cout <= 8:
+ * 3x3 / stride 1 / padding 1. */
+int afb_im2col3x3_c4(const afb_bf16* x, afb_bf16* cols, int batch, int h, int w, afb_stream_t stream);
+int afb_conv3x3_few_out(const afb_bf16* x, const afb_bf16* w8, const float* bias, float* out, int batch, int h, int w,
+                        int channels, int cout, afb_stream_t stream);
 /* number of (sum, sum of squares) partials per row that a STORE GEMM with n output columns emits */
 int afb_gemm_stats_parts(int64_t n);
 

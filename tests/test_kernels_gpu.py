@@ -156,6 +156,37 @@ def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
     assert rel_l2(to_nchw(ops.conv3x3(wide[:, :cin], wp, bias.to(d), None, h, w)), ref) < 4e-3
 
 
+@pytest.mark.parametrize("b,cout,h,w", [(2, 320, 64, 64), (3, 320, 24, 40), (1, 64, 5, 7)])
+def test_conv3x3_four_input_channels(ops, cuda_device, b, cout, h, w):
+    """Conv2d(4, Cout, 3, padding=1) on the latent (openaimodel.py:575-579): im2col kernel + tcgen05 GEMM vs torch."""
+    x = _r("c4.x", (b, 4, h, w)).to(torch.bfloat16)
+    wt = _r("c4.w", (cout, 4, 3, 3), 36 ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("c4.b", (cout,))
+    ref = torch.nn.functional.conv2d(x.float(), wt.float(), bias, padding=1)
+    d = cuda_device
+    xt = x.to(d).permute(0, 2, 3, 1).reshape(b * h * w, 4).contiguous()
+    w64 = torch.zeros((cout, 64), dtype=torch.bfloat16, device=d)
+    w64[:, :36] = wt.to(d).permute(0, 2, 3, 1).reshape(cout, 36)
+    y = ops.conv3x3_c4(xt, w64, bias.to(d), h, w)
+    assert rel_l2(y.float().view(b, h, w, cout).permute(0, 3, 1, 2), ref) < 4e-3
+
+
+@pytest.mark.parametrize("b,c,cout,h,w", [(2, 320, 4, 64, 64), (3, 64, 8, 20, 24), (1, 128, 3, 9, 17), (2, 320, 4, 96, 96)])
+def test_conv3x3_few_output_channels(ops, cuda_device, b, c, cout, h, w):
+    """Conv2d(C, <= 8, 3, padding=1) -> fp32 NCHW (the U-Net's last convolution, openaimodel.py:716-720) vs torch."""
+    x = _r("cf.x", (b, c, h, w)).to(torch.bfloat16)
+    wt = _r("cf.w", (cout, c, 3, 3), (9 * c) ** -0.5).to(torch.bfloat16)
+    bias = 0.1 * _r("cf.b", (cout,))
+    ref = torch.nn.functional.conv2d(x.float(), wt.float(), bias, padding=1)
+    d = cuda_device
+    xt = x.to(d).permute(0, 2, 3, 1).reshape(b * h * w, c).contiguous()
+    w8 = torch.zeros((8, 9 * c), dtype=torch.bfloat16, device=d)
+    w8[:cout] = wt.to(d).permute(0, 2, 3, 1).reshape(cout, 9 * c)
+    y = ops.conv3x3_few_out(xt, w8, bias.to(d), cout, h, w)
+    assert y.shape == (b, cout, h, w) and y.dtype == torch.float32
+    assert rel_l2(y, ref) < 1e-4          # bf16 operands, fp32 accumulate and output
+
+
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 320, 320, 64, 64), (16, 640, 640, 32, 32), (16, 1280, 1280, 16, 16),
                                             (3, 64, 160, 16, 16), (1, 128, 128, 8, 64), (5, 64, 32, 8, 8)])
 def test_conv3x3_stride2_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):

@@ -541,7 +541,7 @@ def test_resblock_and_upsample_vs_reference_golden(afb, cuda_device):
             if tag.startswith("cat"):
                 half = cin // 2
                 pair = U.CatPair(xb[:, :half].contiguous(memory_format=cl), xb[:, half:].contiguous(memory_format=cl))
-                assert pair.virtual() == (tag == "cat")          # the big concatenation stays virtual
+                assert pair.virtual()                            # concatenations stay virtual (both GroupNorm kernels read two sources)
                 y = rb(pair, emb.to(d))
             else:
                 y = rb(xb, emb.to(d))
