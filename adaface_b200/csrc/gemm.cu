@@ -357,6 +357,11 @@ struct GemmTmaDev {
   // walks (tap, 64-channel block); conv_cblocks = Cin / 64 (0: plain GEMM)
   int conv_cblocks, conv_h, conv_w;
   int conv_stride;           // 1, or 2: conv_h / conv_w are the OUTPUT size, tap coordinates are 2 * pixel + (dy, dx)
+  // conv_boxed != 0: the tile's 128 rows are a (bb, bh, bw) sub-box of the image that is NOT a run of consecutive pixels
+  // (image widths like 96 / 48 / 24 / 12: bw = the largest power of two dividing W, ...): row block m_blk is box
+  // (m_blk % conv_tw, (m_blk / conv_tw) % conv_th, m_blk / (conv_tw * conv_th)), and the output / residual tiles move
+  // through 4-D tensor maps over [B, H, W, N] (5-D with one store per image for the folded upsampling)
+  int conv_boxed, conv_bw, conv_bh, conv_bb, conv_tw, conv_th;
   // nearest-2x upsampling folded into the convolution (conv_fold != 0): output phase (py, px) = n_blk / nb_per_phase
   // is a 2x2 convolution of the LOW-resolution image with taps (py - 1 + a, px - 1 + c); its BN-column blocks store to
   // the pixels (2i + py, 2j + px) of the high-resolution output through a 5-D tensor map; fold_cout = N / 4
@@ -455,11 +460,19 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         // filter reads the same box shifted by (dy, dx), out-of-image pixels zero-filled by TMA (= zero padding)
         int cw0 = 0, ch0 = 0, cb0 = 0, cblk = 0, dy = -1, dx = -1, dx0 = -1, dx_end = 2;
         if (p.conv_cblocks != 0) {
-          const int m0 = m_blk * kBM;
-          const int r = m0 / p.conv_w;
-          cw0 = m0 - r * p.conv_w;
-          cb0 = r / p.conv_h;
-          ch0 = r - cb0 * p.conv_h;
+          if (p.conv_boxed != 0) {
+            const int q = m_blk / p.conv_tw;
+            cw0 = (m_blk - q * p.conv_tw) * p.conv_bw;
+            cb0 = q / p.conv_th;
+            ch0 = (q - cb0 * p.conv_th) * p.conv_bh;
+            cb0 *= p.conv_bb;
+          } else {
+            const int m0 = m_blk * kBM;
+            const int r = m0 / p.conv_w;
+            cw0 = m0 - r * p.conv_w;
+            cb0 = r / p.conv_h;
+            ch0 = r - cb0 * p.conv_h;
+          }
           if (p.conv_fold != 0) {
             const int phase = n_blk / p.nb_per_phase;
             dy = (phase >> 1) - 1;
@@ -670,7 +683,15 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
 #pragma unroll
           for (int ch = 0; ch < NC; ++ch) {
             const int n0 = n_blk * BN + ch * 32;
-            if (n0 < p.N) tma_load_2d(&tm_res, &res_full[sb], staging + (sb * NC + ch) * kBoxBytes, n0, m_blk * kBM, kEvictFirst);
+            if (n0 < p.N) {
+              if (p.conv_boxed != 0) {
+                const int q = m_blk / p.conv_tw, bq = q / p.conv_th;
+                tma_load_4d(&tm_res, &res_full[sb], staging + (sb * NC + ch) * kBoxBytes, n0, (m_blk - q * p.conv_tw) * p.conv_bw,
+                            (q - bq * p.conv_th) * p.conv_bh, bq * p.conv_bb, kEvictFirst);
+              } else {
+                tma_load_2d(&tm_res, &res_full[sb], staging + (sb * NC + ch) * kBoxBytes, n0, m_blk * kBM, kEvictFirst);
+              }
+            }
           }
         } else {
           mbar_arrive(&res_full[sb]);
@@ -853,7 +874,21 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
         AFB_GPROF(4)
         named_bar_sync(1 + grp, 128);
         if (leader) {
-          if (p.conv_fold != 0) {
+          if (p.conv_boxed != 0) {
+            const int q = m_blk / p.conv_tw, bq = q / p.conv_th;
+            const int w0 = (m_blk - q * p.conv_tw) * p.conv_bw, h0 = (q - bq * p.conv_th) * p.conv_bh, b0 = bq * p.conv_bb;
+            if (p.conv_fold != 0) {
+              // one store per image of the box: its bh low-res rows are consecutive in the merged (sample, row) dimension
+              const int phase = n_blk / p.nb_per_phase;
+              for (int ib = 0; ib < p.conv_bb; ++ib)
+                tma_store_5d(&tm_out, staging + (sb * NC + ch) * kBoxBytes + ib * (p.conv_bh * p.conv_bw * 64),
+                             n_out0 - phase * p.fold_cout, phase & 1, w0, phase >> 1, (b0 + ib) * p.conv_h + h0);
+            } else if (p.k_splits > 1) {
+              tma_reduce_add_4d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, w0, h0, b0);
+            } else {
+              tma_store_4d(&tm_out, staging + (sb * NC + ch) * kBoxBytes, n_out0, w0, h0, b0);
+            }
+          } else if (p.conv_fold != 0) {
             const int phase = n_blk / p.nb_per_phase;
             const int m0 = m_blk * kBM;
             const int r = m0 / p.conv_w;              // merged (sample, low-res row) index of the tile's first pixel
@@ -895,6 +930,34 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
   }
 }
 
+// Pixel box of a conv-mode row block.  Images whose rows tile into runs of 128 CONSECUTIVE pixels (W a power of two up to
+// 128 or a multiple of 128, H likewise) keep the plain [M, N] view of the output; every other size (96, 48, 24, 12 ...)
+// takes (bb, bh, bw) sub-boxes with bw / bh the largest powers of two dividing W / H.
+struct ConvGeom {
+  bool boxed;
+  uint32_t bw, bh, bb, tw, th, tb;
+};
+inline ConvGeom conv_geom(int W, int H, long long batch) {
+  ConvGeom g{};
+  const int bw0 = W < kBM ? W : kBM, rl = kBM / bw0;
+  if ((W < kBM ? kBM % W == 0 : W % kBM == 0) && (H < rl ? rl % H == 0 : H % rl == 0)) {
+    g.boxed = false;
+    g.bw = bw0;
+    g.bh = H < rl ? H : rl;
+  } else {
+    g.boxed = true;
+    g.bw = 1;
+    while (g.bw < static_cast<uint32_t>(kBM) && W % (2 * g.bw) == 0) g.bw *= 2;
+    g.bh = 1;
+    while (g.bw * g.bh < static_cast<uint32_t>(kBM) && H % (2 * g.bh) == 0) g.bh *= 2;
+  }
+  g.bb = kBM / (g.bw * g.bh);
+  g.tw = W / g.bw;
+  g.th = H / g.bh;
+  g.tb = static_cast<uint32_t>((batch + g.bb - 1) / g.bb);
+  return g;
+}
+
 int make_box_map(CUtensorMap* map, const void* base, int64_t cols, int64_t rows, int64_t ld) {
   const uint64_t dims[2] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(rows)};
   const uint64_t strides[1] = {static_cast<uint64_t>(ld) * 2};
@@ -927,15 +990,15 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
     // NHWC image [B, H, W, Cin], pixel stride lda; the box is 128 consecutive pixels in (b, h, w) order
     const uint64_t cin = static_cast<uint64_t>(a.k / (a.conv_fold != 0 ? 4 : 9)), W = static_cast<uint64_t>(a.conv_w),
                    H = static_cast<uint64_t>(a.conv_h);
-    const uint32_t bw = static_cast<uint32_t>(W < kBM ? W : kBM);
-    const uint32_t bh = static_cast<uint32_t>(H < kBM / bw ? H : kBM / bw);
+    const ConvGeom cg = conv_geom(a.conv_w, a.conv_h, a.m / (static_cast<int64_t>(a.conv_w) * a.conv_h));
+    const uint32_t bw = cg.bw, bh = cg.bh;
     // stride 2: W, H are the output size; the input image is twice as large and the box walks it with element stride 2
     const uint32_t cs = a.conv_stride == 2 ? 2u : 1u;
     const uint64_t Wi = W * cs, Hi = H * cs;
     const uint64_t dims[4] = {cin, Wi, Hi, static_cast<uint64_t>(a.m) / (W * H)};
     const uint64_t strides[3] = {static_cast<uint64_t>(a.lda) * 2, static_cast<uint64_t>(a.lda) * 2 * Wi,
                                  static_cast<uint64_t>(a.lda) * 2 * Wi * Hi};
-    const uint32_t box[4] = {kBK, bw * cs, bh * cs, kBM / (bw * bh)};
+    const uint32_t box[4] = {kBK, bw * cs, bh * cs, cg.bb};
     const uint32_t estr[4] = {1, cs, cs, 1};
     if (int rc = make_tensor_map(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.a, dims, strides, box, Swizzle::B128,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, estr))
@@ -968,18 +1031,34 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
     // of one phase: box {32 channels, 1, bw, 1, bh*bb}
     const uint64_t W = static_cast<uint64_t>(a.conv_w), H = static_cast<uint64_t>(a.conv_h), cout = static_cast<uint64_t>(a.n / 4);
     const uint64_t ld = static_cast<uint64_t>(a.ldo) * 2;
-    const uint32_t bw = static_cast<uint32_t>(W < kBM ? W : kBM);
+    const ConvGeom cg = conv_geom(a.conv_w, a.conv_h, a.m / (static_cast<int64_t>(a.conv_w) * a.conv_h));
     const uint64_t dims[5] = {cout, 2, W, 2, static_cast<uint64_t>(a.m) / W};
     const uint64_t strides[4] = {ld, 2 * ld, 2 * W * ld, 4 * W * ld};
-    const uint32_t box[5] = {32, 1, bw, 1, kBM / bw};
+    // (boxed: one store per image of the box, bh consecutive rows of the merged (sample, low-res row) dimension each)
+    const uint32_t box[5] = {32, 1, cg.bw, 1, cg.boxed ? cg.bh : kBM / cg.bw};
     (void)H;
     if (int rc = make_tensor_map(&tm_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, a.out, dims, strides, box, Swizzle::B64)) return rc;
+  } else if (a.conv_h > 0 && conv_geom(a.conv_w, a.conv_h, 1).boxed) {
+    // sub-box tiles: the output (and the residual) as [B, H, W, N] behind a 4-D map, box {32 channels, bw, bh, bb}
+    const ConvGeom cg = conv_geom(a.conv_w, a.conv_h, a.m / (static_cast<int64_t>(a.conv_w) * a.conv_h));
+    const uint64_t W = static_cast<uint64_t>(a.conv_w), H = static_cast<uint64_t>(a.conv_h);
+    const uint32_t box[4] = {32, cg.bw, cg.bh, cg.bb};
+    auto map4 = [&](CUtensorMap* map, const void* base, int64_t ld) {
+      const uint64_t dims[4] = {static_cast<uint64_t>(n_out), W, H, static_cast<uint64_t>(a.m) / (W * H)};
+      const uint64_t strides[3] = {static_cast<uint64_t>(ld) * 2, static_cast<uint64_t>(ld) * 2 * W, static_cast<uint64_t>(ld) * 2 * W * H};
+      return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, Swizzle::B64);
+    };
+    if (int rc = map4(&tm_out, a.out, a.ldo)) return rc;
+    if (a.residual != nullptr) {
+      if (int rc = map4(&tm_res, a.residual, a.ldr)) return rc;
+    }
   } else if (int rc = make_box_map(&tm_out, a.out, n_out, a.m, a.ldo)) {
     return rc;
   }
-  if (a.residual != nullptr) {
+  const bool boxed = a.conv_h > 0 && conv_geom(a.conv_w, a.conv_h, 1).boxed;
+  if (a.residual != nullptr && !boxed) {
     if (int rc = make_box_map(&tm_res, a.residual, n_out, a.m, a.ldr)) return rc;
-  } else {
+  } else if (a.residual == nullptr) {
     tm_res = tm_out;
   }
   GemmTmaDev p;
@@ -1000,6 +1079,18 @@ int launch_tma_impl(const afb_gemm_args& a, cudaStream_t stream) {
   p.conv_cblocks = a.conv_h > 0 ? static_cast<int>(a.k / taps / kBK) : 0;
   p.conv_fold = a.conv_fold;
   p.k1_blocks = a.a2 != nullptr ? static_cast<int>(k1 / kBK) : p.num_k_blocks;
+  p.conv_boxed = 0;
+  p.conv_bw = p.conv_bh = p.conv_bb = p.conv_tw = p.conv_th = 1;
+  if (a.conv_h > 0) {
+    const ConvGeom cg = conv_geom(a.conv_w, a.conv_h, a.m / (static_cast<int64_t>(a.conv_w) * a.conv_h));
+    p.conv_boxed = cg.boxed ? 1 : 0;
+    p.conv_bw = static_cast<int>(cg.bw);
+    p.conv_bh = static_cast<int>(cg.bh);
+    p.conv_bb = static_cast<int>(cg.bb);
+    p.conv_tw = static_cast<int>(cg.tw);
+    p.conv_th = static_cast<int>(cg.th);
+    if (cg.boxed) p.num_m_blocks = static_cast<int>(cg.tw * cg.th * cg.tb);
+  }
   p.k_splits = 1;
   if constexpr (kPair && !GEGLU && !kLn && !kStats) {
     // fewer tiles than SM pairs and a deep K: split K so that every pair has work (measured on the 3x3 convolutions at
@@ -1181,11 +1272,9 @@ extern "C" int afb_gemm_bf16(const afb_gemm_args* args, afb_stream_t stream_) {
                   "afb_gemm_bf16: folded upsampling needs N = 4 * Cout with Cout a multiple of the tile width (160 or 128), "
                   "no residual and a contiguous [B, 2H, 2W, Cout] output");
     }
-    const int W = a.conv_w, H = a.conv_h;
-    const int bw = W < 128 ? W : 128;
-    AFB_REQUIRE(W < 128 ? 128 % W == 0 : W % 128 == 0, "afb_gemm_bf16: conv width %d does not tile into 128-pixel boxes", W);
-    const int rl = 128 / bw;
-    AFB_REQUIRE(H < rl ? rl % H == 0 : H % rl == 0, "afb_gemm_bf16: conv height %d does not tile into 128-pixel boxes", H);
+    // any image size tiles into 128-pixel boxes (conv_geom); widths / heights with a small power-of-two factor just get
+    // narrow boxes: require at least 4-pixel runs so that a TMA box row is not a single pixel
+    AFB_REQUIRE(a.conv_w % 4 == 0 || kBM % a.conv_w == 0, "afb_gemm_bf16: conv width %d must be a multiple of 4 (or divide 128)", a.conv_w);
     AFB_REQUIRE(a.epilogue == AFB_EPI_STORE && a.out_dtype == AFB_BF16 && (a.residual == nullptr || a.residual_dtype == AFB_BF16) &&
                     a.ln_stats == nullptr && a.row_stats_out == nullptr,
                 "afb_gemm_bf16: conv mode takes the bf16 STORE epilogue (bias, bf16 residual) only");

@@ -160,9 +160,8 @@ class _Bf16Conv(nn.Conv2d):
             if h % 2 or w % 2:
                 return False
             h, w = h // 2, w // 2
-        bw = min(w, 128)
-        rl = 128 // bw
-        return (128 % w == 0 if w < 128 else w % 128 == 0) and (rl % h == 0 if h < rl else h % rl == 0)
+        # any width that is a multiple of 4 (or divides 128) tiles into 128-pixel boxes (csrc/gemm.cu conv_geom)
+        return w % 4 == 0 or 128 % w == 0
 
     def _w_native(self):
         """bf16 [Cout, 9*Cin] with k = (ky*3 + kx)*Cin + c: the channels-last memory of the Conv2d weight."""

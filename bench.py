@@ -201,9 +201,9 @@ def workload_config(world, mode, per_gpu):
             "n_samples_per_gpu": N_SAMPLES, "batch_incl_cfg_per_gpu": 2 * N_SAMPLES, "latent": [4, LATENT, LATENT],
             "ddim_steps_per_image": DDIM_STEPS, "subjects": 1, "parallelism": f"samples sharded over {world} GPU(s), no collective "
             "inside the step" + (" (independent 8-sample replicas: weak scaling)" if world > 1 else ""),
-            "resblocks": "Upsample = nearest-2x folded into four 2x2 phase convolutions on this repo's implicit-GEMM tcgen05 kernel; "
-                         "ResBlock 3x3 / stride-2 / 4-channel convolutions on torch/cuDNN bf16 channels-last unless "
-                         "AFB_CONV=1 (outside the hot path, included in the step)",
+            "resblocks": "every convolution of the U-Net shell on this repo's kernels (3x3 stride 1 / stride 2 and the "
+                         "upsample-folded phases on the implicit-GEMM tcgen05 kernel, conv_in as im2col + GEMM, conv_out as an "
+                         "mma.sync kernel; AFB_CONV=0 moves them back to cuDNN); outside the hot path, included in the step",
             "l2": "no explicit flush: each step streams 1.7 GB of bf16 weights plus > 2 GB of activations, far above "
                   "the 126 MB L2"}
 
@@ -267,6 +267,13 @@ def run_reference(args):
         return
     import torch
     threads = host_threads()
+    # the arm times the workload of the GPU arm it is launched beside: configs[1] at N = 1, the two-subject sharded job
+    # of configs[2] at N > 1 (a CPU does not shard: its throughput in the metric's unit, steps of an 8-sample batch per
+    # second, is 1 / (8 x the time of one sample + CFG pair))
+    mode = args.workload or ("config3" if args.gpus > 1 else "config2")
+    if mode not in ("config2", "config3"):
+        mode = "config2"
+    n_subjects = 2 if mode == "config3" else 1
     steps = args.steps if args.steps is not None else 3
     warmup = args.warmup if args.warmup is not None else 1
     # the same synthetic weights as the GPU arm (drawn per tensor name), held as plain state dicts: none of the product's
@@ -274,19 +281,22 @@ def run_reference(args):
     from oracle import params as P
     sd = {k: torch.empty(shape) for k, shape in P.unet_spec()}
     fill_synthetic_(sd.items(), 0)
-    ada_sd = {k: torch.empty(shape) for k, shape in P.ada_embedding_spec(SUBJ_K, SUBJ_R, 2)}
-    fill_synthetic_(ada_sd.items(), 1)
-    adas = [ada_sd]
-    x_T, c, uc, probes, extra = synthetic_inputs(N_SAMPLES, 1, LATENT)
+    adas = []
+    for i in range(n_subjects):
+        ada_sd = {k: torch.empty(shape) for k, shape in P.ada_embedding_spec(SUBJ_K, SUBJ_R, 2)}
+        fill_synthetic_(ada_sd.items(), 1 + i)
+        adas.append(ada_sd)
+    x_T, c, uc, probes, extra = synthetic_inputs(N_SAMPLES, n_subjects, LATENT)
     scales = __import__("oracle.port", fromlist=["guidance_schedule"]).guidance_schedule(list(GUIDANCE), DDIM_STEPS)
     full_s, full_note = None, ""
-    if host_mem_gb() >= 48.0 and not args.no_full_batch:
+    if host_mem_gb() >= 48.0 and not args.no_full_batch and mode == "config2":
         try:
             _, _, full_s = cpu_unet_call(sd, cpu_subjects(adas, probes, extra, 0, N_SAMPLES), x_T, c, uc, DDIM_STEPS - 1, scales[0])
         except (MemoryError, RuntimeError) as exc:       # ~25 GB of fp32 score tensors at batch 16
             full_note = f"the batch-16 call did not fit ({type(exc).__name__}); "
     else:
-        full_note = "the batch-16 call was skipped (less than 48 GB of host memory available or --no-full-batch); "
+        full_note = ("the 64-sample job is not run in full on the CPU; " if mode == "config3" else
+                     "the batch-16 call was skipped (less than 48 GB of host memory available or --no-full-batch); ")
     subj1 = cpu_subjects(adas, probes, extra, 0, 1)
     x = x_T[:1]
     times = []
@@ -305,8 +315,9 @@ def run_reference(args):
               f"per loop step ({ms_sample:.0f} ms each, which is what ms_per_step reports)")
     line = {"impl": "reference", "metric": "ddim_steps_per_s", "value": val, "unit": "steps/s", "n_gpus": args.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": ms_sample, "ms_per_full_step": step_s * 1e3,
-            "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(1, "config2", N_SAMPLES),
+            "higher_is_better": True, "scaling": "strong" if mode == "config3" else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.gpus, mode, JOB_SAMPLES // max(args.gpus, 1) if mode == "config3" else N_SAMPLES),
             "cpu_baseline": {"value": val, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample,
                              "full_batch_call_s": full_s, "sample_step_ms": ms_sample, "sample_fraction_of_step": 1.0 / N_SAMPLES},
             "e2e": {"value": val, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -822,7 +833,7 @@ def run_inversion(args):
                                        f"({sum(p.numel() for p in params)} values), one flat NCCL all-reduce, AdamW; {world} GPU(s)",
                            "batch_per_gpu": b, "trainable_values": sum(p.numel() for p in params),
                            "parallelism": f"data parallel over {world} GPU(s): one all-reduce of {4 * reducer.flat.numel()} bytes per step"},
-                "clocks": clk, "finite": finite, "loss": float(loss),
+                "clocks": clk, "finite": finite, "loss": float(loss.detach()),
                 "backward_ms": bw_ms, "allreduce_ms": ar_ms, "allreduce_share": ar_ms / ms,
                 "gpu_launches": launches * steps, "gpu_launches_per_step": launches,
                 "kernels": {k: {"ms": round(v["ms"], 3), "launches": v["launches"]} for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])},

@@ -135,7 +135,10 @@ def test_linear_store(ops, cuda_device, m, n, k):
 
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (3, 320, 320, 16, 16), (2, 640, 320, 64, 64),
                                             (16, 1280, 1280, 8, 8), (1, 128, 128, 4, 32), (2, 192, 640, 32, 32),
-                                            (1, 64, 32, 2, 128), (3, 64, 160, 8, 8), (5, 128, 320, 4, 4)])
+                                            (1, 64, 32, 2, 128), (3, 64, 160, 8, 8), (5, 128, 320, 4, 4),
+                                            # sub-box tiles (widths that are not a power of two: config 5's 96 / 48 / 24 / 12)
+                                            (2, 128, 320, 96, 96), (3, 64, 160, 24, 24), (5, 64, 128, 12, 12), (2, 64, 160, 40, 20),
+                                            (17, 1280, 1280, 12, 12)])
 def test_conv3x3_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
     """3x3 / stride 1 / zero padding 1 convolution (ResBlock / Upsample convs, openaimodel.py:95-123,203-238) on the
     tcgen05 GEMM kernel against torch's fp32 conv2d of the same bf16-rounded operands."""
@@ -188,7 +191,8 @@ def test_conv3x3_few_output_channels(ops, cuda_device, b, c, cout, h, w):
 
 
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 320, 320, 64, 64), (16, 640, 640, 32, 32), (16, 1280, 1280, 16, 16),
-                                            (3, 64, 160, 16, 16), (1, 128, 128, 8, 64), (5, 64, 32, 8, 8)])
+                                            (3, 64, 160, 16, 16), (1, 128, 128, 8, 64), (5, 64, 32, 8, 8),
+                                            (2, 64, 160, 96, 96), (3, 128, 128, 48, 24)])      # sub-box output tiles
 def test_conv3x3_stride2_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
     """3x3 / stride 2 / zero padding 1 convolution (Downsample.forward, openaimodel.py:138-165): the same implicit-GEMM
     kernel with a TMA element stride of 2 on the image axes, against torch's fp32 conv2d."""
@@ -206,7 +210,8 @@ def test_conv3x3_stride2_implicit_gemm(ops, cuda_device, b, cin, cout, h, w):
 
 @pytest.mark.parametrize("b,cin,cout,h,w", [(2, 64, 160, 8, 8), (2, 128, 128, 16, 16), (16, 1280, 1280, 8, 8),
                                             (1, 640, 640, 32, 32), (3, 64, 320, 4, 32), (3, 128, 128, 8, 8),
-                                            (5, 64, 160, 4, 4)])
+                                            (5, 64, 160, 4, 4),
+                                            (2, 64, 160, 48, 48), (3, 128, 128, 24, 24), (5, 64, 160, 12, 12)])   # sub-box tiles
 def test_conv3x3_upsample_fold(ops, cuda_device, b, cin, cout, h, w):
     """Upsample.forward (openaimodel.py:95-123): nearest 2x + 3x3 conv as four folded 2x2 phase convolutions of the
     low-resolution image, against torch's fp32 interpolate + conv2d."""
@@ -239,10 +244,10 @@ def test_conv3x3_upsample_fold(ops, cuda_device, b, cin, cout, h, w):
 def test_conv3x3_unsupported_geometry_raises(ops, cuda_device):
     from adaface_b200._lib import AdafaceB200Error
     d = cuda_device
-    x = torch.zeros((96 * 96, 64), dtype=torch.bfloat16, device=d)
+    x = torch.zeros((9 * 9, 64), dtype=torch.bfloat16, device=d)
     wp = torch.zeros((32, 9 * 64), dtype=torch.bfloat16, device=d)
     with pytest.raises(AdafaceB200Error):
-        ops.conv3x3(x, wp, None, None, 96, 96)           # 96-pixel rows do not tile into 128-pixel boxes
+        ops.conv3x3(x, wp, None, None, 9, 9)             # widths must be a multiple of 4 (or divide 128)
     with pytest.raises(AdafaceB200Error):
         ops.conv3x3(torch.zeros((64, 48), dtype=torch.bfloat16, device=d),
                     torch.zeros((32, 9 * 48), dtype=torch.bfloat16, device=d), None, None, 8, 8)   # Cin % 64
