@@ -311,8 +311,8 @@ class ResBlock(TimestepBlock):
             self.__dict__["_out_bias"] = c
         return c[1]
 
-    def _skip_single(self, x: Tensor, h: Tensor, bias: Tensor) -> Tensor:
-        """skip_connection(x) + h + bias with the 1x1 convolution as one GEMM (residual = h)."""
+    def _skip_single(self, x: Tensor, h: Optional[Tensor], bias: Optional[Tensor]) -> Tensor:
+        """skip_connection(x) (+ h + bias) with the 1x1 convolution as one GEMM (residual = h)."""
         sc = self.skip_connection
         key = (sc.weight.data_ptr(), sc.weight._version)
         c = self.__dict__.get("_skip_w")
@@ -322,9 +322,9 @@ class ResBlock(TimestepBlock):
             self.__dict__["_skip_w"] = c
         b_, c_, h_, w_ = x.shape
         if c_ % 8:
-            return add_cl(h, sc(x, False), bias)
+            return sc(x, False) if h is None else add_cl(h, sc(x, False), bias)
         xt = x.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, c_)
-        ht = h.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
+        ht = None if h is None else h.contiguous(memory_format=CL).permute(0, 2, 3, 1).reshape(b_ * h_ * w_, -1)
         out = ops.linear(xt, c[1], bias, ht, False)
         return out.view(b_, h_, w_, sc.out_channels).permute(0, 3, 1, 2)
 
@@ -407,7 +407,7 @@ class ResBlock(TimestepBlock):
                 return conv2.native(h, self.out_bias(), x)
             return add_cl(conv2(h, False), x, self.out_bias())
         if conv2.native_ok(h):                   # conv2 + both biases + skip(x) in the GEMM epilogue
-            skip = self._skip_pair(pair, None, None) if pair is not None else self.skip_connection(x, False)
+            skip = self._skip_pair(pair, None, None) if pair is not None else self._skip_single(x, None, None)
             return conv2.native(h, self.out_bias(), skip)
         # cuDNN conv2: the 1x1 skip convolution runs as a GEMM whose epilogue adds conv2's output and both biases
         # (skip(x) + conv2(h) + bias in the skip GEMM instead of a separate elementwise pass)

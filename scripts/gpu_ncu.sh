@@ -14,8 +14,10 @@ full() {   # name, kernel regex, count
   ncu -i gpurun_out/prof_${TAG}_$1.ncu-rep --page raw --csv > gpurun_out/prof_raw_${TAG}_$1.csv 2>/dev/null
   rm -f gpurun_out/prof_${TAG}_$1.ncu-rep
 }
-full norms 'gn_partial_tok|gn_apply_tok|gn_cluster_tok' 9
-full ada 'ada_pool_main|ada_pool_combine|ada_head|cfg_ddim|add_bias_residual' 10
-full attn 'attention_fwd_kernel' 6
-full gemm 'gemm_bf16_tma_kernel' 14
-ls -la gpurun_out/ | tail -12
+full norms 'gn_partial_tok|gn_apply_tok' 4
+full slab 'gn_slab_tok' 6
+full ada 'ada_pool_main|ada_pool_combine|ada_head' 6
+full small 'cfg_ddim|im2col3x3|conv3x3_few_out|zero_bf16|add_bias_residual' 8
+full attn 'attention_fwd_kernel' 4
+full gemm 'gemm_bf16_tma_kernel' 24
+ls -la gpurun_out/ | tail -14
