@@ -174,7 +174,7 @@ template <int kChunks>
 __global__ void __launch_bounds__(kPoolThreads, (kChunks <= 2 ? 2 : 1)) ada_pool_main_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
     const uint8_t* __restrict__ key_mask, float* __restrict__ scores, float* __restrict__ partials, int N, int C,
-    int tokens_per_block) {
+    int tokens_per_block, float drop_p, uint32_t seed) {
   extern __shared__ float sh[];
   float* s_u = sh;                                      // [2][C] folded queries of this sample
   float* s_part = s_u + 2 * C;                          // [8 warps][2][kChunks * 32] per-chunk dots
@@ -306,6 +306,10 @@ __global__ void __launch_bounds__(kPoolThreads, (kChunks <= 2 ? 2 : 1)) ada_pool
     const float e_fg = __expf(s_fg - m_new), e_bg = __expf(s_bg - m_new);
     l_run = l_run * corr + e_fg + e_bg;
     m_run = m_new;
+    // train mode: dropout on the attention probabilities (:296) - the normaliser keeps every entry, the pooled sums use
+    // the kept ones scaled by 1 / (1 - p)
+    const float e_fg_k = e_fg * pool_drop_scale(seed, b, lane & 7, 0, t, N, drop_p);
+    const float e_bg_k = e_bg * pool_drop_scale(seed, b, lane & 7, 1, t, N, drop_p);
     // every lane scales its channel chunks by their head's factors
 #pragma unroll
     for (int i = 0; i < kChunks; ++i) {
@@ -313,8 +317,8 @@ __global__ void __launch_bounds__(kPoolThreads, (kChunks <= 2 ? 2 : 1)) ada_pool
       const bool ok = ch < nchunks;
       const int g = ok ? ch / chunks_per_group : 0;
       const float cg = __shfl_sync(0xffffffffu, corr, g);
-      const float fg = __shfl_sync(0xffffffffu, e_fg, g);
-      const float bg = __shfl_sync(0xffffffffu, e_bg, g);
+      const float fg = __shfl_sync(0xffffffffu, e_fg_k, g);
+      const float bg = __shfl_sync(0xffffffffu, e_bg_k, g);
       if (ok) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -419,7 +423,7 @@ __global__ void __launch_bounds__(256) ada_pool_combine_kernel(const float* __re
 
 __global__ void __launch_bounds__(256) ada_pool_probs_kernel(const float* __restrict__ scores, const float* __restrict__ stats,
                                                              float* __restrict__ attn_fg, float* __restrict__ attn_bg, int N,
-                                                             long long total) {
+                                                             long long total, float drop_p, uint32_t seed) {
   // scores: [B][8][2][N]; attn_*: [B][8][N]
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -428,7 +432,8 @@ __global__ void __launch_bounds__(256) ada_pool_probs_kernel(const float* __rest
     const long long bgi = bg_idx >> 1;
     const int which = static_cast<int>(bg_idx & 1);
     const float m = stats[bgi * 2], l = stats[bgi * 2 + 1];
-    const float pr = __expf(scores[i] - m) / l;
+    const float pr = __expf(scores[i] - m) / l *
+                     pool_drop_scale(seed, static_cast<int>(bgi >> 3), static_cast<int>(bgi & 7), which, n, N, drop_p);
     (which == 0 ? attn_fg : attn_bg)[bgi * N + n] = pr;
   }
 }
@@ -714,11 +719,12 @@ extern "C" int afb_ada_pool_prep_batched(const afb_ada_prep_item* items, int n_i
 
 extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, float* fg_out,
                             float* bg_out, float* attn_fg, float* attn_bg, float* ws, int batch, int n_tokens, int channels,
-                            afb_stream_t stream_) {
+                            float drop_p, uint32_t seed, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && q && pool_q && fg_out && bg_out && ws, "afb_ada_pool: NULL argument");
   AFB_REQUIRE(batch > 0 && n_tokens > 0, "afb_ada_pool: empty input");
+  AFB_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "afb_ada_pool: drop_p must be in [0, 1)");
   AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool: channels %d must be a multiple of 64, <= 1280", channels);
   AFB_REQUIRE((attn_fg == nullptr) == (attn_bg == nullptr), "afb_ada_pool: attn_fg and attn_bg must both be given or both NULL");
   AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) & 15) == 0, "afb_ada_pool: x/q must be 16-byte aligned");
@@ -747,7 +753,7 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
       set_for = sh_main;                                                                                                  \
     }                                                                                                                     \
     AFB_CHECK_CUDA(launch_pdl(kern, grid, dim3(kPoolThreads), sh_main, stream, 1, xb, qb, pool_q, key_mask, scores_arg,     \
-                              partials, n_tokens, C, tokens_per_block));                                                  \
+                              partials, n_tokens, C, tokens_per_block, drop_p, seed));                                    \
   }
   if (chunks_per_lane <= 2) AFB_LAUNCH_POOL(2)
   else if (chunks_per_lane <= 3) AFB_LAUNCH_POOL(3)
@@ -761,7 +767,7 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
     const long long total = static_cast<long long>(batch) * kHeads * 2 * n_tokens;
     const long long blocks = (total + 255) / 256;
     ada_pool_probs_kernel<<<static_cast<unsigned>(blocks < 2048 ? blocks : 2048), 256, 0, stream>>>(scores, stats, attn_fg, attn_bg,
-                                                                                                 n_tokens, total);
+                                                                                                 n_tokens, total, drop_p, seed);
     count_launch();
   }
   AFB_CHECK_CUDA(cudaGetLastError());

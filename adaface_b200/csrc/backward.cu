@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
     const uint8_t* __restrict__ key_mask, const float* __restrict__ stats, const float* __restrict__ out_fg,
     const float* __restrict__ out_bg, const float* __restrict__ d_fg, const float* __restrict__ d_bg, float* __restrict__ du,
-    int N, int C, int tokens_per_block) {
+    int N, int C, int tokens_per_block, float drop_p, uint32_t seed) {
   extern __shared__ float sh[];
   float* s_u = sh;                       // [2][C]
   float* s_d = s_u + 2 * C;              // [2][C] dout
@@ -541,7 +541,9 @@ __global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_kernel(
     const bool masked = key_mask != nullptr && key_mask[static_cast<long long>(b) * N + t] == 0;
     const int g = lane & 7;
     float dsp = 0.f;                                              // d s' of (i, g) held by lanes 0..15
-    if (lane < 16 && !masked) dsp = __expf(sc - s_m[g]) / s_l[g] * (dp - s_delta[g]);
+    // (train mode: out = sum_t k_t p_t v_t with the dropout keep-scale k_t, so d s'_t = p_t (k_t dp_t - Delta))
+    if (lane < 16 && !masked)
+      dsp = __expf(sc - s_m[g]) / s_l[g] * (pool_drop_scale(seed, b, g, lane >> 3, t, N, drop_p) * dp - s_delta[g]);
     float dtot = dsp;
     dtot += __shfl_xor_sync(0xffffffffu, dtot, 1);
     dtot += __shfl_xor_sync(0xffffffffu, dtot, 2);
@@ -765,7 +767,8 @@ extern "C" int afb_ada_head_bwd(const float* infeat_fg, const float* infeat_bg, 
 
 extern "C" int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
                                 const float* stats, const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg,
-                                float* d_pool_q, int batch, int n_tokens, int channels, afb_stream_t stream_) {
+                                float* d_pool_q, int batch, int n_tokens, int channels, float drop_p, uint32_t seed,
+                                afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && q && pool_q && stats && fg_out && bg_out && d_fg && d_bg && d_pool_q, "afb_ada_pool_bwd: NULL argument");
@@ -792,7 +795,7 @@ extern "C" int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const floa
       set_for = shb;                                                                                                \
     }                                                                                                               \
     kern<<<grid, kPbThreads, shb, stream>>>(xb, qb, pool_q, key_mask, stats, fg_out, bg_out, d_fg, d_bg, d_pool_q, n_tokens, C, \
-                                            tokens_per_block);                                                      \
+                                            tokens_per_block, drop_p, seed);                                        \
   }
   if (cpl <= 2) AFB_LAUNCH_PB(2)
   else if (cpl <= 3) AFB_LAUNCH_PB(3)
@@ -1356,7 +1359,8 @@ __global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_feat_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
     const uint8_t* __restrict__ key_mask, const float* __restrict__ stats, const float* __restrict__ out_fg,
     const float* __restrict__ out_bg, const float* __restrict__ d_fg, const float* __restrict__ d_bg,
-    __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dqo, int N, int C, int tokens_per_block) {
+    __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dqo, int N, int C, int tokens_per_block, float drop_p,
+    uint32_t seed) {
   extern __shared__ float sh[];
   float* s_u = sh;                       // [2][C]
   float* s_d = s_u + 2 * C;              // [2][C] dout
@@ -1456,7 +1460,8 @@ __global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_feat_kernel(
     const int g = lane & 7;
     float pr = 0.f;
     if (lane < 16 && !masked) pr = __expf(sc - s_m[g]) / s_l[g];
-    const float dsp = pr * (dp - s_delta[g]);
+    const float prk = pr * pool_drop_scale(seed, b, g, (lane >> 3) & 1, t, N, drop_p);      // kept probability (train-mode dropout)
+    const float dsp = prk * dp - pr * s_delta[g];
     float dtot = dsp;
     dtot += __shfl_xor_sync(0xffffffffu, dtot, 1);
     dtot += __shfl_xor_sync(0xffffffffu, dtot, 2);
@@ -1469,7 +1474,7 @@ __global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_feat_kernel(
       const bool ok = ch < nchunks;
       const int gg = ok ? ch / chunks_per_group : 0;
       const float f_ds = __shfl_sync(0xffffffffu, ds, gg), b_ds = __shfl_sync(0xffffffffu, ds, 8 + gg);
-      const float f_p = __shfl_sync(0xffffffffu, pr, gg), b_p = __shfl_sync(0xffffffffu, pr, 8 + gg);
+      const float f_p = __shfl_sync(0xffffffffu, prk, gg), b_p = __shfl_sync(0xffffffffu, prk, 8 + gg);
       if (ok) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -1502,7 +1507,7 @@ __global__ void __launch_bounds__(kPbThreads) ada_pool_bwd_feat_kernel(
 extern "C" int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
                                          const float* stats, const float* fg_out, const float* bg_out, const float* d_fg,
                                          const float* d_bg, afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels,
-                                         afb_stream_t stream_) {
+                                         float drop_p, uint32_t seed, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && q && pool_q && stats && fg_out && bg_out && d_fg && d_bg && dx && dq, "afb_ada_pool_bwd_features: NULL argument");
@@ -1532,7 +1537,7 @@ extern "C" int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, c
       set_for = shb;                                                                                                \
     }                                                                                                               \
     kern<<<grid, kPbThreads, shb, stream>>>(xb, qb, pool_q, key_mask, stats, fg_out, bg_out, d_fg, d_bg, dxb, dqb, n_tokens, C, \
-                                            tokens_per_block);                                                      \
+                                            tokens_per_block, drop_p, seed);                                        \
   }
   if (cpl <= 2) AFB_LAUNCH_PBF(2)
   else if (cpl <= 3) AFB_LAUNCH_PBF(3)

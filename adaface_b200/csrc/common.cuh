@@ -232,6 +232,20 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const 
                "r"(smem_u32(smem)), "r"(c0), "r"(c1)
                : "memory");
 }
+// AttentionalPooler train-mode attention dropout (embedding_manager.py:138, 296): keep-scale of probability
+// (sample b, head g, stream i = fg/bg, token t), a counter-based hash of (seed, element index) so that the forward and both
+// backward kernels regenerate the same mask without storing it.  drop_p == 0: always 1.
+__device__ __forceinline__ float pool_drop_scale(uint32_t seed, int b, int g, int i, int t, int n_tokens, float drop_p) {
+  if (drop_p <= 0.f) return 1.f;
+  uint32_t h = (static_cast<uint32_t>((b * 8 + g) * 2 + i) * static_cast<uint32_t>(n_tokens) + static_cast<uint32_t>(t)) * 0x9E3779B1u + seed;
+  h ^= h >> 16;
+  h *= 0x85EBCA6Bu;
+  h ^= h >> 13;
+  h *= 0xC2B2AE35u;
+  h ^= h >> 16;
+  return static_cast<float>(h >> 8) * (1.0f / 16777216.0f) < drop_p ? 0.f : 1.0f / (1.0f - drop_p);
+}
+
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* smem, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(map)),

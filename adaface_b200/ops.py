@@ -620,9 +620,10 @@ class AdaPrepBatch:
 
 @torch.library.custom_op("adaface_b200::ada_pool", mutates_args=())
 def ada_pool(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor],
-             want_attn: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+             want_attn: bool, drop_p: float = 0.0, seed: int = 0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """AttentionalPooler main pass (embedding_manager.py:146-321): x, q bf16 [B,N,C] -> fg_out, bg_out fp32 [B,C]
-    and, when want_attn, attn_fg/attn_bg fp32 [B*8, 1, N] (empty tensors otherwise)."""
+    and, when want_attn, attn_fg/attn_bg fp32 [B*8, 1, N] (empty tensors otherwise).  drop_p > 0: train-mode dropout on
+    the attention probabilities (:296) with the mask a counter-based hash of (seed, element) - see the header."""
     _need_cuda(x, q, pool_q, key_mask)
     if x.dtype != torch.bfloat16 or q.dtype != torch.bfloat16 or not x.is_contiguous() or not q.is_contiguous():
         raise ValueError("ada_pool: contiguous bf16 x and q expected")
@@ -640,13 +641,13 @@ def ada_pool(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor],
         key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
     pool_q = pool_q.contiguous()
     _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg),
-         _ptr(bg), _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c, _stream(),
-         nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+         _ptr(bg), _ptr(a_fg) if want_attn else None, _ptr(a_bg) if want_attn else None, _ptr(ws), b, n, c, float(drop_p),
+         int(seed) & 0xFFFFFFFF, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     return fg, bg, a_fg, a_bg
 
 
 @ada_pool.register_fake
-def _(x, q, pool_q, key_mask, want_attn):
+def _(x, q, pool_q, key_mask, want_attn, drop_p=0.0, seed=0):
     b, n, c = x.shape
     shape = (b * 8, 1, n) if want_attn else (0,)
     f = lambda s: x.new_empty(s, dtype=torch.float32)
@@ -979,7 +980,8 @@ def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, grad_out, wan
 
 
 @torch.library.custom_op("adaface_b200::ada_pool_bwd", mutates_args=())
-def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor, d_bg: Tensor) -> Tensor:
+def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor, d_bg: Tensor,
+                 drop_p: float = 0.0, seed: int = 0) -> Tensor:
     """Backward of `ada_pool` w.r.t. the folded pooling queries: re-runs the forward for its softmax statistics and
     pooled outputs, then one streaming pass over x and q -> d_pool_q fp32 [B, 2, C]."""
     _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg)
@@ -994,18 +996,19 @@ def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor
     fg = torch.empty((b, c), dtype=torch.float32, device=dev)
     bg = torch.empty((b, c), dtype=torch.float32, device=dev)
     _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
-         b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+         b, n, c, float(drop_p), int(seed) & 0xFFFFFFFF, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     off = int(lib.afb_ada_pool_stats_offset(b, n, c))       # the forward's merged (max, sum) per (sample, head)
     stats = ws[off:off + b * 16]
     d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
     d_pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=dev)
     _run("ada_pool_bwd", lib.afb_ada_pool_bwd, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats), _ptr(fg), _ptr(bg),
-         _ptr(d_fg), _ptr(d_bg), _ptr(d_pool_q), b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+         _ptr(d_fg), _ptr(d_bg), _ptr(d_pool_q), b, n, c, float(drop_p), int(seed) & 0xFFFFFFFF, _stream(),
+         nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     return d_pool_q
 
 
 @ada_pool_bwd.register_fake
-def _(x, q, pool_q, key_mask, d_fg, d_bg):
+def _(x, q, pool_q, key_mask, d_fg, d_bg, drop_p=0.0, seed=0):
     return x.new_empty((x.shape[0], 2, x.shape[2]), dtype=torch.float32)
 
 
@@ -1299,7 +1302,7 @@ add_bias_residual.register_autograd(_abr_backward, setup_context=_abr_setup)
 
 @torch.library.custom_op("adaface_b200::ada_pool_bwd_features", mutates_args=())
 def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor,
-                          d_bg: Tensor) -> Tuple[Tensor, Tensor]:
+                          d_bg: Tensor, drop_p: float = 0.0, seed: int = 0) -> Tuple[Tensor, Tensor]:
     """Backward of `ada_pool` towards the layer features: -> (dx, dq) bf16 [B, N, C]."""
     _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg)
     b, n, c = x.shape
@@ -1313,24 +1316,25 @@ def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Option
     fg = torch.empty((b, c), dtype=torch.float32, device=dev)
     bg = torch.empty((b, c), dtype=torch.float32, device=dev)
     _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
-         b, n, c, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+         b, n, c, float(drop_p), int(seed) & 0xFFFFFFFF, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     off = int(lib.afb_ada_pool_stats_offset(b, n, c))       # the forward's merged (max, sum) per (sample, head)
     stats = ws[off:off + b * 16]
     d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
     dx, dq = torch.empty_like(x), torch.empty_like(q)
     _run("ada_pool_bwd_features", lib.afb_ada_pool_bwd_features, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats),
-         _ptr(fg), _ptr(bg), _ptr(d_fg), _ptr(d_bg), _ptr(dx), _ptr(dq), b, n, c, _stream(), nbytes=8.0 * b * n * c,
-         tag=f"b{b}n{n}C{c}")
+         _ptr(fg), _ptr(bg), _ptr(d_fg), _ptr(d_bg), _ptr(dx), _ptr(dq), b, n, c, float(drop_p), int(seed) & 0xFFFFFFFF,
+         _stream(), nbytes=8.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     return dx, dq
 
 
 @ada_pool_bwd_features.register_fake
-def _(x, q, pool_q, key_mask, d_fg, d_bg):
+def _(x, q, pool_q, key_mask, d_fg, d_bg, drop_p=0.0, seed=0):
     return torch.empty_like(x), torch.empty_like(q)
 
 
 def _ada_pool_setup2(ctx, inputs, output):
-    x, q, pool_q, key_mask, want_attn = inputs
+    x, q, pool_q, key_mask, want_attn = inputs[:5]
+    ctx.drop_p, ctx.seed = (inputs[5], inputs[6]) if len(inputs) > 5 else (0.0, 0)
     ctx.save_for_backward(x, q, pool_q, key_mask)
     ctx.feat_needs, ctx.q_needs = x.requires_grad or q.requires_grad, pool_q.requires_grad
 
@@ -1339,11 +1343,11 @@ def _ada_pool_backward2(ctx, g_fg, g_bg, g_afg, g_abg):
     x, q, pool_q, key_mask = ctx.saved_tensors
     z = lambda g: torch.zeros((x.shape[0], x.shape[2]), dtype=torch.float32, device=x.device) if g is None else g
     g_fg, g_bg = z(g_fg), z(g_bg)
-    d_pq = ada_pool_bwd(x, q, pool_q, key_mask, g_fg, g_bg) if ctx.q_needs else None
+    d_pq = ada_pool_bwd(x, q, pool_q, key_mask, g_fg, g_bg, ctx.drop_p, ctx.seed) if ctx.q_needs else None
     dx = dq = None
     if ctx.feat_needs:
-        dx, dq = ada_pool_bwd_features(x, q, pool_q, key_mask, g_fg, g_bg)
-    return dx, dq, d_pq, None, None
+        dx, dq = ada_pool_bwd_features(x, q, pool_q, key_mask, g_fg, g_bg, ctx.drop_p, ctx.seed)
+    return dx, dq, d_pq, None, None, None, None
 
 
 ada_pool.register_autograd(_ada_pool_backward2, setup_context=_ada_pool_setup2)

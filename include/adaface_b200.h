@@ -245,7 +245,12 @@ int afb_ada_pool_prep_batched(const afb_ada_prep_item* items, int n_items, int m
                               afb_stream_t stream);
 int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, float* fg_out,
                  float* bg_out, float* attn_fg, float* attn_bg, float* ws, int batch, int n_tokens, int channels,
-                 afb_stream_t stream);
+                 float drop_p, uint32_t seed, afb_stream_t stream);
+/* drop_p, seed (afb_ada_pool and its two backward entry points): the AttentionalPooler's train-mode Dropout on the
+ * attention probabilities (embedding_manager.py:138, 296).  drop_p = 0 is eval mode.  With drop_p > 0 probability
+ * (b, head, fg/bg, token) is kept (and scaled by 1 / (1 - drop_p)) when a counter-based hash of (seed, element index)
+ * says so; the backward entry points regenerate the same mask from the same (drop_p, seed).  The reference's second
+ * dropout (`out_drop` on the pooled features, :308-313) is an elementwise op on a [B, C] tensor and stays with the caller. */
 
 /* ---- K13: AdaEmbedding head.  Replaces embedding_manager.py:847-893.
  * infeat_fg/bg fp32 [B, C]; time_emb fp32 [B, time_ld] (first TD = C/4 used); coeff_w fp32 [K*r, 2C+TD],
@@ -310,7 +315,7 @@ int afb_ada_head_bwd(const float* infeat_fg, const float* infeat_bg, const float
                      int channels, int td, int num_vectors, int r, int out_dim, afb_stream_t stream);
 int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask, const float* stats,
                      const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg, float* d_pool_q, int batch,
-                     int n_tokens, int channels, afb_stream_t stream);
+                     int n_tokens, int channels, float drop_p, uint32_t seed, afb_stream_t stream);
 int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const float* lora_to_bg_q, const float* lora_to_k,
                           const float* d_pool_q, float* d_lora_to_fg_q, float* d_lora_to_bg_q, float* d_lora_to_k, int batch,
                           int channels, afb_stream_t stream);
@@ -328,7 +333,8 @@ int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const fl
                              int hw, int groups, float eps, afb_stream_t stream);
 int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
                               const float* stats, const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg,
-                              afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels, afb_stream_t stream);
+                              afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels, float drop_p, uint32_t seed,
+                              afb_stream_t stream);
 
 /* ---- layout / dtype helpers on the path's edges ---------------------------------------------------------- */
 int afb_cast_f32_to_bf16(const float* src, afb_bf16* dst, int64_t n, afb_stream_t stream);

@@ -248,8 +248,11 @@ def replace_rows_by_conv_attn(sim: Tensor, q: Tensor, k: Tensor, subj_indices, i
 # --------------------------------------------------------------------------------------------
 def attentional_pooler(x: Tensor, q: Tensor, to_k_weight: Tensor, fg_q_emb: Tensor, bg_q_emb: Tensor,
                        lora_to_k: Tensor, lora_to_fg_q: Tensor, lora_to_bg_q: Tensor,
-                       img_mask: Optional[Tensor] = None, infeat_size=None, n_heads: int = 8):
-    """AttentionalPooler.forward in eval mode: embedding_manager.py:146-321.
+                       img_mask: Optional[Tensor] = None, infeat_size=None, n_heads: int = 8,
+                       attn_keep_scale: Optional[Tensor] = None):
+    """AttentionalPooler.forward: embedding_manager.py:146-321.  Eval mode by default; attn_keep_scale [B, h, 2, N]
+    (0 or 1 / (1 - p)) stands for `self.attn_drop(attn)` in train mode (:296) with the mask given explicitly (the
+    tests pass the mask the kernels regenerate from their seed, `pool_keep_scale`).
 
     x, q: [B,N,C]; to_k_weight: the layer's attn2.to_k weight [C,768]; fg_q_emb [768]; bg_q_emb [B,768];
     lora_*: grouped 1x1 Conv1d weights [C/8, C/8, 1] (8 groups, C/8 -> C/64 each; :124-126).
@@ -283,11 +286,30 @@ def attentional_pooler(x: Tensor, q: Tensor, to_k_weight: Tensor, fg_q_emb: Tens
         m = F.interpolate(img_mask, size=infeat_size, mode="nearest").reshape(b, 1, 1, -1).bool()
         sim = sim.masked_fill(~m, -torch.finfo(sim.dtype).max)
     attn = sim.reshape(b, n_heads, -1).softmax(dim=-1).reshape(sim.shape)  # :273-286 joint over 2N
+    if attn_keep_scale is not None:                                        # :296 train-mode dropout
+        attn = attn * attn_keep_scale
     attn_fg, attn_bg = attn[:, :, 0:1], attn[:, :, 1:2]
     fg_out = torch.matmul(attn_fg, vh).permute(0, 2, 1, 3).reshape(b, c)   # :307,316
     bg_out = torch.matmul(attn_bg, vh).permute(0, 2, 1, 3).reshape(b, c)   # :312,316
     return {"fg_out": fg_out, "bg_out": bg_out,
             "attn_fg": attn_fg.reshape(b * n_heads, 1, n), "attn_bg": attn_bg.reshape(b * n_heads, 1, n)}
+
+
+def pool_keep_scale(seed: int, b: int, n_tokens: int, drop_p: float, n_heads: int = 8) -> Tensor:
+    """The keep-scale [B, h, 2, N] of the pooling kernels' train-mode attention dropout (csrc/common.cuh
+    pool_drop_scale): element (b, g, i, t) hashes (seed, ((b*8 + g)*2 + i)*N + t) with the murmur3 finaliser in 32-bit
+    wrap-around arithmetic; kept (scale 1 / (1 - p)) when the top 24 bits / 2^24 >= p."""
+    m32 = 0xFFFFFFFF
+    idx = torch.arange(b * n_heads * 2 * n_tokens, dtype=torch.int64)
+    h = ((idx & m32) * 0x9E3779B1 + (seed & m32)) & m32
+    h = h ^ (h >> 16)
+    h = (h * 0x85EBCA6B) & m32
+    h = h ^ (h >> 13)
+    h = (h * 0xC2B2AE35) & m32
+    h = h ^ (h >> 16)
+    u = (h >> 8).to(torch.float32) * (1.0 / 16777216.0)
+    keep = (u >= torch.tensor(drop_p, dtype=torch.float32)).to(torch.float32) / (1.0 - drop_p)
+    return keep.reshape(b, n_heads, 2, n_tokens)
 
 
 def ada_embedding(p: Params, ca_layer_idx: int, x: Tensor, q: Tensor, to_k_weight: Tensor,

@@ -159,6 +159,53 @@ def test_ada_embedding_parameter_gradients(cuda_device, ca, n):
     assert all(float(got[k].grad.abs().max()) == 0.0 for k in other)
 
 
+@pytest.mark.parametrize("c,n", [(320, 400), (1280, 64)])
+def test_attentional_pooler_train_mode_dropout(cuda_device, c, n):
+    """AttentionalPooler in TRAIN mode (embedding_manager.py:138-139, 296): Dropout(0.1) on the attention probabilities
+    inside the pooling kernel, mask regenerated by the backward kernels.  Forward and the gradients towards the three
+    grouped-conv weights and the layer features against fp32 autograd through the port with the SAME mask
+    (port.pool_keep_scale restates the kernels' counter-based hash).  out_drop (a torch op on [B, C]) is switched off here
+    so that the comparison is deterministic."""
+    import adaface_b200 as afb
+    d = cuda_device
+    b, layer_idx = 3, 7
+    pooler = afb.AttentionalPooler(layer_idx, c).to(d).train()
+    pooler.out_drop = torch.nn.Identity()
+    w = {k: _r(f"pd.{k}", (c // 8, c // 8, 1), (c // 8) ** -0.5) for k in ("lora_to_k", "lora_to_fg_q", "lora_to_bg_q")}
+    with torch.no_grad():
+        for k, v in w.items():
+            getattr(pooler, k).weight.copy_(v)
+    x, q = (_r(f"pd.{t}", (b, n, c), 1.2).to(torch.bfloat16) for t in ("x", "q"))
+    to_k_w = _r("pd.tok", (c, 768), 768 ** -0.5)
+    probe, extra = _r("pd.pr", (768,), 0.5), _r("pd.ex", (b, 768), 0.5)
+    g_fg, g_bg = _r("pd.gf", (b, c)), _r("pd.gb", (b, c))
+    torch.manual_seed(5)
+    seed = (torch.initial_seed() * 0x9E3779B1 + layer_idx * 0x85EBCA6B + 1 * 0xC2B2AE35) & 0xFFFFFFFF     # first call
+    keep = port.pool_keep_scale(seed, b, n, 0.1)
+    assert 0.05 < float((keep == 0).float().mean()) < 0.15
+    # ---- oracle
+    rw = {k: v.clone().requires_grad_(True) for k, v in w.items()}
+    xr, qr = x.float().requires_grad_(True), q.float().requires_grad_(True)
+    ref = port.attentional_pooler(xr, qr, to_k_w, probe, extra, rw["lora_to_k"], rw["lora_to_fg_q"], rw["lora_to_bg_q"],
+                                  attn_keep_scale=keep)
+    (ref["fg_out"] * g_fg).sum().add((ref["bg_out"] * g_bg).sum()).backward()
+    # ---- product
+    to_k = torch.nn.Linear(768, c, bias=False).to(d).requires_grad_(False)
+    with torch.no_grad():
+        to_k.weight.copy_(to_k_w)
+    xd, qd = x.to(d).requires_grad_(True), q.to(d).requires_grad_(True)
+    out = pooler({"x": xd, "q": qd, "to_k": to_k, "infeat_size": None}, probe.to(d), extra.to(d), want_attn=True)
+    assert rel_l2(out["fg_out"], ref["fg_out"].detach()) < 2e-3 and rel_l2(out["bg_out"], ref["bg_out"].detach()) < 2e-3
+    assert rel_l2(out["attn_fg"], ref["attn_fg"].detach()) < 2e-3          # the returned maps are the dropped ones (:296-298)
+    eval_out = pooler.eval()({"x": xd, "q": qd, "to_k": to_k, "infeat_size": None}, probe.to(d), extra.to(d), want_attn=False)
+    assert rel_l2(eval_out["fg_out"], out["fg_out"]) > 1e-2                 # the mask did something
+    (out["fg_out"] * g_fg.to(d)).sum().add((out["bg_out"] * g_bg.to(d)).sum()).backward()
+    errs = {k: rel_l2(getattr(pooler, k).weight.grad, rw[k].grad) for k in w}
+    errs["x"], errs["q"] = rel_l2(xd.grad.float(), xr.grad), rel_l2(qd.grad.float(), qr.grad)
+    print(f"pooler train mode C={c} N={n}: gradient rel-L2 " + " ".join(f"{k}={v:.1e}" for k, v in errs.items()))
+    assert max(errs[k] for k in w) < 1e-4 and max(errs["x"], errs["q"]) < GRAD_TOL
+
+
 @pytest.mark.parametrize("c,hw,ca", [(320, 16, 0), (640, 8, 3)])
 def test_inversion_step_through_one_spatial_transformer(cuda_device, c, hw, ca):
     """The block-level inversion step: frozen SpatialTransformer, two subjects' AdaEmbeddings wired in, loss = MSE of the
