@@ -1,8 +1,11 @@
 // Explicit (materialised) cross-attention for the optional modes of CrossAttention.forward that need the score
 // matrix itself: `save_attn_vars` (attention.py:245-255 caches attn and attnscore as [B, 8, N, 77]) and the
 // convolutional-attention row replacement (attention.py:208-216 -> ldm/util.py:701-879).  Only the 77-token
-// cross-attention ever runs here (the score tensor is B*8*N*77 fp32, 161 MB at 64x64, B = 16); the default path
-// stays on the fused tcgen05 kernel of attention.cu.  These are plain CUDA-core kernels: 4*N*77*C FLOPs per sample.
+// cross-attention ever runs here (the score tensor is B*8*N*77 fp32, 161 MB at 64x64, B = 16: the kernels are bound by
+// writing and re-reading it); the default path stays on the fused tcgen05 kernel of attention.cu.  The two contractions
+// (Q K^T and P V) run on warp-level tensor-core MMAs (mma.sync.m16n8k16 bf16, fp32 accumulate); the score matrix has to
+// exist in global memory between them (the conv-attention pass rewrites rows of it), which is why this is not a mode of
+// the fused kernel.
 //
 //   cross_scores_kernel     sim[b,h,n,t] = scale * q[b,n,h,:] . k[b,t,h,:]
 //   conv_attn_conv_kernel   conv[i,h,p]  = scale / ks^1.5 * sum_{dy,dx} q[p + (dy,dx) - pad] . k[tok_i[dy*ks+dx]]
@@ -28,32 +31,81 @@ __device__ __forceinline__ float dot8(const uint4& a, const uint4& b, float acc)
   return acc;
 }
 
-// grid (ceil(N / 128), heads, B); dynamic smem: K head slice [T][D] bf16
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// shared-memory row pitches (elements): + 8 keeps every row 16-byte aligned and the 8 rows of an ldmatrix / the 8 key
+// rows of a B fragment on distinct banks for D = 40 (padded to 48), 80, 160 and for the 80-wide probability rows
+template <int D>
+struct ExCfg {
+  static constexpr int kD16 = (D + 15) / 16 * 16;      // head dim padded to whole k16 steps (zero columns)
+  static constexpr int kPitch = kD16 + 8;
+};
+constexpr int kTMax = 256;
+
+// grid (ceil(N / 128), heads, B); block = 4 warps, 32 query rows (two m16 tiles) each.
+// dynamic smem: K head slice [Tp][kPitch], Q tile [128][kPitch] bf16 (Tp = T rounded up to 8; padding rows / columns zero)
 template <int D>
 __global__ void __launch_bounds__(kRows) cross_scores_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k,
                                                          float* __restrict__ sim, int N, int T, int heads, long long ldq,
                                                          long long ldk, float scale) {
+  using X = ExCfg<D>;
   extern __shared__ __align__(16) uint8_t sh_raw[];
-  uint4* sk = reinterpret_cast<uint4*>(sh_raw);                 // [T][D / 8]
-  constexpr int V = D / 8;
-  const int h = blockIdx.y, b = blockIdx.z;
-  for (int i = threadIdx.x; i < T * V; i += blockDim.x) {
+  const int Tp = (T + 7) & ~7;
+  __nv_bfloat16* sk = reinterpret_cast<__nv_bfloat16*>(sh_raw);           // [Tp][kPitch]
+  __nv_bfloat16* sq = sk + Tp * X::kPitch;                                // [128][kPitch]
+  constexpr int V = X::kD16 / 8;                                          // 16-byte vectors per padded row
+  const int h = blockIdx.y, b = blockIdx.z, n0 = blockIdx.x * kRows;
+  const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = threadIdx.x; i < Tp * V; i += blockDim.x) {
     const int t = i / V, c = i % V;
-    sk[i] = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * T + t) * ldk + h * D + c * 8);
+    uint4 val = zero;
+    if (t < T && c * 8 < D) val = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * T + t) * ldk + h * D + c * 8);
+    *reinterpret_cast<uint4*>(sk + t * X::kPitch + c * 8) = val;
+  }
+  for (int i = threadIdx.x; i < kRows * V; i += blockDim.x) {
+    const int r = i / V, c = i % V;
+    uint4 val = zero;
+    if (n0 + r < N && c * 8 < D) val = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * N + n0 + r) * ldq + h * D + c * 8);
+    *reinterpret_cast<uint4*>(sq + r * X::kPitch + c * 8) = val;
   }
   __syncthreads();
-  const int n = blockIdx.x * kRows + threadIdx.x;
-  if (n >= N) return;
-  uint4 qr[V];
-  const uint4* qp = reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * N + n) * ldq + h * D);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+  const int lm_row = ((lane >> 3) & 1) * 8 + (lane & 7), lm_k = (lane >> 4) * 8;
+#pragma unroll 1
+  for (int mt = 0; mt < 2; ++mt) {
+    const int r0 = warp * 32 + mt * 16;
+    uint32_t a[X::kD16 / 16][4];
 #pragma unroll
-  for (int c = 0; c < V; ++c) qr[c] = qp[c];
-  float* out = sim + ((static_cast<long long>(b) * heads + h) * N + n) * T;
-  for (int t = 0; t < T; ++t) {
-    float acc = 0.f;
+    for (int kk = 0; kk < X::kD16 / 16; ++kk)
+      ldmatrix_x4(a[kk], smem_u32(sq + (r0 + lm_row) * X::kPitch + kk * 16 + lm_k));
+    const int row_a = n0 + r0 + g, row_b = row_a + 8;
+    float* out_a = sim + ((static_cast<long long>(b) * heads + h) * N + row_a) * T;
+    float* out_b = out_a + 8ll * T;
+    for (int nt = 0; nt < Tp / 8; ++nt) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const __nv_bfloat16* kb = sk + (nt * 8 + g) * X::kPitch + 2 * t4;
 #pragma unroll
-    for (int c = 0; c < V; ++c) acc = dot8(qr[c], sk[t * V + c], acc);
-    out[t] = acc * scale;
+      for (int kk = 0; kk < X::kD16 / 16; ++kk)
+        mma_16816(acc, a[kk], *reinterpret_cast<const uint32_t*>(kb + kk * 16), *reinterpret_cast<const uint32_t*>(kb + kk * 16 + 8));
+      const int c0 = nt * 8 + 2 * t4;
+      if (row_a < N) {
+        if (c0 < T) out_a[c0] = acc[0] * scale;
+        if (c0 + 1 < T) out_a[c0 + 1] = acc[1] * scale;
+      }
+      if (row_b < N) {
+        if (c0 < T) out_b[c0] = acc[2] * scale;
+        if (c0 + 1 < T) out_b[c0 + 1] = acc[3] * scale;
+      }
+    }
   }
 }
 
@@ -102,55 +154,80 @@ __global__ void conv_attn_scatter_kernel(const float* __restrict__ conv, const i
   sim[((static_cast<long long>(inst_batch[ii]) * heads + h) * N + p) * T + tok[ii * M + m]] = v;
 }
 
-// grid (ceil(N / 128), heads, B); dynamic smem: V head slice [T][D] bf16 + probabilities [T][128] fp32
+// grid (ceil(N / 128), heads, B); block = 4 warps.  Phase 1, one thread per query row: row max, exponentials (kept
+// unnormalised, <= 1) as bf16 into shared memory, 1 / sum per row, the optional normalised fp32 attention matrix.
+// Phase 2: out = (E V) / sum on the tensor cores, 32 rows (two m16 tiles) per warp, V transposed in shared memory so
+// that a B fragment's token pair is one 32-bit load.
+// dynamic smem: E [128][kEP], V^T [kD16][kEP] bf16 (kEP = Tp16 + 8, Tp16 = T rounded up to 16; padding zero), 1/sum [128] fp32
 template <int D>
 __global__ void __launch_bounds__(kRows) softmax_pv_kernel(const float* __restrict__ sim, const __nv_bfloat16* __restrict__ v,
                                                        float* __restrict__ attn, __nv_bfloat16* __restrict__ out, int N, int T,
                                                        int heads, long long ldv, long long ldo) {
+  using X = ExCfg<D>;
   extern __shared__ __align__(16) uint8_t sh_raw[];
-  constexpr int V = D / 8;
-  uint4* sv = reinterpret_cast<uint4*>(sh_raw);                  // [T][V]
-  float* sp = reinterpret_cast<float*>(sh_raw + static_cast<size_t>(T) * V * 16);   // [T][kRows]
-  const int h = blockIdx.y, b = blockIdx.z;
-  for (int i = threadIdx.x; i < T * V; i += blockDim.x) {
-    const int t = i / V, c = i % V;
-    sv[i] = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * T + t) * ldv + h * D + c * 8);
+  const int Tp16 = (T + 15) & ~15, EP = Tp16 + 8;
+  __nv_bfloat16* se = reinterpret_cast<__nv_bfloat16*>(sh_raw);           // [128][EP]
+  __nv_bfloat16* svt = se + kRows * EP;                                   // [kD16][EP]
+  float* s_inv = reinterpret_cast<float*>(svt + X::kD16 * EP);            // [128]
+  const int h = blockIdx.y, b = blockIdx.z, n0 = blockIdx.x * kRows;
+  for (int i = threadIdx.x; i < X::kD16 * EP / 2; i += blockDim.x) reinterpret_cast<uint32_t*>(svt)[i] = 0u;
+  __syncthreads();
+  for (int i = threadIdx.x; i < T * (D / 8); i += blockDim.x) {
+    const int t = i / (D / 8), c = i % (D / 8);
+    const uint4 u = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * T + t) * ldv + h * D + c * 8);
+    const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) svt[(c * 8 + j) * EP + t] = e[j];
+  }
+  {
+    const int n = n0 + threadIdx.x;
+    __nv_bfloat16* erow = se + threadIdx.x * EP;
+    float inv = 0.f;
+    if (n < N) {
+      const long long row = ((static_cast<long long>(b) * heads + h) * N + n) * T;
+      float mx = -INFINITY;
+      for (int t = 0; t < T; ++t) mx = fmaxf(mx, sim[row + t]);
+      float sum = 0.f;
+      for (int t = 0; t < T; ++t) {
+        const float e = __expf(sim[row + t] - mx);          // (second read of the row: L1-resident)
+        sum += e;
+        erow[t] = __float2bfloat16_rn(e);
+      }
+      inv = 1.0f / sum;
+      if (attn != nullptr)
+        for (int t = 0; t < T; ++t) attn[row + t] = __expf(sim[row + t] - mx) * inv;
+      for (int t = T; t < Tp16; ++t) erow[t] = __float2bfloat16_rn(0.f);
+    } else {
+      for (int t = 0; t < Tp16; ++t) erow[t] = __float2bfloat16_rn(0.f);
+    }
+    s_inv[threadIdx.x] = inv;
   }
   __syncthreads();
-  const int n = blockIdx.x * kRows + threadIdx.x;
-  if (n >= N) return;
-  const long long row = ((static_cast<long long>(b) * heads + h) * N + n) * T;
-  float mx = -INFINITY;
-  for (int t = 0; t < T; ++t) {
-    const float s = sim[row + t];
-    sp[t * kRows + threadIdx.x] = s;
-    mx = fmaxf(mx, s);
-  }
-  float sum = 0.f;
-  for (int t = 0; t < T; ++t) {
-    const float e = __expf(sp[t * kRows + threadIdx.x] - mx);
-    sp[t * kRows + threadIdx.x] = e;
-    sum += e;
-  }
-  const float inv = 1.0f / sum;
-  if (attn != nullptr)
-    for (int t = 0; t < T; ++t) attn[row + t] = sp[t * kRows + threadIdx.x] * inv;
-  __nv_bfloat16* orow = out + (static_cast<long long>(b) * N + n) * ldo + h * D;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+  const int lm_row = ((lane >> 3) & 1) * 8 + (lane & 7), lm_k = (lane >> 4) * 8;
+  const int ksteps = Tp16 / 16;
 #pragma unroll 1
-  for (int c = 0; c < V; ++c) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int t = 0; t < T; ++t) {
-      const float pr = sp[t * kRows + threadIdx.x];
-      const uint4 u = sv[t * V + c];
-      const float2 a0 = unpack_bf16x2(u.x), a1 = unpack_bf16x2(u.y), a2 = unpack_bf16x2(u.z), a3 = unpack_bf16x2(u.w);
-      acc[0] = fmaf(pr, a0.x, acc[0]); acc[1] = fmaf(pr, a0.y, acc[1]);
-      acc[2] = fmaf(pr, a1.x, acc[2]); acc[3] = fmaf(pr, a1.y, acc[3]);
-      acc[4] = fmaf(pr, a2.x, acc[4]); acc[5] = fmaf(pr, a2.y, acc[5]);
-      acc[6] = fmaf(pr, a3.x, acc[6]); acc[7] = fmaf(pr, a3.y, acc[7]);
+  for (int mt = 0; mt < 2; ++mt) {
+    const int r0 = warp * 32 + mt * 16;
+    uint32_t a[kTMax / 16][4];
+#pragma unroll
+    for (int kk = 0; kk < kTMax / 16; ++kk)
+      if (kk < ksteps) ldmatrix_x4(a[kk], smem_u32(se + (r0 + lm_row) * EP + kk * 16 + lm_k));
+    const int row_a = n0 + r0 + g, row_b = row_a + 8;
+    const float inv_a = s_inv[r0 + g], inv_b = s_inv[r0 + g + 8];
+    for (int nt = 0; nt < D / 8; ++nt) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const __nv_bfloat16* vb = svt + (nt * 8 + g) * EP + 2 * t4;
+#pragma unroll
+      for (int kk = 0; kk < kTMax / 16; ++kk)
+        if (kk < ksteps)
+          mma_16816(acc, a[kk], *reinterpret_cast<const uint32_t*>(vb + kk * 16), *reinterpret_cast<const uint32_t*>(vb + kk * 16 + 8));
+      const int c0 = h * D + nt * 8 + 2 * t4;
+      if (row_a < N)
+        *reinterpret_cast<uint32_t*>(out + (static_cast<long long>(b) * N + row_a) * ldo + c0) = pack_bf16x2(acc[0] * inv_a, acc[1] * inv_a);
+      if (row_b < N)
+        *reinterpret_cast<uint32_t*>(out + (static_cast<long long>(b) * N + row_b) * ldo + c0) = pack_bf16x2(acc[2] * inv_b, acc[3] * inv_b);
     }
-    *reinterpret_cast<uint4*>(orow + c * 8) =
-        make_uint4(pack_bf16x2(acc[0] * inv, acc[1] * inv), pack_bf16x2(acc[2] * inv, acc[3] * inv),
-                   pack_bf16x2(acc[4] * inv, acc[5] * inv), pack_bf16x2(acc[6] * inv, acc[7] * inv));
   }
 }
 
@@ -168,7 +245,7 @@ int check_common(const void* a, const void* b, int batch, int heads, int head_di
   AFB_REQUIRE(lda >= heads * head_dim && ldb >= heads * head_dim && lda % 8 == 0 && ldb % 8 == 0,
               "%s: leading dimensions must cover heads*head_dim and be multiples of 8", who);
   AFB_REQUIRE(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0, "%s: operands must be 16-byte aligned", who);
-  AFB_REQUIRE(t <= 256, "%s: context length %d > 256 (this path is for the 77-token cross-attention)", who, t);
+  AFB_REQUIRE(t <= kTMax, "%s: context length %d > %d (this path is for the 77-token cross-attention)", who, t, kTMax);
   return 0;
 }
 
@@ -189,7 +266,8 @@ extern "C" int afb_cross_scores(const afb_bf16* q, const afb_bf16* k, float* sim
   if (int rc = check_common(q, k, batch, heads, head_dim, q_len, kv_len, ldq, ldk, "afb_cross_scores")) return rc;
   AFB_REQUIRE(sim != nullptr, "afb_cross_scores: NULL output");
   const dim3 grid((q_len + kRows - 1) / kRows, heads, batch);
-  const size_t sh = static_cast<size_t>(kv_len) * head_dim * 2;
+  const int d16 = (head_dim + 15) / 16 * 16;
+  const size_t sh = (static_cast<size_t>((kv_len + 7) & ~7) + kRows) * (d16 + 8) * 2;
   const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(q);
   const __nv_bfloat16* kb = reinterpret_cast<const __nv_bfloat16*>(k);
   AFB_DISPATCH_D(head_dim, {
@@ -234,7 +312,8 @@ extern "C" int afb_softmax_pv(const float* sim, const afb_bf16* v, float* attn, 
   if (int rc = check_common(v, out, batch, heads, head_dim, q_len, kv_len, ldv, ldo, "afb_softmax_pv")) return rc;
   AFB_REQUIRE(sim != nullptr, "afb_softmax_pv: NULL scores");
   const dim3 grid((q_len + kRows - 1) / kRows, heads, batch);
-  const size_t sh = static_cast<size_t>(kv_len) * head_dim * 2 + static_cast<size_t>(kv_len) * kRows * 4;
+  const int d16 = (head_dim + 15) / 16 * 16, ep = ((kv_len + 15) & ~15) + 8;
+  const size_t sh = (static_cast<size_t>(kRows) + d16) * ep * 2 + kRows * sizeof(float);
   AFB_REQUIRE(sh <= 200 * 1024, "afb_softmax_pv: context too long for shared memory");
   const __nv_bfloat16* vb = reinterpret_cast<const __nv_bfloat16*>(v);
   __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(out);

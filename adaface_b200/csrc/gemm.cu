@@ -295,7 +295,10 @@ struct TCfg {
   //  instead -- a wide tile needs TWO of the three slots, so only one half tile of epilogue overlaps the next mainloop; a
   //  second team of eight epilogue warps, one per half, changed nothing for that reason: 20.9 vs 19.5 us at
   //  16384 x 640 x 640, and was removed)
-  static constexpr int kEpiWarps = GEGLU ? 16 : AFB_GEMM_EPI_WARPS;
+#ifndef AFB_GEMM_WIDE_EPI_WARPS
+#define AFB_GEMM_WIDE_EPI_WARPS 8
+#endif
+  static constexpr int kEpiWarps = GEGLU ? 16 : (kWide ? AFB_GEMM_WIDE_EPI_WARPS : AFB_GEMM_EPI_WARPS);
   static constexpr int kGroups = kEpiWarps / 4;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kStagingBytes = 2 * kOutChunks * kBoxBytes;     // double-buffered
@@ -1177,7 +1180,8 @@ int launch_tma(const afb_gemm_args& a, cudaStream_t stream) {
       // (measured per shape, B200: K >= 1280 gains 2-10 % -- the 3x3 convolutions, FF-out, the C = 1280 projections --,
       //  K = 640 is even, K = 320 loses 10-15 %: its [65536, 320] activation streams from HBM and the three-stage ring of
       //  the wide tile is too shallow for that)
-      if (a.n % (2 * BN) == 0 && a.conv_fold == 0 && a.k >= 1280 && wide_enabled()) {
+      static const int wide_min_k = [] { const char* e = getenv("AFB_GEMM_WIDE_MIN_K"); return e != nullptr ? atoi(e) : 1280; }();
+      if (a.n % (2 * BN) == 0 && a.conv_fold == 0 && a.k >= wide_min_k && wide_enabled()) {
         // waves x operand KB per CTA and k-block: 16 + 2 * 10 for a wide tile, 16 + 10 for a BN-wide one
         const int64_t pairs = num_sms() / 2, m_units = (a.m + 2 * kBM - 1) / (2 * kBM);
         const int64_t wide = (m_units * (a.n / (2 * BN)) + pairs - 1) / pairs * 36, narrow = (m_units * (a.n / BN) + pairs - 1) / pairs * 26;
