@@ -3,10 +3,11 @@ box (reference: ldm/modules/diffusionmodules/openaimodel.py - UNetModel :417-105
 Upsample/Downsample :95-165, TimestepEmbedSequential :76-92; timestep_embedding diffusionmodules/util.py:154).
 
 What is product here: the 16 `SpatialTransformer`s (adaface_b200.attention), the per-layer context plumbing
-(`get_layer_context`, openaimodel.py:863-920) and the AdaEmbedding wiring (`AdaPromptContext`).  The ResBlock /
-up / down-sample convolutions are deliberately left on torch (cuDNN, bf16 channels-last) - `north_star` keeps them
-outside the scope and reports them separately; this file only wraps them.  State-dict keys equal the reference's
-UNetModel, so an SD-1.5 checkpoint (`model.diffusion_model.*`) loads unchanged.
+(`get_layer_context`, openaimodel.py:863-920) and the AdaEmbedding wiring (`AdaPromptContext`).  The shell around
+them - ResBlocks, up / down-sampling, conv_in / conv_out, the time embedding - is outside `north_star`'s hot path (SURVEY.md
+8f N1/N4, reported separately by bench.py) and runs on this repo's kernels too (GroupNorm + SiLU folds, implicit-GEMM 3x3
+convolutions, per-timestep tables); torch ops take over while gradients are recorded and under AFB_CONV=0.  State-dict keys
+equal the reference's UNetModel, so an SD-1.5 checkpoint (`model.diffusion_model.*`) loads unchanged.
 
 Activations between blocks are bf16 channels-last: a [B, C, H, W] channels-last tensor IS the token-major
 [B, H*W, C] layout the transformer kernels use, so no transposition happens at a SpatialTransformer's edges.
@@ -141,7 +142,7 @@ class _Bf16Conv(nn.Conv2d):
 
     def native_ok(self, x) -> bool:
         """True when this convolution runs as an implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3)
-        instead of cuDNN: AFB_CONV=1 and a supported geometry."""
+        instead of cuDNN: the default (AFB_CONV != 0) for every supported geometry."""
         if _NATIVE_CONV == "0" or _differentiated(x):      # (the implicit-GEMM convolution has no backward: cuDNN via torch)
             return False
         if _NATIVE_CONV == "auto":
@@ -738,7 +739,8 @@ class UNetModel(nn.Module):
             ada.prepare_queries(self.spatial_transformers())
         bundle = self.emb_bundle(emb, e_all)
         hs = []
-        h = self.input_blocks[0][0].conv_add(x.to(torch.bfloat16).contiguous(memory_format=CL))
+        with ops.scope("resblock"):                 # (conv_in belongs to the shell, not to the SpatialTransformer path)
+            h = self.input_blocks[0][0].conv_add(x.to(torch.bfloat16).contiguous(memory_format=CL))
         hs.append(h)
         layer_idx = 1
         for module in list(self.input_blocks)[1:]:
