@@ -44,6 +44,33 @@ def gn_cases():
         print(f"groupnorm b{b} n{hw} C{c}{'+%d' % c2 if c2 else ''} act{act}: {us:7.2f} us  {mb / us * 1e3 / 1e3:6.2f} TB/s (read + write once)")
 
 
+def ada_cases():
+    """The AdaEmbedding chain of one cross-attention layer as the U-Net runs it (8 cond samples): pooling (main + combine
+    launches) and the head with the context splice; queries prepared once outside (they are on a side stream in the step)."""
+    d = "cuda"
+    K, r, b = 9, 12, 8
+    for n, c, td in [(4096, 320, 320), (1024, 640, 320), (256, 1280, 320), (64, 1280, 320)]:
+        x = torch.randn(b, n, c, device=d).to(torch.bfloat16)
+        q = torch.randn(b, n, c, device=d).to(torch.bfloat16)
+        pool_q = torch.randn(b, 2, c, device=d)
+        te = torch.randn(b, 1280, device=d)
+        f = 2 * c + td
+        cw, cb = torch.randn(K * r, f, device=d) * f ** -0.5, torch.zeros(K * r, device=d)
+        basis, bias = torch.randn(K, r, 768, device=d), torch.zeros(K, 768, device=d)
+        ctx = torch.zeros(2 * b, 77, 768, device=d, dtype=torch.bfloat16)
+        pos = torch.arange(2, 2 + K, device=d, dtype=torch.int32)
+
+        def pool():
+            return ops.ada_pool(x, q, pool_q, None, False)
+
+        def chain():
+            fg, bg, _, _ = ops.ada_pool(x, q, pool_q, None, False)
+            return ops.ada_head_splice(fg, bg, te, td, cw, cb, basis, bias, ctx, pos)
+
+        t_pool, t_chain = timed(pool), timed(chain)
+        print(f"ada chain b{b} n{n} C{c}: pool (main + combine) {t_pool:6.2f} us, pool + head {t_chain:6.2f} us, head alone {t_chain - t_pool:6.2f} us")
+
+
 if __name__ == "__main__":
     with torch.no_grad():
-        {"gn": gn_cases}[sys.argv[1]]()
+        {"gn": gn_cases, "ada": ada_cases}[sys.argv[1]]()
