@@ -1021,10 +1021,11 @@ __global__ void __launch_bounds__(kAmThreads) attn_bwd_mma_kernel(
     const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
     const __nv_bfloat16* __restrict__ dout, const float* __restrict__ lse, const float* __restrict__ delta,
     float* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv, int q_len, int kv_len, int heads, long long ldq,
-    long long ldk, long long ldv, long long ldo, long long ldg, float scale) {
+    long long ldk, long long ldv, long long ldo, long long ldg, float scale, const uint8_t* __restrict__ key_mask) {
   constexpr int DPAD = (D + 15) / 16 * 16;
   constexpr int LD = DPAD + 8;                   // operand row pitch (bf16 elements)
   constexpr int CW = DPAD / kSplit;              // output columns of this block
+  __shared__ uint8_t s_keep[kAlT];               // key mask of this block's 64 keys (1 = attended)
   constexpr int NT = CW / 8;                     // 8-column accumulator tiles
   static_assert(CW % 8 == 0, "column slice");
   extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -1054,6 +1055,7 @@ __global__ void __launch_bounds__(kAmThreads) attn_bwd_mma_kernel(
     *reinterpret_cast<uint4*>(sV + r * LD + c8) = vv;
   }
   (void)zero;
+  if (tid < kAlT) s_keep[tid] = (key_mask == nullptr || k0 + tid >= kv_len) ? 1 : key_mask[static_cast<long long>(b) * kv_len + k0 + tid];
   float acc_k[NT][4], acc_v[NT][4];
 #pragma unroll
   for (int n = 0; n < NT; ++n)
@@ -1116,6 +1118,13 @@ __global__ void __launch_bounds__(kAmThreads) attn_bwd_mma_kernel(
             const bool ok = row_ok && k0 + c + e < kv_len;
             pr[e] = ok ? exp2f(s_acc[j][2 * half + e] * scale_log2 - l2) : 0.f;
             ds[e] = pr[e] * (p_acc[j][2 * half + e] - dl) * scale;
+            if (s_keep[c + e] == 0) {
+              // masked key (attention.py:223-232, masked_fill after the scaling): its score is a constant, so no gradient
+              // reaches q / k through it; its probability is 0 unless the whole row is masked (the forward's lse is then
+              // the fill value itself and the row averages V uniformly)
+              pr[e] = (ok && l2 < -1.0e29f) ? 1.0f / static_cast<float>(kv_len) : 0.f;
+              ds[e] = 0.f;
+            }
           }
           *reinterpret_cast<uint32_t*>(sP + r * kAmPS + c) = pack_bf16x2(pr[0], pr[1]);
           *reinterpret_cast<uint32_t*>(sS + r * kAmPS + c) = pack_bf16x2(ds[0], ds[1]);
@@ -1209,7 +1218,7 @@ int launch_attn_bwd_mma(const afb_attn_args& a, const __nv_bfloat16* dout, const
   dim3 grid(((a.kv_len + kAlT - 1) / kAlT) * kSplit, a.heads, a.batch);
   kern<<<grid, kAmThreads, sh, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
                                          reinterpret_cast<const __nv_bfloat16*>(a.v), dout, a.lse, delta, dq, dk, dv, a.q_len,
-                                         a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale);
+                                         a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale, a.key_mask);
   return 0;
 }
 
@@ -1249,7 +1258,7 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
   AFB_REQUIRE(args != nullptr && dout && delta_ws && dq && dk && dv, "afb_attention_bwd: NULL argument");
   const afb_attn_args& a = *args;
   AFB_REQUIRE(a.q && a.k && a.v && a.out && a.lse, "afb_attention_bwd: q, k, v, the forward output and its lse are needed");
-  AFB_REQUIRE(a.key_mask == nullptr, "afb_attention_bwd: the backward with a key mask is not built");
+
   AFB_REQUIRE(a.batch > 0 && a.heads > 0 && a.q_len > 0 && a.kv_len > 0 && a.batch <= 65535 && a.heads <= 65535,
               "afb_attention_bwd: bad sizes");
   const int width = a.heads * a.head_dim;
@@ -1270,7 +1279,8 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
   const bool vec_ok = ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |
                         reinterpret_cast<uintptr_t>(dout)) & 15) == 0 &&
                       a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0;
-  const bool mma = attn_bwd_mma_enabled() && vec_ok;
+  const bool mma = (attn_bwd_mma_enabled() || a.key_mask != nullptr) && vec_ok;
+  AFB_REQUIRE(a.key_mask == nullptr || mma, "afb_attention_bwd: the key-masked backward needs 16-byte aligned operands");
   switch (a.head_dim) {
     case 40: rc = mma ? launch_attn_bwd_mma<40, 1>(a, db, delta_ws, dq, dk, dv, ldg, stream)
                       : launch_attn_bwd_long<40>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;

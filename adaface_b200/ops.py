@@ -1170,7 +1170,8 @@ ada_pool_prep.register_autograd(_ada_pool_prep_backward, setup_context=_ada_pool
 
 # ---- second stage: self-attention, GroupNorm and the pooler's gradient towards the layer features --------------------
 @torch.library.custom_op("adaface_b200::attention_lse", mutates_args=())
-def attention_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float) -> Tuple[Tensor, Tensor]:
+def attention_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float,
+                  key_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
     """`attention` that also returns the log2-domain log-sum-exp of every query row, fp32 [B, heads, Nq] - what the
     backward needs to rebuild the probabilities.  Used instead of `attention` while gradients are recorded."""
     _need_cuda(q, k, v)
@@ -1180,7 +1181,9 @@ def attention_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float) -> 
         raise ValueError("attention_lse: shape mismatch")
     out = torch.empty((b, nq, c), dtype=torch.bfloat16, device=q.device)
     lse = torch.empty((b, heads, nq), dtype=torch.float32, device=q.device)
-    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=None, batch=b, heads=heads,
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, nk).to(torch.uint8).contiguous()
+    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=_ptr(key_mask), batch=b, heads=heads,
                     head_dim=c // heads, q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"),
                     ldo=c, scale=scale, lse=_ptr(lse))
     _run("attention_fwd", _lib.load().afb_attention_fwd, C.byref(args), _stream(), flops=4.0 * b * nq * nk * c,
@@ -1189,14 +1192,15 @@ def attention_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float) -> 
 
 
 @attention_lse.register_fake
-def _(q, k, v, heads, scale):
+def _(q, k, v, heads, scale, key_mask=None):
     return q.new_empty(q.shape, dtype=torch.bfloat16), q.new_empty((q.shape[0], heads, q.shape[1]), dtype=torch.float32)
 
 
 @torch.library.custom_op("adaface_b200::attention_bwd", mutates_args=())
 def attention_bwd(q: Tensor, k: Tensor, v: Tensor, out: Tensor, lse: Tensor, dout: Tensor, heads: int,
-                  scale: float) -> Tuple[Tensor, Tensor, Tensor]:
-    """Backward of `attention_lse` for any key length (self-attention): -> (dq, dk, dv) fp32 [B, L, C]."""
+                  scale: float, key_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+    """Backward of `attention_lse` for any key length (self-attention): -> (dq, dk, dv) fp32 [B, L, C].  key_mask
+    (uint8 / bool [B, Nk], 0 = masked) as in the forward: masked keys pass no gradient to q / k (attention.py:223-232)."""
     _need_cuda(q, k, v, out, lse, dout)
     b, nq, c = q.shape
     nk = k.shape[1]
@@ -1208,7 +1212,9 @@ def attention_bwd(q: Tensor, k: Tensor, v: Tensor, out: Tensor, lse: Tensor, dou
     dk = torch.empty((b, nk, c), dtype=torch.float32, device=dev)
     dv = torch.empty((b, nk, c), dtype=torch.float32, device=dev)
     ws = torch.empty((b * heads * nq,), dtype=torch.float32, device=dev)
-    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=None, batch=b, heads=heads,
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, nk).to(torch.uint8).contiguous()
+    args = AttnArgs(q=_ptr(q), k=_ptr(k), v=_ptr(v), out=_ptr(out), key_mask=_ptr(key_mask), batch=b, heads=heads,
                     head_dim=c // heads, q_len=nq, kv_len=nk, ldq=_ld3(q, "q"), ldk=_ld3(k, "k"), ldv=_ld3(v, "v"),
                     ldo=c, scale=scale, lse=_ptr(lse))
     _run("attention_bwd", _lib.load().afb_attention_bwd, C.byref(args), _ptr(dout), _ptr(ws), _ptr(dq), _ptr(dk), _ptr(dv), c,
@@ -1217,22 +1223,23 @@ def attention_bwd(q: Tensor, k: Tensor, v: Tensor, out: Tensor, lse: Tensor, dou
 
 
 @attention_bwd.register_fake
-def _(q, k, v, out, lse, dout, heads, scale):
+def _(q, k, v, out, lse, dout, heads, scale, key_mask=None):
     f = lambda t: t.new_empty(t.shape, dtype=torch.float32)
     return f(q), f(k), f(v)
 
 
 def _attention_lse_setup(ctx, inputs, output):
-    q, k, v, heads, scale = inputs
+    q, k, v, heads, scale = inputs[:5]
+    key_mask = inputs[5] if len(inputs) > 5 else None
     out, lse = output
-    ctx.save_for_backward(q, k, v, out, lse)
+    ctx.save_for_backward(q, k, v, out, lse, key_mask)
     ctx.heads, ctx.scale = heads, scale
 
 
 def _attention_lse_backward(ctx, g, g_lse):
-    q, k, v, out, lse = ctx.saved_tensors
-    dq, dk, dv = attention_bwd(q, k, v, out, lse, _bf16c(g), ctx.heads, ctx.scale)
-    return dq.to(q.dtype), dk.to(k.dtype), dv.to(v.dtype), None, None
+    q, k, v, out, lse, key_mask = ctx.saved_tensors
+    dq, dk, dv = attention_bwd(q, k, v, out, lse, _bf16c(g), ctx.heads, ctx.scale, key_mask)
+    return dq.to(q.dtype), dk.to(k.dtype), dv.to(v.dtype), None, None, None
 
 
 attention_lse.register_autograd(_attention_lse_backward, setup_context=_attention_lse_setup)
@@ -1242,9 +1249,7 @@ def attention_auto(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float, ke
     """`attention`, or - while gradients are recorded through a long key sequence - `attention_lse`, whose backward
     covers self-attention.  (The short-key backward of `attention` needs no saved statistics.)"""
     if torch.is_grad_enabled() and k.shape[1] > 128 and (q.requires_grad or k.requires_grad or v.requires_grad):
-        if key_mask is not None:
-            raise NotImplementedError("adaface_b200: the self-attention backward with a key mask is not built")
-        return attention_lse(q, k, v, heads, scale)[0]
+        return attention_lse(q, k, v, heads, scale, key_mask)[0]
     return attention(q, k, v, heads, scale, key_mask)
 
 

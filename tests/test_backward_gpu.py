@@ -8,8 +8,8 @@ whole frozen U-Net.
 Measured on B200: AdaEmbedding parameter gradients 3e-8..7e-7 (fp32 kernels); block-level inversion step 4.7e-3..7.8e-3
 on every trained tensor; self-attention dQ / dK / dV 1.7e-3; whole-U-Net step: flat gradient of the 3.81 M trained values
 rel-L2 1.2e-2, cosine 0.99993 (worst single tensor 2.5e-2 after 25 bf16 blocks forward and backward).
-ResBlocks / resampling / output head differentiate through torch (outside the path, like their forward convolutions);
-the key-masked self-attention backward and the AttentionalPooler's train-mode Dropout(0.1) are not built."""
+ResBlocks / resampling / output head differentiate through torch (outside the path).  Also covered: the key-masked
+self-attention backward (incl. a fully masked sample) and the AttentionalPooler's train-mode Dropout(0.1)."""
 import math
 
 import pytest
@@ -282,6 +282,35 @@ def test_self_attention_backward(ops, cuda_device, c, nq):
     errs = [rel_l2(qd.grad[..., i * c:(i + 1) * c].float(), ref.grad[..., i * c:(i + 1) * c]) for i in range(3)]
     print(f"self-attention backward C={c} N={nq}: dq {errs[0]:.1e} dk {errs[1]:.1e} dv {errs[2]:.1e}")
     assert max(errs) < GRAD_TOL
+
+
+@pytest.mark.parametrize("c,nq", [(320, 700), (640, 256)])
+def test_self_attention_backward_with_key_mask(ops, cuda_device, c, nq):
+    """Key-masked self-attention (attention.py:223-232: masked_fill(-finfo.max) after the scaling) forward and backward:
+    masked keys pass no gradient to q / k, and a FULLY masked sample averages V uniformly (its dV is dO / N)."""
+    d = cuda_device
+    b, heads = 3, 8
+    qkv = _r("sam.qkv", (b, nq, 3 * c), 0.8).to(torch.bfloat16)
+    go = _r("sam.go", (b, nq, c)).to(torch.bfloat16)
+    mask = _r("sam.m", (b, nq)) > -0.4                    # ~ 2/3 of the keys attended
+    mask[2] = False                                       # sample 2: everything masked
+    scale = (c // heads) ** -0.5
+    ref = qkv.float().requires_grad_(True)
+    qr, kr, vr = ref[..., :c], ref[..., c:2 * c], ref[..., 2 * c:]
+    sim = port.attention_scores(qr, kr, heads, scale)
+    sim = sim.masked_fill(~mask[:, None, None, :], -torch.finfo(sim.dtype).max)
+    o = torch.matmul(sim.softmax(-1), vr.reshape(b, nq, heads, c // heads).permute(0, 2, 1, 3)).permute(0, 2, 1, 3).reshape(b, nq, c)
+    o.backward(go.float())
+    qd = qkv.to(d).requires_grad_(True)
+    out = ops.attention_auto(qd[..., :c], qd[..., c:2 * c], qd[..., 2 * c:], heads, scale, mask.to(d))
+    assert rel_l2(out.float(), o.detach()) < 1e-2
+    out.backward(go.to(d))
+    errs = [rel_l2(qd.grad[..., i * c:(i + 1) * c].float(), ref.grad[..., i * c:(i + 1) * c]) for i in range(3)]
+    print(f"masked self-attention backward C={c} N={nq}: dq {errs[0]:.1e} dk {errs[1]:.1e} dv {errs[2]:.1e}")
+    assert max(errs) < GRAD_TOL
+    g = qd.grad.float().cpu()
+    assert float(g[2, :, :2 * c].abs().max()) == 0.0      # no gradient to q / k of the fully masked sample
+    assert float(g[0, :, c:2 * c][~mask[0]].abs().max()) == 0.0      # nor to masked keys
 
 
 def test_groupnorm_tokens_backward(ops, cuda_device):
