@@ -536,7 +536,9 @@ def run_ours(args):
             # its result inside the timed region.  The context of step i+1 does not depend on step i: its H2D copy is
             # issued on a copy stream into a staging buffer while step i computes (double buffering), and moved into the
             # step's (graph-captured) input buffers by a device copy when the step starts.  x_t and the read-back of
-            # x_prev stay on the compute stream.
+            # x_prev stay on the compute stream; the read-back of step i lands in one of two pinned host buffers and the
+            # host waits for it only before reusing that buffer (step i + 2), so it queues at most two steps ahead and
+            # the device does not idle for a host round trip between steps.
             copy_stream = torch.cuda.Stream()
             stage = [(torch.empty_like(c_d), torch.empty_like(uc_d)) for _ in range(2)]
             staged = [torch.cuda.Event() for _ in range(2)]
@@ -560,11 +562,15 @@ def run_ours(args):
                 consumed[k].record(main)
                 prefetch(i + 1)                                   # overlaps this step's compute
                 xp = ddim_step(x_d, i)
-                x_out_h.copy_(xp, non_blocking=True)
-                main.synchronize()
+                read_back[k].synchronize()                        # step i - 2's read-back has left this host buffer
+                x_out_hs[k].copy_(xp, non_blocking=True)
+                read_back[k].record(main)
 
+            x_out_hs = [x_out_h, torch.empty_like(x_out_h).pin_memory()]
+            read_back = [torch.cuda.Event() for _ in range(2)]
             for k in range(2):
                 consumed[k].record(torch.cuda.current_stream())
+                read_back[k].record(torch.cuda.current_stream())
             prefetch(0)
             for i in range(2):
                 e2e_step(i)
@@ -579,7 +585,8 @@ def run_ours(args):
             d2h = x_out_h.numel() * 4
             e2e_api = ("DDIMSampler.p_sample_ddim on pinned host x_T / context, result read back; every step copies its "
                        "x_t and its whole context from pinned host memory (the context copy of step i+1 is issued on a "
-                       "copy stream while step i computes) and reads x_prev back before the next step starts")
+                       "copy stream while step i computes) and reads x_prev back into one of two pinned host buffers; the host waits "
+                       "for a read-back before reusing its buffer (two steps later), all of them inside the timed region")
         else:
             # ---- timed region: ONE sharded sampling job - K DDIM steps on this rank's samples, then the all-gather of
             # the final latents over NCCL, all between the two events (device time, max over ranks)
