@@ -374,6 +374,369 @@ __global__ void __launch_bounds__(kPoolThreads, (kChunks <= 2 ? 2 : 1)) ada_pool
   }
 }
 
+// ============================================================================================
+// Tensor-core pooling kernel (round 2).  The SIMT kernel above spends ~250 warp instructions per token on a serial
+// chain of warp reductions (ncu: issue-bound at 61 %, 1.2 TB/s); here the three contractions run on warp-level MMAs:
+//   phase A  per token t and (stream i, head g):  Dx = sum_{c in g} u_i[c] x_t[c],  Dq = sum_{c in g} u_i[c] q_t[c],
+//            plus sum_c q_t[c] and sum_c q_t[c]^2:  [tokens x C] x [C x 16] products with the folded queries as a
+//            block-structured B operand (u split into bf16 hi + lo parts: fp32-accurate scores)
+//   phase B  (one warp, lane = token)  LayerNorm statistics of q_t, raw score s8 (Dx + rstd (Dq - mean U_i,g)), head
+//            smoothing, key mask, online joint softmax bookkeeping, probabilities p and p * rstd as bf16 hi + lo tables
+//   phase C  acc^T[c][(i, g(c))] += sum_t x_t[c] p_t + q_t[c] (p_t rstd_t):  [C x tokens] x [tokens x 8] products, A =
+//            the staged tile read transposed (ldmatrix.trans); out_i[c] = s8 (acc - sum_t p_t rstd_t mean_t)
+// v = (x + LN(q)) / sqrt(8) is never formed.  Block = 4 warps, tile = kTok tokens of x and q in shared memory.
+constexpr int kPmThreads = 128;
+
+__device__ __forceinline__ void pm_ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void pm_ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void pm_mma(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void pm_cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int n = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ uint32_t pm_bf16x2_mul(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+// hi + lo bf16 split of an fp32 value (hi = rn(v), lo = rn(v - hi))
+__device__ __forceinline__ void pm_split(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(v);
+  lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
+template <int kC>
+struct PmCfg {
+  static constexpr int kDg = kC / kHeads;                       // channels per head: 40 / 80 / 160
+  static constexpr int kTok = kC <= 320 ? 64 : (kC <= 640 ? 32 : 16);   // tokens per tile (~82 KB of x + q)
+  static constexpr int kMT = kTok / 16;                          // token m16-tiles per tile
+  static constexpr int kKS = 4 / kMT;                            // K slices of phase A (warps per token m-tile)
+  static constexpr int kPitch = kC + 8;                          // tile row pitch (bf16): 16-byte aligned, conflict-free ldmatrix
+  static constexpr int kKSteps = kC / 16;
+  static constexpr int kStepsPerSlice = kKSteps / kKS;
+  static constexpr int kCT = kC / 16;                            // channel m16-tiles of phase C
+  static constexpr int kCTPerWarp = kCT / 4;
+  static constexpr int kPP = kTok + 8;                           // pitch of the transposed probability tables
+  static constexpr int kPartCols = 36;                           // Dx[16] Dq[16] sum sq (+2 pad)
+  static constexpr size_t kSmem = 2ull * kTok * kPitch * 2 + 4ull * kC * 2 + 4ull * 16 * kPP * 2 +
+                                  static_cast<size_t>(kKS) * kTok * kPartCols * 4 + 224 * 4;
+  static_assert(kKSteps % kKS == 0 && kCT % 4 == 0 && kDg % 8 == 0, "geometry");
+};
+
+template <int kC>
+__global__ void __launch_bounds__(kPmThreads, 2) ada_pool_mma_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ q, const float* __restrict__ u,
+    const uint8_t* __restrict__ key_mask, float* __restrict__ scores, float* __restrict__ partials, int N,
+    int tokens_per_block, float drop_p, uint32_t seed) {
+  using P = PmCfg<kC>;
+  extern __shared__ __align__(16) uint8_t pm_smem[];
+  __nv_bfloat16* sx = reinterpret_cast<__nv_bfloat16*>(pm_smem);          // [kTok][kPitch]
+  __nv_bfloat16* sq = sx + P::kTok * P::kPitch;                           // [kTok][kPitch]
+  __nv_bfloat16* su = sq + P::kTok * P::kPitch;                           // [hi fg | hi bg | lo fg | lo bg][kC]
+  __nv_bfloat16* sp = su + 4 * kC;                                        // [p_hi | p_lo | pr_hi | pr_lo][16][kPP]
+  float* s_part = reinterpret_cast<float*>(sp + 4 * 16 * P::kPP);         // [kKS][kTok][kPartCols]
+  float* s_misc = s_part + P::kKS * P::kTok * P::kPartCols;               // [0..8) corr, [8] any rescale, [16..32) U_i,g, [32..48) sum p rstd mean, [48..80) tile max per warp, [80..88) l
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.y, blk = blockIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gl = lane >> 2, t4 = lane & 3;
+  // folded queries of this sample as bf16 hi + lo; U_i,g = sum of u_i over head g (fp32)
+  for (int idx = tid; idx < 2 * kC; idx += kPmThreads) {
+    __nv_bfloat16 hi, lo;
+    pm_split(u[static_cast<long long>(b) * 2 * kC + idx], hi, lo);
+    su[idx] = hi;
+    su[2 * kC + idx] = lo;
+  }
+  {
+    // eight lanes per (stream, head): strided partial sums, then three shuffles
+    const int ig = tid >> 3, sub = tid & 7;
+    const float* up = u + static_cast<long long>(b) * 2 * kC + (ig >> 3) * kC + (ig & 7) * P::kDg;
+    float a = 0.f;
+#pragma unroll 5
+    for (int c = sub; c < P::kDg; c += 8) a += up[c];
+    a += __shfl_xor_sync(0xffffffffu, a, 1);
+    a += __shfl_xor_sync(0xffffffffu, a, 2);
+    a += __shfl_xor_sync(0xffffffffu, a, 4);
+    if (sub == 0) s_misc[16 + ig] = a;
+  }
+  const int t_begin = blk * tokens_per_block;
+  const int t_end = min(N, t_begin + tokens_per_block);
+  // phase A role: token m-tile and K slice of this warp; phase C role: channel m-tiles warp, warp + 4, ...
+  const int a_mt = warp % P::kMT, a_ks = warp / P::kMT;
+  const int lm_row = ((lane >> 3) & 1) * 8 + (lane & 7), lm_k = (lane >> 4) * 8;            // ldmatrix (A = tokens x channels)
+  const int lt_tok = (lane & 7) + (lane >> 4) * 8, lt_ch = ((lane >> 3) & 1) * 8;          // ldmatrix.trans (A = channels x tokens)
+  float acc[P::kCTPerWarp][4];
+#pragma unroll
+  for (int i = 0; i < P::kCTPerWarp; ++i)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+  // softmax state of this thread's (stream, heads) - see phase B: the running max (equal in every thread that owns the
+  // head), its partial sum of exponentials and of p * rstd * mean over the tokens it has handled
+  float m_run[kHeads], l_part[kHeads], c_part[kHeads];
+#pragma unroll
+  for (int g = 0; g < kHeads; ++g) {
+    m_run[g] = -INFINITY;
+    l_part[g] = c_part[g] = 0.f;
+  }
+  const uint32_t sx_u = smem_u32(sx), sq_u = smem_u32(sq);
+
+  for (int t0 = t_begin; t0 < t_end; t0 += P::kTok) {
+    __syncthreads();                                      // the previous tile (and the u tables, first time) is done with
+    // ---- stage the tile: rows past t_end are zero-filled
+    for (int i = tid; i < P::kTok * (kC / 8); i += kPmThreads) {
+      const int r = i / (kC / 8), v = i - r * (kC / 8);
+      const bool ok = t0 + r < t_end;
+      const long long off = (static_cast<long long>(b) * N + (ok ? t0 + r : t_begin)) * kC + v * 8;
+      pm_cp_async16(sx_u + (r * P::kPitch + v * 8) * 2, x + off, ok);
+      pm_cp_async16(sq_u + (r * P::kPitch + v * 8) * 2, q + off, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    // ---- phase A: this warp's 16 tokens x its K slice
+    {
+      float dx[2][4], dq[2][4], dsum[4], dsq[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dx[0][e] = dx[1][e] = dq[0][e] = dq[1][e] = dsum[e] = dsq[e] = 0.f;
+      const uint32_t ax = sx_u + ((a_mt * 16 + lm_row) * P::kPitch + lm_k) * 2;
+      const uint32_t aq = sq_u + ((a_mt * 16 + lm_row) * P::kPitch + lm_k) * 2;
+      const uint32_t ones = 0x3F803F80u;                  // bf16 (1, 1)
+#pragma unroll 2
+      for (int s = 0; s < P::kStepsPerSlice; ++s) {
+        const int ks = a_ks * P::kStepsPerSlice + s;
+        uint32_t fx[4], fq[4], fq2[4];
+        pm_ldmatrix_x4(fx, ax + ks * 32);
+        pm_ldmatrix_x4(fq, aq + ks * 32);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) fq2[e] = pm_bf16x2_mul(fq[e], fq[e]);
+        pm_mma(dsum, fq, ones, ones);
+        pm_mma(dsq, fq2, ones, ones);
+        // B fragments: column n = gl is head gl; rows k = 2 t4, 2 t4 + 1 (b0) and + 8 (b1) are channels of this step
+        const int c0 = ks * 16 + 2 * t4, c1 = c0 + 8;
+        const bool in0 = c0 / P::kDg == gl, in1 = c1 / P::kDg == gl;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const uint32_t h0 = in0 ? *reinterpret_cast<const uint32_t*>(su + i * kC + c0) : 0u;
+          const uint32_t h1 = in1 ? *reinterpret_cast<const uint32_t*>(su + i * kC + c1) : 0u;
+          const uint32_t l0 = in0 ? *reinterpret_cast<const uint32_t*>(su + (2 + i) * kC + c0) : 0u;
+          const uint32_t l1 = in1 ? *reinterpret_cast<const uint32_t*>(su + (2 + i) * kC + c1) : 0u;
+          pm_mma(dx[i], fx, h0, h1);
+          pm_mma(dx[i], fx, l0, l1);
+          pm_mma(dq[i], fq, h0, h1);
+          pm_mma(dq[i], fq, l0, l1);
+        }
+      }
+      // D fragment: rows gl, gl + 8 (tokens of this m-tile), columns 2 t4, 2 t4 + 1 (heads)
+      float* pa = s_part + (a_ks * P::kTok + a_mt * 16 + gl) * P::kPartCols;
+      float* pb = pa + 8 * P::kPartCols;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        pa[i * 8 + 2 * t4] = dx[i][0]; pa[i * 8 + 2 * t4 + 1] = dx[i][1];
+        pb[i * 8 + 2 * t4] = dx[i][2]; pb[i * 8 + 2 * t4 + 1] = dx[i][3];
+        pa[16 + i * 8 + 2 * t4] = dq[i][0]; pa[16 + i * 8 + 2 * t4 + 1] = dq[i][1];
+        pb[16 + i * 8 + 2 * t4] = dq[i][2]; pb[16 + i * 8 + 2 * t4 + 1] = dq[i][3];
+      }
+      if (t4 == 0) {
+        pa[32] = dsum[0]; pa[33] = dsq[0];
+        pb[32] = dsum[2]; pb[33] = dsq[2];
+      }
+    }
+    __syncthreads();
+    // ---- phase B: all 128 threads; the 128 / kTok adjacent lanes of a token split its 2 x 8 (stream, head) scores
+    {
+      constexpr int kLanesPerTok = kPmThreads / P::kTok;          // 2, 4, 8
+      constexpr int kHeadsPerThr = 16 / kLanesPerTok;             // 8, 4, 2 heads of ONE stream
+      const int r = tid / kLanesPerTok, part = tid % kLanesPerTok;
+      const int i = part / (kLanesPerTok / 2);                    // stream: 0 = fg, 1 = bg
+      const int g_lo = (part % (kLanesPerTok / 2)) * kHeadsPerThr;
+      const bool live = t0 + r < t_end;
+      float s_sum = 0.f, s_sq = 0.f;
+#pragma unroll
+      for (int s = 0; s < P::kKS; ++s) {
+        const float2 f = *reinterpret_cast<const float2*>(s_part + (s * P::kTok + r) * P::kPartCols + 32);
+        s_sum += f.x;
+        s_sq += f.y;
+      }
+      const float mean = s_sum * (1.0f / kC);
+      const float rstd = rsqrtf(fmaxf(s_sq * (1.0f / kC) - mean * mean, 0.f) + 1e-5f);          // k_ln = LN(q): :160
+      float sc[kHeadsPerThr];
+      float tot = 0.f;
+#pragma unroll
+      for (int j = 0; j < kHeadsPerThr; ++j) {
+        const int g = g_lo + j;
+        float vx = 0.f, vq = 0.f;
+#pragma unroll
+        for (int s = 0; s < P::kKS; ++s) {
+          const float* pp = s_part + (s * P::kTok + r) * P::kPartCols;
+          vx += pp[i * 8 + g];
+          vq += pp[16 + i * 8 + g];
+        }
+        // s = sum_c u_i[c] v[c], v = (x + (q - mean) rstd) / sqrt(8)   (:178, :247 after the fold)
+        sc[j] = kInvSqrt8 * (vx + rstd * (vq - mean * s_misc[16 + i * 8 + g]));
+        tot += sc[j];
+      }
+      // the other head groups of this (token, stream) sit in the adjacent lanes
+#pragma unroll
+      for (int o = 1; o < kLanesPerTok / 2; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+      const bool masked = live && key_mask != nullptr && key_mask[static_cast<long long>(b) * N + t0 + r] == 0;
+#pragma unroll
+      for (int j = 0; j < kHeadsPerThr; ++j) {
+        float s = 0.5f * sc[j] + 0.5f * (tot * 0.125f);                                          // :251-257
+        if (masked) s = kPoolMasked;                                                            // :259-269
+        if (!live) s = -INFINITY;
+        sc[j] = s;
+        if (scores != nullptr && live)
+          scores[((static_cast<long long>(b) * kHeads + g_lo + j) * 2 + i) * N + t0 + r] = s;
+        // tile max per head over tokens and both streams: lanes with equal head group are kLanesPerTok / 2 apart... reduce
+        // over everything except the head-group bits, then across the four warps through shared memory
+        float mx = s;
+#pragma unroll
+        for (int o = kLanesPerTok / 2; o < 32; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (lane < kLanesPerTok / 2) s_misc[48 + warp * 8 + g_lo + j] = mx;
+      }
+      __syncthreads();
+      __nv_bfloat16* t_hi = sp;
+      __nv_bfloat16* t_lo = sp + 16 * P::kPP;
+      __nv_bfloat16* q_hi = sp + 2 * 16 * P::kPP;
+      __nv_bfloat16* q_lo = sp + 3 * 16 * P::kPP;
+      bool any = false;
+#pragma unroll
+      for (int j = 0; j < kHeadsPerThr; ++j) {
+        const int g = g_lo + j;
+        const float tm = fmaxf(fmaxf(s_misc[48 + g], s_misc[56 + g]), fmaxf(s_misc[64 + g], s_misc[72 + g]));
+        const float m_new = fmaxf(m_run[j], tm);
+        const float corr = (m_run[j] == -INFINITY) ? 0.f : __expf(m_run[j] - m_new);
+        m_run[j] = m_new;
+        l_part[j] *= corr;
+        c_part[j] *= corr;
+        any = any || corr != 1.0f;
+        if (r == 0 && i == 0) s_misc[g] = corr;           // (one writer per head)
+        const float e = live ? __expf(sc[j] - m_new) : 0.f;
+        l_part[j] += e;
+        // train mode: dropout on the probabilities (:296): the normaliser keeps every entry
+        const float ek = e * (live ? pool_drop_scale(seed, b, g, i, t0 + r, N, drop_p) : 0.f);
+        const float er = ek * rstd;
+        c_part[j] = fmaf(er, mean, c_part[j]);
+        __nv_bfloat16 hi, lo;
+        pm_split(ek, hi, lo);
+        t_hi[(i * 8 + g) * P::kPP + r] = hi;
+        t_lo[(i * 8 + g) * P::kPP + r] = lo;
+        pm_split(er, hi, lo);
+        q_hi[(i * 8 + g) * P::kPP + r] = hi;
+        q_lo[(i * 8 + g) * P::kPP + r] = lo;
+      }
+      if (__syncthreads_or(any ? 1 : 0) != 0) {
+        if (tid == 0) s_misc[8] = 1.f;
+      } else if (tid == 0) {
+        s_misc[8] = 0.f;
+      }
+    }
+    __syncthreads();
+    // ---- phase C: acc^T[channel][(i, head of the channel)] += x^T p + q^T (p rstd) over this tile's tokens
+    {
+      const bool rescale = s_misc[8] != 0.f;
+      const __nv_bfloat16* tabs = sp;
+#pragma unroll
+      for (int ci = 0; ci < P::kCTPerWarp; ++ci) {
+        const int c0 = (warp + 4 * ci) * 16;              // first channel of this m16 tile
+        const int h0 = c0 / P::kDg, h1 = (c0 + 15) / P::kDg;
+        if (rescale) {
+          const float fa = s_misc[(c0 + gl) / P::kDg], fb = s_misc[(c0 + gl + 8) / P::kDg];
+          acc[ci][0] *= fa; acc[ci][1] *= fa;
+          acc[ci][2] *= fb; acc[ci][3] *= fb;
+        }
+        // B columns: 0 = (fg, h0), 1 = (bg, h0), 2 = (fg, h1), 3 = (bg, h1), 4..7 = 0; column n = gl of this lane
+        const int col = (gl & 1) * 8 + ((gl & 2) ? h1 : h0);
+        const __nv_bfloat16* bp = tabs + col * P::kPP + 2 * t4;
+        const uint32_t ax = sx_u + (lt_tok * P::kPitch + c0 + lt_ch) * 2;
+        const uint32_t aq = sq_u + (lt_tok * P::kPitch + c0 + lt_ch) * 2;
+#pragma unroll
+        for (int kk = 0; kk < P::kTok / 16; ++kk) {
+          uint32_t fx[4], fq[4];
+          pm_ldmatrix_x4_trans(fx, ax + kk * 16 * P::kPitch * 2);
+          pm_ldmatrix_x4_trans(fq, aq + kk * 16 * P::kPitch * 2);
+          uint32_t bh0 = 0u, bh1 = 0u, bl0 = 0u, bl1 = 0u, rh0 = 0u, rh1 = 0u, rl0 = 0u, rl1 = 0u;
+          if (gl < 4) {
+            const __nv_bfloat16* b = bp + kk * 16;
+            bh0 = *reinterpret_cast<const uint32_t*>(b);
+            bh1 = *reinterpret_cast<const uint32_t*>(b + 8);
+            bl0 = *reinterpret_cast<const uint32_t*>(b + 16 * P::kPP);
+            bl1 = *reinterpret_cast<const uint32_t*>(b + 16 * P::kPP + 8);
+            rh0 = *reinterpret_cast<const uint32_t*>(b + 2 * 16 * P::kPP);
+            rh1 = *reinterpret_cast<const uint32_t*>(b + 2 * 16 * P::kPP + 8);
+            rl0 = *reinterpret_cast<const uint32_t*>(b + 3 * 16 * P::kPP);
+            rl1 = *reinterpret_cast<const uint32_t*>(b + 3 * 16 * P::kPP + 8);
+          }
+          pm_mma(acc[ci], fx, bh0, bh1);
+          pm_mma(acc[ci], fx, bl0, bl1);
+          pm_mma(acc[ci], fq, rh0, rh1);
+          pm_mma(acc[ci], fq, rl0, rl1);
+        }
+      }
+    }
+  }
+
+  // ---- block partial: (max, sum) per head, then the two pooled streams  out_i[c] = s8 (acc - sum_t p rstd mean)
+  float* out = partials + (static_cast<long long>(b) * gridDim.x + blk) * pool_partial_floats(kC);
+  __syncthreads();
+  {
+    // per (stream, head) sums over the tokens: shuffles over the token bits of the lane index, one slot per warp, then
+    // four adds (shared-memory float atomics with 64 contenders per address cost more than the whole token loop)
+    constexpr int kLanesPerTok = kPmThreads / P::kTok;
+    constexpr int kHeadsPerThr = 16 / kLanesPerTok;
+    const int r = tid / kLanesPerTok, part = tid % kLanesPerTok;
+    const int i = part / (kLanesPerTok / 2), g_lo = (part % (kLanesPerTok / 2)) * kHeadsPerThr;
+    float* s_red = s_misc + 96;                           // [4 warps][l | c][16 (stream, head)]
+#pragma unroll
+    for (int j = 0; j < kHeadsPerThr; ++j) {
+      float ls = l_part[j], cs = c_part[j];
+#pragma unroll
+      for (int o = kLanesPerTok; o < 32; o <<= 1) {
+        ls += __shfl_xor_sync(0xffffffffu, ls, o);
+        cs += __shfl_xor_sync(0xffffffffu, cs, o);
+      }
+      if (lane < kLanesPerTok) {
+        s_red[(warp * 2 + 0) * 16 + i * 8 + g_lo + j] = ls;
+        s_red[(warp * 2 + 1) * 16 + i * 8 + g_lo + j] = cs;
+      }
+      if (r == 0 && i == 0) out[g_lo + j] = m_run[j];
+    }
+    __syncthreads();
+    if (tid < 16) s_misc[32 + tid] = s_red[16 + tid] + s_red[48 + tid] + s_red[80 + tid] + s_red[112 + tid];
+    if (tid < 8)
+      out[8 + tid] = (s_red[tid] + s_red[8 + tid]) + (s_red[32 + tid] + s_red[40 + tid]) + (s_red[64 + tid] + s_red[72 + tid]) +
+                     (s_red[96 + tid] + s_red[104 + tid]);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int ci = 0; ci < P::kCTPerWarp; ++ci) {
+    const int c0 = (warp + 4 * ci) * 16;
+    const int h0 = c0 / P::kDg, h1 = (c0 + 15) / P::kDg;
+    // D fragment: rows gl, gl + 8 (channels), columns 2 t4, 2 t4 + 1: t4 = 0 holds (fg, bg) of head h0, t4 = 1 of head h1
+    if (t4 < 2) {
+      const int hh = t4 == 0 ? h0 : h1;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int c = c0 + gl + 8 * half;
+        if (c / P::kDg == hh && (t4 == 0 || h1 != h0)) {
+          out[16 + c] = kInvSqrt8 * (acc[ci][2 * half] - s_misc[32 + hh]);
+          out[16 + kC + c] = kInvSqrt8 * (acc[ci][2 * half + 1] - s_misc[40 + hh]);
+        }
+      }
+    }
+  }
+}
+
 // grid (B, ceil(2C / 256)): every block recomputes the 8 heads' merge factors (nblocks exps each), then one thread
 // per pooled channel sums its nblocks partials
 __global__ void __launch_bounds__(256) ada_pool_combine_kernel(const float* __restrict__ partials, int nblocks, int C,
@@ -755,10 +1118,27 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
     AFB_CHECK_CUDA(launch_pdl(kern, grid, dim3(kPoolThreads), sh_main, stream, 1, xb, qb, pool_q, key_mask, scores_arg,     \
                               partials, n_tokens, C, tokens_per_block, drop_p, seed));                                    \
   }
-  if (chunks_per_lane <= 2) AFB_LAUNCH_POOL(2)
+#define AFB_LAUNCH_POOL_MMA(KC)                                                                                           \
+  {                                                                                                                       \
+    auto kern = ada_pool_mma_kernel<KC>;                                                                                  \
+    static bool set = false;                                                                                              \
+    if (!set) {                                                                                                           \
+      AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(PmCfg<KC>::kSmem))); \
+      set = true;                                                                                                         \
+    }                                                                                                                     \
+    AFB_CHECK_CUDA(launch_pdl(kern, grid, dim3(kPmThreads), PmCfg<KC>::kSmem, stream, 1, xb, qb, pool_q, key_mask, scores_arg, \
+                              partials, n_tokens, tokens_per_block, drop_p, seed));                                       \
+  }
+  // AFB_ADA_POOL=simt keeps the round-1 CUDA-core kernel (A/B measurement and cross-check); read once
+  static const bool pool_mma = [] { const char* e = getenv("AFB_ADA_POOL"); return e == nullptr || e[0] != 's'; }();
+  if (pool_mma && C == 320) AFB_LAUNCH_POOL_MMA(320)
+  else if (pool_mma && C == 640) AFB_LAUNCH_POOL_MMA(640)
+  else if (pool_mma && C == 1280) AFB_LAUNCH_POOL_MMA(1280)
+  else if (chunks_per_lane <= 2) AFB_LAUNCH_POOL(2)
   else if (chunks_per_lane <= 3) AFB_LAUNCH_POOL(3)
   else AFB_LAUNCH_POOL(kMaxChunksPerLane)
 #undef AFB_LAUNCH_POOL
+#undef AFB_LAUNCH_POOL_MMA
   count_launch();
   AFB_CHECK_CUDA(launch_pdl(ada_pool_combine_kernel, dim3(batch, (2 * C + 255) / 256), dim3(256), grid_x * 8 * sizeof(float), stream, 1,
                             partials, grid_x, C, fg_out, bg_out, stats));
