@@ -70,6 +70,7 @@ _SIGNATURES = {
     "afb_ada_pool_prep_batched": (_I, [_P, _I, _I, _I, _I, _P]),
     "afb_ada_pool": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, C.c_uint32, _P]),
     "afb_ada_head": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _I, _I, _I, _I, _I, _I, _P]),
+    "afb_ada_head_pooled": (_I, [_P, _I, _P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _I, _I, _I, _I, _I, _I, _P]),
     "afb_static_layerwise_embedding": (_I, [_P, _P, _P, _I, _P, _P, _P, _I, _I, _I, _I, _P]),
     "afb_first_token_pos": (_I, [_P, _I64, _P, _I, _I, _P]),
     "afb_splice_static_embedding": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),

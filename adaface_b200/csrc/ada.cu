@@ -812,9 +812,13 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
                                                        const float* __restrict__ basis, const float* __restrict__ bias,
                                                        float* __restrict__ out, __nv_bfloat16* __restrict__ ctx_out,
                                                        const int* __restrict__ token_pos, long long ctx_sample_stride,
-                                                       long long basis_sample_stride, int C, int TD, int K, int R, int D) {
-  extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D]
+                                                       long long basis_sample_stride, int C, int TD, int K, int R, int D,
+                                                       const float* __restrict__ partials, int nblocks,
+                                                       float* __restrict__ fg_out, float* __restrict__ bg_out,
+                                                       float* __restrict__ stats_out) {
+  extern __shared__ float sh[];    // feat [2C + TD], coeffs [R], vec [D], (fused combine) merge factors [nblocks][8]
   __shared__ float red[32];
+  __shared__ float s_lsum[kHeads];
   const int k = blockIdx.x, b = blockIdx.y;
   const int F = 2 * C + TD;
   {
@@ -835,12 +839,58 @@ __global__ void __launch_bounds__(256) ada_head_kernel(const float* __restrict__
   float* feat = sh;
   float* coeffs = feat + F;
   float* vec = coeffs + ((R + 3) & ~3);
-  for (int i = threadIdx.x; i < F; i += blockDim.x) {
-    float v;
-    if (i < C) v = infeat_fg[static_cast<long long>(b) * C + i];
-    else if (i < 2 * C) v = infeat_bg[static_cast<long long>(b) * C + i - C];
-    else v = time_emb[static_cast<long long>(b) * time_ld + i - 2 * C];        // time_emb[:, :TD]  :849
-    feat[i] = v;
+  if (partials != nullptr) {
+    // the pooling kernel's chunk partials are merged HERE (the separate combine launch, 6.6 us on the critical path of
+    // every cross-attention layer, disappears): every block recomputes the 8 heads' merge factors, then each thread sums
+    // its pooled channels over the chunks; the k = 0 blocks also publish the pooled features and the softmax statistics
+    float* s_scl = vec + D;
+    const int dg = C / kHeads;
+    const long long rec = pool_partial_floats(C);
+    const float* base = partials + static_cast<long long>(b) * nblocks * rec;
+    const int warp_ = threadIdx.x >> 5, lane_ = threadIdx.x & 31;
+    {
+      const int g = warp_;              // 8 warps = 8 heads
+      float m = -INFINITY;
+      for (int j = lane_; j < nblocks; j += 32) m = fmaxf(m, base[j * rec + g]);
+      m = warp_max(m);
+      float l = 0.f;
+      for (int j = lane_; j < nblocks; j += 32) {
+        const float mj = base[j * rec + g];
+        const float scl = (mj == -INFINITY) ? 0.f : __expf(mj - m);
+        s_scl[j * 8 + g] = scl;
+        l += scl * base[j * rec + 8 + g];
+      }
+      l = warp_sum(l);
+      if (lane_ == 0) {
+        s_lsum[g] = l;
+        if (k == 0 && stats_out != nullptr) {
+          stats_out[(static_cast<long long>(b) * 8 + g) * 2] = m;
+          stats_out[(static_cast<long long>(b) * 8 + g) * 2 + 1] = l;
+        }
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
+      const int c = i % C, g = c / dg;
+      float a = 0.f;
+      for (int j = 0; j < nblocks; ++j) a += s_scl[j * 8 + g] * base[j * rec + 16 + i];
+      a /= s_lsum[g];
+      if (k == 0) {
+        if (i < C) { if (fg_out != nullptr) fg_out[static_cast<long long>(b) * C + c] = a; }
+        else if (bg_out != nullptr) bg_out[static_cast<long long>(b) * C + c] = a;
+      }
+      if (i >= C && infeat_bg != nullptr) a = infeat_bg[static_cast<long long>(b) * C + c];   // cached bg pooling (:789-792)
+      feat[i] = a;
+    }
+    for (int i = 2 * C + threadIdx.x; i < F; i += blockDim.x) feat[i] = time_emb[static_cast<long long>(b) * time_ld + i - 2 * C];
+  } else {
+    for (int i = threadIdx.x; i < F; i += blockDim.x) {
+      float v;
+      if (i < C) v = infeat_fg[static_cast<long long>(b) * C + i];
+      else if (i < 2 * C) v = infeat_bg[static_cast<long long>(b) * C + i - C];
+      else v = time_emb[static_cast<long long>(b) * time_ld + i - 2 * C];        // time_emb[:, :TD]  :849
+      feat[i] = v;
+    }
   }
   __syncthreads();
   // LNCat3 (:38-58): LayerNorm (no affine) on the pooled features and on the time slice separately
@@ -1085,7 +1135,11 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
                             float drop_p, uint32_t seed, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  AFB_REQUIRE(x && q && pool_q && fg_out && bg_out && ws, "afb_ada_pool: NULL argument");
+  AFB_REQUIRE(x && q && pool_q && ws, "afb_ada_pool: NULL argument");
+  // fg_out == bg_out == NULL: the chunk partials stay in ws and afb_ada_head_pooled merges them (no combine launch)
+  const bool deferred = fg_out == nullptr && bg_out == nullptr;
+  AFB_REQUIRE(deferred || (fg_out && bg_out), "afb_ada_pool: fg_out and bg_out must both be given or both NULL");
+  AFB_REQUIRE(!deferred || attn_fg == nullptr, "afb_ada_pool: attention maps need the merged statistics (give fg_out / bg_out)");
   AFB_REQUIRE(batch > 0 && n_tokens > 0, "afb_ada_pool: empty input");
   AFB_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "afb_ada_pool: drop_p must be in [0, 1)");
   AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_pool: channels %d must be a multiple of 64, <= 1280", channels);
@@ -1140,9 +1194,11 @@ extern "C" int afb_ada_pool(const afb_bf16* x, const afb_bf16* q, const float* p
 #undef AFB_LAUNCH_POOL
 #undef AFB_LAUNCH_POOL_MMA
   count_launch();
-  AFB_CHECK_CUDA(launch_pdl(ada_pool_combine_kernel, dim3(batch, (2 * C + 255) / 256), dim3(256), grid_x * 8 * sizeof(float), stream, 1,
-                            partials, grid_x, C, fg_out, bg_out, stats));
-  count_launch();
+  if (!deferred) {
+    AFB_CHECK_CUDA(launch_pdl(ada_pool_combine_kernel, dim3(batch, (2 * C + 255) / 256), dim3(256), grid_x * 8 * sizeof(float), stream, 1,
+                              partials, grid_x, C, fg_out, bg_out, stats));
+    count_launch();
+  }
   if (attn_fg != nullptr) {
     const long long total = static_cast<long long>(batch) * kHeads * 2 * n_tokens;
     const long long blocks = (total + 255) / 256;
@@ -1171,7 +1227,41 @@ extern "C" int afb_ada_head(const float* infeat_fg, const float* infeat_bg, cons
   AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head: feature vector too large for one block (%zu bytes)", sh);
   AFB_CHECK_CUDA(launch_pdl(ada_head_kernel, dim3(num_vectors, batch), dim3(256), sh, stream, 1, infeat_fg, infeat_bg, time_emb,
                             time_ld, coeff_w, coeff_b, basis, bias, out, reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos,
-                            ctx_sample_stride, basis_sample_stride, channels, td, num_vectors, r, out_dim));
+                            ctx_sample_stride, basis_sample_stride, channels, td, num_vectors, r, out_dim,
+                            static_cast<const float*>(nullptr), 0, static_cast<float*>(nullptr), static_cast<float*>(nullptr),
+                            static_cast<float*>(nullptr)));
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int afb_ada_head_pooled(const float* pool_ws, int n_tokens, float* fg_out, float* bg_out, const float* cached_bg,
+                                   const float* time_emb, int time_ld, const float* coeff_w, const float* coeff_b,
+                                   const float* basis, const float* bias, float* out, afb_bf16* ctx_out, const int* token_pos,
+                                   int64_t ctx_sample_stride, int64_t basis_sample_stride, int batch, int channels, int td,
+                                   int num_vectors, int r, int out_dim, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(pool_ws && time_emb && coeff_w && coeff_b && basis && out, "afb_ada_head_pooled: NULL argument");
+  AFB_REQUIRE(batch > 0 && n_tokens > 0 && channels > 0 && td > 0 && td <= time_ld && num_vectors > 0 && r > 0 && out_dim > 0,
+              "afb_ada_head_pooled: bad sizes");
+  AFB_REQUIRE(channels % 64 == 0 && channels <= 1280, "afb_ada_head_pooled: channels %d must be a multiple of 64, <= 1280", channels);
+  AFB_REQUIRE((2 * channels + td) % 4 == 0 && (reinterpret_cast<uintptr_t>(coeff_w) & 15) == 0,
+              "afb_ada_head_pooled: coefficient map rows must be 16-byte aligned (2C + TD multiple of 4)");
+  AFB_REQUIRE((ctx_out == nullptr) == (token_pos == nullptr), "afb_ada_head_pooled: ctx_out and token_pos go together");
+  // the geometry afb_ada_pool used for the same (batch, n_tokens, channels)
+  const int nblocks0 = pool_blocks_per_sample(batch, n_tokens, channels);
+  const int tokens_per_block = (n_tokens + nblocks0 - 1) / nblocks0;
+  const int grid_x = (n_tokens + tokens_per_block - 1) / tokens_per_block;
+  const float* partials = pool_ws + static_cast<long long>(batch) * kHeads * 2 * n_tokens;
+  float* stats = const_cast<float*>(partials) + static_cast<long long>(batch) * grid_x * pool_partial_floats(channels);
+  const size_t sh = (2 * static_cast<size_t>(channels) + td + static_cast<size_t>((r + 3) & ~3) + out_dim +
+                     static_cast<size_t>(grid_x) * 8) * sizeof(float);
+  AFB_REQUIRE(sh <= 48 * 1024, "afb_ada_head_pooled: feature vector too large for one block (%zu bytes)", sh);
+  AFB_CHECK_CUDA(launch_pdl(ada_head_kernel, dim3(num_vectors, batch), dim3(256), sh, stream, 1, static_cast<const float*>(nullptr),
+                            cached_bg, time_emb, time_ld, coeff_w, coeff_b, basis, bias, out,
+                            reinterpret_cast<__nv_bfloat16*>(ctx_out), token_pos, ctx_sample_stride, basis_sample_stride, channels,
+                            td, num_vectors, r, out_dim, partials, grid_x, fg_out, bg_out, stats));
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

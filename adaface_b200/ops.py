@@ -685,6 +685,58 @@ def _ada_head_impl(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, 
     return out
 
 
+@torch.library.custom_op("adaface_b200::ada_pool_head_splice", mutates_args=("ctx_out",))
+def ada_pool_head_splice(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], cached_bg: Optional[Tensor],
+                         time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor, basis: Tensor, bias: Optional[Tensor],
+                         ctx_out: Tensor, token_pos: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """`ada_pool` + `ada_head_splice` in two launches instead of three: the pooling kernel leaves its chunk partials in the
+    workspace and the head merges them in its prologue (inference path of one cross-attention layer).
+    Returns (out fp32 [B, K, D], fg_out, bg_out fp32 [B, C]); cached_bg replaces the pooled bg stream as the head's input."""
+    _need_cuda(x, q, pool_q, key_mask, cached_bg, time_emb, coeff_w, coeff_b, basis, bias, ctx_out, token_pos)
+    if x.dtype != torch.bfloat16 or q.dtype != torch.bfloat16 or not x.is_contiguous() or not q.is_contiguous():
+        raise ValueError("ada_pool_head_splice: contiguous bf16 x and q expected")
+    b, n, c = x.shape
+    if pool_q.shape != (b, 2, c) or pool_q.dtype != torch.float32:
+        raise ValueError("ada_pool_head_splice: pool_q must be fp32 [B, 2, C] (from ada_pool_prep)")
+    if basis.dim() == 4:
+        if basis.shape[0] != b:
+            raise ValueError("ada_pool_head_splice: per-instance basis must be [B, K, r, D]")
+        k, r, d = basis.shape[1:]
+        basis_stride = k * r * d
+    else:
+        k, r, d = basis.shape
+        basis_stride = 0
+    f = lambda t: None if t is None else t.to(torch.float32).contiguous()
+    cached_bg, time_emb, coeff_w, coeff_b, basis, bias = map(f, (cached_bg, time_emb, coeff_w, coeff_b, basis, bias))
+    if coeff_w.shape != (k * r, 2 * c + td):
+        raise ValueError(f"ada_pool_head_splice: coefficient map {tuple(coeff_w.shape)} does not match ({k * r}, {2 * c + td})")
+    if token_pos.dtype != torch.int32 or token_pos.numel() != k or ctx_out.dtype != torch.bfloat16 or ctx_out.dim() != 3 \
+            or ctx_out.shape[2] != d or ctx_out.stride(2) != 1 or ctx_out.stride(1) != d or ctx_out.shape[0] < b:
+        raise ValueError("ada_pool_head_splice: ctx_out must be bf16 [B, T, D] with contiguous rows, token_pos int32 [K]")
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
+    pool_q = pool_q.contiguous()
+    lib = _lib.load()
+    dev = x.device
+    ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
+    fg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    bg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    out = torch.empty((b, k, d), dtype=torch.float32, device=dev)
+    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), None, None, None, None, _ptr(ws), b, n, c,
+         0.0, 0, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
+    _run("ada_head", lib.afb_ada_head_pooled, _ptr(ws), n, _ptr(fg), _ptr(bg), _ptr(cached_bg), _ptr(time_emb), time_emb.stride(0),
+         _ptr(coeff_w), _ptr(coeff_b), _ptr(basis), _ptr(bias), _ptr(out), _ptr(ctx_out), _ptr(token_pos), ctx_out.stride(0),
+         basis_stride, b, c, td, k, r, d, _stream(), nbytes=4.0 * (coeff_w.numel() + basis.numel()))
+    return out, fg, bg
+
+
+@ada_pool_head_splice.register_fake
+def _(x, q, pool_q, key_mask, cached_bg, time_emb, td, coeff_w, coeff_b, basis, bias, ctx_out, token_pos):
+    b, _, c = x.shape
+    f = lambda s_: x.new_empty(s_, dtype=torch.float32)
+    return f((b, basis.shape[-3], basis.shape[-1])), f((b, c)), f((b, c))
+
+
 @torch.library.custom_op("adaface_b200::ada_head", mutates_args=())
 def ada_head(infeat_fg: Tensor, infeat_bg: Tensor, time_emb: Tensor, td: int, coeff_w: Tensor, coeff_b: Tensor,
              basis: Tensor, bias: Optional[Tensor]) -> Tensor:

@@ -264,6 +264,17 @@ int afb_ada_head(const float* infeat_fg, const float* infeat_bg, const float* ti
                  const float* coeff_w, const float* coeff_b, const float* basis, const float* bias, float* out,
                  afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride, int64_t basis_sample_stride, int batch, int channels, int td,
                  int num_vectors, int r, int out_dim, afb_stream_t stream);
+/* The same head fed straight from the pooling kernel's chunk partials: afb_ada_pool called with fg_out = bg_out = NULL
+ * leaves them in its workspace, and this entry point merges them in its prologue (the separate combine launch disappears
+ * from the critical path of every cross-attention layer).  pool_ws / n_tokens / batch / channels as given to afb_ada_pool;
+ * fg_out, bg_out fp32 [B, C] (optional) receive the pooled features, and the workspace's statistics slot
+ * (afb_ada_pool_stats_offset) the merged softmax (max, sum); cached_bg (optional fp32 [B, C]) replaces the pooled bg
+ * stream as the head's input (embedding_manager.py:789-792).  Other arguments as afb_ada_head. */
+int afb_ada_head_pooled(const float* pool_ws, int n_tokens, float* fg_out, float* bg_out, const float* cached_bg,
+                        const float* time_emb, int time_ld, const float* coeff_w, const float* coeff_b, const float* basis,
+                        const float* bias, float* out, afb_bf16* ctx_out, const int* token_pos, int64_t ctx_sample_stride,
+                        int64_t basis_sample_stride, int batch, int channels, int td, int num_vectors, int r, int out_dim,
+                        afb_stream_t stream);
 
 /* ---- N2: StaticLayerwiseEmbedding and the splice of its rows into the layerwise prompt.
  * afb_static_layerwise_embedding replaces StaticLayerwiseEmbedding.forward (not zero-shot),
