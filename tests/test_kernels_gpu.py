@@ -506,6 +506,45 @@ def test_ada_pool_and_head(ops, cuda_device, ca_idx, n):
     assert float(ctx[:b, :5].abs().max()) == 0 and float(ctx[b].abs().max()) == 0 and float(ctx[:b, 5 + K:].abs().max()) == 0
 
 
+@pytest.mark.parametrize("ca_idx,n,masked", [(0, 256, False), (4, 64, True), (0, 4096, False)])
+def test_ada_head_pooled_matches_separate_launches(ops, cuda_device, ca_idx, n, masked):
+    """afb_ada_head_pooled (the head merges the pooling partials in its prologue; opt-in through AFB_ADA_FUSE=1) against
+    the default chain afb_ada_pool (with its combine launch) + afb_ada_head: same partials, same merge order in fp32, so
+    the pooled features agree to rounding and the K vectors to 1e-5; the cached-bg variant feeds the given bg stream."""
+    seed, b, K, r = 16, 2, 9, 12
+    sd = P.init_ada_embedding(seed, K, r, 2)
+    c = P.CA_INFEAT_DIMS[ca_idx]
+    d = cuda_device
+    x = P.randn(f"adaf.{ca_idx}.x", (b, n, c), seed).to(torch.bfloat16).to(d)
+    q = P.randn(f"adaf.{ca_idx}.q", (b, n, c), seed, 2.0).to(torch.bfloat16).to(d)
+    to_k = P.draw(f"adaf.{ca_idx}.to_k", (c, 768), seed).to(d)
+    time_emb = P.randn("adaf.time_emb", (b, 1280), seed).to(d)
+    probe = P.randn(f"adaf.{ca_idx}.probe", (768,), seed, 0.5).to(d)
+    extra = P.randn(f"adaf.{ca_idx}.extra", (b, 768), seed, 0.5).to(d)
+    g = lambda key: sd[key].to(d)
+    pool_q = ops.ada_pool_prep(to_k, probe, extra, g(f"poolers.{ca_idx}.lora_to_fg_q.weight").squeeze(-1),
+                               g(f"poolers.{ca_idx}.lora_to_bg_q.weight").squeeze(-1),
+                               g(f"poolers.{ca_idx}.lora_to_k.weight").squeeze(-1))
+    mask = None
+    if masked:
+        mask = (torch.arange(n, device=d)[None, :] % 3 != 1).expand(b, n).contiguous()
+    td = int(0.25 * c)
+    cw, cb = g(f"layer_coeff_maps.{ca_idx}.weight"), g(f"layer_coeff_maps.{ca_idx}.bias")
+    basis = torch.cat([sd["pre_vecs"], sd["basis_vecs"]], dim=1).to(d)
+    bias = sd["bias"][ca_idx].to(d)
+    pos = torch.arange(5, 5 + K, dtype=torch.int32, device=d)
+    fg, bg, _, _ = ops.ada_pool(x, q, pool_q, mask, False)
+    for cached in (None, torch.flip(bg, dims=(0,)).contiguous()):
+        ctx_a = torch.zeros((b + 1, 77, 768), dtype=torch.bfloat16, device=d)
+        ctx_b = torch.zeros_like(ctx_a)
+        want = ops.ada_head_splice(fg, bg if cached is None else cached, time_emb, td, cw, cb, basis, bias, ctx_a, pos)
+        out, fg2, bg2 = ops.ada_pool_head_splice(x, q, pool_q, mask, cached, time_emb, td, cw, cb, basis, bias, ctx_b, pos)
+        assert rel_l2(fg2, fg) < 1e-6 and rel_l2(bg2, bg) < 1e-6
+        assert rel_l2(out, want) < 1e-5
+        assert rel_l2(ctx_b.float(), ctx_a.float()) < 1e-3        # bf16 rows: at most a last-bit flip on a few elements
+        assert float(ctx_b[b].abs().max()) == 0 and float(ctx_b[:b, :5].abs().max()) == 0
+
+
 def test_ada_pool_prep_batched_equals_per_layer(ops, cuda_device):
     """afb_ada_pool_prep_batched (every layer / subject of a U-Net call in two launches) against the per-layer entry
     point: same arithmetic, so identical results; a second run() recomputes in place."""
