@@ -709,37 +709,6 @@ int launch_attn_bwd(const afb_attn_args& a, const __nv_bfloat16* dout, __nv_bflo
 }  // namespace
 }  // namespace afb
 
-extern "C" int afb_attention_bwd_short(const afb_attn_args* args, const afb_bf16* dout, afb_bf16* dq, float* dk, float* dv,
-                                       int64_t lddq, int64_t lddk, afb_stream_t stream_) {
-  using namespace afb;
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  AFB_REQUIRE(args != nullptr && dout && dk && dv, "afb_attention_bwd_short: NULL argument");
-  const afb_attn_args& a = *args;
-  AFB_REQUIRE(a.q && a.k && a.v, "afb_attention_bwd_short: NULL operand");
-  AFB_REQUIRE(a.key_mask == nullptr, "afb_attention_bwd_short: key masks are a self-attention feature (not built for the backward)");
-  AFB_REQUIRE(a.batch > 0 && a.heads > 0 && a.q_len > 0 && a.kv_len > 0 && a.batch <= 65535 && a.heads <= 65535,
-              "afb_attention_bwd_short: bad sizes");
-  const int max_keys = a.head_dim >= 160 ? 80 : kAbMaxKeys;
-  AFB_REQUIRE(a.kv_len <= max_keys, "afb_attention_bwd_short: kv_len %d > %d: only the short-key (cross-attention) backward is "
-              "built; the self-attention backward is not", a.kv_len, max_keys);
-  const int width = a.heads * a.head_dim;
-  AFB_REQUIRE(a.ldq >= width && a.ldk >= width && a.ldv >= width && a.ldo >= width && lddk >= width && (dq == nullptr || lddq >= width),
-              "afb_attention_bwd_short: leading dimension smaller than heads*head_dim");
-  const __nv_bfloat16* db = reinterpret_cast<const __nv_bfloat16*>(dout);
-  __nv_bfloat16* dqb = reinterpret_cast<__nv_bfloat16*>(dq);
-  int rc;
-  switch (a.head_dim) {
-    case 40: rc = launch_attn_bwd<40>(a, db, dqb, dk, dv, lddq, lddk, stream); break;
-    case 80: rc = launch_attn_bwd<80>(a, db, dqb, dk, dv, lddq, lddk, stream); break;
-    case 160: rc = launch_attn_bwd<160>(a, db, dqb, dk, dv, lddq, lddk, stream); break;
-    default: AFB_FAIL(2, "afb_attention_bwd_short: head_dim %d not supported (SD-1.5 uses 40, 80, 160)", a.head_dim);
-  }
-  if (rc) return rc;
-  count_launch();
-  AFB_CHECK_CUDA(cudaGetLastError());
-  return 0;
-}
-
 extern "C" int afb_ada_head_bwd(const float* infeat_fg, const float* infeat_bg, const float* time_emb, int time_ld,
                                 const float* coeff_w, const float* coeff_b, const float* basis, const float* grad_out,
                                 float* d_coeff_w, float* d_coeff_b, float* d_basis, float* d_bias, float* d_feat_ws,
@@ -1222,14 +1191,569 @@ int launch_attn_bwd_mma(const afb_attn_args& a, const __nv_bfloat16* dout, const
   return 0;
 }
 
-// AFB_ATTN_BWD=simt keeps the CUDA-core version (A/B measurement and cross-check); read once
-bool attn_bwd_mma_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("AFB_ATTN_BWD");
-    return e == nullptr || e[0] != 's';
-  }();
-  return on;
+// ---- second tensor-core version (the default): 128-key tiles, 8 warps, every fragment through ldmatrix ----------------
+// The first version spends its issue slots on shared-memory loads (a 32-bit load per A / B register, two 16-bit loads per
+// transposed one: ~490 loads for 120 MMAs per warp and tile) and sends 24 scalar fp32 atomics per thread and tile to dQ.
+// Here: K / V of 128 keys stay resident, the 64-row Q / dO tiles (+ lse, delta) arrive through a cp.async double buffer
+// while the previous tile computes, all operand fragments come from ldmatrix / ldmatrix.trans (78 loads per warp and
+// tile), P = 2^(s - lse) on ex2.approx, and dQ leaves as red.global.add.v2.f32 - 8x fewer atomic instructions per key.
+// Warp w = (rw = w & 3, kh = w >> 2): S / dP for rows 16 rw.. x keys 64 kh.. (two 32-key halves to bound the registers),
+// dQ for rows 16 rw.. x column half kh over all 128 keys, dK / dV for keys 16 w.. over the 64 rows.
+constexpr int kA2Keys = 128;
+constexpr int kA2Rows = 64;
+constexpr int kA2Threads = 256;
+constexpr int kA2PS = kA2Keys + 8;     // row pitch of the P / dS tiles (bf16): 272 B, conflict-free ldmatrix rows
+
+template <int D, int kSplit>
+struct A2Cfg {
+  static constexpr int DPAD = (D + 15) / 16 * 16;
+  static constexpr int LD = DPAD + 8;              // operand row pitch (bf16): 16-byte aligned rows, conflict-free ldmatrix
+  static constexpr int CW = DPAD / kSplit;         // output columns of this block
+  static constexpr int NT = CW / 8;                // dK / dV accumulator tiles of a warp
+  static constexpr int NTQ = CW / 16;              // dQ accumulator tiles of a warp (half of the block's columns)
+  static constexpr int kStages = DPAD <= 80 ? 2 : 1;
+  static constexpr int kMinBlocks = DPAD <= 48 ? 2 : 1;
+  static constexpr size_t kSmem = (static_cast<size_t>(2 * kA2Keys + kStages * 2 * kA2Rows) * LD + 2 * kA2Rows * kA2PS) * 2 +
+                                  static_cast<size_t>(kStages) * 2 * kA2Rows * sizeof(float);
+  static_assert(CW % 16 == 0 && NT % 2 == 0, "column slice");
+  static_assert(kSmem <= 227 * 1024, "shared memory budget");
+};
+
+__device__ __forceinline__ void bw_ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
+__device__ __forceinline__ void bw_ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void bw_ldsm_x2_t(uint32_t& r0, uint32_t& r1, uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(addr));
+}
+__device__ __forceinline__ void bw_cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int n = valid ? 16 : 0;                            // src-size 0: the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void bw_cp_async4(uint32_t dst, const void* src, bool valid) {
+  const int n = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void bw_red_add_v2(float* dst, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst), "f"(a), "f"(b) : "memory");
+}
+
+template <int D, int kSplit>
+__global__ void __launch_bounds__(kA2Threads, A2Cfg<D, kSplit>::kMinBlocks) attn_bwd_mma2_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
+    const __nv_bfloat16* __restrict__ dout, const float* __restrict__ lse, const float* __restrict__ delta,
+    float* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv, int q_len, int kv_len, int heads, long long ldq,
+    long long ldk, long long ldv, long long ldo, long long ldg, float scale, const uint8_t* __restrict__ key_mask) {
+  using C = A2Cfg<D, kSplit>;
+  constexpr int DPAD = C::DPAD, LD = C::LD, CW = C::CW, NT = C::NT, NTQ = C::NTQ, NS = C::kStages;
+  constexpr int PS = kA2PS;
+  __shared__ uint8_t s_keep[kA2Keys];            // key mask of this block's keys (1 = attended)
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);      // [128][LD]
+  __nv_bfloat16* sV = sK + kA2Keys * LD;
+  __nv_bfloat16* sQ = sV + kA2Keys * LD;                               // [NS][64][LD]
+  __nv_bfloat16* sO = sQ + NS * kA2Rows * LD;                          // [NS][64][LD]  dO tiles
+  __nv_bfloat16* sP = sO + NS * kA2Rows * LD;                          // [64][PS]
+  __nv_bfloat16* sS = sP + kA2Rows * PS;                               // [64][PS]      dS
+  float* sL = reinterpret_cast<float*>(sS + kA2Rows * PS);             // [NS][lse 64 | delta 64]
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int k0 = (blockIdx.x / kSplit) * kA2Keys;
+  const int cs = (blockIdx.x % kSplit) * CW;     // first output column of this block
+  const int col0 = head * D;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int rw = warp & 3, kh = warp >> 2;
+  const float scale_log2 = scale * 1.4426950408889634f;
+  const bool has_mask = key_mask != nullptr;
+  // ldmatrix lane offsets.  A operand, rows x k (plain): matrices (rows 0-7, k 0-7), (rows 8-15, k 0-7), (rows 0-7, k 8-15), ..
+  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8, la_col = (lane >> 4) * 8;
+  // B operand from a [n][k] tile (plain): (n 0-7, k 0-7), (n 0-7, k 8-15), (n 8-15, k 0-7), (n 8-15, k 8-15)
+  const int lb_row = (lane & 7) + (lane >> 4) * 8, lb_col = ((lane >> 3) & 1) * 8;
+  // transposed loads read a [k][m or n] tile: same lane pattern as the A operand with rows = k
+  //   B: (k 0-7, n 0-7), (k 8-15, n 0-7), (k 0-7, n 8-15), (k 8-15, n 8-15)        -> la_row / la_col
+  //   A: (k 0-7, m 0-7), (k 0-7, m 8-15), (k 8-15, m 0-7), (k 8-15, m 8-15)        -> lb_row / lb_col
+  auto issue_tile = [&](int it, int stage) {
+    const int r0 = it * kA2Rows;
+    const uint32_t uq = smem_u32(sQ + stage * kA2Rows * LD), uo = smem_u32(sO + stage * kA2Rows * LD);
+    for (int idx = tid; idx < kA2Rows * (DPAD / 8); idx += kA2Threads) {
+      const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+      const bool ok = r0 + r < q_len && c8 < D;
+      const long long row = static_cast<long long>(b) * q_len + (ok ? r0 + r : 0);
+      const int cc = ok ? c8 : 0;
+      bw_cp_async16(uq + (r * LD + c8) * 2, q + row * ldq + col0 + cc, ok);
+      bw_cp_async16(uo + (r * LD + c8) * 2, dout + row * ldo + col0 + cc, ok);
+    }
+    if (tid < 2 * kA2Rows) {
+      const int r = tid & (kA2Rows - 1);
+      const bool ok = r0 + r < q_len;
+      const long long li = (static_cast<long long>(b) * heads + head) * q_len + (ok ? r0 + r : 0);
+      bw_cp_async4(smem_u32(sL + stage * 2 * kA2Rows + tid), (tid < kA2Rows ? lse : delta) + li, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (NS == 2) issue_tile(0, 0);
+  // K, V tiles (rows past kv_len and the padding columns are zero)
+  for (int idx = tid; idx < kA2Keys * (DPAD / 8); idx += kA2Threads) {
+    const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+    uint4 kk4 = make_uint4(0, 0, 0, 0), vv4 = kk4;
+    if (k0 + r < kv_len && c8 < D) {
+      kk4 = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * kv_len + k0 + r) * ldk + col0 + c8);
+      vv4 = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * kv_len + k0 + r) * ldv + col0 + c8);
+    }
+    *reinterpret_cast<uint4*>(sK + r * LD + c8) = kk4;
+    *reinterpret_cast<uint4*>(sV + r * LD + c8) = vv4;
+  }
+  if (tid < kA2Keys)
+    s_keep[tid] = (!has_mask || k0 + tid >= kv_len) ? 1 : key_mask[static_cast<long long>(b) * kv_len + k0 + tid];
+  float acc_k[NT][4], acc_v[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; ++n)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc_k[n][e] = acc_v[n][e] = 0.f;
+  const uint32_t uK = smem_u32(sK), uV = smem_u32(sV), uP = smem_u32(sP), uS = smem_u32(sS);
+  const bool keys_full = k0 + kA2Keys <= kv_len && !has_mask;
+
+  const int n_tiles = (q_len + kA2Rows - 1) / kA2Rows;
+  for (int it = 0; it < n_tiles; ++it) {
+    const int st = NS == 2 ? (it & 1) : 0;
+    const int r0 = it * kA2Rows;
+    if (NS == 1) {
+      __syncthreads();                            // the single stage is consumed
+      issue_tile(it, 0);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                              // tile `it` (and, first time, K / V) visible; tile it-1 fully consumed
+    if (NS == 2 && it + 1 < n_tiles) issue_tile(it + 1, st ^ 1);
+    const uint32_t uQ = smem_u32(sQ + st * kA2Rows * LD), uO = smem_u32(sO + st * kA2Rows * LD);
+    const float* tl = sL + st * 2 * kA2Rows;
+    const bool full = keys_full && r0 + kA2Rows <= q_len;
+    // ---- S = Q K^T and dP = dO V^T: rows 16 rw .., keys 64 kh .. in two halves of 32
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int key_base = 64 * kh + 32 * hh;
+      float s_acc[4][4], p_acc[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) s_acc[j][e] = p_acc[j][e] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < DPAD / 16; ++kk) {
+        uint32_t aq[4], ao[4];
+        const uint32_t a_off = ((16 * rw + la_row) * LD + kk * 16 + la_col) * 2;
+        bw_ldsm_x4(aq, uQ + a_off);
+        bw_ldsm_x4(ao, uO + a_off);
+#pragma unroll
+        for (int jp = 0; jp < 2; ++jp) {
+          uint32_t bk[4], bv[4];
+          const uint32_t b_off = ((key_base + jp * 16 + lb_row) * LD + kk * 16 + lb_col) * 2;
+          bw_ldsm_x4(bk, uK + b_off);
+          bw_ldsm_x4(bv, uV + b_off);
+          mma_bf16_16816(s_acc[2 * jp], aq, bk[0], bk[1]);
+          mma_bf16_16816(s_acc[2 * jp + 1], aq, bk[2], bk[3]);
+          mma_bf16_16816(p_acc[2 * jp], ao, bv[0], bv[1]);
+          mma_bf16_16816(p_acc[2 * jp + 1], ao, bv[2], bv[3]);
+        }
+      }
+      // P and dS of rows g and g + 8 of this warp's 16, keys key_base + 8 j + 2 t, + 1
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = 16 * rw + g + 8 * half;
+        const bool row_ok = r0 + r < q_len;
+        const float l2 = tl[r], dl = tl[kA2Rows + r];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c = key_base + 8 * j + 2 * t;
+          float pr[2], ds[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const bool ok = full || (row_ok && k0 + c + e < kv_len);
+            pr[e] = ok ? ex2_approx(fmaf(s_acc[j][2 * half + e], scale_log2, -l2)) : 0.f;
+            ds[e] = pr[e] * (p_acc[j][2 * half + e] - dl) * scale;
+            if (has_mask && s_keep[c + e] == 0) {
+              // masked key (attention.py:223-232, masked_fill after the scaling): its score is a constant, so no gradient
+              // reaches q / k through it; its probability is 0 unless the whole row is masked (the forward's lse is then
+              // the fill value itself and the row averages V uniformly)
+              pr[e] = (ok && l2 < -1.0e29f) ? 1.0f / static_cast<float>(kv_len) : 0.f;
+              ds[e] = 0.f;
+            }
+          }
+          *reinterpret_cast<uint32_t*>(sP + r * PS + c) = pack_bf16x2(pr[0], pr[1]);
+          *reinterpret_cast<uint32_t*>(sS + r * PS + c) = pack_bf16x2(ds[0], ds[1]);
+        }
+      }
+    }
+    __syncthreads();                              // every warp's P and dS are in shared memory
+    // ---- dQ[16 rows][CW / 2] = dS[16 x 128] K[128 x CW / 2]
+    {
+      float d_acc[NTQ][4];
+#pragma unroll
+      for (int n = 0; n < NTQ; ++n)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) d_acc[n][e] = 0.f;
+      const int cq = cs + kh * (CW / 2);
+#pragma unroll
+      for (int kk = 0; kk < kA2Keys / 16; ++kk) {
+        uint32_t a[4];
+        bw_ldsm_x4(a, uS + ((16 * rw + la_row) * PS + kk * 16 + la_col) * 2);
+#pragma unroll
+        for (int n = 0; n < NTQ; n += 2) {
+          if (n + 1 < NTQ) {
+            uint32_t bb[4];
+            bw_ldsm_x4_t(bb, uK + ((kk * 16 + la_row) * LD + cq + 8 * n + la_col) * 2);
+            mma_bf16_16816(d_acc[n], a, bb[0], bb[1]);
+            mma_bf16_16816(d_acc[n + 1 < NTQ ? n + 1 : n], a, bb[2], bb[3]);
+          } else {
+            uint32_t b0, b1;
+            bw_ldsm_x2_t(b0, b1, uK + ((kk * 16 + la_row) * LD + cq + 8 * n) * 2);
+            mma_bf16_16816(d_acc[n], a, b0, b1);
+          }
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = r0 + 16 * rw + g + 8 * half;
+        if (r < q_len) {
+          float* dst = dq + (static_cast<long long>(b) * q_len + r) * ldg + col0;
+#pragma unroll
+          for (int n = 0; n < NTQ; ++n) {
+            const int c = cq + 8 * n + 2 * t;          // even; D is a multiple of 8, so c < D covers c + 1
+            if (c < D) bw_red_add_v2(dst + c, d_acc[n][2 * half], d_acc[n][2 * half + 1]);
+          }
+        }
+      }
+    }
+    // ---- dV[16 keys][CW] += P^T dO,  dK[16 keys][CW] += dS^T Q  (keys 16 w .. of the tile; A = the tiles read transposed)
+#pragma unroll
+    for (int kk = 0; kk < kA2Rows / 16; ++kk) {
+      uint32_t ap[4], as[4];
+      const uint32_t a_off = ((kk * 16 + lb_row) * PS + 16 * warp + lb_col) * 2;
+      bw_ldsm_x4_t(ap, uP + a_off);
+      bw_ldsm_x4_t(as, uS + a_off);
+#pragma unroll
+      for (int n = 0; n < NT; n += 2) {
+        uint32_t bo[4], bq[4];
+        const uint32_t b_off = ((kk * 16 + la_row) * LD + cs + 8 * n + la_col) * 2;
+        bw_ldsm_x4_t(bo, uO + b_off);
+        bw_ldsm_x4_t(bq, uQ + b_off);
+        mma_bf16_16816(acc_v[n], ap, bo[0], bo[1]);
+        mma_bf16_16816(acc_v[n + 1], ap, bo[2], bo[3]);
+        mma_bf16_16816(acc_k[n], as, bq[0], bq[1]);
+        mma_bf16_16816(acc_k[n + 1], as, bq[2], bq[3]);
+      }
+    }
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int key = k0 + 16 * warp + g + 8 * half;
+    if (key < kv_len) {
+      const long long o = (static_cast<long long>(b) * kv_len + key) * ldg + col0;
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        const int c = cs + 8 * n + 2 * t;
+        if (c < D) {
+          *reinterpret_cast<float2*>(dk + o + c) = make_float2(acc_k[n][2 * half], acc_k[n][2 * half + 1]);
+          *reinterpret_cast<float2*>(dv + o + c) = make_float2(acc_v[n][2 * half], acc_v[n][2 * half + 1]);
+        }
+      }
+    }
+  }
+}
+
+template <int D, int kSplit>
+int launch_attn_bwd_mma2(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
+                         long long ldg, cudaStream_t stream) {
+  using C = A2Cfg<D, kSplit>;
+  auto kern = attn_bwd_mma2_kernel<D, kSplit>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(C::kSmem)));
+    attr_set = true;
+  }
+  dim3 grid(((a.kv_len + kA2Keys - 1) / kA2Keys) * kSplit, a.heads, a.batch);
+  kern<<<grid, kA2Threads, C::kSmem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
+                                               reinterpret_cast<const __nv_bfloat16*>(a.v), dout, a.lse, delta, dq, dk, dv, a.q_len,
+                                               a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale, a.key_mask);
+  return 0;
+}
+
+// ---- the short-key backward (cross-attention, 77 keys) on tensor cores -------------------------------------------------
+// All keys of a head fit one tile (80 = 10 n8 tiles), so the softmax of a row is complete inside the warp that owns it:
+// block (row chunk, head, sample) = 5 warps walks 80-row query tiles; warp w computes S = Q K^T and dP = dO V^T of rows
+// 16 w .. (accumulators in registers), the row softmax / delta / dS with quad shuffles, dQ = dS K with dS as the A operand
+// straight from those registers (bf16 rows written once, no atomics), leaves P and dS in shared memory and then owns keys
+// 16 w .. for dV += P^T dO and dK += dS^T Q over the tile's 80 rows (ldmatrix.trans operands; accumulators in registers
+// over all tiles of the block, added to global memory once at the end as vector atomics: dk / dv zero on entry).
+// The first version (attn_bwd_short_kernel: fp32 CUDA cores, scalar bf16 loads) took 1.62 ms for one 64x64 layer at
+// batch 8 - 14 ms of the 78 ms inversion step for 8 GFLOP per layer.
+constexpr int kAsKeys = 80;
+constexpr int kAsRows = 80;
+constexpr int kAsThreads = 160;
+constexpr int kAsPS = kAsKeys + 8;     // row pitch of the P / dS tiles (bf16): 176 B, conflict-free ldmatrix rows
+
+template <int D, int kSplit>
+struct AsCfg {
+  static constexpr int DPAD = (D + 15) / 16 * 16;
+  static constexpr int LD = DPAD + 8;
+  static constexpr int CW = DPAD / kSplit;         // output columns of this block (dQ, dK, dV)
+  static constexpr int NT = CW / 8;
+  static constexpr int kStages = DPAD <= 80 ? 2 : 1;
+  static constexpr size_t kSmem = (static_cast<size_t>(2 * kAsKeys + kStages * 2 * kAsRows) * LD + 2 * kAsRows * kAsPS) * 2;
+  static_assert(NT % 2 == 0, "column slice");
+  static_assert(kSmem <= 227 * 1024, "shared memory budget");
+};
+
+template <int D, int kSplit>
+__global__ void __launch_bounds__(kAsThreads) attn_bwd_short_mma_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
+    const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv,
+    int q_len, int kv_len, long long ldq, long long ldk, long long ldv, long long ldo, long long lddq, long long lddk,
+    float scale, int tiles_per_block) {
+  using C = AsCfg<D, kSplit>;
+  constexpr int DPAD = C::DPAD, LD = C::LD, CW = C::CW, NT = C::NT, NS = C::kStages, PS = kAsPS;
+  constexpr int NJ = kAsKeys / 8;                // key tiles of the score accumulators
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);      // [80][LD]
+  __nv_bfloat16* sV = sK + kAsKeys * LD;
+  __nv_bfloat16* sQ = sV + kAsKeys * LD;                               // [NS][80][LD]
+  __nv_bfloat16* sO = sQ + NS * kAsRows * LD;                          // [NS][80][LD]  dO tiles
+  __nv_bfloat16* sP = sO + NS * kAsRows * LD;                          // [80][PS]
+  __nv_bfloat16* sS = sP + kAsRows * PS;                               // [80][PS]      dS
+  const int head = blockIdx.y, b = blockIdx.z, T = kv_len;
+  const int cs = (blockIdx.x % kSplit) * CW;
+  const int col0 = head * D;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int n_tiles = (q_len + kAsRows - 1) / kAsRows;
+  const int tile0 = (blockIdx.x / kSplit) * tiles_per_block;
+  const int tile_end = tile0 + tiles_per_block < n_tiles ? tile0 + tiles_per_block : n_tiles;
+  if (tile0 >= tile_end) return;
+  const float scale_log2 = scale * 1.4426950408889634f;
+  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8, la_col = (lane >> 4) * 8;     // see attn_bwd_mma2_kernel
+  const int lb_row = (lane & 7) + (lane >> 4) * 8, lb_col = ((lane >> 3) & 1) * 8;
+  auto issue_tile = [&](int it, int stage) {
+    const int r0 = it * kAsRows;
+    const uint32_t uq = smem_u32(sQ + stage * kAsRows * LD), uo = smem_u32(sO + stage * kAsRows * LD);
+    for (int idx = tid; idx < kAsRows * (DPAD / 8); idx += kAsThreads) {
+      const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+      const bool ok = r0 + r < q_len && c8 < D;
+      const long long row = static_cast<long long>(b) * q_len + (ok ? r0 + r : 0);
+      const int cc = ok ? c8 : 0;
+      bw_cp_async16(uq + (r * LD + c8) * 2, q + row * ldq + col0 + cc, ok);
+      bw_cp_async16(uo + (r * LD + c8) * 2, dout + row * ldo + col0 + cc, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (NS == 2) issue_tile(tile0, 0);
+  for (int idx = tid; idx < kAsKeys * (DPAD / 8); idx += kAsThreads) {
+    const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+    uint4 kk4 = make_uint4(0, 0, 0, 0), vv4 = kk4;
+    if (r < T && c8 < D) {
+      kk4 = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * T + r) * ldk + col0 + c8);
+      vv4 = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * T + r) * ldv + col0 + c8);
+    }
+    *reinterpret_cast<uint4*>(sK + r * LD + c8) = kk4;
+    *reinterpret_cast<uint4*>(sV + r * LD + c8) = vv4;
+  }
+  float acc_k[NT][4], acc_v[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; ++n)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc_k[n][e] = acc_v[n][e] = 0.f;
+  const uint32_t uK = smem_u32(sK), uV = smem_u32(sV), uP = smem_u32(sP), uS = smem_u32(sS);
+
+  for (int it = tile0; it < tile_end; ++it) {
+    const int st = NS == 2 ? ((it - tile0) & 1) : 0;
+    const int r0 = it * kAsRows;
+    if (NS == 1) {
+      __syncthreads();
+      issue_tile(it, 0);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                              // tile `it` (first time: K / V) visible; the previous tile is consumed
+    if (NS == 2 && it + 1 < tile_end) issue_tile(it + 1, st ^ 1);
+    const uint32_t uQ = smem_u32(sQ + st * kAsRows * LD), uO = smem_u32(sO + st * kAsRows * LD);
+    // ---- S = Q K^T, dP = dO V^T: rows 16 w .. x all keys
+    float s_acc[NJ][4], p_acc[NJ][4];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s_acc[j][e] = p_acc[j][e] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < DPAD / 16; ++kk) {
+      uint32_t aq[4], ao[4];
+      const uint32_t a_off = ((16 * warp + la_row) * LD + kk * 16 + la_col) * 2;
+      bw_ldsm_x4(aq, uQ + a_off);
+      bw_ldsm_x4(ao, uO + a_off);
+#pragma unroll
+      for (int jp = 0; jp < NJ / 2; ++jp) {
+        uint32_t bk[4], bv[4];
+        const uint32_t b_off = ((jp * 16 + lb_row) * LD + kk * 16 + lb_col) * 2;
+        bw_ldsm_x4(bk, uK + b_off);
+        bw_ldsm_x4(bv, uV + b_off);
+        mma_bf16_16816(s_acc[2 * jp], aq, bk[0], bk[1]);
+        mma_bf16_16816(s_acc[2 * jp + 1], aq, bk[2], bk[3]);
+        mma_bf16_16816(p_acc[2 * jp], ao, bv[0], bv[1]);
+        mma_bf16_16816(p_acc[2 * jp + 1], ao, bv[2], bv[3]);
+      }
+    }
+    // ---- softmax, delta = sum_t P dP, dS = P (dP - delta) scale for rows g and g + 8 (a row lives in one quad)
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const bool live = r0 + 16 * warp + g + 8 * half < q_len;
+      float mx = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+          if (8 * j + 2 * t + e < T) mx = fmaxf(mx, s_acc[j][2 * half + e]);
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float off = mx * scale_log2;
+      float l = 0.f;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float pr = (8 * j + 2 * t + e < T) ? ex2_approx(fmaf(s_acc[j][2 * half + e], scale_log2, -off)) : 0.f;
+          s_acc[j][2 * half + e] = pr;
+          l += pr;
+        }
+      l += __shfl_xor_sync(0xffffffffu, l, 1);
+      l += __shfl_xor_sync(0xffffffffu, l, 2);
+      const float inv = live ? 1.0f / l : 0.f;       // rows past q_len contribute nothing
+      float dl = 0.f;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float pr = s_acc[j][2 * half + e] * inv;
+          s_acc[j][2 * half + e] = pr;
+          dl = fmaf(pr, p_acc[j][2 * half + e], dl);
+        }
+      dl += __shfl_xor_sync(0xffffffffu, dl, 1);
+      dl += __shfl_xor_sync(0xffffffffu, dl, 2);
+#pragma unroll
+      for (int j = 0; j < NJ; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) p_acc[j][2 * half + e] = s_acc[j][2 * half + e] * (p_acc[j][2 * half + e] - dl) * scale;
+    }
+    uint32_t ds_pk[NJ][2];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = 16 * warp + g + 8 * half, c = 8 * j + 2 * t;
+        ds_pk[j][half] = pack_bf16x2(p_acc[j][2 * half], p_acc[j][2 * half + 1]);
+        *reinterpret_cast<uint32_t*>(sP + r * PS + c) = pack_bf16x2(s_acc[j][2 * half], s_acc[j][2 * half + 1]);
+        *reinterpret_cast<uint32_t*>(sS + r * PS + c) = ds_pk[j][half];
+      }
+    // ---- dQ[16 rows][CW] = dS[16 x 80] K[80 x CW]: A from the registers above
+    if (dq != nullptr) {
+      float d_acc[NT][4];
+#pragma unroll
+      for (int n = 0; n < NT; ++n)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) d_acc[n][e] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < NJ / 2; ++kk) {
+        const uint32_t a[4] = {ds_pk[2 * kk][0], ds_pk[2 * kk][1], ds_pk[2 * kk + 1][0], ds_pk[2 * kk + 1][1]};
+#pragma unroll
+        for (int n = 0; n < NT; n += 2) {
+          uint32_t bb[4];
+          bw_ldsm_x4_t(bb, uK + ((kk * 16 + la_row) * LD + cs + 8 * n + la_col) * 2);
+          mma_bf16_16816(d_acc[n], a, bb[0], bb[1]);
+          mma_bf16_16816(d_acc[n + 1], a, bb[2], bb[3]);
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = r0 + 16 * warp + g + 8 * half;
+        if (r < q_len) {
+          __nv_bfloat16* dst = dq + (static_cast<long long>(b) * q_len + r) * lddq + col0;
+#pragma unroll
+          for (int n = 0; n < NT; ++n) {
+            const int c = cs + 8 * n + 2 * t;
+            if (c < D) *reinterpret_cast<uint32_t*>(dst + c) = pack_bf16x2(d_acc[n][2 * half], d_acc[n][2 * half + 1]);
+          }
+        }
+      }
+    }
+    __syncthreads();                              // every warp's P and dS rows are in shared memory
+    // ---- dV[16 keys][CW] += P^T dO,  dK[16 keys][CW] += dS^T Q  (keys 16 w ..; A = the tiles read transposed)
+#pragma unroll
+    for (int kk = 0; kk < kAsRows / 16; ++kk) {
+      uint32_t ap[4], as[4];
+      const uint32_t a_off = ((kk * 16 + lb_row) * PS + 16 * warp + lb_col) * 2;
+      bw_ldsm_x4_t(ap, uP + a_off);
+      bw_ldsm_x4_t(as, uS + a_off);
+#pragma unroll
+      for (int n = 0; n < NT; n += 2) {
+        uint32_t bo[4], bq[4];
+        const uint32_t b_off = ((kk * 16 + la_row) * LD + cs + 8 * n + la_col) * 2;
+        bw_ldsm_x4_t(bo, uO + b_off);
+        bw_ldsm_x4_t(bq, uQ + b_off);
+        mma_bf16_16816(acc_v[n], ap, bo[0], bo[1]);
+        mma_bf16_16816(acc_v[n + 1], ap, bo[2], bo[3]);
+        mma_bf16_16816(acc_k[n], as, bq[0], bq[1]);
+        mma_bf16_16816(acc_k[n + 1], as, bq[2], bq[3]);
+      }
+    }
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int key = 16 * warp + g + 8 * half;
+    if (key < T) {
+      const long long o = (static_cast<long long>(b) * T + key) * lddk + col0;
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        const int c = cs + 8 * n + 2 * t;
+        if (c < D) {
+          bw_red_add_v2(dk + o + c, acc_k[n][2 * half], acc_k[n][2 * half + 1]);
+          bw_red_add_v2(dv + o + c, acc_v[n][2 * half], acc_v[n][2 * half + 1]);
+        }
+      }
+    }
+  }
+}
+
+template <int D, int kSplit>
+int launch_attn_bwd_short_mma(const afb_attn_args& a, const __nv_bfloat16* dout, __nv_bfloat16* dq, float* dk, float* dv,
+                              long long lddq, long long lddk, cudaStream_t stream) {
+  using C = AsCfg<D, kSplit>;
+  auto kern = attn_bwd_short_mma_kernel<D, kSplit>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(C::kSmem)));
+    attr_set = true;
+  }
+  const int tiles = (a.q_len + kAsRows - 1) / kAsRows;
+  // about two resident sets of blocks; every block keeps its dK / dV partial in registers over its tiles
+  const int per_sm = C::kSmem + 1024 <= 113 * 1024 ? 2 : 1;
+  int chunks = (2 * per_sm * num_sms() + a.batch * a.heads * kSplit - 1) / (a.batch * a.heads * kSplit);
+  if (chunks > tiles) chunks = tiles;
+  if (chunks < 1) chunks = 1;
+  const int tiles_per_block = (tiles + chunks - 1) / chunks;
+  dim3 grid(((tiles + tiles_per_block - 1) / tiles_per_block) * kSplit, a.heads, a.batch);
+  kern<<<grid, kAsThreads, C::kSmem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
+                                               reinterpret_cast<const __nv_bfloat16*>(a.v), dout, dq, dk, dv, a.q_len, a.kv_len, a.ldq,
+                                               a.ldk, a.ldv, a.ldo, lddq, lddk, a.scale, tiles_per_block);
+  return 0;
+}
+
+// AFB_ATTN_BWD: unset = the 128-key ldmatrix version; "mma1" = the first tensor-core version, "simt" = the CUDA-core
+// version (A/B measurement and cross-check); read once
+int attn_bwd_mode() {      // 2 = mma2, 1 = mma1, 0 = simt
+  static const int mode = [] {
+    const char* e = getenv("AFB_ATTN_BWD");
+    if (e == nullptr) return 2;
+    if (e[0] == 's') return 0;
+    return (e[0] == 'm' && e[1] == 'm' && e[2] == 'a' && e[3] == '1') ? 1 : 2;
+  }();
+  return mode;
+}
+
 
 template <int D>
 int launch_attn_bwd_long(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
@@ -1250,6 +1774,51 @@ int launch_attn_bwd_long(const afb_attn_args& a, const __nv_bfloat16* dout, cons
 
 }  // namespace
 }  // namespace afb
+
+extern "C" int afb_attention_bwd_short(const afb_attn_args* args, const afb_bf16* dout, afb_bf16* dq, float* dk, float* dv,
+                                       int64_t lddq, int64_t lddk, afb_stream_t stream_) {
+  using namespace afb;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  AFB_REQUIRE(args != nullptr && dout && dk && dv, "afb_attention_bwd_short: NULL argument");
+  const afb_attn_args& a = *args;
+  AFB_REQUIRE(a.q && a.k && a.v, "afb_attention_bwd_short: NULL operand");
+  AFB_REQUIRE(a.key_mask == nullptr, "afb_attention_bwd_short: key masks are a self-attention feature (not built for the backward)");
+  AFB_REQUIRE(a.batch > 0 && a.heads > 0 && a.q_len > 0 && a.kv_len > 0 && a.batch <= 65535 && a.heads <= 65535,
+              "afb_attention_bwd_short: bad sizes");
+  const int max_keys = a.head_dim >= 160 ? 80 : kAbMaxKeys;
+  AFB_REQUIRE(a.kv_len <= max_keys, "afb_attention_bwd_short: kv_len %d > %d: only the short-key (cross-attention) backward is "
+              "built; the self-attention backward is not", a.kv_len, max_keys);
+  const int width = a.heads * a.head_dim;
+  AFB_REQUIRE(a.ldq >= width && a.ldk >= width && a.ldv >= width && a.ldo >= width && lddk >= width && (dq == nullptr || lddq >= width),
+              "afb_attention_bwd_short: leading dimension smaller than heads*head_dim");
+  const __nv_bfloat16* db = reinterpret_cast<const __nv_bfloat16*>(dout);
+  __nv_bfloat16* dqb = reinterpret_cast<__nv_bfloat16*>(dq);
+  int rc;
+  // the tensor-core version: up to 80 keys, 16-byte vector loads, bf16x2 dQ stores, 8-byte vector atomics for dK / dV
+  // (AFB_ATTN_BWD=simt or mma1 keeps the CUDA-core version for the A/B measurement)
+  const bool mma = attn_bwd_mode() == 2 && a.kv_len <= kAsKeys && a.head_dim % 8 == 0 &&
+                   ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |
+                     reinterpret_cast<uintptr_t>(dout)) & 15) == 0 &&
+                   a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0 && a.ldo % 8 == 0 && lddk % 2 == 0 &&
+                   ((reinterpret_cast<uintptr_t>(dk) | reinterpret_cast<uintptr_t>(dv)) & 7) == 0 &&
+                   (dq == nullptr || (lddq % 2 == 0 && (reinterpret_cast<uintptr_t>(dq) & 3) == 0));
+#define AFB_BWD_CASE(DIM, SPLIT)                                                                      \
+  case DIM:                                                                                           \
+    rc = mma ? launch_attn_bwd_short_mma<DIM, SPLIT>(a, db, dqb, dk, dv, lddq, lddk, stream)          \
+             : launch_attn_bwd<DIM>(a, db, dqb, dk, dv, lddq, lddk, stream);                          \
+    break;
+  switch (a.head_dim) {
+    AFB_BWD_CASE(40, 1)
+    AFB_BWD_CASE(80, 1)
+    AFB_BWD_CASE(160, 2)
+    default: AFB_FAIL(2, "afb_attention_bwd_short: head_dim %d not supported (SD-1.5 uses 40, 80, 160)", a.head_dim);
+  }
+#undef AFB_BWD_CASE
+  if (rc) return rc;
+  count_launch();
+  AFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
 
 extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout, float* delta_ws, float* dq, float* dk,
                                  float* dv, int64_t ldg, afb_stream_t stream_) {
@@ -1279,17 +1848,24 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
   const bool vec_ok = ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |
                         reinterpret_cast<uintptr_t>(dout)) & 15) == 0 &&
                       a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0;
-  const bool mma = (attn_bwd_mma_enabled() || a.key_mask != nullptr) && vec_ok;
+  const bool mma = (attn_bwd_mode() != 0 || a.key_mask != nullptr) && vec_ok;
   AFB_REQUIRE(a.key_mask == nullptr || mma, "afb_attention_bwd: the key-masked backward needs 16-byte aligned operands");
+  // the 128-key version sends dQ as 8-byte vector atomics and stores dK / dV as float2
+  const bool mma2 = mma && attn_bwd_mode() == 2 && ldg % 2 == 0 &&
+                    ((reinterpret_cast<uintptr_t>(dq) | reinterpret_cast<uintptr_t>(dk) | reinterpret_cast<uintptr_t>(dv)) & 7) == 0;
+#define AFB_BWD_CASE(DIM, SPLIT)                                                                                \
+  case DIM:                                                                                                     \
+    rc = mma2 ? launch_attn_bwd_mma2<DIM, SPLIT>(a, db, delta_ws, dq, dk, dv, ldg, stream)                      \
+       : mma  ? launch_attn_bwd_mma<DIM, SPLIT>(a, db, delta_ws, dq, dk, dv, ldg, stream)                       \
+              : launch_attn_bwd_long<DIM>(a, db, delta_ws, dq, dk, dv, ldg, stream);                            \
+    break;
   switch (a.head_dim) {
-    case 40: rc = mma ? launch_attn_bwd_mma<40, 1>(a, db, delta_ws, dq, dk, dv, ldg, stream)
-                      : launch_attn_bwd_long<40>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
-    case 80: rc = mma ? launch_attn_bwd_mma<80, 1>(a, db, delta_ws, dq, dk, dv, ldg, stream)
-                      : launch_attn_bwd_long<80>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
-    case 160: rc = mma ? launch_attn_bwd_mma<160, 2>(a, db, delta_ws, dq, dk, dv, ldg, stream)
-                       : launch_attn_bwd_long<160>(a, db, delta_ws, dq, dk, dv, ldg, stream); break;
+    AFB_BWD_CASE(40, 1)
+    AFB_BWD_CASE(80, 1)
+    AFB_BWD_CASE(160, 2)
     default: AFB_FAIL(2, "afb_attention_bwd: head_dim %d not supported (SD-1.5 uses 40, 80, 160)", a.head_dim);
   }
+#undef AFB_BWD_CASE
   if (rc) return rc;
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());

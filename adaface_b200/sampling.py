@@ -77,8 +77,8 @@ class FlatGradAllReduce:
     replicated, only the AdaEmbedding / StaticLayerwiseEmbedding parameters (3.8 M floats = 15 MB) carry gradients,
     so a data-parallel optimizer step needs ONE all-reduce: every gradient is copied into a persistent flat fp32
     buffer, summed over the ranks (NCCL over NVLink; gloo in the CPU tests), divided by the world size and copied
-    back - the arithmetic of the reference's Lightning-DDP wrapper (main.py:862) on its trainable set.  Only the
-    collective is built: the backward kernels that would produce these gradients are not.
+    back - the arithmetic of the reference's Lightning-DDP wrapper (main.py:862) on its trainable set.  The gradients
+    come from the backward kernels registered on the custom ops (csrc/backward.cu).
     Parameters whose `.grad` is None on a rank contribute zeros (DDP's find_unused_parameters semantics)."""
 
     def __init__(self, params, group=None):
@@ -139,3 +139,59 @@ class FlatGradAllReduce:
             else:
                 p.grad.copy_(g)
         return self.flat
+
+
+class CapturedGradStep:
+    """Forward + loss + backward of one inversion step (ddpm.py:519-637: training_step -> guided_denoise ->
+    calc_recon_loss -> manual_backward) as ONE CUDA graph.  The step is ~750 launches of this repo's kernels plus the
+    torch ops of the U-Net shell, and issued eagerly it is bound by the host (the kernels of one batch-8 step add up to
+    about 2/3 of its wall time); replayed as a graph the device runs them back to back.
+
+    `loss_fn(*inputs) -> scalar` must be shape-static and free of host synchronisation; the parameters' `.grad` must be
+    views of `reducer.flat` (`FlatGradAllReduce.attach()`), which the graph zeroes first, so that a replay leaves this
+    step's gradients in the flat buffer, ready for the all-reduce and the optimizer (both stay outside the graph: NCCL
+    and the optimizer's step counter).  Train-mode AttentionalPooler dropout takes its seed on the host per call, so a
+    captured step would replay ONE mask: modules must be in eval mode (checked by the caller that owns them).  No
+    autograd graph from an earlier eager step over the same parameters may be alive at construction (its AccumulateGrad
+    nodes are bound to the stream they ran on and would pull that stream into the capture).
+    Not a CPU path: capture needs a CUDA device."""
+
+    def __init__(self, loss_fn: Callable[..., Tensor], example_inputs: Sequence[Tensor], reducer: FlatGradAllReduce,
+                 warmup: int = 3):
+        if not example_inputs or not all(t.is_cuda for t in example_inputs):
+            raise RuntimeError("CapturedGradStep: CUDA example inputs expected (CUDA graphs have no CPU counterpart)")
+        for p_, off in zip(reducer.params, reducer.offsets):
+            if not reducer._is_view(p_, off):
+                raise ValueError("CapturedGradStep: call FlatGradAllReduce.attach() first - every .grad must live in the flat buffer")
+        self.reducer = reducer
+        self.inputs = [t.detach().clone() for t in example_inputs]
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):                         # warm-up off the capture stream (allocator, lazy inits)
+            for _ in range(max(warmup, 1)):
+                reducer.flat.zero_()
+                loss_fn(*self.inputs).backward()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            reducer.flat.zero_()
+            loss = loss_fn(*self.inputs)
+            loss.backward()
+        self.loss = loss.detach()                             # drops the captured autograd graph and its AccumulateGrad nodes
+        del loss
+        for p_, off in zip(reducer.params, reducer.offsets):
+            if not reducer._is_view(p_, off):
+                raise RuntimeError("CapturedGradStep: backward replaced a .grad tensor during capture")
+
+    def __call__(self, *inputs: Tensor) -> Tensor:
+        """Copies the inputs into the graph's buffers and replays; returns the (graph-owned) loss tensor."""
+        if len(inputs) != len(self.inputs):
+            raise ValueError(f"CapturedGradStep: {len(self.inputs)} inputs expected")
+        for dst, src in zip(self.inputs, inputs):
+            if dst.shape != src.shape or dst.dtype != src.dtype:
+                raise ValueError("CapturedGradStep: input shape / dtype differs from the captured one")
+            dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return self.loss

@@ -773,19 +773,36 @@ def run_inversion(args):
     ar0, ar1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     bw0 = torch.cuda.Event(enable_timing=True)
 
-    def step():
-        t = torch.randint(0, 1000, (b,), device=dev, generator=gen)
-        noise = torch.randn(x_start.shape, device=dev, generator=gen)
+    def loss_fn(t, noise):
         x_noisy = model.q_sample(x_start, t, noise)
         eps = unet(x_noisy, t, context=ctx, extra_info=info)
-        loss = ((eps.float() - noise) ** 2).mean()
-        bw0.record()
-        loss.backward()
+        return ((eps.float() - noise) ** 2).mean()
+
+    def draw():
+        return (torch.randint(0, 1000, (b,), device=dev, generator=gen),
+                torch.randn(x_start.shape, device=dev, generator=gen))
+
+    use_graph = not args.no_graph
+    if use_graph:
+        # forward + loss + backward replayed as one CUDA graph (sampling.CapturedGradStep); the all-reduce and the
+        # optimizer stay eager.  --no-graph issues the ~750 launches eagerly (host-bound: the round's earlier numbers)
+        from adaface_b200.sampling import CapturedGradStep
+        captured = CapturedGradStep(loss_fn, draw(), reducer, warmup=2)
+
+    def step():
+        t, noise = draw()
+        if use_graph:
+            bw0.record()
+            loss = captured(t, noise)
+        else:
+            reducer.flat.zero_()
+            loss = loss_fn(t, noise)
+            bw0.record()
+            loss.backward()
         ar0.record()
         reducer()
         ar1.record()
         opt.step()
-        opt.zero_grad(set_to_none=False)
         return loss
 
     def barrier():
@@ -802,10 +819,12 @@ def run_inversion(args):
 
     for _ in range(warmup):
         loss = step()
+    graphed, use_graph = use_graph, False          # launches of OUR kernels per step: one eager step through the C ABI
     n0 = _lib.launch_count()
     step()
     torch.cuda.synchronize()
     launches = _lib.launch_count() - n0
+    use_graph = graphed
     clocks = ClockSampler(local)
     barrier()
     clocks.start()
@@ -823,9 +842,12 @@ def run_inversion(args):
     finite = bool(torch.isfinite(loss)) and all(bool(torch.isfinite(p.grad).all()) for p in params)
     # kernel breakdown of one instrumented step (forward and backward kernels by name)
     torch.cuda.synchronize()
+    use_graph = False                              # the instrumented step goes through the C ABI launch by launch
     ops.start_timing()
     step()
     recs = ops.stop_timing()
+    if args.dump_kernels and rank == 0:
+        dump_kernels(args.dump_kernels, recs)
     groups = {}
     for r_ in recs:
         gk = groups.setdefault(r_["name"], {"ms": 0.0, "launches": 0})
@@ -841,11 +863,12 @@ def run_inversion(args):
                            "batch_per_gpu": b, "trainable_values": sum(p.numel() for p in params),
                            "parallelism": f"data parallel over {world} GPU(s): one all-reduce of {4 * reducer.flat.numel()} bytes per step"},
                 "clocks": clk, "finite": finite, "loss": float(loss.detach()),
-                "backward_ms": bw_ms, "allreduce_ms": ar_ms, "allreduce_share": ar_ms / ms,
+                ("forward_backward_graph_ms" if graphed else "backward_ms"): bw_ms, "cuda_graph": graphed,
+                "allreduce_ms": ar_ms, "allreduce_share": ar_ms / ms,
                 "gpu_launches": launches * steps, "gpu_launches_per_step": launches,
                 "kernels": {k: {"ms": round(v["ms"], 3), "launches": v["launches"]} for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])},
                 "note": "parity of this step: tests/test_backward_gpu.py (gradients vs fp32 autograd through the port); the "
-                        "self-attention backward is a first CUDA-core version, which is what dominates the step"}
+                        "self-attention backward runs on warp-level tensor-core MMAs (mma.sync), not yet on tcgen05"}
         print(json.dumps(line), file=_RESULT_OUT, flush=True)
     if world > 1:
         dist.barrier()

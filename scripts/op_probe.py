@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Device time of single ops without host starvation: each case is captured as a CUDA graph of N back-to-back calls and
-the replay is timed with CUDA events.  Usage: python scripts/op_probe.py gn|ada [N]"""
+the replay is timed with CUDA events.  Usage: python scripts/op_probe.py gn|ada|attn_bwd"""
 import sys
 
 import torch
@@ -71,6 +71,26 @@ def ada_cases():
         print(f"ada chain b{b} n{n} C{c}: pool (main + combine) {t_pool:6.2f} us, pool + head {t_chain:6.2f} us, head alone {t_chain - t_pool:6.2f} us")
 
 
+def attn_bwd_cases():
+    """Self-attention backward of the inversion step (batch 8, SD-1.5 head sizes); AFB_ATTN_BWD=mma1 / simt select the
+    earlier versions (read once per process)."""
+    import os
+    d = "cuda"
+    for b, n, c, heads in [(8, 4096, 320, 8), (8, 1024, 640, 8), (8, 256, 1280, 8), (8, 64, 1280, 8)]:
+        dh = c // heads
+        qkv = (torch.randn(b, n, 3 * c, device=d) * 0.5).to(torch.bfloat16)
+        q, k, v = qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:]
+        out, lse = ops.attention_lse(q, k, v, heads, dh ** -0.5)
+        dout = torch.randn(b, n, c, device=d).to(torch.bfloat16)
+        us = timed(lambda: ops.attention_bwd(q, k, v, out, lse, dout, heads, dh ** -0.5), n=3, reps=3)
+        fl = 10.0 * b * n * n * c
+        print(f"attention_bwd[{os.environ.get('AFB_ATTN_BWD', 'mma2')}] b{b} n{n} d{dh}: {us:9.1f} us  {fl / us / 1e6:7.1f} TFLOP/s")
+        kc = (torch.randn(b, 77, 2 * c, device=d) * 0.5).to(torch.bfloat16)
+        us = timed(lambda: ops.attention_bwd_short(q, kc[..., :c], kc[..., c:], dout, heads, dh ** -0.5, True), n=3, reps=3)
+        fl = 10.0 * b * n * 77 * c
+        print(f"attention_bwd_short[{os.environ.get('AFB_ATTN_BWD', 'mma2')}] b{b} n{n} k77 d{dh}: {us:9.1f} us  {fl / us / 1e6:7.1f} TFLOP/s")
+
+
 if __name__ == "__main__":
     with torch.no_grad():
-        {"gn": gn_cases, "ada": ada_cases}[sys.argv[1]]()
+        {"gn": gn_cases, "ada": ada_cases, "attn_bwd": attn_bwd_cases}[sys.argv[1]]()

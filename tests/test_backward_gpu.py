@@ -374,3 +374,35 @@ def test_inversion_step_through_the_whole_unet(cuda_device):
     # bf16 activations through 25 blocks forward and backward: the flat gradient within 5e-2 / cosine 0.998; the per-tensor
     # bar of SURVEY.md 8d (2e-2) is met at block level (test_inversion_step_through_one_spatial_transformer)
     assert total < 5e-2 and cos > 0.998
+
+    # the same step replayed as one CUDA graph (sampling.CapturedGradStep: forward + loss + backward, gradients left in the
+    # all-reduce's flat buffer): equal to the eager step up to the order of the fp32 atomics, for the captured inputs and
+    # for new ones copied into the graph's buffers
+    from adaface_b200.sampling import CapturedGradStep, FlatGradAllReduce
+    params = [p for p in adas[0].parameters() if p.requires_grad]
+    eager_grad = torch.cat([p.grad.flatten() for p in params]).clone()
+    loss = float(loss)
+    del eps           # the eager step's autograd graph (and its AccumulateGrad nodes on the default stream) must be gone
+    reducer = FlatGradAllReduce(params).attach()
+    xd, cd = x.to(d), ctx.to(d)
+
+    def loss_fn(t_, noise_):
+        return ((unet(xd, t_, context=cd, extra_info=info).float() - noise_) ** 2).mean()
+
+    captured = CapturedGradStep(loss_fn, (t.to(d), noise.to(d)), reducer, warmup=2)
+    loss_g = captured(t.to(d), noise.to(d))
+    graph_grad = reducer.flat.clone()
+    reducer.flat.zero_()
+    loss_fn(t.to(d), noise.to(d)).backward()                  # a second eager run: the run-to-run noise floor
+    noise_floor = rel_l2(reducer.flat, eager_grad)
+    # (not bit-equal: the K-split GEMMs reduce bf16 partials and the backward adds fp32 atomics in arrival order)
+    print(f"captured step vs eager: loss {float(loss_g):.6f} vs {loss:.6f}, flat gradient rel-L2 {rel_l2(graph_grad, eager_grad):.2e} "
+          f"(eager vs eager {noise_floor:.2e})")
+    assert abs(float(loss_g) - loss) < 1e-3 * abs(loss)
+    assert rel_l2(graph_grad, eager_grad) < max(3 * noise_floor, 1e-4)
+    t2, noise2 = torch.tensor([40, 903], dtype=torch.long, device=d), _r("inv4.noise2", (b, 4, hw, hw)).to(d)
+    captured(t2, noise2)
+    replayed = reducer.flat.clone()
+    reducer.flat.zero_()
+    loss_fn(t2, noise2).backward()
+    assert rel_l2(replayed, reducer.flat) < max(3 * noise_floor, 1e-4) and rel_l2(replayed, eager_grad) > 0.1     # new inputs, new gradients
