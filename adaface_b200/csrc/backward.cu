@@ -1875,59 +1875,100 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
 namespace afb {
 namespace {
 
-// ---- GroupNorm backward (attention.py:71-72,325: GroupNorm(32, C, eps) without activation, token-major bf16 in and
-// out): block (group, sample) walks the group's cpg channels of all tokens three times (the slab is L2 resident):
-// statistics of x, then the two means of the LayerNorm-style backward, then
-//   dx = rstd (gamma g - mean(gamma g) - x_hat mean(gamma g x_hat)).
+constexpr int kGnBwdMaxCpg = 128;      // channels per group the backward stages (SD-1.5: 10 .. 80)
+
+// ---- GroupNorm backward (attention.py:71-72,325: GroupNorm(32, C, eps), token-major bf16 in and out; kSilu: the
+// ResBlocks' GroupNorm32 -> SiLU with the conv-bias / time-embedding pre-add, openaimodel.py:259-279): block (group,
+// sample) walks the group's cpg channels of all tokens three times (the slab is L2 resident) with 4-byte loads:
+// statistics of u = x + pre_add, then the two means of the LayerNorm-style backward, then
+//   dx = rstd (gg - mean(gg) - x_hat mean(gg x_hat)),  gg = gamma g  (times silu'(gamma x_hat + beta) when fused).
+template <bool kSilu>
 __global__ void __launch_bounds__(512) gn_bwd_tok_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ g,
-                                                         const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dx, int C,
-                                                         int HW, int cpg, float eps) {
+                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                         const float* __restrict__ pre_add, long long add_ld,
+                                                         __nv_bfloat16* __restrict__ dx, int C, int HW, int cpg, float eps) {
   __shared__ float red[32];
+  __shared__ float s_gamma[kGnBwdMaxCpg], s_beta[kGnBwdMaxCpg], s_pre[kGnBwdMaxCpg];
   const int grp = blockIdx.x, b = blockIdx.y;
   const long long base = static_cast<long long>(b) * HW * C + grp * cpg;
+  if (threadIdx.x < cpg) {
+    s_gamma[threadIdx.x] = gamma[grp * cpg + threadIdx.x];
+    s_beta[threadIdx.x] = beta != nullptr ? beta[grp * cpg + threadIdx.x] : 0.f;
+    s_pre[threadIdx.x] = pre_add != nullptr ? pre_add[b * add_ld + grp * cpg + threadIdx.x] : 0.f;
+  }
+  __syncthreads();
+  const int half = cpg >> 1;                     // channel pairs per token (cpg is even: 4-byte loads)
+  const int n2 = HW * half;
   const int n = HW * cpg;
   float s = 0.f, s2 = 0.f;
-  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
-    const int t = idx / cpg, j = idx - t * cpg;
-    const float v = __bfloat162float(x[base + static_cast<long long>(t) * C + j]);
-    s += v;
-    s2 = fmaf(v, v, s2);
+  for (int idx = threadIdx.x; idx < n2; idx += blockDim.x) {
+    const int t = idx / half, j = 2 * (idx - t * half);
+    const float2 v = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(x + base + static_cast<long long>(t) * C + j));
+    const float a0 = v.x + s_pre[j], a1 = v.y + s_pre[j + 1];
+    s += a0 + a1;
+    s2 = fmaf(a0, a0, fmaf(a1, a1, s2));
   }
   const float mean = block_sum_t(s, red) / n;
   const float var = fmaxf(block_sum_t(s2, red) / n - mean * mean, 0.f);
   const float rstd = rsqrtf(var + eps);
+  // gamma * dL/dz of one element: through the SiLU when fused (z = gamma x_hat + beta, silu'(z) = s (1 + z (1 - s)))
+  auto gz = [&](float xh, float gy, int j) {
+    float d = gy;
+    if (kSilu) {
+      const float z = fmaf(s_gamma[j], xh, s_beta[j]);
+      const float sg = 1.0f / (1.0f + __expf(-z));
+      d *= sg * fmaf(z, 1.0f - sg, 1.0f);
+    }
+    return d * s_gamma[j];
+  };
   float sg = 0.f, sgx = 0.f;
-  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
-    const int t = idx / cpg, j = idx - t * cpg;
+  for (int idx = threadIdx.x; idx < n2; idx += blockDim.x) {
+    const int t = idx / half, j = 2 * (idx - t * half);
     const long long o = base + static_cast<long long>(t) * C + j;
-    const float xh = (__bfloat162float(x[o]) - mean) * rstd;
-    const float gg = __bfloat162float(g[o]) * gamma[grp * cpg + j];
-    sg += gg;
-    sgx = fmaf(gg, xh, sgx);
+    const float2 v = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(x + o));
+    const float2 gy = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(g + o));
+    const float xh0 = (v.x + s_pre[j] - mean) * rstd, xh1 = (v.y + s_pre[j + 1] - mean) * rstd;
+    const float g0 = gz(xh0, gy.x, j), g1 = gz(xh1, gy.y, j + 1);
+    sg += g0 + g1;
+    sgx = fmaf(g0, xh0, fmaf(g1, xh1, sgx));
   }
   const float mg = block_sum_t(sg, red) / n, mgx = block_sum_t(sgx, red) / n;
-  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
-    const int t = idx / cpg, j = idx - t * cpg;
+  for (int idx = threadIdx.x; idx < n2; idx += blockDim.x) {
+    const int t = idx / half, j = 2 * (idx - t * half);
     const long long o = base + static_cast<long long>(t) * C + j;
-    const float xh = (__bfloat162float(x[o]) - mean) * rstd;
-    const float gg = __bfloat162float(g[o]) * gamma[grp * cpg + j];
-    dx[o] = __float2bfloat16_rn(rstd * (gg - mg - xh * mgx));
+    const float2 v = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(x + o));
+    const float2 gy = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(g + o));
+    const float xh0 = (v.x + s_pre[j] - mean) * rstd, xh1 = (v.y + s_pre[j + 1] - mean) * rstd;
+    const float g0 = gz(xh0, gy.x, j), g1 = gz(xh1, gy.y, j + 1);
+    *reinterpret_cast<uint32_t*>(dx + o) = pack_bf16x2(rstd * (g0 - mg - xh0 * mgx), rstd * (g1 - mg - xh1 * mgx));
   }
 }
 
 }  // namespace
 }  // namespace afb
 
-extern "C" int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, afb_bf16* dx, int batch,
-                                        int channels, int hw, int groups, float eps, afb_stream_t stream_) {
+extern "C" int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, const float* beta,
+                                        const float* pre_add, int64_t add_ld, int act, afb_bf16* dx, int batch, int channels,
+                                        int hw, int groups, float eps, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && grad_y && gamma && dx, "afb_groupnorm_tokens_bwd: NULL argument");
   AFB_REQUIRE(batch > 0 && batch <= 65535 && channels > 0 && hw > 0 && groups > 0 && channels % groups == 0,
               "afb_groupnorm_tokens_bwd: bad sizes");
-  gn_bwd_tok_kernel<<<dim3(groups, batch), 512, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
-                                                             reinterpret_cast<const __nv_bfloat16*>(grad_y), gamma,
-                                                             reinterpret_cast<__nv_bfloat16*>(dx), channels, hw, channels / groups, eps);
+  const int cpg = channels / groups;
+  AFB_REQUIRE(cpg % 2 == 0 && cpg <= kGnBwdMaxCpg, "afb_groupnorm_tokens_bwd: channels per group %d must be even and <= %d", cpg,
+              kGnBwdMaxCpg);
+  AFB_REQUIRE(act == 0 || act == 1, "afb_groupnorm_tokens_bwd: act must be 0 (none) or 1 (SiLU)");
+  AFB_REQUIRE(act == 0 || beta != nullptr, "afb_groupnorm_tokens_bwd: the SiLU backward needs beta");
+  AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(grad_y) | reinterpret_cast<uintptr_t>(dx)) & 3) == 0,
+              "afb_groupnorm_tokens_bwd: buffers must be 4-byte aligned");
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(grad_y);
+  __nv_bfloat16* db = reinterpret_cast<__nv_bfloat16*>(dx);
+  if (act == 1)
+    gn_bwd_tok_kernel<true><<<dim3(groups, batch), 512, 0, stream>>>(xb, gb, gamma, beta, pre_add, add_ld, db, channels, hw, cpg, eps);
+  else
+    gn_bwd_tok_kernel<false><<<dim3(groups, batch), 512, 0, stream>>>(xb, gb, gamma, beta, pre_add, add_ld, db, channels, hw, cpg, eps);
   count_launch();
   AFB_CHECK_CUDA(cudaGetLastError());
   return 0;

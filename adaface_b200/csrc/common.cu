@@ -95,7 +95,7 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
 }  // namespace afb
 
 extern "C" const char* afb_last_error(void) { return afb::g_error; }
-extern "C" int afb_abi_version(void) { return 12; }
+extern "C" int afb_abi_version(void) { return 13; }
 #ifndef AFB_HEADER_DIGEST
 #define AFB_HEADER_DIGEST "unknown"
 #endif

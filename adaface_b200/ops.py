@@ -1306,41 +1306,87 @@ def attention_auto(q: Tensor, k: Tensor, v: Tensor, heads: int, scale: float, ke
 
 
 @torch.library.custom_op("adaface_b200::groupnorm_tokens_bwd", mutates_args=())
-def groupnorm_tokens_bwd(x: Tensor, grad_y: Tensor, gamma: Tensor, groups: int, eps: float) -> Tensor:
-    """Backward of `groupnorm_tokens` (no activation, no pre-add) for a bf16 channels-last x [B,C,h,w] and grad_y bf16
-    [B, h*w, C] -> dx bf16 channels-last [B,C,h,w]."""
-    _need_cuda(x, grad_y, gamma)
+def groupnorm_tokens_bwd(x: Tensor, grad_y: Tensor, gamma: Tensor, groups: int, eps: float, beta: Optional[Tensor] = None,
+                         act: int = 0, pre_add: Optional[Tensor] = None) -> Tensor:
+    """Backward of `groupnorm_tokens` for a bf16 channels-last x [B,C,h,w] and grad_y bf16 [B, h*w, C] -> dx bf16
+    channels-last [B,C,h,w]; act = 1 with beta: through the fused SiLU, pre_add: what the forward added to x."""
+    _need_cuda(x, grad_y, gamma, beta, pre_add)
     b, c, h, w = x.shape
     if x.dtype != torch.bfloat16 or not x.permute(0, 2, 3, 1).is_contiguous():
         raise NotImplementedError("groupnorm_tokens_bwd: only the bf16 channels-last layout is built")
     grad_y = _bf16c(grad_y)
     dx = torch.empty_like(x)                                  # preserves channels-last
-    _run("groupnorm_tokens_bwd", _lib.load().afb_groupnorm_tokens_bwd, _ptr(x), _ptr(grad_y), _ptr(gamma.detach().float().contiguous()),
-         _ptr(dx), b, c, h * w, groups, eps, _stream(), nbytes=6.0 * x.numel(), tag=f"b{b}n{h * w}C{c}")
+    f = lambda t: None if t is None else t.detach().float().contiguous()
+    gamma, beta = f(gamma), f(beta)
+    add_ld = 0
+    if pre_add is not None:
+        if pre_add.dtype != torch.float32 or pre_add.shape != (b, c) or pre_add.stride(1) != 1:
+            raise ValueError("groupnorm_tokens_bwd: pre_add must be fp32 [B, C] with contiguous rows")
+        add_ld = pre_add.stride(0)
+    _run("groupnorm_tokens_bwd", _lib.load().afb_groupnorm_tokens_bwd, _ptr(x), _ptr(grad_y), _ptr(gamma), _ptr(beta), _ptr(pre_add),
+         add_ld, act, _ptr(dx), b, c, h * w, groups, eps, _stream(), nbytes=6.0 * x.numel(), tag=f"b{b}n{h * w}C{c}")
     return dx
 
 
 @groupnorm_tokens_bwd.register_fake
-def _(x, grad_y, gamma, groups, eps):
+def _(x, grad_y, gamma, groups, eps, beta=None, act=0, pre_add=None):
     return torch.empty_like(x)
 
 
 def _gn_setup(ctx, inputs, output):
     x, gamma, beta, groups, eps, act, pre_add = inputs
-    _frozen(gamma, beta)
-    if act != 0 or pre_add is not None:
-        raise NotImplementedError("adaface_b200: the backward of the GroupNorm + SiLU / pre-add fusion of the ResBlocks is "
-                                  "not built (ResBlocks take their torch path while gradients are recorded)")
-    ctx.save_for_backward(x, gamma)
-    ctx.groups, ctx.eps = groups, eps
+    _frozen(gamma, beta, pre_add)
+    ctx.save_for_backward(x, gamma, beta, pre_add)
+    ctx.groups, ctx.eps, ctx.act = groups, eps, act
 
 
 def _gn_backward(ctx, g):
-    x, gamma = ctx.saved_tensors
-    return groupnorm_tokens_bwd(x, g, gamma, ctx.groups, ctx.eps), None, None, None, None, None, None
+    x, gamma, beta, pre_add = ctx.saved_tensors
+    return groupnorm_tokens_bwd(x, g, gamma, ctx.groups, ctx.eps, beta, ctx.act, pre_add), None, None, None, None, None, None
 
 
 groupnorm_tokens.register_autograd(_gn_backward, setup_context=_gn_setup)
+
+
+# 3x3 convolution against a frozen weight: dX = the same implicit GEMM with the transposed, spatially flipped weight
+# (w [Cout, 9*Cin], k = (ky*3 + kx)*Cin + c  ->  [Cin, 9*Cout], k' = ((2-ky)*3 + (2-kx))*Cout + o); cached per weight
+_CONV_DX_W = {}
+
+
+def conv3x3_dx_weight(w: Tensor) -> Tensor:
+    key = (w.data_ptr(), w._version, tuple(w.shape))
+    c = _CONV_DX_W.get(key)
+    if c is None:
+        cout, k9 = w.shape
+        cin = k9 // 9
+        with torch.no_grad():
+            c = w.detach().view(cout, 3, 3, cin).flip(1, 2).permute(3, 1, 2, 0).reshape(cin, 9 * cout).contiguous()
+        if len(_CONV_DX_W) > 256:
+            _CONV_DX_W.clear()
+        _CONV_DX_W[key] = c
+    return c
+
+
+def _conv3x3_setup(ctx, inputs, output):
+    x, w, bias, residual, h, width = inputs
+    _frozen(w, bias)
+    if w.shape[0] % 64:
+        raise NotImplementedError("conv3x3 backward: Cout must be a multiple of 64 (it is the K dimension of the dX convolution)")
+    ctx.save_for_backward(w)
+    ctx.hw = (h, width)
+    ctx.x_needs, ctx.res_needs = x.requires_grad, residual is not None and residual.requires_grad
+    ctx.x_dtype, ctx.res_dtype = x.dtype, (None if residual is None else residual.dtype)
+
+
+def _conv3x3_backward(ctx, g):
+    (w,) = ctx.saved_tensors
+    gb = _bf16c(g)
+    dx = conv3x3(gb, conv3x3_dx_weight(w), None, None, ctx.hw[0], ctx.hw[1]).to(ctx.x_dtype) if ctx.x_needs else None
+    dres = g.to(ctx.res_dtype) if ctx.res_needs else None
+    return dx, None, None, dres, None, None
+
+
+conv3x3.register_autograd(_conv3x3_backward, setup_context=_conv3x3_setup)
 
 
 def _abr_setup(ctx, inputs, output):

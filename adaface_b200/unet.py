@@ -40,6 +40,9 @@ _NATIVE_CONV_AUTO = {(2560, 1280, 16), (960, 320, 64), (1920, 1280, 16), (640, 1
 _NATIVE_CONV_W = tuple(int(v) for v in os.environ.get("AFB_CONV_W", "").split(",") if v)
 _NATIVE_UPSAMPLE = os.environ.get("AFB_UPSAMPLE_FOLD", "1") != "0"
 _VIRTUAL_CAT = os.environ.get("AFB_CAT", "1") != "0"
+# AFB_RESBLOCK_BWD=0: ResBlocks go back to differentiable torch ops while gradients are recorded (the A/B switch of the
+# native ResBlock backward: GroupNorm + SiLU backward kernel, dX convolutions on the implicit-GEMM kernel)
+_NATIVE_RESBLOCK_BWD = os.environ.get("AFB_RESBLOCK_BWD", "1") != "0"
 
 
 def timestep_embedding(timesteps: Tensor, dim: int, max_period: int = 10000) -> Tensor:
@@ -68,9 +71,10 @@ class GroupNorm32(nn.GroupNorm):
 
 def _differentiated(*ts) -> bool:
     """True when gradients are being recorded through one of the tensors (the inversion step, BASELINE.json configs[3]).
-    The ResBlocks, up / down-sampling and the output head - outside the hot path, north_star keeps them on torch - then
-    run as plain differentiable torch ops (fp32 GroupNorm + SiLU, bf16 cuDNN convolutions) instead of this repo's fused
-    forward-only kernels; the SpatialTransformers keep their kernels and use the backward of csrc/backward.cu."""
+    Up / down-sampling, the output head and the input convolution then run as plain differentiable torch ops (bf16 cuDNN
+    convolutions); the SpatialTransformers and the ResBlocks keep their kernels and use the backward of csrc/backward.cu
+    (ResBlocks: GroupNorm + SiLU backward, dX convolutions = the implicit GEMM with the transposed, flipped weight;
+    AFB_RESBLOCK_BWD=0 puts them back on torch's fp32 GroupNorm + SiLU and cuDNN)."""
     return torch.is_grad_enabled() and any(isinstance(t, torch.Tensor) and t.requires_grad for t in ts)
 
 
@@ -84,7 +88,8 @@ def _gn_silu_torch(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None
 
 def gn_silu(gn: nn.GroupNorm, x: Tensor, pre_add: Optional[Tensor] = None) -> Tensor:
     """x bf16 channels-last [B, C, H, W] -> SiLU(GroupNorm(x + pre_add[:, :, None, None])), same format."""
-    if _differentiated(x, pre_add):
+    if _differentiated(x, pre_add) and not (_NATIVE_RESBLOCK_BWD and x.is_cuda and x.dtype == torch.bfloat16
+                                            and not _differentiated(pre_add) and (x.shape[1] // gn.num_groups) % 2 == 0):
         return _gn_silu_torch(gn, x, pre_add)
     b, c, h, w = x.shape
     x = x.contiguous(memory_format=CL)
@@ -143,8 +148,10 @@ class _Bf16Conv(nn.Conv2d):
     def native_ok(self, x) -> bool:
         """True when this convolution runs as an implicit GEMM on this repo's tcgen05 GEMM kernel (ops.conv3x3)
         instead of cuDNN: the default (AFB_CONV != 0) for every supported geometry."""
-        if _NATIVE_CONV == "0" or _differentiated(x):      # (the implicit-GEMM convolution has no backward: cuDNN via torch)
+        if _NATIVE_CONV == "0":
             return False
+        if _differentiated(x) and not (_NATIVE_RESBLOCK_BWD and self.stride == (1, 1) and self.out_channels % 64 == 0):
+            return False                     # dX exists for stride 1 (ops.conv3x3 autograd); the rest: cuDNN via torch
         if _NATIVE_CONV == "auto":
             return (self.in_channels, self.out_channels, x.shape[3]) in _NATIVE_CONV_AUTO and self.geometry_ok(x)
         return (not _NATIVE_CONV_W or x.shape[3] in _NATIVE_CONV_W) and self.geometry_ok(x)
@@ -357,6 +364,23 @@ class ResBlock(TimestepBlock):
         with ops.scope("resblock"):
             return self._forward(x, emb)
 
+    def _native_backward_ok(self, x) -> bool:
+        """Gradients can flow through this block's own kernels: both 3x3 convolutions on the implicit GEMM (their dX is
+        the same kernel), even channels per group for the GroupNorm backward's 4-byte loads, bf16 CUDA input."""
+        if not _NATIVE_RESBLOCK_BWD or _NATIVE_CONV != "1":
+            return False
+        shape = x.shape
+        probe = (x.a if isinstance(x, CatPair) else x)
+        if not probe.is_cuda or probe.dtype != torch.bfloat16:
+            return False
+        conv1, conv2 = self.in_layers[2], self.out_layers[3]
+        meta1 = torch.empty(shape, dtype=torch.bfloat16, device="meta")
+        meta2 = torch.empty((shape[0], self.out_channels, shape[2], shape[3]), dtype=torch.bfloat16, device="meta")
+        geo = lambda conv, m: (conv.stride == (1, 1) and conv.kernel_size == (3, 3) and conv.padding == (1, 1) and m.shape[1] % 64 == 0
+                               and conv.out_channels % 64 == 0 and (m.shape[3] % 4 == 0 or 128 % m.shape[3] == 0))
+        return (geo(conv1, meta1) and geo(conv2, meta2) and (shape[1] // self.in_layers[0].num_groups) % 2 == 0
+                and (self.out_channels // self.out_layers[0].num_groups) % 2 == 0)
+
     def _forward_torch(self, x, emb):
         """openaimodel.py:259-279 as differentiable torch ops (frozen bf16 weights), used while gradients are recorded."""
         if isinstance(x, CatPair):
@@ -381,11 +405,14 @@ class ResBlock(TimestepBlock):
         if self.training and self.out_layers[2].p > 0:
             raise NotImplementedError("adaface_b200.ResBlock: dropout > 0 in training mode is not supported")
         pre_probe = emb.per_block[id(self)] if isinstance(emb, EmbBundle) else emb
-        if _differentiated(pre_probe, *((x.a, x.b) if isinstance(x, CatPair) else (x,))):
+        grads = _differentiated(*((x.a, x.b) if isinstance(x, CatPair) else (x,)))
+        if _differentiated(pre_probe) or (grads and not self._native_backward_ok(x)):
             return self._forward_torch(x, emb)
         pair = None
         if isinstance(x, CatPair):
-            if x.virtual() and not isinstance(self.skip_connection, nn.Identity):
+            # (while gradients are recorded the concatenation is materialised: the two-source GroupNorm and skip GEMM
+            #  have no backward, torch.cat's is two slices)
+            if x.virtual() and not isinstance(self.skip_connection, nn.Identity) and not grads:
                 pair = x
             else:
                 x = x.cat()

@@ -334,14 +334,19 @@ int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const
 /* Second stage: what carries a layer's gradient further down the U-Net.
  * afb_attention_bwd: any key length (self-attention), no key mask.  args as in the forward call that produced args->out
  *   and args->lse (both required); dout bf16 with the row pitch of out (ldo); delta_ws fp32 [B * heads * q_len];
- *   dq (zeroed inside), dk, dv fp32 [B * len, ldg].  CUDA-core arithmetic: a first, correct version.
- * afb_groupnorm_tokens_bwd: GroupNorm without activation, token-major bf16 x / grad_y [B, HW, C] -> dx bf16.
+ *   dq (zeroed inside), dk, dv fp32 [B * len, ldg].  Warp-level tensor-core MMAs (mma.sync), 128-key tiles; a key mask
+ *   (args->key_mask) is honoured as in the forward.
+ * afb_groupnorm_tokens_bwd: token-major bf16 x / grad_y [B, HW, C] -> dx bf16.  act = 0: plain GroupNorm (the
+ *   SpatialTransformer's Normalize, attention.py:71-72); act = 1: GroupNorm -> SiLU (the ResBlocks, openaimodel.py:259-279;
+ *   beta required).  pre_add (fp32 [B, C] rows of pitch add_ld, or NULL) is what the forward added to x before the
+ *   statistics (a ResBlock's conv bias + time-embedding projection); gamma / beta / pre_add are frozen: no gradient.
  * afb_ada_pool_bwd_features: the pooler's gradient towards x and q (bf16 [B, N, C] each); other arguments as
  *   afb_ada_pool_bwd. */
 int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout, float* delta_ws, float* dq, float* dk, float* dv,
                       int64_t ldg, afb_stream_t stream);
-int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, afb_bf16* dx, int batch, int channels,
-                             int hw, int groups, float eps, afb_stream_t stream);
+int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, const float* beta,
+                             const float* pre_add, int64_t add_ld, int act, afb_bf16* dx, int batch, int channels, int hw,
+                             int groups, float eps, afb_stream_t stream);
 int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
                               const float* stats, const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg,
                               afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels, float drop_p, uint32_t seed,

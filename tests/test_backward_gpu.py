@@ -326,6 +326,40 @@ def test_groupnorm_tokens_backward(ops, cuda_device):
         assert rel_l2(xd.grad.float(), xr.grad) < 1e-2
 
 
+@pytest.mark.parametrize("tag,cin,cout,hw", [("same", 320, 320, 16), ("skip", 320, 640, 16), ("cat", 640, 320, 32),
+                                             ("cat_small", 2560, 1280, 8), ("w24", 640, 640, 24)])
+def test_resblock_backward_on_own_kernels(cuda_device, tag, cin, cout, hw):
+    """N1 backward (openaimodel.py:259-279 differentiated by autograd in the reference): dX of a ResBlock through this
+    repo's kernels - GroupNorm + SiLU backward (with the conv-bias / time-embedding pre-add), both 3x3 convolutions' dX as
+    the implicit GEMM with the transposed, flipped weight, the 1x1 skip GEMM's dX - against fp32 autograd through the
+    port's res_block; also for the decoder's concatenated input (gradients to both halves)."""
+    from adaface_b200 import ops, unet as U
+    d, seed, cl = cuda_device, 23, torch.channels_last
+    sd = P.init_resblock(cin, cout, seed)
+    rb = U.ResBlock(cin, 1280, 0.0, out_channels=cout)
+    rb.load_state_dict(sd, strict=True)
+    rb = rb.to(d).eval().requires_grad_(False)
+    x = P.randn(f"rbb.{tag}.x", (2, cin, hw, hw), seed).to(torch.bfloat16)
+    emb = P.randn(f"rbb.{tag}.emb", (2, 1280), seed)
+    go = P.randn(f"rbb.{tag}.go", (2, cout, hw, hw), seed).to(torch.bfloat16)
+    xr = x.float().requires_grad_(True)
+    yr = port.res_block(xr, emb, sd, "")
+    yr.backward(go.float())
+    xd = x.to(d).contiguous(memory_format=cl).requires_grad_(True)
+    ops.start_timing()
+    if tag.startswith("cat"):
+        half = cin // 2
+        y = rb(U.CatPair(xd[:, :half], xd[:, half:]), emb.to(d))
+    else:
+        y = rb(xd, emb.to(d))
+    y.backward(go.to(d))
+    names = [r["name"] for r in ops.stop_timing()]
+    assert names.count("conv3x3_bf16") == 4 and "groupnorm_tokens_bwd" in names, names     # 2 forward + 2 dX convolutions
+    e_y, e_dx = rel_l2(y.float(), yr.detach()), rel_l2(xd.grad.float(), xr.grad)
+    print(f"ResBlock {tag} ({cin}->{cout} @ {hw}x{hw}): y {e_y:.1e}, dX {e_dx:.1e}")
+    assert e_y < 1e-2 and e_dx < GRAD_TOL
+
+
 @pytest.mark.slow
 def test_inversion_step_through_the_whole_unet(cuda_device):
     """BASELINE.json configs[3] at reduced size: batch 2 (no CFG pair), one random timestep per sample, loss = MSE(eps, noise)
