@@ -43,6 +43,7 @@ _VIRTUAL_CAT = os.environ.get("AFB_CAT", "1") != "0"
 # AFB_RESBLOCK_BWD=0: ResBlocks go back to differentiable torch ops while gradients are recorded (the A/B switch of the
 # native ResBlock backward: GroupNorm + SiLU backward kernel, dX convolutions on the implicit-GEMM kernel)
 _NATIVE_RESBLOCK_BWD = os.environ.get("AFB_RESBLOCK_BWD", "1") != "0"
+_ADA_PREP_SIDE = os.environ.get("AFB_ADA_PREP_SIDE", "1") != "0"
 
 
 def timestep_embedding(timesteps: Tensor, dim: int, max_period: int = 10000) -> Tensor:
@@ -493,13 +494,30 @@ class AdaPromptContext:
             self._pos[key] = torch.tensor(self.subjects[i].token_positions, dtype=torch.int32, device=device)
         return self._pos[key]
 
-    def prepare_queries(self, layers) -> None:
+    def prepare_queries(self, layers, differentiable: bool = False) -> None:
         """The fg/bg pooling queries of every (layer, subject) depend on the prompt and on weights only, so one U-Net
         call computes all of them up front on a side stream, concurrently with the first convolutions; `apply` joins
-        the stream before the first pooling.  `layers`: [(layer_idx, SpatialTransformer)]."""
+        the stream before the first pooling.  `layers`: [(layer_idx, SpatialTransformer)].
+        differentiable (the inversion step): the per-layer op whose backward reaches the pooler weights
+        (AttentionalPooler.prepare_queries -> ops.ada_pool_prep) instead of the batched launch, still on the side stream -
+        autograd runs each backward on its forward's stream, so the 16 preparations and their backwards leave the
+        critical path in both directions.  AFB_ADA_PREP_SIDE=0 keeps them inline (A/B)."""
         main = torch.cuda.current_stream()
         if self.__dict__.get("_side") is None:
             self._side = torch.cuda.Stream()
+        if differentiable:
+            self._pool_q, self._joined = {}, False
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                for layer_idx, st in layers:
+                    ca = LAYER_IDX2CA_LAYER_IDX[layer_idx]
+                    to_k = st.transformer_blocks[0].attn2.to_k
+                    for i, s in enumerate(self.subjects):
+                        n = s.n_instances
+                        pq = s.embedder.poolers[ca].prepare_queries(to_k, s.layer_probes[ca], s.layer_extra_means[ca][:n], n)
+                        pq.record_stream(main)
+                        self._pool_q[(layer_idx, i)] = pq
+            return
         # one descriptor table for every (layer, subject): built once per set of weights / prompt tensors, then the whole
         # preparation is two launches per U-Net call (afb_ada_pool_prep_batched)
         items, where, key = [], [], []
@@ -762,8 +780,8 @@ class UNetModel(nn.Module):
 
         ada_trains = ada is not None and torch.is_grad_enabled() and any(
             p.requires_grad for s_ in ada.subjects for p in s_.embedder.parameters())
-        if ada is not None and x.is_cuda and not ada_trains:      # (inversion step: per-layer, differentiable preparation)
-            ada.prepare_queries(self.spatial_transformers())
+        if ada is not None and x.is_cuda and (not ada_trains or _ADA_PREP_SIDE):
+            ada.prepare_queries(self.spatial_transformers(), differentiable=ada_trains)
         bundle = self.emb_bundle(emb, e_all)
         hs = []
         with ops.scope("resblock"):                 # (conv_in belongs to the shell, not to the SpatialTransformer path)
