@@ -88,6 +88,20 @@ struct AttnDev {
 #ifndef AFB_ATTN_HALF
 #define AFB_ATTN_HALF 0
 #endif
+// Column-split softmax (d = 40, long key sequences), OFF: TWO warps per TMEM lane quarter and query tile, each taking 32
+// of the round's 64 score columns of the same 32 rows (the row max crosses between them through shared memory and a
+// 64-thread named barrier), with three query tiles per CTA: 24 softmax warps = six per SM sub-partition instead of
+// four, each with half the serial chain (load -> max -> exponentials -> store -> MMA round trip).  The idea came from
+// ncu on the four-warp version - issue slots 60 %, XU 63 %, top stall long_scoreboard (TMEM loads, barrier waits) -
+// read as latency that more warps would hide.  MEASURED SLOWER (B200, 4096 x 4096, batch 16, in the step): 703 us with
+// one S buffer (-DAFB_ATTN_COLSPLIT=1), 715 us with two (=2, 3 x (128 + 40) TMEM columns, row sums back in registers)
+// against 556 us: per query tile a 64-key round takes ~670 instead of ~600 cycles.  Every softmax warp pays a fixed
+// per-round cost (barrier waits, fences, the publish, loop control, and now the max exchange) that the split doubles
+// while the exponentials stay the same, i.e. the kernel is bound by the instruction stream the softmax warps issue, not
+// by exposed latency: fewer instructions per score is the only lever (finding 5 of DESIGN.md section 4).
+#ifndef AFB_ATTN_COLSPLIT
+#define AFB_ATTN_COLSPLIT 0
+#endif
 
 // kSmall: the variant for a short key sequence (the 77-token context, the 8x8 image's self-attention): such a CTA is
 // one serial chain (set-up, loads, two score tiles, epilogue) with nothing to pipeline, so instead of four query tiles
@@ -114,10 +128,15 @@ struct AttnCfg {
   // clocks per 64 keys of the four tiles, and the softmax warps wait for the pipe (2100 instead of 800 clocks per 64
   // keys) instead of for the round trip.  Off by default; -DAFB_ATTN_HALF=1 builds it.
   static constexpr bool kHalf = AFB_ATTN_HALF != 0 && kPTmem && !kSmall && D <= 40 && AFB_ATTN_SDOUBLE < 2;
-  static constexpr bool kSDouble = kHalf || (AFB_ATTN_SDOUBLE != 0 && kPTmem && !kSmall && D <= 80 && (D > 40 || AFB_ATTN_SDOUBLE >= 2));
+  // (AFB_ATTN_COLSPLIT: 1 = column split over one S buffer, 2 = column split over two S buffers)
+  static constexpr bool kColSplit = AFB_ATTN_COLSPLIT != 0 && kPTmem && !kSmall && D <= 40 && AFB_ATTN_HALF == 0;
+  static constexpr bool kSDouble = kHalf || (AFB_ATTN_SDOUBLE != 0 && kPTmem && !kSmall && D <= 80 &&
+                                             (D > 40 || AFB_ATTN_SDOUBLE >= 2 || (kColSplit && AFB_ATTN_COLSPLIT >= 2)));
   static constexpr int kSKeys = kHalf ? 32 : kBlockKV;          // keys per S buffer = keys per softmax round
-  static constexpr int kQTiles = kSmall ? 1 : ((D <= 40) ? ((kSDouble && !kHalf) ? 3 : 4) : 2);   // query tiles per CTA
-  static constexpr int kThreads = 64 + kQTiles * 128;
+  static constexpr int kQTiles = kSmall ? 1 : ((D <= 40) ? (((kSDouble && !kHalf) || kColSplit) ? 3 : 4) : 2);   // query tiles per CTA
+  static constexpr int kWarpsPerTile = kColSplit ? 8 : 4;        // softmax warps of one query tile
+  static constexpr int kThreads = 64 + kQTiles * kWarpsPerTile * 32;
+  static constexpr int kCols = kColSplit ? kSKeys / 2 : kSKeys;  // score columns a softmax thread holds per round
   static constexpr int kAtoms = (D + 63) / 64;                 // 64-column (128-byte) swizzle atoms per row
   static constexpr int kDPadK = (D + 15) / 16 * 16;            // K extent of S = Q K^T (UMMA K step 16)
   static constexpr bool kOnes = AFB_ATTN_ONES != 0 && D <= 40 && (!kSDouble || kHalf);   // d = 80 is tensor-bound: the wider P V costs more there
@@ -126,7 +145,8 @@ struct AttnCfg {
   static constexpr int kQTileBytes = kAtoms * kBlockQ * 128;   // one query tile: atom a at a * 16 KB
   static constexpr int kKVTileBytes = kAtoms * kBlockKV * 128;  // one of K or V
   static constexpr int kPBytes = kBlockQ * 128;                 // one query tile's P (64 keys = one atom)
-  static constexpr int kStages = kSmall ? 2 : ((D <= 40) ? 4 : (D <= 80 ? 3 : 2));
+  // (column split: three query tiles leave room for a fifth K/V stage, and keep the CTA above half the SM's shared memory)
+  static constexpr int kStages = kSmall ? 2 : ((D <= 40) ? (kColSplit ? 5 : 4) : (D <= 80 ? 3 : 2));
 #ifndef AFB_ATTN_POLY_EVERY
 #define AFB_ATTN_POLY_EVERY 3
 #endif
@@ -186,6 +206,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   constexpr int NT = C::kQTiles;
   extern __shared__ __align__(1024) uint8_t smem[];     // SWIZZLE_128B atoms need 1024-byte alignment
   __shared__ __align__(8) uint64_t bars[2 + 6 * NT + 4 * NS + 1];
+  __shared__ float s_mx[C::kColSplit ? 2 * NT * 2 * kBlockQ : 1];      // column split: partial row maxima [parity][tile][half][row]
+  __shared__ float s_lsum[(C::kColSplit && !C::kOnes) ? NT * 2 * kBlockQ : 1];   // ... and partial row sums (epilogue)
+  static_assert(!C::kColSplit || C::kPTmem, "column split: P through tensor memory");
   uint8_t* sQ = smem;                                   // [NT] query tiles
   uint8_t* sK = sQ + NT * C::kQTileBytes;               // [NS] K tiles
   uint8_t* sV = sK + NS * C::kKVTileBytes;              // [NS] V tiles
@@ -216,13 +239,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
     mbar_init(q_full, 1);
-    mbar_init(q_ready, 4 * n_tiles);
+    mbar_init(q_ready, C::kWarpsPerTile * n_tiles);
     for (int t = 0; t < NT; ++t) {
       mbar_init(&s_full[2 * t], 1);
       mbar_init(&s_full[2 * t + 1], 1);
       mbar_init(&s_free[t], C::kSDouble ? 1 : 4);
-      mbar_init(&p_ready[2 * t], 4);
-      mbar_init(&p_ready[2 * t + 1], 4);
+      mbar_init(&p_ready[2 * t], C::kWarpsPerTile);
+      mbar_init(&p_ready[2 * t + 1], C::kWarpsPerTile);
       mbar_init(&pv_done[t], 1);
     }
     for (int i = 0; i < 4 * NS; ++i) mbar_init(&k_full[i], 1);
@@ -474,10 +497,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       }
 #endif
     }
-  } else if (warp < 2 + 4 * n_tiles) {
+  } else if (warp < 2 + C::kWarpsPerTile * n_tiles) {
     // ------------------------------------------------------------------ softmax / correction / epilogue
-    const int t = (warp - 2) >> 2;                        // query tile
+    const int t = (warp - 2) / C::kWarpsPerTile;          // query tile
     const int quarter = warp & 3;                         // TMEM lane quarter this warp may access (= its SMSP)
+    // column split: the tile's warps 0-3 take score columns 0-31 of a round, warps 4-7 columns 32-63 (8 t = 0 mod 4, so
+    // both halves see every lane quarter)
+    const int ch = C::kColSplit ? (((warp - 2) % C::kWarpsPerTile) >> 2) : 0;
+    constexpr int CN = C::kCols;                          // score columns per thread and round
     const int row = quarter * 32 + lane;                  // query row inside the tile
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
     const uint32_t tmem_s0 = tmem_base + lane_addr + C::kTmemS + t * C::kSStride;
@@ -495,7 +522,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       constexpr int chunk = D / 8;                        // 16-byte chunk index inside the 128-byte row
       uint8_t* dst = sQ + t * C::kQTileBytes + (C::kAtoms - 1) * (kBlockQ * 128) + row * 128 +
                      (((chunk & 7) ^ (row & 7)) << 4);
-      *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+      if (ch == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
       fence_proxy_async_smem();
     }
     __syncwarp();
@@ -526,9 +553,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       mbar_wait(&s_full[2 * t + sbuf], C::kSDouble ? ((j >> 1) & 1) : (j & 1));
       tc_fence_after();
       AFB_PROF(0);                                        // wait for S
-      uint32_t r[BS];
+      uint32_t r[CN];
 #pragma unroll
-      for (int c = 0; c < BS / 32; ++c) tmem_ld32p(tmem_s + c * 32, &r[c * 32]);
+      for (int c = 0; c < CN / 32; ++c) tmem_ld32p(tmem_s + ch * CN + c * 32, &r[c * 32]);
       tmem_ld_wait();
       if constexpr (!C::kPTmem) {
         tc_fence_before();
@@ -537,31 +564,43 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       }
       AFB_PROF(1);                                        // TMEM load
 
-      const int kv0 = j * BS;
+      const int kv0 = j * BS + ch * CN;                   // first key of this thread's columns
       if (kHasMask) {
         // masked keys get a large finite negative IN THE SCALED DOMAIN (like the reference's masked_fill after the
         // scaling): a fully masked row then cancels exactly to exp2(0) and averages uniformly
 #pragma unroll
-        for (int i = 0; i < BS; ++i) {
+        for (int i = 0; i < CN; ++i) {
           float v = __uint_as_float(r[i]) * sc;
           if (kv0 + i < p.kv_len && mask_row[kv0 + i] == 0) v = kMaskedScore;
           r[i] = __float_as_uint(v);
         }
       }
-      if (kv0 + BS > p.kv_len) {
+      if (kv0 + CN > p.kv_len) {
 #pragma unroll
-        for (int i = 0; i < BS; ++i)
+        for (int i = 0; i < CN; ++i)
           if (kv0 + i >= p.kv_len) r[i] = 0xff800000u;    // -inf
       }
       float mx[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
 #pragma unroll
-      for (int i = 4; i < BS; i += 8) {
+      for (int i = 4; i < CN; i += 8) {
 #pragma unroll
         for (int c = 0; c < 4; ++c)
-          if (i + 2 * c + 1 < BS)
+          if (i + 2 * c + 1 < CN)
             mx[c] = fmax3(mx[c], __uint_as_float(r[i + 2 * c]), __uint_as_float(r[i + 2 * c + 1]));
       }
-      const float m_raw = fmaxf(fmax3(mx[0], mx[1], mx[2]), mx[3]);
+      float m_raw = fmaxf(fmax3(mx[0], mx[1], mx[2]), mx[3]);
+      if constexpr (C::kColSplit) {
+        // the row's other 32 columns belong to the partner warp (same lane quarter, other column half): swap partial
+        // maxima through shared memory (double-buffered by round parity) across a 64-thread named barrier.  The barrier
+        // also orders the partner's tcgen05.ld of ITS score columns before this warp's P store, which overwrites the
+        // first 32 columns of the S buffer.
+        float* slot = s_mx + (((j & 1) * NT + t) * 2) * kBlockQ + row;
+        slot[ch * kBlockQ] = m_raw;
+        tc_fence_before();
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + t * 4 + quarter) : "memory");
+        tc_fence_after();
+        m_raw = fmaxf(m_raw, slot[(ch ^ 1) * kBlockQ]);
+      }
       const float m_tile = kHasMask ? m_raw : m_raw * sc;   // scale > 0
 
       const bool need = (j == 0) || (m_tile > m_used + kRescaleThreshold);
@@ -579,8 +618,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         const float alpha = ex2_approx(m_used - m_new);  // 1 for rows that keep their reference max
         m_used = m_new;
         l_run *= alpha;
+        // (column split: the two warps of a row rescale half of its O columns each)
+        constexpr int kOChunks = C::kDPadN / 8, kOHalf = (kOChunks + 1) / 2;
 #pragma unroll
-        for (int c = 0; c < C::kDPadN / 8; ++c) {
+        for (int c = 0; c < kOChunks; ++c) {
+          if (C::kColSplit && (c < kOHalf) != (ch == 0)) continue;
           uint32_t o[8];
           tmem_ld8(tmem_o + c * 8, o);
           tmem_ld_wait();
@@ -596,7 +638,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       const uint64_t nm2 = pack_f32x2(-m_used, -m_used);
       uint64_t acc0 = 0ull, acc1 = 0ull;                 // two packed partial sums
 #pragma unroll
-      for (int i = 0; i < BS / 2; ++i) {
+      for (int i = 0; i < CN / 2; ++i) {
         uint64_t x = pack_f32x2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
         x = kHasMask ? fadd2(x, nm2) : ffma2(x, sc2, nm2);
         float lo, hi;
@@ -624,13 +666,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 
       if constexpr (C::kPTmem) {
         // P_j (bf16 pairs, BS / 2 columns) over the first half of this round's S columns
-        if constexpr (BS == 64) {
+        if constexpr (CN == 64) {
           tmem_st32p(tmem_s, r);
         } else {
+          // 32 scores -> 16 columns of bf16 pairs (column split: the second warp's keys follow the first warp's)
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) pk[i] = r[i];
-          tmem_st16(tmem_s, pk);
+          tmem_st16(tmem_s + ch * (CN / 2), pk);
         }
         tmem_st_wait();
       } else {
@@ -668,12 +711,20 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       tmem_ld_wait();
       l_run = __uint_as_float(o[0]);
     }
+    if constexpr (C::kColSplit && !C::kOnes) {
+      // row sum in registers: each of the row's two warps holds the sum over its own score columns
+      float* slot = s_lsum + (t * 2) * kBlockQ + row;
+      slot[ch * kBlockQ] = l_run;
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + t * 4 + quarter) : "memory");
+      l_run += slot[(ch ^ 1) * kBlockQ];
+    }
     const float inv_l = 1.0f / l_run;
-    if (p.lse != nullptr && q_idx < p.q_len)      // P = 2^(s * scale * log2(e) - lse)
+    if (p.lse != nullptr && q_idx < p.q_len && ch == 0)      // P = 2^(s * scale * log2(e) - lse)
       p.lse[(static_cast<long long>(b) * p.heads + head) * p.q_len + q_idx] = m_used + log2f(l_run);
     __nv_bfloat16* orow = p.out + (static_cast<long long>(b) * p.q_len + q_idx) * p.ldo + col0;
 #pragma unroll
     for (int c = 0; c < D / 8; ++c) {
+      if (C::kColSplit && (c < (D / 8 + 1) / 2) != (ch == 0)) continue;     // each of the row's two warps writes its half
       uint32_t o[8];
       tmem_ld8(tmem_o + c * 8, o);
       tmem_ld_wait();
