@@ -81,7 +81,7 @@ _SIGNATURES = {
     "afb_ada_pool_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, C.c_uint32, _P]),
     "afb_ada_pool_prep_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "afb_attention_bwd": (_I, [C.POINTER(AttnArgs), _P, _P, _P, _P, _P, _I64, _P]),
-    "afb_groupnorm_tokens_bwd": (_I, [_P, _P, _P, _P, _P, _I64, _I, _P, _I, _I, _I, _I, _F, _P]),
+    "afb_groupnorm_tokens_bwd": (_I, [_P, _P, _P, _P, _P, _I64, _I, _P, _P, _I, _I, _I, _I, _F, _P]),
     "afb_ada_pool_bwd_features": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, C.c_uint32, _P]),
     "afb_cast_f32_to_bf16": (_I, [_P, _P, _I64, _P]),
     "afb_cast_bf16_to_f32": (_I, [_P, _P, _I64, _P]),

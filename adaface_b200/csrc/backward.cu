@@ -1944,12 +1944,150 @@ __global__ void __launch_bounds__(512) gn_bwd_tok_kernel(const __nv_bfloat16* __
   }
 }
 
+// ---- streaming version for large slabs (the ResBlocks' and SpatialTransformers' GroupNorms at 32x32 and above) --------
+// The slab kernel above reads 20..160-byte channel runs of a (sample, group) with 4-byte loads, 256 blocks per launch:
+// 86 us for a 21 MB tensor (b8 n4096 C320).  Here every block streams whole token rows (16-byte loads, all channels) of
+// a token range; a thread owns one 8-channel column over its rows, so the per-channel constants live in registers.
+// Three passes: per-group sums of u = x + pre_add and u^2; per-group sums of gg and gg x_hat; dx.  Per-group partials go
+// through shared memory into fp32 atomics on a [B, G, 4] workspace (zeroed by the entry point).
+template <int kPass, bool kSilu>
+__global__ void __launch_bounds__(320) gn_bwd_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ g,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            const float* __restrict__ pre_add, long long add_ld,
+                                                            float* __restrict__ ws, __nv_bfloat16* __restrict__ dx, int C, int HW,
+                                                            int cpg, float eps, int tokens_per_block, int rpi) {
+  extern __shared__ float sh[];                 // [rpi][C][2] per-channel partials of this block's rows
+  __shared__ float sg[2 * 64];                  // per-group partials
+  const int b = blockIdx.y, G = C / cpg;
+  const int nvec = C >> 3;
+  const int cv = threadIdx.x % nvec, r = threadIdx.x / nvec;
+  const int c0 = cv * 8;
+  const int t0 = blockIdx.x * tokens_per_block;
+  const int t1 = min(HW, t0 + tokens_per_block);
+  const float inv_n = 1.0f / (static_cast<float>(HW) * cpg);
+  float ga[8], be[8], pa[8], mean[8], rstd[8], mg[8], mgx[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int ch = c0 + j, grp = ch / cpg;
+    pa[j] = pre_add != nullptr ? pre_add[b * add_ld + ch] : 0.f;
+    ga[j] = be[j] = mean[j] = rstd[j] = mg[j] = mgx[j] = 0.f;
+    if (kPass >= 1) {
+      const float* w = ws + (static_cast<long long>(b) * G + grp) * 4;
+      ga[j] = gamma[ch];
+      be[j] = beta != nullptr ? beta[ch] : 0.f;
+      mean[j] = w[0] * inv_n;
+      rstd[j] = rsqrtf(fmaxf(w[1] * inv_n - mean[j] * mean[j], 0.f) + eps);
+      if (kPass == 2) {
+        mg[j] = w[2] * inv_n;
+        mgx[j] = w[3] * inv_n;
+      }
+    }
+  }
+  float a0[8], a1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a0[j] = a1[j] = 0.f;
+  // two rows per iteration: both rows' 16-byte loads are in flight before either is consumed
+  for (int t = t0 + r; t < t1; t += 2 * rpi) {
+    const bool two = t + rpi < t1;
+    const long long o0 = (static_cast<long long>(b) * HW + t) * C + c0;
+    const long long o1 = two ? o0 + static_cast<long long>(rpi) * C : o0;
+    uint4 xr[2], gr[2];
+    xr[0] = *reinterpret_cast<const uint4*>(x + o0);
+    xr[1] = *reinterpret_cast<const uint4*>(x + o1);
+    if (kPass >= 1) {
+      gr[0] = *reinterpret_cast<const uint4*>(g + o0);
+      gr[1] = *reinterpret_cast<const uint4*>(g + o1);
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (h == 1 && !two) break;
+      float xv[8], gv[8], out[8];
+      unpack8f(xr[h], xv);
+      if (kPass >= 1) unpack8f(gr[h], gv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float u = xv[j] + pa[j];
+        if (kPass == 0) {
+          a0[j] += u;
+          a1[j] = fmaf(u, u, a1[j]);
+        } else {
+          const float xh = (u - mean[j]) * rstd[j];
+          float d = gv[j];
+          if (kSilu) {
+            const float z = fmaf(ga[j], xh, be[j]);
+            const float s = 1.0f / (1.0f + __expf(-z));
+            d *= s * fmaf(z, 1.0f - s, 1.0f);
+          }
+          const float gg = d * ga[j];
+          if (kPass == 1) {
+            a0[j] += gg;
+            a1[j] = fmaf(gg, xh, a1[j]);
+          } else {
+            out[j] = rstd[j] * (gg - mg[j] - xh * mgx[j]);
+          }
+        }
+      }
+      if (kPass == 2) *reinterpret_cast<uint4*>(dx + (h == 0 ? o0 : o1)) = pack8f(out);
+    }
+  }
+  if (kPass == 2) return;
+  if (threadIdx.x < 2 * G) sg[threadIdx.x] = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sh[(r * C + c0 + j) * 2] = a0[j];
+    sh[(r * C + c0 + j) * 2 + 1] = a1[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s0 = 0.f, s1 = 0.f;
+    for (int rr = 0; rr < rpi; ++rr) {
+      s0 += sh[(rr * C + c) * 2];
+      s1 += sh[(rr * C + c) * 2 + 1];
+    }
+    atomicAdd(&sg[2 * (c / cpg)], s0);
+    atomicAdd(&sg[2 * (c / cpg) + 1], s1);
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * G)
+    atomicAdd(ws + (static_cast<long long>(b) * G + (threadIdx.x >> 1)) * 4 + 2 * kPass + (threadIdx.x & 1), sg[threadIdx.x]);
+}
+
+// AFB_GN_BWD=slab keeps the (sample, group) slab kernel for every shape (A/B)
+bool gn_bwd_stream_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("AFB_GN_BWD");
+    return e == nullptr || !(e[0] == 's' && e[1] == 'l');
+  }();
+  return on;
+}
+
+template <bool kSilu>
+int launch_gn_bwd_stream(const __nv_bfloat16* x, const __nv_bfloat16* g, const float* gamma, const float* beta, const float* pre_add,
+                         long long add_ld, float* ws, __nv_bfloat16* dx, int batch, int C, int HW, int groups, float eps,
+                         cudaStream_t stream) {
+  const int nvec = C / 8;
+  const int rpi = nvec >= 256 ? 1 : 256 / nvec;
+  const int threads = nvec * rpi;
+  // about two blocks per SM: a thread sets up the constants of its 8 channels once and should then walk >= 16 rows
+  long long tpb = (static_cast<long long>(batch) * HW + 2 * num_sms() - 1) / (2 * num_sms());
+  if (tpb < rpi) tpb = rpi;
+  tpb = (tpb + rpi - 1) / rpi * rpi;
+  const dim3 grid(static_cast<unsigned>((HW + tpb - 1) / tpb), batch);
+  const size_t sh = static_cast<size_t>(rpi) * C * 2 * sizeof(float);
+  AFB_CHECK_CUDA(cudaMemsetAsync(ws, 0, static_cast<size_t>(batch) * groups * 4 * sizeof(float), stream));
+  const int cpg = C / groups, t = static_cast<int>(tpb);
+  gn_bwd_stream_kernel<0, kSilu><<<grid, threads, sh, stream>>>(x, g, gamma, beta, pre_add, add_ld, ws, dx, C, HW, cpg, eps, t, rpi);
+  gn_bwd_stream_kernel<1, kSilu><<<grid, threads, sh, stream>>>(x, g, gamma, beta, pre_add, add_ld, ws, dx, C, HW, cpg, eps, t, rpi);
+  gn_bwd_stream_kernel<2, kSilu><<<grid, threads, 0, stream>>>(x, g, gamma, beta, pre_add, add_ld, ws, dx, C, HW, cpg, eps, t, rpi);
+  return 0;
+}
+
 }  // namespace
 }  // namespace afb
 
 extern "C" int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, const float* beta,
-                                        const float* pre_add, int64_t add_ld, int act, afb_bf16* dx, int batch, int channels,
-                                        int hw, int groups, float eps, afb_stream_t stream_) {
+                                        const float* pre_add, int64_t add_ld, int act, afb_bf16* dx, float* ws, int batch,
+                                        int channels, int hw, int groups, float eps, afb_stream_t stream_) {
   using namespace afb;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AFB_REQUIRE(x && grad_y && gamma && dx, "afb_groupnorm_tokens_bwd: NULL argument");
@@ -1965,7 +2103,15 @@ extern "C" int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_
   const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
   const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(grad_y);
   __nv_bfloat16* db = reinterpret_cast<__nv_bfloat16*>(dx);
-  if (act == 1)
+  // large slabs: three streaming passes over whole token rows (needs the [B, G, 4] workspace and 16-byte rows)
+  const bool stream_ok = ws != nullptr && gn_bwd_stream_enabled() && channels % 8 == 0 && channels / 8 <= 320 && groups <= 64 &&
+                         cpg >= 8 && hw >= 2048 &&      // (measured: below ~2k tokens per sample the slab kernel is faster)
+                         ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(grad_y) | reinterpret_cast<uintptr_t>(dx)) & 15) == 0;
+  if (stream_ok) {
+    const int rc = act == 1 ? launch_gn_bwd_stream<true>(xb, gb, gamma, beta, pre_add, add_ld, ws, db, batch, channels, hw, groups, eps, stream)
+                            : launch_gn_bwd_stream<false>(xb, gb, gamma, beta, pre_add, add_ld, ws, db, batch, channels, hw, groups, eps, stream);
+    if (rc) return rc;
+  } else if (act == 1)
     gn_bwd_tok_kernel<true><<<dim3(groups, batch), 512, 0, stream>>>(xb, gb, gamma, beta, pre_add, add_ld, db, channels, hw, cpg, eps);
   else
     gn_bwd_tok_kernel<false><<<dim3(groups, batch), 512, 0, stream>>>(xb, gb, gamma, beta, pre_add, add_ld, db, channels, hw, cpg, eps);

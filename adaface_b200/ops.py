@@ -1323,8 +1323,9 @@ def groupnorm_tokens_bwd(x: Tensor, grad_y: Tensor, gamma: Tensor, groups: int, 
         if pre_add.dtype != torch.float32 or pre_add.shape != (b, c) or pre_add.stride(1) != 1:
             raise ValueError("groupnorm_tokens_bwd: pre_add must be fp32 [B, C] with contiguous rows")
         add_ld = pre_add.stride(0)
+    ws = torch.empty((b * groups * 4,), dtype=torch.float32, device=x.device)
     _run("groupnorm_tokens_bwd", _lib.load().afb_groupnorm_tokens_bwd, _ptr(x), _ptr(grad_y), _ptr(gamma), _ptr(beta), _ptr(pre_add),
-         add_ld, act, _ptr(dx), b, c, h * w, groups, eps, _stream(), nbytes=6.0 * x.numel(), tag=f"b{b}n{h * w}C{c}")
+         add_ld, act, _ptr(dx), _ptr(ws), b, c, h * w, groups, eps, _stream(), nbytes=6.0 * x.numel(), tag=f"b{b}n{h * w}C{c}")
     return dx
 
 

@@ -340,13 +340,15 @@ int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const
  *   SpatialTransformer's Normalize, attention.py:71-72); act = 1: GroupNorm -> SiLU (the ResBlocks, openaimodel.py:259-279;
  *   beta required).  pre_add (fp32 [B, C] rows of pitch add_ld, or NULL) is what the forward added to x before the
  *   statistics (a ResBlock's conv bias + time-embedding projection); gamma / beta / pre_add are frozen: no gradient.
+ *   ws: fp32 [batch * groups * 4] scratch (zeroed inside) for the streaming three-pass version that large slabs take
+ *   (hw >= 2048); NULL keeps the single-kernel (sample, group) slab version for every shape.
  * afb_ada_pool_bwd_features: the pooler's gradient towards x and q (bf16 [B, N, C] each); other arguments as
  *   afb_ada_pool_bwd. */
 int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout, float* delta_ws, float* dq, float* dk, float* dv,
                       int64_t ldg, afb_stream_t stream);
 int afb_groupnorm_tokens_bwd(const afb_bf16* x, const afb_bf16* grad_y, const float* gamma, const float* beta,
-                             const float* pre_add, int64_t add_ld, int act, afb_bf16* dx, int batch, int channels, int hw,
-                             int groups, float eps, afb_stream_t stream);
+                             const float* pre_add, int64_t add_ld, int act, afb_bf16* dx, float* ws, int batch, int channels,
+                             int hw, int groups, float eps, afb_stream_t stream);
 int afb_ada_pool_bwd_features(const afb_bf16* x, const afb_bf16* q, const float* pool_q, const uint8_t* key_mask,
                               const float* stats, const float* fg_out, const float* bg_out, const float* d_fg, const float* d_bg,
                               afb_bf16* dx, afb_bf16* dq, int batch, int n_tokens, int channels, float drop_p, uint32_t seed,

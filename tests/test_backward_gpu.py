@@ -315,7 +315,8 @@ def test_self_attention_backward_with_key_mask(ops, cuda_device, c, nq):
 
 def test_groupnorm_tokens_backward(ops, cuda_device):
     d = cuda_device
-    for b, c, hw in ((2, 320, 16), (3, 1280, 4)):
+    # (hw * hw >= 2048: the streaming three-pass kernels, incl. the 320-thread column layout at C = 2560; below: the slab kernel)
+    for b, c, hw in ((2, 320, 16), (3, 1280, 4), (1, 2560, 48), (2, 960, 64), (2, 320, 64)):
         x = (_r("gnb.x", (b, c, hw, hw)) * 1.4 + 0.3).to(torch.bfloat16)
         g, be = 1 + 0.1 * _r("gnb.g", (c,)), 0.1 * _r("gnb.b", (c,))
         go = _r("gnb.go", (b, hw * hw, c)).to(torch.bfloat16)
