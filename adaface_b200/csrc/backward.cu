@@ -745,7 +745,14 @@ extern "C" int afb_ada_pool_bwd(const afb_bf16* x, const afb_bf16* q, const floa
   AFB_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) & 15) == 0, "afb_ada_pool_bwd: x/q must be 16-byte aligned");
   const int C = channels;
   int blocks = 2 * num_sms() / batch;
-  const int max_blocks = (n_tokens + 7) / 8;
+  // at least AFB_ADA_BWD_MIN_TOKENS (default 32) tokens per block: every block ends with 2 C atomics on du, which is what
+  // a 16x16 layer's launch consisted of at one token per warp
+  static const int min_tokens = [] {
+    const char* e = getenv("AFB_ADA_BWD_MIN_TOKENS");
+    const int v = e ? atoi(e) : 32;
+    return v < 8 ? 8 : v;
+  }();
+  const int max_blocks = (n_tokens + min_tokens - 1) / min_tokens;
   if (blocks > max_blocks) blocks = max_blocks;
   if (blocks < 1) blocks = 1;
   const int tokens_per_block = (n_tokens + blocks - 1) / blocks;
