@@ -274,6 +274,20 @@ def test_inversion_gradient_allreduce_world_size_2_gloo(tmp_path):
         assert torch.allclose(r0["grads"][i], want, atol=1e-6) and torch.equal(r0["grads"][i], r1["grads"][i])
 
 
+def test_captured_grad_step_fails_loudly_without_cuda_or_attached_gradients():
+    """sampling.CapturedGradStep (the inversion step as one CUDA graph) has no CPU counterpart and needs every .grad to be
+    a view of the all-reduce's flat buffer: both are errors, not silent fallbacks."""
+    from adaface_b200.sampling import CapturedGradStep, FlatGradAllReduce
+    p = torch.nn.Parameter(torch.randn(4, 3))
+    reducer = FlatGradAllReduce([p])
+    with pytest.raises(RuntimeError, match="CUDA"):
+        CapturedGradStep(lambda x: (p * x).sum(), (torch.ones(4, 3),), reducer.attach())
+    if torch.cuda.is_available():
+        q = torch.nn.Parameter(torch.randn(4, 3, device="cuda"))
+        with pytest.raises(ValueError, match="attach"):
+            CapturedGradStep(lambda x: (q * x).sum(), (torch.ones(4, 3, device="cuda"),), FlatGradAllReduce([q]))
+
+
 def test_reference_embedding_checkpoint_loads_without_ldm():
     """a checkpoint written by torch.save with LIVE reference modules (pickled class path
     ldm.modules.embedding_manager.StaticLayerwiseEmbedding; fixture made by oracle/gen_golden.py from the imported
