@@ -973,234 +973,18 @@ __global__ void __launch_bounds__(kAlThreads) attn_bwd_long_kernel(
 }
 
 // ---- the same backward on the tensor cores (warp-level mma.sync m16n8k16, bf16 operands, fp32 accumulation) ------
-// Block = 4 warps, one 64-key tile, walks the 64-row query tiles.  Warp w owns query rows 16w..16w+15 for S = Q K^T,
-// dP = dO V^T and dQ += dS K, and keys 16w..16w+15 of the tile for dV += P^T dO and dK += dS^T Q (accumulators in
-// registers over all query tiles).  Operand tiles live in shared memory as bf16 with padded rows (conflict-free fragment
-// loads); P and dS cross from the score layout to the transposed A operand through shared memory.  kSplit > 1 (d = 160)
-// gives a block only a slice of the output columns to bound the accumulators (the scores are recomputed per slice).
+// (The first version of this - 64-key tiles, 4 warps, a 32-bit shared-memory load per fragment register and 24 scalar
+//  atomics per thread and tile for dQ - ran a 64x64 layer at batch 8 in 3.78 ms; it is gone, the numbers are in
+//  profiles/r02_attention_bwd_probe.txt.)
 __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
-__device__ __forceinline__ uint32_t ld32(const __nv_bfloat16* p) { return *reinterpret_cast<const uint32_t*>(p); }
-__device__ __forceinline__ uint32_t ld16x2(const __nv_bfloat16* p0, const __nv_bfloat16* p1) {
-  return static_cast<uint32_t>(*reinterpret_cast<const uint16_t*>(p0)) |
-         (static_cast<uint32_t>(*reinterpret_cast<const uint16_t*>(p1)) << 16);
-}
 
-constexpr int kAmThreads = 128;
-constexpr int kAmPS = kAlT + 8;        // row pitch of the P / dS tiles (bf16 elements)
-
-template <int D, int kSplit>
-__global__ void __launch_bounds__(kAmThreads) attn_bwd_mma_kernel(
-    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
-    const __nv_bfloat16* __restrict__ dout, const float* __restrict__ lse, const float* __restrict__ delta,
-    float* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv, int q_len, int kv_len, int heads, long long ldq,
-    long long ldk, long long ldv, long long ldo, long long ldg, float scale, const uint8_t* __restrict__ key_mask) {
-  constexpr int DPAD = (D + 15) / 16 * 16;
-  constexpr int LD = DPAD + 8;                   // operand row pitch (bf16 elements)
-  constexpr int CW = DPAD / kSplit;              // output columns of this block
-  __shared__ uint8_t s_keep[kAlT];               // key mask of this block's 64 keys (1 = attended)
-  constexpr int NT = CW / 8;                     // 8-column accumulator tiles
-  static_assert(CW % 8 == 0, "column slice");
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);
-  __nv_bfloat16* sV = sK + kAlT * LD;
-  __nv_bfloat16* sQ = sV + kAlT * LD;
-  __nv_bfloat16* sO = sQ + kAlT * LD;
-  __nv_bfloat16* sP = sO + kAlT * LD;            // [64][kAmPS]
-  __nv_bfloat16* sS = sP + kAlT * kAmPS;
-  float* sL = reinterpret_cast<float*>(sS + kAlT * kAmPS);     // [64] lse, [64] delta
-  const int head = blockIdx.y, b = blockIdx.z;
-  const int k0 = (blockIdx.x / kSplit) * kAlT;
-  const int cs = (blockIdx.x % kSplit) * CW;     // first output column of this block
-  const int col0 = head * D;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-  const float scale_log2 = scale * 1.4426950408889634f;
-  const __nv_bfloat16 zero = __float2bfloat16(0.f);
-  // K, V tiles (rows past kv_len and the padding columns are zero)
-  for (int idx = tid; idx < kAlT * (DPAD / 8); idx += kAmThreads) {
-    const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
-    uint4 kk = make_uint4(0, 0, 0, 0), vv = kk;
-    if (k0 + r < kv_len && c8 < D) {
-      kk = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * kv_len + k0 + r) * ldk + col0 + c8);
-      vv = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * kv_len + k0 + r) * ldv + col0 + c8);
-    }
-    *reinterpret_cast<uint4*>(sK + r * LD + c8) = kk;
-    *reinterpret_cast<uint4*>(sV + r * LD + c8) = vv;
-  }
-  (void)zero;
-  if (tid < kAlT) s_keep[tid] = (key_mask == nullptr || k0 + tid >= kv_len) ? 1 : key_mask[static_cast<long long>(b) * kv_len + k0 + tid];
-  float acc_k[NT][4], acc_v[NT][4];
-#pragma unroll
-  for (int n = 0; n < NT; ++n)
-#pragma unroll
-    for (int e = 0; e < 4; ++e) acc_k[n][e] = acc_v[n][e] = 0.f;
-
-  for (int r0 = 0; r0 < q_len; r0 += kAlT) {
-    __syncthreads();                              // previous tile fully consumed
-    for (int idx = tid; idx < kAlT * (DPAD / 8); idx += kAmThreads) {
-      const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
-      uint4 qq = make_uint4(0, 0, 0, 0), oo = qq;
-      if (r0 + r < q_len && c8 < D) {
-        qq = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * q_len + r0 + r) * ldq + col0 + c8);
-        oo = *reinterpret_cast<const uint4*>(dout + (static_cast<long long>(b) * q_len + r0 + r) * ldo + col0 + c8);
-      }
-      *reinterpret_cast<uint4*>(sQ + r * LD + c8) = qq;
-      *reinterpret_cast<uint4*>(sO + r * LD + c8) = oo;
-    }
-    if (tid < kAlT) {
-      const bool ok = r0 + tid < q_len;
-      const long long li = (static_cast<long long>(b) * heads + head) * q_len + r0 + tid;
-      sL[tid] = ok ? lse[li] : 0.f;
-      sL[kAlT + tid] = ok ? delta[li] : 0.f;
-    }
-    __syncthreads();
-    // ---- S = Q K^T and dP = dO V^T for this warp's 16 rows x 64 keys
-    {
-      float s_acc[8][4], p_acc[8][4];
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) s_acc[j][e] = p_acc[j][e] = 0.f;
-      const __nv_bfloat16* qa = sQ + (16 * warp + g) * LD + 2 * t;
-      const __nv_bfloat16* oa = sO + (16 * warp + g) * LD + 2 * t;
-#pragma unroll
-      for (int kk = 0; kk < DPAD / 16; ++kk) {
-        uint32_t aq[4], ao[4];
-        aq[0] = ld32(qa + kk * 16); aq[1] = ld32(qa + 8 * LD + kk * 16); aq[2] = ld32(qa + kk * 16 + 8); aq[3] = ld32(qa + 8 * LD + kk * 16 + 8);
-        ao[0] = ld32(oa + kk * 16); ao[1] = ld32(oa + 8 * LD + kk * 16); ao[2] = ld32(oa + kk * 16 + 8); ao[3] = ld32(oa + 8 * LD + kk * 16 + 8);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const __nv_bfloat16* kb = sK + (8 * j + g) * LD + kk * 16 + 2 * t;
-          const __nv_bfloat16* vb = sV + (8 * j + g) * LD + kk * 16 + 2 * t;
-          mma_bf16_16816(s_acc[j], aq, ld32(kb), ld32(kb + 8));
-          mma_bf16_16816(p_acc[j], ao, ld32(vb), ld32(vb + 8));
-        }
-      }
-      // P and dS of the rows g and g + 8 of this warp's 16, columns 8 j + 2 t, + 1
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int r = 16 * warp + g + 8 * half;
-        const bool row_ok = r0 + r < q_len;
-        const float l2 = sL[r], dl = sL[kAlT + r];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int c = 8 * j + 2 * t;
-          float pr[2], ds[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const bool ok = row_ok && k0 + c + e < kv_len;
-            pr[e] = ok ? exp2f(s_acc[j][2 * half + e] * scale_log2 - l2) : 0.f;
-            ds[e] = pr[e] * (p_acc[j][2 * half + e] - dl) * scale;
-            if (s_keep[c + e] == 0) {
-              // masked key (attention.py:223-232, masked_fill after the scaling): its score is a constant, so no gradient
-              // reaches q / k through it; its probability is 0 unless the whole row is masked (the forward's lse is then
-              // the fill value itself and the row averages V uniformly)
-              pr[e] = (ok && l2 < -1.0e29f) ? 1.0f / static_cast<float>(kv_len) : 0.f;
-              ds[e] = 0.f;
-            }
-          }
-          *reinterpret_cast<uint32_t*>(sP + r * kAmPS + c) = pack_bf16x2(pr[0], pr[1]);
-          *reinterpret_cast<uint32_t*>(sS + r * kAmPS + c) = pack_bf16x2(ds[0], ds[1]);
-        }
-      }
-    }
-    __syncwarp();
-    // ---- dQ[16 rows][CW] = dS[16 x 64] K[64 x CW]  (this warp's own rows of dS)
-    {
-      float d_acc[NT][4];
-#pragma unroll
-      for (int n = 0; n < NT; ++n)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) d_acc[n][e] = 0.f;
-      const __nv_bfloat16* sa = sS + (16 * warp + g) * kAmPS + 2 * t;
-#pragma unroll
-      for (int kk = 0; kk < kAlT / 16; ++kk) {
-        uint32_t a[4];
-        a[0] = ld32(sa + kk * 16); a[1] = ld32(sa + 8 * kAmPS + kk * 16); a[2] = ld32(sa + kk * 16 + 8); a[3] = ld32(sa + 8 * kAmPS + kk * 16 + 8);
-        const __nv_bfloat16* kr = sK + (kk * 16 + 2 * t) * LD + cs + g;      // B[k = key][n = column]
-#pragma unroll
-        for (int n = 0; n < NT; ++n)
-          mma_bf16_16816(d_acc[n], a, ld16x2(kr + 8 * n, kr + LD + 8 * n), ld16x2(kr + 8 * LD + 8 * n, kr + 9 * LD + 8 * n));
-      }
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int r = r0 + 16 * warp + g + 8 * half;
-        if (r < q_len) {
-          float* dst = dq + (static_cast<long long>(b) * q_len + r) * ldg + col0;
-#pragma unroll
-          for (int n = 0; n < NT; ++n) {
-            const int c = cs + 8 * n + 2 * t;
-            if (c < D) atomicAdd(dst + c, d_acc[n][2 * half]);
-            if (c + 1 < D) atomicAdd(dst + c + 1, d_acc[n][2 * half + 1]);
-          }
-        }
-      }
-    }
-    __syncthreads();                              // every warp's P and dS rows are in shared memory
-    // ---- dV[16 keys][CW] += P^T dO,  dK[16 keys][CW] += dS^T Q  (keys 16 w .. of the tile; A = transposed tiles)
-#pragma unroll
-    for (int kk = 0; kk < kAlT / 16; ++kk) {
-      const __nv_bfloat16* pr = sP + (kk * 16 + 2 * t) * kAmPS + 16 * warp + g;     // A[m = key][k = row] = P[row][key]
-      const __nv_bfloat16* sr = sS + (kk * 16 + 2 * t) * kAmPS + 16 * warp + g;
-      uint32_t ap[4], as[4];
-      ap[0] = ld16x2(pr, pr + kAmPS); ap[1] = ld16x2(pr + 8, pr + kAmPS + 8);
-      ap[2] = ld16x2(pr + 8 * kAmPS, pr + 9 * kAmPS); ap[3] = ld16x2(pr + 8 * kAmPS + 8, pr + 9 * kAmPS + 8);
-      as[0] = ld16x2(sr, sr + kAmPS); as[1] = ld16x2(sr + 8, sr + kAmPS + 8);
-      as[2] = ld16x2(sr + 8 * kAmPS, sr + 9 * kAmPS); as[3] = ld16x2(sr + 8 * kAmPS + 8, sr + 9 * kAmPS + 8);
-      const __nv_bfloat16* orow = sO + (kk * 16 + 2 * t) * LD + cs + g;              // B[k = row][n = column]
-      const __nv_bfloat16* qrow = sQ + (kk * 16 + 2 * t) * LD + cs + g;
-#pragma unroll
-      for (int n = 0; n < NT; ++n) {
-        mma_bf16_16816(acc_v[n], ap, ld16x2(orow + 8 * n, orow + LD + 8 * n), ld16x2(orow + 8 * LD + 8 * n, orow + 9 * LD + 8 * n));
-        mma_bf16_16816(acc_k[n], as, ld16x2(qrow + 8 * n, qrow + LD + 8 * n), ld16x2(qrow + 8 * LD + 8 * n, qrow + 9 * LD + 8 * n));
-      }
-    }
-  }
-#pragma unroll
-  for (int half = 0; half < 2; ++half) {
-    const int key = k0 + 16 * warp + g + 8 * half;
-    if (key < kv_len) {
-      const long long o = (static_cast<long long>(b) * kv_len + key) * ldg + col0;
-#pragma unroll
-      for (int n = 0; n < NT; ++n) {
-        const int c = cs + 8 * n + 2 * t;
-        if (c < D) {
-          dk[o + c] = acc_k[n][2 * half];
-          dv[o + c] = acc_v[n][2 * half];
-        }
-        if (c + 1 < D) {
-          dk[o + c + 1] = acc_k[n][2 * half + 1];
-          dv[o + c + 1] = acc_v[n][2 * half + 1];
-        }
-      }
-    }
-  }
-}
-
-template <int D, int kSplit>
-int launch_attn_bwd_mma(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
-                        long long ldg, cudaStream_t stream) {
-  constexpr int DPAD = (D + 15) / 16 * 16;
-  const size_t sh = (4 * static_cast<size_t>(kAlT) * (DPAD + 8) + 2 * static_cast<size_t>(kAlT) * kAmPS) * 2 + 2 * kAlT * sizeof(float);
-  auto kern = attn_bwd_mma_kernel<D, kSplit>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sh)));
-    attr_set = true;
-  }
-  dim3 grid(((a.kv_len + kAlT - 1) / kAlT) * kSplit, a.heads, a.batch);
-  kern<<<grid, kAmThreads, sh, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
-                                         reinterpret_cast<const __nv_bfloat16*>(a.v), dout, a.lse, delta, dq, dk, dv, a.q_len,
-                                         a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale, a.key_mask);
-  return 0;
-}
-
-// ---- second tensor-core version (the default): 128-key tiles, 8 warps, every fragment through ldmatrix ----------------
-// The first version spends its issue slots on shared-memory loads (a 32-bit load per A / B register, two 16-bit loads per
-// transposed one: ~490 loads for 120 MMAs per warp and tile) and sends 24 scalar fp32 atomics per thread and tile to dQ.
+// ---- 128-key tiles, 8 warps, every fragment through ldmatrix (AFB_ATTN_BWD=mma2; the default at d = 160) -----------
+// The first version spent its issue slots on shared-memory loads (a 32-bit load per A / B register, two 16-bit loads per
+// transposed one: ~490 loads for 120 MMAs per warp and tile) and sent 24 scalar fp32 atomics per thread and tile to dQ.
 // Here: K / V of 128 keys stay resident, the 64-row Q / dO tiles (+ lse, delta) arrive through a cp.async double buffer
 // while the previous tile computes, all operand fragments come from ldmatrix / ldmatrix.trans (78 loads per warp and
 // tile), P = 2^(s - lse) on ex2.approx, and dQ leaves as red.global.add.v2.f32 - 8x fewer atomic instructions per key.
@@ -1486,6 +1270,279 @@ int launch_attn_bwd_mma2(const afb_attn_args& a, const __nv_bfloat16* dout, cons
   return 0;
 }
 
+// ---- third version (the default): the scores are computed TRANSPOSED, so P^T and dS^T never leave the registers -------
+// ncu on the version above: the shared-memory data pipe is 88 % busy with (almost conflict-free) ldmatrix wavefronts -
+// 352 per warp and tile - while the HMMA pipe idles at 42 %.  Here warp w owns keys 16 w .. for everything but dQ:
+// S^T = K Q^T and dP^T = V dO^T take their A operand (the warp's 16 keys of K / V) from fragments that are loaded ONCE
+// per block and stay in registers, and their accumulators (m = key, n = query row) have exactly the layout of the A
+// operand of dV += P^T dO and dK += dS^T Q, so P^T and dS^T go from accumulators to MMA operands through a bf16 pack -
+// no P tile in shared memory, no transposed re-read.  Only dS^T is written out ([key][row], 16 stores per thread) for
+// dQ = dS K, which reads it back transposed as before.  The 64-row tile is walked in 16-row steps (one k16 step of the
+// dV / dK MMAs) to bound the registers.  Per warp and tile: ~300 shared-memory wavefronts instead of ~390.
+constexpr int kA3TS = kA2Rows + 8;       // row pitch of the dS^T tile (bf16): 144 B, conflict-free ldmatrix rows
+
+template <int D, int kSplit>
+struct A3Cfg {
+  static constexpr int DPAD = (D + 15) / 16 * 16;
+  static constexpr int LD = DPAD + 8;
+  static constexpr int CW = DPAD / kSplit;
+  static constexpr int NT = CW / 8;
+  static constexpr int NTQ = CW / 16;
+  static constexpr int KK = DPAD / 16;
+  static constexpr bool kKeepKV = DPAD <= 80;       // K / V fragments of the warp's keys stay in registers
+  static constexpr int kUnroll = DPAD <= 48 ? 4 : 1;  // 16-row steps unrolled where the registers allow (d = 40: 128)
+  static constexpr int kStages = DPAD <= 80 ? 2 : 1;
+  static constexpr int kMinBlocks = DPAD <= 48 ? 2 : 1;
+  static constexpr size_t kSmem = (static_cast<size_t>(2 * kA2Keys + kStages * 2 * kA2Rows) * LD + kA2Keys * kA3TS) * 2 +
+                                  static_cast<size_t>(kStages) * 2 * kA2Rows * sizeof(float);
+  static_assert(CW % 16 == 0 && NT % 2 == 0, "column slice");
+  static_assert(kSmem <= 227 * 1024, "shared memory budget");
+};
+
+template <int D, int kSplit>
+__global__ void __launch_bounds__(kA2Threads, A3Cfg<D, kSplit>::kMinBlocks) attn_bwd_mma3_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ v,
+    const __nv_bfloat16* __restrict__ dout, const float* __restrict__ lse, const float* __restrict__ delta,
+    float* __restrict__ dq, float* __restrict__ dk, float* __restrict__ dv, int q_len, int kv_len, int heads, long long ldq,
+    long long ldk, long long ldv, long long ldo, long long ldg, float scale, const uint8_t* __restrict__ key_mask) {
+  using C = A3Cfg<D, kSplit>;
+  constexpr int DPAD = C::DPAD, LD = C::LD, CW = C::CW, NT = C::NT, NTQ = C::NTQ, NS = C::kStages, KK = C::KK;
+  constexpr int TS = kA3TS;
+  __shared__ uint8_t s_keep[kA2Keys];
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);      // [128][LD]
+  __nv_bfloat16* sV = sK + kA2Keys * LD;
+  __nv_bfloat16* sQ = sV + kA2Keys * LD;                               // [NS][64][LD]
+  __nv_bfloat16* sO = sQ + NS * kA2Rows * LD;                          // [NS][64][LD]  dO tiles
+  __nv_bfloat16* sT = sO + NS * kA2Rows * LD;                          // [128][TS]     dS^T: [key][row]
+  float* sL = reinterpret_cast<float*>(sT + kA2Keys * TS);             // [NS][lse 64 | delta 64]
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int k0 = (blockIdx.x / kSplit) * kA2Keys;
+  const int cs = (blockIdx.x % kSplit) * CW;
+  const int col0 = head * D;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int rw = warp & 3, kh = warp >> 2;
+  const float scale_log2 = scale * 1.4426950408889634f;
+  const bool has_mask = key_mask != nullptr;
+  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8, la_col = (lane >> 4) * 8;     // see attn_bwd_mma2_kernel
+  const int lb_row = (lane & 7) + (lane >> 4) * 8, lb_col = ((lane >> 3) & 1) * 8;
+  auto issue_tile = [&](int it, int stage) {
+    const int r0 = it * kA2Rows;
+    const uint32_t uq = smem_u32(sQ + stage * kA2Rows * LD), uo = smem_u32(sO + stage * kA2Rows * LD);
+    for (int idx = tid; idx < kA2Rows * (DPAD / 8); idx += kA2Threads) {
+      const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+      const bool ok = r0 + r < q_len && c8 < D;
+      const long long row = static_cast<long long>(b) * q_len + (ok ? r0 + r : 0);
+      const int cc = ok ? c8 : 0;
+      bw_cp_async16(uq + (r * LD + c8) * 2, q + row * ldq + col0 + cc, ok);
+      bw_cp_async16(uo + (r * LD + c8) * 2, dout + row * ldo + col0 + cc, ok);
+    }
+    if (tid < 2 * kA2Rows) {
+      const int r = tid & (kA2Rows - 1);
+      const bool ok = r0 + r < q_len;
+      const long long li = (static_cast<long long>(b) * heads + head) * q_len + (ok ? r0 + r : 0);
+      bw_cp_async4(smem_u32(sL + stage * 2 * kA2Rows + tid), (tid < kA2Rows ? lse : delta) + li, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (NS == 2) issue_tile(0, 0);
+  for (int idx = tid; idx < kA2Keys * (DPAD / 8); idx += kA2Threads) {
+    const int r = idx / (DPAD / 8), c8 = (idx % (DPAD / 8)) * 8;
+    uint4 kk4 = make_uint4(0, 0, 0, 0), vv4 = kk4;
+    if (k0 + r < kv_len && c8 < D) {
+      kk4 = *reinterpret_cast<const uint4*>(k + (static_cast<long long>(b) * kv_len + k0 + r) * ldk + col0 + c8);
+      vv4 = *reinterpret_cast<const uint4*>(v + (static_cast<long long>(b) * kv_len + k0 + r) * ldv + col0 + c8);
+    }
+    *reinterpret_cast<uint4*>(sK + r * LD + c8) = kk4;
+    *reinterpret_cast<uint4*>(sV + r * LD + c8) = vv4;
+  }
+  if (tid < kA2Keys)
+    s_keep[tid] = (!has_mask || k0 + tid >= kv_len) ? 1 : key_mask[static_cast<long long>(b) * kv_len + k0 + tid];
+  float acc_k[NT][4], acc_v[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; ++n)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc_k[n][e] = acc_v[n][e] = 0.f;
+  const uint32_t uK = smem_u32(sK), uV = smem_u32(sV), uT = smem_u32(sT);
+  __syncthreads();                                // K / V / s_keep visible
+  // this warp's 16 keys of K and V as A fragments (m = key, k = channel)
+  uint32_t fk[C::kKeepKV ? KK : 1][4], fv[C::kKeepKV ? KK : 1][4];
+  if constexpr (C::kKeepKV) {
+#pragma unroll
+    for (int kk = 0; kk < KK; ++kk) {
+      const uint32_t a_off = ((16 * warp + la_row) * LD + kk * 16 + la_col) * 2;
+      bw_ldsm_x4(fk[kk], uK + a_off);
+      bw_ldsm_x4(fv[kk], uV + a_off);
+    }
+  }
+  const int key_lo = 16 * warp + g;               // this thread's accumulator rows: keys key_lo and key_lo + 8 of the tile
+  const bool kvalid[2] = {k0 + key_lo < kv_len, k0 + key_lo + 8 < kv_len};
+  const bool kkeep[2] = {s_keep[key_lo] != 0, s_keep[key_lo + 8] != 0};
+  const bool keys_full = k0 + kA2Keys <= kv_len && !has_mask;
+  const float inv_kv = 1.0f / static_cast<float>(kv_len);
+
+  const int n_tiles = (q_len + kA2Rows - 1) / kA2Rows;
+  for (int it = 0; it < n_tiles; ++it) {
+    const int st = NS == 2 ? (it & 1) : 0;
+    const int r0 = it * kA2Rows;
+    if (NS == 1) {
+      __syncthreads();                            // the single stage is consumed
+      issue_tile(it, 0);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                              // tile `it` visible; tile it-1 (and its dS^T) fully consumed
+    if (NS == 2 && it + 1 < n_tiles) issue_tile(it + 1, st ^ 1);
+    const uint32_t uQ = smem_u32(sQ + st * kA2Rows * LD), uO = smem_u32(sO + st * kA2Rows * LD);
+    const float* tl = sL + st * 2 * kA2Rows;
+    const bool full = keys_full && r0 + kA2Rows <= q_len;
+#pragma unroll(C::kUnroll)
+    for (int s16 = 0; s16 < kA2Rows / 16; ++s16) {
+      // ---- S^T = K Q^T, dP^T = V dO^T: keys 16 w .. x rows 16 s16 ..
+      float st_acc[2][4], dp_acc[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) st_acc[j][e] = dp_acc[j][e] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < KK; ++kk) {
+        uint32_t bq[4], bo[4];
+        const uint32_t b_off = ((16 * s16 + lb_row) * LD + kk * 16 + lb_col) * 2;       // B: n = row, k = channel
+        bw_ldsm_x4(bq, uQ + b_off);
+        bw_ldsm_x4(bo, uO + b_off);
+        if constexpr (C::kKeepKV) {
+          mma_bf16_16816(st_acc[0], fk[kk], bq[0], bq[1]);
+          mma_bf16_16816(st_acc[1], fk[kk], bq[2], bq[3]);
+          mma_bf16_16816(dp_acc[0], fv[kk], bo[0], bo[1]);
+          mma_bf16_16816(dp_acc[1], fv[kk], bo[2], bo[3]);
+        } else {
+          uint32_t ak[4], av[4];
+          const uint32_t a_off = ((16 * warp + la_row) * LD + kk * 16 + la_col) * 2;
+          bw_ldsm_x4(ak, uK + a_off);
+          bw_ldsm_x4(av, uV + a_off);
+          mma_bf16_16816(st_acc[0], ak, bq[0], bq[1]);
+          mma_bf16_16816(st_acc[1], ak, bq[2], bq[3]);
+          mma_bf16_16816(dp_acc[0], av, bo[0], bo[1]);
+          mma_bf16_16816(dp_acc[1], av, bo[2], bo[3]);
+        }
+      }
+      // ---- P^T, dS^T: accumulator element (j, 2 half + e) = key key_lo + 8 half, row 16 s16 + 8 j + 2 t + e
+      uint32_t ap[4], as[4];                      // A fragments of the dV / dK MMAs: index 2 j + half
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int r = 16 * s16 + 8 * j + 2 * t;
+        const float2 l2 = *reinterpret_cast<const float2*>(tl + r);
+        const float2 dl = *reinterpret_cast<const float2*>(tl + kA2Rows + r);
+        const bool rok[2] = {r0 + r < q_len, r0 + r + 1 < q_len};
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float pr[2], ds[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const float le = e ? l2.y : l2.x, de = e ? dl.y : dl.x;
+            const bool ok = full || (rok[e] && kvalid[half]);
+            pr[e] = ok ? ex2_approx(fmaf(st_acc[j][2 * half + e], scale_log2, -le)) : 0.f;
+            ds[e] = pr[e] * (dp_acc[j][2 * half + e] - de) * scale;
+            if (has_mask && !kkeep[half]) {
+              // masked key (attention.py:223-232, masked_fill after the scaling): its score is a constant, so no gradient
+              // reaches q / k through it; its probability is 0 unless the whole row is masked (the forward's lse is then
+              // the fill value itself and the row averages V uniformly)
+              pr[e] = (ok && le < -1.0e29f) ? inv_kv : 0.f;
+              ds[e] = 0.f;
+            }
+          }
+          ap[2 * j + half] = pack_bf16x2(pr[0], pr[1]);
+          as[2 * j + half] = pack_bf16x2(ds[0], ds[1]);
+          *reinterpret_cast<uint32_t*>(sT + (key_lo + 8 * half) * TS + r) = as[2 * j + half];
+        }
+      }
+      // ---- dV[16 keys][CW] += P^T dO,  dK[16 keys][CW] += dS^T Q over these 16 rows (one k16 step)
+#pragma unroll
+      for (int n = 0; n < NT; n += 2) {
+        uint32_t bo[4], bq[4];
+        const uint32_t b_off = ((16 * s16 + la_row) * LD + cs + 8 * n + la_col) * 2;    // B: k = row, n = channel
+        bw_ldsm_x4_t(bo, uO + b_off);
+        bw_ldsm_x4_t(bq, uQ + b_off);
+        mma_bf16_16816(acc_v[n], ap, bo[0], bo[1]);
+        mma_bf16_16816(acc_v[n + 1], ap, bo[2], bo[3]);
+        mma_bf16_16816(acc_k[n], as, bq[0], bq[1]);
+        mma_bf16_16816(acc_k[n + 1], as, bq[2], bq[3]);
+      }
+    }
+    __syncthreads();                              // dS^T of the whole tile is in shared memory
+    // ---- dQ[16 rows][CW / 2] = dS[16 x 128] K[128 x CW / 2]: rows 16 rw .., column half kh
+    {
+      float d_acc[NTQ][4];
+#pragma unroll
+      for (int n = 0; n < NTQ; ++n)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) d_acc[n][e] = 0.f;
+      const int cq = cs + kh * (CW / 2);
+#pragma unroll
+      for (int kk = 0; kk < kA2Keys / 16; ++kk) {
+        uint32_t a[4];
+        bw_ldsm_x4_t(a, uT + ((kk * 16 + lb_row) * TS + 16 * rw + lb_col) * 2);           // A: k = key, m = row
+#pragma unroll
+        for (int n = 0; n < NTQ; n += 2) {
+          if (n + 1 < NTQ) {
+            uint32_t bb[4];
+            bw_ldsm_x4_t(bb, uK + ((kk * 16 + la_row) * LD + cq + 8 * n + la_col) * 2);
+            mma_bf16_16816(d_acc[n], a, bb[0], bb[1]);
+            mma_bf16_16816(d_acc[n + 1 < NTQ ? n + 1 : n], a, bb[2], bb[3]);
+          } else {
+            uint32_t b0, b1;
+            bw_ldsm_x2_t(b0, b1, uK + ((kk * 16 + la_row) * LD + cq + 8 * n) * 2);
+            mma_bf16_16816(d_acc[n], a, b0, b1);
+          }
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int r = r0 + 16 * rw + g + 8 * half;
+        if (r < q_len) {
+          float* dst = dq + (static_cast<long long>(b) * q_len + r) * ldg + col0;
+#pragma unroll
+          for (int n = 0; n < NTQ; ++n) {
+            const int c = cq + 8 * n + 2 * t;
+            if (c < D) bw_red_add_v2(dst + c, d_acc[n][2 * half], d_acc[n][2 * half + 1]);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int key = k0 + key_lo + 8 * half;
+    if (key < kv_len) {
+      const long long o = (static_cast<long long>(b) * kv_len + key) * ldg + col0;
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        const int c = cs + 8 * n + 2 * t;
+        if (c < D) {
+          *reinterpret_cast<float2*>(dk + o + c) = make_float2(acc_k[n][2 * half], acc_k[n][2 * half + 1]);
+          *reinterpret_cast<float2*>(dv + o + c) = make_float2(acc_v[n][2 * half], acc_v[n][2 * half + 1]);
+        }
+      }
+    }
+  }
+}
+
+template <int D, int kSplit>
+int launch_attn_bwd_mma3(const afb_attn_args& a, const __nv_bfloat16* dout, const float* delta, float* dq, float* dk, float* dv,
+                         long long ldg, cudaStream_t stream) {
+  using C = A3Cfg<D, kSplit>;
+  auto kern = attn_bwd_mma3_kernel<D, kSplit>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(C::kSmem)));
+    attr_set = true;
+  }
+  dim3 grid(((a.kv_len + kA2Keys - 1) / kA2Keys) * kSplit, a.heads, a.batch);
+  kern<<<grid, kA2Threads, C::kSmem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.q), reinterpret_cast<const __nv_bfloat16*>(a.k),
+                                               reinterpret_cast<const __nv_bfloat16*>(a.v), dout, a.lse, delta, dq, dk, dv, a.q_len,
+                                               a.kv_len, a.heads, a.ldq, a.ldk, a.ldv, a.ldo, ldg, a.scale, a.key_mask);
+  return 0;
+}
+
 // ---- the short-key backward (cross-attention, 77 keys) on tensor cores -------------------------------------------------
 // All keys of a head fit one tile (80 = 10 n8 tiles), so the softmax of a row is complete inside the warp that owns it:
 // block (row chunk, head, sample) = 5 warps walks 80-row query tiles; warp w computes S = Q K^T and dP = dO V^T of rows
@@ -1749,14 +1806,14 @@ int launch_attn_bwd_short_mma(const afb_attn_args& a, const __nv_bfloat16* dout,
   return 0;
 }
 
-// AFB_ATTN_BWD: unset = the 128-key ldmatrix version; "mma1" = the first tensor-core version, "simt" = the CUDA-core
+// AFB_ATTN_BWD: unset = the transposed-score version (mma3); "mma2" = the 128-key ldmatrix version, "simt" = the CUDA-core
 // version (A/B measurement and cross-check); read once
-int attn_bwd_mode() {      // 2 = mma2, 1 = mma1, 0 = simt
+int attn_bwd_mode() {      // 3 = mma3 (default), 2 = mma2, 0 = simt
   static const int mode = [] {
     const char* e = getenv("AFB_ATTN_BWD");
-    if (e == nullptr) return 2;
+    if (e == nullptr) return 3;
     if (e[0] == 's') return 0;
-    return (e[0] == 'm' && e[1] == 'm' && e[2] == 'a' && e[3] == '1') ? 1 : 2;
+    return (e[0] == 'm' && e[1] == 'm' && e[2] == 'a' && e[3] == '2') ? 2 : 3;
   }();
   return mode;
 }
@@ -1802,8 +1859,8 @@ extern "C" int afb_attention_bwd_short(const afb_attn_args* args, const afb_bf16
   __nv_bfloat16* dqb = reinterpret_cast<__nv_bfloat16*>(dq);
   int rc;
   // the tensor-core version: up to 80 keys, 16-byte vector loads, bf16x2 dQ stores, 8-byte vector atomics for dK / dV
-  // (AFB_ATTN_BWD=simt or mma1 keeps the CUDA-core version for the A/B measurement)
-  const bool mma = attn_bwd_mode() == 2 && a.kv_len <= kAsKeys && a.head_dim % 8 == 0 &&
+  // (AFB_ATTN_BWD=simt keeps the CUDA-core version for the A/B measurement)
+  const bool mma = attn_bwd_mode() >= 2 && a.kv_len <= kAsKeys && a.head_dim % 8 == 0 &&
                    ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |
                      reinterpret_cast<uintptr_t>(dout)) & 15) == 0 &&
                    a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0 && a.ldo % 8 == 0 && lddk % 2 == 0 &&
@@ -1855,15 +1912,16 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
   const bool vec_ok = ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |
                         reinterpret_cast<uintptr_t>(dout)) & 15) == 0 &&
                       a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0;
-  const bool mma = (attn_bwd_mode() != 0 || a.key_mask != nullptr) && vec_ok;
-  AFB_REQUIRE(a.key_mask == nullptr || mma, "afb_attention_bwd: the key-masked backward needs 16-byte aligned operands");
-  // the 128-key version sends dQ as 8-byte vector atomics and stores dK / dV as float2
-  const bool mma2 = mma && attn_bwd_mode() == 2 && ldg % 2 == 0 &&
+  // the tensor-core versions read 16-byte vectors, send dQ as 8-byte vector atomics and store dK / dV as float2
+  const bool mma2 = (attn_bwd_mode() != 0 || a.key_mask != nullptr) && vec_ok && ldg % 2 == 0 &&
                     ((reinterpret_cast<uintptr_t>(dq) | reinterpret_cast<uintptr_t>(dk) | reinterpret_cast<uintptr_t>(dv)) & 7) == 0;
+  AFB_REQUIRE(a.key_mask == nullptr || mma2, "afb_attention_bwd: the key-masked backward needs 16-byte aligned operands, "
+              "8-byte aligned gradients and an even ldg");
+  const bool mma3 = mma2 && attn_bwd_mode() == 3 && a.head_dim <= 80;      // (d = 160 reloads its K / V fragments: 72 vs 68 us)
 #define AFB_BWD_CASE(DIM, SPLIT)                                                                                \
   case DIM:                                                                                                     \
-    rc = mma2 ? launch_attn_bwd_mma2<DIM, SPLIT>(a, db, delta_ws, dq, dk, dv, ldg, stream)                      \
-       : mma  ? launch_attn_bwd_mma<DIM, SPLIT>(a, db, delta_ws, dq, dk, dv, ldg, stream)                       \
+    rc = mma3 ? launch_attn_bwd_mma3<DIM, SPLIT>(a, db, delta_ws, dq, dk, dv, ldg, stream)                      \
+       : mma2 ? launch_attn_bwd_mma2<DIM, SPLIT>(a, db, delta_ws, dq, dk, dv, ldg, stream)                      \
               : launch_attn_bwd_long<DIM>(a, db, delta_ws, dq, dk, dv, ldg, stream);                            \
     break;
   switch (a.head_dim) {

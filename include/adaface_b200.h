@@ -334,7 +334,7 @@ int afb_ada_pool_prep_bwd(const float* proj_ws, const float* lora_to_fg_q, const
 /* Second stage: what carries a layer's gradient further down the U-Net.
  * afb_attention_bwd: any key length (self-attention), no key mask.  args as in the forward call that produced args->out
  *   and args->lse (both required); dout bf16 with the row pitch of out (ldo); delta_ws fp32 [B * heads * q_len];
- *   dq (zeroed inside), dk, dv fp32 [B * len, ldg].  Warp-level tensor-core MMAs (mma.sync), 128-key tiles; a key mask
+ *   dq (zeroed inside), dk, dv fp32 [B * len, ldg].  Warp-level tensor-core MMAs (mma.sync), 128-key tiles, scores computed transposed; a key mask
  *   (args->key_mask) is honoured as in the forward.
  * afb_groupnorm_tokens_bwd: token-major bf16 x / grad_y [B, HW, C] -> dx bf16.  act = 0: plain GroupNorm (the
  *   SpatialTransformer's Normalize, attention.py:71-72); act = 1: GroupNorm -> SiLU (the ResBlocks, openaimodel.py:259-279;

@@ -72,7 +72,7 @@ def ada_cases():
 
 
 def attn_bwd_cases():
-    """Self-attention backward of the inversion step (batch 8, SD-1.5 head sizes); AFB_ATTN_BWD=mma1 / simt select the
+    """Self-attention backward of the inversion step (batch 8, SD-1.5 head sizes); AFB_ATTN_BWD=mma2 / simt select the
     earlier versions (read once per process)."""
     import os
     d = "cuda"
@@ -84,11 +84,11 @@ def attn_bwd_cases():
         dout = torch.randn(b, n, c, device=d).to(torch.bfloat16)
         us = timed(lambda: ops.attention_bwd(q, k, v, out, lse, dout, heads, dh ** -0.5), n=3, reps=3)
         fl = 10.0 * b * n * n * c
-        print(f"attention_bwd[{os.environ.get('AFB_ATTN_BWD', 'mma2')}] b{b} n{n} d{dh}: {us:9.1f} us  {fl / us / 1e6:7.1f} TFLOP/s")
+        print(f"attention_bwd[{os.environ.get('AFB_ATTN_BWD', 'mma3')}] b{b} n{n} d{dh}: {us:9.1f} us  {fl / us / 1e6:7.1f} TFLOP/s")
         kc = (torch.randn(b, 77, 2 * c, device=d) * 0.5).to(torch.bfloat16)
         us = timed(lambda: ops.attention_bwd_short(q, kc[..., :c], kc[..., c:], dout, heads, dh ** -0.5, True), n=3, reps=3)
         fl = 10.0 * b * n * 77 * c
-        print(f"attention_bwd_short[{os.environ.get('AFB_ATTN_BWD', 'mma2')}] b{b} n{n} k77 d{dh}: {us:9.1f} us  {fl / us / 1e6:7.1f} TFLOP/s")
+        print(f"attention_bwd_short[{os.environ.get('AFB_ATTN_BWD', 'mma3')}] b{b} n{n} k77 d{dh}: {us:9.1f} us  {fl / us / 1e6:7.1f} TFLOP/s")
 
 
 if __name__ == "__main__":

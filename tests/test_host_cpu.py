@@ -49,7 +49,7 @@ def test_sass_contains_blackwell_tensor_and_tma_instructions():
     assert "UTMALDG" in sass
     assert "LDTM" in sass
     # warp-level mma.sync is allowed off the default forward path only: the self-attention backward of the inversion step
-    # (csrc/backward.cu attn_bwd_mma_kernel / attn_bwd_mma2_kernel / attn_bwd_short_mma_kernel), the U-Net's last convolution, 320 -> 4 channels, whose 4 output columns cannot
+    # (csrc/backward.cu attn_bwd_mma3_kernel / attn_bwd_mma2_kernel / attn_bwd_short_mma_kernel), the U-Net's last convolution, 320 -> 4 channels, whose 4 output columns cannot
     # feed a 128-row tcgen05 tile (csrc/conv_small.cu), and the explicit (materialised-score) cross-attention of the
     # save_attn_vars / conv-attention modes (csrc/attn_explicit.cu); every GEMM / attention kernel of the default path
     # must be tcgen05
@@ -60,7 +60,7 @@ def test_sass_contains_blackwell_tensor_and_tma_instructions():
             legacy.add(name.strip())
     # (+ the AdaEmbedding pooling kernel: [tokens x C] x [C x 16] and [C x tokens] x [tokens x 8] contractions, far too
     #  skinny for a 128 x N tcgen05 tile)
-    allowed = ("attn_bwd_mma_kernel", "attn_bwd_mma2_kernel", "attn_bwd_short_mma_kernel", "conv3x3_few_out_kernel", "cross_scores_kernel", "softmax_pv_kernel", "ada_pool_mma_kernel")
+    allowed = ("attn_bwd_mma2_kernel", "attn_bwd_mma3_kernel", "attn_bwd_short_mma_kernel", "conv3x3_few_out_kernel", "cross_scores_kernel", "softmax_pv_kernel", "ada_pool_mma_kernel")
     assert legacy and all(any(a in n for a in allowed) for n in legacy), legacy
 
 
