@@ -233,8 +233,7 @@ class CrossAttention(nn.Module, _PackedWeights):
         p = self.packed()
         inner = p["wq"].shape[0]
         qkv = ops.linear(x.view(b * n, c), p["wqkv"], None, None, False).view(b, n, 3 * inner)
-        a = ops.attention_auto(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
-                          key_mask)
+        a = ops.self_attention_auto(qkv, self.heads, self.scale, key_mask)
         return ops.linear(a.view(b * n, inner), p["wo"], p["bo"], residual, False)
 
     def out_projection(self, a2d: Tensor, residual: Optional[Tensor], want_stats: bool = False):
@@ -249,8 +248,7 @@ class CrossAttention(nn.Module, _PackedWeights):
         self._check_modes(None, False)
         b, n, w3 = qkv.shape
         inner = w3 // 3
-        a = ops.attention_auto(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads, self.scale,
-                          key_mask)
+        a = ops.self_attention_auto(qkv, self.heads, self.scale, key_mask)
         return a.view(b * n, inner)
 
     def project_query(self, x: Tensor) -> Tensor:

@@ -1906,7 +1906,11 @@ extern "C" int afb_attention_bwd(const afb_attn_args* args, const afb_bf16* dout
                                                                                 delta_ws, rows, a.q_len, a.heads, a.head_dim,
                                                                                 a.ldo, a.ldo);
   count_launch();
-  AFB_CHECK_CUDA(cudaMemsetAsync(dq, 0, static_cast<size_t>(rows) * ldg * sizeof(float), stream));
+  // dQ is accumulated with atomics: zero its `width` columns of every row (dq / dk / dv may be column blocks of one
+  // [rows, 3 C] gradient buffer with ldg = 3 C: only the dQ block is cleared)
+  if (ldg == width) AFB_CHECK_CUDA(cudaMemsetAsync(dq, 0, static_cast<size_t>(rows) * ldg * sizeof(float), stream));
+  else AFB_CHECK_CUDA(cudaMemset2DAsync(dq, static_cast<size_t>(ldg) * sizeof(float), 0, static_cast<size_t>(width) * sizeof(float),
+                                        static_cast<size_t>(rows), stream));
   int rc;
   // the tensor-core version reads its operands with 16-byte vector loads
   const bool vec_ok = ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) | reinterpret_cast<uintptr_t>(a.v) |

@@ -1280,6 +1280,76 @@ def _(q, k, v, out, lse, dout, heads, scale, key_mask=None):
     return f(q), f(k), f(v)
 
 
+@torch.library.custom_op("adaface_b200::self_attention_qkv", mutates_args=())
+def self_attention_qkv(qkv: Tensor, heads: int, scale: float, key_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+    """Self-attention on the fused projection buffer qkv bf16 [B, N, 3C] (q | k | v column blocks) -> (out bf16 [B, N, C],
+    lse).  Same kernels as `attention_lse` on the three column slices; the point is the backward: ONE gradient tensor of
+    qkv's shape written in place by the attention backward (row pitch 3C), where slicing would have autograd zero-fill
+    three qkv-sized buffers, copy the three slices in and add them up."""
+    c = qkv.shape[2] // 3
+    return attention_lse(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], heads, scale, key_mask)
+
+
+@self_attention_qkv.register_fake
+def _(qkv, heads, scale, key_mask=None):
+    b, n, c3 = qkv.shape
+    return qkv.new_empty((b, n, c3 // 3), dtype=torch.bfloat16), qkv.new_empty((b, heads, n), dtype=torch.float32)
+
+
+@torch.library.custom_op("adaface_b200::self_attention_qkv_bwd", mutates_args=())
+def self_attention_qkv_bwd(qkv: Tensor, out: Tensor, lse: Tensor, dout: Tensor, heads: int, scale: float,
+                           key_mask: Optional[Tensor] = None) -> Tensor:
+    """Backward of `self_attention_qkv`: d_qkv bf16 [B, N, 3C] (dq | dk | dv written by afb_attention_bwd with ldg = 3C)."""
+    _need_cuda(qkv, out, lse, dout)
+    b, n, c3 = qkv.shape
+    c = c3 // 3
+    out, dout, lse = out.contiguous(), dout.contiguous(), lse.contiguous()
+    if dout.dtype != torch.bfloat16 or dout.shape != (b, n, c) or out.shape != (b, n, c) or qkv.stride(2) != 1 or qkv.stride(1) < c3:
+        raise ValueError("self_attention_qkv_bwd: bf16 out / dout [B, N, C] and a row-contiguous qkv [B, N, 3C] expected")
+    dev = qkv.device
+    d = torch.empty((b, n, c3), dtype=torch.float32, device=dev)
+    ws = torch.empty((b * heads * n,), dtype=torch.float32, device=dev)
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
+    ld = _ld3(qkv, "qkv")
+    base = qkv.data_ptr()
+    args = AttnArgs(q=base, k=base + 2 * c, v=base + 4 * c, out=_ptr(out), key_mask=_ptr(key_mask), batch=b, heads=heads,
+                    head_dim=c // heads, q_len=n, kv_len=n, ldq=ld, ldk=ld, ldv=ld, ldo=c, scale=scale, lse=_ptr(lse))
+    _run("attention_bwd", _lib.load().afb_attention_bwd, C.byref(args), _ptr(dout), _ptr(ws), d.data_ptr(), d.data_ptr() + 4 * c,
+         d.data_ptr() + 8 * c, c3, _stream(), flops=10.0 * b * n * n * c, tag=f"b{b}q{n}k{n}d{c // heads}")
+    return d.to(torch.bfloat16)
+
+
+@self_attention_qkv_bwd.register_fake
+def _(qkv, out, lse, dout, heads, scale, key_mask=None):
+    return torch.empty_like(qkv, memory_format=torch.contiguous_format)
+
+
+def _self_attention_qkv_setup(ctx, inputs, output):
+    qkv, heads, scale = inputs[:3]
+    key_mask = inputs[3] if len(inputs) > 3 else None
+    out, lse = output
+    ctx.save_for_backward(qkv, out, lse, key_mask)
+    ctx.heads, ctx.scale = heads, scale
+
+
+def _self_attention_qkv_backward(ctx, g, g_lse):
+    qkv, out, lse, key_mask = ctx.saved_tensors
+    return self_attention_qkv_bwd(qkv, out, lse, _bf16c(g), ctx.heads, ctx.scale, key_mask).to(qkv.dtype), None, None, None
+
+
+self_attention_qkv.register_autograd(_self_attention_qkv_backward, setup_context=_self_attention_qkv_setup)
+
+
+def self_attention_auto(qkv: Tensor, heads: int, scale: float, key_mask: Optional[Tensor]) -> Tensor:
+    """Self-attention on the fused q | k | v buffer: `attention` on its column slices, or - while gradients are recorded
+    through it - `self_attention_qkv`, whose backward hands autograd one packed gradient."""
+    c = qkv.shape[2] // 3
+    if torch.is_grad_enabled() and qkv.requires_grad and qkv.shape[1] > 128:
+        return self_attention_qkv(qkv, heads, scale, key_mask)[0]
+    return attention_auto(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], heads, scale, key_mask)
+
+
 def _attention_lse_setup(ctx, inputs, output):
     q, k, v, heads, scale = inputs[:5]
     key_mask = inputs[5] if len(inputs) > 5 else None

@@ -282,6 +282,13 @@ def test_self_attention_backward(ops, cuda_device, c, nq):
     errs = [rel_l2(qd.grad[..., i * c:(i + 1) * c].float(), ref.grad[..., i * c:(i + 1) * c]) for i in range(3)]
     print(f"self-attention backward C={c} N={nq}: dq {errs[0]:.1e} dk {errs[1]:.1e} dv {errs[2]:.1e}")
     assert max(errs) < GRAD_TOL
+    # the fused-buffer op the modules use (ops.self_attention_qkv): same kernels, ONE packed gradient [B, N, 3C] written
+    # in place by the backward (row pitch 3C) instead of three sliced ones that autograd has to zero-fill and add
+    q2 = qkv.to(d).requires_grad_(True)
+    out2 = ops.self_attention_auto(q2, heads, scale, None)
+    assert torch.equal(out2, out)
+    out2.backward(go.to(d))
+    assert rel_l2(q2.grad.float(), ref.grad) < GRAD_TOL and rel_l2(q2.grad.float(), qd.grad.float()) < 2e-3
 
 
 @pytest.mark.parametrize("c,nq", [(320, 700), (640, 256)])
@@ -308,6 +315,9 @@ def test_self_attention_backward_with_key_mask(ops, cuda_device, c, nq):
     errs = [rel_l2(qd.grad[..., i * c:(i + 1) * c].float(), ref.grad[..., i * c:(i + 1) * c]) for i in range(3)]
     print(f"masked self-attention backward C={c} N={nq}: dq {errs[0]:.1e} dk {errs[1]:.1e} dv {errs[2]:.1e}")
     assert max(errs) < GRAD_TOL
+    q2 = qkv.to(d).requires_grad_(True)
+    ops.self_attention_auto(q2, heads, scale, mask.to(d)).backward(go.to(d))
+    assert rel_l2(q2.grad.float(), ref.grad) < GRAD_TOL
     g = qd.grad.float().cpu()
     assert float(g[2, :, :2 * c].abs().max()) == 0.0      # no gradient to q / k of the fully masked sample
     assert float(g[0, :, c:2 * c][~mask[0]].abs().max()) == 0.0      # nor to masked keys
