@@ -1031,12 +1031,14 @@ def _(infeat_fg, infeat_bg, time_emb, td, coeff_w, coeff_b, basis, grad_out, wan
         f(infeat_fg), f(infeat_bg)
 
 
-@torch.library.custom_op("adaface_b200::ada_pool_bwd", mutates_args=())
-def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor, d_bg: Tensor,
-                 drop_p: float = 0.0, seed: int = 0) -> Tensor:
-    """Backward of `ada_pool` w.r.t. the folded pooling queries: re-runs the forward for its softmax statistics and
-    pooled outputs, then one streaming pass over x and q -> d_pool_q fp32 [B, 2, C]."""
-    _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg)
+@torch.library.custom_op("adaface_b200::ada_pool_fwd_state", mutates_args=())
+def ada_pool_fwd_state(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], drop_p: float = 0.0,
+                       seed: int = 0) -> Tensor:
+    """What both pooler backwards need from the forward, in one fp32 vector: the merged softmax statistics (max, sum) per
+    (sample, head) [B * 16] followed by the pooled outputs fg [B, C] and bg [B, C].  One re-run of the pooling kernel per
+    layer and backward (the forward op does not return its statistics), shared by `ada_pool_bwd` and
+    `ada_pool_bwd_features`."""
+    _need_cuda(x, q, pool_q, key_mask)
     b, n, c = x.shape
     lib = _lib.load()
     dev = x.device
@@ -1045,12 +1047,43 @@ def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor
     if key_mask is not None:
         key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
     ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
-    fg = torch.empty((b, c), dtype=torch.float32, device=dev)
-    bg = torch.empty((b, c), dtype=torch.float32, device=dev)
+    state = torch.empty((b * 16 + 2 * b * c,), dtype=torch.float32, device=dev)
+    fg, bg = state[b * 16:b * 16 + b * c], state[b * 16 + b * c:]
     _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
          b, n, c, float(drop_p), int(seed) & 0xFFFFFFFF, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
     off = int(lib.afb_ada_pool_stats_offset(b, n, c))       # the forward's merged (max, sum) per (sample, head)
-    stats = ws[off:off + b * 16]
+    state[:b * 16].copy_(ws[off:off + b * 16])
+    return state
+
+
+@ada_pool_fwd_state.register_fake
+def _(x, q, pool_q, key_mask, drop_p=0.0, seed=0):
+    return x.new_empty((x.shape[0] * 16 + 2 * x.shape[0] * x.shape[2],), dtype=torch.float32)
+
+
+def _split_fwd_state(state: Tensor, b: int, c: int):
+    if state.dtype != torch.float32 or state.numel() != b * 16 + 2 * b * c or not state.is_contiguous():
+        raise ValueError("ada_pool backward: fwd_state must be the fp32 vector of ada_pool_fwd_state")
+    return state[:b * 16], state[b * 16:b * 16 + b * c], state[b * 16 + b * c:]
+
+
+@torch.library.custom_op("adaface_b200::ada_pool_bwd", mutates_args=())
+def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor, d_bg: Tensor,
+                 drop_p: float = 0.0, seed: int = 0, fwd_state: Optional[Tensor] = None) -> Tensor:
+    """Backward of `ada_pool` w.r.t. the folded pooling queries: needs the forward's softmax statistics and pooled outputs
+    (`fwd_state` from `ada_pool_fwd_state`, else the forward is re-run here), then one streaming pass over x and q ->
+    d_pool_q fp32 [B, 2, C]."""
+    _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg, fwd_state)
+    b, n, c = x.shape
+    lib = _lib.load()
+    dev = x.device
+    x, q = x.contiguous(), q.contiguous()
+    pool_q = pool_q.detach().to(torch.float32).contiguous()
+    if key_mask is not None:
+        key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
+    if fwd_state is None:
+        fwd_state = ada_pool_fwd_state(x, q, pool_q, key_mask, drop_p, seed)
+    stats, fg, bg = _split_fwd_state(fwd_state, b, c)
     d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
     d_pool_q = torch.empty((b, 2, c), dtype=torch.float32, device=dev)
     _run("ada_pool_bwd", lib.afb_ada_pool_bwd, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats), _ptr(fg), _ptr(bg),
@@ -1060,7 +1093,7 @@ def ada_pool_bwd(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor
 
 
 @ada_pool_bwd.register_fake
-def _(x, q, pool_q, key_mask, d_fg, d_bg, drop_p=0.0, seed=0):
+def _(x, q, pool_q, key_mask, d_fg, d_bg, drop_p=0.0, seed=0, fwd_state=None):
     return x.new_empty((x.shape[0], 2, x.shape[2]), dtype=torch.float32)
 
 
@@ -1476,9 +1509,10 @@ add_bias_residual.register_autograd(_abr_backward, setup_context=_abr_setup)
 
 @torch.library.custom_op("adaface_b200::ada_pool_bwd_features", mutates_args=())
 def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Optional[Tensor], d_fg: Tensor,
-                          d_bg: Tensor, drop_p: float = 0.0, seed: int = 0) -> Tuple[Tensor, Tensor]:
-    """Backward of `ada_pool` towards the layer features: -> (dx, dq) bf16 [B, N, C]."""
-    _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg)
+                          d_bg: Tensor, drop_p: float = 0.0, seed: int = 0,
+                          fwd_state: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+    """Backward of `ada_pool` towards the layer features: -> (dx, dq) bf16 [B, N, C] (`fwd_state` as in `ada_pool_bwd`)."""
+    _need_cuda(x, q, pool_q, key_mask, d_fg, d_bg, fwd_state)
     b, n, c = x.shape
     lib = _lib.load()
     dev = x.device
@@ -1486,13 +1520,9 @@ def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Option
     pool_q = pool_q.detach().to(torch.float32).contiguous()
     if key_mask is not None:
         key_mask = key_mask.reshape(b, n).to(torch.uint8).contiguous()
-    ws = torch.empty(int(lib.afb_ada_pool_ws_floats(b, n, c)), dtype=torch.float32, device=dev)
-    fg = torch.empty((b, c), dtype=torch.float32, device=dev)
-    bg = torch.empty((b, c), dtype=torch.float32, device=dev)
-    _run("ada_pool", lib.afb_ada_pool, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(fg), _ptr(bg), None, None, _ptr(ws),
-         b, n, c, float(drop_p), int(seed) & 0xFFFFFFFF, _stream(), nbytes=4.0 * b * n * c, tag=f"b{b}n{n}C{c}")
-    off = int(lib.afb_ada_pool_stats_offset(b, n, c))       # the forward's merged (max, sum) per (sample, head)
-    stats = ws[off:off + b * 16]
+    if fwd_state is None:
+        fwd_state = ada_pool_fwd_state(x, q, pool_q, key_mask, drop_p, seed)
+    stats, fg, bg = _split_fwd_state(fwd_state, b, c)
     d_fg, d_bg = d_fg.detach().to(torch.float32).contiguous(), d_bg.detach().to(torch.float32).contiguous()
     dx, dq = torch.empty_like(x), torch.empty_like(q)
     _run("ada_pool_bwd_features", lib.afb_ada_pool_bwd_features, _ptr(x), _ptr(q), _ptr(pool_q), _ptr(key_mask), _ptr(stats),
@@ -1502,7 +1532,7 @@ def ada_pool_bwd_features(x: Tensor, q: Tensor, pool_q: Tensor, key_mask: Option
 
 
 @ada_pool_bwd_features.register_fake
-def _(x, q, pool_q, key_mask, d_fg, d_bg, drop_p=0.0, seed=0):
+def _(x, q, pool_q, key_mask, d_fg, d_bg, drop_p=0.0, seed=0, fwd_state=None):
     return torch.empty_like(x), torch.empty_like(q)
 
 
@@ -1517,10 +1547,11 @@ def _ada_pool_backward2(ctx, g_fg, g_bg, g_afg, g_abg):
     x, q, pool_q, key_mask = ctx.saved_tensors
     z = lambda g: torch.zeros((x.shape[0], x.shape[2]), dtype=torch.float32, device=x.device) if g is None else g
     g_fg, g_bg = z(g_fg), z(g_bg)
-    d_pq = ada_pool_bwd(x, q, pool_q, key_mask, g_fg, g_bg, ctx.drop_p, ctx.seed) if ctx.q_needs else None
+    state = ada_pool_fwd_state(x, q, pool_q.detach(), key_mask, ctx.drop_p, ctx.seed) if (ctx.q_needs or ctx.feat_needs) else None
+    d_pq = ada_pool_bwd(x, q, pool_q, key_mask, g_fg, g_bg, ctx.drop_p, ctx.seed, state) if ctx.q_needs else None
     dx = dq = None
     if ctx.feat_needs:
-        dx, dq = ada_pool_bwd_features(x, q, pool_q, key_mask, g_fg, g_bg, ctx.drop_p, ctx.seed)
+        dx, dq = ada_pool_bwd_features(x, q, pool_q, key_mask, g_fg, g_bg, ctx.drop_p, ctx.seed, state)
     return dx, dq, d_pq, None, None, None, None
 
 
