@@ -297,7 +297,8 @@ class Downsample(nn.Module):
 
 
 class ResBlock(TimestepBlock):
-    """openaimodel.py:167-281 without up/down and scale-shift norm (SD-1.5 uses neither).  torch path."""
+    """openaimodel.py:167-281 without up/down and scale-shift norm (SD-1.5 uses neither): fused GroupNorm + SiLU, implicit-GEMM
+    convolutions with the skip / bias tails in their epilogues; differentiable through the same kernels (dX only)."""
 
     def __init__(self, channels: int, emb_channels: int, dropout: float, out_channels: Optional[int] = None, **_):
         super().__init__()

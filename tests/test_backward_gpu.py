@@ -8,7 +8,8 @@ whole frozen U-Net.
 Measured on B200: AdaEmbedding parameter gradients 3e-8..7e-7 (fp32 kernels); block-level inversion step 4.7e-3..7.8e-3
 on every trained tensor; self-attention dQ / dK / dV 1.7e-3; whole-U-Net step: flat gradient of the 3.81 M trained values
 rel-L2 1.2e-2, cosine 0.99993 (worst single tensor 2.5e-2 after 25 bf16 blocks forward and backward).
-ResBlocks / resampling / output head differentiate through torch (outside the path).  Also covered: the key-masked
+The ResBlocks differentiate through this repo's kernels too (GroupNorm + SiLU backward, dX convolutions: dX 2.5e-3..3.5e-3);
+resampling / input / output convolutions differentiate through torch (outside the path).  Also covered: the key-masked
 self-attention backward (incl. a fully masked sample) and the AttentionalPooler's train-mode Dropout(0.1)."""
 import math
 
@@ -377,7 +378,8 @@ def test_inversion_step_through_the_whole_unet(cuda_device):
     (ddpm.py:3567-3591 with unit masks), frozen SD-1.5 U-Net, gradients on the AdaEmbedding parameters of all 16 layers
     against fp32 autograd through the port's composed U-Net.  The gradient crosses every kernel of the path backwards:
     GEMM dX, folded LayerNorms, GEGLU, self- and cross-attention, GroupNorm, the pooler (towards its queries AND the layer
-    features) and the AdaEmbedding head; ResBlocks / resampling differentiate through torch (outside the path)."""
+    features), the AdaEmbedding head, and the ResBlocks' GroupNorm + SiLU / dX convolutions; resampling differentiates through torch
+    (outside the path).  The same step is then replayed as one CUDA graph (sampling.CapturedGradStep)."""
     import adaface_b200 as afb
     from adaface_b200.unet import SD15_UNET_CONFIG, AdaPromptContext, AdaSubject, UNetModel
     d = cuda_device
