@@ -7,6 +7,7 @@ fallback - a non-CUDA tensor or a missing library raises.
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -1459,15 +1460,16 @@ _CONV_DX_W = {}
 
 def conv3x3_dx_weight(w: Tensor) -> Tensor:
     key = (w.data_ptr(), w._version, tuple(w.shape))
-    c = _CONV_DX_W.get(key)
-    if c is None:
-        cout, k9 = w.shape
-        cin = k9 // 9
-        with torch.no_grad():
-            c = w.detach().view(cout, 3, 3, cin).flip(1, 2).permute(3, 1, 2, 0).reshape(cin, 9 * cout).contiguous()
-        if len(_CONV_DX_W) > 256:
-            _CONV_DX_W.clear()
-        _CONV_DX_W[key] = c
+    hit = _CONV_DX_W.get(key)
+    if hit is not None and hit[0]() is w:          # the same tensor object, not a new one that reuses the address
+        return hit[1]
+    cout, k9 = w.shape
+    cin = k9 // 9
+    with torch.no_grad():
+        c = w.detach().view(cout, 3, 3, cin).flip(1, 2).permute(3, 1, 2, 0).reshape(cin, 9 * cout).contiguous()
+    if len(_CONV_DX_W) > 256:
+        _CONV_DX_W.clear()
+    _CONV_DX_W[key] = (weakref.ref(w), c)
     return c
 
 

@@ -274,6 +274,27 @@ def test_inversion_gradient_allreduce_world_size_2_gloo(tmp_path):
         assert torch.allclose(r0["grads"][i], want, atol=1e-6) and torch.equal(r0["grads"][i], r1["grads"][i])
 
 
+def test_conv3x3_dx_weight_is_the_transposed_flipped_filter():
+    """ops.conv3x3's backward runs the forward kernel on `conv3x3_dx_weight(w)`: check on CPU, with torch's own conv2d
+    and autograd, that this matrix ([Cin, 9*Cout], taps flipped) is the filter whose convolution is dX; the result is cached
+    per weight TENSOR (a new tensor at a reused address must not hit)."""
+    import torch.nn.functional as F
+    from adaface_b200 import ops
+    cout, cin = 64, 128
+    w = torch.randn(cout, 9 * cin).to(torch.bfloat16)                       # [Cout, (ky, kx, c)] as _Bf16Conv._w_native packs it
+    wt = ops.conv3x3_dx_weight(w)
+    assert wt.shape == (cin, 9 * cout) and ops.conv3x3_dx_weight(w) is wt
+    W = w.float().view(cout, 3, 3, cin).permute(0, 3, 1, 2)
+    x = torch.randn(2, cin, 6, 5, requires_grad=True)
+    y = F.conv2d(x, W, padding=1)
+    g = torch.randn_like(y)
+    y.backward(g)
+    dx = F.conv2d(g, wt.float().view(cin, 3, 3, cout).permute(0, 3, 1, 2), padding=1)
+    assert torch.allclose(dx, x.grad, atol=1e-3, rtol=1e-4)
+    w2 = w.clone()
+    assert ops.conv3x3_dx_weight(w2) is not wt
+
+
 def test_captured_grad_step_fails_loudly_without_cuda_or_attached_gradients():
     """sampling.CapturedGradStep (the inversion step as one CUDA graph) has no CPU counterpart and needs every .grad to be
     a view of the all-reduce's flat buffer: both are errors, not silent fallbacks."""
