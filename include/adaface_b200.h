@@ -307,7 +307,7 @@ int afb_splice_static_embedding(const float* embedded_text, const int* first_pos
  *   bf16 [rows, C], add = NULL or bf16 [rows, C] (gradient arriving along the residual stream) -> da bf16.
  * afb_attention_bwd_short: kv_len <= 128 (d = 160: <= 80), no key mask - the 77-token cross-attention.  args as in
  *   afb_attention_fwd (`out` unused), dout bf16 [B*q_len, ldo]; dq bf16 [B*q_len, lddq] or NULL; dk, dv fp32
- *   [B*kv_len, lddk] "+=".  The self-attention backward (long key sequences) is not built: the call fails with code 2.
+ *   [B*kv_len, lddk] "+=".  Up to 80 keys run on warp-level tensor-core MMAs, longer ones on CUDA cores (see afb_attention_bwd for self-attention).
  * afb_ada_head_bwd: grad_out fp32 [B, K, D] -> d_coeff_w [K*r, 2C+TD], d_coeff_b [K*r], d_basis [K, r, D], d_bias [K, D]
  *   or NULL (all "+="), d_infeat_fg / d_infeat_bg fp32 [B, C] (written); d_feat_ws: fp32 workspace [B, 2C+TD].
  * afb_ada_pool_bwd: gradient of the pooled features w.r.t. the folded pooling queries: stats fp32 [B, 8, 2] = the
